@@ -1,0 +1,166 @@
+/*
+ * netsdb_b200.h -- C ABI of libnetsdb_b200.so, the B200 (sm_100a) implementation of netsDB's
+ * in-database DNN inference hot path (src/FF, src/conv2d_memory_fusion, word2vec block join).
+ *
+ * Plain C types only: pointers, sizes, ints.  All host pointers are caller-owned and are never
+ * retained after a call returns.  Every function returns 0 (NB200_OK) on success or an
+ * nb200_status code; nb200_last_error() returns a thread-local description of the last failure,
+ * which the host wrappers turn into the reference's `false + errMsg` / print-and-exit(1)
+ * convention.
+ *
+ * There is no CPU fallback: if no sm_100 device is present nb200_init fails.
+ *
+ * Paths in the citations are relative to the netsDB tree (venkate5hgunda/netsdb).
+ */
+#ifndef NETSDB_B200_H
+#define NETSDB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    NB200_OK = 0,
+    NB200_ERR_INVALID = 1, /* bad argument                                            */
+    NB200_ERR_CUDA = 2,    /* a CUDA runtime/driver call failed                       */
+    NB200_ERR_SHAPE = 3,   /* "Block dimemsions mismatch!" (FFTransposeMult.h:61-65)  */
+    NB200_ERR_NOMEM = 4,
+    NB200_ERR_STATE = 5,   /* not initialised / set missing a needed representation   */
+    NB200_ERR_KERNEL = 6   /* a kernel reported an internal fault (e.g. pipeline wait timed out) */
+} nb200_status;
+
+/* Join flavour: which reference JoinComp the block GEMM replaces. */
+typedef enum {
+    NB200_OP_NT = 0, /* FFTransposeMult  (FFTransposeMult.h:38-39,80-92): C(i,j) = sum_k A(i,k) B(j,k)^T */
+    NB200_OP_NN = 1  /* FFInputLayerJoin (FFInputLayerJoin.h:30-31,72-86): C(i,j) = sum_k A(i,k) B(k,j)  */
+} nb200_op;
+
+/* What is fused after the aggregation. */
+typedef enum {
+    NB200_EPI_NONE = 0,
+    NB200_EPI_BIAS_RELU = 1,     /* FFReluBiasSum (FFReluBiasSum.h:63-71): max(0, C[i,j] + bias[i]), dropout 0 */
+    NB200_EPI_BIAS_TRANSPOSE = 2 /* FFTransposeBiasSum intended form (FFTransposeBiasSum.h:64-104):
+                                    out = (C[i,j] + bias[i])^T; the exp() is applied by nb200_softmax_rows /
+                                    on download of the `yo` view so that the device never overflows */
+} nb200_epilogue;
+
+/* Arithmetic of the block GEMM.  The reference is fp64 end to end (FFMatrixData.h:35-36). */
+typedef enum {
+    NB200_PREC_BF16 = 0,   /* one tcgen05 kind::f16 pass, bf16 operands, fp32 TMEM accumulation        */
+    NB200_PREC_BF16X3 = 1, /* bf16 hi/lo split, 3 passes (hi*hi + hi*lo + lo*hi), ~fp32-grade products   */
+    NB200_PREC_FP64 = 2    /* exact-path DFMA kernel (also used to re-evaluate near-tie rows)            */
+} nb200_precision;
+
+/* Opaque handle on a device-resident user set of FFMatrixBlocks (db, set) -- the counterpart of
+ * what ScanUserSet<FFMatrixBlock>(db, set) scans (builtInPDBObjects/headers/ScanUserSet.h:53-58).
+ * On the device the blocks of a set are de-blocked into one dense matrix. */
+typedef struct nb200_set nb200_set;
+
+/* Counters filled by nb200_ff_inference_unit. */
+typedef struct {
+    float ms_convert;     /* fp64 -> bf16 plane conversion of `inputs`              */
+    float ms_gemm1;       /* layer-1 block GEMM incl. split-K reduction + bias/relu */
+    float ms_gemm2;       /* layer-2 block GEMM + bias                              */
+    float ms_softmax;     /* row softmax / argmax / near-tie scan                   */
+    float ms_refine;      /* fp64 re-evaluation of near-tie rows                    */
+    float ms_total;
+    float ms_gemm1_kernel; /* the tcgen05 kernel of layer 1 alone                   */
+    int refined_rows;     /* rows re-evaluated in fp64                              */
+    int kernel_launches;  /* kernels launched by this call                          */
+    int splits1;          /* split-K factor used by layer 1                         */
+} nb200_ff_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+/* Bind the calling process to CUDA device `device` (lazily creates the context; call after
+ * fork(), cf. mainServer/source/WorkerMain.cc:107).  Idempotent for the same device. */
+int nb200_init(int device);
+int nb200_shutdown(void);
+const char *nb200_last_error(void);
+int nb200_device_count(int *count);
+/* Launch everything on `cuda_stream` (a cudaStream_t) instead of the library's own stream. */
+int nb200_set_stream(void *cuda_stream);
+int nb200_synchronize(void);
+/* Number of kernels this library has launched since nb200_init (monotonic). */
+int64_t nb200_launch_count(void);
+
+/* Page-lock a host range so block uploads/downloads run as async DMA -- the shared-memory
+ * buffer pool of memory/source/SharedMem.cc:128 or any client allocation block. */
+int nb200_pin_pool(void *base, size_t bytes);
+int nb200_unpin_pool(void *base);
+
+/* ---- sets ------------------------------------------------------------------------------------ */
+/* PDBClient::createSet<FFMatrixBlock>(db, set, ...) (mainClient/headers/PDBClient.h:74-259).
+ * total_* are FFMatrixMeta::totalRows/totalCols, block_* the nominal FFMatrixData::rowNums/colNums. */
+int nb200_set_create(const char *db, const char *set, int total_rows, int total_cols, int block_rows,
+                     int block_cols, nb200_set **out);
+int nb200_set_lookup(const char *db, const char *set, nb200_set **out);
+int nb200_set_destroy(nb200_set *s); /* PDBClient::removeSet */
+int nb200_set_info(const nb200_set *s, int *total_rows, int *total_cols, int *block_rows, int *block_cols);
+
+/* PDBClient::sendData<FFMatrixBlock> for one block: `host` is FFMatrixData::rawData->c_ptr(),
+ * row-major rows x cols (full-size zero-padded edge blocks as ff::loadMatrix builds them,
+ * FFMatrixUtil.cc:245-302, or trimmed ones).  Padding beyond totalRows/totalCols is dropped. */
+int nb200_upload_block(nb200_set *s, int block_row, int block_col, const double *host, int rows, int cols);
+/* Arbitrary rectangle (row-granular sharding across GPUs): element (r,c) of the rectangle is
+ * host[r*ld + c] and lands at (row0 + r, col0 + c) of the set. */
+int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int rows, int cols, int64_t ld);
+/* getSetIterator<FFMatrixBlock> for one block: fills a rows x cols row-major block, zero padded
+ * outside the set's totals (queries/headers/SetIterator.h:12-68). */
+int nb200_download_block(nb200_set *s, int block_row, int block_col, double *host, int rows, int cols);
+int nb200_download_rect(nb200_set *s, int row0, int col0, double *host, int rows, int cols, int64_t ld);
+/* Seeded device-side stand-in for ff::loadMatrix's value distribution (FFMatrixUtil.cc:229-237):
+ * element (r,c) = synth(seed, (row_offset + r) * total_cols + c).  Bit-identical to the CPU oracle's
+ * generator.  row_offset lets a row shard reproduce its slice of a larger matrix. */
+int nb200_set_fill_synth(nb200_set *s, uint64_t seed, int64_t row_offset);
+/* Drop the derived bf16 operand planes of a set (they are rebuilt from the fp64 data on next use). */
+int nb200_set_invalidate_planes(nb200_set *s);
+
+/* ---- operators ------------------------------------------------------------------------------- */
+/* JoinComp + ClusterAggregateComp as ONE block GEMM: FFTransposeMult|FFInputLayerJoin followed by
+ * FFAggMatrix (FFAggMatrix.h:11-35; ClusterAggregateComp.h:40-344), optionally with the next
+ * bias join fused.  The K-block partial products are accumulated inside the kernel (fp32 TMEM /
+ * split-K workspace), never materialised per pair.  Result set (db, out_set) is created (or
+ * replaced); its meta follow the reference (FFTransposeMult.h:68-71, FFInputLayerJoin.h:64-67,
+ * FFTransposeBiasSum.h:64-67).  `bias` must be (rows of C) x 1 (FFReluBiasSum.h:49-56). */
+int nb200_gemm_blocks(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision,
+                      const char *db, const char *out_set, nb200_set **out);
+
+/* FFRowAggregate + FFOutputLayer (FFRowAggregate.h:11-29, FFMatrixBlock.h:116-142,
+ * FFOutputLayer.h:31-57 intended form) on a set of pre-exp logits (batch x labels):
+ * out[i,j] = exp(z[i,j]) / sum_j exp(z[i,j]), evaluated in the max-subtracted form.
+ * labels_host (optional, length = rows) receives the first row argmax of z. */
+int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, nb200_set **out,
+                       int32_t *labels_host);
+
+/* The whole of ff::inference_unit (FF/source/SimpleFF.cc:331-424) as one fused stage:
+ * y1 = relu(w1 . inputs^T + b1); z = (wo . y1 + bo)^T; output = softmax_rows(z).
+ * Creates sets (db, "yo") [a view: exp(z)] and (db, out_set).  With a tensor-core precision, rows
+ * whose top-2 logit gap is inside the low-precision error band are re-evaluated in fp64 so that
+ * labels equal the fp64 pipeline's.  labels_host (optional) gets one int32 per input row. */
+int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb200_set *b1, nb200_set *bo,
+                            int precision, const char *db, const char *out_set, nb200_set **out,
+                            int32_t *labels_host, nb200_ff_stats *stats);
+
+/* ---- conv2d_memory_fusion ---------------------------------------------------------------------- */
+/* Image set -> `image_flat` (Image.h:26-57, ImageToChunks.h:43-102, ImageChunksToBlock.h:35-50,
+ * ImageBlockToMatrix.h:46-73): rows img*windows+win, cols ch*k*k+i*k+j plus a trailing 1.0 column.
+ * images_host: n x c x h x w row-major fp64. */
+int nb200_conv2d_image_flat(const double *images_host, int n, int c, int h, int w, int k, int stride, int padding,
+                            int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out);
+/* Kernel set (+ bias) -> `kernel_flat` (KernelToChunks.h:39-83, KernelBiasJoin.h:42-46). */
+int nb200_conv2d_kernel_flat(const double *kernels_host, const double *bias_host, int kout, int c, int k,
+                             int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out);
+/* The `conv2d` job of PipelinedConv2dMemFuseTest.cc:249-273 (FFTransposeMult + FFAggMatrix on
+ * image_flat x kernel_flat) without materialising image_flat: implicit-GEMM over the image.
+ * result[(img, ho, wo), cout] = conv + bias, optional ReLU (config C4).  Stride 1. */
+int nb200_conv2d_fused(const double *images_host, int n, int c, int h, int w, const double *kernels_host,
+                       const double *bias_host, int kout, int k, int padding, int relu, int precision,
+                       int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,739 @@
+// nb200_api.cu -- the extern "C" boundary of libnetsdb_b200.so (see include/netsdb_b200.h):
+// context, device block sets, block upload/download (de-blocking on the way in, re-blocking on
+// the way out), the fused operators and the fused ff::inference_unit stage.
+#include "nb200_internal.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace nb200 {
+
+static thread_local char g_err[1024] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static Context *g_ctx = nullptr;
+static std::mutex g_mu;
+static std::map<std::pair<std::string, std::string>, nb200_set *> g_sets;
+
+Context *ctx() { return g_ctx; }
+
+int ensure_ws(Context *c, size_t bytes) {
+    if (bytes <= c->ws_bytes) return NB200_OK;
+    if (c->ws) {
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        cudaFree(c->ws);
+        c->ws = nullptr;
+        c->ws_bytes = 0;
+    }
+    NB_CUDA(cudaMalloc(&c->ws, bytes));
+    c->ws_bytes = bytes;
+    return NB200_OK;
+}
+
+static int ensure_stage(Context *c, size_t bytes) {
+    if (bytes <= c->stage_bytes) return NB200_OK;
+    if (c->stage) {
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        cudaFree(c->stage);
+        c->stage = nullptr;
+        c->stage_bytes = 0;
+    }
+    NB_CUDA(cudaMalloc(&c->stage, bytes));
+    c->stage_bytes = bytes;
+    return NB200_OK;
+}
+
+int check_kernel_fault(Context *c, const char *what) {
+    NB_CUDA(cudaMemcpyAsync(c->err_flag_host, c->err_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    if (*c->err_flag_host != 0) {
+        const int code = *c->err_flag_host;
+        cudaMemsetAsync(c->err_flag, 0, sizeof(int), c->stream);
+        set_error("%s: kernel fault %d (101 TMA producer / 102 MMA issuer / 103 epilogue timed out on a pipeline barrier)",
+                  what, code);
+        return NB200_ERR_KERNEL;
+    }
+    return NB200_OK;
+}
+
+static void free_planes(Planes *p) {
+    cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
+    *p = Planes();
+}
+
+static void free_set_storage(nb200_set *s) {
+    cudaFree(s->f64); s->f64 = nullptr;
+    cudaFree(s->f32); s->f32 = nullptr;
+    cudaFree(s->wo_rownorm_max); s->wo_rownorm_max = nullptr;
+    free_planes(&s->rowp);
+    free_planes(&s->colp);
+}
+
+#define NEED_CTX()                                              \
+    Context *c = ::nb200::ctx();                                \
+    if (!c) {                                                   \
+        ::nb200::set_error("nb200_init has not been called");   \
+        return NB200_ERR_STATE;                                 \
+    }
+
+// ---- derived representations ------------------------------------------------------------------
+static int ensure_f64(Context *c, nb200_set *s) {
+    if (s->f64) return NB200_OK;
+    const size_t n = static_cast<size_t>(s->total_rows) * s->total_cols;
+    NB_CUDA(cudaMalloc(&s->f64, (n ? n : 1) * sizeof(double)));
+    NB_CUDA(cudaMemsetAsync(s->f64, 0, (n ? n : 1) * sizeof(double), c->stream));
+    return NB200_OK;
+}
+static int ensure_f32(Context *c, nb200_set *s) {
+    if (s->f32) return NB200_OK;
+    if (!s->f64) { set_error("set %s:%s holds no data", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
+    const size_t n = static_cast<size_t>(s->total_rows) * s->total_cols;
+    NB_CUDA(cudaMalloc(&s->f32, (n ? n : 1) * sizeof(float)));
+    s->f32_ld = s->total_cols;
+    return launch_f64_to_f32(c, s->f64, static_cast<int64_t>(n), s->f32);
+}
+static int ensure_rowp(Context *c, nb200_set *s, bool want_lo) {
+    if (s->rowp.valid && (!want_lo || s->rowp.lo_valid)) return NB200_OK;
+    if (s->f64) return launch_convert_planes(c, s->f64, true, s->total_rows, s->total_cols, s->total_cols, &s->rowp, want_lo);
+    if (s->f32) return launch_convert_planes(c, s->f32, false, s->total_rows, s->total_cols, s->f32_ld, &s->rowp, want_lo);
+    set_error("set %s:%s holds no data", s->db.c_str(), s->name.c_str());
+    return NB200_ERR_STATE;
+}
+static int ensure_colp(Context *c, nb200_set *s, bool want_lo) {
+    if (s->colp.valid && (!want_lo || s->colp.lo_valid)) return NB200_OK;
+    if (s->f64) return launch_convert_planes_t(c, s->f64, true, s->total_rows, s->total_cols, s->total_cols, &s->colp, want_lo);
+    if (s->f32) return launch_convert_planes_t(c, s->f32, false, s->total_rows, s->total_cols, s->f32_ld, &s->colp, want_lo);
+    set_error("set %s:%s holds no data", s->db.c_str(), s->name.c_str());
+    return NB200_ERR_STATE;
+}
+
+static int make_set(const char *db, const char *name, int tr, int tc, int br, int bc, nb200_set **out) {
+    if (!db || !name || tr < 0 || tc < 0 || br <= 0 || bc <= 0) {
+        set_error("set_create: invalid arguments (total %d x %d, block %d x %d)", tr, tc, br, bc);
+        return NB200_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto key = std::make_pair(std::string(db), std::string(name));
+    auto it = g_sets.find(key);
+    nb200_set *s;
+    if (it != g_sets.end()) {  // createSet on an existing set: replace its contents
+        s = it->second;
+        free_set_storage(s);
+    } else {
+        s = new nb200_set();
+        g_sets[key] = s;
+    }
+    s->db = db; s->name = name;
+    s->total_rows = tr; s->total_cols = tc; s->block_rows = br; s->block_cols = bc;
+    s->view_exp = false; s->view_of = nullptr;
+    *out = s;
+    return NB200_OK;
+}
+
+static float prec_unit(int precision) {
+    // unit of the relative rounding error of one product (DESIGN.md "error model")
+    return precision == NB200_PREC_BF16 ? 0.00390625f /* 2^-8 */ : 0.0001220703125f /* 2^-13 */;
+}
+
+}  // namespace nb200
+
+using namespace nb200;
+
+extern "C" {
+
+const char *nb200_last_error(void) { return g_err; }
+
+int nb200_device_count(int *count) {
+    if (!count) return NB200_ERR_INVALID;
+    NB_CUDA(cudaGetDeviceCount(count));
+    return NB200_OK;
+}
+
+int nb200_init(int device) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_ctx) {
+        if (g_ctx->device == device) return NB200_OK;
+        set_error("nb200_init: already bound to device %d (one device per process)", g_ctx->device);
+        return NB200_ERR_STATE;
+    }
+    int n = 0;
+    NB_CUDA(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) {
+        set_error("nb200_init: device %d out of range (%d visible); there is no CPU fallback", device, n);
+        return NB200_ERR_INVALID;
+    }
+    NB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    NB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("nb200_init: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+        return NB200_ERR_STATE;
+    }
+    Context *c = new Context();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    NB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    NB_CUDA(cudaMalloc(&c->err_flag, sizeof(int)));
+    NB_CUDA(cudaMemset(c->err_flag, 0, sizeof(int)));
+    NB_CUDA(cudaMallocHost(&c->err_flag_host, sizeof(int)));
+    for (auto &e : c->ev) NB_CUDA(cudaEventCreate(&e));
+    g_ctx = c;
+    return NB200_OK;
+}
+
+int nb200_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_ctx) return NB200_OK;
+    cudaStreamSynchronize(g_ctx->stream);
+    for (auto &kv : g_sets) {
+        free_set_storage(kv.second);
+        delete kv.second;
+    }
+    g_sets.clear();
+    cudaFree(g_ctx->ws);
+    cudaFree(g_ctx->stage);
+    cudaFree(g_ctx->err_flag);
+    cudaFreeHost(g_ctx->err_flag_host);
+    for (auto &e : g_ctx->ev) cudaEventDestroy(e);
+    cudaStreamDestroy(g_ctx->own_stream);
+    delete g_ctx;
+    g_ctx = nullptr;
+    return NB200_OK;
+}
+
+int nb200_set_stream(void *cuda_stream) {
+    NEED_CTX();
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : c->own_stream;
+    return NB200_OK;
+}
+
+int nb200_synchronize(void) {
+    NEED_CTX();
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB200_OK;
+}
+
+int64_t nb200_launch_count(void) { return g_ctx ? g_ctx->launches : 0; }
+
+int nb200_pin_pool(void *base, size_t bytes) {
+    NEED_CTX();
+    (void)c;
+    NB_CUDA(cudaHostRegister(base, bytes, cudaHostRegisterPortable));
+    return NB200_OK;
+}
+int nb200_unpin_pool(void *base) {
+    NEED_CTX();
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    NB_CUDA(cudaHostUnregister(base));
+    return NB200_OK;
+}
+
+// ---- sets ---------------------------------------------------------------------------------------
+int nb200_set_create(const char *db, const char *set, int total_rows, int total_cols, int block_rows, int block_cols,
+                     nb200_set **out) {
+    NEED_CTX();
+    (void)c;
+    if (!out) return NB200_ERR_INVALID;
+    return make_set(db, set, total_rows, total_cols, block_rows, block_cols, out);
+}
+
+int nb200_set_lookup(const char *db, const char *set, nb200_set **out) {
+    if (!db || !set || !out) return NB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_sets.find(std::make_pair(std::string(db), std::string(set)));
+    if (it == g_sets.end()) {
+        set_error("set %s:%s does not exist", db, set);
+        return NB200_ERR_STATE;
+    }
+    *out = it->second;
+    return NB200_OK;
+}
+
+int nb200_set_destroy(nb200_set *s) {
+    NEED_CTX();
+    if (!s) return NB200_ERR_INVALID;
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (auto &kv : g_sets)
+        if (kv.second->view_of == s) kv.second->view_of = nullptr;
+    g_sets.erase(std::make_pair(s->db, s->name));
+    free_set_storage(s);
+    delete s;
+    return NB200_OK;
+}
+
+int nb200_set_info(const nb200_set *s, int *total_rows, int *total_cols, int *block_rows, int *block_cols) {
+    if (!s) return NB200_ERR_INVALID;
+    if (total_rows) *total_rows = s->total_rows;
+    if (total_cols) *total_cols = s->total_cols;
+    if (block_rows) *block_rows = s->block_rows;
+    if (block_cols) *block_cols = s->block_cols;
+    return NB200_OK;
+}
+
+static void drop_derived(nb200_set *s) {
+    s->rowp.valid = s->rowp.lo_valid = false;
+    s->colp.valid = s->colp.lo_valid = false;
+    if (s->f64 && s->f32) { cudaFree(s->f32); s->f32 = nullptr; }
+}
+
+int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int rows, int cols, int64_t ld) {
+    NEED_CTX();
+    if (!s || !host || row0 < 0 || col0 < 0 || rows < 0 || cols < 0 || ld < cols) {
+        set_error("upload: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    if (s->view_of) { set_error("upload: %s:%s is a read-only view", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
+    NB_TRY(ensure_f64(c, s));
+    const int vr = std::min(rows, s->total_rows - row0), vc = std::min(cols, s->total_cols - col0);
+    drop_derived(s);
+    if (vr <= 0 || vc <= 0) return NB200_OK;  // a block that is all padding
+    NB_CUDA(cudaMemcpy2DAsync(s->f64 + static_cast<size_t>(row0) * s->total_cols + col0,
+                              static_cast<size_t>(s->total_cols) * sizeof(double), host,
+                              static_cast<size_t>(ld) * sizeof(double), static_cast<size_t>(vc) * sizeof(double), vr,
+                              cudaMemcpyHostToDevice, c->stream));
+    return NB200_OK;
+}
+
+int nb200_upload_block(nb200_set *s, int block_row, int block_col, const double *host, int rows, int cols) {
+    if (!s || block_row < 0 || block_col < 0) {
+        set_error("upload_block: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    return nb200_upload_rect(s, block_row * s->block_rows, block_col * s->block_cols, host, rows, cols, cols);
+}
+
+int nb200_download_rect(nb200_set *s, int row0, int col0, double *host, int rows, int cols, int64_t ld) {
+    NEED_CTX();
+    if (!s || !host || row0 < 0 || col0 < 0 || rows < 0 || cols < 0 || ld < cols) {
+        set_error("download: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    nb200_set *src = s->view_of ? s->view_of : s;
+    const int vr = std::max(0, std::min(rows, s->total_rows - row0)), vc = std::max(0, std::min(cols, s->total_cols - col0));
+    if (rows == 0 || cols == 0) return NB200_OK;
+    if (src->f64 && !s->view_exp) {
+        if (vr < rows || vc < cols)
+            for (int r = 0; r < rows; r++) memset(host + static_cast<size_t>(r) * ld, 0, static_cast<size_t>(cols) * sizeof(double));
+        if (vr > 0 && vc > 0)
+            NB_CUDA(cudaMemcpy2DAsync(host, static_cast<size_t>(ld) * sizeof(double),
+                                      src->f64 + static_cast<size_t>(row0) * src->total_cols + col0,
+                                      static_cast<size_t>(src->total_cols) * sizeof(double),
+                                      static_cast<size_t>(vc) * sizeof(double), vr, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        return NB200_OK;
+    }
+    if (!src->f32) { set_error("download: set %s:%s holds no data", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
+    NB_TRY(ensure_stage(c, static_cast<size_t>(rows) * cols * sizeof(double)));
+    NB_TRY(launch_extract_f32_to_f64(c, src->f32, src->f32_ld, row0, col0, rows, cols, vr, vc, c->stage, cols, s->view_exp ? 1 : 0));
+    NB_CUDA(cudaMemcpy2DAsync(host, static_cast<size_t>(ld) * sizeof(double), c->stage, static_cast<size_t>(cols) * sizeof(double),
+                              static_cast<size_t>(cols) * sizeof(double), rows, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB200_OK;
+}
+
+int nb200_download_block(nb200_set *s, int block_row, int block_col, double *host, int rows, int cols) {
+    if (!s || block_row < 0 || block_col < 0) {
+        set_error("download_block: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    return nb200_download_rect(s, block_row * s->block_rows, block_col * s->block_cols, host, rows, cols, cols);
+}
+
+int nb200_set_fill_synth(nb200_set *s, uint64_t seed, int64_t row_offset) {
+    NEED_CTX();
+    if (!s) return NB200_ERR_INVALID;
+    NB_TRY(ensure_f64(c, s));
+    drop_derived(s);
+    return launch_synth_fill(c, s->f64, s->total_rows, s->total_cols, s->total_cols, seed, row_offset, s->total_cols);
+}
+
+int nb200_set_invalidate_planes(nb200_set *s) {
+    if (!s) return NB200_ERR_INVALID;
+    s->rowp.valid = s->rowp.lo_valid = false;
+    s->colp.valid = s->colp.lo_valid = false;
+    return NB200_OK;
+}
+
+// ---- operators ------------------------------------------------------------------------------------
+static int bias_check(nb200_set *bias, int rows, const char *who) {
+    // FFReluBiasSum.h:49-56 / FFTransposeBiasSum.h:56-60: in2 must be (rows of in1) x 1
+    if (!bias || bias->total_cols != 1 || bias->total_rows != rows) {
+        set_error("[%s] Block dimemsions mismatch! bias must be %d x 1", who, rows);
+        return NB200_ERR_SHAPE;
+    }
+    return NB200_OK;
+}
+
+static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision,
+                            const char *db, const char *out_set, nb200_set **out, int extra_relu) {
+    NEED_CTX();
+    if (!a || !b || !db || !out_set || !out || (op != NB200_OP_NT && op != NB200_OP_NN) || epilogue < 0 || epilogue > 2 ||
+        precision < 0 || precision > 2) {
+        set_error("gemm_blocks: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    // join predicate + per-pair dimension check (FFTransposeMult.h:38-39,61-65; FFInputLayerJoin.h:30-31,57-60)
+    const int K = a->total_cols;
+    const int Kb = (op == NB200_OP_NT) ? b->total_cols : b->total_rows;
+    const int bkA = a->block_cols, bkB = (op == NB200_OP_NT) ? b->block_cols : b->block_rows;
+    if (K != Kb || bkA != bkB) {
+        set_error("Block dimemsions mismatch! (K %d vs %d, block K %d vs %d)", K, Kb, bkA, bkB);
+        return NB200_ERR_SHAPE;
+    }
+    const int I = a->total_rows, J = (op == NB200_OP_NT) ? b->total_rows : b->total_cols;
+    const int bI = a->block_rows, bJ = (op == NB200_OP_NT) ? b->block_rows : b->block_cols;
+    if (epilogue != NB200_EPI_NONE) NB_TRY(bias_check(bias, I, epilogue == NB200_EPI_BIAS_RELU ? "ReluBiasSum" : "TransposeBiasSum"));
+    const bool transpose_out = (epilogue == NB200_EPI_BIAS_TRANSPOSE);
+    // output meta: FFTransposeMult.h:68-71 / FFInputLayerJoin.h:64-67 / FFTransposeBiasSum.h:64-67
+    nb200_set *o = nullptr;
+    NB_TRY(make_set(db, out_set, transpose_out ? J : I, transpose_out ? I : J, transpose_out ? bJ : bI,
+                    transpose_out ? bI : bJ, &o));
+    const int relu = (epilogue == NB200_EPI_BIAS_RELU) || extra_relu;
+    const size_t on = static_cast<size_t>(o->total_rows) * o->total_cols;
+
+    if (precision == NB200_PREC_FP64) {
+        if (!a->f64 || !b->f64 || (bias && !bias->f64)) { set_error("gemm_blocks(FP64): inputs hold no fp64 data"); return NB200_ERR_STATE; }
+        NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+        F64Epilogue e;
+        e.relu = relu;
+        // element strides of A(i,k) and B'(j,k)
+        const int64_t a_sm = a->total_cols, a_sk = 1;
+        const int64_t b_sn = (op == NB200_OP_NT) ? b->total_cols : 1, b_sk = (op == NB200_OP_NT) ? 1 : b->total_cols;
+        if (!transpose_out) {
+            e.bias_m = bias ? bias->f64 : nullptr;
+            NB_TRY(launch_gemm_f64(c, a->f64, a_sm, a_sk, b->f64, b_sn, b_sk, I, J, K, o->f64, o->total_cols, e));
+        } else {
+            e.bias_n = bias->f64;
+            NB_TRY(launch_gemm_f64(c, b->f64, b_sn, b_sk, a->f64, a_sm, a_sk, J, I, K, o->f64, o->total_cols, e));
+        }
+        *out = o;
+        return NB200_OK;
+    }
+
+    const int nterms = (precision == NB200_PREC_BF16X3) ? 3 : 1;
+    const bool lo = nterms == 3;
+    NB_TRY(ensure_rowp(c, a, lo));
+    if (op == NB200_OP_NT) NB_TRY(ensure_rowp(c, b, lo));
+    else NB_TRY(ensure_colp(c, b, lo));
+    const Planes &pa = a->rowp;
+    const Planes &pb = (op == NB200_OP_NT) ? b->rowp : b->colp;
+    const float *bias32 = nullptr;
+    if (bias) {
+        NB_TRY(ensure_f32(c, bias));
+        bias32 = bias->f32;
+    }
+    NB_CUDA(cudaMalloc(&o->f32, (on ? on : 1) * sizeof(float)));
+    o->f32_ld = o->total_cols;
+    // P is always the logical output: roles are swapped for the transposing epilogue
+    const Planes &U = transpose_out ? pb : pa;
+    const Planes &V = transpose_out ? pa : pb;
+    const int M = o->total_rows, N = o->total_cols;
+    if (M == 0 || N == 0) { *out = o; return NB200_OK; }
+    const int splits = choose_splits(c, M, N, U.ldk, nterms);
+    int Mpad = 0, Npad = 0;
+    if (splits == 1) {
+        GemmEpilogue ge;
+        ge.mode = 1; ge.out = o->f32; ge.out_ld = o->f32_ld; ge.relu = relu;
+        if (transpose_out) ge.bias_n = bias32; else ge.bias_m = bias32;
+        NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, 1, ge, &Mpad, &Npad, nullptr));
+    } else {
+        GemmEpilogue ge;
+        ge.mode = 0;
+        int real_splits = splits;
+        NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, splits, ge, &Mpad, &Npad, &real_splits));
+        ReduceOut ro;
+        ro.f32 = o->f32; ro.f32_ld = o->f32_ld;
+        NB_TRY(launch_splitk_reduce(c, M, N, real_splits, Mpad, Npad, transpose_out ? nullptr : bias32,
+                                    transpose_out ? bias32 : nullptr, relu, ro));
+    }
+    NB_TRY(check_kernel_fault(c, "gemm_blocks"));
+    *out = o;
+    return NB200_OK;
+}
+
+int nb200_gemm_blocks(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision, const char *db,
+                      const char *out_set, nb200_set **out) {
+    return gemm_blocks_impl(op, a, b, epilogue, bias, precision, db, out_set, out, 0);
+}
+
+int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, nb200_set **out, int32_t *labels_host) {
+    NEED_CTX();
+    if (!logits || !db || !out_set || !out) return NB200_ERR_INVALID;
+    nb200_set *src = logits->view_of ? logits->view_of : logits;
+    nb200_set *o = nullptr;
+    NB_TRY(make_set(db, out_set, logits->total_rows, logits->total_cols, logits->block_rows, logits->block_cols, &o));
+    const int64_t rows = o->total_rows, cols = o->total_cols;
+    const size_t on = static_cast<size_t>(rows) * cols;
+    NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+    int32_t *labels = nullptr;
+    NB_CUDA(cudaMalloc(&labels, (rows ? rows : 1) * sizeof(int32_t)));
+    int st;
+    if (src->f64) st = launch_softmax_rows(c, src->f64, true, rows, cols, src->total_cols, o->f64, cols, labels, nullptr, nullptr, 0, 0);
+    else if (src->f32) st = launch_softmax_rows(c, src->f32, false, rows, cols, src->f32_ld, o->f64, cols, labels, nullptr, nullptr, 0, 0);
+    else { set_error("softmax_rows: set %s:%s holds no data", logits->db.c_str(), logits->name.c_str()); st = NB200_ERR_STATE; }
+    if (st == NB200_OK && labels_host && rows)
+        if (cudaMemcpyAsync(labels_host, labels, rows * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
+    cudaStreamSynchronize(c->stream);
+    cudaFree(labels);
+    if (st != NB200_OK) return st;
+    *out = o;
+    return NB200_OK;
+}
+
+// ---- fused ff::inference_unit -------------------------------------------------------------------
+struct FFScratch {  // reused across calls
+    Planes y1;                 // relu(X W1^T + b1) as operand planes, rows = batch, K = hidden
+    float *logits = nullptr;   // batch x ld fp32
+    int64_t logits_rows = 0, logits_ld = 0;
+    int32_t *labels = nullptr;
+    float *gap = nullptr;
+    int32_t *list = nullptr;
+    int *count = nullptr;
+    int *count_host = nullptr;
+    int64_t cap_rows = 0;
+    double *xg = nullptr, *y1g = nullptr, *zg = nullptr;  // fp64 refinement buffers
+    size_t xg_bytes = 0, y1g_bytes = 0, zg_bytes = 0;
+};
+static FFScratch g_ff;
+
+static int grow(double **p, size_t *have, size_t need) {
+    if (need <= *have) return NB200_OK;
+    cudaFree(*p);
+    *p = nullptr;
+    *have = 0;
+    NB_CUDA(cudaMalloc(p, need));
+    *have = need;
+    return NB200_OK;
+}
+
+int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb200_set *b1, nb200_set *bo, int precision,
+                            const char *db, const char *out_set, nb200_set **out, int32_t *labels_host,
+                            nb200_ff_stats *stats) {
+    NEED_CTX();
+    if (!w1 || !wo || !inputs || !b1 || !bo || !db || !out_set || !out || precision < 0 || precision > 2) {
+        set_error("ff_inference_unit: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    const int B = inputs->total_rows, F = inputs->total_cols, H = w1->total_rows, Lb = wo->total_rows;
+    // FFTransposeMult predicate/dimension check (w1 x inputs), FFInputLayerJoin (wo x y1)
+    if (w1->total_cols != F || w1->block_cols != inputs->block_cols) { set_error("Block dimemsions mismatch! (w1 vs inputs)"); return NB200_ERR_SHAPE; }
+    if (wo->total_cols != H || wo->block_cols != w1->block_rows) { set_error("Block dimemsions mismatch! (wo vs y1)"); return NB200_ERR_SHAPE; }
+    NB_TRY(bias_check(b1, H, "ReluBiasSum"));
+    NB_TRY(bias_check(bo, Lb, "TransposeBiasSum"));
+    if (!w1->f64 || !wo->f64 || !inputs->f64 || !b1->f64 || !bo->f64) { set_error("ff_inference_unit: an input set holds no data"); return NB200_ERR_STATE; }
+
+    const int64_t launches0 = c->launches;
+    // output sets: yo (view: exp of the logits, FFTransposeBiasSum.h:64-67 meta) and `output`
+    nb200_set *zset = nullptr, *yo = nullptr, *o = nullptr;
+    NB_TRY(make_set(db, "__logits", B, Lb, inputs->block_rows, wo->block_rows, &zset));
+    NB_TRY(make_set(db, "yo", B, Lb, inputs->block_rows, wo->block_rows, &yo));
+    yo->view_of = zset;
+    yo->view_exp = true;
+    NB_TRY(make_set(db, out_set, B, Lb, inputs->block_rows, wo->block_rows, &o));
+    const size_t on = static_cast<size_t>(B) * Lb;
+    NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+
+    FFScratch &S = g_ff;
+    if (S.cap_rows < B) {
+        cudaFree(S.labels); cudaFree(S.gap); cudaFree(S.list);
+        NB_CUDA(cudaMalloc(&S.labels, (B ? B : 1) * sizeof(int32_t)));
+        NB_CUDA(cudaMalloc(&S.gap, (B ? B : 1) * sizeof(float)));
+        NB_CUDA(cudaMalloc(&S.list, (B ? B : 1) * sizeof(int32_t)));
+        S.cap_rows = B;
+    }
+    if (!S.count) {
+        NB_CUDA(cudaMalloc(&S.count, sizeof(int)));
+        NB_CUDA(cudaMallocHost(&S.count_host, sizeof(int)));
+    }
+    cudaEvent_t *ev = c->ev;
+    NB_CUDA(cudaEventRecord(ev[0], c->stream));
+    int refined = 0, splits1 = 1;
+    float ms_k1 = 0.f;
+
+    if (B == 0 || Lb == 0) {
+        *out = o;
+        if (stats) memset(stats, 0, sizeof(*stats));
+        return NB200_OK;
+    }
+
+    if (precision == NB200_PREC_FP64) {
+        // exact path: everything in fp64 DFMA
+        NB_TRY(grow(&S.y1g, &S.y1g_bytes, static_cast<size_t>(B) * H * sizeof(double)));
+        NB_CUDA(cudaMalloc(&zset->f64, on * sizeof(double)));
+        NB_CUDA(cudaEventRecord(ev[1], c->stream));
+        F64Epilogue e1; e1.bias_n = b1->f64; e1.relu = 1;
+        NB_TRY(launch_gemm_f64(c, inputs->f64, F, 1, w1->f64, F, 1, B, H, F, S.y1g, H, e1));
+        NB_CUDA(cudaEventRecord(ev[2], c->stream));
+        F64Epilogue e2; e2.bias_n = bo->f64;
+        NB_TRY(launch_gemm_f64(c, S.y1g, H, 1, wo->f64, H, 1, B, Lb, H, zset->f64, Lb, e2));
+        NB_CUDA(cudaEventRecord(ev[3], c->stream));
+        NB_TRY(launch_softmax_rows(c, zset->f64, true, B, Lb, Lb, o->f64, Lb, S.labels, nullptr, nullptr, 0, 0));
+        NB_CUDA(cudaEventRecord(ev[4], c->stream));
+        NB_CUDA(cudaEventRecord(ev[5], c->stream));
+    } else {
+        const int nterms = (precision == NB200_PREC_BF16X3) ? 3 : 1;
+        const bool lo = nterms == 3;
+        // model side (cached across calls, like a materialised model): weight planes, fp32 biases
+        NB_TRY(ensure_rowp(c, w1, lo));
+        NB_TRY(ensure_rowp(c, wo, lo));
+        NB_TRY(ensure_f32(c, b1));
+        NB_TRY(ensure_f32(c, bo));
+        if (!wo->wo_rownorm_max) NB_CUDA(cudaMalloc(&wo->wo_rownorm_max, sizeof(float)));
+        NB_TRY(launch_max_rownorm(c, wo->rowp.row_sumsq, Lb, wo->wo_rownorm_max));
+        NB_CUDA(cudaEventRecord(ev[0], c->stream));
+        // query side: de-blocked fp64 inputs -> bf16 planes
+        NB_TRY(ensure_rowp(c, inputs, lo));
+        NB_CUDA(cudaEventRecord(ev[1], c->stream));
+        // layer 1: y1 = relu(X W1^T + b1)   [FFTransposeMult + FFAggMatrix + FFReluBiasSum]
+        splits1 = choose_splits(c, B, H, inputs->rowp.ldk, nterms);
+        int Mpad = 0, Npad = 0;
+        GemmEpilogue g1; g1.mode = 0;
+        NB_CUDA(cudaEventRecord(ev[6], c->stream));
+        NB_TRY(launch_gemm_tc(c, inputs->rowp, w1->rowp, B, H, nterms, splits1, g1, &Mpad, &Npad, &splits1));
+        NB_CUDA(cudaEventRecord(ev[7], c->stream));
+        ReduceOut r1; r1.planes = &S.y1; r1.want_lo = lo;
+        NB_TRY(launch_splitk_reduce(c, B, H, splits1, Mpad, Npad, nullptr, b1->f32, 1, r1));
+        NB_CUDA(cudaEventRecord(ev[2], c->stream));
+        // layer 2: z = y1 Wo^T + bo          [FFInputLayerJoin + FFAggMatrix + FFTransposeBiasSum (pre-exp)]
+        NB_CUDA(cudaMalloc(&zset->f32, on * sizeof(float)));
+        zset->f32_ld = Lb;
+        const int splits2 = choose_splits(c, B, Lb, S.y1.ldk, nterms);
+        if (splits2 == 1) {
+            GemmEpilogue g2; g2.mode = 1; g2.out = zset->f32; g2.out_ld = Lb; g2.bias_n = bo->f32;
+            NB_TRY(launch_gemm_tc(c, S.y1, wo->rowp, B, Lb, nterms, 1, g2, &Mpad, &Npad, nullptr));
+        } else {
+            GemmEpilogue g2; g2.mode = 0;
+            int used2 = splits2;
+            NB_TRY(launch_gemm_tc(c, S.y1, wo->rowp, B, Lb, nterms, splits2, g2, &Mpad, &Npad, &used2));
+            ReduceOut r2; r2.f32 = zset->f32; r2.f32_ld = Lb;
+            NB_TRY(launch_splitk_reduce(c, B, Lb, used2, Mpad, Npad, nullptr, bo->f32, 0, r2));
+        }
+        NB_CUDA(cudaEventRecord(ev[3], c->stream));
+        // FFRowAggregate + FFOutputLayer + label, and the near-tie scan
+        NB_TRY(launch_softmax_rows(c, zset->f32, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, nullptr, 0, 0));
+        NB_CUDA(cudaMemsetAsync(S.count, 0, sizeof(int), c->stream));
+        NB_TRY(launch_flag_rows(c, B, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs, wo->rowp.maxabs,
+                                wo->wo_rownorm_max, prec_unit(precision), 4.0f, S.list, S.count, B));
+        NB_CUDA(cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaEventRecord(ev[4], c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        refined = std::min(*S.count_host, B);
+        // fp64 re-evaluation of the flagged rows (K9), in chunks that bound the gather buffer
+        const int chunk = 256;
+        for (int r0 = 0; r0 < refined; r0 += chunk) {
+            const int R = std::min(chunk, refined - r0);
+            NB_TRY(grow(&S.xg, &S.xg_bytes, static_cast<size_t>(chunk) * F * sizeof(double)));
+            NB_TRY(grow(&S.y1g, &S.y1g_bytes, static_cast<size_t>(chunk) * H * sizeof(double)));
+            NB_TRY(grow(&S.zg, &S.zg_bytes, static_cast<size_t>(chunk) * Lb * sizeof(double)));
+            NB_TRY(launch_gather_rows_f64(c, inputs->f64, F, F, S.list + r0, R, S.xg));
+            F64Epilogue e1; e1.bias_n = b1->f64; e1.relu = 1;
+            NB_TRY(launch_gemm_f64(c, S.xg, F, 1, w1->f64, F, 1, R, H, F, S.y1g, H, e1));
+            F64Epilogue e2; e2.bias_n = bo->f64;
+            NB_TRY(launch_gemm_f64(c, S.y1g, H, 1, wo->f64, H, 1, R, Lb, H, S.zg, Lb, e2));
+            NB_TRY(launch_scatter_rows(c, S.zg, Lb, S.list + r0, R, zset->f32, Lb));
+            NB_TRY(launch_softmax_rows(c, S.zg, true, B, Lb, Lb, o->f64, Lb, S.labels, nullptr, S.list + r0, R, 1));
+        }
+        NB_CUDA(cudaEventRecord(ev[5], c->stream));
+    }
+    if (labels_host) NB_CUDA(cudaMemcpyAsync(labels_host, S.labels, static_cast<size_t>(B) * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    NB_TRY(check_kernel_fault(c, "ff_inference_unit"));
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        cudaEventElapsedTime(&stats->ms_convert, ev[0], ev[1]);
+        cudaEventElapsedTime(&stats->ms_gemm1, ev[1], ev[2]);
+        cudaEventElapsedTime(&stats->ms_gemm2, ev[2], ev[3]);
+        cudaEventElapsedTime(&stats->ms_softmax, ev[3], ev[4]);
+        cudaEventElapsedTime(&stats->ms_refine, ev[4], ev[5]);
+        cudaEventElapsedTime(&stats->ms_total, ev[0], ev[5]);
+        if (precision != NB200_PREC_FP64) cudaEventElapsedTime(&ms_k1, ev[6], ev[7]);
+        stats->ms_gemm1_kernel = ms_k1;
+        stats->refined_rows = refined;
+        stats->kernel_launches = static_cast<int>(c->launches - launches0);
+        stats->splits1 = splits1;
+    }
+    *out = o;
+    return NB200_OK;
+}
+
+// ---- conv2d_memory_fusion -------------------------------------------------------------------------
+int nb200_conv2d_image_flat(const double *images_host, int n, int ch, int h, int w, int k, int stride, int padding,
+                            int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out) {
+    NEED_CTX();
+    if (!images_host || n <= 0 || ch <= 0 || h <= 0 || w <= 0 || k <= 0 || stride <= 0 || padding < 0 || !out) {
+        set_error("conv2d_image_flat: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    const int vs = (h + 2 * padding - k) / stride + 1, hs = (w + 2 * padding - k) / stride + 1;
+    if (vs <= 0 || hs <= 0) { set_error("conv2d_image_flat: kernel larger than image"); return NB200_ERR_SHAPE; }
+    nb200_set *o = nullptr;
+    NB_TRY(make_set(db, out_set, n * vs * hs, ch * k * k + 1, block_rows, block_cols, &o));
+    NB_TRY(ensure_f64(c, o));
+    const size_t ib = static_cast<size_t>(n) * ch * h * w * sizeof(double);
+    double *dimg = nullptr;
+    NB_CUDA(cudaMalloc(&dimg, ib));
+    int st = NB200_OK;
+    if (cudaMemcpyAsync(dimg, images_host, ib, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
+    if (st == NB200_OK) st = launch_im2col(c, dimg, n, ch, h, w, k, stride, padding, o->f64, o->total_cols);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(dimg);
+    if (st != NB200_OK) return st;
+    *out = o;
+    return NB200_OK;
+}
+
+int nb200_conv2d_kernel_flat(const double *kernels_host, const double *bias_host, int kout, int ch, int k, int block_rows,
+                             int block_cols, const char *db, const char *out_set, nb200_set **out) {
+    NEED_CTX();
+    if (!kernels_host || !bias_host || kout <= 0 || ch <= 0 || k <= 0 || !out) {
+        set_error("conv2d_kernel_flat: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    // tiny one-off pack on the host (KernelToChunks.h:39-83 column order, KernelBiasJoin.h:42-46 bias column)
+    const int cols = ch * k * k + 1;
+    std::vector<double> flat(static_cast<size_t>(kout) * cols);
+    for (int r = 0; r < kout; r++) {
+        memcpy(&flat[static_cast<size_t>(r) * cols], kernels_host + static_cast<size_t>(r) * (cols - 1), (cols - 1) * sizeof(double));
+        flat[static_cast<size_t>(r) * cols + cols - 1] = bias_host[r];
+    }
+    nb200_set *o = nullptr;
+    NB_TRY(make_set(db, out_set, kout, cols, block_rows, block_cols, &o));
+    NB_TRY(ensure_f64(c, o));
+    NB_CUDA(cudaMemcpyAsync(o->f64, flat.data(), flat.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    *out = o;
+    return NB200_OK;
+}
+
+int nb200_conv2d_fused(const double *images_host, int n, int ch, int h, int w, const double *kernels_host,
+                       const double *bias_host, int kout, int k, int padding, int relu, int precision, int block_rows,
+                       int block_cols, const char *db, const char *out_set, nb200_set **out) {
+    // First cut: im2col on the device (never leaves HBM, never blocked) + the block GEMM.  The
+    // implicit-GEMM producer that skips the materialised image_flat is the next step.
+    NEED_CTX();
+    (void)c;
+    nb200_set *img = nullptr, *ker = nullptr, *res = nullptr;
+    NB_TRY(nb200_conv2d_image_flat(images_host, n, ch, h, w, k, 1, padding, block_rows, block_cols, db, "__image_flat", &img));
+    NB_TRY(nb200_conv2d_kernel_flat(kernels_host, bias_host, kout, ch, k, block_rows, block_cols, db, "__kernel_flat", &ker));
+    int st = gemm_blocks_impl(NB200_OP_NT, img, ker, NB200_EPI_NONE, nullptr, precision, db, out_set, &res, relu ? 1 : 0);
+    nb200_set_destroy(img);
+    nb200_set_destroy(ker);
+    if (st != NB200_OK) return st;
+    *out = res;
+    return NB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,327 @@
+// nb200_gemm.cu -- the JoinComp + ClusterAggregateComp pair as ONE tensor-core block GEMM.
+//
+// Replaces: FFTransposeMult / FFInputLayerJoin projection lambdas (one Eigen fp64 GEMM per joined
+// block pair, FF/headers/FFTransposeMult.h:80-92, FFInputLayerJoin.h:72-86) followed by the
+// aggregation sink's FFMatrixData::operator+ over materialised partial blocks
+// (queryExecution/headers/CombinedShuffleSink.h:112-144, AggregationProcessor.cc:131-156).
+//
+// Here the K-block partial products never exist as blocks: a CTA owns one 128 x BN tile of the
+// output and a contiguous range of 64-wide K blocks; TMA streams the bf16 operand tiles into a
+// 128B-swizzled shared-memory ring, one elected thread issues tcgen05.mma (kind::f16, bf16 in,
+// fp32 accumulate in TMEM) and four epilogue warps drain TMEM.  With split-K the fp32 partial
+// tiles go to a workspace that nb200_kernels.cu reduces in a fixed order (deterministic), fused
+// with bias / ReLU / re-quantisation for the next layer.
+//
+// P[M x N] = U[M x K] . V[N x K]^T, U and V K-major bf16 planes (row pitch ldk, multiple of 64,
+// zero padded).  nterms = 3 runs the bf16 hi/lo split: hi*hi + hi*lo + lo*hi.
+#include "nb200_internal.h"
+#include "nb200_ptx.cuh"
+
+namespace nb200 {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;                    // 64 bf16 = 128 bytes = one swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kThreads = 192;                  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
+
+struct GemmArgs {
+    int M, N;
+    int tiles_n;
+    int num_kb;        // 64-wide K blocks in total
+    int kb_per_split;
+    int nterms;
+    int mode;          // 0: partial -> ws, 1: direct epilogue
+    float *ws;
+    long long ws_split_stride;  // Mpad * Npad
+    int ws_ld;                  // Npad
+    float *out;
+    long long out_ld;
+    const float *bias_m;
+    const float *bias_n;
+    int relu;
+    int *err_flag;
+};
+
+template <int BN, int STAGES>
+struct SmemLayout {
+    static constexpr uint32_t kBBytes = BN * kBlockK * 2;
+    static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+    static constexpr uint32_t kBarOffset = STAGES * kStageBytes;
+    static constexpr uint32_t kTotal = kBarOffset + (2 * STAGES + 1) * 8 + 16 + 1024 /* alignment slack */;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant__ CUtensorMap map_u_lo,
+             const __grid_constant__ CUtensorMap map_v_hi, const __grid_constant__ CUtensorMap map_v_lo,
+             const GemmArgs g) {
+    using L = SmemLayout<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B tiles need 1024-byte alignment
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + L::kBarOffset);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tmem_full_bar = empty_bar + STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int tile_m = blockIdx.x / g.tiles_n;
+    const int tile_n = blockIdx.x % g.tiles_n;
+    const int split = blockIdx.y;
+    const int kb0 = split * g.kb_per_split;
+    const int kb1 = min(kb0 + g.kb_per_split, g.num_kb);
+    const int n_iter = max(kb1 - kb0, 0) * g.nterms;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_u_hi);
+        tma_prefetch_desc(&map_v_hi);
+        if (g.nterms > 1) {
+            tma_prefetch_desc(&map_u_lo);
+            tma_prefetch_desc(&map_v_lo);
+        }
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, BN);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int it = 0; it < n_iter; it++) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                if (!mbar_wait(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 101); break; }
+                const int kb = kb0 + it / g.nterms;
+                const int t = it % g.nterms;  // 0: hi*hi, 1: hi*lo, 2: lo*hi
+                const CUtensorMap *mu = (t == 2) ? &map_u_lo : &map_u_hi;
+                const CUtensorMap *mv = (t == 1) ? &map_v_lo : &map_v_hi;
+                uint8_t *sa = smem + s * L::kStageBytes;
+                uint8_t *sb = sa + kABytes;
+                mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+                tma_load_2d(mu, &full_bar[s], sa, kb * kBlockK, tile_m * kBlockM, kEvictNormal);
+                tma_load_2d(mv, &full_bar[s], sb, kb * kBlockK, tile_n * BN, kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BN);
+            bool ok = true;
+            for (int it = 0; it < n_iter && ok; it++) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                if (!mbar_wait(&full_bar[s], ph)) { atomicExch(g.err_flag, 102); ok = false; break; }
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + s * L::kStageBytes);
+                const uint32_t sb = sa + kABytes;
+                const uint64_t da = umma_desc_k_sw128(sa);
+                const uint64_t db = umma_desc_k_sw128(sb);
+#pragma unroll
+                for (int k = 0; k < kBlockK / kUmmaK; k++) {
+                    // advance 32 bytes (16 bf16) inside the 128B swizzle row: +2 in 16-byte units
+                    umma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);  // frees the smem slot when these MMAs retire
+            }
+            umma_commit(tmem_full_bar);      // accumulator complete
+        }
+    } else {
+        // ===== epilogue warps: TMEM -> registers -> global =====
+        const int q = warp & 3;              // TMEM lane quarter this warp may access
+        const int row_in_tile = q * 32 + lane;
+        const long long row = static_cast<long long>(tile_m) * kBlockM + row_in_tile;
+        bool ok = mbar_wait(tmem_full_bar, 0);
+        if (!ok && lane == 0) atomicExch(g.err_flag, 103);
+        ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+        tc_fence_after();
+        if (ok) {
+            const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+            const float bm = (g.mode == 1 && g.bias_m != nullptr && row < g.M) ? g.bias_m[row] : 0.f;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c++) {
+                uint32_t r[32];
+                if (n_iter > 0) {
+                    tmem_ld_32x32b_x32(lane_addr + c * 32, r);
+                    tmem_ld_wait();
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) r[j] = 0u;
+                }
+                const int col0 = tile_n * BN + c * 32;
+                if (g.mode == 0) {
+                    float *dst = g.ws + split * g.ws_split_stride + row * g.ws_ld + col0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<uint4 *>(dst + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+                } else if (row < g.M) {
+                    float *dst = g.out + row * g.out_ld + col0;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        if (col0 + j < g.N) {
+                            float v = __uint_as_float(r[j]) + bm;
+                            if (g.bias_n != nullptr) v += g.bias_n[col0 + j];
+                            if (g.relu) v = fmaxf(v, 0.f);
+                            dst[j] = v;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN);
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2D bf16 K-major plane: dim0 = K (padded pitch), dim1 = rows; box = 64 x box_rows, SWIZZLE_128B.
+static int make_plane_map(CUtensorMap *m, const __nv_bfloat16 *base, int64_t rows, int64_t ldk, int box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return NB200_ERR_CUDA;
+    }
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(ldk), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ldk) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(base), dims, strides, box,
+                     estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld ldk=%lld box_rows=%d)", (int)r,
+                  (long long)rows, (long long)ldk, box_rows);
+        return NB200_ERR_CUDA;
+    }
+    return NB200_OK;
+}
+
+// Split-K factor: the skinny FF shapes (Amazon-14K layer 1: 79 x 4 tiles, K = 597,540) have far
+// fewer output tiles than SMs x waves, so K is cut until the grid is a whole number of waves and
+// every CTA still runs a long (>= 32 K-block) main loop.
+int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms) {
+    (void)nterms;
+    const int64_t tiles = ceil_div(M, kBlockM) * ceil_div(N, 256);
+    const int64_t num_kb = ldk / kBlockK;
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    if (tiles >= 4 * sms || num_kb < 64) return 1;
+    int best = 1;
+    double best_cost = 1e30;
+    const int max_s = static_cast<int>(num_kb / 32 > 0 ? (num_kb / 32 < 256 ? num_kb / 32 : 256) : 1);
+    for (int s = 1; s <= max_s; s++) {
+        const int64_t per = ceil_div(num_kb, s);
+        if (ceil_div(num_kb, per) != s) continue;  // would leave an empty split
+        const int64_t waves = ceil_div(tiles * s, sms);
+        // time ~ waves * (main loop + fixed per-CTA cost) + reduction traffic
+        const double cost = waves * (per + 6.0) + 0.02 * s;
+        if (cost < best_cost) { best_cost = cost; best = s; }
+    }
+    return best;
+}
+
+template <int BN, int STAGES>
+static int launch_impl(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
+                       const CUtensorMap &mv_lo, const GemmArgs &g, int tiles, int splits) {
+    using L = SmemLayout<BN, STAGES>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NB_CUDA(cudaFuncSetAttribute(k_block_gemm<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    dim3 grid(tiles, splits);
+    k_block_gemm<BN, STAGES><<<grid, kThreads, L::kTotal, c->stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, int nterms, int splits,
+                   const GemmEpilogue &epi, int *Mpad_out, int *Npad_out, int *splits_used) {
+    if (!u.valid || !v.valid || u.ldk != v.ldk || u.ldk % kBlockK != 0) {
+        set_error("block GEMM: operand planes missing or K pitch mismatch (%lld vs %lld)", (long long)u.ldk,
+                  (long long)v.ldk);
+        return NB200_ERR_STATE;
+    }
+    if (nterms == 3 && (!u.lo_valid || !v.lo_valid)) {
+        set_error("block GEMM: BF16X3 needs the residual planes");
+        return NB200_ERR_STATE;
+    }
+    const int BN = (N <= 128) ? 128 : 256;
+    const int tiles_m = static_cast<int>(ceil_div(M, kBlockM)), tiles_n = static_cast<int>(ceil_div(N, BN));
+    const int Mpad = tiles_m * kBlockM, Npad = tiles_n * BN;
+    if (Mpad_out) *Mpad_out = Mpad;
+    if (Npad_out) *Npad_out = Npad;
+    const int num_kb = static_cast<int>(u.ldk / kBlockK);
+    if (splits < 1) splits = 1;
+    if (splits > num_kb) splits = num_kb > 0 ? num_kb : 1;
+    int per = static_cast<int>(ceil_div(num_kb, splits));
+    splits = static_cast<int>(ceil_div(num_kb, per > 0 ? per : 1));
+    if (splits < 1) splits = 1;
+    if (splits_used) *splits_used = splits;
+    if (epi.mode == 1 && splits != 1) {
+        set_error("block GEMM: direct epilogue requires splits == 1");
+        return NB200_ERR_INVALID;
+    }
+
+    GemmArgs g{};
+    g.M = M; g.N = N; g.tiles_n = tiles_n; g.num_kb = num_kb; g.kb_per_split = per; g.nterms = nterms;
+    g.mode = epi.mode;
+    if (epi.mode == 0) {
+        const size_t need = static_cast<size_t>(splits) * Mpad * Npad * sizeof(float);
+        NB_TRY(ensure_ws(c, need));
+        g.ws = c->ws;
+        g.ws_split_stride = static_cast<long long>(Mpad) * Npad;
+        g.ws_ld = Npad;
+    } else {
+        g.out = epi.out; g.out_ld = epi.out_ld; g.bias_m = epi.bias_m; g.bias_n = epi.bias_n; g.relu = epi.relu;
+    }
+    g.err_flag = c->err_flag;
+
+    CUtensorMap mu_hi, mu_lo, mv_hi, mv_lo;
+    NB_TRY(make_plane_map(&mu_hi, u.hi, u.rows, u.ldk, kBlockM));
+    NB_TRY(make_plane_map(&mv_hi, v.hi, v.rows, v.ldk, BN));
+    if (nterms == 3) {
+        NB_TRY(make_plane_map(&mu_lo, u.lo, u.rows, u.ldk, kBlockM));
+        NB_TRY(make_plane_map(&mv_lo, v.lo, v.rows, v.ldk, BN));
+    } else {
+        mu_lo = mu_hi;
+        mv_lo = mv_hi;
+    }
+    if (BN == 256) return launch_impl<256, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
+    return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
+}
+
+}  // namespace nb200

@@ -1,0 +1,149 @@
+// nb200_internal.h -- declarations shared by the translation units of libnetsdb_b200.so.
+// Not part of the public ABI (that is include/netsdb_b200.h).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+
+#include "../../include/netsdb_b200.h"
+
+namespace nb200 {
+
+// ---- error plumbing -------------------------------------------------------------------------
+void set_error(const char *fmt, ...);
+#define NB_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            ::nb200::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return NB200_ERR_CUDA;                                                                 \
+        }                                                                                          \
+    } while (0)
+#define NB_TRY(expr)                \
+    do {                            \
+        int _s = (expr);            \
+        if (_s != NB200_OK) return _s; \
+    } while (0)
+
+// ---- context --------------------------------------------------------------------------------
+struct Context {
+    int device = -1;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;      // stream everything is launched on
+    cudaStream_t own_stream = nullptr;  // created by nb200_init
+    int *err_flag = nullptr;            // device int: nonzero = kernel-internal fault code
+    int *err_flag_host = nullptr;       // pinned mirror
+    float *ws = nullptr;                // split-K workspace (grown on demand)
+    size_t ws_bytes = 0;
+    double *stage = nullptr;            // staging for transposed / converting downloads
+    size_t stage_bytes = 0;
+    int64_t launches = 0;
+    cudaEvent_t ev[8] = {};
+};
+Context *ctx();                                   // nullptr before nb200_init
+int ensure_ws(Context *c, size_t bytes);          // grows c->ws
+int check_kernel_fault(Context *c, const char *what);  // syncs the stream and reads err_flag
+
+inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// bf16 operand planes: K-major, rows x ldk with ldk a multiple of 64 and the padding zeroed.
+struct Planes {
+    __nv_bfloat16 *hi = nullptr;
+    __nv_bfloat16 *lo = nullptr;  // residual plane (x - bf16(x)), only for BF16X3
+    int64_t rows = 0, k = 0, ldk = 0;
+    float *row_sumsq = nullptr;   // per row sum of squares of the source values
+    float *maxabs = nullptr;      // device scalar: max |value|
+    bool valid = false, lo_valid = false;
+};
+
+// ---- block GEMM on tensor cores (nb200_gemm.cu) ------------------------------------------------
+struct GemmEpilogue {
+    // mode 0: every split writes its fp32 partial tile to the workspace; a reduce kernel follows.
+    // mode 1: (splits == 1) bias/relu applied in the kernel, fp32 result written to `out`.
+    int mode = 0;
+    float *out = nullptr;
+    int64_t out_ld = 0;
+    const float *bias_m = nullptr;  // per row of P
+    const float *bias_n = nullptr;  // per column of P
+    int relu = 0;
+};
+// P[M x N] = U[M x K] * V[N x K]^T with U,V bf16 K-major planes; nterms 1 (hi*hi) or 3.
+// splits > 1 (or mode 0) leaves partials in ctx->ws laid out [split][Mpad][Npad].
+int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, int nterms, int splits,
+                   const GemmEpilogue &epi, int *Mpad, int *Npad, int *splits_used);
+int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms);
+
+// ---- other kernels (nb200_kernels.cu) -----------------------------------------------------------
+// source (double or float, row-major rows x cols, ld) -> planes of the same orientation
+int launch_convert_planes(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld,
+                          Planes *p, bool want_lo);
+// source rows x cols -> planes of the transpose (plane rows = cols, K = rows)
+int launch_convert_planes_t(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld,
+                            Planes *p, bool want_lo);
+struct ReduceOut {
+    float *f32 = nullptr;  // P orientation, ld = f32_ld
+    int64_t f32_ld = 0;
+    double *f64 = nullptr;
+    int64_t f64_ld = 0;
+    Planes *planes = nullptr;  // P orientation (rows = M, K = N)
+    bool want_lo = false;
+};
+int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npad, const float *bias_m,
+                         const float *bias_n, int relu, const ReduceOut &o);
+int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t cols, int64_t ld, float *dst, int64_t dld);
+int launch_f64_to_f32(Context *c, const double *src, int64_t n, float *dst);
+int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
+                      int64_t row_offset, int64_t total_cols);
+
+// fp64 GEMM P[M x N] = U * V^T, U(m,k) = u[m*u_sm + k*u_sk], V(n,k) = v[n*v_sn + k*v_sk]; split-K in fp64.
+struct F64Epilogue {
+    const double *bias_m = nullptr;
+    const double *bias_n = nullptr;
+    int relu = 0;
+};
+int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, const double *v, int64_t v_sn,
+                    int64_t v_sk, int M, int N, int64_t K, double *out, int64_t out_ld, const F64Epilogue &e);
+
+// row softmax / argmax / top-2 gap over logits (float or double).  probs may be null.
+int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t rows, int64_t cols, int64_t ld,
+                        double *probs, int64_t probs_ld, int32_t *labels, float *gap, const int32_t *row_list,
+                        int nrows_list, int in_compact);
+// flag rows whose top-2 gap is inside tau * eps_r; appends to list, counts in *count
+int launch_flag_rows(Context *c, int64_t rows, const float *gap, const float *x_sumsq, const float *y_sumsq,
+                     const float *w1_maxabs, const float *wo_maxabs, const float *wo_rownorm_max, float u, float tau,
+                     int32_t *list, int *count, int max_list);
+int launch_gather_rows_f64(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
+                           double *dst);
+int launch_max_rownorm(Context *c, const float *row_sumsq, int64_t rows, float *out_scalar);
+int launch_extract_f32_to_f64(Context *c, const float *src, int64_t ld, int64_t row0, int64_t col0, int rows, int cols,
+                              int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp);
+int launch_scatter_rows(Context *c, const double *src, int64_t cols, const int32_t *list, int n, float *dst_f32,
+                        int64_t dst_ld);
+int launch_im2col(Context *c, const double *images, int n, int ch, int h, int w, int k, int stride, int padding,
+                  double *out, int64_t out_ld);
+
+}  // namespace nb200
+
+// ---- device block set ---------------------------------------------------------------------------
+// A user set of FFMatrixBlocks, de-blocked on the device.  Logical matrix total_rows x total_cols.
+// Representations (any subset may be present; the others are derived on demand):
+//   f64    logical row-major fp64 (what uploads write; the fp64 "master")
+//   f32    logical row-major fp32 (tensor-core results)
+//   rowp   bf16 planes with rows = logical rows, K = logical cols
+//   colp   bf16 planes with rows = logical cols, K = logical rows
+struct nb200_set {
+    std::string db, name;
+    int total_rows = 0, total_cols = 0, block_rows = 0, block_cols = 0;
+    double *f64 = nullptr;
+    float *f32 = nullptr;
+    int64_t f32_ld = 0;
+    nb200::Planes rowp, colp;
+    float *wo_rownorm_max = nullptr;  // device scalar derived from rowp.row_sumsq (error model)
+    bool view_exp = false;         // downloads apply exp() (the `yo` view of the logits)
+    nb200_set *view_of = nullptr;  // set whose storage a view reads
+};

@@ -1,0 +1,703 @@
+// nb200_kernels.cu -- the HBM-bound kernels around the block GEMM:
+//   * fp64 -> bf16 (hi / lo) operand-plane conversion, de-blocked K-major layout        (new, K8)
+//   * split-K reduction fused with bias / ReLU / re-quantisation (FFAggMatrix's sum +
+//     FFReluBiasSum.h:63-71 + the conversion for the next layer)                         (K3)
+//   * row softmax / argmax / top-2 gap (FFRowAggregate + FFOutputLayer + label)          (K5)
+//   * fp64 DFMA GEMM used for the exact path and for re-evaluating near-tie rows         (K9)
+//   * seeded generator, transposes, im2col (ImageToChunks.h:43-102), gather/scatter.
+#include "nb200_internal.h"
+
+#include <cfloat>
+#include <math_constants.h>
+
+namespace nb200 {
+
+#define NB_LAUNCH_CHECK(c)           \
+    do {                             \
+        (c)->launches++;             \
+        NB_CUDA(cudaGetLastError()); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// bf16 hi/lo split
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void split_bf16(T x, __nv_bfloat16 &hi, __nv_bfloat16 &lo) {
+    const float xf = static_cast<float>(x);
+    hi = __float2bfloat16_rn(xf);
+    // residual in the source precision, then rounded once
+    const T res = x - static_cast<T>(__bfloat162float(hi));
+    lo = __float2bfloat16_rn(static_cast<float>(res));
+}
+
+__device__ __forceinline__ float block_reduce_sum(float v, float *sh) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    v = (threadIdx.x < nw) ? sh[threadIdx.x] : 0.f;
+    if (w == 0)
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    return v;  // valid in thread 0
+}
+__device__ __forceinline__ float block_reduce_max(float v, float *sh) {
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    v = (threadIdx.x < nw) ? sh[threadIdx.x] : 0.f;
+    if (w == 0)
+        for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();
+    return v;
+}
+
+constexpr int kCvtThreads = 256;
+constexpr int kCvtPerThread = 8;
+constexpr int kCvtChunk = kCvtThreads * kCvtPerThread;  // elements of one row per block
+
+// grid: (rows, ceil(ldk / kCvtChunk)).  Reads the row once, writes hi (and lo) planes, zero pads
+// the K tail, accumulates the row's sum of squares and the global max |x| for the error model.
+template <typename T, bool WANT_LO>
+__global__ void __launch_bounds__(kCvtThreads)
+k_convert_planes(const T *__restrict__ src, long long ld, long long cols, __nv_bfloat16 *__restrict__ hi,
+                 __nv_bfloat16 *__restrict__ lo, long long ldk, float *__restrict__ row_sumsq,
+                 float *__restrict__ maxabs) {
+    __shared__ float sh[32];
+    const long long row = blockIdx.x;
+    const long long c0 = static_cast<long long>(blockIdx.y) * kCvtChunk + threadIdx.x * 4;
+    const T *srow = src + row * ld;
+    float ss = 0.f, mx = 0.f;
+#pragma unroll
+    for (int h = 0; h < kCvtPerThread / 4; h++) {
+        const long long c = c0 + static_cast<long long>(h) * kCvtThreads * 4;
+        if (c >= ldk) continue;
+        T v[4];
+        if (c + 3 < cols && ((reinterpret_cast<uintptr_t>(srow + c) & (sizeof(T) * 2 - 1)) == 0)) {
+            // two 16-byte (double) or one 16-byte (float) loads
+            if (sizeof(T) == 8) {
+                const double2 a = *reinterpret_cast<const double2 *>(srow + c);
+                const double2 b = *reinterpret_cast<const double2 *>(srow + c + 2);
+                v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+            } else {
+                const float2 a = *reinterpret_cast<const float2 *>(srow + c);
+                const float2 b = *reinterpret_cast<const float2 *>(srow + c + 2);
+                v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) v[j] = (c + j < cols) ? srow[c + j] : T(0);
+        }
+        __nv_bfloat16 h4[4], l4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            split_bf16<T>(v[j], h4[j], l4[j]);
+            const float f = static_cast<float>(v[j]);
+            ss += f * f;
+            mx = fmaxf(mx, fabsf(f));
+        }
+        *reinterpret_cast<uint2 *>(hi + row * ldk + c) = *reinterpret_cast<uint2 *>(h4);
+        if (WANT_LO) *reinterpret_cast<uint2 *>(lo + row * ldk + c) = *reinterpret_cast<uint2 *>(l4);
+    }
+    ss = block_reduce_sum(ss, sh);
+    mx = block_reduce_max(mx, sh);
+    if (threadIdx.x == 0) {
+        if (row_sumsq) atomicAdd(row_sumsq + row, ss);
+        if (maxabs) atomicMax(reinterpret_cast<unsigned int *>(maxabs), __float_as_uint(mx));
+    }
+}
+
+static int alloc_planes(Planes *p, int64_t rows, int64_t k, bool want_lo) {
+    const int64_t ldk = round_up(k, 64);
+    if (p->hi && (p->rows != rows || p->ldk != ldk)) {
+        cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
+        *p = Planes();
+    }
+    p->rows = rows; p->k = k; p->ldk = ldk;
+    const size_t bytes = static_cast<size_t>(rows) * ldk * sizeof(__nv_bfloat16);
+    if (!p->hi) NB_CUDA(cudaMalloc(&p->hi, bytes));
+    if (want_lo && !p->lo) NB_CUDA(cudaMalloc(&p->lo, bytes));
+    if (!p->row_sumsq) NB_CUDA(cudaMalloc(&p->row_sumsq, static_cast<size_t>(rows) * sizeof(float)));
+    if (!p->maxabs) NB_CUDA(cudaMalloc(&p->maxabs, sizeof(float)));
+    return NB200_OK;
+}
+
+int launch_convert_planes(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld,
+                          Planes *p, bool want_lo) {
+    NB_TRY(alloc_planes(p, rows, cols, want_lo));
+    NB_CUDA(cudaMemsetAsync(p->row_sumsq, 0, static_cast<size_t>(rows) * sizeof(float), c->stream));
+    NB_CUDA(cudaMemsetAsync(p->maxabs, 0, sizeof(float), c->stream));
+    if (rows == 0 || cols == 0) { p->valid = true; p->lo_valid = want_lo; return NB200_OK; }
+    dim3 grid(static_cast<unsigned>(rows), static_cast<unsigned>(ceil_div(p->ldk, kCvtChunk)));
+    if (grid.y > 65535) { set_error("convert: K too large for one launch (%lld)", (long long)cols); return NB200_ERR_INVALID; }
+    if (src_is_f64) {
+        if (want_lo) k_convert_planes<double, true><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        else k_convert_planes<double, false><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+    } else {
+        if (want_lo) k_convert_planes<float, true><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        else k_convert_planes<float, false><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+    }
+    NB_LAUNCH_CHECK(c);
+    p->valid = true;
+    p->lo_valid = want_lo;
+    return NB200_OK;
+}
+
+// Transposing conversion: plane[c][r] = src[r][c].  32 x 32 tiles through shared memory so both
+// the read (along c) and the write (along r, the plane's K) are coalesced.
+template <typename T, bool WANT_LO>
+__global__ void __launch_bounds__(256)
+k_convert_planes_t(const T *__restrict__ src, long long ld, long long rows, long long cols,
+                   __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo, long long ldk,
+                   float *__restrict__ row_sumsq, float *__restrict__ maxabs) {
+    __shared__ T tile[32][33];
+    const long long r0 = static_cast<long long>(blockIdx.y) * 32, c0 = static_cast<long long>(blockIdx.x) * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int i = ty; i < 32; i += 8) {
+        const long long r = r0 + i, cc = c0 + tx;
+        tile[i][tx] = (r < rows && cc < cols) ? src[r * ld + cc] : T(0);
+    }
+    __syncthreads();
+    float mx = 0.f;
+    for (int i = ty; i < 32; i += 8) {
+        const long long pc = c0 + i;  // plane row = source column
+        const long long pr = r0 + tx; // plane K index = source row
+        const T v = tile[tx][i];
+        __nv_bfloat16 h, l;
+        split_bf16<T>(v, h, l);
+        const float f = static_cast<float>(v);
+        float ss = f * f;
+        mx = fmaxf(mx, fabsf(f));
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if (pc < cols && pr < ldk) {
+            hi[pc * ldk + pr] = h;
+            if (WANT_LO) lo[pc * ldk + pr] = l;
+        }
+        if (tx == 0 && pc < cols && row_sumsq) atomicAdd(row_sumsq + pc, ss);
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (tx == 0 && maxabs) atomicMax(reinterpret_cast<unsigned int *>(maxabs), __float_as_uint(mx));
+}
+
+int launch_convert_planes_t(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld,
+                            Planes *p, bool want_lo) {
+    NB_TRY(alloc_planes(p, cols, rows, want_lo));
+    NB_CUDA(cudaMemsetAsync(p->row_sumsq, 0, static_cast<size_t>(cols) * sizeof(float), c->stream));
+    NB_CUDA(cudaMemsetAsync(p->maxabs, 0, sizeof(float), c->stream));
+    if (rows == 0 || cols == 0) { p->valid = true; p->lo_valid = want_lo; return NB200_OK; }
+    // the tile grid covers K up to ldk so that the zero padding is (re)written too
+    dim3 grid(static_cast<unsigned>(ceil_div(cols, 32)), static_cast<unsigned>(ceil_div(p->ldk, 32)));
+    if (grid.y > 65535) { set_error("transposing convert: source has too many rows (%lld)", (long long)rows); return NB200_ERR_INVALID; }
+    if (src_is_f64) {
+        if (want_lo) k_convert_planes_t<double, true><<<grid, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        else k_convert_planes_t<double, false><<<grid, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+    } else {
+        if (want_lo) k_convert_planes_t<float, true><<<grid, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        else k_convert_planes_t<float, false><<<grid, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+    }
+    NB_LAUNCH_CHECK(c);
+    p->valid = true;
+    p->lo_valid = want_lo;
+    return NB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// split-K reduction + FFReluBiasSum epilogue + re-quantisation
+// ---------------------------------------------------------------------------------------------
+// grid: (M, ceil(Ncover / (256*4))) where Ncover = planes ? ldk : N.  Splits are summed in index
+// order, so the result does not depend on scheduling (the reference's aggregation order is
+// arrival order, CombinedShuffleSink.h:112-144).
+__global__ void __launch_bounds__(256)
+k_splitk_reduce(const float *__restrict__ ws, long long split_stride, int ws_ld, int splits, int M, int N,
+                const float *__restrict__ bias_m, const float *__restrict__ bias_n, int relu,
+                float *__restrict__ of32, long long of32_ld, double *__restrict__ of64, long long of64_ld,
+                __nv_bfloat16 *__restrict__ phi, __nv_bfloat16 *__restrict__ plo, long long ldk,
+                float *__restrict__ row_sumsq) {
+    __shared__ float sh[32];
+    const long long m = blockIdx.x;
+    const int n0 = (blockIdx.y * 256 + threadIdx.x) * 4;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    const bool in_ws = n0 < ws_ld;  // ws_ld is a multiple of 128, so all four or none
+    if (in_ws && n0 < N) {
+        const float *p = ws + m * ws_ld + n0;
+        float4 acc = *reinterpret_cast<const float4 *>(p);
+        for (int s = 1; s < splits; s++) {
+            const float4 t = *reinterpret_cast<const float4 *>(p + s * split_stride);
+            acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
+        v[0] = acc.x; v[1] = acc.y; v[2] = acc.z; v[3] = acc.w;
+        const float bm = bias_m ? bias_m[m] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (n0 + j < N) {
+                v[j] += bm + (bias_n ? bias_n[n0 + j] : 0.f);
+                if (relu) v[j] = fmaxf(v[j], 0.f);
+            } else {
+                v[j] = 0.f;
+            }
+        }
+    }
+    if (of32) {
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if (n0 + j < N) of32[m * of32_ld + n0 + j] = v[j];
+    }
+    if (of64) {
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if (n0 + j < N) of64[m * of64_ld + n0 + j] = static_cast<double>(v[j]);
+    }
+    float ss = 0.f;
+    if (phi && n0 < ldk) {
+        __nv_bfloat16 h4[4], l4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            split_bf16<float>(v[j], h4[j], l4[j]);
+            ss += v[j] * v[j];
+        }
+        *reinterpret_cast<uint2 *>(phi + m * ldk + n0) = *reinterpret_cast<uint2 *>(h4);
+        if (plo) *reinterpret_cast<uint2 *>(plo + m * ldk + n0) = *reinterpret_cast<uint2 *>(l4);
+    }
+    if (row_sumsq) {
+        ss = block_reduce_sum(ss, sh);
+        if (threadIdx.x == 0) atomicAdd(row_sumsq + m, ss);
+    }
+}
+
+// planes only: global max |v| of a freshly written plane is not needed (error model uses weights')
+int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npad, const float *bias_m,
+                         const float *bias_n, int relu, const ReduceOut &o) {
+    Planes *p = o.planes;
+    if (p) {
+        NB_TRY(alloc_planes(p, M, N, o.want_lo));
+        NB_CUDA(cudaMemsetAsync(p->row_sumsq, 0, static_cast<size_t>(M) * sizeof(float), c->stream));
+    }
+    const int64_t cover = p ? p->ldk : N;
+    dim3 grid(static_cast<unsigned>(M), static_cast<unsigned>(ceil_div(cover, 1024)));
+    k_splitk_reduce<<<grid, 256, 0, c->stream>>>(c->ws, static_cast<long long>(Mpad) * Npad, Npad, splits, M, N, bias_m,
+                                                 bias_n, relu, o.f32, o.f32_ld, o.f64, o.f64_ld, p ? p->hi : nullptr,
+                                                 (p && o.want_lo) ? p->lo : nullptr, p ? p->ldk : 0,
+                                                 p ? p->row_sumsq : nullptr);
+    NB_LAUNCH_CHECK(c);
+    if (p) { p->valid = true; p->lo_valid = o.want_lo; }
+    return NB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// small utilities
+// ---------------------------------------------------------------------------------------------
+__global__ void k_transpose_f32(const float *__restrict__ src, long long rows, long long cols, long long ld,
+                                float *__restrict__ dst, long long dld) {
+    __shared__ float tile[32][33];
+    const long long r0 = static_cast<long long>(blockIdx.y) * 32, c0 = static_cast<long long>(blockIdx.x) * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int i = ty; i < 32; i += 8)
+        if (r0 + i < rows && c0 + tx < cols) tile[i][tx] = src[(r0 + i) * ld + c0 + tx];
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8)
+        if (c0 + i < cols && r0 + tx < rows) dst[(c0 + i) * dld + r0 + tx] = tile[tx][i];
+}
+int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t cols, int64_t ld, float *dst, int64_t dld) {
+    if (rows == 0 || cols == 0) return NB200_OK;
+    dim3 grid(static_cast<unsigned>(ceil_div(cols, 32)), static_cast<unsigned>(ceil_div(rows, 32)));
+    k_transpose_f32<<<grid, 256, 0, c->stream>>>(src, rows, cols, ld, dst, dld);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+__global__ void k_f64_to_f32(const double *__restrict__ s, long long n, float *__restrict__ d) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x)
+        d[i] = static_cast<float>(s[i]);
+}
+int launch_f64_to_f32(Context *c, const double *src, int64_t n, float *dst) {
+    if (n == 0) return NB200_OK;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+    k_f64_to_f32<<<blocks, 256, 0, c->stream>>>(src, n, dst);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+// Seeded generator; the test suite's CPU generator is defined to match it bit for bit (explicit _rn intrinsics
+// keep the compiler from contracting the multiply-add, which would change the rounding).
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__global__ void k_synth_fill(double *__restrict__ dst, long long rows, long long cols, long long ld,
+                             unsigned long long seed_mixed, long long row_offset, long long total_cols) {
+    const long long n = rows * cols;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / cols, cc = i % cols;
+        const unsigned long long idx = static_cast<unsigned long long>((row_offset + r) * total_cols + cc);
+        const unsigned long long h = splitmix64(seed_mixed ^ (idx * 0xD1342543DE82EF95ull + 1ull));
+        const double u = __dmul_rn(static_cast<double>(h >> 11), 1.0 / 9007199254740992.0);
+        double mag = __dmul_rn(u, 0.5 - 0.0001);
+        mag = __dadd_rn(mag, 0.0001);
+        dst[r * ld + cc] = (h & 1ull) ? -mag : mag;
+    }
+}
+static unsigned long long host_splitmix64(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
+                      int64_t row_offset, int64_t total_cols) {
+    if (rows == 0 || cols == 0) return NB200_OK;
+    k_synth_fill<<<148 * 8, 256, 0, c->stream>>>(dst, rows, cols, ld, host_splitmix64(seed), row_offset, total_cols);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp64 GEMM (exact path): P[M x N] += U[M x K] . V^T, V(n,k) = v[n*v_sn + k*v_sk]
+// 256 threads, 4 x 4 register micro-tiles, BK = 16, split-K with fp64 atomics into a zeroed P.
+// ---------------------------------------------------------------------------------------------
+template <int BM, int BN>
+__global__ void __launch_bounds__(256)
+k_gemm_f64(const double *__restrict__ u, long long u_sm, long long u_sk, const double *__restrict__ v, long long v_sn,
+           long long v_sk, int M, int N, long long K, long long k_per_split, double *__restrict__ out, long long out_ld) {
+    constexpr int BK = 16;
+    static_assert(BM * BN == 4096, "256 threads x 16 outputs");
+    __shared__ double su[BK][BM + 1];
+    __shared__ double sv[BK][BN + 1];
+    constexpr int TM = BM / 4;  // thread groups along m
+    const int tid = threadIdx.x;
+    const int tm = tid % TM, tn = tid / TM;  // micro-tile origin (tm*4, tn*4)
+    const long long m0 = static_cast<long long>(blockIdx.y) * BM, n0 = static_cast<long long>(blockIdx.x) * BN;
+    const long long kbeg = static_cast<long long>(blockIdx.z) * k_per_split;
+    const long long kend = (kbeg + k_per_split < K) ? kbeg + k_per_split : K;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
+    for (long long k0 = kbeg; k0 < kend; k0 += BK) {
+        if (u_sk == 1) {  // k fastest in memory
+            for (int e = tid; e < BM * BK; e += 256) {
+                const int kk = e % BK, mm = e / BK;
+                const long long gm = m0 + mm, gk = k0 + kk;
+                su[kk][mm] = (gm < M && gk < kend) ? u[gm * u_sm + gk] : 0.0;
+            }
+        } else {  // m fastest in memory
+            for (int e = tid; e < BM * BK; e += 256) {
+                const int mm = e % BM, kk = e / BM;
+                const long long gm = m0 + mm, gk = k0 + kk;
+                su[kk][mm] = (gm < M && gk < kend) ? u[gm * u_sm + gk * u_sk] : 0.0;
+            }
+        }
+        if (v_sk == 1) {
+            for (int e = tid; e < BN * BK; e += 256) {
+                const int kk = e % BK, nn = e / BK;
+                const long long gn = n0 + nn, gk = k0 + kk;
+                sv[kk][nn] = (gn < N && gk < kend) ? v[gn * v_sn + gk] : 0.0;
+            }
+        } else {  // n fastest in memory
+            for (int e = tid; e < BN * BK; e += 256) {
+                const int nn = e % BN, kk = e / BN;
+                const long long gn = n0 + nn, gk = k0 + kk;
+                sv[kk][nn] = (gn < N && gk < kend) ? v[gn * v_sn + gk * v_sk] : 0.0;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < BK; kk++) {
+            double a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) a[i] = su[kk][tm * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; j++) b[j] = sv[kk][tn * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const long long gm = m0 + tm * 4 + i, gn = n0 + tn * 4 + j;
+            if (gm < M && gn < N) {
+                if (gridDim.z == 1) out[gm * out_ld + gn] = acc[i][j];
+                else atomicAdd(out + gm * out_ld + gn, acc[i][j]);
+            }
+        }
+}
+__global__ void k_bias_relu_f64(double *__restrict__ p, int M, int N, long long ld, const double *__restrict__ bias_m,
+                                const double *__restrict__ bias_n, int relu) {
+    const long long n = static_cast<long long>(M) * N;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / N, cc = i % N;
+        double x = p[r * ld + cc];
+        if (bias_m) x += bias_m[r];
+        if (bias_n) x += bias_n[cc];
+        if (relu) x = x > 0.0 ? x : 0.0;
+        p[r * ld + cc] = x;
+    }
+}
+int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, const double *v, int64_t v_sn,
+                    int64_t v_sk, int M, int N, int64_t K, double *out, int64_t out_ld, const F64Epilogue &e) {
+    if (M == 0 || N == 0) return NB200_OK;
+    const bool skinny = M <= 16;
+    const int BM = skinny ? 16 : 64, BN = skinny ? 256 : 64;
+    const int64_t tiles = ceil_div(M, BM) * ceil_div(N, BN);
+    int splits = 1;
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    if (tiles < 2 * sms && K >= 2048) {
+        splits = static_cast<int>(ceil_div(2 * sms, tiles));
+        const int64_t maxs = K / 1024;
+        if (splits > maxs) splits = static_cast<int>(maxs);
+        if (splits < 1) splits = 1;
+    }
+    int64_t kper = round_up(ceil_div(K, splits), 16);
+    splits = static_cast<int>(ceil_div(K, kper));
+    if (splits > 1) NB_CUDA(cudaMemset2DAsync(out, out_ld * sizeof(double), 0, static_cast<size_t>(N) * sizeof(double), M, c->stream));
+    dim3 grid(static_cast<unsigned>(ceil_div(N, BN)), static_cast<unsigned>(ceil_div(M, BM)), splits);
+    if (skinny) k_gemm_f64<16, 256><<<grid, 256, 0, c->stream>>>(u, u_sm, u_sk, v, v_sn, v_sk, M, N, K, kper, out, out_ld);
+    else k_gemm_f64<64, 64><<<grid, 256, 0, c->stream>>>(u, u_sm, u_sk, v, v_sn, v_sk, M, N, K, kper, out, out_ld);
+    NB_LAUNCH_CHECK(c);
+    if (e.bias_m || e.bias_n || e.relu) {
+        const int64_t n = static_cast<int64_t>(M) * N;
+        const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+        k_bias_relu_f64<<<blocks, 256, 0, c->stream>>>(out, M, N, out_ld, e.bias_m, e.bias_n, e.relu);
+        NB_LAUNCH_CHECK(c);
+    }
+    return NB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// row softmax / argmax / top-2 gap
+// ---------------------------------------------------------------------------------------------
+struct Top2 {
+    float m1, m2;
+    int i1;
+};
+__device__ __forceinline__ Top2 top2_merge(Top2 a, Top2 b) {
+    // first maximum wins on ties (smaller index), as a sequential scan would
+    Top2 r;
+    if (b.m1 > a.m1 || (b.m1 == a.m1 && b.i1 < a.i1)) {
+        r.m1 = b.m1; r.i1 = b.i1; r.m2 = fmaxf(a.m1, b.m2);
+    } else {
+        r.m1 = a.m1; r.i1 = a.i1; r.m2 = fmaxf(a.m2, b.m1);
+    }
+    return r;
+}
+template <typename T> struct TopD { T m1, m2; int i1; };
+
+// One block per row.  T = float (tensor-core logits) or double (exact path).
+// out[i,j] = exp(z - max) / sum_j exp(z - max)   (== exp(z)/sum exp(z) of FFOutputLayer, stable form)
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restrict__ probs, long long probs_ld,
+               int32_t *__restrict__ labels, float *__restrict__ gap, const int32_t *__restrict__ row_list,
+               int in_compact) {
+    __shared__ T s_m1[8], s_m2[8];
+    __shared__ int s_i1[8];
+    __shared__ double s_sum[8];
+    __shared__ T b_m1;
+    __shared__ double b_sum;
+    // row_list: only those rows are (re)computed; in_compact: z holds just the listed rows, packed
+    const long long row = row_list ? row_list[blockIdx.x] : blockIdx.x;
+    const T *zr = z + (in_compact ? static_cast<long long>(blockIdx.x) : row) * ld;
+    const T NEG = static_cast<T>(-CUDART_INF);
+    T m1 = NEG, m2 = NEG;
+    int i1 = 0x7fffffff;
+    for (int j = threadIdx.x; j < cols; j += 256) {
+        const T v = zr[j];
+        if (v > m1) { m2 = m1; m1 = v; i1 = j; }
+        else if (v > m2) m2 = v;
+    }
+    // warp merge
+    for (int o = 16; o > 0; o >>= 1) {
+        const T om1 = __shfl_xor_sync(0xffffffffu, m1, o), om2 = __shfl_xor_sync(0xffffffffu, m2, o);
+        const int oi1 = __shfl_xor_sync(0xffffffffu, i1, o);
+        if (om1 > m1 || (om1 == m1 && oi1 < i1)) { m2 = (m1 > om2) ? m1 : om2; m1 = om1; i1 = oi1; }
+        else { m2 = (m2 > om1) ? m2 : om1; }
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { s_m1[w] = m1; s_m2[w] = m2; s_i1[w] = i1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        T a1 = s_m1[0], a2 = s_m2[0];
+        int ai = s_i1[0];
+        for (int k = 1; k < 8; k++) {
+            const T om1 = s_m1[k], om2 = s_m2[k];
+            const int oi1 = s_i1[k];
+            if (om1 > a1 || (om1 == a1 && oi1 < ai)) { a2 = (a1 > om2) ? a1 : om2; a1 = om1; ai = oi1; }
+            else { a2 = (a2 > om1) ? a2 : om1; }
+        }
+        b_m1 = a1;
+        if (labels) labels[row] = ai;
+        if (gap) gap[row] = static_cast<float>(a1 - a2);
+    }
+    __syncthreads();
+    if (!probs) return;
+    const T mx = b_m1;
+    double sum = 0.0;
+    for (int j = threadIdx.x; j < cols; j += 256) sum += exp(static_cast<double>(zr[j] - mx));
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (l == 0) s_sum[w] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 8; k++) t += s_sum[k];
+        b_sum = t;
+    }
+    __syncthreads();
+    const double inv = 1.0 / b_sum;
+    double *pr = probs + row * probs_ld;
+    for (int j = threadIdx.x; j < cols; j += 256) pr[j] = exp(static_cast<double>(zr[j] - mx)) * inv;
+}
+int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t rows, int64_t cols, int64_t ld,
+                        double *probs, int64_t probs_ld, int32_t *labels, float *gap, const int32_t *row_list,
+                        int nrows_list, int in_compact) {
+    const int64_t n = row_list ? nrows_list : rows;
+    if (n == 0 || cols == 0) return NB200_OK;
+    if (is_f64) k_softmax_rows<double><<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const double *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+    else k_softmax_rows<float><<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+// eps_r = u * (||y1_r|| * max|wo| + ||x_r|| * max|w1| * max_l ||wo_l||): a one-sigma-style estimate
+// of the low-precision logit error of row r (DESIGN.md "error model"); rows with gap < tau*eps_r are
+// re-evaluated in fp64.
+__global__ void k_flag_rows(long long rows, const float *__restrict__ gap, const float *__restrict__ x_sumsq,
+                            const float *__restrict__ y_sumsq, const float *__restrict__ w1_maxabs,
+                            const float *__restrict__ wo_maxabs, const float *__restrict__ wo_rownorm_max, float u,
+                            float tau, int32_t *__restrict__ list, int *__restrict__ count, int max_list) {
+    const long long r = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (r >= rows) return;
+    const float eps = u * (sqrtf(y_sumsq[r]) * (*wo_maxabs) + sqrtf(x_sumsq[r]) * (*w1_maxabs) * (*wo_rownorm_max));
+    if (!(gap[r] >= tau * eps)) {  // also catches NaN
+        const int slot = atomicAdd(count, 1);
+        if (slot < max_list) list[slot] = static_cast<int32_t>(r);
+    }
+}
+int launch_flag_rows(Context *c, int64_t rows, const float *gap, const float *x_sumsq, const float *y_sumsq,
+                     const float *w1_maxabs, const float *wo_maxabs, const float *wo_rownorm_max, float u, float tau,
+                     int32_t *list, int *count, int max_list) {
+    if (rows == 0) return NB200_OK;
+    k_flag_rows<<<static_cast<unsigned>(ceil_div(rows, 256)), 256, 0, c->stream>>>(rows, gap, x_sumsq, y_sumsq, w1_maxabs, wo_maxabs, wo_rownorm_max, u, tau, list, count, max_list);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+__global__ void k_max_rownorm(const float *__restrict__ row_sumsq, long long rows, float *__restrict__ out) {
+    float mx = 0.f;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < rows;
+         i += static_cast<long long>(gridDim.x) * blockDim.x)
+        mx = fmaxf(mx, sqrtf(row_sumsq[i]));
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<unsigned int *>(out), __float_as_uint(mx));
+}
+int launch_max_rownorm(Context *c, const float *row_sumsq, int64_t rows, float *out_scalar) {
+    NB_CUDA(cudaMemsetAsync(out_scalar, 0, sizeof(float), c->stream));
+    if (rows == 0) return NB200_OK;
+    k_max_rownorm<<<static_cast<unsigned>(ceil_div(rows, 256) < 256 ? ceil_div(rows, 256) : 256), 256, 0, c->stream>>>(row_sumsq, rows, out_scalar);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+__global__ void k_gather_rows_f64(const double *__restrict__ src, long long ld, long long cols,
+                                  const int32_t *__restrict__ list, double *__restrict__ dst) {
+    const long long r = list[blockIdx.y];
+    for (long long j = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; j < cols;
+         j += static_cast<long long>(gridDim.x) * blockDim.x)
+        dst[static_cast<long long>(blockIdx.y) * cols + j] = src[r * ld + j];
+}
+int launch_gather_rows_f64(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
+                           double *dst) {
+    if (n == 0 || cols == 0) return NB200_OK;
+    dim3 grid(static_cast<unsigned>(ceil_div(cols, 256) < 64 ? ceil_div(cols, 256) : 64), n);
+    k_gather_rows_f64<<<grid, 256, 0, c->stream>>>(src, ld, cols, list, dst);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+// refined fp64 logits of the listed rows back into the fp32 logits matrix
+__global__ void k_scatter_rows(const double *__restrict__ src, long long cols, const int32_t *__restrict__ list,
+                               float *__restrict__ dst, long long dst_ld) {
+    const long long r = list[blockIdx.y];
+    for (long long j = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; j < cols;
+         j += static_cast<long long>(gridDim.x) * blockDim.x)
+        dst[r * dst_ld + j] = static_cast<float>(src[static_cast<long long>(blockIdx.y) * cols + j]);
+}
+int launch_scatter_rows(Context *c, const double *src, int64_t cols, const int32_t *list, int n, float *dst_f32,
+                        int64_t dst_ld) {
+    if (n == 0 || cols == 0) return NB200_OK;
+    dim3 grid(static_cast<unsigned>(ceil_div(cols, 256) < 64 ? ceil_div(cols, 256) : 64), n);
+    k_scatter_rows<<<grid, 256, 0, c->stream>>>(src, cols, list, dst_f32, dst_ld);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+// fp32 master -> fp64 block staging (rows x cols, zero padded outside valid), optional exp (the
+// `yo` view: FFTransposeBiasSum.h:94-104 applies exp only inside the un-padded region)
+__global__ void k_extract_f32_to_f64(const float *__restrict__ src, long long ld, long long row0, long long col0,
+                                     int rows, int cols, int valid_rows, int valid_cols, double *__restrict__ dst,
+                                     long long dst_ld, int apply_exp) {
+    const long long n = static_cast<long long>(rows) * cols;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int r = static_cast<int>(i / cols), cc = static_cast<int>(i % cols);
+        double v = 0.0;
+        if (r < valid_rows && cc < valid_cols) {
+            v = static_cast<double>(src[(row0 + r) * ld + col0 + cc]);
+            if (apply_exp) v = exp(v);
+        }
+        dst[r * dst_ld + cc] = v;
+    }
+}
+int launch_extract_f32_to_f64(Context *c, const float *src, int64_t ld, int64_t row0, int64_t col0, int rows, int cols,
+                              int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp) {
+    const int64_t n = static_cast<int64_t>(rows) * cols;
+    if (n == 0) return NB200_OK;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+    k_extract_f32_to_f64<<<blocks, 256, 0, c->stream>>>(src, ld, row0, col0, rows, cols, valid_rows, valid_cols, dst, dst_ld, apply_exp);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+// im2col with the reference's column order and trailing 1.0 column
+// (Image.h:36-57 get_win_value, ImageToChunks.h:52,67,75-84,98)
+__global__ void k_im2col(const double *__restrict__ img, int n, int ch, int h, int w, int k, int stride, int padding,
+                         int v_slides, int h_slides, double *__restrict__ out, long long out_ld) {
+    const long long windows = static_cast<long long>(v_slides) * h_slides;
+    const int cols = ch * k * k + 1;
+    const long long total = static_cast<long long>(n) * windows * cols;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long row = i / cols;
+        const int col = static_cast<int>(i % cols);
+        double v;
+        if (col == cols - 1) v = 1.0;
+        else {
+            const int im = static_cast<int>(row / windows), win = static_cast<int>(row % windows);
+            const int c = col / (k * k), rem = col % (k * k), ki = rem / k, kj = rem % k;
+            const int x = (win / h_slides) * stride + ki - padding, y = (win % h_slides) * stride + kj - padding;
+            if (padding > 0 && (x < 0 || y < 0 || x >= h || y >= w)) v = 0.0;
+            else v = img[((static_cast<long long>(im) * ch + c) * h + x) * w + y];
+        }
+        out[row * out_ld + col] = v;
+    }
+}
+int launch_im2col(Context *c, const double *images, int n, int ch, int h, int w, int k, int stride, int padding,
+                  double *out, int64_t out_ld) {
+    const int vs = (h + 2 * padding - k) / stride + 1, hs = (w + 2 * padding - k) / stride + 1;
+    k_im2col<<<148 * 8, 256, 0, c->stream>>>(images, n, ch, h, w, k, stride, padding, vs, hs, out, out_ld);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
+}  // namespace nb200

@@ -1,0 +1,119 @@
+/*
+ * ff_oracle.h -- CPU restatement (plain C, fp64) of netsDB's block-partitioned FF inference
+ * path, the conv2d_memory_fusion im2col path and the word2vec block join.
+ *
+ * THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load it.  The product path
+ * (libnetsdb_b200.so) never links, loads or calls anything in oracle/.
+ *
+ * PARITY UNPINNED: the reference ships no golden vectors, known-answer tests or fixtures for
+ * this path and cannot be compiled here (its FF headers need Eigen 3,
+ * which is absent, and the object model needs SCons-generated sources).  The oracle is
+ * therefore a restatement of the UDF arithmetic, cross-checked against a dense numpy fp64
+ * evaluation (oracle/ff_oracle.py) and hand-computable KATs (tests/golden/), not against
+ * outputs of the reference binary.
+ *
+ * Each function cites the reference file:line it follows (paths relative to the netsDB tree).
+ * Where this fork's debugging edits changed results the
+ * oracle implements the INTENDED semantics; debug prints (Q5) are omitted; dropout is 0 (Q3).
+ */
+#ifndef NB200_FF_ORACLE_H
+#define NB200_FF_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* One FFMatrixBlock: src/FF/headers/FFMatrixBlock.h:18-66, FFMatrixData.h:11-36,
+ * FFMatrixMeta.h:7-24.  data is row-major rows x cols (FFMatrixData::rawData). */
+typedef struct {
+    int block_row, block_col;   /* FFMatrixMeta::blockRowIndex / blockColIndex */
+    int rows, cols;             /* FFMatrixData::rowNums / colNums             */
+    int total_rows, total_cols; /* FFMatrixMeta::totalRows / totalCols         */
+    double *data;
+} nbo_block;
+
+/* A user set of FFMatrixBlocks (what ScanUserSet<FFMatrixBlock> iterates). */
+typedef struct {
+    int n, cap;
+    nbo_block *blocks;
+} nbo_set;
+
+/* ---- generator ---------------------------------------------------------------------------
+ * Seeded stand-in for ff::loadMatrix's value distribution (src/FF/source/FFMatrixUtil.cc:
+ * 229-237, 280-282): sign Bernoulli(1/2), magnitude U(1e-4, 0.5).  Counter based so the CUDA
+ * generator reproduces it bit for bit: value(seed, row * total_cols + col). */
+double nbo_synth_value(uint64_t seed, uint64_t index);
+void nbo_synth_dense(double *out, int64_t rows, int64_t cols, uint64_t seed);
+
+/* ---- sets ------------------------------------------------------------------------------ */
+nbo_set *nbo_set_new(void);
+void nbo_set_free(nbo_set *s);
+int nbo_set_size(const nbo_set *s);
+const nbo_block *nbo_set_get(const nbo_set *s, int i);
+const nbo_block *nbo_set_find(const nbo_set *s, int block_row, int block_col);
+
+/* ff::loadMatrix blocking and zero padding (FFMatrixUtil.cc:245-302): dense row-major
+ * total_rows x total_cols -> ceil() grid of full-size blocks; dont_pad_* as in the reference. */
+nbo_set *nbo_load_matrix(const double *dense, int total_rows, int total_cols, int block_rows,
+                         int block_cols, int dont_pad_rows, int dont_pad_cols);
+/* Same, values straight from the generator (no dense copy). */
+nbo_set *nbo_load_matrix_synth(uint64_t seed, int total_rows, int total_cols, int block_rows,
+                               int block_cols);
+/* Gather a set back into a dense total_rows x total_cols matrix (padding dropped). */
+void nbo_set_to_dense(const nbo_set *s, double *dense, int total_rows, int total_cols);
+
+/* ---- FF operators ---------------------------------------------------------------------- */
+/* FFTransposeMult (FFTransposeMult.h:38-39 predicate, :58-92 projection) followed by
+ * FFAggMatrix (FFAggMatrix.h:20-33; FFMatrixData::operator+ FFMatrixData.h:38-57) with the
+ * two-level merge of CombinedShuffleSink.h:78-159 + AggregationProcessor.cc:131-156:
+ * out(i,j) = sum_k A(i,k) * B(j,k)^T.  threads = pipeline threads (hash partitions). */
+nbo_set *nbo_transpose_mult_agg(const nbo_set *a, const nbo_set *b, int threads);
+/* FFInputLayerJoin (FFInputLayerJoin.h:30-31, :51-98) + FFAggMatrix:
+ * out(i,j) = sum_k A(i,k) * B(k,j). */
+nbo_set *nbo_input_layer_join_agg(const nbo_set *a, const nbo_set *b, int threads);
+/* FFReluBiasSum (FFReluBiasSum.h:34-35, :46-71), dropout_rate = 0. */
+nbo_set *nbo_relu_bias_sum(const nbo_set *in, const nbo_set *bias);
+/* FFTransposeBiasSum, intended semantics (FFTransposeBiasSum.h:64-67 output meta, :84 the
+ * surviving comment `currentMatrix1.colwise() + currentMatrix2`, :94-104 masked exp):
+ * out = exp(in + bias[row])^T on the un-padded region, 0 elsewhere.  apply_exp = 0 returns the
+ * pre-exp logits (used to define labels when exp overflows). */
+nbo_set *nbo_transpose_bias_sum(const nbo_set *in, const nbo_set *bias, int apply_exp);
+/* FFRowAggregate (FFRowAggregate.h:21-28; FFMatrixBlock.h:116-142). */
+nbo_set *nbo_row_aggregate(const nbo_set *in);
+/* FFOutputLayer, intended semantics (FFOutputLayer.h:21-22, :31-57: in1[i,j] / in2[i]). */
+nbo_set *nbo_output_layer(const nbo_set *in, const nbo_set *rowsum);
+
+/* ff::inference_unit (src/FF/source/SimpleFF.cc:331-424).  Returns the `output` set
+ * (softmax probabilities, batch x labels blocks); *logits_out (optional) receives the pre-exp
+ * batch x labels set; labels (optional, length batch) = first row argmax of the logits. */
+nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_set *inputs,
+                               const nbo_set *b1, const nbo_set *bo, int threads,
+                               nbo_set **logits_out, int32_t *labels);
+
+/* ---- conv2d_memory_fusion -------------------------------------------------------------- */
+/* Image -> image_flat: Image.h:26-57, ImageToChunks.h:43-102, ImageChunksToBlock.h:35-50,
+ * ImageBlockToMatrix.h:46-73.  images: n x c x h x w row-major.  Row = img * windows + win,
+ * col = ch*k*k + i*k + j, plus the trailing column of 1.0.  Blocks are zero padded
+ * (block_padding = true in PipelinedConv2dMemFuseTest.cc:77). */
+nbo_set *nbo_image_flat(const double *images, int n, int c, int h, int w, int k, int stride,
+                        int padding, int block_rows, int block_cols);
+/* Kernel -> kernel_flat with bias: KernelToChunks.h:39-83, KernelBiasJoin.h:42-46 (bias lands
+ * in the last real column; Q6: callers keep (c*k*k+1) % block_cols != 0). */
+nbo_set *nbo_kernel_flat(const double *kernels, const double *bias, int kout, int c, int k,
+                         int block_rows, int block_cols);
+
+/* ---- misc ------------------------------------------------------------------------------ */
+/* plain fp64 GEMM used by the pair products: C(MxN) = A(MxK) * B^T (B is NxK) if b_trans else
+ * A(MxK) * B(KxN); all row-major. */
+void nbo_dgemm(int m, int n, int k, const double *a, int lda, const double *b, int ldb,
+               int b_trans, double *c, int ldc);
+int nbo_hw_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,137 @@
+"""CPU tests: the C oracle against the golden fixtures, numpy and its own invariants.
+
+The oracle restates the reference's UDF arithmetic (oracle/ff_oracle.h cites file:line); parity is
+UNPINNED against the reference binary (it ships no golden vectors and cannot be built here), so
+these tests pin it to hand-computed KATs and an independent numpy evaluation instead."""
+import os
+
+import numpy as np
+import pytest
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _load_ff(oracle, x, w1, b1, wo, bo, block):
+    X = oracle.load_matrix(x, block, block)
+    W1 = oracle.load_matrix(w1, block, block)
+    B1 = oracle.load_matrix(b1, block, 1)       # FFTest.cc:109: (block_x, 1)
+    WO = oracle.load_matrix(wo, block, block)   # FFTest.cc:112-113: (block_x, block_x)
+    BO = oracle.load_matrix(bo, block, 1)
+    return X, W1, B1, WO, BO
+
+
+def test_generator_matches_numpy_restatement(oracle):
+    a = oracle.synth_dense(13, 31, 42)
+    assert np.array_equal(a, oracle.synth_dense_numpy(13, 31, 42))
+    # distribution of ff::loadMatrix (FFMatrixUtil.cc:229-237): |v| in [1e-4, 0.5), both signs
+    big = oracle.synth_dense(200, 500, 1)
+    assert np.abs(big).min() >= 1e-4 and np.abs(big).max() < 0.5
+    assert 0.45 < (big < 0).mean() < 0.55
+    assert abs(np.abs(big).mean() - 0.25005) < 5e-3
+
+
+def test_load_matrix_blocking_and_padding(oracle):
+    d = np.arange(7 * 5, dtype=np.float64).reshape(7, 5) + 1
+    s = oracle.load_matrix(d, 3, 2)
+    blocks = {(br, bc): (tr, tc, arr.copy()) for br, bc, tr, tc, arr in s.blocks()}
+    assert len(blocks) == 3 * 3
+    assert all(v[2].shape == (3, 2) and v[0] == 7 and v[1] == 5 for v in blocks.values())
+    assert np.array_equal(blocks[(2, 2)][2], [[35, 0], [0, 0], [0, 0]])  # zero padded edge block
+    assert np.array_equal(s.dense(), d)
+    t = oracle.load_matrix(d, 3, 2, dont_pad_rows=True, dont_pad_cols=True)
+    shapes = {(br, bc): arr.shape for br, bc, _, _, arr in t.blocks()}
+    assert shapes[(2, 2)] == (1, 1) and shapes[(0, 0)] == (3, 2)
+
+
+def test_kat_2x3(oracle):
+    g = np.load(os.path.join(G, "kat_2x3.npz"))
+    X, W1, B1, WO, BO = _load_ff(oracle, g["x"], g["w1"], g["b1"], g["wo"], g["bo"], int(g["block"]))
+    y1 = oracle.relu_bias_sum(oracle.transpose_mult_agg(W1, X, 2), B1)
+    assert y1.totals() == (2, 2)                      # hidden x batch (FFTransposeMult.h:68-71)
+    assert np.allclose(y1.dense(), g["y1"], atol=0, rtol=0)
+    out, logits, labels = oracle.ff_inference_unit(W1, WO, X, B1, BO, threads=2)
+    assert np.allclose(logits.dense(), g["logits"], atol=1e-15)
+    assert np.allclose(out.dense(), g["probs"], atol=1e-15)
+    assert np.array_equal(labels, g["labels"])
+
+
+def test_ff_small_vs_numpy_golden(oracle):
+    g = np.load(os.path.join(G, "ff_small.npz"))
+    batch, feat, hid, lab, block = (int(g[k]) for k in ("batch", "feat", "hid", "lab", "block"))
+    x = oracle.synth_dense(batch, feat, 1)
+    w1 = oracle.synth_dense(hid, feat, 2)
+    assert np.array_equal(x[:2, :5], g["x_head"]) and np.array_equal(w1[:2, :5], g["w1_head"])
+    b1 = oracle.synth_dense(hid, 1, 3)
+    wo = oracle.synth_dense(lab, hid, 4) * float(g["wo_scale"])
+    bo = oracle.synth_dense(lab, 1, 5)
+    for threads in (1, 3):
+        out, logits, labels = oracle.ff_inference_unit(*[_load_ff(oracle, x, w1, b1, wo, bo, block)[i] for i in (1, 3, 0, 2, 4)],
+                                                       threads=threads)
+        assert out.totals() == (batch, lab)
+        assert np.abs(logits.dense() - g["logits"]).max() <= 1e-12 * np.abs(g["logits"]).max()
+        assert np.abs(out.dense() - g["probs"]).max() <= 1e-12
+        assert np.array_equal(labels, g["labels"])
+
+
+def test_output_block_meta_and_padding(oracle):
+    """yo / output blocks: (in.blockCol, in.blockRow), J x I, totals swapped (FFTransposeBiasSum.h:64-67);
+    exp only inside the un-padded region (:94-104) so padded entries stay 0 and do not enter the row sum."""
+    batch, feat, hid, lab, block = 5, 6, 4, 3, 4
+    x, w1, b1 = oracle.synth_dense(batch, feat, 1), oracle.synth_dense(hid, feat, 2), oracle.synth_dense(hid, 1, 3)
+    wo, bo = oracle.synth_dense(lab, hid, 4), oracle.synth_dense(lab, 1, 5)
+    X, W1, B1, WO, BO = _load_ff(oracle, x, w1, b1, wo, bo, block)
+    z = oracle.input_layer_join_agg(WO, oracle.relu_bias_sum(oracle.transpose_mult_agg(W1, X), B1))
+    assert z.totals() == (lab, batch)
+    yo = oracle.transpose_bias_sum(z, BO)
+    assert yo.totals() == (batch, lab)
+    for br, bc, tr, tc, arr in yo.blocks():
+        assert arr.shape == (block, block)
+        rr, cc = np.meshgrid(br * block + np.arange(block), bc * block + np.arange(block), indexing="ij")
+        pad = (rr >= batch) | (cc >= lab)
+        assert np.all(arr[pad] == 0.0) and np.all(arr[~pad] > 0.0)
+    rs = oracle.row_aggregate(yo)
+    assert rs.totals() == (batch, 1)
+    probs = oracle.output_layer(yo, rs).dense()
+    assert np.allclose(probs.sum(axis=1), 1.0, atol=1e-14)
+
+
+def test_join_dimension_mismatch_is_an_error(oracle):
+    a = oracle.load_matrix(np.ones((4, 6)), 2, 3)
+    b = oracle.load_matrix(np.ones((4, 6)), 2, 2)  # block K differs: "Block dimemsions mismatch!" FFTransposeMult.h:61-65
+    with pytest.raises(RuntimeError):
+        oracle.transpose_mult_agg(a, b)
+
+
+def test_blocked_gemm_ops_vs_numpy(oracle):
+    rng = np.random.default_rng(0)
+    a, b = rng.standard_normal((23, 41)), rng.standard_normal((17, 41))
+    for threads in (1, 4):
+        c = oracle.transpose_mult_agg(oracle.load_matrix(a, 5, 7), oracle.load_matrix(b, 6, 7), threads)
+        assert c.totals() == (23, 17)
+        assert np.allclose(c.dense(), a @ b.T, rtol=0, atol=1e-12)
+    b2 = rng.standard_normal((41, 9))
+    c = oracle.input_layer_join_agg(oracle.load_matrix(a, 5, 7), oracle.load_matrix(b2, 7, 4), 2)
+    assert c.totals() == (23, 9) and np.allclose(c.dense(), a @ b2, rtol=0, atol=1e-12)
+    # empty input: loadMatrix returns without creating blocks when a dimension is 0 (FFMatrixUtil.cc:221-225)
+    assert len(oracle.load_matrix(np.zeros((0, 5)), 2, 2)) == 0
+
+
+def test_conv2d_memory_fusion_golden(oracle):
+    g = np.load(os.path.join(G, "conv_small.npz"))
+    IF = oracle.image_flat(g["images"], 3, 1, 0, 4, 5)
+    assert np.array_equal(IF.dense(), g["image_flat"])
+    assert IF.totals() == (2 * 4 * 3, 3 * 9 + 1)
+    KF = oracle.kernel_flat(g["kernels"], g["bias"], 4, 5)
+    assert np.array_equal(KF.dense(), g["kernel_flat"])
+    res = oracle.transpose_mult_agg(IF, KF, 2)  # PipelinedConv2dMemFuseTest.cc:249-262
+    assert np.allclose(res.dense(), g["result"], rtol=0, atol=1e-12)
+    # padding > 0 and stride > 1 (Image.h:26-57)
+    for k, s, p in ((3, 2, 1), (2, 1, 2)):
+        assert np.array_equal(oracle.image_flat(g["images"], k, s, p, 8, 8).dense(), oracle.im2col_numpy(g["images"], k, s, p))
+
+
+def test_word2vec_shape(oracle):
+    """Word2Vec.cc:53-71: weights (dim x vocab) joined with inputs (batch x vocab) by FFTransposeMult."""
+    w, x = oracle.synth_dense(6, 50, 9), oracle.synth_dense(11, 50, 10)
+    out = oracle.transpose_mult_agg(oracle.load_matrix(w, 4, 16), oracle.load_matrix(x, 4, 16), 3)
+    assert out.totals() == (6, 11) and np.allclose(out.dense(), w @ x.T, atol=1e-13)
