@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py -- FF inference rows/s on the Amazon-14K shape (BASELINE.json configs[1]) on N B200s.
+
+One step = one pass of the fused ff::inference_unit stage (FF/source/SimpleFF.cc:331-424) over one
+batch of synthetic input blocks: fp64 -> bf16 plane conversion of the inputs, layer-1 tcgen05 block
+GEMM (+ split-K reduce + bias + ReLU), layer-2 block GEMM (+ bias), row softmax / argmax, fp64
+re-evaluation of near-tie rows, labels copied to the host.  Weights are model-resident (converted
+once), inputs start every step as de-blocked fp64 in HBM (`value`) or as fp64 blocks in pinned
+host memory (`e2e`).
+
+N > 1: one process per GPU (torchrun), each rank holds the replicated weights and its own batch of
+`--batch` rows (weak scaling, no data-path collective); value = all rows / max-over-ranks time.
+
+--impl reference times the CPU restatement of the reference pipeline (oracle/, the only place this
+file executes it besides cpu_baseline) on all host threads, on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "FF inference rows/s (Amazon-14K shape)"
+UNIT = "rows/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("NB200_PRECISION", "bf16x3"), choices=["bf16", "bf16x3", "fp64"])
+    ap.add_argument("--batch", type=int, default=10000)
+    ap.add_argument("--features", type=int, default=597540)
+    ap.add_argument("--hidden", type=int, default=1000)
+    ap.add_argument("--labels", type=int, default=14588)
+    ap.add_argument("--block", type=int, default=1000)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the baseline sample")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"FF Amazon-14K shape: batch {a.batch} x {a.features} features, hidden {a.hidden}, {a.labels} labels, "
+            f"{a.block}x{a.block} FFMatrixBlocks per GPU")
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU arm (oracle): bounded sample, extrapolated linearly in the number of feature column blocks
+# ------------------------------------------------------------------------------------------------------
+def cpu_reference_sample(a, target_seconds: float):
+    """Times the CPU restatement of the reference pipeline on a K-slice of the workload.
+
+    Layer 1 (FFTransposeMult + FFAggMatrix + FFReluBiasSum) is timed on `cb` of the feature column
+    blocks and scaled by (all column blocks / cb); layer 2 + softmax are timed in full.  Rows/s is the
+    sample's rows over the extrapolated time.  Debug prints of the fork are omitted."""
+    from oracle import ff_oracle as fo
+
+    threads = fo.hw_threads()
+    blk = a.block
+    n_cb = (a.features + blk - 1) // blk
+    n_rb = (a.batch + blk - 1) // blk
+    # calibrate one pair product (single thread)
+    A = fo.load_matrix_synth(1, blk, blk, blk, blk)
+    B = fo.load_matrix_synth(2, min(a.hidden, blk), blk, blk, blk)
+    t0 = time.perf_counter()
+    fo.transpose_mult_agg(B, A, 1)
+    t_pair = max(time.perf_counter() - t0, 1e-4)
+    n_hb = (a.hidden + blk - 1) // blk
+    pairs_budget = target_seconds * threads / t_pair
+    rb = max(1, min(n_rb, 2))                                  # sample rows: up to 2 row blocks
+    cb = int(max(min(threads, n_cb), min(n_cb, pairs_budget / (rb * n_hb))))
+    rows = min(a.batch, rb * blk)
+    feats = min(a.features, cb * blk)
+    X = fo.load_matrix_synth(1, rows, feats, blk, blk)
+    W1 = fo.load_matrix_synth(2, a.hidden, feats, blk, blk)
+    B1 = fo.load_matrix_synth(3, a.hidden, 1, blk, 1)
+    WO = fo.load_matrix_synth(4, a.labels, a.hidden, blk, blk)
+    BO = fo.load_matrix_synth(5, a.labels, 1, blk, 1)
+    t0 = time.perf_counter()
+    y1pre = fo.transpose_mult_agg(W1, X, threads)
+    t_l1 = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    y1 = fo.relu_bias_sum(y1pre, B1)
+    z = fo.input_layer_join_agg(WO, y1, threads)
+    yo = fo.transpose_bias_sum(z, BO, True)
+    out = fo.output_layer(yo, fo.row_aggregate(yo))
+    t_rest = time.perf_counter() - t0
+    del out
+    t_full = t_l1 * (a.features / feats) + t_rest
+    return dict(value=rows / t_full, unit=UNIT, cores=threads, kind="port",
+                sample=(f"{rows} rows x {feats} of {a.features} features ({cb} of {n_cb} column blocks), hidden {a.hidden}, "
+                        f"{a.labels} labels; layer-1 time {t_l1:.2f}s scaled by {a.features / feats:.2f}, rest {t_rest:.2f}s in full; "
+                        f"fp64, {threads} threads, debug prints omitted"))
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals, last = [], None
+    for i in range(a.warmup + a.steps):
+        per = max(2.0, min(a.cpu_seconds, 120.0 / max(1, a.warmup + a.steps)))
+        last = cpu_reference_sample(a, per)
+        if i >= a.warmup:
+            vals.append(last["value"])
+    v = sum(vals) / len(vals)
+    last["value"] = v
+    line = dict(metric=METRIC, value=v, unit=UNIT, n_gpus=a.gpus, steps=a.steps, warmup=a.warmup,
+                ms_per_step=1000.0 * a.batch / v, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64",
+                data="synthetic", impl="reference", config=dict(workload=workload_name(a)), cpu_baseline=last,
+                e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks sampler
+# ------------------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append((time.perf_counter(), ln.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, ln in self.rows:
+            if not (t0 - 0.05 <= t <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in ln.split(",")]
+            try:
+                sm.append(float(f[1])); mx = float(f[2])
+            except Exception:
+                continue
+            for nme, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        sm.sort()
+        return dict(sm_mhz=(sm[len(sm) // 2] if sm else None), sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+
+
+# ------------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------------
+def run_b200(a):
+    import numpy as np
+    import torch
+
+    from netsdb_b200 import capi
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    capi.init(local)
+    stream = torch.cuda.current_stream()
+    capi.set_stream(stream.cuda_stream)
+    prec = capi.PRECISIONS[a.precision]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # --- synthetic sets, generated on the device by the seeded generator (same values as the oracle's) ---
+    blk = a.block
+    DS = capi.DeviceSet
+    w1 = DS.create("ff", "w1", a.hidden, a.features, blk, blk); w1.fill_synth(2)
+    b1 = DS.create("ff", "b1", a.hidden, 1, blk, 1); b1.fill_synth(3)
+    wo = DS.create("ff", "wo", a.labels, a.hidden, blk, blk); wo.fill_synth(4)
+    bo = DS.create("ff", "bo", a.labels, 1, blk, 1); bo.fill_synth(5)
+    x = DS.create("ff", "inputs", a.batch, a.features, blk, blk); x.fill_synth(1, row_offset=rank * a.batch)
+    capi.synchronize()
+
+    def step():
+        x.invalidate_planes()  # inputs start each step as fp64 in HBM; their conversion is part of the step
+        return capi.ff_inference_unit(w1, wo, x, b1, bo, prec, "ff", "output")
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    barrier()
+    clocks = Clocks(local)
+    clocks.start()
+    time.sleep(0.3)
+    l0 = capi.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(stream)
+    agg = {}
+    for _ in range(a.steps):
+        _, labels, st = step()
+        for k, v in st.items():
+            agg[k] = agg.get(k, 0.0) + v
+    e1.record(stream)
+    barrier()
+    t1 = time.perf_counter()
+    launches = capi.launch_count() - l0
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop(t0, t1)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / a.steps
+    value = world * a.batch / (ms_per_step / 1000.0)
+    stats = {k: v / a.steps for k, v in agg.items()}
+
+    # --- roofline of the dominant kernel: the layer-1 tcgen05 block GEMM ---
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = float(peaks.get("bf16_tflops", 1590.0))
+    which = "measured burst (MEASURED_PEAKS.json bf16_tflops)" if peaks else "fallback 1.59 PFLOP/s"
+    flops1 = 2.0 * a.batch * a.hidden * a.features  # algorithmic (useful) flops of one launch
+    k_ms = stats.get("ms_gemm1_kernel", 0.0)
+    ach = flops1 / (k_ms / 1000.0) / 1e12 if k_ms > 0 else None
+    roofline = dict(bound="tensor", kernel="k_block_gemm (layer 1)", achieved=ach, peak=peak_tf, unit="TFLOP/s",
+                    frac=(ach / peak_tf if ach else None), traffic=None, peak_source=which,
+                    executed_over_useful=3 if a.precision == "bf16x3" else 1)
+
+    # --- e2e: host blocks -> device -> labels + output blocks back, through the public C ABI ---
+    e2e = None
+    if not a.no_e2e:
+        e2e = run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world)
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        try:
+            cpu = cpu_reference_sample(a, a.cpu_seconds)
+        except Exception as ex:  # the bench line must still come out
+            cpu = dict(value=None, unit=UNIT, cores=None, kind="port", sample=f"failed: {ex}")
+
+    if rank == 0:
+        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=a.steps, warmup=max(a.warmup, 3),
+                    ms_per_step=ms_per_step, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype={"bf16": "bf16", "bf16x3": "bf16x3 (bf16 hi/lo split, fp32 accumulate)", "fp64": "f64"}[a.precision],
+                    data="synthetic",
+                    config=dict(workload=workload_name(a), parallelism=f"row-sharded dp{world}, weights replicated",
+                                l2="inputs (47.8 GB fp64 per GPU) exceed L2, no flush needed",
+                                labels="bit-exact vs fp64 by re-evaluating near-tie rows in fp64",
+                                precision=a.precision),
+                    clocks=clk, e2e=e2e, gpu_launches=int(launches), roofline=roofline, cpu_baseline=cpu,
+                    breakdown_ms={k: round(v, 4) for k, v in stats.items()})
+        print(json.dumps(line), flush=True)
+    capi.shutdown()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):
+    """Same metric through the reference-facing C ABI with HOST buffers: every step uploads the
+    inputs block by block from pinned host memory (nb200_upload_block), runs the fused stage and reads
+    the labels and the `output` set back (nb200_download_rect)."""
+    import numpy as np
+
+    blk = a.block
+    n_rb, n_cb = (a.batch + blk - 1) // blk, (a.features + blk - 1) // blk
+    in_bytes = a.batch * a.features * 8
+    out_bytes = a.batch * a.labels * 8
+    try:
+        avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+    except Exception:
+        avail = 0
+    if avail < (in_bytes + out_bytes) * world * 1.3:
+        return dict(value=None, unit=UNIT, h2d_bytes_per_step=in_bytes, d2h_bytes_per_step=out_bytes,
+                    note=f"skipped: host has {avail >> 30} GiB available, needs {(in_bytes + out_bytes) * world >> 30} GiB pinned")
+    # pinned host pool holding the inputs as the reference stores them: one row-major fp64 buffer per FFMatrixBlock
+    host = torch.empty(in_bytes // 8, dtype=torch.float64).pin_memory()
+    out_host = torch.empty(out_bytes // 8, dtype=torch.float64).pin_memory()
+    hx = host.numpy()
+    # fill the host blocks from the device copy of the same synthetic inputs (one-off, untimed)
+    blocks, off = [], 0
+    for i in range(n_rb):
+        rows = min(blk, a.batch - i * blk)
+        for j in range(n_cb):
+            cols = min(blk, a.features - j * blk)
+            view = hx[off:off + rows * cols].reshape(rows, cols)
+            capi.check(capi.lib().nb200_download_rect(x.ptr, i * blk, j * blk, view.ctypes.data, rows, cols, cols))
+            blocks.append((i, j, view))
+            off += rows * cols
+    oh = out_host.numpy().reshape(a.batch, a.labels)
+
+    def step():
+        for i, j, view in blocks:
+            capi.check(capi.lib().nb200_upload_block(x.ptr, i, j, view.ctypes.data, view.shape[0], view.shape[1]))
+        out, labels, _ = capi.ff_inference_unit(w1, wo, x, b1, bo, prec, "ff", "output")
+        capi.check(capi.lib().nb200_download_rect(out.ptr, 0, 0, oh.ctypes.data, a.batch, a.labels, a.labels))
+        return labels
+
+    step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s = torch.cuda.current_stream()
+    t0 = time.perf_counter()
+    e0.record(s)
+    for _ in range(a.e2e_steps):
+        step()
+    e1.record(s)
+    barrier()
+    wall = (time.perf_counter() - t0) * 1000.0
+    ms = max(e0.elapsed_time(e1), wall)  # host-side issue time counts too
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    v = world * a.batch / (ms / a.e2e_steps / 1000.0)
+    return dict(value=v, unit=UNIT, h2d_bytes_per_step=in_bytes, d2h_bytes_per_step=out_bytes + a.batch * 4,
+                ms_per_step=ms / a.e2e_steps, steps=a.e2e_steps,
+                note="inputs uploaded as fp64 FFMatrixBlocks from pinned host memory every step; weights model-resident")
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -336,9 +336,10 @@ int nb200_download_rect(nb200_set *s, int row0, int col0, double *host, int rows
         NB_CUDA(cudaStreamSynchronize(c->stream));
         return NB200_OK;
     }
-    if (!src->f32) { set_error("download: set %s:%s holds no data", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
+    if (!src->f32 && !src->f64) { set_error("download: set %s:%s holds no data", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
     NB_TRY(ensure_stage(c, static_cast<size_t>(rows) * cols * sizeof(double)));
-    NB_TRY(launch_extract_f32_to_f64(c, src->f32, src->f32_ld, row0, col0, rows, cols, vr, vc, c->stage, cols, s->view_exp ? 1 : 0));
+    if (src->f64) NB_TRY(launch_extract_to_f64(c, src->f64, true, src->total_cols, row0, col0, rows, cols, vr, vc, c->stage, cols, s->view_exp ? 1 : 0));
+    else NB_TRY(launch_extract_to_f64(c, src->f32, false, src->f32_ld, row0, col0, rows, cols, vr, vc, c->stage, cols, s->view_exp ? 1 : 0));
     NB_CUDA(cudaMemcpy2DAsync(host, static_cast<size_t>(ld) * sizeof(double), c->stage, static_cast<size_t>(cols) * sizeof(double),
                               static_cast<size_t>(cols) * sizeof(double), rows, cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));

@@ -120,8 +120,8 @@ int launch_flag_rows(Context *c, int64_t rows, const float *gap, const float *x_
 int launch_gather_rows_f64(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
                            double *dst);
 int launch_max_rownorm(Context *c, const float *row_sumsq, int64_t rows, float *out_scalar);
-int launch_extract_f32_to_f64(Context *c, const float *src, int64_t ld, int64_t row0, int64_t col0, int rows, int cols,
-                              int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp);
+int launch_extract_to_f64(Context *c, const void *src, bool src_is_f64, int64_t ld, int64_t row0, int64_t col0, int rows,
+                          int cols, int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp);
 int launch_scatter_rows(Context *c, const double *src, int64_t cols, const int32_t *list, int n, float *dst_f32,
                         int64_t dst_ld);
 int launch_im2col(Context *c, const double *images, int n, int ch, int h, int w, int k, int stride, int padding,

@@ -644,7 +644,8 @@ int launch_scatter_rows(Context *c, const double *src, int64_t cols, const int32
 
 // fp32 master -> fp64 block staging (rows x cols, zero padded outside valid), optional exp (the
 // `yo` view: FFTransposeBiasSum.h:94-104 applies exp only inside the un-padded region)
-__global__ void k_extract_f32_to_f64(const float *__restrict__ src, long long ld, long long row0, long long col0,
+template <typename T>
+__global__ void k_extract_to_f64(const T *__restrict__ src, long long ld, long long row0, long long col0,
                                      int rows, int cols, int valid_rows, int valid_cols, double *__restrict__ dst,
                                      long long dst_ld, int apply_exp) {
     const long long n = static_cast<long long>(rows) * cols;
@@ -659,12 +660,13 @@ __global__ void k_extract_f32_to_f64(const float *__restrict__ src, long long ld
         dst[r * dst_ld + cc] = v;
     }
 }
-int launch_extract_f32_to_f64(Context *c, const float *src, int64_t ld, int64_t row0, int64_t col0, int rows, int cols,
-                              int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp) {
+int launch_extract_to_f64(Context *c, const void *src, bool src_is_f64, int64_t ld, int64_t row0, int64_t col0, int rows,
+                          int cols, int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp) {
     const int64_t n = static_cast<int64_t>(rows) * cols;
     if (n == 0) return NB200_OK;
     const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
-    k_extract_f32_to_f64<<<blocks, 256, 0, c->stream>>>(src, ld, row0, col0, rows, cols, valid_rows, valid_cols, dst, dst_ld, apply_exp);
+    if (src_is_f64) k_extract_to_f64<double><<<blocks, 256, 0, c->stream>>>((const double *)src, ld, row0, col0, rows, cols, valid_rows, valid_cols, dst, dst_ld, apply_exp);
+    else k_extract_to_f64<float><<<blocks, 256, 0, c->stream>>>((const float *)src, ld, row0, col0, rows, cols, valid_rows, valid_cols, dst, dst_ld, apply_exp);
     NB_LAUNCH_CHECK(c);
     return NB200_OK;
 }

@@ -1,0 +1,243 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on identical seeded
+blocks.  Bars: bit-exact for generator / layout / index work and for predicted labels; logits within
+the stated tolerance relative to the logit scale max|z|:
+    FP64   1e-12   (summation order only)
+    BF16X3 1e-4    (north_star: <= 1e-4 at fp32 accumulation)
+    BF16   2e-2    (the looser stated bound for the single-pass bf16 variant)
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+TOL = {"fp64": 1e-12, "bf16x3": 1e-4, "bf16": 2e-2}
+
+
+def rel(a, b):
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+
+
+def test_generator_bit_exact(nb, oracle):
+    s = nb.DeviceSet.create("t", "gen", 37, 53, 10, 10)
+    s.fill_synth(42)
+    assert np.array_equal(s.download_dense(), oracle.synth_dense(37, 53, 42))
+    s.fill_synth(42, row_offset=5)  # a row shard reproduces its slice of the larger matrix
+    assert np.array_equal(s.download_dense(), oracle.synth_dense(42, 53, 42)[5:])
+    s.destroy()
+
+
+def test_block_upload_download_roundtrip(nb, oracle):
+    """sendData / getSetIterator: full-size zero-padded edge blocks in, zero-padded blocks out."""
+    d = oracle.synth_dense(23, 17, 3)
+    ref = oracle.load_matrix(d, 10, 6)
+    s = nb.DeviceSet.create("t", "rt", 23, 17, 10, 6)
+    for br, bc, _, _, arr in ref.blocks():
+        s.upload_block(br, bc, np.ascontiguousarray(arr))
+    nb.synchronize()
+    assert np.array_equal(s.download_dense(), d)
+    for br, bc, _, _, arr in ref.blocks():
+        assert np.array_equal(s.download_block(br, bc), arr)
+    # trimmed (dont_pad) blocks and an all-padding block
+    t = nb.DeviceSet.create("t", "rt2", 23, 17, 10, 6)
+    for br, bc, _, _, arr in oracle.load_matrix(d, 10, 6, True, True).blocks():
+        t.upload_block(br, bc, np.ascontiguousarray(arr))
+    t.upload_block(5, 5, np.ones((10, 6)))
+    nb.synchronize()
+    assert np.array_equal(t.download_dense(), d)
+    s.destroy(), t.destroy()
+
+
+@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16"])
+@pytest.mark.parametrize("shape", [(230, 310, 150, 100), (64, 128, 64, 64), (5, 7, 3, 4), (300, 2500, 129, 100)])
+def test_transpose_mult_and_input_layer_join(nb, oracle, prec, shape):
+    I, K, J, blk = shape
+    a, b = oracle.synth_dense(I, K, 11), oracle.synth_dense(J, K, 12)
+    A = nb.DeviceSet.create("t", "a", I, K, blk, blk); A.upload_dense(a)
+    B = nb.DeviceSet.create("t", "b", J, K, blk, blk); B.upload_dense(b)
+    C = nb.gemm_blocks(nb.OP_NT, A, B, nb.EPI_NONE, None, nb.PRECISIONS[prec], "t", "c")
+    ref = oracle.transpose_mult_agg(oracle.load_matrix(a, blk, blk), oracle.load_matrix(b, blk, blk), 2)
+    assert C.info() == (I, J, blk, blk) == ref.totals() + (blk, blk)   # FFTransposeMult.h:68-71
+    assert rel(C.download_dense(), ref.dense()) <= TOL[prec]
+    # blocks come back zero padded like the reference's
+    for br, bc, _, _, arr in ref.blocks():
+        got = C.download_block(br, bc)
+        assert got.shape == arr.shape and np.abs(got - arr).max() <= TOL[prec] * np.abs(ref.dense()).max()
+    # FFInputLayerJoin: in1(I x K) . in2(K x J)
+    bt = np.ascontiguousarray(b.T)
+    Bt = nb.DeviceSet.create("t", "bt", K, J, blk, blk); Bt.upload_dense(bt)
+    C2 = nb.gemm_blocks(nb.OP_NN, A, Bt, nb.EPI_NONE, None, nb.PRECISIONS[prec], "t", "c2")
+    ref2 = oracle.input_layer_join_agg(oracle.load_matrix(a, blk, blk), oracle.load_matrix(bt, blk, blk), 2)
+    assert C2.info()[:2] == ref2.totals()
+    assert rel(C2.download_dense(), ref2.dense()) <= TOL[prec]
+
+
+@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16"])
+def test_fused_bias_epilogues(nb, oracle, prec):
+    I, K, J, blk = 130, 270, 90, 50
+    a, b, bias = oracle.synth_dense(I, K, 1), oracle.synth_dense(J, K, 2), oracle.synth_dense(I, 1, 3) * 20
+    A = nb.DeviceSet.create("t", "a", I, K, blk, blk); A.upload_dense(a)
+    B = nb.DeviceSet.create("t", "b", J, K, blk, blk); B.upload_dense(b)
+    Bi = nb.DeviceSet.create("t", "bias", I, 1, blk, 1); Bi.upload_dense(bias)
+    oa, ob, obias = oracle.load_matrix(a, blk, blk), oracle.load_matrix(b, blk, blk), oracle.load_matrix(bias, blk, 1)
+    pre = oracle.transpose_mult_agg(oa, ob, 1)
+    scale = np.abs(pre.dense()).max()
+    relu = nb.gemm_blocks(nb.OP_NT, A, B, nb.EPI_BIAS_RELU, Bi, nb.PRECISIONS[prec], "t", "relu")
+    ref = oracle.relu_bias_sum(pre, obias).dense()
+    got = relu.download_dense()
+    assert np.abs(got - ref).max() <= TOL[prec] * scale and (got >= 0).all() and (got == 0).any()
+    tr = nb.gemm_blocks(nb.OP_NT, A, B, nb.EPI_BIAS_TRANSPOSE, Bi, nb.PRECISIONS[prec], "t", "tr")
+    reft = oracle.transpose_bias_sum(pre, obias, apply_exp=False)
+    assert tr.info() == (J, I, blk, blk) == reft.totals() + (blk, blk)  # FFTransposeBiasSum.h:64-67
+    assert np.abs(tr.download_dense() - reft.dense()).max() <= TOL[prec] * scale
+
+
+def test_bias_shape_mismatch_is_reported(nb, oracle):
+    A = nb.DeviceSet.create("t", "a", 8, 8, 4, 4); A.fill_synth(1)
+    B = nb.DeviceSet.create("t", "b", 8, 8, 4, 4); B.fill_synth(2)
+    bad = nb.DeviceSet.create("t", "bad", 8, 2, 4, 2); bad.fill_synth(3)
+    with pytest.raises(nb.Nb200Error, match="mismatch"):
+        nb.gemm_blocks(nb.OP_NT, A, B, nb.EPI_BIAS_RELU, bad, nb.PREC_BF16X3, "t", "x")
+    B2 = nb.DeviceSet.create("t", "b2", 8, 8, 4, 2); B2.fill_synth(2)  # block K differs (FFTransposeMult.h:61-65)
+    with pytest.raises(nb.Nb200Error, match="mismatch"):
+        nb.gemm_blocks(nb.OP_NT, A, B2, nb.EPI_NONE, None, nb.PREC_BF16X3, "t", "x")
+
+
+def test_softmax_rows_vs_row_aggregate_output_layer(nb, oracle):
+    z = oracle.synth_dense(57, 301, 8) * 40      # |z| up to 20: exp stays finite in the oracle
+    Z = nb.DeviceSet.create("t", "z", 57, 301, 25, 100); Z.upload_dense(z)
+    P, labels = nb.softmax_rows(Z, "t", "p")
+    yo = oracle.load_matrix(np.exp(z), 25, 100)
+    ref = oracle.output_layer(yo, oracle.row_aggregate(yo)).dense()
+    assert np.abs(P.download_dense() - ref).max() <= 1e-14
+    assert np.array_equal(labels, np.argmax(z, axis=1))
+    # first maximum wins on exact ties
+    z[3, 7] = z[3, 200] = 99.0
+    Z.upload_dense(z)
+    _, labels = nb.softmax_rows(Z, "t", "p")
+    assert labels[3] == 7
+
+
+def _ff_sets(nb, oracle, batch, feat, hid, lab, blk, wo_scale=1.0, dense=None):
+    if dense is None:
+        dense = dict(x=oracle.synth_dense(batch, feat, 1), w1=oracle.synth_dense(hid, feat, 2),
+                     b1=oracle.synth_dense(hid, 1, 3), wo=oracle.synth_dense(lab, hid, 4) * wo_scale,
+                     bo=oracle.synth_dense(lab, 1, 5))
+    dims = dict(x=(batch, feat, blk, blk), w1=(hid, feat, blk, blk), b1=(hid, 1, blk, 1), wo=(lab, hid, blk, blk),
+                bo=(lab, 1, blk, 1))
+    names = dict(x="inputs", w1="w1", b1="b1", wo="wo", bo="bo")
+    dev, ora = {}, {}
+    for k, (r, c, br, bc) in dims.items():
+        dev[k] = nb.DeviceSet.create("ff", names[k], r, c, br, bc)
+        dev[k].upload_dense(dense[k])
+        ora[k] = oracle.load_matrix(dense[k], br, bc)
+    return dev, ora, dense
+
+
+@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16"])
+def test_ff_inference_unit_config1(nb, oracle, prec):
+    """BASELINE config 1: batch 1,000 x 1,024 features, hidden 1,024, 10 labels, 100 x 100 blocks."""
+    dev, ora, _ = _ff_sets(nb, oracle, 1000, 1024, 1024, 10, 100)
+    out, labels, stats = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
+    ref_out, ref_logits, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=4)
+    assert np.array_equal(labels, ref_labels), f"{(labels != ref_labels).sum()} labels differ"
+    assert out.info() == (1000, 10, 100, 100) == ref_out.totals() + (100, 100)
+    z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
+    zr = ref_logits.dense()
+    assert rel(z, zr) <= TOL[prec], rel(z, zr)
+    p, pr = out.download_dense(), ref_out.dense()
+    assert np.isfinite(pr).all()
+    assert np.abs(p.sum(axis=1) - 1).max() <= 1e-12
+    assert np.abs(p - pr).max() <= 4 * TOL[prec] * np.abs(zr).max() + 1e-13
+    # the `yo` set of the reference (exp of the transposed, biased logits) is a view on the device
+    yo = nb.DeviceSet.lookup("ff", "yo").download_dense()
+    assert np.allclose(yo, np.exp(z), rtol=1e-12)
+    assert stats["kernel_launches"] > 0
+
+
+def test_ff_golden_fixtures(nb, oracle):
+    g = np.load(os.path.join(G, "kat_2x3.npz"))
+    dense = {k: g[k] for k in ("x", "w1", "b1", "wo", "bo")}
+    for prec in ("fp64", "bf16x3", "bf16"):
+        dev, _, _ = _ff_sets(nb, oracle, 2, 3, 2, 2, int(g["block"]), dense=dense)
+        out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
+        assert np.array_equal(labels, g["labels"])
+        # every value of this KAT is exactly representable in bf16, so all precisions agree to fp64 rounding
+        assert np.abs(out.download_dense() - g["probs"]).max() <= 1e-6 if prec != "fp64" else 1e-15
+    g = np.load(os.path.join(G, "ff_small.npz"))
+    batch, feat, hid, lab, blk = (int(g[k]) for k in ("batch", "feat", "hid", "lab", "block"))
+    for prec in ("fp64", "bf16x3", "bf16"):
+        dev, _, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk, wo_scale=float(g["wo_scale"]))
+        out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
+        assert np.array_equal(labels, g["labels"])
+        z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
+        assert rel(z, g["logits"]) <= TOL[prec]
+
+
+def test_ff_ragged_and_tiny_and_empty(nb, oracle):
+    for (batch, feat, hid, lab, blk) in [(1, 1, 1, 1, 1), (3, 5, 2, 4, 2), (129, 65, 257, 33, 64), (130, 1000, 70, 300, 100)]:
+        dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk)
+        ref_out, ref_logits, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=2)
+        for prec in ("fp64", "bf16x3", "bf16"):
+            out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
+            assert np.array_equal(labels, ref_labels), (batch, feat, hid, lab, prec)
+            z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
+            assert rel(z, ref_logits.dense()) <= TOL[prec]
+    # empty batch: nothing to do, no error
+    w1 = nb.DeviceSet.lookup("ff", "w1"); wo = nb.DeviceSet.lookup("ff", "wo")
+    b1 = nb.DeviceSet.lookup("ff", "b1"); bo = nb.DeviceSet.lookup("ff", "bo")
+    empty = nb.DeviceSet.create("ff", "inputs", 0, 1000, 100, 100); empty.fill_synth(1)
+    out, labels, _ = nb.ff_inference_unit(w1, wo, empty, b1, bo, nb.PREC_BF16X3)
+    assert out.info()[0] == 0 and labels.shape == (0,)
+
+
+def test_near_tie_rows_are_re_evaluated(nb, oracle):
+    """Two identical label rows in wo make every row an exact top-2 tie candidate for those labels: the
+    low-precision path must flag and re-evaluate, and still return the first maximum like the oracle."""
+    batch, feat, hid, lab, blk = 200, 640, 128, 12, 64
+    dense = dict(x=oracle.synth_dense(batch, feat, 1), w1=oracle.synth_dense(hid, feat, 2),
+                 b1=oracle.synth_dense(hid, 1, 3), wo=oracle.synth_dense(lab, hid, 4), bo=oracle.synth_dense(lab, 1, 5))
+    dense["wo"][7] = dense["wo"][2] * (1 + 1e-9)   # nearly identical logits for labels 2 and 7
+    dense["bo"][7] = dense["bo"][2]
+    dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk, dense=dense)
+    _, _, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=2)
+    for prec in ("bf16x3", "bf16"):
+        _, labels, stats = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
+        assert np.array_equal(labels, ref_labels)
+        assert stats["refined_rows"] >= int(np.isin(ref_labels, (2, 7)).sum())
+
+
+def test_conv2d_memory_fusion(nb, oracle):
+    g = np.load(os.path.join(G, "conv_small.npz"))
+    IF = nb.conv2d_image_flat(g["images"], 3, 1, 0, 4, 5)
+    assert np.array_equal(IF.download_dense(), g["image_flat"])           # pure data movement: bit exact
+    KF = nb.conv2d_kernel_flat(g["kernels"], g["bias"], 4, 5)
+    assert np.array_equal(KF.download_dense(), g["kernel_flat"])
+    for prec in ("fp64", "bf16x3", "bf16"):
+        R = nb.gemm_blocks(nb.OP_NT, IF, KF, nb.EPI_NONE, None, nb.PRECISIONS[prec], "conv2d", "result")
+        assert rel(R.download_dense(), g["result"]) <= TOL[prec]
+        F = nb.conv2d_fused(g["images"], g["kernels"], g["bias"], 0, True, nb.PRECISIONS[prec], 4, 5)
+        assert np.abs(F.download_dense() - np.maximum(g["result"], 0)).max() <= TOL[prec] * np.abs(g["result"]).max()
+    # larger, padded / strided im2col against the oracle's blocked image_flat
+    imgs = oracle.synth_dense(3 * 8, 20 * 19, 5).reshape(3, 8, 20, 19)
+    for k, s, p in ((3, 1, 0), (3, 2, 1), (5, 1, 2)):
+        ref = oracle.image_flat(imgs, k, s, p, 32, 32)
+        got = nb.conv2d_image_flat(imgs, k, s, p, 32, 32)
+        assert got.info() == ref.totals() + (32, 32)
+        assert np.array_equal(got.download_dense(), ref.dense())
+        for br, bc, _, _, arr in list(ref.blocks())[:6]:
+            assert np.array_equal(got.download_block(br, bc), arr)
+
+
+def test_word2vec_block_join(nb, oracle):
+    """Word2Vec.cc:53-71 at reduced size: weights (dim x vocab) x inputs (batch x vocab) by FFTransposeMult."""
+    dim, vocab, batch, blk = 50, 20000, 300, 1000
+    w, x = oracle.synth_dense(dim, vocab, 21), oracle.synth_dense(batch, vocab, 22)
+    W = nb.DeviceSet.create("word2vec", "weights0", dim, vocab, blk, blk); W.upload_dense(w)
+    X = nb.DeviceSet.create("word2vec", "inputs", batch, vocab, blk, blk); X.upload_dense(x)
+    ref = oracle.transpose_mult_agg(oracle.load_matrix(w, blk, blk), oracle.load_matrix(x, blk, blk), 4).dense()
+    for prec in ("fp64", "bf16x3", "bf16"):
+        out = nb.gemm_blocks(nb.OP_NT, W, X, nb.EPI_NONE, None, nb.PRECISIONS[prec], "word2vec", "outputs")
+        assert out.info()[:2] == (dim, batch)
+        assert rel(out.download_dense(), ref) <= TOL[prec]
