@@ -69,6 +69,7 @@ typedef struct {
     float ms_total;
     float ms_gemm1_kernel; /* the tcgen05 kernel of layer 1 alone                   */
     int refined_rows;     /* rows re-evaluated in fp64                              */
+    int relevel_rows;     /* rows re-run in bf16x3 by the single-pass variant       */
     int kernel_launches;  /* kernels launched by this call                          */
     int splits1;          /* split-K factor used by layer 1                         */
 } nb200_ff_stats;

@@ -33,7 +33,8 @@ EXPORTS = [
 class FFStats(C.Structure):
     _fields_ = [("ms_convert", C.c_float), ("ms_gemm1", C.c_float), ("ms_gemm2", C.c_float),
                 ("ms_softmax", C.c_float), ("ms_refine", C.c_float), ("ms_total", C.c_float),
-                ("ms_gemm1_kernel", C.c_float), ("refined_rows", C.c_int), ("kernel_launches", C.c_int),
+                ("ms_gemm1_kernel", C.c_float), ("refined_rows", C.c_int), ("relevel_rows", C.c_int),
+                ("kernel_launches", C.c_int),
                 ("splits1", C.c_int)]
 
     def as_dict(self):

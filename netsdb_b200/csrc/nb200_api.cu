@@ -143,7 +143,7 @@ static int make_set(const char *db, const char *name, int tr, int tc, int br, in
 
 static float prec_unit(int precision) {
     // unit of the relative rounding error of one product (DESIGN.md "error model")
-    return precision == NB200_PREC_BF16 ? 0.00390625f /* 2^-8 */ : 0.0001220703125f /* 2^-13 */;
+    return precision == NB200_PREC_BF16 ? 0.00390625f /* 2^-8 */ : 1.52587890625e-05f /* 2^-16 */;
 }
 
 }  // namespace nb200
@@ -496,6 +496,42 @@ int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, n
 }
 
 // ---- fused ff::inference_unit -------------------------------------------------------------------
+// One tensor-core forward pass over `rows` rows whose bf16 planes are X:
+//   y1 = relu(X W1^T + b1)  (split-K block GEMM + fused reduce, written as operand planes for layer 2)
+//   logits = y1 Wo^T + bo   (block GEMM with the bias in its epilogue)
+static int tc_forward(Context *c, const Planes &X, int rows, int nterms, nb200_set *w1, nb200_set *wo, const float *b1,
+                      const float *bo, Planes *y1, float *logits, int64_t logits_ld, int H, int Lb, int *splits1,
+                      cudaEvent_t k0, cudaEvent_t k1, cudaEvent_t after_l1) {
+    const bool lo = nterms == 3;
+    int Mpad = 0, Npad = 0, used1 = 1;
+    GemmEpilogue g1;
+    g1.mode = 0;
+    if (k0) NB_CUDA(cudaEventRecord(k0, c->stream));
+    NB_TRY(launch_gemm_tc(c, X, w1->rowp, rows, H, nterms, choose_splits(c, rows, H, X.ldk, nterms), g1, &Mpad, &Npad, &used1));
+    if (k1) NB_CUDA(cudaEventRecord(k1, c->stream));
+    *splits1 = used1;
+    ReduceOut r1;
+    r1.planes = y1;
+    r1.want_lo = lo;
+    NB_TRY(launch_splitk_reduce(c, rows, H, used1, Mpad, Npad, nullptr, b1, 1, r1));
+    if (after_l1) NB_CUDA(cudaEventRecord(after_l1, c->stream));
+    const int splits2 = choose_splits(c, rows, Lb, y1->ldk, nterms);
+    if (splits2 == 1) {
+        GemmEpilogue g2;
+        g2.mode = 1; g2.out = logits; g2.out_ld = logits_ld; g2.bias_n = bo;
+        NB_TRY(launch_gemm_tc(c, *y1, wo->rowp, rows, Lb, nterms, 1, g2, &Mpad, &Npad, nullptr));
+    } else {
+        GemmEpilogue g2;
+        g2.mode = 0;
+        int used2 = splits2;
+        NB_TRY(launch_gemm_tc(c, *y1, wo->rowp, rows, Lb, nterms, splits2, g2, &Mpad, &Npad, &used2));
+        ReduceOut r2;
+        r2.f32 = logits; r2.f32_ld = logits_ld;
+        NB_TRY(launch_splitk_reduce(c, rows, Lb, used2, Mpad, Npad, nullptr, bo, 0, r2));
+    }
+    return NB200_OK;
+}
+
 struct FFScratch {  // reused across calls
     Planes y1;                 // relu(X W1^T + b1) as operand planes, rows = batch, K = hidden
     float *logits = nullptr;   // batch x ld fp32
@@ -508,6 +544,12 @@ struct FFScratch {  // reused across calls
     int64_t cap_rows = 0;
     double *xg = nullptr, *y1g = nullptr, *zg = nullptr;  // fp64 refinement buffers
     size_t xg_bytes = 0, y1g_bytes = 0, zg_bytes = 0;
+    // second cascade level (bf16x3 on the rows the single-pass result left undecided)
+    Planes xsub, y1sub;
+    float *logits_sub = nullptr;
+    size_t logits_sub_bytes = 0;
+    int32_t *list2 = nullptr;
+    int64_t list2_cap = 0;
 };
 static FFScratch g_ff;
 
@@ -562,7 +604,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     }
     cudaEvent_t *ev = c->ev;
     NB_CUDA(cudaEventRecord(ev[0], c->stream));
-    int refined = 0, splits1 = 1;
+    int refined = 0, splits1 = 1, relevel = 0;
     float ms_k1 = 0.f;
 
     if (B == 0 || Lb == 0) {
@@ -588,9 +630,10 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     } else {
         const int nterms = (precision == NB200_PREC_BF16X3) ? 3 : 1;
         const bool lo = nterms == 3;
-        // model side (cached across calls, like a materialised model): weight planes, fp32 biases
-        NB_TRY(ensure_rowp(c, w1, lo));
-        NB_TRY(ensure_rowp(c, wo, lo));
+        // model side (cached across calls, like a materialised model): weight planes, fp32 biases.
+        // The single-pass variant also keeps the residual planes: its undecided rows are re-run in bf16x3.
+        NB_TRY(ensure_rowp(c, w1, true));
+        NB_TRY(ensure_rowp(c, wo, true));
         NB_TRY(ensure_f32(c, b1));
         NB_TRY(ensure_f32(c, bo));
         if (!wo->wo_rownorm_max) NB_CUDA(cudaMalloc(&wo->wo_rownorm_max, sizeof(float)));
@@ -599,54 +642,72 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         // query side: de-blocked fp64 inputs -> bf16 planes
         NB_TRY(ensure_rowp(c, inputs, lo));
         NB_CUDA(cudaEventRecord(ev[1], c->stream));
-        // layer 1: y1 = relu(X W1^T + b1)   [FFTransposeMult + FFAggMatrix + FFReluBiasSum]
-        splits1 = choose_splits(c, B, H, inputs->rowp.ldk, nterms);
-        int Mpad = 0, Npad = 0;
-        GemmEpilogue g1; g1.mode = 0;
-        NB_CUDA(cudaEventRecord(ev[6], c->stream));
-        NB_TRY(launch_gemm_tc(c, inputs->rowp, w1->rowp, B, H, nterms, splits1, g1, &Mpad, &Npad, &splits1));
-        NB_CUDA(cudaEventRecord(ev[7], c->stream));
-        ReduceOut r1; r1.planes = &S.y1; r1.want_lo = lo;
-        NB_TRY(launch_splitk_reduce(c, B, H, splits1, Mpad, Npad, nullptr, b1->f32, 1, r1));
-        NB_CUDA(cudaEventRecord(ev[2], c->stream));
-        // layer 2: z = y1 Wo^T + bo          [FFInputLayerJoin + FFAggMatrix + FFTransposeBiasSum (pre-exp)]
         NB_CUDA(cudaMalloc(&zset->f32, on * sizeof(float)));
         zset->f32_ld = Lb;
-        const int splits2 = choose_splits(c, B, Lb, S.y1.ldk, nterms);
-        if (splits2 == 1) {
-            GemmEpilogue g2; g2.mode = 1; g2.out = zset->f32; g2.out_ld = Lb; g2.bias_n = bo->f32;
-            NB_TRY(launch_gemm_tc(c, S.y1, wo->rowp, B, Lb, nterms, 1, g2, &Mpad, &Npad, nullptr));
-        } else {
-            GemmEpilogue g2; g2.mode = 0;
-            int used2 = splits2;
-            NB_TRY(launch_gemm_tc(c, S.y1, wo->rowp, B, Lb, nterms, splits2, g2, &Mpad, &Npad, &used2));
-            ReduceOut r2; r2.f32 = zset->f32; r2.f32_ld = Lb;
-            NB_TRY(launch_splitk_reduce(c, B, Lb, used2, Mpad, Npad, nullptr, bo->f32, 0, r2));
-        }
+        // level 1 on every row
+        NB_TRY(tc_forward(c, inputs->rowp, B, nterms, w1, wo, b1->f32, bo->f32, &S.y1, zset->f32, Lb, H, Lb, &splits1,
+                          ev[6], ev[7], ev[2]));
         NB_CUDA(cudaEventRecord(ev[3], c->stream));
         // FFRowAggregate + FFOutputLayer + label, and the near-tie scan
         NB_TRY(launch_softmax_rows(c, zset->f32, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, nullptr, 0, 0));
         NB_CUDA(cudaMemsetAsync(S.count, 0, sizeof(int), c->stream));
         NB_TRY(launch_flag_rows(c, B, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs, wo->rowp.maxabs,
-                                wo->wo_rownorm_max, prec_unit(precision), 4.0f, S.list, S.count, B));
+                                wo->wo_rownorm_max, prec_unit(precision), 4.0f, S.list, S.count, B, nullptr));
         NB_CUDA(cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaEventRecord(ev[4], c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        refined = std::min(*S.count_host, B);
-        // fp64 re-evaluation of the flagged rows (K9), in chunks that bound the gather buffer
+        int n1 = std::min(*S.count_host, B);
+        const int32_t *final_list = S.list;
+        refined = n1;
+        if (precision == NB200_PREC_BF16 && n1 > 0) {
+            // level 2: bf16x3 on the undecided rows only (gathered straight from the fp64 inputs)
+            if (S.list2_cap < B) {
+                cudaFree(S.list2);
+                NB_CUDA(cudaMalloc(&S.list2, static_cast<size_t>(B) * sizeof(int32_t)));
+                S.list2_cap = B;
+            }
+            NB_CUDA(cudaMemsetAsync(S.count, 0, sizeof(int), c->stream));
+            const int chunk2 = 8192;
+            for (int r0 = 0; r0 < n1; r0 += chunk2) {
+                const int R = std::min(chunk2, n1 - r0);
+                NB_TRY(launch_gather_convert_rows(c, inputs->f64, F, F, S.list + r0, R, &S.xsub));
+                const size_t need = static_cast<size_t>(R) * Lb * sizeof(float);
+                if (need > S.logits_sub_bytes) {
+                    cudaFree(S.logits_sub);
+                    S.logits_sub = nullptr;
+                    S.logits_sub_bytes = 0;
+                    NB_CUDA(cudaMalloc(&S.logits_sub, need));
+                    S.logits_sub_bytes = need;
+                }
+                int dummy = 0;
+                NB_TRY(tc_forward(c, S.xsub, R, 3, w1, wo, b1->f32, bo->f32, &S.y1sub, S.logits_sub, Lb, H, Lb, &dummy,
+                                  nullptr, nullptr, nullptr));
+                NB_TRY(launch_scatter_rows_f32(c, S.logits_sub, Lb, Lb, S.list + r0, R, zset->f32, Lb));
+                NB_TRY(launch_softmax_rows(c, S.logits_sub, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, S.list + r0, R, 1));
+                NB_TRY(launch_flag_rows(c, R, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs,
+                                        wo->rowp.maxabs, wo->wo_rownorm_max, prec_unit(NB200_PREC_BF16X3), 4.0f, S.list2,
+                                        S.count, B, S.list + r0));
+            }
+            NB_CUDA(cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            refined = std::min(*S.count_host, B);
+            final_list = S.list2;
+            relevel = n1;
+        }
+        // last level: fp64 re-evaluation of what is still undecided (K9), in chunks that bound the gather buffer
         const int chunk = 256;
         for (int r0 = 0; r0 < refined; r0 += chunk) {
             const int R = std::min(chunk, refined - r0);
             NB_TRY(grow(&S.xg, &S.xg_bytes, static_cast<size_t>(chunk) * F * sizeof(double)));
             NB_TRY(grow(&S.y1g, &S.y1g_bytes, static_cast<size_t>(chunk) * H * sizeof(double)));
             NB_TRY(grow(&S.zg, &S.zg_bytes, static_cast<size_t>(chunk) * Lb * sizeof(double)));
-            NB_TRY(launch_gather_rows_f64(c, inputs->f64, F, F, S.list + r0, R, S.xg));
+            NB_TRY(launch_gather_rows_f64(c, inputs->f64, F, F, final_list + r0, R, S.xg));
             F64Epilogue e1; e1.bias_n = b1->f64; e1.relu = 1;
             NB_TRY(launch_gemm_f64(c, S.xg, F, 1, w1->f64, F, 1, R, H, F, S.y1g, H, e1));
             F64Epilogue e2; e2.bias_n = bo->f64;
             NB_TRY(launch_gemm_f64(c, S.y1g, H, 1, wo->f64, H, 1, R, Lb, H, S.zg, Lb, e2));
-            NB_TRY(launch_scatter_rows(c, S.zg, Lb, S.list + r0, R, zset->f32, Lb));
-            NB_TRY(launch_softmax_rows(c, S.zg, true, B, Lb, Lb, o->f64, Lb, S.labels, nullptr, S.list + r0, R, 1));
+            NB_TRY(launch_scatter_rows(c, S.zg, Lb, final_list + r0, R, zset->f32, Lb));
+            NB_TRY(launch_softmax_rows(c, S.zg, true, B, Lb, Lb, o->f64, Lb, S.labels, nullptr, final_list + r0, R, 1));
         }
         NB_CUDA(cudaEventRecord(ev[5], c->stream));
     }
@@ -663,6 +724,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         if (precision != NB200_PREC_FP64) cudaEventElapsedTime(&ms_k1, ev[6], ev[7]);
         stats->ms_gemm1_kernel = ms_k1;
         stats->refined_rows = refined;
+        stats->relevel_rows = relevel;
         stats->kernel_launches = static_cast<int>(c->launches - launches0);
         stats->splits1 = splits1;
     }

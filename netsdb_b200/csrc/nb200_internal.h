@@ -56,6 +56,7 @@ struct Planes {
     __nv_bfloat16 *hi = nullptr;
     __nv_bfloat16 *lo = nullptr;  // residual plane (x - bf16(x)), only for BF16X3
     int64_t rows = 0, k = 0, ldk = 0;
+    int64_t cap_rows = 0;         // allocated rows (>= rows); scratch planes are reused across calls
     float *row_sumsq = nullptr;   // per row sum of squares of the source values
     float *maxabs = nullptr;      // device scalar: max |value|
     bool valid = false, lo_valid = false;
@@ -116,7 +117,11 @@ int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t row
 // flag rows whose top-2 gap is inside tau * eps_r; appends to list, counts in *count
 int launch_flag_rows(Context *c, int64_t rows, const float *gap, const float *x_sumsq, const float *y_sumsq,
                      const float *w1_maxabs, const float *wo_maxabs, const float *wo_rownorm_max, float u, float tau,
-                     int32_t *list, int *count, int max_list);
+                     int32_t *list, int *count, int max_list, const int32_t *src_list);
+int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
+                               Planes *p);
+int launch_scatter_rows_f32(Context *c, const float *src, int64_t src_ld, int64_t cols, const int32_t *list, int n,
+                            float *dst, int64_t dst_ld);
 int launch_gather_rows_f64(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
                            double *dst);
 int launch_max_rownorm(Context *c, const float *row_sumsq, int64_t rows, float *out_scalar);

@@ -112,15 +112,16 @@ k_convert_planes(const T *__restrict__ src, long long ld, long long cols, __nv_b
 
 static int alloc_planes(Planes *p, int64_t rows, int64_t k, bool want_lo) {
     const int64_t ldk = round_up(k, 64);
-    if (p->hi && (p->rows != rows || p->ldk != ldk)) {
+    if (p->hi && (p->cap_rows < rows || p->ldk != ldk)) {
         cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
         *p = Planes();
     }
+    if (!p->hi) p->cap_rows = rows;
     p->rows = rows; p->k = k; p->ldk = ldk;
-    const size_t bytes = static_cast<size_t>(rows) * ldk * sizeof(__nv_bfloat16);
+    const size_t bytes = static_cast<size_t>(p->cap_rows ? p->cap_rows : 1) * ldk * sizeof(__nv_bfloat16);
     if (!p->hi) NB_CUDA(cudaMalloc(&p->hi, bytes));
     if (want_lo && !p->lo) NB_CUDA(cudaMalloc(&p->lo, bytes));
-    if (!p->row_sumsq) NB_CUDA(cudaMalloc(&p->row_sumsq, static_cast<size_t>(rows) * sizeof(float)));
+    if (!p->row_sumsq) NB_CUDA(cudaMalloc(&p->row_sumsq, static_cast<size_t>(p->cap_rows ? p->cap_rows : 1) * sizeof(float)));
     if (!p->maxabs) NB_CUDA(cudaMalloc(&p->maxabs, sizeof(float)));
     return NB200_OK;
 }
@@ -201,6 +202,51 @@ int launch_convert_planes_t(Context *c, const void *src, bool src_is_f64, int64_
     NB_LAUNCH_CHECK(c);
     p->valid = true;
     p->lo_valid = want_lo;
+    return NB200_OK;
+}
+
+
+// Gather the listed rows of an fp64 matrix straight into compact bf16 hi/lo planes (the inputs of the
+// second cascade level): plane row i = source row list[i].
+__global__ void __launch_bounds__(kCvtThreads)
+k_gather_convert_rows(const double *__restrict__ src, long long ld, long long cols, const int32_t *__restrict__ list,
+                      __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo, long long ldk) {
+    const long long i = blockIdx.x;
+    const double *srow = src + static_cast<long long>(list[i]) * ld;
+    for (long long c = (static_cast<long long>(blockIdx.y) * kCvtThreads + threadIdx.x) * 4; c < ldk;
+         c += static_cast<long long>(gridDim.y) * kCvtThreads * 4) {
+        __nv_bfloat16 h4[4], l4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) split_bf16<double>((c + j < cols) ? srow[c + j] : 0.0, h4[j], l4[j]);
+        *reinterpret_cast<uint2 *>(hi + i * ldk + c) = *reinterpret_cast<uint2 *>(h4);
+        *reinterpret_cast<uint2 *>(lo + i * ldk + c) = *reinterpret_cast<uint2 *>(l4);
+    }
+}
+int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
+                               Planes *p) {
+    NB_TRY(alloc_planes(p, n, cols, true));
+    p->valid = p->lo_valid = true;
+    if (n == 0) return NB200_OK;
+    const int64_t chunks = ceil_div(p->ldk, kCvtThreads * 4);
+    dim3 grid(n, static_cast<unsigned>(chunks < 64 ? chunks : 64));
+    k_gather_convert_rows<<<grid, kCvtThreads, 0, c->stream>>>(src, ld, cols, list, p->hi, p->lo, p->ldk);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+// compact fp32 rows -> rows list[i] of a larger fp32 matrix
+__global__ void k_scatter_rows_f32(const float *__restrict__ src, long long src_ld, long long cols,
+                                   const int32_t *__restrict__ list, float *__restrict__ dst, long long dst_ld) {
+    const long long r = list[blockIdx.y];
+    for (long long j = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; j < cols;
+         j += static_cast<long long>(gridDim.x) * blockDim.x)
+        dst[r * dst_ld + j] = src[static_cast<long long>(blockIdx.y) * src_ld + j];
+}
+int launch_scatter_rows_f32(Context *c, const float *src, int64_t src_ld, int64_t cols, const int32_t *list, int n,
+                            float *dst, int64_t dst_ld) {
+    if (n == 0 || cols == 0) return NB200_OK;
+    dim3 grid(static_cast<unsigned>(ceil_div(cols, 256) < 64 ? ceil_div(cols, 256) : 64), n);
+    k_scatter_rows_f32<<<grid, 256, 0, c->stream>>>(src, src_ld, cols, list, dst, dst_ld);
+    NB_LAUNCH_CHECK(c);
     return NB200_OK;
 }
 
@@ -433,6 +479,110 @@ k_gemm_f64(const double *__restrict__ u, long long u_sm, long long u_sk, const d
             }
         }
 }
+
+// ---------------------------------------------------------------------------------------------
+// fp64 GEMM on the DMMA tensor path (mma.sync.m8n8k4.f64): P[M x N] (+)= U[M x K] . V[N x K]^T with
+// both operands K-contiguous.  Used to re-evaluate near-tie rows (K9): M is the handful of flagged
+// rows, N the hidden width, K the full feature count, so the grid is (N tiles, M tiles, K splits)
+// and split partials are combined with fp64 atomics into a zeroed P.
+// Fragment layout of m8n8k4 (row.col): lane t holds A[t/4][t%4], B[t%4][t/4], C[t/4][2*(t%4) + {0,1}].
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// 128 threads = 4 warps arranged WARPS_M x WARPS_N, each warp computes a (8*MT) x 32 tile.
+template <int MT, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(128)
+k_gemm_f64_mma(const double *__restrict__ u, long long u_ld, const double *__restrict__ v, long long v_ld, int M, int N,
+               long long K, long long k_per_split, double *__restrict__ out, long long out_ld) {
+    constexpr int BM = 8 * MT * WARPS_M, BN = 32 * WARPS_N, BK = 16, LDS = BK + 4;  // +4: conflict-free fragment reads
+    static_assert(WARPS_M * WARPS_N == 4, "4 warps");
+    __shared__ double su[2][BM * LDS];
+    __shared__ double sv[2][BN * LDS];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp / WARPS_N, wn = warp % WARPS_N;
+    const long long m0 = static_cast<long long>(blockIdx.y) * BM, n0 = static_cast<long long>(blockIdx.x) * BN;
+    const long long kbeg = static_cast<long long>(blockIdx.z) * k_per_split;
+    const long long kend = (kbeg + k_per_split < K) ? kbeg + k_per_split : K;
+    double acc[MT][4][2];
+#pragma unroll
+    for (int i = 0; i < MT; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    constexpr int U_ELEMS = BM * BK / 128, V_ELEMS = BN * BK / 128;  // doubles per thread per stage
+    double ru[U_ELEMS], rv[V_ELEMS];
+    auto gload = [&](long long k0) {
+#pragma unroll
+        for (int e = 0; e < U_ELEMS; e++) {
+            const int idx = e * 128 + tid, r = idx / BK, kk = idx % BK;
+            const long long gm = m0 + r, gk = k0 + kk;
+            ru[e] = (gm < M && gk < kend) ? u[gm * u_ld + gk] : 0.0;
+        }
+#pragma unroll
+        for (int e = 0; e < V_ELEMS; e++) {
+            const int idx = e * 128 + tid, r = idx / BK, kk = idx % BK;
+            const long long gn = n0 + r, gk = k0 + kk;
+            rv[e] = (gn < N && gk < kend) ? v[gn * v_ld + gk] : 0.0;
+        }
+    };
+    auto sstore = [&](int buf) {
+#pragma unroll
+        for (int e = 0; e < U_ELEMS; e++) {
+            const int idx = e * 128 + tid;
+            su[buf][(idx / BK) * LDS + idx % BK] = ru[e];
+        }
+#pragma unroll
+        for (int e = 0; e < V_ELEMS; e++) {
+            const int idx = e * 128 + tid;
+            sv[buf][(idx / BK) * LDS + idx % BK] = rv[e];
+        }
+    };
+    int buf = 0;
+    if (kbeg < kend) {
+        gload(kbeg);
+        sstore(0);
+    }
+    __syncthreads();
+    for (long long k0 = kbeg; k0 < kend; k0 += BK) {
+        const bool more = k0 + BK < kend;
+        if (more) gload(k0 + BK);  // global loads in flight while the tensor pipe works
+        const double *pu = su[buf] + (wm * 8 * MT + lane / 4) * LDS + lane % 4;
+        const double *pv = sv[buf] + (wn * 32 + lane / 4) * LDS + lane % 4;
+#pragma unroll
+        for (int ks = 0; ks < BK; ks += 4) {
+            double a[MT], b[4];
+#pragma unroll
+            for (int i = 0; i < MT; i++) a[i] = pu[i * 8 * LDS + ks];
+#pragma unroll
+            for (int j = 0; j < 4; j++) b[j] = pv[j * 8 * LDS + ks];
+#pragma unroll
+            for (int i = 0; i < MT; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) dmma_m8n8k4(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        if (more) sstore(buf ^ 1);
+        __syncthreads();
+        buf ^= 1;
+    }
+#pragma unroll
+    for (int i = 0; i < MT; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const long long gm = m0 + wm * 8 * MT + i * 8 + lane / 4;
+                const long long gn = n0 + wn * 32 + j * 8 + 2 * (lane % 4) + e;
+                if (gm < M && gn < N) {
+                    if (gridDim.z == 1) out[gm * out_ld + gn] = acc[i][j][e];
+                    else atomicAdd(out + gm * out_ld + gn, acc[i][j][e]);
+                }
+            }
+}
+
 __global__ void k_bias_relu_f64(double *__restrict__ p, int M, int N, long long ld, const double *__restrict__ bias_m,
                                 const double *__restrict__ bias_n, int relu) {
     const long long n = static_cast<long long>(M) * N;
@@ -449,6 +599,33 @@ __global__ void k_bias_relu_f64(double *__restrict__ p, int M, int N, long long 
 int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, const double *v, int64_t v_sn,
                     int64_t v_sk, int M, int N, int64_t K, double *out, int64_t out_ld, const F64Epilogue &e) {
     if (M == 0 || N == 0) return NB200_OK;
+    if (u_sk == 1 && v_sk == 1) {  // both K-contiguous: tensor (DMMA) path
+        const bool small = M <= 16;
+        const int BMm = small ? 16 : 64, BNm = small ? 128 : 64;
+        const int64_t tiles = ceil_div(M, BMm) * ceil_div(N, BNm);
+        const int sms = c->sm_count > 0 ? c->sm_count : 148;
+        int splits = 1;
+        if (tiles < 4 * sms && K >= 4096) {
+            splits = static_cast<int>(ceil_div(4 * sms, tiles));
+            const int64_t maxs = K / 2048;
+            if (splits > maxs) splits = static_cast<int>(maxs);
+            if (splits < 1) splits = 1;
+        }
+        const int64_t kper = round_up(ceil_div(K, splits), 16);
+        splits = static_cast<int>(ceil_div(K, kper));
+        if (splits > 1) NB_CUDA(cudaMemset2DAsync(out, out_ld * sizeof(double), 0, static_cast<size_t>(N) * sizeof(double), M, c->stream));
+        dim3 grid(static_cast<unsigned>(ceil_div(N, BNm)), static_cast<unsigned>(ceil_div(M, BMm)), splits);
+        if (small) k_gemm_f64_mma<2, 1, 4><<<grid, 128, 0, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kper, out, out_ld);
+        else k_gemm_f64_mma<4, 2, 2><<<grid, 128, 0, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kper, out, out_ld);
+        NB_LAUNCH_CHECK(c);
+        if (e.bias_m || e.bias_n || e.relu) {
+            const int64_t n = static_cast<int64_t>(M) * N;
+            const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+            k_bias_relu_f64<<<blocks, 256, 0, c->stream>>>(out, M, N, out_ld, e.bias_m, e.bias_n, e.relu);
+            NB_LAUNCH_CHECK(c);
+        }
+        return NB200_OK;
+    }
     const bool skinny = M <= 16;
     const int BM = skinny ? 16 : 64, BN = skinny ? 256 : 64;
     const int64_t tiles = ceil_div(M, BM) * ceil_div(N, BN);
@@ -576,9 +753,11 @@ int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t row
 __global__ void k_flag_rows(long long rows, const float *__restrict__ gap, const float *__restrict__ x_sumsq,
                             const float *__restrict__ y_sumsq, const float *__restrict__ w1_maxabs,
                             const float *__restrict__ wo_maxabs, const float *__restrict__ wo_rownorm_max, float u,
-                            float tau, int32_t *__restrict__ list, int *__restrict__ count, int max_list) {
-    const long long r = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
-    if (r >= rows) return;
+                            float tau, int32_t *__restrict__ list, int *__restrict__ count, int max_list,
+                            const int32_t *__restrict__ src_list) {
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= rows) return;
+    const long long r = src_list ? src_list[i] : i;  // src_list: only re-examine those rows
     const float eps = u * (sqrtf(y_sumsq[r]) * (*wo_maxabs) + sqrtf(x_sumsq[r]) * (*w1_maxabs) * (*wo_rownorm_max));
     if (!(gap[r] >= tau * eps)) {  // also catches NaN
         const int slot = atomicAdd(count, 1);
@@ -587,9 +766,9 @@ __global__ void k_flag_rows(long long rows, const float *__restrict__ gap, const
 }
 int launch_flag_rows(Context *c, int64_t rows, const float *gap, const float *x_sumsq, const float *y_sumsq,
                      const float *w1_maxabs, const float *wo_maxabs, const float *wo_rownorm_max, float u, float tau,
-                     int32_t *list, int *count, int max_list) {
+                     int32_t *list, int *count, int max_list, const int32_t *src_list) {
     if (rows == 0) return NB200_OK;
-    k_flag_rows<<<static_cast<unsigned>(ceil_div(rows, 256)), 256, 0, c->stream>>>(rows, gap, x_sumsq, y_sumsq, w1_maxabs, wo_maxabs, wo_rownorm_max, u, tau, list, count, max_list);
+    k_flag_rows<<<static_cast<unsigned>(ceil_div(rows, 256)), 256, 0, c->stream>>>(rows, gap, x_sumsq, y_sumsq, w1_maxabs, wo_maxabs, wo_rownorm_max, u, tau, list, count, max_list, src_list);
     NB_LAUNCH_CHECK(c);
     return NB200_OK;
 }
