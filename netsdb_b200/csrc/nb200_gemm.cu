@@ -17,6 +17,9 @@
 #include "nb200_internal.h"
 #include "nb200_ptx.cuh"
 
+#include <cstdlib>
+#include <cstring>
+
 namespace nb200 {
 
 constexpr int kBlockM = 128;
@@ -189,6 +192,171 @@ k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// 2-SM variant (tcgen05 cta_group::2).  A CTA pair (cluster of 2) owns one 256 x BN output tile:
+// each CTA loads its own 128 rows of U and HALF of the V tile; the leader's single MMA thread issues
+// M = 256 instructions that read both CTAs' shared memory and write both CTAs' TMEM.  Per SM and
+// 64-wide K step that is 16 KB (U) + BN/2 x 128 B (V) of shared-memory fill for BN/256 x 512 MMA
+// cycles: 64 B/cycle at BN = 256 and 47 B/cycle at BN = 512, against 96 B/cycle for the 1-SM
+// 128 x 256 tile -- the 1-SM kernel is bound by L2 -> SM bandwidth at about half of tensor peak
+// (profiles/r01_*).  BN = 512 uses all 512 TMEM columns (two N = 256 accumulators).
+//
+// Column bookkeeping: CTA r holds V rows [r*BN/2, (r+1)*BN/2) of the tile as NSUB chunks of 128;
+// MMA `sub` consumes chunk `sub` of both CTAs, so TMEM column t = sub*256 + j maps to tile column
+// (j < 128 ? sub*128 + j : BN/2 + sub*128 + j - 128).
+// ---------------------------------------------------------------------------------------------
+template <int NSUB, int STAGES>
+struct SmemLayout2 {
+    static constexpr int BN = 256 * NSUB;
+    static constexpr uint32_t kBBytes = (BN / 2) * kBlockK * 2;
+    static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+    static constexpr uint32_t kBarOffset = STAGES * kStageBytes;
+    static constexpr uint32_t kTotal = kBarOffset + (2 * STAGES + 1) * 8 + 16 + 1024;
+};
+
+template <int NSUB, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant__ CUtensorMap map_u_lo,
+                 const __grid_constant__ CUtensorMap map_v_hi, const __grid_constant__ CUtensorMap map_v_lo,
+                 const GemmArgs g) {
+    using L = SmemLayout2<NSUB, STAGES>;
+    constexpr int BN = L::BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + L::kBarOffset);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tmem_full_bar = empty_bar + STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int pair = blockIdx.x >> 1;
+    const int tile_m = pair / g.tiles_n;
+    const int tile_n = pair % g.tiles_n;
+    const int split = blockIdx.y;
+    const int kb0 = split * g.kb_per_split;
+    const int kb1 = min(kb0 + g.kb_per_split, g.num_kb);
+    const int n_iter = max(kb1 - kb0, 0) * g.nterms;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_u_hi);
+        tma_prefetch_desc(&map_v_hi);
+        if (g.nterms > 1) {
+            tma_prefetch_desc(&map_u_lo);
+            tma_prefetch_desc(&map_v_lo);
+        }
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full_bar[s], 2);   // leader's arrive.expect_tx + the peer's remote arrive
+            mbar_init(&empty_bar[s], 1);  // the leader's multicast commit
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {  // one warp of EACH CTA of the pair takes part in the 2-SM allocation
+        tmem_alloc_2sm(tmem_slot, BN);
+        tmem_relinquish_2sm();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs) =====
+        if (lane == 0) {
+            for (int it = 0; it < n_iter; it++) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                if (!mbar_wait(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 201); break; }
+                const int kb = kb0 + it / g.nterms;
+                const int t = it % g.nterms;
+                const CUtensorMap *mu = (t == 2) ? &map_u_lo : &map_u_hi;
+                const CUtensorMap *mv = (t == 1) ? &map_v_lo : &map_v_hi;
+                uint8_t *sa = smem + s * L::kStageBytes;
+                uint8_t *sb = sa + kABytes;
+                if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * L::kStageBytes);
+                else mbar_arrive_remote(&full_bar[s], 0);
+                tma_load_2d_2sm(mu, &full_bar[s], sa, kb * kBlockK, tile_m * 256 + static_cast<int>(rank) * kBlockM,
+                                kEvictNormal);
+                tma_load_2d_2sm(mv, &full_bar[s], sb, kb * kBlockK, tile_n * BN + static_cast<int>(rank) * (BN / 2),
+                                kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one thread of the leader CTA =====
+        if (leader && lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(256, 256);
+            bool ok = true;
+            for (int it = 0; it < n_iter && ok; it++) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                if (!mbar_wait(&full_bar[s], ph)) { atomicExch(g.err_flag, 202); ok = false; break; }
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + s * L::kStageBytes);
+                const uint32_t sb = sa + kABytes;
+                const uint64_t da = umma_desc_k_sw128(sa);
+#pragma unroll
+                for (int k = 0; k < kBlockK / kUmmaK; k++) {
+#pragma unroll
+                    for (int sub = 0; sub < NSUB; sub++) {
+                        const uint64_t db = umma_desc_k_sw128(sb + sub * (128 * kBlockK * 2));
+                        umma_f16_2sm(tmem_base + sub * 256, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    }
+                }
+                umma_commit_2sm(&empty_bar[s], 0x3);  // frees the slot in BOTH CTAs
+            }
+            umma_commit_2sm(tmem_full_bar, 0x3);
+        }
+    } else {
+        // ===== epilogue warps (both CTAs drain their own 128 TMEM lanes) =====
+        const int q = warp & 3;
+        const long long row = static_cast<long long>(tile_m) * 256 + rank * kBlockM + q * 32 + lane;
+        bool ok = mbar_wait(tmem_full_bar, 0);
+        if (!ok && lane == 0) atomicExch(g.err_flag, 203);
+        ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+        tc_fence_after();
+        if (ok) {
+            const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+            const float bm = (g.mode == 1 && g.bias_m != nullptr && row < g.M) ? g.bias_m[row] : 0.f;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c++) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(lane_addr + c * 32, r);
+                tmem_ld_wait();
+                const int sub = (c * 32) / 256, j = (c * 32) % 256;
+                const int tcol = (j < 128) ? sub * 128 + j : BN / 2 + sub * 128 + (j - 128);
+                const int col0 = tile_n * BN + tcol;
+                if (g.mode == 0) {
+                    float *dst = g.ws + split * g.ws_split_stride + row * g.ws_ld + col0;
+#pragma unroll
+                    for (int jj = 0; jj < 32; jj += 4)
+                        *reinterpret_cast<uint4 *>(dst + jj) = make_uint4(r[jj], r[jj + 1], r[jj + 2], r[jj + 3]);
+                } else if (row < g.M) {
+                    float *dst = g.out + row * g.out_ld + col0;
+#pragma unroll
+                    for (int jj = 0; jj < 32; jj++) {
+                        if (col0 + jj < g.N) {
+                            float v = __uint_as_float(r[jj]) + bm;
+                            if (g.bias_n != nullptr) v += g.bias_n[col0 + jj];
+                            if (g.relu) v = fmaxf(v, 0.f);
+                            dst[jj] = v;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();  // the peer's TMEM / smem must not go away while the leader's MMAs use them
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2sm(tmem_base, BN);
+    }
+}
+
 // ---- host side -----------------------------------------------------------------------------------
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -232,24 +400,64 @@ static int make_plane_map(CUtensorMap *m, const __nv_bfloat16 *base, int64_t row
 // Split-K factor: the skinny FF shapes (Amazon-14K layer 1: 79 x 4 tiles, K = 597,540) have far
 // fewer output tiles than SMs x waves, so K is cut until the grid is a whole number of waves and
 // every CTA still runs a long (>= 32 K-block) main loop.
+static int pick_kernel(int M, int N, int64_t ldk);
+
 int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms) {
     (void)nterms;
-    const int64_t tiles = ceil_div(M, kBlockM) * ceil_div(N, 256);
+    const int kind = pick_kernel(M, N, ldk);
+    const int BN = kind == 2 ? 512 : (kind == 1 ? 256 : ((N <= 128) ? 128 : 256));
+    const int BM = kind == 0 ? kBlockM : 256;
+    const int64_t tiles = ceil_div(M, BM) * ceil_div(N, BN);
     const int64_t num_kb = ldk / kBlockK;
-    const int sms = c->sm_count > 0 ? c->sm_count : 148;
-    if (tiles >= 4 * sms || num_kb < 64) return 1;
+    int units = c->sm_count > 0 ? c->sm_count : 148;  // concurrently resident tiles
+    if (kind != 0) units /= 2;
+    if (tiles >= 4 * units || num_kb < 64) return 1;
     int best = 1;
     double best_cost = 1e30;
     const int max_s = static_cast<int>(num_kb / 32 > 0 ? (num_kb / 32 < 256 ? num_kb / 32 : 256) : 1);
     for (int s = 1; s <= max_s; s++) {
         const int64_t per = ceil_div(num_kb, s);
         if (ceil_div(num_kb, per) != s) continue;  // would leave an empty split
-        const int64_t waves = ceil_div(tiles * s, sms);
-        // time ~ waves * (main loop + fixed per-CTA cost) + reduction traffic
-        const double cost = waves * (per + 6.0) + 0.02 * s;
+        const int64_t waves = ceil_div(tiles * s, units);
+        // time ~ waves * (main loop + fixed per-CTA prologue/epilogue) + reduction traffic
+        const double cost = waves * (per + 8.0) + 0.02 * s;
         if (cost < best_cost) { best_cost = cost; best = s; }
     }
     return best;
+}
+
+template <int NSUB, int STAGES>
+static int launch_impl_2sm(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
+                           const CUtensorMap &mv_lo, const GemmArgs &g, int pair_tiles, int splits) {
+    using L = SmemLayout2<NSUB, STAGES>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NB_CUDA(cudaFuncSetAttribute(k_block_gemm_2sm<NSUB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    dim3 grid(2 * pair_tiles, splits);
+    k_block_gemm_2sm<NSUB, STAGES><<<grid, kThreads, L::kTotal, c->stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+// Which kernel / tile for a shape.  NB200_GEMM_KERNEL=1sm|2sm256|2sm512 overrides (experiments).
+static int pick_kernel(int M, int N, int64_t ldk) {
+    static int forced = -2;
+    if (forced == -2) {
+        const char *e = getenv("NB200_GEMM_KERNEL");
+        forced = -1;
+        if (e) {
+            if (!strcmp(e, "1sm")) forced = 0;
+            else if (!strcmp(e, "2sm256")) forced = 1;
+            else if (!strcmp(e, "2sm512")) forced = 2;
+        }
+    }
+    if (forced >= 0) return forced;
+    if (M <= 128 || N <= 128) return 0;          // a pair tile would be mostly padding
+    if (ldk >= 4096) return N > 256 ? 2 : 1;     // long K: the L2 -> SM fill rate decides
+    return 0;
 }
 
 template <int BN, int STAGES>
@@ -279,9 +487,11 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
         set_error("block GEMM: BF16X3 needs the residual planes");
         return NB200_ERR_STATE;
     }
-    const int BN = (N <= 128) ? 128 : 256;
-    const int tiles_m = static_cast<int>(ceil_div(M, kBlockM)), tiles_n = static_cast<int>(ceil_div(N, BN));
-    const int Mpad = tiles_m * kBlockM, Npad = tiles_n * BN;
+    const int kind = pick_kernel(M, N, u.ldk);  // 0: 1-SM 128 x {128,256}; 1: 2-SM 256 x 256; 2: 2-SM 256 x 512
+    const int BN = kind == 2 ? 512 : (kind == 1 ? 256 : ((N <= 128) ? 128 : 256));
+    const int BM = kind == 0 ? kBlockM : 256;
+    const int tiles_m = static_cast<int>(ceil_div(M, BM)), tiles_n = static_cast<int>(ceil_div(N, BN));
+    const int Mpad = tiles_m * BM, Npad = tiles_n * BN;
     if (Mpad_out) *Mpad_out = Mpad;
     if (Npad_out) *Npad_out = Npad;
     const int num_kb = static_cast<int>(u.ldk / kBlockK);
@@ -311,15 +521,18 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     g.err_flag = c->err_flag;
 
     CUtensorMap mu_hi, mu_lo, mv_hi, mv_lo;
+    const int v_box = kind == 0 ? BN : BN / 2;  // the 2-SM kernels load half of the V tile per CTA
     NB_TRY(make_plane_map(&mu_hi, u.hi, u.rows, u.ldk, kBlockM));
-    NB_TRY(make_plane_map(&mv_hi, v.hi, v.rows, v.ldk, BN));
+    NB_TRY(make_plane_map(&mv_hi, v.hi, v.rows, v.ldk, v_box));
     if (nterms == 3) {
         NB_TRY(make_plane_map(&mu_lo, u.lo, u.rows, u.ldk, kBlockM));
-        NB_TRY(make_plane_map(&mv_lo, v.lo, v.rows, v.ldk, BN));
+        NB_TRY(make_plane_map(&mv_lo, v.lo, v.rows, v.ldk, v_box));
     } else {
         mu_lo = mu_hi;
         mv_lo = mv_hi;
     }
+    if (kind == 2) return launch_impl_2sm<2, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
+    if (kind == 1) return launch_impl_2sm<1, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
     if (BN == 256) return launch_impl<256, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
     return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
 }
