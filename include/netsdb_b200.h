@@ -161,6 +161,34 @@ int nb200_conv2d_fused(const double *images_host, int n, int c, int h, int w, co
                        const double *bias_host, int kout, int k, int padding, int relu, int precision,
                        int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out);
 
+/* ---- allocation-free variant ----------------------------------------------------------------------
+ * This entry point has no counterpart in the reference.
+ *
+ * C[I x J] = A[I x K] . B[J x K]^T -- the FFTransposeMult + FFAggMatrix product -- for callers that are
+ * not allowed to allocate device memory: a pipeline thread that lives inside an HBM arena the engine's
+ * buffer pool sized up front, a call site between cudaStreamBeginCapture/EndCapture, or a serving
+ * thread that cannot afford cudaMalloc's device-wide synchronisation.  The regular entry points grow a
+ * split-K workspace and operand planes with cudaMalloc on demand; this one keeps that scratch in a
+ * fixed array inside the library image instead and calls no cudaMalloc, cudaFree or allocating library
+ * routine.  It does not need nb200_init.
+ *
+ * a_dev, b_dev, c_dev are DEVICE pointers to row-major fp64 matrices (pitches lda, ldb, ldc in
+ * elements) on the current device; the work is queued on cuda_stream (a cudaStream_t, NULL = default
+ * stream) and the call returns without waiting.  Arithmetic is the single-pass bf16 tensor-core block
+ * GEMM (same as NB200_PREC_BF16, without the near-tie cascade).
+ *
+ * Limits and rules:
+ *  - scratch needed = bf16 copies of A and B (K rounded up to 64) + split-K partial tiles; it must fit
+ *    NB200_NOALLOC_SCRATCH_BYTES (64 MiB, held by every GPU that loads the library until exit).  Larger
+ *    requests are refused with NB200_ERR_INVALID and a message stating need and limit.
+ *  - the first call on a device looks up the scratch array's device address and sets kernel attributes;
+ *    make that first call before any stream capture.
+ *  - all calls share the one array, which still holds the previous call's data: calls whose GPU work
+ *    can overlap (different streams, different threads) race and must be serialised by the caller. */
+#define NB200_NOALLOC_SCRATCH_BYTES (64u << 20)
+int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, const double *b_dev, int64_t ldb, int I, int J,
+                                 int K, double *c_dev, int64_t ldc, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

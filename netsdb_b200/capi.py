@@ -26,7 +26,7 @@ EXPORTS = [
     "nb200_set_lookup", "nb200_set_destroy", "nb200_set_info", "nb200_upload_block", "nb200_upload_rect",
     "nb200_download_block", "nb200_download_rect", "nb200_set_fill_synth", "nb200_set_invalidate_planes",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
-    "nb200_conv2d_kernel_flat", "nb200_conv2d_fused",
+    "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
 ]
 
 
@@ -84,6 +84,7 @@ def lib():
         L.nb200_conv2d_kernel_flat.argtypes = [vp, vp, i, i, i, i, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_conv2d_fused.argtypes = [vp, i, i, i, i, vp, vp, i, i, i, i, i, i, i, C.c_char_p, C.c_char_p,
                                          C.POINTER(vp)]
+        L.nb200_transpose_mult_noalloc.argtypes = [vp, i64, vp, i64, i, i, i, vp, i64, vp]
         _lib = L
     return _lib
 

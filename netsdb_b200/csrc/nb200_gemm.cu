@@ -537,4 +537,125 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Allocation-free FFTransposeMult + FFAggMatrix product (nb200_transpose_mult_noalloc).
+//
+// Some callers may not allocate: a pipeline thread confined to an arena the buffer pool sized up
+// front, code between stream-capture begin/end, a serving thread that must not trigger cudaMalloc's
+// device-wide synchronisation.  For them the scratch the regular path grows on demand (bf16 operand
+// planes + split-K partial tiles) lives in this fixed array, which is part of the library image: every
+// GPU that loads the library holds it until exit.
+//
+// On the host the array's NAME is only a stand-in: passing it to a kernel would hand the device a host
+// address.  The device address comes from cudaGetSymbolAddress, once per device with that device
+// current (first call = set-up; do it before any stream capture).  Device code may name the array
+// directly, as k_na_reduce does.  The array is shared by all calls and keeps the last call's contents:
+// nothing in it needs to start at zero except the fault word (cleared per call), because every split
+// overwrites its whole partial tile and the conversion rewrites the K padding; calls whose GPU work
+// overlaps race on it.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NB200_NOALLOC_SCRATCH_BYTES];
+
+// fp64 row-major -> bf16 K-major plane with the K tail zeroed (grid: rows x chunks)
+__global__ void __launch_bounds__(256)
+k_na_convert(const double *__restrict__ src, long long ld, int cols, __nv_bfloat16 *__restrict__ dst, int ldk) {
+    const long long row = blockIdx.x;
+    for (int c = blockIdx.y * 256 + threadIdx.x; c < ldk; c += gridDim.y * 256)
+        dst[row * ldk + c] = __float2bfloat16_rn(c < cols ? static_cast<float>(src[row * ld + c]) : 0.f);
+}
+
+// sum the split-K partial tiles (fixed order) into the caller's fp64 output; reads the scratch by name
+__global__ void __launch_bounds__(256)
+k_na_reduce(unsigned long long partial_off, long long split_stride, int ws_ld, int splits, int M, int N,
+            double *__restrict__ out, long long out_ld) {
+    const float *ws = reinterpret_cast<const float *>(g_noalloc_scratch + partial_off);
+    const long long m = blockIdx.x;
+    for (int n = blockIdx.y * 256 + threadIdx.x; n < N; n += gridDim.y * 256) {
+        float acc = 0.f;
+        for (int s = 0; s < splits; s++) acc += ws[s * split_stride + m * ws_ld + n];
+        out[m * out_ld + n] = static_cast<double>(acc);
+    }
+}
+
+}  // namespace nb200
+
+#include <mutex>
+
+extern "C" int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, const double *b_dev, int64_t ldb, int I,
+                                            int J, int K, double *c_dev, int64_t ldc, void *cuda_stream) {
+    using namespace nb200;
+    if (!a_dev || !b_dev || !c_dev || I <= 0 || J <= 0 || K <= 0 || lda < K || ldb < K || ldc < J) {
+        set_error("transpose_mult_noalloc: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    int dev = 0;
+    NB_CUDA(cudaGetDevice(&dev));
+    // ---- once per device: device address of the scratch array, kernel attributes ----
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static unsigned char *base_of[kMaxDev] = {};
+    static int sms_of[kMaxDev] = {};
+    if (dev < 0 || dev >= kMaxDev) { set_error("transpose_mult_noalloc: device index %d not supported", dev); return NB200_ERR_INVALID; }
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!base_of[dev]) {
+            unsigned char *p = nullptr;
+            NB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_noalloc_scratch));
+            NB_CUDA(cudaFuncSetAttribute(k_block_gemm<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout<256, 4>::kTotal));
+            NB_CUDA(cudaFuncSetAttribute(k_block_gemm<128, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout<128, 6>::kTotal));
+            int sms = 0;
+            NB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            sms_of[dev] = sms > 0 ? sms : 148;
+            base_of[dev] = p;
+        }
+    }
+    unsigned char *base = base_of[dev];
+    // ---- carve the scratch: [A plane][B plane][split-K partials][fault word] ----
+    const int64_t ldk = round_up(K, kBlockK);
+    const int BN = (J <= 128) ? 128 : 256;
+    const int tiles_m = static_cast<int>(ceil_div(I, kBlockM)), tiles_n = static_cast<int>(ceil_div(J, BN));
+    const int Mpad = tiles_m * kBlockM, Npad = tiles_n * BN;
+    const int num_kb = static_cast<int>(ldk / kBlockK);
+    int splits = static_cast<int>(ceil_div(2 * sms_of[dev], static_cast<int64_t>(tiles_m) * tiles_n));
+    if (splits > num_kb / 8) splits = num_kb / 8;  // at least 8 K blocks per split
+    if (splits < 1) splits = 1;
+    const int per = static_cast<int>(ceil_div(num_kb, splits));
+    splits = static_cast<int>(ceil_div(num_kb, per));
+    const uint64_t a_bytes = round_up(static_cast<int64_t>(I) * ldk * 2, 1024);
+    const uint64_t b_bytes = round_up(static_cast<int64_t>(J) * ldk * 2, 1024);
+    const uint64_t p_bytes = static_cast<uint64_t>(splits) * Mpad * Npad * sizeof(float);
+    const uint64_t need = a_bytes + b_bytes + p_bytes + 256;
+    if (need > NB200_NOALLOC_SCRATCH_BYTES) {
+        set_error("transpose_mult_noalloc: %d x %d x %d needs %llu bytes of scratch, the fixed array holds %u "
+                  "(NB200_NOALLOC_SCRATCH_BYTES); use nb200_gemm_blocks for larger products",
+                  I, J, K, static_cast<unsigned long long>(need), NB200_NOALLOC_SCRATCH_BYTES);
+        return NB200_ERR_INVALID;
+    }
+    __nv_bfloat16 *pa = reinterpret_cast<__nv_bfloat16 *>(base);
+    __nv_bfloat16 *pb = reinterpret_cast<__nv_bfloat16 *>(base + a_bytes);
+    float *partial = reinterpret_cast<float *>(base + a_bytes + b_bytes);
+    int *fault = reinterpret_cast<int *>(base + a_bytes + b_bytes + p_bytes);
+    NB_CUDA(cudaMemsetAsync(fault, 0, sizeof(int), stream));  // the one word that must start at zero
+    const unsigned chunks = static_cast<unsigned>(ceil_div(ldk, 256) < 32 ? ceil_div(ldk, 256) : 32);
+    k_na_convert<<<dim3(I, chunks), 256, 0, stream>>>(a_dev, lda, K, pa, static_cast<int>(ldk));
+    k_na_convert<<<dim3(J, chunks), 256, 0, stream>>>(b_dev, ldb, K, pb, static_cast<int>(ldk));
+    NB_CUDA(cudaGetLastError());
+    CUtensorMap ma, mb;
+    NB_TRY(make_plane_map(&ma, pa, I, ldk, kBlockM));
+    NB_TRY(make_plane_map(&mb, pb, J, ldk, BN));
+    GemmArgs g{};
+    g.M = I; g.N = J; g.tiles_n = tiles_n; g.num_kb = num_kb; g.kb_per_split = per; g.nterms = 1; g.mode = 0;
+    g.ws = partial; g.ws_split_stride = static_cast<long long>(Mpad) * Npad; g.ws_ld = Npad; g.err_flag = fault;
+    const dim3 grid(tiles_m * tiles_n, splits);
+    if (BN == 256) k_block_gemm<256, 4><<<grid, kThreads, SmemLayout<256, 4>::kTotal, stream>>>(ma, ma, mb, mb, g);
+    else k_block_gemm<128, 6><<<grid, kThreads, SmemLayout<128, 6>::kTotal, stream>>>(ma, ma, mb, mb, g);
+    NB_CUDA(cudaGetLastError());
+    const unsigned nchunks = static_cast<unsigned>(ceil_div(J, 256) < 32 ? ceil_div(J, 256) : 32);
+    k_na_reduce<<<dim3(I, nchunks), 256, 0, stream>>>(a_bytes + b_bytes, g.ws_split_stride, Npad, splits, I, J, c_dev, ldc);
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+namespace nb200 {
 }  // namespace nb200
