@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("NB200_PRECISION", "bf16x3"), choices=["bf16", "bf16x3", "fp64"])
+    ap.add_argument("--precision", default=os.environ.get("NB200_PRECISION", "bf16"), choices=["bf16", "bf16x3", "fp64"])
     ap.add_argument("--batch", type=int, default=10000)
     ap.add_argument("--features", type=int, default=597540)
     ap.add_argument("--hidden", type=int, default=1000)

@@ -116,6 +116,11 @@ int nb200_download_rect(nb200_set *s, int row0, int col0, double *host, int rows
  * element (r,c) = synth(seed, (row_offset + r) * total_cols + c).  Bit-identical to the CPU oracle's
  * generator.  row_offset lets a row shard reproduce its slice of a larger matrix. */
 int nb200_set_fill_synth(nb200_set *s, uint64_t seed, int64_t row_offset);
+/* A read-only view of `src` under another name whose downloads apply exp() inside the un-padded region --
+ * the reference's `yo` (FFTransposeBiasSum.h:94-104) over a set of pre-exp logits. */
+int nb200_set_exp_view(nb200_set *src, const char *db, const char *set, nb200_set **out);
+/* Re-register a set under another (db, set) name; an existing set of that name is replaced. */
+int nb200_set_rename(nb200_set *s, const char *db, const char *set);
 /* Drop the derived bf16 operand planes of a set (they are rebuilt from the fp64 data on next use). */
 int nb200_set_invalidate_planes(nb200_set *s);
 

@@ -41,5 +41,36 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+HOST = os.path.join(HERE, "host")
+HOST_BIN = os.path.join(HOST, "bin")
+HOST_SRCS = [os.path.join(HOST, "src", f) for f in ("SimpleFF.cc", "FFMatrixUtil.cc")]
+REF_DRIVER = "/root/reference/src/tests/source/FFTest.cc"
+
+
+def build_host(force: bool = False) -> dict:
+    """Compile the C++ host shim drivers against libnetsdb_b200.so.
+
+    FFTest          our driver in the shape of the reference's (adds a label dump for the parity tests)
+    FFTest_netsdb   the reference's own, UNMODIFIED src/tests/source/FFTest.cc compiled in place against the
+                    shim headers (only where /root/reference exists; the binary travels to the GPU box)."""
+    build()
+    os.makedirs(HOST_BIN, exist_ok=True)
+    inc = ["-I" + os.path.join(HERE, "..", "include"), "-I" + os.path.join(HOST, "include")]
+    common = ["/usr/bin/g++", "-std=c++17", "-O2", "-ffp-contract=off", *inc]
+    link = ["-L" + HERE, "-lnetsdb_b200", "-Wl,-rpath,$ORIGIN/../.."]
+    out = {}
+    targets = [("FFTest", os.path.join(HOST, "src", "FFTest.cc"))]
+    if os.path.exists(REF_DRIVER):
+        targets.append(("FFTest_netsdb", REF_DRIVER))
+    for name, main_src in targets:
+        exe = os.path.join(HOST_BIN, name)
+        deps = [main_src, *HOST_SRCS, LIB] + [os.path.join(HOST, "include", f) for f in os.listdir(os.path.join(HOST, "include"))]
+        if force or not os.path.exists(exe) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
+            subprocess.check_call([*common, main_src, *HOST_SRCS, *link, "-o", exe])
+        out[name] = exe
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

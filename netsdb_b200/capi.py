@@ -25,6 +25,7 @@ EXPORTS = [
     "nb200_synchronize", "nb200_launch_count", "nb200_pin_pool", "nb200_unpin_pool", "nb200_set_create",
     "nb200_set_lookup", "nb200_set_destroy", "nb200_set_info", "nb200_upload_block", "nb200_upload_rect",
     "nb200_download_block", "nb200_download_rect", "nb200_set_fill_synth", "nb200_set_invalidate_planes",
+    "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
 ]
@@ -76,6 +77,8 @@ def lib():
         L.nb200_download_rect.argtypes = [vp, i, i, vp, i, i, i64]
         L.nb200_set_fill_synth.argtypes = [vp, C.c_uint64, i64]
         L.nb200_set_invalidate_planes.argtypes = [vp]
+        L.nb200_set_exp_view.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(vp)]
+        L.nb200_set_rename.argtypes = [vp, C.c_char_p, C.c_char_p]
         L.nb200_gemm_blocks.argtypes = [i, vp, vp, i, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_softmax_rows.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(vp), vp]
         L.nb200_ff_inference_unit.argtypes = [vp, vp, vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp), vp,

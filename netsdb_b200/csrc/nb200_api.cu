@@ -362,6 +362,42 @@ int nb200_set_fill_synth(nb200_set *s, uint64_t seed, int64_t row_offset) {
     return launch_synth_fill(c, s->f64, s->total_rows, s->total_cols, s->total_cols, seed, row_offset, s->total_cols);
 }
 
+int nb200_set_exp_view(nb200_set *src, const char *db, const char *set, nb200_set **out) {
+    NEED_CTX();
+    (void)c;
+    if (!src || !db || !set || !out) return NB200_ERR_INVALID;
+    nb200_set *base = src->view_of ? src->view_of : src;
+    nb200_set *v = nullptr;
+    NB_TRY(make_set(db, set, base->total_rows, base->total_cols, base->block_rows, base->block_cols, &v));
+    v->view_of = base;
+    v->view_exp = true;
+    *out = v;
+    return NB200_OK;
+}
+
+int nb200_set_rename(nb200_set *s, const char *db, const char *set) {
+    NEED_CTX();
+    if (!s || !db || !set) return NB200_ERR_INVALID;
+    if (s->db == db && s->name == set) return NB200_OK;
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto key = std::make_pair(std::string(db), std::string(set));
+    auto it = g_sets.find(key);
+    if (it != g_sets.end() && it->second != s) {
+        nb200_set *old = it->second;
+        for (auto &kv : g_sets)
+            if (kv.second->view_of == old) kv.second->view_of = nullptr;
+        free_set_storage(old);
+        delete old;
+        g_sets.erase(it);
+    }
+    g_sets.erase(std::make_pair(s->db, s->name));
+    s->db = db;
+    s->name = set;
+    g_sets[key] = s;
+    return NB200_OK;
+}
+
 int nb200_set_invalidate_planes(nb200_set *s) {
     if (!s) return NB200_ERR_INVALID;
     s->rowp.valid = s->rowp.lo_valid = false;

@@ -1,0 +1,3 @@
+// FFAggMatrix.h -- same header name as src/FF/headers/FFAggMatrix.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

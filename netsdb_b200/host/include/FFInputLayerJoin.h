@@ -1,0 +1,3 @@
+// FFInputLayerJoin.h -- same header name as src/FF/headers/FFInputLayerJoin.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

@@ -1,0 +1,3 @@
+// FFMatrixBlockScanner.h -- same header name as src/FF/headers/FFMatrixBlockScanner.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

@@ -1,0 +1,3 @@
+// FFMatrixWriter.h -- same header name as src/FF/headers/FFMatrixWriter.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

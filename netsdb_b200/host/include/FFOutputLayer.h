@@ -1,0 +1,3 @@
+// FFOutputLayer.h -- same header name as src/FF/headers/FFOutputLayer.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

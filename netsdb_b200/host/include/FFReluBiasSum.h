@@ -1,0 +1,3 @@
+// FFReluBiasSum.h -- same header name as src/FF/headers/FFReluBiasSum.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

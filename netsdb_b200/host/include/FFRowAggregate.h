@@ -1,0 +1,3 @@
+// FFRowAggregate.h -- same header name as src/FF/headers/FFRowAggregate.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

@@ -1,0 +1,3 @@
+// FFTransposeBiasSum.h -- same header name as src/FF/headers/FFTransposeBiasSum.h; the class lives in ff_udfs.h
+#pragma once
+#include "ff_udfs.h"

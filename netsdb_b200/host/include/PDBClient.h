@@ -1,0 +1,133 @@
+// PDBClient.h -- the client facade the drivers use (mainClient/headers/PDBClient.h:40-259), in process:
+// sets live on the device behind the C ABI, executeComputations hands the graph to the fused FF stage.
+// Calls return bool + errMsg like the reference's; nothing here computes on the host.
+#pragma once
+// the real PDBClient.h pulls these in transitively and the reference drivers rely on that
+#include <unistd.h>
+
+#include <chrono>
+#include <fstream>
+
+#include "ff_stage.h"
+
+namespace pdb {
+
+class CatalogClient {
+public:
+    CatalogClient() {}
+    CatalogClient(int, std::string, PDBLoggerPtr) {}
+    bool setExists(const std::string &db, const std::string &set) {
+        nb200_set *s = nullptr;
+        return nb200_set_lookup(db.c_str(), set.c_str(), &s) == NB200_OK;
+    }
+};
+
+// getSetIterator<T>(db, set): range-for over Handle<FFMatrixBlock>, one download per block
+// (queries/headers/SetIterator.h:12-68)
+template <class T>
+class SetIterator {
+public:
+    class It {
+    public:
+        It(nb200_set *s, int idx, int n, int nbc) : s(s), idx(idx), n(n), nbc(nbc) {}
+        bool operator!=(const It &o) const { return idx != o.idx; }
+        void operator++() { idx++; }
+        Handle<T> operator*() const { return nb200_host::fetch_block(s, idx / nbc, idx % nbc); }
+
+    private:
+        nb200_set *s;
+        int idx, n, nbc;
+    };
+    SetIterator() {}
+    explicit SetIterator(nb200_set *s) : s(s) {
+        if (s) {
+            int tr, tc, br, bc;
+            nb200_set_info(s, &tr, &tc, &br, &bc);
+            nbr = (tr + br - 1) / br;
+            nbc = (tc + bc - 1) / bc;
+        }
+    }
+    It begin() { return It(s, 0, nbr * nbc, nbc > 0 ? nbc : 1); }
+    It end() { return It(s, nbr * nbc, nbr * nbc, nbc > 0 ? nbc : 1); }
+
+private:
+    nb200_set *s = nullptr;
+    int nbr = 0, nbc = 0;
+};
+
+class PDBClient {
+public:
+    PDBClient() { nb200_host::ensure_init(); }
+    PDBClient(int /*port*/, std::string /*address*/, PDBLoggerPtr /*logger*/, bool /*usePangea*/ = false,
+              bool /*useQueryScheduler*/ = false) { nb200_host::ensure_init(); }
+
+    bool createDatabase(const std::string &, std::string &) { return true; }
+    bool removeDatabase(const std::string &, std::string &) { return true; }
+    bool registerType(const std::string &, std::string &) { return true; }  // UDF .so shipping: nothing to ship
+    // the device set is sized when the first block arrives (sendData), as the reference's set is filled by sendData
+    template <class T>
+    bool createSet(const std::string &db, const std::string &set, std::string &, size_t = 0, const std::string & = "",
+                   Handle<Computation> = nullptr, Handle<Computation> = nullptr) {
+        declared.insert(std::make_pair(db, set));
+        return true;
+    }
+    bool createSet(const std::string &db, const std::string &set, const std::string & /*typeName*/, std::string &,
+                   size_t = 0, const std::string & = "") {
+        declared.insert(std::make_pair(db, set));
+        return true;
+    }
+    bool removeSet(const std::string &db, const std::string &set, std::string &) { return drop(db, set); }
+    bool clearSet(const std::string &db, const std::string &set, const std::string &, std::string &) { return drop(db, set); }
+    bool flushData(std::string &errMsg) { return ok(nb200_synchronize(), errMsg); }
+
+    // NOTE the (set, db) order of the pair, as in the reference (FFMatrixUtil.cc:110-111)
+    template <class T>
+    bool sendData(std::pair<std::string, std::string> setAndDatabase, Handle<Vector<Handle<T>>> data, std::string &errMsg) {
+        const std::string &set = setAndDatabase.first, &db = setAndDatabase.second;
+        for (size_t i = 0; i < data->size(); i++)
+            if (!ok(nb200_host::ship_block(db, set, (*data)[i]), errMsg)) return false;
+        return ok(nb200_synchronize(), errMsg);  // the caller reuses its allocation block after sendData
+    }
+
+    template <class... Sinks>
+    bool executeComputations(std::string &errMsg, const std::string &jobName, bool /*preCompile*/, Handle<Computation> first,
+                             Sinks... rest) {
+        std::vector<Handle<Computation>> sinks{first, Handle<Computation>(rest)...};
+        return stage.run(jobName, sinks, errMsg);
+    }
+    template <class... Sinks>
+    bool executeComputations(std::string &errMsg, const std::string &jobName, Handle<Computation> first, Sinks... rest) {
+        return executeComputations(errMsg, jobName, false, first, rest...);
+    }
+    template <class... Sinks>
+    bool executeComputations(std::string &errMsg, Handle<Computation> first, Sinks... rest) {
+        return executeComputations(errMsg, std::string("job"), false, first, rest...);
+    }
+
+    template <class T>
+    SetIterator<T> getSetIterator(const std::string &db, const std::string &set) {
+        nb200_set *s = nullptr;
+        if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) return SetIterator<T>();
+        return SetIterator<T>(s);
+    }
+
+    // extension: labels of the last fused inference (first row argmax of the logits, equal to the fp64 pipeline's)
+    const std::vector<int32_t> &lastLabels() const { return stage.labels; }
+    const nb200_ff_stats &lastStats() const { return stage.stats; }
+    nb200_host::FusedStage stage;
+
+private:
+    static bool ok(int st, std::string &errMsg) {
+        if (st == NB200_OK) return true;
+        errMsg = nb200_last_error();
+        return false;
+    }
+    bool drop(const std::string &db, const std::string &set) {
+        nb200_set *s = nullptr;
+        if (nb200_set_lookup(db.c_str(), set.c_str(), &s) == NB200_OK) nb200_set_destroy(s);
+        return true;
+    }
+    std::set<std::pair<std::string, std::string>> declared;
+};
+
+}  // namespace pdb

@@ -1,0 +1,202 @@
+// ff_stage.h -- the "queryExecution stage" of this path: lowers a netsDB Computation graph built from
+// the FF UDFs to calls into the CUDA library.  It stands where PipelineStage::runPipeline would probe the
+// join, run the projection lambda per pair and push partial blocks into the aggregation sink
+// (queryExecution/source/PipelineStage.cc:334-930, lambdas/headers/JoinTuple.h:381-565,
+// queryExecution/headers/CombinedShuffleSink.h:78-159).  Recognised shapes:
+//
+//   FFAggMatrix(FFTransposeMult|FFInputLayerJoin(a, b))                          -> one block GEMM
+//   FFReluBiasSum(FFAggMatrix(join), bias) / FFTransposeBiasSum(..., bias)       -> the same GEMM with the bias join fused
+//   FFOutputLayer(x, FFRowAggregate(x))                                          -> row softmax
+//   the whole graph of ff::inference_unit (SimpleFF.cc:340-389)                  -> the fused stage with the
+//                                                                                   label-exact precision cascade
+// Anything else is rejected: there is no CPU fallback.
+#pragma once
+#include <set>
+#include <sstream>
+
+#include "ff_udfs.h"
+
+namespace nb200_host {
+
+inline int precision_from_env() {
+    const char *e = getenv("NB200_PRECISION");
+    if (!e) return NB200_PREC_BF16;
+    if (!strcmp(e, "bf16x3")) return NB200_PREC_BF16X3;
+    if (!strcmp(e, "fp64")) return NB200_PREC_FP64;
+    return NB200_PREC_BF16;
+}
+
+inline void ensure_init() {
+    static bool done = false;
+    if (done) return;
+    const char *d = getenv("NB200_DEVICE");
+    if (nb200_init(d ? atoi(d) : 0) != NB200_OK) {
+        std::cerr << nb200_last_error() << std::endl;  // reference convention: print and exit(1)
+        exit(1);
+    }
+    done = true;
+}
+
+// sendData for one FFMatrixBlock: the device set is created from the first block's meta
+inline int ship_block(const std::string &db, const std::string &set, pdb::Handle<FFMatrixBlock> &b) {
+    nb200_set *s = nullptr;
+    if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) {
+        // nominal block size = size of the first block sent (block (0,0) in ff::loadMatrix's order)
+        int st = nb200_set_create(db.c_str(), set.c_str(), b->getTotalRowNums(), b->getTotalColNums(), b->getRowNums(),
+                                  b->getColNums(), &s);
+        if (st != NB200_OK) return st;
+    }
+    return nb200_upload_block(s, b->getBlockRowIndex(), b->getBlockColIndex(), b->getValue().rawData->c_ptr(), b->getRowNums(),
+                              b->getColNums());
+}
+
+// getSetIterator: re-wrap one device block as an FFMatrixBlock (full-size, zero padded, reference meta)
+inline pdb::Handle<FFMatrixBlock> fetch_block(nb200_set *s, int br, int bc) {
+    int tr, tc, rows, cols;
+    nb200_set_info(s, &tr, &tc, &rows, &cols);
+    pdb::Handle<FFMatrixBlock> out = pdb::makeObject<FFMatrixBlock>(br, bc, rows, cols, tr, tc, false);
+    if (nb200_download_block(s, br, bc, out->getValue().rawData->c_ptr(), rows, cols) != NB200_OK) {
+        std::cerr << nb200_last_error() << std::endl;
+        exit(1);
+    }
+    return out;
+}
+
+class FusedStage {
+public:
+    std::vector<int32_t> labels;
+    nb200_ff_stats stats{};
+
+    bool run(const std::string &jobName, const std::vector<pdb::Handle<pdb::Computation>> &sinks, std::string &errMsg) {
+        (void)jobName;
+        try {
+            for (auto &sink : sinks) {
+                auto *w = dynamic_cast<pdb::WriteSetBase *>(sink.ptr().get());
+                if (!w) throw std::runtime_error("sink is not a WriteUserSet");
+                if (try_inference_unit(w)) continue;
+                eval(w->getIthInput(0), w->getDatabaseName(), w->getSetName());
+            }
+        } catch (const std::exception &e) {
+            errMsg = e.what();
+            return false;
+        }
+        return true;
+    }
+
+private:
+    int tmp_id = 0;
+    std::map<std::string, std::string> fused_output_of;  // db:yo-set -> pending fused `output` set name
+
+    static void check(int st) {
+        if (st != NB200_OK) throw std::runtime_error(nb200_last_error());
+    }
+    static nb200_set *lookup(const std::string &db, const std::string &set) {
+        nb200_set *s = nullptr;
+        check(nb200_set_lookup(db.c_str(), set.c_str(), &s));
+        return s;
+    }
+    template <class T> static T *as(const pdb::Handle<pdb::Computation> &c) { return dynamic_cast<T *>(c.ptr().get()); }
+    std::string tmp() { return "__tmp" + std::to_string(tmp_id++); }
+    static void dropout_must_be_zero(FFReluBiasSum *r) {
+        if (r->dropout_rate == 0) return;
+        // FFReluBiasSum.h:67,73-80 draws from srand(time(NULL)): irreproducible, so parity runs need 0
+        if (getenv("NB200_DROPOUT_AS_ZERO")) {
+            std::cerr << "warning: dropout_rate " << r->dropout_rate << " ignored (NB200_DROPOUT_AS_ZERO)" << std::endl;
+            return;
+        }
+        throw std::runtime_error("FFReluBiasSum: dropout_rate must be 0 (the reference's dropout is time-seeded)");
+    }
+
+    // JoinComp(FFTransposeMult|FFInputLayerJoin) -> FFAggMatrix [-> bias join] as ONE device call
+    nb200_set *lower_join(const pdb::Handle<pdb::Computation> &agg, int epilogue, nb200_set *bias, const std::string &db,
+                          const std::string &out) {
+        if (!as<FFAggMatrix>(agg)) throw std::runtime_error("expected FFAggMatrix below the bias join (no CPU fallback)");
+        pdb::Handle<pdb::Computation> join = agg->getIthInput(0);
+        int op;
+        if (as<FFTransposeMult>(join)) op = NB200_OP_NT;
+        else if (as<FFInputLayerJoin>(join)) op = NB200_OP_NN;
+        else throw std::runtime_error("FFAggMatrix over an unsupported join (no CPU fallback)");
+        nb200_set *a = eval(join->getIthInput(0), db, ""), *b = eval(join->getIthInput(1), db, "");
+        nb200_set *c = nullptr;
+        check(nb200_gemm_blocks(op, a, b, epilogue, bias, precision_from_env(), db.c_str(), out.c_str(), &c));
+        return c;
+    }
+
+    nb200_set *eval(const pdb::Handle<pdb::Computation> &c, const std::string &db, const std::string &out_name) {
+        if (c == nullptr) throw std::runtime_error("computation has a missing input");
+        const std::string out = out_name.empty() ? tmp() : out_name;
+        if (auto *scan = as<pdb::ScanSetBase>(c)) return lookup(scan->getDatabaseName(), scan->getSetName());
+        if (as<FFAggMatrix>(c)) return lower_join(c, NB200_EPI_NONE, nullptr, db, out);
+        if (auto *r = as<FFReluBiasSum>(c)) {
+            dropout_must_be_zero(r);
+            return lower_join(c->getIthInput(0), NB200_EPI_BIAS_RELU, eval(c->getIthInput(1), db, ""), db, out);
+        }
+        if (as<FFTransposeBiasSum>(c)) {
+            nb200_set *z = lower_join(c->getIthInput(0), NB200_EPI_BIAS_TRANSPOSE, eval(c->getIthInput(1), db, ""), db,
+                                      "__logits_of_" + out);
+            nb200_set *view = nullptr;
+            check(nb200_set_exp_view(z, db.c_str(), out.c_str(), &view));  // the reference's yo holds exp(.)
+            return view;
+        }
+        if (as<FFOutputLayer>(c)) {
+            auto *ra = as<FFRowAggregate>(c->getIthInput(1));
+            if (!ra) throw std::runtime_error("FFOutputLayer needs FFRowAggregate as its second input (no CPU fallback)");
+            auto *s0 = as<pdb::ScanSetBase>(c->getIthInput(0));
+            auto *s1 = as<pdb::ScanSetBase>(ra->getIthInput(0));
+            if (s0 && s1 && s0->getSetName() == s1->getSetName()) {
+                auto it = fused_output_of.find(s0->getDatabaseName() + ":" + s0->getSetName());
+                if (it != fused_output_of.end()) {  // already produced by the fused stage: just publish it
+                    nb200_set *o = lookup(s0->getDatabaseName(), it->second);
+                    check(nb200_set_rename(o, db.c_str(), out.c_str()));
+                    fused_output_of.erase(it);
+                    return o;
+                }
+            }
+            nb200_set *yo = eval(c->getIthInput(0), db, "");
+            nb200_set *o = nullptr;
+            check(nb200_softmax_rows(yo, db.c_str(), out.c_str(), &o, nullptr));
+            return o;
+        }
+        throw std::runtime_error("computation graph not supported on the device (no CPU fallback): " + c->getComputationType());
+    }
+
+    // The graph of ff::inference_unit (SimpleFF.cc:340-389): Write(yo) <- FFTransposeBiasSum(FFAggMatrix(FFInputLayerJoin(
+    // Scan(wo), FFReluBiasSum(FFAggMatrix(FFTransposeMult(Scan(w1), Scan(inputs))), Scan(b1)))), Scan(bo))
+    bool try_inference_unit(pdb::WriteSetBase *w) {
+        auto tbs = w->getIthInput(0);
+        if (!as<FFTransposeBiasSum>(tbs)) return false;
+        auto agg2 = tbs->getIthInput(0);
+        auto *bo = as<pdb::ScanSetBase>(tbs->getIthInput(1));
+        if (!as<FFAggMatrix>(agg2) || !bo) return false;
+        auto j2 = agg2->getIthInput(0);
+        if (!as<FFInputLayerJoin>(j2)) return false;
+        auto *wo = as<pdb::ScanSetBase>(j2->getIthInput(0));
+        auto relu = j2->getIthInput(1);
+        auto *r = as<FFReluBiasSum>(relu);
+        if (!wo || !r) return false;
+        auto agg1 = relu->getIthInput(0);
+        auto *b1 = as<pdb::ScanSetBase>(relu->getIthInput(1));
+        if (!as<FFAggMatrix>(agg1) || !b1) return false;
+        auto j1 = agg1->getIthInput(0);
+        if (!as<FFTransposeMult>(j1)) return false;
+        auto *w1 = as<pdb::ScanSetBase>(j1->getIthInput(0));
+        auto *in = as<pdb::ScanSetBase>(j1->getIthInput(1));
+        if (!w1 || !in) return false;
+        dropout_must_be_zero(r);
+        const std::string db = w->getDatabaseName();
+        nb200_set *sin = lookup(in->getDatabaseName(), in->getSetName());
+        int rows = 0;
+        nb200_set_info(sin, &rows, nullptr, nullptr, nullptr);
+        labels.assign(rows, -1);
+        nb200_set *out = nullptr;
+        check(nb200_ff_inference_unit(lookup(w1->getDatabaseName(), w1->getSetName()), lookup(wo->getDatabaseName(), wo->getSetName()),
+                                      sin, lookup(b1->getDatabaseName(), b1->getSetName()),
+                                      lookup(bo->getDatabaseName(), bo->getSetName()), precision_from_env(), db.c_str(),
+                                      "__ff_output", &out, labels.data(), &stats));
+        if (w->getSetName() != "yo") check(nb200_set_rename(lookup(db, "yo"), db.c_str(), w->getSetName().c_str()));
+        fused_output_of[db + ":" + w->getSetName()] = "__ff_output";
+        return true;
+    }
+};
+
+}  // namespace nb200_host

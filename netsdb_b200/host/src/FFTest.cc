@@ -1,0 +1,81 @@
+// FFTest -- driver in the shape of the reference's src/tests/source/FFTest.cc (same arguments, same sets
+// in database "ff", same ff:: calls), plus what the reference driver lacks: a machine-readable dump of the
+// predicted labels and a few probabilities, so that the parity tests can compare against the oracle.
+//
+//   FFTest blockX blockY batch features neurons labels [dump.txt]
+#include <chrono>
+#include <cstdio>
+
+#include "FFMatrixUtil.h"
+#include "PDBClient.h"
+#include "SimpleFF.h"
+
+int main(int argc, char *argv[]) {
+    if (argc < 7) {
+        std::cout << "Usage: blockDimensionX blockDimensionY batchSize numFeatures numNeurons numLabels [dumpFile]" << std::endl;
+        return -1;
+    }
+    const int block_x = atoi(argv[1]), block_y = atoi(argv[2]), batch_size = atoi(argv[3]);
+    const int numFeatures = atoi(argv[4]), numNeurons = atoi(argv[5]), numLabels = atoi(argv[6]);
+    std::string errMsg;
+    pdb::PDBLoggerPtr clientLogger = std::make_shared<pdb::PDBLogger>("FFclientLog");
+    pdb::PDBClient pdbClient(8108, "localhost", clientLogger, false, true);
+    pdb::CatalogClient catalogClient(8108, "localhost", clientLogger);
+
+    ff::createDatabase(pdbClient, "ff");
+    ff::setup(pdbClient, "ff");
+    for (const char *s : {"inputs", "label", "w1", "b1", "wo", "bo"}) ff::createSet(pdbClient, "ff", s, s, 64);
+    ff::createSet(pdbClient, "ff", "output", "Output", 256);
+    ff::createSet(pdbClient, "ff", "y1", "Y1", 64);
+    ff::createSet(pdbClient, "ff", "yo", "YO", 64);
+
+    // same shapes and block sizes as the reference driver (FFTest.cc:99-117)
+    ff::loadMatrix(pdbClient, "ff", "inputs", batch_size, numFeatures, block_x, block_y, false, false, errMsg);
+    ff::loadMatrix(pdbClient, "ff", "w1", numNeurons, numFeatures, block_x, block_y, false, false, errMsg);
+    ff::loadMatrix(pdbClient, "ff", "b1", numNeurons, 1, block_x, 1, false, true, errMsg);
+    ff::loadMatrix(pdbClient, "ff", "wo", numLabels, numNeurons, block_x, block_x, false, false, errMsg);
+    ff::loadMatrix(pdbClient, "ff", "bo", numLabels, 1, block_x, 1, false, true, errMsg);
+
+    const double dropout_rate = 0;  // the reference driver passes 0.5 drawn from a time-seeded rand(); parity needs 0
+    auto begin = std::chrono::high_resolution_clock::now();
+    ff::inference_unit(pdbClient, "ff", "w1", "wo", "inputs", "b1", "bo", "output", dropout_rate);
+    auto end = std::chrono::high_resolution_clock::now();
+    std::cout << "*****FFTest End-to-End Time Duration: ****" << std::chrono::duration<float>(end - begin).count() << " secs."
+              << std::endl;
+
+    // read the output set block by block like the reference (FFTest.cc:150-170) and take the row argmax
+    std::vector<int> label(batch_size, -1);
+    std::vector<double> best(batch_size, -1.0), p0(batch_size, 0.0);
+    int count = 0;
+    {
+        const pdb::UseTemporaryAllocationBlock tempBlock{1024 * 1024 * 128};
+        auto it = pdbClient.getSetIterator<FFMatrixBlock>("ff", "output");
+        for (auto r : it) {
+            count++;
+            double *data = r->getRawDataHandle()->c_ptr();
+            for (int i = 0; i < r->getRowNums(); i++) {
+                const int row = r->getBlockRowIndex() * r->getRowNums() + i;
+                if (row >= batch_size) break;
+                for (int j = 0; j < r->getColNums(); j++) {
+                    const int col = r->getBlockColIndex() * r->getColNums() + j;
+                    if (col >= numLabels) break;
+                    const double v = data[static_cast<long>(i) * r->getColNums() + j];
+                    if (col == 0) p0[row] = v;
+                    if (v > best[row]) { best[row] = v; label[row] = col; }
+                }
+            }
+        }
+    }
+    std::cout << "count=" << count << std::endl;
+    int agree = 0;
+    const std::vector<int32_t> &fused = pdbClient.lastLabels();
+    for (int i = 0; i < batch_size && i < static_cast<int>(fused.size()); i++) agree += fused[i] == label[i];
+    std::cout << "labels from the output set agree with the fused stage's on " << agree << "/" << batch_size << " rows" << std::endl;
+    if (argc > 7) {
+        FILE *f = fopen(argv[7], "w");
+        for (int i = 0; i < batch_size; i++)
+            fprintf(f, "%d %d %.17g\n", i < static_cast<int>(fused.size()) ? fused[i] : -1, label[i], p0[i]);
+        fclose(f);
+    }
+    return 0;
+}

@@ -56,3 +56,14 @@ def test_product_package_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cc", ".cpp", ".hpp")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "ff_oracle" not in text and "import oracle" not in text and "from oracle" not in text, f
+
+
+def test_cpp_shim_drivers_compile():
+    """The C++ host shim: our FFTest driver and -- where the reference tree is present -- the reference's own
+    unmodified src/tests/source/FFTest.cc both compile and link against libnetsdb_b200.so."""
+    from netsdb_b200 import build
+
+    exes = build.build_host()
+    assert os.path.exists(exes["FFTest"])
+    if os.path.exists(build.REF_DRIVER):
+        assert os.path.exists(exes["FFTest_netsdb"])
