@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("NB200_PRECISION", "bf16"), choices=["bf16", "bf16x3", "fp64"])
+    ap.add_argument("--precision", default=os.environ.get("NB200_PRECISION", "f16"), choices=["bf16", "f16", "bf16x3", "fp64"])
     ap.add_argument("--batch", type=int, default=10000)
     ap.add_argument("--features", type=int, default=597540)
     ap.add_argument("--hidden", type=int, default=1000)
@@ -272,7 +272,7 @@ def run_b200(a):
     if rank == 0:
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=a.steps, warmup=max(a.warmup, 3),
                     ms_per_step=ms_per_step, higher_is_better=True, scaling="weak", vs_baseline=None,
-                    dtype={"bf16": "bf16", "bf16x3": "bf16x3 (bf16 hi/lo split, fp32 accumulate)", "fp64": "f64"}[a.precision],
+                    dtype={"bf16": "bf16", "f16": "f16", "bf16x3": "bf16x3 (bf16 hi/lo split, fp32 accumulate)", "fp64": "f64"}[a.precision],
                     data="synthetic",
                     config=dict(workload=workload_name(a), parallelism=f"row-sharded dp{world}, weights replicated",
                                 l2="inputs (47.8 GB fp64 per GPU) exceed L2, no flush needed",

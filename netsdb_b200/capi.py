@@ -16,8 +16,8 @@ LIB_PATH = os.path.join(_HERE, "libnetsdb_b200.so")
 OK = 0
 OP_NT, OP_NN = 0, 1
 EPI_NONE, EPI_BIAS_RELU, EPI_BIAS_TRANSPOSE = 0, 1, 2
-PREC_BF16, PREC_BF16X3, PREC_FP64 = 0, 1, 2
-PRECISIONS = {"bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "fp64": PREC_FP64}
+PREC_BF16, PREC_BF16X3, PREC_FP64, PREC_F16 = 0, 1, 2, 3
+PRECISIONS = {"bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "fp64": PREC_FP64, "f16": PREC_F16}
 
 # every symbol include/netsdb_b200.h declares (tests check the .so exports each one)
 EXPORTS = [

@@ -69,6 +69,7 @@ int check_kernel_fault(Context *c, const char *what) {
 
 static void free_planes(Planes *p) {
     cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
+    cudaFree(p->f16); cudaFree(p->f16_exp); cudaFree(p->f16_maxscaled);
     *p = Planes();
 }
 
@@ -143,7 +144,30 @@ static int make_set(const char *db, const char *name, int tr, int tc, int br, in
 
 static float prec_unit(int precision) {
     // unit of the relative rounding error of one product (DESIGN.md "error model")
-    return precision == NB200_PREC_BF16 ? 0.00390625f /* 2^-8 */ : 1.52587890625e-05f /* 2^-16 */;
+    if (precision == NB200_PREC_BF16) return 0.00390625f;      // 2^-8
+    if (precision == NB200_PREC_F16) return 0.00048828125f;    // 2^-11
+    return 1.52587890625e-05f;                                 // 2^-16 (bf16x3)
+}
+
+// fp16 planes: exact scale for model-side sets (stride 1), sampled scale for per-query inputs
+static int ensure_f16_row(Context *c, nb200_set *s, int sample_stride) {
+    if (s->rowp.f16_valid) return NB200_OK;
+    if (s->f64) return launch_convert_f16(c, s->f64, true, s->total_rows, s->total_cols, s->total_cols, &s->rowp, sample_stride, nullptr);
+    if (s->f32) return launch_convert_f16(c, s->f32, false, s->total_rows, s->total_cols, s->f32_ld, &s->rowp, sample_stride, nullptr);
+    set_error("set %s:%s holds no data", s->db.c_str(), s->name.c_str());
+    return NB200_ERR_STATE;
+}
+static int ensure_f16_col(Context *c, nb200_set *s) {
+    if (s->colp.f16_valid) return NB200_OK;
+    NB_TRY(ensure_f32(c, s));
+    float *t = nullptr;  // transposed fp32 copy, then a plain conversion
+    const size_t n = static_cast<size_t>(s->total_rows) * s->total_cols;
+    NB_CUDA(cudaMalloc(&t, (n ? n : 1) * sizeof(float)));
+    int st = launch_transpose_f32(c, s->f32, s->total_rows, s->total_cols, s->f32_ld, t, s->total_rows);
+    if (st == NB200_OK) st = launch_convert_f16(c, t, false, s->total_cols, s->total_rows, s->total_rows, &s->colp, 1, nullptr);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(t);
+    return st;
 }
 
 }  // namespace nb200
@@ -285,8 +309,8 @@ int nb200_set_info(const nb200_set *s, int *total_rows, int *total_cols, int *bl
 }
 
 static void drop_derived(nb200_set *s) {
-    s->rowp.valid = s->rowp.lo_valid = false;
-    s->colp.valid = s->colp.lo_valid = false;
+    s->rowp.valid = s->rowp.lo_valid = s->rowp.f16_valid = false;
+    s->colp.valid = s->colp.lo_valid = s->colp.f16_valid = false;
     if (s->f64 && s->f32) { cudaFree(s->f32); s->f32 = nullptr; }
 }
 
@@ -400,8 +424,8 @@ int nb200_set_rename(nb200_set *s, const char *db, const char *set) {
 
 int nb200_set_invalidate_planes(nb200_set *s) {
     if (!s) return NB200_ERR_INVALID;
-    s->rowp.valid = s->rowp.lo_valid = false;
-    s->colp.valid = s->colp.lo_valid = false;
+    s->rowp.valid = s->rowp.lo_valid = s->rowp.f16_valid = false;
+    s->colp.valid = s->colp.lo_valid = s->colp.f16_valid = false;
     return NB200_OK;
 }
 
@@ -419,7 +443,7 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
                             const char *db, const char *out_set, nb200_set **out, int extra_relu) {
     NEED_CTX();
     if (!a || !b || !db || !out_set || !out || (op != NB200_OP_NT && op != NB200_OP_NN) || epilogue < 0 || epilogue > 2 ||
-        precision < 0 || precision > 2) {
+        precision < 0 || precision > 3) {
         set_error("gemm_blocks: invalid arguments");
         return NB200_ERR_INVALID;
     }
@@ -463,9 +487,16 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
 
     const int nterms = (precision == NB200_PREC_BF16X3) ? 3 : 1;
     const bool lo = nterms == 3;
-    NB_TRY(ensure_rowp(c, a, lo));
-    if (op == NB200_OP_NT) NB_TRY(ensure_rowp(c, b, lo));
-    else NB_TRY(ensure_colp(c, b, lo));
+    const int fmt = (precision == NB200_PREC_F16) ? kFmtF16 : kFmtBF16;
+    if (fmt == kFmtF16) {
+        NB_TRY(ensure_f16_row(c, a, 1));
+        if (op == NB200_OP_NT) NB_TRY(ensure_f16_row(c, b, 1));
+        else NB_TRY(ensure_f16_col(c, b));
+    } else {
+        NB_TRY(ensure_rowp(c, a, lo));
+        if (op == NB200_OP_NT) NB_TRY(ensure_rowp(c, b, lo));
+        else NB_TRY(ensure_colp(c, b, lo));
+    }
     const Planes &pa = a->rowp;
     const Planes &pb = (op == NB200_OP_NT) ? b->rowp : b->colp;
     const float *bias32 = nullptr;
@@ -486,14 +517,15 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
         GemmEpilogue ge;
         ge.mode = 1; ge.out = o->f32; ge.out_ld = o->f32_ld; ge.relu = relu;
         if (transpose_out) ge.bias_n = bias32; else ge.bias_m = bias32;
-        NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, 1, ge, &Mpad, &Npad, nullptr));
+        NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, 1, ge, &Mpad, &Npad, nullptr, fmt));
     } else {
         GemmEpilogue ge;
         ge.mode = 0;
         int real_splits = splits;
-        NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, splits, ge, &Mpad, &Npad, &real_splits));
+        NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, splits, ge, &Mpad, &Npad, &real_splits, fmt));
         ReduceOut ro;
         ro.f32 = o->f32; ro.f32_ld = o->f32_ld;
+        if (fmt == kFmtF16) { ro.exp_u = U.f16_exp; ro.exp_v = V.f16_exp; }
         NB_TRY(launch_splitk_reduce(c, M, N, real_splits, Mpad, Npad, transpose_out ? nullptr : bias32,
                                     transpose_out ? bias32 : nullptr, relu, ro));
     }
@@ -535,34 +567,53 @@ int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, n
 // One tensor-core forward pass over `rows` rows whose bf16 planes are X:
 //   y1 = relu(X W1^T + b1)  (split-K block GEMM + fused reduce, written as operand planes for layer 2)
 //   logits = y1 Wo^T + bo   (block GEMM with the bias in its epilogue)
-static int tc_forward(Context *c, const Planes &X, int rows, int nterms, nb200_set *w1, nb200_set *wo, const float *b1,
-                      const float *bo, Planes *y1, float *logits, int64_t logits_ld, int H, int Lb, int *splits1,
-                      cudaEvent_t k0, cudaEvent_t k1, cudaEvent_t after_l1) {
+static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt, nb200_set *w1, nb200_set *wo, const float *b1,
+                      const float *bo, Planes *y1, float **y1_f32, size_t *y1_f32_bytes, float *y1_max, float *logits,
+                      int64_t logits_ld, int H, int Lb, int *splits1, cudaEvent_t k0, cudaEvent_t k1, cudaEvent_t after_l1) {
     const bool lo = nterms == 3;
+    const bool f16 = fmt == kFmtF16;
     int Mpad = 0, Npad = 0, used1 = 1;
     GemmEpilogue g1;
     g1.mode = 0;
     if (k0) NB_CUDA(cudaEventRecord(k0, c->stream));
-    NB_TRY(launch_gemm_tc(c, X, w1->rowp, rows, H, nterms, choose_splits(c, rows, H, X.ldk, nterms), g1, &Mpad, &Npad, &used1));
+    NB_TRY(launch_gemm_tc(c, X, w1->rowp, rows, H, nterms, choose_splits(c, rows, H, X.ldk, nterms), g1, &Mpad, &Npad, &used1, fmt));
     if (k1) NB_CUDA(cudaEventRecord(k1, c->stream));
     *splits1 = used1;
     ReduceOut r1;
-    r1.planes = y1;
-    r1.want_lo = lo;
-    NB_TRY(launch_splitk_reduce(c, rows, H, used1, Mpad, Npad, nullptr, b1, 1, r1));
+    if (!f16) {
+        r1.planes = y1;
+        r1.want_lo = lo;
+        NB_TRY(launch_splitk_reduce(c, rows, H, used1, Mpad, Npad, nullptr, b1, 1, r1));
+    } else {
+        // fp16: un-scale the partial sums, keep y1 in fp32 for a moment to learn its maximum, then pick its scale
+        const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
+        if (need > *y1_f32_bytes) {
+            cudaFree(*y1_f32);
+            *y1_f32 = nullptr;
+            *y1_f32_bytes = 0;
+            NB_CUDA(cudaMalloc(y1_f32, need));
+            *y1_f32_bytes = need;
+        }
+        r1.f32 = *y1_f32; r1.f32_ld = H;
+        r1.exp_u = X.f16_exp; r1.exp_v = w1->rowp.f16_exp;
+        r1.out_maxabs = y1_max;
+        NB_TRY(launch_splitk_reduce(c, rows, H, used1, Mpad, Npad, nullptr, b1, 1, r1));
+        NB_TRY(launch_convert_f16(c, *y1_f32, false, rows, H, H, y1, 1, y1_max));
+    }
     if (after_l1) NB_CUDA(cudaEventRecord(after_l1, c->stream));
     const int splits2 = choose_splits(c, rows, Lb, y1->ldk, nterms);
     if (splits2 == 1) {
         GemmEpilogue g2;
         g2.mode = 1; g2.out = logits; g2.out_ld = logits_ld; g2.bias_n = bo;
-        NB_TRY(launch_gemm_tc(c, *y1, wo->rowp, rows, Lb, nterms, 1, g2, &Mpad, &Npad, nullptr));
+        NB_TRY(launch_gemm_tc(c, *y1, wo->rowp, rows, Lb, nterms, 1, g2, &Mpad, &Npad, nullptr, fmt));
     } else {
         GemmEpilogue g2;
         g2.mode = 0;
         int used2 = splits2;
-        NB_TRY(launch_gemm_tc(c, *y1, wo->rowp, rows, Lb, nterms, splits2, g2, &Mpad, &Npad, &used2));
+        NB_TRY(launch_gemm_tc(c, *y1, wo->rowp, rows, Lb, nterms, splits2, g2, &Mpad, &Npad, &used2, fmt));
         ReduceOut r2;
         r2.f32 = logits; r2.f32_ld = logits_ld;
+        if (f16) { r2.exp_u = y1->f16_exp; r2.exp_v = wo->rowp.f16_exp; }
         NB_TRY(launch_splitk_reduce(c, rows, Lb, used2, Mpad, Npad, nullptr, bo, 0, r2));
     }
     return NB200_OK;
@@ -586,6 +637,10 @@ struct FFScratch {  // reused across calls
     size_t logits_sub_bytes = 0;
     int32_t *list2 = nullptr;
     int64_t list2_cap = 0;
+    float *y1_f32 = nullptr;   // fp16 path: layer-1 result before its scale is known
+    size_t y1_f32_bytes = 0;
+    float *y1_max = nullptr;
+    float *host_scalars = nullptr;  // pinned: [0] = largest scaled |x| of the inputs' fp16 conversion
 };
 static FFScratch g_ff;
 
@@ -603,7 +658,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
                             const char *db, const char *out_set, nb200_set **out, int32_t *labels_host,
                             nb200_ff_stats *stats) {
     NEED_CTX();
-    if (!w1 || !wo || !inputs || !b1 || !bo || !db || !out_set || !out || precision < 0 || precision > 2) {
+    if (!w1 || !wo || !inputs || !b1 || !bo || !db || !out_set || !out || precision < 0 || precision > 3) {
         set_error("ff_inference_unit: invalid arguments");
         return NB200_ERR_INVALID;
     }
@@ -637,6 +692,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     if (!S.count) {
         NB_CUDA(cudaMalloc(&S.count, sizeof(int)));
         NB_CUDA(cudaMallocHost(&S.count_host, sizeof(int)));
+        NB_CUDA(cudaMalloc(&S.y1_max, sizeof(float)));
+        NB_CUDA(cudaMallocHost(&S.host_scalars, 4 * sizeof(float)));
     }
     cudaEvent_t *ev = c->ev;
     NB_CUDA(cudaEventRecord(ev[0], c->stream));
@@ -666,23 +723,29 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     } else {
         const int nterms = (precision == NB200_PREC_BF16X3) ? 3 : 1;
         const bool lo = nterms == 3;
+        const int fmt = (precision == NB200_PREC_F16) ? kFmtF16 : kFmtBF16;
         // model side (cached across calls, like a materialised model): weight planes, fp32 biases.
-        // The single-pass variant also keeps the residual planes: its undecided rows are re-run in bf16x3.
+        // The single-pass variants also keep the residual planes: their undecided rows are re-run in bf16x3.
         NB_TRY(ensure_rowp(c, w1, true));
         NB_TRY(ensure_rowp(c, wo, true));
+        if (fmt == kFmtF16) {
+            NB_TRY(ensure_f16_row(c, w1, 1));
+            NB_TRY(ensure_f16_row(c, wo, 1));
+        }
         NB_TRY(ensure_f32(c, b1));
         NB_TRY(ensure_f32(c, bo));
         if (!wo->wo_rownorm_max) NB_CUDA(cudaMalloc(&wo->wo_rownorm_max, sizeof(float)));
         NB_TRY(launch_max_rownorm(c, wo->rowp.row_sumsq, Lb, wo->wo_rownorm_max));
         NB_CUDA(cudaEventRecord(ev[0], c->stream));
-        // query side: de-blocked fp64 inputs -> bf16 planes
-        NB_TRY(ensure_rowp(c, inputs, lo));
+        // query side: de-blocked fp64 inputs -> 16-bit operand planes
+        if (fmt == kFmtF16) NB_TRY(ensure_f16_row(c, inputs, 64));
+        else NB_TRY(ensure_rowp(c, inputs, lo));
         NB_CUDA(cudaEventRecord(ev[1], c->stream));
         NB_CUDA(cudaMalloc(&zset->f32, on * sizeof(float)));
         zset->f32_ld = Lb;
         // level 1 on every row
-        NB_TRY(tc_forward(c, inputs->rowp, B, nterms, w1, wo, b1->f32, bo->f32, &S.y1, zset->f32, Lb, H, Lb, &splits1,
-                          ev[6], ev[7], ev[2]));
+        NB_TRY(tc_forward(c, inputs->rowp, B, nterms, fmt, w1, wo, b1->f32, bo->f32, &S.y1, &S.y1_f32, &S.y1_f32_bytes, S.y1_max,
+                          zset->f32, Lb, H, Lb, &splits1, ev[6], ev[7], ev[2]));
         NB_CUDA(cudaEventRecord(ev[3], c->stream));
         // FFRowAggregate + FFOutputLayer + label, and the near-tie scan
         NB_TRY(launch_softmax_rows(c, zset->f32, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, nullptr, 0, 0));
@@ -690,12 +753,19 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         NB_TRY(launch_flag_rows(c, B, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs, wo->rowp.maxabs,
                                 wo->wo_rownorm_max, prec_unit(precision), 4.0f, S.list, S.count, B, nullptr));
         NB_CUDA(cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        if (fmt == kFmtF16)
+            NB_CUDA(cudaMemcpyAsync(S.host_scalars, inputs->rowp.f16_maxscaled, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaEventRecord(ev[4], c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
+        if (fmt == kFmtF16 && !(S.host_scalars[0] < 65504.f)) {
+            // the sampled scale let an input overflow fp16: redo this call in bf16 (full exponent range)
+            inputs->rowp.f16_valid = false;
+            return nb200_ff_inference_unit(w1, wo, inputs, b1, bo, NB200_PREC_BF16, db, out_set, out, labels_host, stats);
+        }
         int n1 = std::min(*S.count_host, B);
         const int32_t *final_list = S.list;
         refined = n1;
-        if (precision == NB200_PREC_BF16 && n1 > 0) {
+        if ((precision == NB200_PREC_BF16 || precision == NB200_PREC_F16) && n1 > 0) {
             // level 2: bf16x3 on the undecided rows only (gathered straight from the fp64 inputs)
             if (S.list2_cap < B) {
                 cudaFree(S.list2);
@@ -716,8 +786,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
                     S.logits_sub_bytes = need;
                 }
                 int dummy = 0;
-                NB_TRY(tc_forward(c, S.xsub, R, 3, w1, wo, b1->f32, bo->f32, &S.y1sub, S.logits_sub, Lb, H, Lb, &dummy,
-                                  nullptr, nullptr, nullptr));
+                NB_TRY(tc_forward(c, S.xsub, R, 3, kFmtBF16, w1, wo, b1->f32, bo->f32, &S.y1sub, nullptr, nullptr, nullptr,
+                                  S.logits_sub, Lb, H, Lb, &dummy, nullptr, nullptr, nullptr));
                 NB_TRY(launch_scatter_rows_f32(c, S.logits_sub, Lb, Lb, S.list + r0, R, zset->f32, Lb));
                 NB_TRY(launch_softmax_rows(c, S.logits_sub, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, S.list + r0, R, 1));
                 NB_TRY(launch_flag_rows(c, R, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs,

@@ -44,6 +44,9 @@ struct GemmArgs {
     const float *bias_n;
     int relu;
     int *err_flag;
+    unsigned int idesc;  // tcgen05 instruction descriptor (operand format bf16 or fp16, tile shape)
+    const int *exp_u;    // fp16 operand scales (device ints, may be null): result *= 2^-(exp_u + exp_v)
+    const int *exp_v;
 };
 
 template <int BN, int STAGES>
@@ -121,7 +124,7 @@ k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BN);
+            const uint32_t idesc = g.idesc;
             bool ok = true;
             for (int it = 0; it < n_iter && ok; it++) {
                 const int s = it % STAGES;
@@ -153,6 +156,7 @@ k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant
         if (ok) {
             const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
             const float bm = (g.mode == 1 && g.bias_m != nullptr && row < g.M) ? g.bias_m[row] : 0.f;
+            const float oscale = (g.mode == 1 && g.exp_u != nullptr) ? exp2f(-static_cast<float>(*g.exp_u + *g.exp_v)) : 1.f;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; c++) {
                 uint32_t r[32];
@@ -174,7 +178,7 @@ k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
                         if (col0 + j < g.N) {
-                            float v = __uint_as_float(r[j]) + bm;
+                            float v = __uint_as_float(r[j]) * oscale + bm;
                             if (g.bias_n != nullptr) v += g.bias_n[col0 + j];
                             if (g.relu) v = fmaxf(v, 0.f);
                             dst[j] = v;
@@ -288,7 +292,7 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
     } else if (warp == 1) {
         // ===== MMA issuer: one thread of the leader CTA =====
         if (leader && lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(256, 256);
+            const uint32_t idesc = g.idesc;
             bool ok = true;
             for (int it = 0; it < n_iter && ok; it++) {
                 const int s = it % STAGES;
@@ -321,6 +325,7 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
         if (ok) {
             const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
             const float bm = (g.mode == 1 && g.bias_m != nullptr && row < g.M) ? g.bias_m[row] : 0.f;
+            const float oscale = (g.mode == 1 && g.exp_u != nullptr) ? exp2f(-static_cast<float>(*g.exp_u + *g.exp_v)) : 1.f;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; c++) {
                 uint32_t r[32];
@@ -339,7 +344,7 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
 #pragma unroll
                     for (int jj = 0; jj < 32; jj++) {
                         if (col0 + jj < g.N) {
-                            float v = __uint_as_float(r[jj]) + bm;
+                            float v = __uint_as_float(r[jj]) * oscale + bm;
                             if (g.bias_n != nullptr) v += g.bias_n[col0 + jj];
                             if (g.relu) v = fmaxf(v, 0.f);
                             dst[jj] = v;
@@ -477,8 +482,13 @@ static int launch_impl(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &
 }
 
 int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, int nterms, int splits,
-                   const GemmEpilogue &epi, int *Mpad_out, int *Npad_out, int *splits_used) {
-    if (!u.valid || !v.valid || u.ldk != v.ldk || u.ldk % kBlockK != 0) {
+                   const GemmEpilogue &epi, int *Mpad_out, int *Npad_out, int *splits_used, int fmt) {
+    const bool f16 = fmt == kFmtF16;
+    if (f16 && (nterms != 1 || !u.f16_valid || !v.f16_valid)) {
+        set_error("block GEMM: fp16 operands missing (or asked for a split-precision pass)");
+        return NB200_ERR_STATE;
+    }
+    if ((!f16 && (!u.valid || !v.valid)) || u.ldk != v.ldk || u.ldk % kBlockK != 0) {
         set_error("block GEMM: operand planes missing or K pitch mismatch (%lld vs %lld)", (long long)u.ldk,
                   (long long)v.ldk);
         return NB200_ERR_STATE;
@@ -519,11 +529,20 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
         g.out = epi.out; g.out_ld = epi.out_ld; g.bias_m = epi.bias_m; g.bias_n = epi.bias_n; g.relu = epi.relu;
     }
     g.err_flag = c->err_flag;
+    // operand format field of the instruction descriptor: 1 = BF16, 0 = F16 (bits 7-9 and 10-12)
+    g.idesc = umma_idesc_bf16(kind == 0 ? kBlockM : 256, kind == 0 ? BN : 256);
+    if (f16) {
+        g.idesc &= ~((7u << 7) | (7u << 10));
+        g.exp_u = u.f16_exp;
+        g.exp_v = v.f16_exp;
+    }
+    const __nv_bfloat16 *u_hi = f16 ? reinterpret_cast<const __nv_bfloat16 *>(u.f16) : u.hi;  // TMA only moves 16-bit words
+    const __nv_bfloat16 *v_hi = f16 ? reinterpret_cast<const __nv_bfloat16 *>(v.f16) : v.hi;
 
     CUtensorMap mu_hi, mu_lo, mv_hi, mv_lo;
     const int v_box = kind == 0 ? BN : BN / 2;  // the 2-SM kernels load half of the V tile per CTA
-    NB_TRY(make_plane_map(&mu_hi, u.hi, u.rows, u.ldk, kBlockM));
-    NB_TRY(make_plane_map(&mv_hi, v.hi, v.rows, v.ldk, v_box));
+    NB_TRY(make_plane_map(&mu_hi, u_hi, u.rows, u.ldk, kBlockM));
+    NB_TRY(make_plane_map(&mv_hi, v_hi, v.rows, v.ldk, v_box));
     if (nterms == 3) {
         NB_TRY(make_plane_map(&mu_lo, u.lo, u.rows, u.ldk, kBlockM));
         NB_TRY(make_plane_map(&mv_lo, v.lo, v.rows, v.ldk, v_box));
@@ -647,6 +666,7 @@ extern "C" int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, co
     GemmArgs g{};
     g.M = I; g.N = J; g.tiles_n = tiles_n; g.num_kb = num_kb; g.kb_per_split = per; g.nterms = 1; g.mode = 0;
     g.ws = partial; g.ws_split_stride = static_cast<long long>(Mpad) * Npad; g.ws_ld = Npad; g.err_flag = fault;
+    g.idesc = umma_idesc_bf16(kBlockM, BN);
     const dim3 grid(tiles_m * tiles_n, splits);
     if (BN == 256) k_block_gemm<256, 4><<<grid, kThreads, SmemLayout<256, 4>::kTotal, stream>>>(ma, ma, mb, mb, g);
     else k_block_gemm<128, 6><<<grid, kThreads, SmemLayout<128, 6>::kTotal, stream>>>(ma, ma, mb, mb, g);

@@ -4,6 +4,7 @@
 
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -60,6 +61,11 @@ struct Planes {
     float *row_sumsq = nullptr;   // per row sum of squares of the source values
     float *maxabs = nullptr;      // device scalar: max |value|
     bool valid = false, lo_valid = false;
+    // fp16 plane (NB200_PREC_F16): f16 = half(x * 2^e) with e a per-plane power-of-two exponent held on the device
+    __half *f16 = nullptr;
+    int *f16_exp = nullptr;        // device int
+    float *f16_maxscaled = nullptr; // device float: max |x * 2^e| seen by the conversion (overflow check)
+    bool f16_valid = false;
 };
 
 // ---- block GEMM on tensor cores (nb200_gemm.cu) ------------------------------------------------
@@ -73,10 +79,11 @@ struct GemmEpilogue {
     const float *bias_n = nullptr;  // per column of P
     int relu = 0;
 };
+enum { kFmtBF16 = 0, kFmtF16 = 1 };
 // P[M x N] = U[M x K] * V[N x K]^T with U,V bf16 K-major planes; nterms 1 (hi*hi) or 3.
 // splits > 1 (or mode 0) leaves partials in ctx->ws laid out [split][Mpad][Npad].
 int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, int nterms, int splits,
-                   const GemmEpilogue &epi, int *Mpad, int *Npad, int *splits_used);
+                   const GemmEpilogue &epi, int *Mpad, int *Npad, int *splits_used, int fmt = kFmtBF16);
 int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms);
 
 // ---- other kernels (nb200_kernels.cu) -----------------------------------------------------------
@@ -93,9 +100,17 @@ struct ReduceOut {
     int64_t f64_ld = 0;
     Planes *planes = nullptr;  // P orientation (rows = M, K = N)
     bool want_lo = false;
+    // fp16 operands carry power-of-two scales: the partial sums are multiplied by 2^-(exp_u + exp_v)
+    const int *exp_u = nullptr, *exp_v = nullptr;
+    float *out_maxabs = nullptr;  // device float: max |result| (to pick the next layer's fp16 scale)
 };
 int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npad, const float *bias_m,
                          const float *bias_n, int relu, const ReduceOut &o);
+// fp16 plane of `src` (same orientation): picks the exponent from a row sample (sample_stride > 1) or exactly
+int launch_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
+                       int sample_stride, const float *known_maxabs);
+int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
+                               Planes *p);
 int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t cols, int64_t ld, float *dst, int64_t dld);
 int launch_f64_to_f32(Context *c, const double *src, int64_t n, float *dst);
 int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,

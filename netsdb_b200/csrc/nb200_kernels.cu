@@ -112,11 +112,12 @@ k_convert_planes(const T *__restrict__ src, long long ld, long long cols, __nv_b
 
 static int alloc_planes(Planes *p, int64_t rows, int64_t k, bool want_lo) {
     const int64_t ldk = round_up(k, 64);
-    if (p->hi && (p->cap_rows < rows || p->ldk != ldk)) {
+    if ((p->hi || p->f16) && (p->cap_rows < rows || p->ldk != ldk)) {
         cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
+        cudaFree(p->f16); cudaFree(p->f16_exp); cudaFree(p->f16_maxscaled);
         *p = Planes();
     }
-    if (!p->hi) p->cap_rows = rows;
+    if (!p->hi && !p->f16) p->cap_rows = rows;
     p->rows = rows; p->k = k; p->ldk = ldk;
     const size_t bytes = static_cast<size_t>(p->cap_rows ? p->cap_rows : 1) * ldk * sizeof(__nv_bfloat16);
     if (!p->hi) NB_CUDA(cudaMalloc(&p->hi, bytes));
@@ -144,6 +145,124 @@ int launch_convert_planes(Context *c, const void *src, bool src_is_f64, int64_t 
     NB_LAUNCH_CHECK(c);
     p->valid = true;
     p->lo_valid = want_lo;
+    return NB200_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// fp16 operand planes (NB200_PREC_F16).  fp16 has 3 more mantissa bits than bf16 at the same tensor
+// rate but only 5 exponent bits, so every plane carries a power-of-two scale 2^e chosen from max |x|:
+// with the exact maximum the largest element lands in [2^14, 2^15); with a maximum estimated from a
+// sample of rows (the per-query inputs, where a full extra pass over 47.8 GB would cost as much as the
+// conversion itself) it lands in [2^10, 2^11), leaving 32x headroom, and the conversion records the
+// largest scaled magnitude so that an overflow is detected and the caller can fall back.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_max_sampled(const T *__restrict__ src, long long ld, long long rows, long long cols, int stride,
+              float *__restrict__ maxabs) {
+    float mx = 0.f;
+    for (long long r = static_cast<long long>(blockIdx.x) * stride; r < rows; r += static_cast<long long>(gridDim.x) * stride) {
+        const T *srow = src + r * ld;
+        for (long long c = threadIdx.x; c < cols; c += 256) mx = fmaxf(mx, fabsf(static_cast<float>(srow[c])));
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<unsigned int *>(maxabs), __float_as_uint(mx));
+}
+__global__ void k_exp_from_max(const float *__restrict__ maxabs, int target_log2, int *__restrict__ exp_out) {
+    int q = 0;
+    const float m = *maxabs;
+    if (m > 0.f && isfinite(m)) frexpf(m, &q);  // m = f * 2^q with f in [0.5, 1)  =>  m * 2^(target - q) < 2^target
+    *exp_out = (m > 0.f && isfinite(m)) ? target_log2 - q : 0;
+}
+template <typename T>
+__global__ void __launch_bounds__(kCvtThreads)
+k_convert_f16(const T *__restrict__ src, long long ld, long long cols, __half *__restrict__ dst, long long ldk,
+              const int *__restrict__ exp_in, float *__restrict__ row_sumsq, float *__restrict__ maxscaled) {
+    __shared__ float sh[32];
+    const long long row = blockIdx.x;
+    const long long c0 = static_cast<long long>(blockIdx.y) * kCvtChunk + threadIdx.x * 4;
+    const T *srow = src + row * ld;
+    const float scale = exp2f(static_cast<float>(*exp_in));
+    float ss = 0.f, mx = 0.f;
+#pragma unroll
+    for (int h = 0; h < kCvtPerThread / 4; h++) {
+        const long long c = c0 + static_cast<long long>(h) * kCvtThreads * 4;
+        if (c >= ldk) continue;
+        T v[4];
+        if (c + 3 < cols && ((reinterpret_cast<uintptr_t>(srow + c) & (sizeof(T) * 2 - 1)) == 0)) {
+            if (sizeof(T) == 8) {
+                const double2 a = *reinterpret_cast<const double2 *>(srow + c);
+                const double2 b = *reinterpret_cast<const double2 *>(srow + c + 2);
+                v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+            } else {
+                const float2 a = *reinterpret_cast<const float2 *>(srow + c);
+                const float2 b = *reinterpret_cast<const float2 *>(srow + c + 2);
+                v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) v[j] = (c + j < cols) ? srow[c + j] : T(0);
+        }
+        __half h4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float f = static_cast<float>(v[j]);
+            const float sc = f * scale;  // exact (power of two) unless it overflows
+            h4[j] = __float2half_rn(sc);
+            ss += f * f;
+            mx = fmaxf(mx, fabsf(sc));
+        }
+        *reinterpret_cast<uint2 *>(dst + row * ldk + c) = *reinterpret_cast<uint2 *>(h4);
+    }
+    ss = block_reduce_sum(ss, sh);
+    mx = block_reduce_max(mx, sh);
+    if (threadIdx.x == 0) {
+        if (row_sumsq) atomicAdd(row_sumsq + row, ss);
+        if (maxscaled) atomicMax(reinterpret_cast<unsigned int *>(maxscaled), __float_as_uint(mx));
+    }
+}
+
+int launch_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
+                       int sample_stride, const float *known_maxabs) {
+    const int64_t ldk = round_up(cols, 64);
+    if ((p->hi || p->f16) && (p->cap_rows < rows || p->ldk != ldk)) {
+        cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
+        cudaFree(p->f16); cudaFree(p->f16_exp); cudaFree(p->f16_maxscaled);
+        *p = Planes();
+    }
+    if (!p->hi && !p->f16) p->cap_rows = rows;
+    p->rows = rows; p->k = cols; p->ldk = ldk;
+    const size_t cap = static_cast<size_t>(p->cap_rows ? p->cap_rows : 1);
+    if (!p->f16) NB_CUDA(cudaMalloc(&p->f16, cap * ldk * sizeof(__half)));
+    if (!p->f16_exp) NB_CUDA(cudaMalloc(&p->f16_exp, sizeof(int)));
+    if (!p->f16_maxscaled) NB_CUDA(cudaMalloc(&p->f16_maxscaled, sizeof(float)));
+    if (!p->row_sumsq) NB_CUDA(cudaMalloc(&p->row_sumsq, cap * sizeof(float)));
+    if (!p->maxabs) NB_CUDA(cudaMalloc(&p->maxabs, sizeof(float)));
+    NB_CUDA(cudaMemsetAsync(p->row_sumsq, 0, static_cast<size_t>(rows ? rows : 1) * sizeof(float), c->stream));
+    NB_CUDA(cudaMemsetAsync(p->f16_maxscaled, 0, sizeof(float), c->stream));
+    p->f16_valid = true;
+    if (rows == 0 || cols == 0) {
+        NB_CUDA(cudaMemsetAsync(p->f16_exp, 0, sizeof(int), c->stream));
+        return NB200_OK;
+    }
+    const float *mx = known_maxabs;
+    if (!mx) {
+        NB_CUDA(cudaMemsetAsync(p->maxabs, 0, sizeof(float), c->stream));
+        const int stride = sample_stride > 1 ? sample_stride : 1;
+        const int64_t nsamp = ceil_div(rows, stride);
+        const unsigned blocks = static_cast<unsigned>(nsamp < 148 * 16 ? nsamp : 148 * 16);
+        if (src_is_f64) k_max_sampled<double><<<blocks, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, stride, p->maxabs);
+        else k_max_sampled<float><<<blocks, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, stride, p->maxabs);
+        NB_LAUNCH_CHECK(c);
+        mx = p->maxabs;
+    }
+    k_exp_from_max<<<1, 1, 0, c->stream>>>(mx, (!known_maxabs && sample_stride > 1) ? 11 : 15, p->f16_exp);
+    NB_LAUNCH_CHECK(c);
+    dim3 grid(static_cast<unsigned>(rows), static_cast<unsigned>(ceil_div(ldk, kCvtChunk)));
+    if (src_is_f64) k_convert_f16<double><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->f16, ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled);
+    else k_convert_f16<float><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->f16, ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled);
+    NB_LAUNCH_CHECK(c);
     return NB200_OK;
 }
 
@@ -261,8 +380,10 @@ k_splitk_reduce(const float *__restrict__ ws, long long split_stride, int ws_ld,
                 const float *__restrict__ bias_m, const float *__restrict__ bias_n, int relu,
                 float *__restrict__ of32, long long of32_ld, double *__restrict__ of64, long long of64_ld,
                 __nv_bfloat16 *__restrict__ phi, __nv_bfloat16 *__restrict__ plo, long long ldk,
-                float *__restrict__ row_sumsq) {
+                float *__restrict__ row_sumsq, const int *__restrict__ exp_u, const int *__restrict__ exp_v,
+                float *__restrict__ out_maxabs) {
     __shared__ float sh[32];
+    const float oscale = exp_u ? exp2f(-static_cast<float>(*exp_u + *exp_v)) : 1.f;
     const long long m = blockIdx.x;
     const int n0 = (blockIdx.y * 256 + threadIdx.x) * 4;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
@@ -274,7 +395,7 @@ k_splitk_reduce(const float *__restrict__ ws, long long split_stride, int ws_ld,
             const float4 t = *reinterpret_cast<const float4 *>(p + s * split_stride);
             acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
         }
-        v[0] = acc.x; v[1] = acc.y; v[2] = acc.z; v[3] = acc.w;
+        v[0] = acc.x * oscale; v[1] = acc.y * oscale; v[2] = acc.z * oscale; v[3] = acc.w * oscale;
         const float bm = bias_m ? bias_m[m] : 0.f;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
@@ -311,12 +432,18 @@ k_splitk_reduce(const float *__restrict__ ws, long long split_stride, int ws_ld,
         ss = block_reduce_sum(ss, sh);
         if (threadIdx.x == 0) atomicAdd(row_sumsq + m, ss);
     }
+    if (out_maxabs) {
+        float mx = fmaxf(fmaxf(fabsf(v[0]), fabsf(v[1])), fmaxf(fabsf(v[2]), fabsf(v[3])));
+        mx = block_reduce_max(mx, sh);
+        if (threadIdx.x == 0) atomicMax(reinterpret_cast<unsigned int *>(out_maxabs), __float_as_uint(mx));
+    }
 }
 
 // planes only: global max |v| of a freshly written plane is not needed (error model uses weights')
 int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npad, const float *bias_m,
                          const float *bias_n, int relu, const ReduceOut &o) {
     Planes *p = o.planes;
+    if (o.out_maxabs) NB_CUDA(cudaMemsetAsync(o.out_maxabs, 0, sizeof(float), c->stream));
     if (p) {
         NB_TRY(alloc_planes(p, M, N, o.want_lo));
         NB_CUDA(cudaMemsetAsync(p->row_sumsq, 0, static_cast<size_t>(M) * sizeof(float), c->stream));
@@ -326,7 +453,7 @@ int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npa
     k_splitk_reduce<<<grid, 256, 0, c->stream>>>(c->ws, static_cast<long long>(Mpad) * Npad, Npad, splits, M, N, bias_m,
                                                  bias_n, relu, o.f32, o.f32_ld, o.f64, o.f64_ld, p ? p->hi : nullptr,
                                                  (p && o.want_lo) ? p->lo : nullptr, p ? p->ldk : 0,
-                                                 p ? p->row_sumsq : nullptr);
+                                                 p ? p->row_sumsq : nullptr, o.exp_u, o.exp_v, o.out_maxabs);
     NB_LAUNCH_CHECK(c);
     if (p) { p->valid = true; p->lo_valid = o.want_lo; }
     return NB200_OK;

@@ -23,6 +23,7 @@ inline int precision_from_env() {
     if (!e) return NB200_PREC_BF16;
     if (!strcmp(e, "bf16x3")) return NB200_PREC_BF16X3;
     if (!strcmp(e, "fp64")) return NB200_PREC_FP64;
+    if (!strcmp(e, "f16")) return NB200_PREC_F16;
     return NB200_PREC_BF16;
 }
 

@@ -4,6 +4,7 @@ the stated tolerance relative to the logit scale max|z|:
     FP64   1e-12   (summation order only)
     BF16X3 1e-4    (north_star: <= 1e-4 at fp32 accumulation)
     BF16   2e-2    (the looser stated bound for the single-pass bf16 variant)
+    F16    2.5e-3  (single-pass fp16 with power-of-two scaling: 3 more mantissa bits than bf16)
 """
 import os
 
@@ -12,7 +13,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 G = os.path.join(os.path.dirname(__file__), "golden")
-TOL = {"fp64": 1e-12, "bf16x3": 1e-4, "bf16": 2e-2}
+TOL = {"fp64": 1e-12, "bf16x3": 1e-4, "bf16": 2e-2, "f16": 2.5e-3}
 
 
 def rel(a, b):
@@ -49,7 +50,7 @@ def test_block_upload_download_roundtrip(nb, oracle):
     s.destroy(), t.destroy()
 
 
-@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16"])
+@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16", "f16"])
 @pytest.mark.parametrize("shape", [(230, 310, 150, 100), (64, 128, 64, 64), (5, 7, 3, 4), (300, 2500, 129, 100)])
 def test_transpose_mult_and_input_layer_join(nb, oracle, prec, shape):
     I, K, J, blk = shape
@@ -73,7 +74,7 @@ def test_transpose_mult_and_input_layer_join(nb, oracle, prec, shape):
     assert rel(C2.download_dense(), ref2.dense()) <= TOL[prec]
 
 
-@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16"])
+@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16", "f16"])
 def test_fused_bias_epilogues(nb, oracle, prec):
     I, K, J, blk = 130, 270, 90, 50
     a, b, bias = oracle.synth_dense(I, K, 1), oracle.synth_dense(J, K, 2), oracle.synth_dense(I, 1, 3) * 20
@@ -135,7 +136,7 @@ def _ff_sets(nb, oracle, batch, feat, hid, lab, blk, wo_scale=1.0, dense=None):
     return dev, ora, dense
 
 
-@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16"])
+@pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16", "f16"])
 def test_ff_inference_unit_config1(nb, oracle, prec):
     """BASELINE config 1: batch 1,000 x 1,024 features, hidden 1,024, 10 labels, 100 x 100 blocks."""
     dev, ora, _ = _ff_sets(nb, oracle, 1000, 1024, 1024, 10, 100)
@@ -159,7 +160,7 @@ def test_ff_inference_unit_config1(nb, oracle, prec):
 def test_ff_golden_fixtures(nb, oracle):
     g = np.load(os.path.join(G, "kat_2x3.npz"))
     dense = {k: g[k] for k in ("x", "w1", "b1", "wo", "bo")}
-    for prec in ("fp64", "bf16x3", "bf16"):
+    for prec in ("fp64", "bf16x3", "bf16", "f16"):
         dev, _, _ = _ff_sets(nb, oracle, 2, 3, 2, 2, int(g["block"]), dense=dense)
         out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
         assert np.array_equal(labels, g["labels"])
@@ -167,7 +168,7 @@ def test_ff_golden_fixtures(nb, oracle):
         assert np.abs(out.download_dense() - g["probs"]).max() <= 1e-6 if prec != "fp64" else 1e-15
     g = np.load(os.path.join(G, "ff_small.npz"))
     batch, feat, hid, lab, blk = (int(g[k]) for k in ("batch", "feat", "hid", "lab", "block"))
-    for prec in ("fp64", "bf16x3", "bf16"):
+    for prec in ("fp64", "bf16x3", "bf16", "f16"):
         dev, _, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk, wo_scale=float(g["wo_scale"]))
         out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
         assert np.array_equal(labels, g["labels"])
@@ -179,7 +180,7 @@ def test_ff_ragged_and_tiny_and_empty(nb, oracle):
     for (batch, feat, hid, lab, blk) in [(1, 1, 1, 1, 1), (3, 5, 2, 4, 2), (129, 65, 257, 33, 64), (130, 1000, 70, 300, 100)]:
         dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk)
         ref_out, ref_logits, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=2)
-        for prec in ("fp64", "bf16x3", "bf16"):
+        for prec in ("fp64", "bf16x3", "bf16", "f16"):
             out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
             assert np.array_equal(labels, ref_labels), (batch, feat, hid, lab, prec)
             z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
@@ -202,10 +203,33 @@ def test_near_tie_rows_are_re_evaluated(nb, oracle):
     dense["bo"][7] = dense["bo"][2]
     dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk, dense=dense)
     _, _, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=2)
-    for prec in ("bf16x3", "bf16"):
+    for prec in ("bf16x3", "bf16", "f16"):
         _, labels, stats = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PRECISIONS[prec])
         assert np.array_equal(labels, ref_labels)
         assert stats["refined_rows"] >= int(np.isin(ref_labels, (2, 7)).sum())
+
+
+def test_f16_scaling_handles_large_and_tiny_magnitudes(nb, oracle):
+    """fp16 has 5 exponent bits; the per-matrix power-of-two scales must keep products of very large or very small
+    inputs inside range, and an input outlier that the sampled scale misses must fall back (not return inf)."""
+    I, K, J, blk = 150, 900, 140, 100
+    a, b = oracle.synth_dense(I, K, 31), oracle.synth_dense(J, K, 32)
+    for sa, sb in ((1e6, 3e5), (1e-6, 2e-7), (1e5, 1e-5)):
+        A = nb.DeviceSet.create("t", "a", I, K, blk, blk); A.upload_dense(a * sa)
+        B = nb.DeviceSet.create("t", "b", J, K, blk, blk); B.upload_dense(b * sb)
+        C = nb.gemm_blocks(nb.OP_NT, A, B, nb.EPI_NONE, None, nb.PREC_F16, "t", "c").download_dense()
+        assert np.isfinite(C).all() and rel(C, (a * sa) @ (b * sb).T) <= TOL["f16"]
+    # inference with one huge input element in a row that the 1-in-64 row sample does not see
+    batch, feat, hid, lab = 200, 300, 64, 7
+    dense = dict(x=oracle.synth_dense(batch, feat, 1), w1=oracle.synth_dense(hid, feat, 2), b1=oracle.synth_dense(hid, 1, 3),
+                 wo=oracle.synth_dense(lab, hid, 4), bo=oracle.synth_dense(lab, 1, 5))
+    dense["x"][37, 11] = 4.0e3          # 8000x the typical magnitude: beyond the 32x headroom of the sampled scale
+    dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, 50, dense=dense)
+    _, ref_logits, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=2)
+    _, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PREC_F16)
+    z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
+    assert np.isfinite(z).all() and np.array_equal(labels, ref_labels)
+    assert rel(z, ref_logits.dense()) <= TOL["bf16"]
 
 
 def test_conv2d_memory_fusion(nb, oracle):
@@ -214,7 +238,7 @@ def test_conv2d_memory_fusion(nb, oracle):
     assert np.array_equal(IF.download_dense(), g["image_flat"])           # pure data movement: bit exact
     KF = nb.conv2d_kernel_flat(g["kernels"], g["bias"], 4, 5)
     assert np.array_equal(KF.download_dense(), g["kernel_flat"])
-    for prec in ("fp64", "bf16x3", "bf16"):
+    for prec in ("fp64", "bf16x3", "bf16", "f16"):
         R = nb.gemm_blocks(nb.OP_NT, IF, KF, nb.EPI_NONE, None, nb.PRECISIONS[prec], "conv2d", "result")
         assert rel(R.download_dense(), g["result"]) <= TOL[prec]
         F = nb.conv2d_fused(g["images"], g["kernels"], g["bias"], 0, True, nb.PRECISIONS[prec], 4, 5)
@@ -237,7 +261,7 @@ def test_word2vec_block_join(nb, oracle):
     W = nb.DeviceSet.create("word2vec", "weights0", dim, vocab, blk, blk); W.upload_dense(w)
     X = nb.DeviceSet.create("word2vec", "inputs", batch, vocab, blk, blk); X.upload_dense(x)
     ref = oracle.transpose_mult_agg(oracle.load_matrix(w, blk, blk), oracle.load_matrix(x, blk, blk), 4).dense()
-    for prec in ("fp64", "bf16x3", "bf16"):
+    for prec in ("fp64", "bf16x3", "bf16", "f16"):
         out = nb.gemm_blocks(nb.OP_NT, W, X, nb.EPI_NONE, None, nb.PRECISIONS[prec], "word2vec", "outputs")
         assert out.info()[:2] == (dim, batch)
         assert rel(out.download_dense(), ref) <= TOL[prec]
@@ -250,7 +274,7 @@ def _run(cmd, env_extra, timeout=300):
     return subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
 
 
-@pytest.mark.parametrize("prec", ["bf16", "bf16x3", "fp64"])
+@pytest.mark.parametrize("prec", ["bf16", "f16", "bf16x3", "fp64"])
 def test_cpp_driver_through_netsdb_api(oracle, prec, tmp_path):
     """The C++ host shim end to end: FFTest builds the reference's Computation graphs (FFTransposeMult ->
     FFAggMatrix -> FFReluBiasSum -> FFInputLayerJoin -> FFAggMatrix -> FFTransposeBiasSum; FFRowAggregate ->
