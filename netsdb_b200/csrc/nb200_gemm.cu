@@ -47,6 +47,7 @@ struct GemmArgs {
     unsigned int idesc;  // tcgen05 instruction descriptor (operand format bf16 or fp16, tile shape)
     const int *exp_u;    // fp16 operand scales (device ints, may be null): result *= 2^-(exp_u + exp_v)
     const int *exp_v;
+    int split_offset;    // blockIdx.y + split_offset = global split index (partial launches)
 };
 
 template <int BN, int STAGES>
@@ -75,7 +76,7 @@ k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant
     const int lane = threadIdx.x & 31;
     const int tile_m = blockIdx.x / g.tiles_n;
     const int tile_n = blockIdx.x % g.tiles_n;
-    const int split = blockIdx.y;
+    const int split = blockIdx.y + g.split_offset;
     const int kb0 = split * g.kb_per_split;
     const int kb1 = min(kb0 + g.kb_per_split, g.num_kb);
     const int n_iter = max(kb1 - kb0, 0) * g.nterms;
@@ -240,7 +241,7 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
     const int pair = blockIdx.x >> 1;
     const int tile_m = pair / g.tiles_n;
     const int tile_n = pair % g.tiles_n;
-    const int split = blockIdx.y;
+    const int split = blockIdx.y + g.split_offset;
     const int kb0 = split * g.kb_per_split;
     const int kb1 = min(kb0 + g.kb_per_split, g.num_kb);
     const int n_iter = max(kb1 - kb0, 0) * g.nterms;
@@ -433,7 +434,7 @@ int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms) {
 
 template <int NSUB, int STAGES>
 static int launch_impl_2sm(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
-                           const CUtensorMap &mv_lo, const GemmArgs &g, int pair_tiles, int splits) {
+                           const CUtensorMap &mv_lo, const GemmArgs &g, int pair_tiles, int splits, cudaStream_t stream) {
     using L = SmemLayout2<NSUB, STAGES>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -441,7 +442,7 @@ static int launch_impl_2sm(Context *c, const CUtensorMap &mu_hi, const CUtensorM
         attr_set = true;
     }
     dim3 grid(2 * pair_tiles, splits);
-    k_block_gemm_2sm<NSUB, STAGES><<<grid, kThreads, L::kTotal, c->stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
+    k_block_gemm_2sm<NSUB, STAGES><<<grid, kThreads, L::kTotal, stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     return NB200_OK;
@@ -467,7 +468,7 @@ static int pick_kernel(int M, int N, int64_t ldk) {
 
 template <int BN, int STAGES>
 static int launch_impl(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
-                       const CUtensorMap &mv_lo, const GemmArgs &g, int tiles, int splits) {
+                       const CUtensorMap &mv_lo, const GemmArgs &g, int tiles, int splits, cudaStream_t stream) {
     using L = SmemLayout<BN, STAGES>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -475,7 +476,7 @@ static int launch_impl(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &
         attr_set = true;
     }
     dim3 grid(tiles, splits);
-    k_block_gemm<BN, STAGES><<<grid, kThreads, L::kTotal, c->stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
+    k_block_gemm<BN, STAGES><<<grid, kThreads, L::kTotal, stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     return NB200_OK;
@@ -550,10 +551,19 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
         mu_lo = mu_hi;
         mv_lo = mv_hi;
     }
-    if (kind == 2) return launch_impl_2sm<2, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
-    if (kind == 1) return launch_impl_2sm<1, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
-    if (BN == 256) return launch_impl<256, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
-    return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, splits);
+    // partial launch: only splits [split_begin, split_begin + split_count)
+    int launch_splits = splits;
+    if (epi.split_count >= 0) {
+        g.split_offset = epi.split_begin;
+        launch_splits = epi.split_count;
+        if (epi.split_begin + launch_splits > splits) launch_splits = splits - epi.split_begin;
+        if (launch_splits <= 0) return NB200_OK;
+    }
+    cudaStream_t stream = epi.stream ? epi.stream : c->stream;
+    if (kind == 2) return launch_impl_2sm<2, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    if (kind == 1) return launch_impl_2sm<1, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    if (BN == 256) return launch_impl<256, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -44,6 +44,10 @@ struct Context {
     size_t stage_bytes = 0;
     int64_t launches = 0;
     cudaEvent_t ev[8] = {};
+    // K-chunk pipelining of layer 1: conversion of chunk j+1 runs beside the GEMM of chunk j
+    cudaStream_t aux[3] = {};        // [0] conversion, [1],[2] alternating GEMM streams
+    cudaEvent_t chunk_ev[64] = {};   // conversion of chunk j done
+    cudaEvent_t join_ev[4] = {};
 };
 Context *ctx();                                   // nullptr before nb200_init
 int ensure_ws(Context *c, size_t bytes);          // grows c->ws
@@ -78,6 +82,10 @@ struct GemmEpilogue {
     const float *bias_m = nullptr;  // per row of P
     const float *bias_n = nullptr;  // per column of P
     int relu = 0;
+    // launch only splits [split_begin, split_begin + split_count) of the `splits` the workspace is laid out for,
+    // on `stream` (default: the context's stream)
+    int split_begin = 0, split_count = -1;
+    cudaStream_t stream = nullptr;
 };
 enum { kFmtBF16 = 0, kFmtF16 = 1 };
 // P[M x N] = U[M x K] * V[N x K]^T with U,V bf16 K-major planes; nterms 1 (hi*hi) or 3.
@@ -109,6 +117,11 @@ int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npa
 // fp16 plane of `src` (same orientation): picks the exponent from a row sample (sample_stride > 1) or exactly
 int launch_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
                        int sample_stride, const float *known_maxabs);
+// the same in two steps: pick the scale (and clear the statistics) now, convert column ranges later on any stream
+int prepare_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
+                        int sample_stride, const float *known_maxabs);
+int launch_convert_f16_cols(Context *c, cudaStream_t stream, const void *src, bool src_is_f64, int64_t rows, int64_t cols,
+                            int64_t ld, Planes *p, int64_t col_begin, int64_t col_count);
 int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_t cols, const int32_t *list, int n,
                                Planes *p);
 int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t cols, int64_t ld, float *dst, int64_t dld);

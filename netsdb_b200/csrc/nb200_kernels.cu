@@ -8,6 +8,7 @@
 #include "nb200_internal.h"
 
 #include <cfloat>
+#include <cstdlib>
 #include <math_constants.h>
 
 namespace nb200 {
@@ -175,56 +176,69 @@ __global__ void k_exp_from_max(const float *__restrict__ maxabs, int target_log2
     if (m > 0.f && isfinite(m)) frexpf(m, &q);  // m = f * 2^q with f in [0.5, 1)  =>  m * 2^(target - q) < 2^target
     *exp_out = (m > 0.f && isfinite(m)) ? target_log2 - q : 0;
 }
+// Persistent: a bounded number of CTAs walks over (row, 4096-column piece) tiles of the column range, so that
+// when this conversion runs beside the layer-1 GEMM (K-chunk pipelining) it leaves SM thread slots to the GEMM's
+// CTAs instead of flooding the block scheduler with millions of tiny CTAs.  16 elements (4 x 32-byte loads) per
+// thread are in flight to keep HBM busy at that low occupancy.
+constexpr int kF16Piece = kCvtThreads * 16;
 template <typename T>
 __global__ void __launch_bounds__(kCvtThreads)
-k_convert_f16(const T *__restrict__ src, long long ld, long long cols, __half *__restrict__ dst, long long ldk,
-              const int *__restrict__ exp_in, float *__restrict__ row_sumsq, float *__restrict__ maxscaled) {
+k_convert_f16(const T *__restrict__ src, long long ld, long long rows, long long cols, __half *__restrict__ dst,
+              long long ldk, const int *__restrict__ exp_in, float *__restrict__ row_sumsq,
+              float *__restrict__ maxscaled, long long col_begin, long long col_end) {
     __shared__ float sh[32];
-    const long long row = blockIdx.x;
-    const long long c0 = static_cast<long long>(blockIdx.y) * kCvtChunk + threadIdx.x * 4;
-    const T *srow = src + row * ld;
     const float scale = exp2f(static_cast<float>(*exp_in));
-    float ss = 0.f, mx = 0.f;
+    const long long pieces = (col_end - col_begin + kF16Piece - 1) / kF16Piece;
+    const long long tiles = rows * pieces;
+    float mx = 0.f;
+    for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const long long row = t / pieces, piece = t % pieces;
+        const T *srow = src + row * ld;
+        const long long c0 = col_begin + piece * kF16Piece + threadIdx.x * 4;
+        T v[4][4];
 #pragma unroll
-    for (int h = 0; h < kCvtPerThread / 4; h++) {
-        const long long c = c0 + static_cast<long long>(h) * kCvtThreads * 4;
-        if (c >= ldk) continue;
-        T v[4];
-        if (c + 3 < cols && ((reinterpret_cast<uintptr_t>(srow + c) & (sizeof(T) * 2 - 1)) == 0)) {
-            if (sizeof(T) == 8) {
-                const double2 a = *reinterpret_cast<const double2 *>(srow + c);
-                const double2 b = *reinterpret_cast<const double2 *>(srow + c + 2);
-                v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+        for (int h = 0; h < 4; h++) {
+            const long long c = c0 + static_cast<long long>(h) * kCvtThreads * 4;
+            if (c + 3 < cols && c + 3 < col_end && ((reinterpret_cast<uintptr_t>(srow + c) & (sizeof(T) * 2 - 1)) == 0)) {
+                if (sizeof(T) == 8) {
+                    const double2 a = *reinterpret_cast<const double2 *>(srow + c);
+                    const double2 b = *reinterpret_cast<const double2 *>(srow + c + 2);
+                    v[h][0] = a.x; v[h][1] = a.y; v[h][2] = b.x; v[h][3] = b.y;
+                } else {
+                    const float2 a = *reinterpret_cast<const float2 *>(srow + c);
+                    const float2 b = *reinterpret_cast<const float2 *>(srow + c + 2);
+                    v[h][0] = a.x; v[h][1] = a.y; v[h][2] = b.x; v[h][3] = b.y;
+                }
             } else {
-                const float2 a = *reinterpret_cast<const float2 *>(srow + c);
-                const float2 b = *reinterpret_cast<const float2 *>(srow + c + 2);
-                v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+#pragma unroll
+                for (int j = 0; j < 4; j++) v[h][j] = (c + j < cols && c + j < col_end) ? srow[c + j] : T(0);
             }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; j++) v[j] = (c + j < cols) ? srow[c + j] : T(0);
         }
-        __half h4[4];
+        float ss = 0.f;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const float f = static_cast<float>(v[j]);
-            const float sc = f * scale;  // exact (power of two) unless it overflows
-            h4[j] = __float2half_rn(sc);
-            ss += f * f;
-            mx = fmaxf(mx, fabsf(sc));
+        for (int h = 0; h < 4; h++) {
+            const long long c = c0 + static_cast<long long>(h) * kCvtThreads * 4;
+            if (c >= col_end) continue;  // col_end is a multiple of 64, c of 4: whole vector in or out
+            __half h4[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float f = static_cast<float>(v[h][j]);
+                const float sc = f * scale;  // exact (power of two) unless it overflows
+                h4[j] = __float2half_rn(sc);
+                ss += f * f;
+                mx = fmaxf(mx, fabsf(sc));
+            }
+            *reinterpret_cast<uint2 *>(dst + row * ldk + c) = *reinterpret_cast<uint2 *>(h4);
         }
-        *reinterpret_cast<uint2 *>(dst + row * ldk + c) = *reinterpret_cast<uint2 *>(h4);
+        ss = block_reduce_sum(ss, sh);
+        if (threadIdx.x == 0 && row_sumsq) atomicAdd(row_sumsq + row, ss);
     }
-    ss = block_reduce_sum(ss, sh);
     mx = block_reduce_max(mx, sh);
-    if (threadIdx.x == 0) {
-        if (row_sumsq) atomicAdd(row_sumsq + row, ss);
-        if (maxscaled) atomicMax(reinterpret_cast<unsigned int *>(maxscaled), __float_as_uint(mx));
-    }
+    if (threadIdx.x == 0 && maxscaled) atomicMax(reinterpret_cast<unsigned int *>(maxscaled), __float_as_uint(mx));
 }
 
-int launch_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
-                       int sample_stride, const float *known_maxabs) {
+int prepare_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
+                        int sample_stride, const float *known_maxabs) {
     const int64_t ldk = round_up(cols, 64);
     if ((p->hi || p->f16) && (p->cap_rows < rows || p->ldk != ldk)) {
         cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
@@ -259,11 +273,38 @@ int launch_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t row
     }
     k_exp_from_max<<<1, 1, 0, c->stream>>>(mx, (!known_maxabs && sample_stride > 1) ? 11 : 15, p->f16_exp);
     NB_LAUNCH_CHECK(c);
-    dim3 grid(static_cast<unsigned>(rows), static_cast<unsigned>(ceil_div(ldk, kCvtChunk)));
-    if (src_is_f64) k_convert_f16<double><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->f16, ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled);
-    else k_convert_f16<float><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->f16, ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled);
+    return NB200_OK;
+}
+
+int launch_convert_f16_cols(Context *c, cudaStream_t stream, const void *src, bool src_is_f64, int64_t rows, int64_t cols,
+                            int64_t ld, Planes *p, int64_t col_begin, int64_t col_count) {
+    if (rows == 0 || cols == 0 || col_count <= 0) return NB200_OK;
+    const int64_t col_end = (col_begin + col_count < p->ldk) ? col_begin + col_count : p->ldk;
+    if (col_end <= col_begin) return NB200_OK;
+    const int64_t tiles = rows * ceil_div(col_end - col_begin, kF16Piece);
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    // beside the GEMM (side stream): 2 CTAs per SM; alone: 8 per SM
+    static const int side_ctas = getenv("NB200_CVT_CTAS") ? atoi(getenv("NB200_CVT_CTAS")) : 4;
+    const int64_t cap = static_cast<int64_t>(sms) * (stream == c->stream ? 8 : side_ctas);
+    const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
+    static bool carveout_set = false;
+    if (!carveout_set) {
+        // CTAs of kernels that want different shared-memory carve-outs do not share an SM: ask for the GEMM's
+        // (maximum shared memory) so that this kernel can run beside it
+        NB_CUDA(cudaFuncSetAttribute(k_convert_f16<double>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        NB_CUDA(cudaFuncSetAttribute(k_convert_f16<float>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        carveout_set = true;
+    }
+    if (src_is_f64) k_convert_f16<double><<<grid, kCvtThreads, 0, stream>>>((const double *)src, ld, rows, cols, p->f16, p->ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled, col_begin, col_end);
+    else k_convert_f16<float><<<grid, kCvtThreads, 0, stream>>>((const float *)src, ld, rows, cols, p->f16, p->ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled, col_begin, col_end);
     NB_LAUNCH_CHECK(c);
     return NB200_OK;
+}
+
+int launch_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
+                       int sample_stride, const float *known_maxabs) {
+    NB_TRY(prepare_convert_f16(c, src, src_is_f64, rows, cols, ld, p, sample_stride, known_maxabs));
+    return launch_convert_f16_cols(c, c->stream, src, src_is_f64, rows, cols, ld, p, 0, p->ldk);
 }
 
 // Transposing conversion: plane[c][r] = src[r][c].  32 x 32 tiles through shared memory so both
