@@ -253,8 +253,16 @@ def run_b200(a):
     flops1 = 2.0 * a.batch * a.hidden * a.features  # algorithmic (useful) flops of one launch
     k_ms = stats.get("ms_gemm1_kernel", 0.0)
     ach = flops1 / (k_ms / 1000.0) / 1e12 if k_ms > 0 else None
-    roofline = dict(bound="tensor", kernel="k_block_gemm (layer 1)", achieved=ach, peak=peak_tf, unit="TFLOP/s",
-                    frac=(ach / peak_tf if ach else None), traffic=None, peak_source=which,
+    traffic = None  # dram bytes per launch of that kernel, from the committed `ncu --set full` capture of this workload
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        if (a.batch, a.features, a.hidden) == (10000, 597540, 1000) and a.precision in ("f16", "bf16"):
+            traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+    except Exception:
+        pass
+    roofline = dict(bound="tensor", kernel="k_block_gemm_2sm<2,4> (layer 1)", achieved=ach, peak=peak_tf, unit="TFLOP/s",
+                    frac=(ach / peak_tf if ach else None), traffic=traffic, peak_source=which,
+                    algorithmic_flops_per_launch=flops1,
                     executed_over_useful=3 if a.precision == "bf16x3" else 1)
 
     # --- e2e: host blocks -> device -> labels + output blocks back, through the public C ABI ---
