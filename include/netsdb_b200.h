@@ -152,6 +152,25 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
                             int precision, const char *db, const char *out_set, nb200_set **out,
                             int32_t *labels_host, nb200_ff_stats *stats);
 
+/* ---- K-sharded variant (weights larger than one GPU's HBM) ---------------------------------------------
+ * The reference hash-partitions blocks by blockColIndex (FFMatrixBlock.h:151-156), so each worker multiplies a
+ * slice of K and the aggregation sums the partials across workers over TCP (PipelineStage.cc:120-205).  Here each
+ * GPU holds a column shard of `inputs` and `w1`; nb200_ff_layer1_partial leaves that shard's fp32 partial of
+ * w1 . inputs^T (stored batch x hidden, row-major, pitch ld, NO bias) in a caller-owned DEVICE buffer, the
+ * caller sums the partials across GPUs with one NCCL reduce-scatter / all-reduce over NVLink, and
+ * nb200_ff_finish_from_layer1 applies FFReluBiasSum and runs layer 2 and the softmax on the rows this GPU owns.
+ * The label-exact cascade is not available in this variant (the fp64 rows are sharded too); the number of
+ * undecided rows is returned so that the caller knows how many labels rest on the tensor-core precision.
+ * For that estimate the partial buffer may carry one extra column (ld > hidden): column `hidden` receives the
+ * shard's per-row sum of squares of the inputs, which the same reduction turns into the global one, and the
+ * caller passes the maximum of nb200_set_maxabs(w1_shard) over all ranks as w1_maxabs (0 = skip the estimate). */
+int nb200_ff_layer1_partial(nb200_set *w1_shard, nb200_set *inputs_shard, int precision, float *partial_dev, int64_t ld);
+int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb200_set *b1, nb200_set *wo, nb200_set *bo,
+                                int precision, float w1_maxabs, const char *db, const char *out_set, nb200_set **out,
+                                int32_t *labels_host, int *undecided_rows);
+/* max |x| over a set (computed with its operand planes). */
+int nb200_set_maxabs(nb200_set *s, float *out);
+
 /* ---- conv2d_memory_fusion ---------------------------------------------------------------------- */
 /* Image set -> `image_flat` (Image.h:26-57, ImageToChunks.h:43-102, ImageChunksToBlock.h:35-50,
  * ImageBlockToMatrix.h:46-73): rows img*windows+win, cols ch*k*k+i*k+j plus a trailing 1.0 column.

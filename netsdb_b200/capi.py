@@ -28,6 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs",
 ]
 
 
@@ -87,6 +88,9 @@ def lib():
         L.nb200_conv2d_kernel_flat.argtypes = [vp, vp, i, i, i, i, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_conv2d_fused.argtypes = [vp, i, i, i, i, vp, vp, i, i, i, i, i, i, i, C.c_char_p, C.c_char_p,
                                          C.POINTER(vp)]
+        L.nb200_ff_layer1_partial.argtypes = [vp, vp, i, vp, i64]
+        L.nb200_ff_finish_from_layer1.argtypes = [vp, i64, i, vp, vp, vp, i, C.c_float, C.c_char_p, C.c_char_p, C.POINTER(vp), vp, ip]
+        L.nb200_set_maxabs.argtypes = [vp, C.POINTER(C.c_float)]
         L.nb200_transpose_mult_noalloc.argtypes = [vp, i64, vp, i64, i, i, i, vp, i64, vp]
         _lib = L
     return _lib

@@ -434,6 +434,16 @@ int nb200_set_rename(nb200_set *s, const char *db, const char *set) {
     return NB200_OK;
 }
 
+int nb200_set_maxabs(nb200_set *s, float *out) {
+    NEED_CTX();
+    if (!s || !out) return NB200_ERR_INVALID;
+    if (!s->rowp.valid && !s->rowp.f16_valid && !s->colp.valid) NB_TRY(ensure_rowp(c, s, false));
+    const Planes &p = (s->rowp.valid || s->rowp.f16_valid) ? s->rowp : s->colp;
+    NB_CUDA(cudaMemcpyAsync(out, p.maxabs, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB200_OK;
+}
+
 int nb200_set_invalidate_planes(nb200_set *s) {
     if (!s) return NB200_ERR_INVALID;
     s->rowp.valid = s->rowp.lo_valid = s->rowp.f16_valid = false;
@@ -909,6 +919,153 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     }
     *out = o;
     return NB200_OK;
+}
+
+
+// ---- K-sharded variant ----------------------------------------------------------------------------
+int nb200_ff_layer1_partial(nb200_set *w1, nb200_set *inputs, int precision, float *partial_dev, int64_t ld) {
+    NEED_CTX();
+    if (!w1 || !inputs || !partial_dev || precision == NB200_PREC_FP64 || precision < 0 || precision > 3) {
+        set_error("ff_layer1_partial: invalid arguments (tensor-core precisions only)");
+        return NB200_ERR_INVALID;
+    }
+    const int B = inputs->total_rows, Fs = inputs->total_cols, H = w1->total_rows;
+    if (w1->total_cols != Fs || w1->block_cols != inputs->block_cols || ld < H) {
+        set_error("Block dimemsions mismatch! (w1 shard vs inputs shard)");
+        return NB200_ERR_SHAPE;
+    }
+    if (B == 0 || H == 0) return NB200_OK;
+    const int nterms = precision == NB200_PREC_BF16X3 ? 3 : 1;
+    const int fmt = precision == NB200_PREC_F16 ? kFmtF16 : kFmtBF16;
+    if (fmt == kFmtF16) {
+        NB_TRY(ensure_f16_row(c, w1, 1));
+        NB_TRY(ensure_f16_row(c, inputs, 64));
+    } else {
+        NB_TRY(ensure_rowp(c, w1, nterms == 3));
+        NB_TRY(ensure_rowp(c, inputs, nterms == 3));
+    }
+    int Mpad = 0, Npad = 0, used = 1;
+    GemmEpilogue g;
+    g.mode = 0;
+    NB_TRY(launch_gemm_tc(c, inputs->rowp, w1->rowp, B, H, nterms, choose_splits(c, B, H, inputs->rowp.ldk, nterms), g, &Mpad,
+                          &Npad, &used, fmt));
+    ReduceOut r;
+    r.f32 = partial_dev; r.f32_ld = ld;
+    if (fmt == kFmtF16) { r.exp_u = inputs->rowp.f16_exp; r.exp_v = w1->rowp.f16_exp; }
+    NB_TRY(launch_splitk_reduce(c, B, H, used, Mpad, Npad, nullptr, nullptr, 0, r));
+    if (ld > H)  // extra column: this shard's per-row sum of squares of the inputs (summed by the caller's reduction)
+        NB_CUDA(cudaMemcpy2DAsync(partial_dev + H, static_cast<size_t>(ld) * sizeof(float), inputs->rowp.row_sumsq, sizeof(float),
+                                  sizeof(float), B, cudaMemcpyDeviceToDevice, c->stream));
+    if (fmt == kFmtF16) {  // a sampled scale that overflowed would have produced inf: report instead of returning garbage
+        float mx = 0.f;
+        NB_CUDA(cudaMemcpyAsync(&mx, inputs->rowp.f16_maxscaled, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        if (!(mx < 65504.f)) {
+            inputs->rowp.f16_valid = false;
+            set_error("ff_layer1_partial: an input overflowed the sampled fp16 scale; use NB200_PREC_BF16 or BF16X3");
+            return NB200_ERR_STATE;
+        }
+    }
+    return check_kernel_fault(c, "ff_layer1_partial");
+}
+
+int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb200_set *b1, nb200_set *wo, nb200_set *bo,
+                                int precision, float w1_maxabs, const char *db, const char *out_set, nb200_set **out,
+                                int32_t *labels_host, int *undecided_rows) {
+    NEED_CTX();
+    if (!y1pre_dev || !b1 || !wo || !bo || !db || !out_set || !out || rows < 0 || precision == NB200_PREC_FP64 ||
+        precision < 0 || precision > 3) {
+        set_error("ff_finish_from_layer1: invalid arguments (tensor-core precisions only)");
+        return NB200_ERR_INVALID;
+    }
+    const int H = wo->total_cols, Lb = wo->total_rows;
+    NB_TRY(bias_check(b1, H, "ReluBiasSum"));
+    NB_TRY(bias_check(bo, Lb, "TransposeBiasSum"));
+    if (ld < H) { set_error("ff_finish_from_layer1: pitch smaller than the hidden width"); return NB200_ERR_INVALID; }
+    nb200_set *zset = nullptr, *yo = nullptr, *o = nullptr;
+    NB_TRY(make_set(db, "__logits", rows, Lb, b1->block_rows, wo->block_rows, &zset));
+    NB_TRY(make_set(db, "yo", rows, Lb, b1->block_rows, wo->block_rows, &yo));
+    yo->view_of = zset;
+    yo->view_exp = true;
+    NB_TRY(make_set(db, out_set, rows, Lb, b1->block_rows, wo->block_rows, &o));
+    const size_t on = static_cast<size_t>(rows) * Lb;
+    NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+    NB_CUDA(cudaMalloc(&zset->f32, (on ? on : 1) * sizeof(float)));
+    zset->f32_ld = Lb;
+    *out = o;
+    if (undecided_rows) *undecided_rows = 0;
+    if (rows == 0 || Lb == 0) return NB200_OK;
+    const int nterms = precision == NB200_PREC_BF16X3 ? 3 : 1;
+    const int fmt = precision == NB200_PREC_F16 ? kFmtF16 : kFmtBF16;
+    NB_TRY(ensure_f32(c, b1));
+    NB_TRY(ensure_f32(c, bo));
+    NB_TRY(ensure_rowp(c, wo, nterms == 3));
+    if (fmt == kFmtF16) NB_TRY(ensure_f16_row(c, wo, 1));
+    // y1 = relu(sum of partials + b1)  [FFReluBiasSum], then operand planes for layer 2
+    FFScratch &S = g_ff;
+    const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
+    if (need > S.y1_f32_bytes) {
+        cudaFree(S.y1_f32);
+        S.y1_f32 = nullptr;
+        S.y1_f32_bytes = 0;
+        NB_CUDA(cudaMalloc(&S.y1_f32, need));
+        S.y1_f32_bytes = need;
+    }
+    NB_CUDA(cudaMemcpy2DAsync(S.y1_f32, static_cast<size_t>(H) * sizeof(float), y1pre_dev, static_cast<size_t>(ld) * sizeof(float),
+                              static_cast<size_t>(H) * sizeof(float), rows, cudaMemcpyDeviceToDevice, c->stream));
+    NB_TRY(launch_bias_relu_f32(c, S.y1_f32, rows, H, H, b1->f32));
+    if (fmt == kFmtF16) NB_TRY(launch_convert_f16(c, S.y1_f32, false, rows, H, H, &S.y1, 1, nullptr));
+    else NB_TRY(launch_convert_planes(c, S.y1_f32, false, rows, H, H, &S.y1, nterms == 3));
+    int Mpad = 0, Npad = 0, used = 1;
+    const int splits2 = choose_splits(c, rows, Lb, S.y1.ldk, nterms);
+    GemmEpilogue g2;
+    if (splits2 == 1) {
+        g2.mode = 1; g2.out = zset->f32; g2.out_ld = Lb; g2.bias_n = bo->f32;
+        NB_TRY(launch_gemm_tc(c, S.y1, wo->rowp, rows, Lb, nterms, 1, g2, &Mpad, &Npad, nullptr, fmt));
+    } else {
+        g2.mode = 0;
+        NB_TRY(launch_gemm_tc(c, S.y1, wo->rowp, rows, Lb, nterms, splits2, g2, &Mpad, &Npad, &used, fmt));
+        ReduceOut r2;
+        r2.f32 = zset->f32; r2.f32_ld = Lb;
+        if (fmt == kFmtF16) { r2.exp_u = S.y1.f16_exp; r2.exp_v = wo->rowp.f16_exp; }
+        NB_TRY(launch_splitk_reduce(c, rows, Lb, used, Mpad, Npad, nullptr, bo->f32, 0, r2));
+    }
+    if (S.cap_rows < rows) {
+        cudaFree(S.labels); cudaFree(S.gap); cudaFree(S.list);
+        NB_CUDA(cudaMalloc(&S.labels, static_cast<size_t>(rows) * sizeof(int32_t)));
+        NB_CUDA(cudaMalloc(&S.gap, static_cast<size_t>(rows) * sizeof(float)));
+        NB_CUDA(cudaMalloc(&S.list, static_cast<size_t>(rows) * sizeof(int32_t)));
+        S.cap_rows = rows;
+    }
+    NB_TRY(launch_softmax_rows(c, zset->f32, false, rows, Lb, Lb, o->f64, Lb, S.labels, S.gap, nullptr, 0, 0));
+    if (labels_host) NB_CUDA(cudaMemcpyAsync(labels_host, S.labels, static_cast<size_t>(rows) * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (undecided_rows && ld > H && w1_maxabs > 0.f) {
+        // same near-tie criterion as the fused stage, with the globally reduced ||x_r||^2 and max |w1|
+        if (!S.count) {
+            NB_CUDA(cudaMalloc(&S.count, sizeof(int)));
+            NB_CUDA(cudaMallocHost(&S.count_host, sizeof(int)));
+            NB_CUDA(cudaMalloc(&S.y1_max, sizeof(float)));
+            NB_CUDA(cudaMallocHost(&S.host_scalars, 4 * sizeof(float)));
+        }
+        float *xs = nullptr;
+        NB_CUDA(cudaMalloc(&xs, static_cast<size_t>(rows + 1) * sizeof(float)));
+        int st = NB200_OK;
+        if (cudaMemcpy2DAsync(xs, sizeof(float), y1pre_dev + H, static_cast<size_t>(ld) * sizeof(float), sizeof(float), rows,
+                              cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
+        if (st == NB200_OK && cudaMemcpyAsync(xs + rows, &w1_maxabs, sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
+        if (!wo->wo_rownorm_max && st == NB200_OK && cudaMalloc(&wo->wo_rownorm_max, sizeof(float)) != cudaSuccess) st = NB200_ERR_CUDA;
+        if (st == NB200_OK) st = launch_max_rownorm(c, wo->rowp.row_sumsq, Lb, wo->wo_rownorm_max);
+        if (st == NB200_OK && cudaMemsetAsync(S.count, 0, sizeof(int), c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
+        if (st == NB200_OK)
+            st = launch_flag_rows(c, rows, S.gap, xs, S.y1.row_sumsq, xs + rows, wo->rowp.maxabs, wo->wo_rownorm_max,
+                                  prec_unit(precision), 4.0f, S.list, S.count, rows, nullptr);
+        if (st == NB200_OK && cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
+        cudaStreamSynchronize(c->stream);
+        cudaFree(xs);
+        if (st != NB200_OK) return st;
+        *undecided_rows = *S.count_host;
+    }
+    return check_kernel_fault(c, "ff_finish_from_layer1");
 }
 
 // ---- conv2d_memory_fusion -------------------------------------------------------------------------

@@ -126,6 +126,7 @@ int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_
                                Planes *p);
 int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t cols, int64_t ld, float *dst, int64_t dld);
 int launch_f64_to_f32(Context *c, const double *src, int64_t n, float *dst);
+int launch_bias_relu_f32(Context *c, float *p, int64_t rows, int64_t cols, int64_t ld, const float *bias_n);
 int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
                       int64_t row_offset, int64_t total_cols);
 

@@ -522,6 +522,25 @@ int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t col
     return NB200_OK;
 }
 
+// y = max(0, x + bias[col]) in place on an fp32 matrix (FFReluBiasSum.h:68-71 on the reduced layer-1 partials)
+__global__ void k_bias_relu_f32(float *__restrict__ p, long long rows, long long cols, long long ld,
+                                const float *__restrict__ bias_n) {
+    const long long n = rows * cols;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / cols, cc = i % cols;
+        p[r * ld + cc] = fmaxf(p[r * ld + cc] + bias_n[cc], 0.f);
+    }
+}
+int launch_bias_relu_f32(Context *c, float *p, int64_t rows, int64_t cols, int64_t ld, const float *bias_n) {
+    const int64_t n = rows * cols;
+    if (n == 0) return NB200_OK;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+    k_bias_relu_f32<<<blocks, 256, 0, c->stream>>>(p, rows, cols, ld, bias_n);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
 __global__ void k_f64_to_f32(const double *__restrict__ s, long long n, float *__restrict__ d) {
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<long long>(gridDim.x) * blockDim.x)

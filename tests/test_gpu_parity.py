@@ -312,3 +312,19 @@ def test_unmodified_reference_driver_runs(tmp_path):
     r = _run([exe, "50", "50", "120", "200", "100", "2", "Y"], {"NB200_DROPOUT_AS_ZERO": "1"}, timeout=120)
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
     assert "count=3" in r.stdout  # 120 rows / 50 = 3 row blocks x 1 column block of the output set
+
+
+def test_k_sharded_variant_two_gpus():
+    """K-sharded layer 1 + NCCL reduce-scatter (the fallback for weights larger than one GPU's HBM) against the oracle;
+    needs two visible GPUs, so it is skipped on the single-GPU test box (run under `gpurun --gpus 2`)."""
+    import sys
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+              "--master-port", "29547", os.path.join(root, "tools", "ksharded_check.py")], {}, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("OK  k-sharded") == 3

@@ -90,3 +90,14 @@ def test_row_sharded_pipeline_equals_unsharded_world2_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert results == {0: True, 1: True}
+
+
+def test_col_shard_is_block_aligned_and_complete():
+    from netsdb_b200.ksharded import col_shard
+
+    for total, blk in ((597540, 1000), (9000, 500), (1024, 100), (7, 3)):
+        for world in (1, 2, 4, 8):
+            cuts = [col_shard(total, blk, world, r) for r in range(world)]
+            assert cuts[0][0] == 0 and sum(n for _, n in cuts) == total
+            for (a0, an), (b0, _) in zip(cuts, cuts[1:]):
+                assert a0 + an == b0 and b0 % blk == 0 or b0 >= total
