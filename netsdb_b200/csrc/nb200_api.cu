@@ -1120,18 +1120,66 @@ int nb200_conv2d_kernel_flat(const double *kernels_host, const double *bias_host
 int nb200_conv2d_fused(const double *images_host, int n, int ch, int h, int w, const double *kernels_host,
                        const double *bias_host, int kout, int k, int padding, int relu, int precision, int block_rows,
                        int block_cols, const char *db, const char *out_set, nb200_set **out) {
-    // First cut: im2col on the device (never leaves HBM, never blocked) + the block GEMM.  The
-    // implicit-GEMM producer that skips the materialised image_flat is the next step.
     NEED_CTX();
-    (void)c;
-    nb200_set *img = nullptr, *ker = nullptr, *res = nullptr;
-    NB_TRY(nb200_conv2d_image_flat(images_host, n, ch, h, w, k, 1, padding, block_rows, block_cols, db, "__image_flat", &img));
-    NB_TRY(nb200_conv2d_kernel_flat(kernels_host, bias_host, kout, ch, k, block_rows, block_cols, db, "__kernel_flat", &ker));
-    int st = gemm_blocks_impl(NB200_OP_NT, img, ker, NB200_EPI_NONE, nullptr, precision, db, out_set, &res, relu ? 1 : 0);
-    nb200_set_destroy(img);
-    nb200_set_destroy(ker);
+    if (!images_host || !kernels_host || !bias_host || n <= 0 || ch <= 0 || h <= 0 || w <= 0 || kout <= 0 || k <= 0 ||
+        padding < 0 || !db || !out_set || !out || precision < 0 || precision > 3) {
+        set_error("conv2d_fused: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    const int hout = h + 2 * padding - k + 1, wout = w + 2 * padding - k + 1;
+    if (hout <= 0 || wout <= 0) { set_error("conv2d_fused: kernel larger than image"); return NB200_ERR_SHAPE; }
+    if (precision == NB200_PREC_FP64 || kout > 256) {
+        // exact path (and very wide filters): materialised im2col on the device + the block GEMM
+        nb200_set *img = nullptr, *ker = nullptr, *res = nullptr;
+        NB_TRY(nb200_conv2d_image_flat(images_host, n, ch, h, w, k, 1, padding, block_rows, block_cols, db, "__image_flat", &img));
+        NB_TRY(nb200_conv2d_kernel_flat(kernels_host, bias_host, kout, ch, k, block_rows, block_cols, db, "__kernel_flat", &ker));
+        int st = gemm_blocks_impl(NB200_OP_NT, img, ker, NB200_EPI_NONE, nullptr, precision, db, out_set, &res, relu ? 1 : 0);
+        nb200_set_destroy(img);
+        nb200_set_destroy(ker);
+        if (st != NB200_OK) return st;
+        *out = res;
+        return NB200_OK;
+    }
+    // implicit GEMM: image_flat is never built (K6).  bf16 (fp16 requests use bf16 planes here: the operands are
+    // tiny and the kernel is HBM-bound on the result) or bf16x3.
+    const int nterms = precision == NB200_PREC_BF16X3 ? 3 : 1;
+    const int cp = static_cast<int>(round_up(ch, 64));
+    const size_t img_elems = static_cast<size_t>(n) * ch * h * w, nhwc_elems = static_cast<size_t>(n) * h * w * cp;
+    double *dimg = nullptr, *dker = nullptr;
+    float *dbias = nullptr;
+    __nv_bfloat16 *ihi = nullptr, *ilo = nullptr;
+    Planes kp;
+    nb200_set *o = nullptr;
+    int st = make_set(db, out_set, n * hout * wout, kout, block_rows, block_cols, &o);
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(c->stream);
+        cudaFree(dimg); cudaFree(dker); cudaFree(dbias); cudaFree(ihi); cudaFree(ilo);
+        free_planes(&kp);
+    };
+#define CONV_TRY(x) do { if (st == NB200_OK && (x) != cudaSuccess) { set_error("conv2d_fused: %s failed", #x); st = NB200_ERR_CUDA; } } while (0)
+    CONV_TRY(cudaMalloc(&dimg, img_elems * sizeof(double)));
+    CONV_TRY(cudaMalloc(&dker, static_cast<size_t>(kout) * ch * k * k * sizeof(double)));
+    CONV_TRY(cudaMalloc(&dbias, static_cast<size_t>(kout) * sizeof(float)));
+    CONV_TRY(cudaMalloc(&ihi, nhwc_elems * sizeof(__nv_bfloat16)));
+    if (nterms == 3) CONV_TRY(cudaMalloc(&ilo, nhwc_elems * sizeof(__nv_bfloat16)));
+    const size_t on = static_cast<size_t>(n) * hout * wout * kout;
+    if (st == NB200_OK) {
+        CONV_TRY(cudaMalloc(&o->f32, (on ? on : 1) * sizeof(float)));
+        o->f32_ld = kout;
+    }
+    std::vector<float> bias32(kout);
+    for (int i = 0; i < kout; i++) bias32[i] = static_cast<float>(bias_host[i]);
+    CONV_TRY(cudaMemcpyAsync(dimg, images_host, img_elems * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CONV_TRY(cudaMemcpyAsync(dker, kernels_host, static_cast<size_t>(kout) * ch * k * k * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CONV_TRY(cudaMemcpyAsync(dbias, bias32.data(), static_cast<size_t>(kout) * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+#undef CONV_TRY
+    if (st == NB200_OK) st = launch_nchw_to_nhwc_planes(c, dimg, n, ch, h, w, cp, ihi, ilo);
+    if (st == NB200_OK) st = launch_kernel_to_planes(c, dker, kout, ch, k, cp, &kp, nterms == 3);
+    if (st == NB200_OK) st = launch_conv_implicit(c, ihi, ilo, n, h, w, cp, kp, kout, k, padding, nterms, dbias, relu, o->f32);
+    if (st == NB200_OK) st = check_kernel_fault(c, "conv2d_fused");
+    cleanup();
     if (st != NB200_OK) return st;
-    *out = res;
+    *out = o;
     return NB200_OK;
 }
 

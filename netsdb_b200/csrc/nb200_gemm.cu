@@ -566,6 +566,201 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// conv2d_memory_fusion as an implicit GEMM (K6).  The reference materialises the im2col matrix
+// `image_flat` through ImageToChunks -> ImageChunksToBlock -> ImageBlockToMatrix
+// (conv2d_memory_fusion/headers/ImageToChunks.h:43-102, ImageBlockToMatrix.h:46-73) and multiplies it
+// with `kernel_flat` by FFTransposeMult + FFAggMatrix (tests/source/PipelinedConv2dMemFuseTest.cc:249-262).
+// Here image_flat never exists: the image is kept NHWC in bf16 (channels padded to 64), a CTA owns one
+// run of up to 128 output positions of one output row, and for every filter tap (i, j) a 4-D TMA box
+// {64 channels, 128 pixels, 1, 1} at (c0, wo0 + j - pad, ho + i - pad, n) lands in shared memory exactly
+// as a K-major 128-byte-swizzled operand tile (out-of-image pixels are zero filled by TMA = padding).
+// K is ordered (tap, channel); the bias column of kernel_flat becomes the epilogue bias.
+// result[(n, ho, wo), cout] = conv + bias (+ ReLU).  Stride 1.
+// ---------------------------------------------------------------------------------------------
+struct ConvArgs {
+    int n, h, w, hout, wout, k, pad, cblocks;  // cblocks = padded channels / 64
+    int kout;
+    int wsegs;                                  // ceil(wout / 128)
+    int nterms;
+    float *out;                                 // [(n*hout + ho)*wout + wo][kout]
+    const float *bias;
+    int relu;
+    int *err_flag;
+    unsigned int idesc;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+k_conv_implicit(const __grid_constant__ CUtensorMap map_img_hi, const __grid_constant__ CUtensorMap map_img_lo,
+                const __grid_constant__ CUtensorMap map_ker_hi, const __grid_constant__ CUtensorMap map_ker_lo,
+                const ConvArgs g) {
+    using L = SmemLayout<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + L::kBarOffset);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tmem_full_bar = empty_bar + STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_full_bar + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // tile -> (image, output row, 128-wide segment of that row)
+    const int seg = blockIdx.x % g.wsegs;
+    const int ho = (blockIdx.x / g.wsegs) % g.hout;
+    const int img = blockIdx.x / (g.wsegs * g.hout);
+    const int wo0 = seg * kBlockM;
+    const int taps = g.k * g.k;
+    const int n_iter = taps * g.cblocks * g.nterms;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_img_hi);
+        tma_prefetch_desc(&map_ker_hi);
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, BN < 32 ? 32 : BN);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int it = 0; it < n_iter; it++) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                if (!mbar_wait(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 301); break; }
+                const int t = it % g.nterms;
+                const int kb = it / g.nterms;           // = tap * cblocks + cb
+                const int tap = kb / g.cblocks, cb = kb % g.cblocks;
+                const int fi = tap / g.k, fj = tap % g.k;
+                const CUtensorMap *mi = (t == 2) ? &map_img_lo : &map_img_hi;
+                const CUtensorMap *mk = (t == 1) ? &map_ker_lo : &map_ker_hi;
+                uint8_t *sa = smem + s * L::kStageBytes;
+                uint8_t *sb = sa + kABytes;
+                mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+                tma_load_4d(mi, &full_bar[s], sa, cb * kBlockK, wo0 + fj - g.pad, ho + fi - g.pad, img, kEvictNormal);
+                tma_load_2d(mk, &full_bar[s], sb, kb * kBlockK, 0, kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            for (int it = 0; it < n_iter; it++) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                if (!mbar_wait(&full_bar[s], ph)) { atomicExch(g.err_flag, 302); break; }
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + s * L::kStageBytes);
+                const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + kABytes);
+#pragma unroll
+                for (int k = 0; k < kBlockK / kUmmaK; k++)
+                    umma_f16(tmem_base, da + 2 * k, db + 2 * k, g.idesc, (it > 0 || k > 0) ? 1u : 0u);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(tmem_full_bar);
+        }
+    } else {
+        const int q = warp & 3;
+        const int wo = wo0 + q * 32 + lane;
+        bool ok = mbar_wait(tmem_full_bar, 0);
+        if (!ok && lane == 0) atomicExch(g.err_flag, 303);
+        ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+        tc_fence_after();
+        if (ok) {
+            const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+            const long long row = (static_cast<long long>(img) * g.hout + ho) * g.wout + wo;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c++) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(lane_addr + c * 32, r);
+                tmem_ld_wait();
+                if (wo < g.wout) {
+                    float *dst = g.out + row * g.kout + c * 32;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const int col = c * 32 + j;
+                        if (col < g.kout) {
+                            float v = __uint_as_float(r[j]) + (g.bias ? g.bias[col] : 0.f);
+                            if (g.relu) v = fmaxf(v, 0.f);
+                            dst[j] = v;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+    }
+}
+
+// NHWC bf16 image: dims {Cp, W, H, N}; box {64, 128, 1, 1}; out-of-range coordinates (the padding) read as zero
+static int make_image_map(CUtensorMap *m, const __nv_bfloat16 *base, int n, int h, int w, int cp) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return NB200_ERR_CUDA; }
+    cuuint64_t dims[4] = {(cuuint64_t)cp, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
+    cuuint64_t strides[3] = {(cuuint64_t)cp * 2, (cuuint64_t)w * cp * 2, (cuuint64_t)h * w * cp * 2};
+    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)kBlockM, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16 *>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (image) failed with CUresult %d", (int)r); return NB200_ERR_CUDA; }
+    return NB200_OK;
+}
+
+template <int BN, int STAGES>
+static int launch_conv_impl(Context *c, const CUtensorMap &ih, const CUtensorMap &il, const CUtensorMap &kh,
+                            const CUtensorMap &kl, const ConvArgs &g, int tiles) {
+    using L = SmemLayout<BN, STAGES>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NB_CUDA(cudaFuncSetAttribute(k_conv_implicit<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    k_conv_implicit<BN, STAGES><<<tiles, kThreads, L::kTotal, c->stream>>>(ih, il, kh, kl, g);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+// img_hi/lo: NHWC bf16 [n][h][w][cp]; ker: planes [kout][k*k*cp] with K ordered (tap, channel)
+int launch_conv_implicit(Context *c, const __nv_bfloat16 *img_hi, const __nv_bfloat16 *img_lo, int n, int h, int w, int cp,
+                         const Planes &ker, int kout, int k, int pad, int nterms, const float *bias, int relu, float *out) {
+    const int hout = h + 2 * pad - k + 1, wout = w + 2 * pad - k + 1;
+    if (hout <= 0 || wout <= 0 || kout > 256 || cp % 64 != 0) {
+        set_error("conv2d implicit GEMM: unsupported shape (kout %d > 256 or kernel larger than image)", kout);
+        return NB200_ERR_SHAPE;
+    }
+    ConvArgs g{};
+    g.n = n; g.h = h; g.w = w; g.hout = hout; g.wout = wout; g.k = k; g.pad = pad; g.cblocks = cp / 64; g.kout = kout;
+    g.wsegs = static_cast<int>(ceil_div(wout, kBlockM));
+    g.nterms = nterms; g.out = out; g.bias = bias; g.relu = relu; g.err_flag = c->err_flag;
+    const int BN = kout <= 64 ? 64 : (kout <= 128 ? 128 : 256);
+    g.idesc = umma_idesc_bf16(kBlockM, BN);
+    CUtensorMap ih, il, kh, kl;
+    NB_TRY(make_image_map(&ih, img_hi, n, h, w, cp));
+    NB_TRY(make_plane_map(&kh, ker.hi, ker.rows, ker.ldk, BN));
+    if (nterms == 3) {
+        NB_TRY(make_image_map(&il, img_lo, n, h, w, cp));
+        NB_TRY(make_plane_map(&kl, ker.lo, ker.rows, ker.ldk, BN));
+    } else { il = ih; kl = kh; }
+    const int tiles = n * hout * g.wsegs;
+    if (BN == 64) return launch_conv_impl<64, 6>(c, ih, il, kh, kl, g, tiles);
+    if (BN == 128) return launch_conv_impl<128, 6>(c, ih, il, kh, kl, g, tiles);
+    return launch_conv_impl<256, 4>(c, ih, il, kh, kl, g, tiles);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Allocation-free FFTransposeMult + FFAggMatrix product (nb200_transpose_mult_noalloc).
 //

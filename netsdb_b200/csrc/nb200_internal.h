@@ -93,6 +93,13 @@ enum { kFmtBF16 = 0, kFmtF16 = 1 };
 int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, int nterms, int splits,
                    const GemmEpilogue &epi, int *Mpad, int *Npad, int *splits_used, int fmt = kFmtBF16);
 int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms);
+// conv2d as implicit GEMM: NHWC bf16 image (channels padded to cp, multiple of 64), kernel planes with K = (tap, channel)
+int launch_conv_implicit(Context *c, const __nv_bfloat16 *img_hi, const __nv_bfloat16 *img_lo, int n, int h, int w, int cp,
+                         const Planes &ker, int kout, int k, int pad, int nterms, const float *bias, int relu, float *out);
+// fp64 NCHW images -> bf16 hi/lo NHWC with channels zero padded to cp; fp64 kernels [kout][c][k][k] -> planes (tap, channel)
+int launch_nchw_to_nhwc_planes(Context *c, const double *img, int n, int ch, int h, int w, int cp, __nv_bfloat16 *hi,
+                               __nv_bfloat16 *lo);
+int launch_kernel_to_planes(Context *c, const double *ker, int kout, int ch, int k, int cp, Planes *p, bool want_lo);
 
 // ---- other kernels (nb200_kernels.cu) -----------------------------------------------------------
 // source (double or float, row-major rows x cols, ld) -> planes of the same orientation

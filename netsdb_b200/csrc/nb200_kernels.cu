@@ -500,6 +500,59 @@ int launch_splitk_reduce(Context *c, int M, int N, int splits, int Mpad, int Npa
     return NB200_OK;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// conv2d operand preparation for the implicit GEMM
+// ---------------------------------------------------------------------------------------------
+// fp64 NCHW -> bf16 hi/lo NHWC, channels zero padded to cp.  One block per (image, row): reads are coalesced along w
+// per channel, writes along (w, c) through shared memory.
+__global__ void __launch_bounds__(256)
+k_nchw_to_nhwc(const double *__restrict__ img, int ch, int h, int w, int cp, __nv_bfloat16 *__restrict__ hi,
+               __nv_bfloat16 *__restrict__ lo) {
+    const int y = blockIdx.x % h, n = blockIdx.x / h;
+    const long long total = static_cast<long long>(w) * cp;
+    for (long long e = threadIdx.x; e < total; e += 256) {
+        const int x = static_cast<int>(e / cp), c = static_cast<int>(e % cp);
+        const double v = c < ch ? img[((static_cast<long long>(n) * ch + c) * h + y) * w + x] : 0.0;
+        __nv_bfloat16 a, b;
+        split_bf16<double>(v, a, b);
+        const long long o = ((static_cast<long long>(n) * h + y) * w + x) * cp + c;
+        hi[o] = a;
+        if (lo) lo[o] = b;
+    }
+}
+int launch_nchw_to_nhwc_planes(Context *c, const double *img, int n, int ch, int h, int w, int cp, __nv_bfloat16 *hi,
+                               __nv_bfloat16 *lo) {
+    k_nchw_to_nhwc<<<n * h, 256, 0, c->stream>>>(img, ch, h, w, cp, hi, lo);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+// kernels [kout][ch][k][k] fp64 -> planes [kout][k*k*cp], K index = (i*k + j)*cp + c  (tap major, channel minor)
+__global__ void k_kernel_to_planes(const double *__restrict__ ker, int kout, int ch, int k, int cp,
+                                   __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo, long long ldk) {
+    const long long total = static_cast<long long>(kout) * ldk;
+    for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
+         e += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int o = static_cast<int>(e / ldk);
+        const long long kk = e % ldk;
+        const int tap = static_cast<int>(kk / cp), c = static_cast<int>(kk % cp);
+        double v = 0.0;
+        if (tap < k * k && c < ch) v = ker[((static_cast<long long>(o) * ch + c) * k + tap / k) * k + tap % k];
+        __nv_bfloat16 a, b;
+        split_bf16<double>(v, a, b);
+        hi[e] = a;
+        if (lo) lo[e] = b;
+    }
+}
+int launch_kernel_to_planes(Context *c, const double *ker, int kout, int ch, int k, int cp, Planes *p, bool want_lo) {
+    NB_TRY(alloc_planes(p, kout, static_cast<int64_t>(k) * k * cp, want_lo));
+    k_kernel_to_planes<<<148, 256, 0, c->stream>>>(ker, kout, ch, k, cp, p->hi, want_lo ? p->lo : nullptr, p->ldk);
+    NB_LAUNCH_CHECK(c);
+    p->valid = true;
+    p->lo_valid = want_lo;
+    return NB200_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // small utilities
 // ---------------------------------------------------------------------------------------------

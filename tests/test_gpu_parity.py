@@ -328,3 +328,24 @@ def test_k_sharded_variant_two_gpus():
               "--master-port", "29547", os.path.join(root, "tools", "ksharded_check.py")], {}, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("OK  k-sharded") == 3
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 20, 19, 5, 3, 0), (3, 8, 17, 150, 40, 3, 1), (2, 64, 30, 30, 64, 3, 0),
+                                   (1, 70, 12, 140, 130, 5, 2), (2, 3, 16, 16, 7, 7, 3)])
+def test_conv2d_implicit_gemm_vs_blocked_oracle(nb, oracle, shape):
+    """nb200_conv2d_fused (implicit GEMM, image_flat never built) against the reference pipeline restated by the
+    oracle: image_flat x kernel_flat by FFTransposeMult + FFAggMatrix, then ReLU (config C4's "+ ReLU")."""
+    n, c, h, w, kout, k, pad = shape
+    imgs = oracle.synth_dense(n * c, h * w, 41).reshape(n, c, h, w)
+    kern = oracle.synth_dense(kout * c, k * k, 42).reshape(kout, c, k, k)
+    bias = oracle.synth_dense(kout, 1, 43).reshape(kout)
+    ref = oracle.transpose_mult_agg(oracle.image_flat(imgs, k, 1, pad, 64, 64), oracle.kernel_flat(kern, bias, 64, 64), 4)
+    refd = ref.dense()
+    hout, wout = h + 2 * pad - k + 1, w + 2 * pad - k + 1
+    assert ref.totals() == (n * hout * wout, kout)
+    for prec in ("fp64", "bf16x3", "bf16"):
+        for relu in (False, True):
+            R = nb.conv2d_fused(imgs, kern, bias, pad, relu, nb.PRECISIONS[prec], 64, 64)
+            assert R.info()[:2] == (n * hout * wout, kout)
+            want = np.maximum(refd, 0) if relu else refd
+            assert np.abs(R.download_dense() - want).max() <= TOL[prec] * np.abs(refd).max(), (prec, relu)
