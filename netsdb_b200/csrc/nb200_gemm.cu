@@ -176,13 +176,28 @@ k_block_gemm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant
                         *reinterpret_cast<uint4 *>(dst + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
                 } else if (row < g.M) {
                     float *dst = g.out + row * g.out_ld + col0;
+                    if (col0 + 32 <= g.N && (g.out_ld & 3) == 0 && (reinterpret_cast<uintptr_t>(g.out) & 15) == 0) {
+                        // whole chunk in range: 8 x 16-byte stores, the thread's 128 bytes fill one line of its row
 #pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        if (col0 + j < g.N) {
-                            float v = __uint_as_float(r[j]) * oscale + bm;
-                            if (g.bias_n != nullptr) v += g.bias_n[col0 + j];
-                            if (g.relu) v = fmaxf(v, 0.f);
-                            dst[j] = v;
+                        for (int j = 0; j < 32; j += 4) {
+                            float v[4];
+#pragma unroll
+                            for (int e = 0; e < 4; e++) {
+                                v[e] = __uint_as_float(r[j + e]) * oscale + bm;
+                                if (g.bias_n != nullptr) v[e] += __ldg(g.bias_n + col0 + j + e);
+                                if (g.relu) v[e] = fmaxf(v[e], 0.f);
+                            }
+                            *reinterpret_cast<float4 *>(dst + j) = make_float4(v[0], v[1], v[2], v[3]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j++) {
+                            if (col0 + j < g.N) {
+                                float v = __uint_as_float(r[j]) * oscale + bm;
+                                if (g.bias_n != nullptr) v += g.bias_n[col0 + j];
+                                if (g.relu) v = fmaxf(v, 0.f);
+                                dst[j] = v;
+                            }
                         }
                     }
                 }
@@ -342,13 +357,27 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
                         *reinterpret_cast<uint4 *>(dst + jj) = make_uint4(r[jj], r[jj + 1], r[jj + 2], r[jj + 3]);
                 } else if (row < g.M) {
                     float *dst = g.out + row * g.out_ld + col0;
+                    if (col0 + 32 <= g.N && (g.out_ld & 3) == 0 && (reinterpret_cast<uintptr_t>(g.out) & 15) == 0) {
 #pragma unroll
-                    for (int jj = 0; jj < 32; jj++) {
-                        if (col0 + jj < g.N) {
-                            float v = __uint_as_float(r[jj]) * oscale + bm;
-                            if (g.bias_n != nullptr) v += g.bias_n[col0 + jj];
-                            if (g.relu) v = fmaxf(v, 0.f);
-                            dst[jj] = v;
+                        for (int jj = 0; jj < 32; jj += 4) {
+                            float v[4];
+#pragma unroll
+                            for (int e = 0; e < 4; e++) {
+                                v[e] = __uint_as_float(r[jj + e]) * oscale + bm;
+                                if (g.bias_n != nullptr) v[e] += __ldg(g.bias_n + col0 + jj + e);
+                                if (g.relu) v[e] = fmaxf(v[e], 0.f);
+                            }
+                            *reinterpret_cast<float4 *>(dst + jj) = make_float4(v[0], v[1], v[2], v[3]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int jj = 0; jj < 32; jj++) {
+                            if (col0 + jj < g.N) {
+                                float v = __uint_as_float(r[jj]) * oscale + bm;
+                                if (g.bias_n != nullptr) v += g.bias_n[col0 + jj];
+                                if (g.relu) v = fmaxf(v, 0.f);
+                                dst[jj] = v;
+                            }
                         }
                     }
                 }
@@ -463,7 +492,12 @@ static int pick_kernel(int M, int N, int64_t ldk) {
     if (forced >= 0) return forced;
     if (M <= 128 || N <= 128) return 0;          // a pair tile would be mostly padding
     if (ldk >= 4096) return N > 256 ? 2 : 1;     // long K: the L2 -> SM fill rate decides
-    return 0;
+    static int shortk = -2;
+    if (shortk == -2) {
+        const char *e = getenv("NB200_GEMM_KERNEL_SHORTK");
+        shortk = e ? atoi(e) : 0;
+    }
+    return (M >= 1024 && N >= 1024) ? shortk : 0;
 }
 
 template <int BN, int STAGES>

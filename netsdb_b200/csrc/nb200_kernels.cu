@@ -287,14 +287,6 @@ int launch_convert_f16_cols(Context *c, cudaStream_t stream, const void *src, bo
     static const int side_ctas = getenv("NB200_CVT_CTAS") ? atoi(getenv("NB200_CVT_CTAS")) : 4;
     const int64_t cap = static_cast<int64_t>(sms) * (stream == c->stream ? 8 : side_ctas);
     const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
-    static bool carveout_set = false;
-    if (!carveout_set) {
-        // CTAs of kernels that want different shared-memory carve-outs do not share an SM: ask for the GEMM's
-        // (maximum shared memory) so that this kernel can run beside it
-        NB_CUDA(cudaFuncSetAttribute(k_convert_f16<double>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        NB_CUDA(cudaFuncSetAttribute(k_convert_f16<float>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        carveout_set = true;
-    }
     if (src_is_f64) k_convert_f16<double><<<grid, kCvtThreads, 0, stream>>>((const double *)src, ld, rows, cols, p->f16, p->ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled, col_begin, col_end);
     else k_convert_f16<float><<<grid, kCvtThreads, 0, stream>>>((const float *)src, ld, rows, cols, p->f16, p->ldk, p->f16_exp, p->row_sumsq, p->f16_maxscaled, col_begin, col_end);
     NB_LAUNCH_CHECK(c);
