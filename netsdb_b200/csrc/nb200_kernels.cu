@@ -968,11 +968,110 @@ k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restri
     double *pr = probs + row * probs_ld;
     for (int j = threadIdx.x; j < cols; j += 256) pr[j] = exp(static_cast<double>(zr[j] - mx)) * inv;
 }
+
+// Register-resident variant for fp32 logits with at most 16,384 columns (pitch a multiple of 4): the row is read
+// from HBM exactly once as float4, kept in registers for the max / argmax / top-2 scan, the exp-sum and the
+// normalisation, and the probabilities leave as 16-byte stores.  exp is evaluated in fp32 (the logits are fp32
+// tensor-core results; their own error dominates) and widened to the fp64 output type of the reference.
+__global__ void __launch_bounds__(256)
+k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *__restrict__ probs, long long probs_ld,
+                   int32_t *__restrict__ labels, float *__restrict__ gap, const int32_t *__restrict__ row_list,
+                   int in_compact) {
+    constexpr int NV = 16;  // float4 per thread
+    __shared__ float s_m1[8], s_m2[8];
+    __shared__ double s_sum[8];
+    __shared__ int s_i1[8];
+    __shared__ float b_m1;
+    __shared__ double b_sum;
+    const long long row = row_list ? row_list[blockIdx.x] : blockIdx.x;
+    const float4 *zr = reinterpret_cast<const float4 *>(z + (in_compact ? static_cast<long long>(blockIdx.x) : row) * ld);
+    const int nvec = cols >> 2;  // cols % 4 == 0 guaranteed by the launcher
+    float4 v[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        const int q = threadIdx.x + i * 256;
+        v[i] = q < nvec ? __ldg(zr + q) : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+    }
+    float m1 = -CUDART_INF_F, m2 = -CUDART_INF_F;
+    int i1 = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        const int base = (threadIdx.x + i * 256) * 4;
+        const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (e[j] > m1) { m2 = m1; m1 = e[j]; i1 = base + j; }
+            else if (e[j] > m2) m2 = e[j];
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const float om1 = __shfl_xor_sync(0xffffffffu, m1, o), om2 = __shfl_xor_sync(0xffffffffu, m2, o);
+        const int oi1 = __shfl_xor_sync(0xffffffffu, i1, o);
+        if (om1 > m1 || (om1 == m1 && oi1 < i1)) { m2 = fmaxf(m1, om2); m1 = om1; i1 = oi1; }
+        else m2 = fmaxf(m2, om1);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { s_m1[w] = m1; s_m2[w] = m2; s_i1[w] = i1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a1 = s_m1[0], a2 = s_m2[0];
+        int ai = s_i1[0];
+        for (int k = 1; k < 8; k++) {
+            const float om1 = s_m1[k], om2 = s_m2[k];
+            const int oi1 = s_i1[k];
+            if (om1 > a1 || (om1 == a1 && oi1 < ai)) { a2 = fmaxf(a1, om2); a1 = om1; ai = oi1; }
+            else a2 = fmaxf(a2, om1);
+        }
+        b_m1 = a1;
+        if (labels) labels[row] = ai;
+        if (gap) gap[row] = a1 - a2;
+    }
+    __syncthreads();
+    if (!probs) return;
+    const float mx = b_m1;
+    double sum = 0.0;  // summed in fp64 so that the probabilities of a row add up to 1 to fp64 rounding
+#pragma unroll
+    for (int i = 0; i < NV; i++) {  // exp(-inf) = 0 for the out-of-range slots
+        v[i].x = __expf(v[i].x - mx); v[i].y = __expf(v[i].y - mx); v[i].z = __expf(v[i].z - mx); v[i].w = __expf(v[i].w - mx);
+        sum += (static_cast<double>(v[i].x) + static_cast<double>(v[i].y)) + (static_cast<double>(v[i].z) + static_cast<double>(v[i].w));
+    }
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (l == 0) s_sum[w] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 8; k++) t += s_sum[k];
+        b_sum = t;
+    }
+    __syncthreads();
+    const double inv = 1.0 / b_sum;
+    double *pr = probs + row * probs_ld;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(pr) & 15) == 0);
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        const int q = threadIdx.x + i * 256;
+        if (q < nvec) {
+            const double a = v[i].x * inv, b = v[i].y * inv, cc = v[i].z * inv, d = v[i].w * inv;
+            if (aligned) {
+                *reinterpret_cast<double2 *>(pr + q * 4) = make_double2(a, b);
+                *reinterpret_cast<double2 *>(pr + q * 4 + 2) = make_double2(cc, d);
+            } else {
+                pr[q * 4] = a; pr[q * 4 + 1] = b; pr[q * 4 + 2] = cc; pr[q * 4 + 3] = d;
+            }
+        }
+    }
+}
+
 int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t rows, int64_t cols, int64_t ld,
                         double *probs, int64_t probs_ld, int32_t *labels, float *gap, const int32_t *row_list,
                         int nrows_list, int in_compact) {
     const int64_t n = row_list ? nrows_list : rows;
     if (n == 0 || cols == 0) return NB200_OK;
+    if (!is_f64 && cols <= 16384 && (cols & 3) == 0 && (ld & 3) == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0) {
+        k_softmax_rows_reg<<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+        NB_LAUNCH_CHECK(c);
+        return NB200_OK;
+    }
     if (is_f64) k_softmax_rows<double><<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const double *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
     else k_softmax_rows<float><<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
     NB_LAUNCH_CHECK(c);
