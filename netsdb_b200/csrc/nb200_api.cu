@@ -54,6 +54,16 @@ static int ensure_stage(Context *c, size_t bytes) {
     return NB200_OK;
 }
 
+int wait_uploads(Context *c) {
+    if (!c->uploads_pending) return NB200_OK;
+    for (int i = 0; i < 2; i++) {
+        NB_CUDA(cudaEventRecord(c->up_ev[i], c->copy[i]));
+        NB_CUDA(cudaStreamWaitEvent(c->stream, c->up_ev[i], 0));
+    }
+    c->uploads_pending = false;
+    return NB200_OK;
+}
+
 int check_kernel_fault(Context *c, const char *what) {
     NB_CUDA(cudaMemcpyAsync(c->err_flag_host, c->err_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
@@ -81,11 +91,19 @@ static void free_set_storage(nb200_set *s) {
     free_planes(&s->colp);
 }
 
-#define NEED_CTX()                                              \
+#define NEED_CTX_RAW()                                          \
     Context *c = ::nb200::ctx();                                \
     if (!c) {                                                   \
         ::nb200::set_error("nb200_init has not been called");   \
         return NB200_ERR_STATE;                                 \
+    }
+// every entry point that reads or writes set data on the compute stream first orders itself after queued uploads
+#define NEED_CTX()                                              \
+    NEED_CTX_RAW()                                              \
+    {                                                           \
+        int _w = ::nb200::wait_uploads(c);                      \
+        if (_w != NB200_OK) return _w;                          \
+        c->main_dirty = true;                                   \
     }
 
 // ---- derived representations ------------------------------------------------------------------
@@ -222,6 +240,9 @@ int nb200_init(int device) {
     }
     for (auto &e : c->chunk_ev) NB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : c->join_ev) NB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &st : c->copy) NB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto &e : c->up_ev) NB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    NB_CUDA(cudaEventCreateWithFlags(&c->main_ev, cudaEventDisableTiming));
     g_ctx = c;
     return NB200_OK;
 }
@@ -243,6 +264,10 @@ int nb200_shutdown(void) {
     for (auto &e : g_ctx->chunk_ev) cudaEventDestroy(e);
     for (auto &e : g_ctx->join_ev) cudaEventDestroy(e);
     for (auto &st : g_ctx->aux) cudaStreamDestroy(st);
+    for (auto &st : g_ctx->copy) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    for (auto &e : g_ctx->up_ev) cudaEventDestroy(e);
+    cudaEventDestroy(g_ctx->main_ev);
+    cudaFree(g_ctx->up_stage[0]); cudaFree(g_ctx->up_stage[1]);
     cudaStreamDestroy(g_ctx->own_stream);
     delete g_ctx;
     g_ctx = nullptr;
@@ -258,7 +283,7 @@ int nb200_set_stream(void *cuda_stream) {
 
 int nb200_synchronize(void) {
     NEED_CTX();
-    NB_CUDA(cudaStreamSynchronize(c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));  // NEED_CTX made it wait for the copy streams
     return NB200_OK;
 }
 
@@ -327,20 +352,48 @@ static void drop_derived(nb200_set *s) {
 }
 
 int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int rows, int cols, int64_t ld) {
-    NEED_CTX();
+    NEED_CTX_RAW();
     if (!s || !host || row0 < 0 || col0 < 0 || rows < 0 || cols < 0 || ld < cols) {
         set_error("upload: invalid arguments");
         return NB200_ERR_INVALID;
     }
     if (s->view_of) { set_error("upload: %s:%s is a read-only view", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
-    NB_TRY(ensure_f64(c, s));
+    if (!s->f64) {  // first block of the set: allocate + zero on the compute stream
+        NB_TRY(ensure_f64(c, s));
+        c->main_dirty = true;
+    }
     const int vr = std::min(rows, s->total_rows - row0), vc = std::min(cols, s->total_cols - col0);
     drop_derived(s);
     if (vr <= 0 || vc <= 0) return NB200_OK;  // a block that is all padding
-    NB_CUDA(cudaMemcpy2DAsync(s->f64 + static_cast<size_t>(row0) * s->total_cols + col0,
-                              static_cast<size_t>(s->total_cols) * sizeof(double), host,
-                              static_cast<size_t>(ld) * sizeof(double), static_cast<size_t>(vc) * sizeof(double), vr,
-                              cudaMemcpyHostToDevice, c->stream));
+    if (c->main_dirty) {  // the copy streams must not overtake compute-stream work that touches the set
+        NB_CUDA(cudaEventRecord(c->main_ev, c->stream));
+        for (auto &st : c->copy) NB_CUDA(cudaStreamWaitEvent(st, c->main_ev, 0));
+        c->main_dirty = false;
+    }
+    const int slot = c->up_next;
+    c->up_next ^= 1;
+    cudaStream_t cs = c->copy[slot];
+    double *dst = s->f64 + static_cast<size_t>(row0) * s->total_cols + col0;
+    const size_t dpitch = static_cast<size_t>(s->total_cols) * sizeof(double);
+    const size_t block_bytes = static_cast<size_t>(vr) * ld * sizeof(double);
+    if (block_bytes >= (1u << 20) && dpitch != static_cast<size_t>(ld) * sizeof(double)) {
+        // contiguous H2D of the host rows into a staging slot, then de-block on the device
+        if (c->up_bytes[slot] < block_bytes) {
+            NB_CUDA(cudaStreamSynchronize(cs));
+            cudaFree(c->up_stage[slot]);
+            c->up_stage[slot] = nullptr;
+            c->up_bytes[slot] = 0;
+            NB_CUDA(cudaMalloc(&c->up_stage[slot], block_bytes));
+            c->up_bytes[slot] = block_bytes;
+        }
+        NB_CUDA(cudaMemcpyAsync(c->up_stage[slot], host, block_bytes, cudaMemcpyHostToDevice, cs));
+        NB_CUDA(cudaMemcpy2DAsync(dst, dpitch, c->up_stage[slot], static_cast<size_t>(ld) * sizeof(double),
+                                  static_cast<size_t>(vc) * sizeof(double), vr, cudaMemcpyDeviceToDevice, cs));
+    } else {
+        NB_CUDA(cudaMemcpy2DAsync(dst, dpitch, host, static_cast<size_t>(ld) * sizeof(double),
+                                  static_cast<size_t>(vc) * sizeof(double), vr, cudaMemcpyHostToDevice, cs));
+    }
+    c->uploads_pending = true;
     return NB200_OK;
 }
 

@@ -48,7 +48,18 @@ struct Context {
     cudaStream_t aux[3] = {};        // [0] conversion, [1],[2] alternating GEMM streams
     cudaEvent_t chunk_ev[64] = {};   // conversion of chunk j done
     cudaEvent_t join_ev[4] = {};
+    // block uploads: contiguous H2D into a staging slot, then a device-side de-blocking copy, on two alternating
+    // side streams (a pitched 2-D H2D copy reaches 47 GB/s on this platform, a contiguous one 55 GB/s)
+    cudaStream_t copy[2] = {};
+    double *up_stage[2] = {};
+    size_t up_bytes[2] = {};
+    cudaEvent_t up_ev[2] = {};
+    cudaEvent_t main_ev = nullptr;
+    int up_next = 0;
+    bool uploads_pending = false;  // work queued on the copy streams that the compute stream has not waited for
+    bool main_dirty = true;        // compute-stream work queued since the copy streams last waited for it
 };
+int wait_uploads(Context *c);      // make the compute stream wait for every queued upload
 Context *ctx();                                   // nullptr before nb200_init
 int ensure_ws(Context *c, size_t bytes);          // grows c->ws
 int check_kernel_fault(Context *c, const char *what);  // syncs the stream and reads err_flag
