@@ -650,6 +650,7 @@ struct PipeSrc {
     bool is_f64;
     int64_t ld, cols;
     Planes *planes;
+    FusedScratch *fused;  // non-null: use the fused conversion + GEMM kernel (fp64 source, fp16 operands)
 };
 static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt, nb200_set *w1, nb200_set *wo, const float *b1,
                       const float *bo, Planes *y1, float **y1_f32, size_t *y1_f32_bytes, float *y1_max, float *logits,
@@ -662,7 +663,57 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
     g1.mode = 0;
     if (k0) NB_CUDA(cudaEventRecord(k0, c->stream));
     const int want_splits = choose_splits(c, rows, H, X.ldk, nterms);
-    if (!pipe) {
+    bool fused_done = false;
+    if (pipe && pipe->fused && f16 && pipe->is_f64) {
+        // Fused layer 1: as many whole 256-row tiles as there are SM pairs go through the persistent kernel that
+        // converts fp64 -> fp16 inside the GEMM; the left-over rows take the two-kernel path first.
+        const int sms = c->sm_count > 0 ? c->sm_count : 148;
+        const int tiles_n = static_cast<int>(ceil_div(H, 512));
+        int n_mtiles = (sms / 2) / tiles_n;
+        if (n_mtiles > rows / 256) n_mtiles = rows / 256;
+        if (n_mtiles >= 8 && X.ldk >= 4096) {
+            const int rows_f = n_mtiles * 256;
+            const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
+            if (need > *y1_f32_bytes) {
+                cudaFree(*y1_f32);
+                *y1_f32 = nullptr;
+                *y1_f32_bytes = 0;
+                NB_CUDA(cudaMalloc(y1_f32, need));
+                *y1_f32_bytes = need;
+            }
+            NB_CUDA(cudaMemsetAsync(y1_max, 0, sizeof(float), c->stream));
+            if (rows_f < rows) {
+                Planes sub = *pipe->planes;  // view on the tail rows of the fp16 plane
+                sub.f16 += static_cast<int64_t>(rows_f) * sub.ldk;
+                sub.row_sumsq += rows_f;
+                sub.rows = rows - rows_f;
+                NB_TRY(launch_convert_f16_cols(c, c->stream, static_cast<const double *>(pipe->src) + static_cast<int64_t>(rows_f) * pipe->ld,
+                                               true, rows - rows_f, pipe->cols, pipe->ld, &sub, 0, sub.ldk));
+                int mp = 0, np = 0, used = 1;
+                GemmEpilogue gl;
+                gl.mode = 0;
+                NB_TRY(launch_gemm_tc(c, sub, w1->rowp, rows - rows_f, H, 1, choose_splits(c, rows - rows_f, H, sub.ldk, 1), gl, &mp, &np, &used, fmt));
+                ReduceOut rl;
+                rl.f32 = *y1_f32 + static_cast<int64_t>(rows_f) * H; rl.f32_ld = H;
+                rl.exp_u = sub.f16_exp; rl.exp_v = w1->rowp.f16_exp;
+                rl.out_maxabs = y1_max;  // cleared and set here; the fused kernel folds its own maximum in afterwards
+                NB_TRY(launch_splitk_reduce(c, rows - rows_f, H, used, mp, np, nullptr, b1, 1, rl));
+            }
+            NB_TRY(launch_l1_fused(c, static_cast<const double *>(pipe->src), pipe->ld, rows, static_cast<int>(pipe->cols), 0, n_mtiles,
+                                   *pipe->planes, w1->rowp, H, b1, *y1_f32, H, y1_max, pipe->fused));
+            pipe->planes->f16_valid = false;  // the full fp16 plane of the inputs was never materialised
+            fused_done = true;
+            used1 = 1;
+        }
+    }
+    if (fused_done) {
+        if (k1) NB_CUDA(cudaEventRecord(k1, c->stream));
+        *splits1 = 1;
+        NB_TRY(launch_convert_f16(c, *y1_f32, false, rows, H, H, y1, 1, y1_max));
+        if (after_l1) NB_CUDA(cudaEventRecord(after_l1, c->stream));
+    } else if (!pipe || pipe->fused) {
+        if (pipe)  // fused path requested but the shape does not suit it: materialise the fp16 plane now
+            NB_TRY(launch_convert_f16_cols(c, c->stream, pipe->src, pipe->is_f64, rows, pipe->cols, pipe->ld, pipe->planes, 0, pipe->planes->ldk));
         NB_TRY(launch_gemm_tc(c, X, w1->rowp, rows, H, nterms, want_splits, g1, &Mpad, &Npad, &used1, fmt));
     } else {
         const int64_t num_kb = X.ldk / 64;
@@ -685,6 +736,7 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->join_ev[1], 0));
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->join_ev[2], 0));
     }
+    if (!fused_done) {
     if (k1) NB_CUDA(cudaEventRecord(k1, c->stream));
     *splits1 = used1;
     ReduceOut r1;
@@ -709,6 +761,7 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
         NB_TRY(launch_convert_f16(c, *y1_f32, false, rows, H, H, y1, 1, y1_max));
     }
     if (after_l1) NB_CUDA(cudaEventRecord(after_l1, c->stream));
+    }  // !fused_done
     const int splits2 = choose_splits(c, rows, Lb, y1->ldk, nterms);
     if (splits2 == 1) {
         GemmEpilogue g2;
@@ -749,6 +802,7 @@ struct FFScratch {  // reused across calls
     size_t y1_f32_bytes = 0;
     float *y1_max = nullptr;
     float *host_scalars = nullptr;  // pinned: [0] = largest scaled |x| of the inputs' fp16 conversion
+    FusedScratch fused;             // ring + flags of the fused layer-1 kernel
 };
 static FFScratch g_ff;
 
@@ -864,10 +918,11 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         // pipelined with the layer-1 GEMM chunk by chunk (tc_forward) and only the scale is picked here; measured on
         // B200 the two kernels do not overlap usefully (phase time = sum of both), so it is off by default.
         static const bool overlap = getenv("NB200_OVERLAP") && atoi(getenv("NB200_OVERLAP")) != 0;  // off by default, see DESIGN.md
-        PipeSrc pipe{inputs->f64, true, F, F, &inputs->rowp};
+        static const bool fused = !(getenv("NB200_FUSED") && atoi(getenv("NB200_FUSED")) == 0);
+        PipeSrc pipe{inputs->f64, true, F, F, &inputs->rowp, fused ? &S.fused : nullptr};
         bool pipelined = false;
         if (fmt == kFmtF16) {
-            if (!inputs->rowp.f16_valid && overlap && static_cast<int64_t>(F) >= 8192) {
+            if (!inputs->rowp.f16_valid && (overlap || fused) && static_cast<int64_t>(F) >= 8192) {
                 NB_TRY(prepare_convert_f16(c, inputs->f64, true, B, F, F, &inputs->rowp, 64, nullptr));
                 pipelined = true;
             } else {

@@ -601,6 +601,351 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
 }
 
 
+
+// ---------------------------------------------------------------------------------------------
+// Fused layer 1: fp64 inputs -> fp16 -> tcgen05 in ONE persistent kernel.
+//
+// The two-kernel path reads X (fp64, 47.8 GB on the Amazon shape), writes its fp16 plane (12 GB) and reads the plane
+// back in the GEMM: 9.2 ms + 8.8 ms, both at their own rooflines (HBM, tensor).  Here every CTA pair owns ONE
+// 256 x 512 output tile for the whole K (accumulators stay in TMEM, no split-K), all pairs sweep K together, and
+// eight extra "converter" warps per CTA convert the next K slabs of X into a small ring of fp16 slabs that lives in
+// L2 (tens of MB) and is consumed by the TMA producers a few slabs later.  The fp16 copy of X never goes to HBM, so
+// the phase costs max(read X once from HBM, tensor time) instead of their sum.
+//
+//   converter warps:  wait done[S - ring] == pairs      (slot free)      | consumer (TMA thread of each CTA):
+//                     convert rows x 256 columns of super-slab S -> ring |   wait ready[S] == CTAs, fence.proxy.async,
+//                     fence, ++ready[S]                                  |   TMA ring slab + W1 tile -> smem ring
+//   MMA leader:       after the last K block of S has landed in smem: ++done[S]
+//
+// All CTAs must be resident at once (grid = 2 x pairs <= SM count, 1 CTA / SM); every wait is bounded.
+// ---------------------------------------------------------------------------------------------
+constexpr int kCvtWarps = 8;
+constexpr int kFusedThreads = kThreads + kCvtWarps * 32;  // 448
+// K blocks (of 64) per conversion super-slab are a run-time parameter (FusedArgs::super_kb)
+
+struct FusedArgs {
+    const double *x;        // [rows_total x cols], pitch x_ld
+    long long x_ld;
+    int rows_total, cols;   // B, F
+    int row_base;           // first row of this launch
+    int rows_fused;         // rows covered by this launch (multiple of 256, may exceed rows_total - row_base)
+    int tiles_n;            // N tiles of 512
+    int num_kb;             // ldk / 64
+    int super_kb;           // K blocks per conversion super-slab (multiple of 4: converters work in 256-column pieces)
+    int ring_kb;            // ring length in K blocks (multiple of super_kb)
+    __half *ring;           // [rows_fused][ring_kb * 64]
+    const int *exp_x;       // fp16 scale exponent of X
+    const int *exp_v;       // ... of W1
+    int *ready;             // [num_super]
+    int *done;              // [num_super]
+    float *row_sumsq;       // [rows_total], zeroed by the host
+    float *maxscaled;       // largest |x * 2^e| seen (overflow check)
+    float *out;             // y1 fp32 [rows_total x N], pitch out_ld, receives relu(acc * scale + bias)
+    long long out_ld;
+    const float *bias_n;
+    int N;
+    float *out_maxabs;
+    int *err_flag;
+    unsigned int idesc;
+};
+
+__device__ __forceinline__ int ld_acquire_gpu(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool wait_flag_ge(const int *p, int target) {
+    if (ld_acquire_gpu(p) >= target) return true;
+    const long long t0 = clock64();
+    while (ld_acquire_gpu(p) < target) {
+        __nanosleep(64);
+        if (clock64() - t0 > (1ll << 31)) return false;
+    }
+    return true;
+}
+
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFusedThreads, 1)
+k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__ CUtensorMap map_v, const FusedArgs g) {
+    using L = SmemLayout2<2, STAGES>;
+    constexpr int BN = 512;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + L::kBarOffset);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tmem_full_bar = empty_bar + STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int tile_m = pair / g.tiles_n, tile_n = pair % g.tiles_n;
+    const int kSuperKb = g.super_kb;
+    const int num_super = (g.num_kb + kSuperKb - 1) / kSuperKb;
+    const int ring_super = g.ring_kb / kSuperKb;
+    const int ring_ld = g.ring_kb * kBlockK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_ring);
+        tma_prefetch_desc(&map_v);
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full_bar[s], 2);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_2sm(tmem_slot, BN);
+        tmem_relinquish_2sm();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs): ring slab of X (fp16) + W1 tile =====
+        if (lane == 0) {
+            for (int kb = 0; kb < g.num_kb; kb++) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                if (kb % kSuperKb == 0) {
+                    if (!wait_flag_ge(g.ready + kb / kSuperKb, static_cast<int>(gridDim.x))) { atomicExch(g.err_flag, 404); break; }
+                    asm volatile("fence.proxy.async;" ::: "memory");  // converters wrote the slab through the generic proxy
+                }
+                if (!mbar_wait(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 401); break; }
+                uint8_t *sa = smem + s * L::kStageBytes;
+                uint8_t *sb = sa + kABytes;
+                if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * L::kStageBytes);
+                else mbar_arrive_remote(&full_bar[s], 0);
+                tma_load_2d_2sm(&map_ring, &full_bar[s], sa, (kb % g.ring_kb) * kBlockK,
+                                tile_m * 256 + static_cast<int>(rank) * kBlockM, kEvictNormal);
+                tma_load_2d_2sm(&map_v, &full_bar[s], sb, kb * kBlockK, tile_n * BN + static_cast<int>(rank) * (BN / 2), kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader) =====
+        if (leader && lane == 0) {
+            for (int kb = 0; kb < g.num_kb; kb++) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                if (!mbar_wait(&full_bar[s], ph)) { atomicExch(g.err_flag, 402); break; }
+                tc_fence_after();
+                // both CTAs' loads of this K block have landed: once the super-slab's last block is in, its ring slot is free
+                if (kb % kSuperKb == kSuperKb - 1 || kb == g.num_kb - 1) atomicAdd(g.done + kb / kSuperKb, 1);
+                const uint32_t sa = smem_u32(smem + s * L::kStageBytes);
+                const uint32_t sb = sa + kABytes;
+                const uint64_t da = umma_desc_k_sw128(sa);
+#pragma unroll
+                for (int k = 0; k < kBlockK / kUmmaK; k++) {
+#pragma unroll
+                    for (int sub = 0; sub < 2; sub++) {
+                        const uint64_t db = umma_desc_k_sw128(sb + sub * (128 * kBlockK * 2));
+                        umma_f16_2sm(tmem_base + sub * 256, da + 2 * k, db + 2 * k, g.idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                }
+                umma_commit_2sm(&empty_bar[s], 0x3);
+            }
+            umma_commit_2sm(tmem_full_bar, 0x3);
+        }
+    } else if (warp < 6) {
+        // ===== epilogue: y1 = relu(acc * 2^-(ex+ev) + b1), fp32, and its maximum =====
+        const int q = warp & 3;
+        const long long row = static_cast<long long>(g.row_base) + tile_m * 256 + rank * kBlockM + q * 32 + lane;
+        bool ok = mbar_wait(tmem_full_bar, 0);
+        if (!ok && lane == 0) atomicExch(g.err_flag, 403);
+        ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+        tc_fence_after();
+        if (ok) {
+            const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+            const float oscale = exp2f(-static_cast<float>(*g.exp_x + *g.exp_v));
+            float mx = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c++) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(lane_addr + c * 32, r);
+                tmem_ld_wait();
+                const int sub = (c * 32) / 256, j = (c * 32) % 256;
+                const int tcol = (j < 128) ? sub * 128 + j : BN / 2 + sub * 128 + (j - 128);
+                const int col0 = tile_n * BN + tcol;
+                if (row < g.rows_total) {
+                    float *dst = g.out + row * g.out_ld + col0;
+#pragma unroll
+                    for (int jj = 0; jj < 32; jj++) {
+                        if (col0 + jj < g.N) {
+                            const float v = fmaxf(__uint_as_float(r[jj]) * oscale + g.bias_n[col0 + jj], 0.f);
+                            dst[jj] = v;
+                            mx = fmaxf(mx, v);
+                        }
+                    }
+                }
+            }
+            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            if (lane == 0) atomicMax(reinterpret_cast<unsigned int *>(g.out_maxabs), __float_as_uint(mx));
+        }
+    } else {
+        // ===== converter warps: this CTA's share of the rows, one 256-column super-slab at a time =====
+        const int cw = warp - 6;                        // 0..7
+        const int ct = threadIdx.x - kThreads;          // 0..255
+        const int nctas = gridDim.x;
+        const int rpc = (g.rows_fused + nctas - 1) / nctas;  // rows per CTA (<= 128 by construction)
+        const int r_begin = blockIdx.x * rpc;
+        const float scale = exp2f(static_cast<float>(*g.exp_x));
+        __shared__ int s_abort;                          // written by one thread, read by all after the barrier
+        if (ct == 0) s_abort = 0;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        float mx = 0.f;
+        float ss_acc[16];                                // per-warp rows: rpc / 8 <= 16
+#pragma unroll
+        for (int i = 0; i < 16; i++) ss_acc[i] = 0.f;
+        bool alive = true;
+        for (int S = 0; S < num_super && alive; S++) {
+            if (S >= ring_super) {
+                if (ct == 0 && !wait_flag_ge(g.done + S - ring_super, npairs)) { atomicExch(g.err_flag, 405); s_abort = 1; }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (*reinterpret_cast<volatile int *>(&s_abort) != 0) alive = false;  // same value for all 256 threads
+                if (!alive) break;
+            }
+            // (row, 256-column piece) items of this warp; per item a lane loads 4 x 16 bytes at a 512-byte stride so
+            // that every load instruction of the warp is one contiguous 512-byte run (streaming, evict-first)
+            const int pieces = kSuperKb / 4;
+            const int my_rows = (rpc - cw + kCvtWarps - 1) / kCvtWarps;  // rows cw, cw+8, ... below rpc
+            const int items = my_rows * pieces;
+            // software pipelined by hand in groups of GI items: all loads of a group are issued before any of its
+            // conversions, so GI x 4 x 16 bytes per lane are in flight (the compiler will not hoist loads over the
+            // ring stores by itself)
+            constexpr int GI = 4;
+            for (int it0 = 0; it0 < items; it0 += GI) {
+                double2 v[GI][4];
+#pragma unroll
+                for (int u = 0; u < GI; u++) {
+                    const int it = it0 + u;
+                    const int i = it / pieces, q = it % pieces;
+                    const int rl = r_begin + cw + i * kCvtWarps;
+                    const long long row = static_cast<long long>(g.row_base) + rl;
+                    const long long cbase = (static_cast<long long>(S) * kSuperKb + q * 4) * kBlockK;
+                    const double *p = g.x + row * g.x_ld + cbase + lane * 2;
+                    const bool in = it < items && rl < g.rows_fused && row < g.rows_total;
+                    if (in && cbase + 255 < g.cols && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+#pragma unroll
+                        for (int e = 0; e < 4; e++) v[u][e] = __ldcs(reinterpret_cast<const double2 *>(p + e * 64));
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const long long cc = cbase + e * 64 + lane * 2;
+                            v[u][e].x = (in && cc < g.cols) ? g.x[row * g.x_ld + cc] : 0.0;
+                            v[u][e].y = (in && cc + 1 < g.cols) ? g.x[row * g.x_ld + cc + 1] : 0.0;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < GI; u++) {
+                    const int it = it0 + u;
+                    const int i = it / pieces, q = it % pieces;
+                    const int rl = r_begin + cw + i * kCvtWarps;
+                    if (it >= items || rl >= g.rows_fused) continue;
+                    const int ring_col = ((S % ring_super) * kSuperKb + q * 4) * kBlockK;
+                    __half *dst = g.ring + static_cast<long long>(rl) * ring_ld + ring_col + lane * 2;
+                    float ss = 0.f;
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const float f0 = static_cast<float>(v[u][e].x), f1 = static_cast<float>(v[u][e].y);
+                        const float s0 = f0 * scale, s1 = f1 * scale;
+                        *reinterpret_cast<__half2 *>(dst + e * 64) = __floats2half2_rn(s0, s1);
+                        ss += f0 * f0 + f1 * f1;
+                        mx = fmaxf(mx, fmaxf(fabsf(s0), fabsf(s1)));
+                    }
+                    ss_acc[i] += ss;
+                }
+            }
+            asm volatile("fence.proxy.async;" ::: "memory");
+            __threadfence();
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (ct == 0) atomicAdd(g.ready + S, 1);
+        }
+        // per-row sum of squares (error model) and the overflow check value
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            float ss = ss_acc[i];
+            for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            const int rl = r_begin + cw + i * kCvtWarps;
+            const long long row = static_cast<long long>(g.row_base) + rl;
+            if (lane == 0 && i * kCvtWarps + cw < rpc && rl < g.rows_fused && row < g.rows_total) atomicAdd(g.row_sumsq + row, ss);
+        }
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (lane == 0) atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), __float_as_uint(mx));
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2sm(tmem_base, BN);
+    }
+}
+
+// Host side.  Returns NB200_ERR_STATE (without launching) when the shape does not suit the fused kernel.
+int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, int cols, int row_base, int n_mtiles,
+                    const Planes &xp, const Planes &w1, int N, const float *bias_n, float *out, int64_t out_ld,
+                    float *out_maxabs, FusedScratch *fs) {
+    const int tiles_n = static_cast<int>(ceil_div(N, 512));
+    const int npairs = n_mtiles * tiles_n;
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    if (npairs < 1 || 2 * npairs > sms || !w1.f16_valid || w1.ldk % kBlockK != 0) {
+        set_error("fused layer 1: shape not supported");
+        return NB200_ERR_STATE;
+    }
+    const int num_kb = static_cast<int>(w1.ldk / kBlockK);
+    static int super_env = getenv("NB200_SUPER_KB") ? atoi(getenv("NB200_SUPER_KB")) : 16;
+    const int kSuperKb = (super_env / 4 > 0 ? super_env / 4 : 1) * 4;
+    const int num_super = (num_kb + kSuperKb - 1) / kSuperKb;
+    const int rows_fused = n_mtiles * 256;
+    const int nctas = 2 * npairs;
+    if ((rows_fused + nctas - 1) / nctas > 16 * kCvtWarps) { set_error("fused layer 1: too many rows per CTA"); return NB200_ERR_STATE; }
+    static int ring_kb_env = getenv("NB200_RING_KB") ? atoi(getenv("NB200_RING_KB")) : 48;
+    const int ring_kb = (ring_kb_env / kSuperKb > 1 ? ring_kb_env / kSuperKb : 2) * kSuperKb;
+    const size_t ring_bytes = static_cast<size_t>(rows_fused) * ring_kb * kBlockK * sizeof(__half);
+    if (fs->ring_bytes < ring_bytes) {
+        cudaFree(fs->ring);
+        fs->ring = nullptr;
+        fs->ring_bytes = 0;
+        NB_CUDA(cudaMalloc(&fs->ring, ring_bytes));
+        fs->ring_bytes = ring_bytes;
+    }
+    NB_CUDA(cudaMemsetAsync(fs->ring, 0, ring_bytes, c->stream));  // rows beyond the batch must read as zero
+    if (fs->flag_cap < 2 * num_super) {
+        cudaFree(fs->flags);
+        fs->flags = nullptr;
+        fs->flag_cap = 0;
+        NB_CUDA(cudaMalloc(&fs->flags, static_cast<size_t>(2 * num_super) * sizeof(int)));
+        fs->flag_cap = 2 * num_super;
+    }
+    NB_CUDA(cudaMemsetAsync(fs->flags, 0, static_cast<size_t>(2 * num_super) * sizeof(int), c->stream));
+    // out_maxabs is NOT cleared here: the caller may already have folded the left-over rows' maximum into it
+
+    FusedArgs g{};
+    g.x = x; g.x_ld = x_ld; g.rows_total = rows_total; g.cols = cols; g.row_base = row_base; g.rows_fused = rows_fused;
+    g.tiles_n = tiles_n; g.num_kb = num_kb; g.super_kb = kSuperKb; g.ring_kb = ring_kb; g.ring = fs->ring;
+    g.exp_x = xp.f16_exp; g.exp_v = w1.f16_exp; g.ready = fs->flags; g.done = fs->flags + num_super;
+    g.row_sumsq = xp.row_sumsq; g.maxscaled = xp.f16_maxscaled; g.out = out; g.out_ld = out_ld; g.bias_n = bias_n; g.N = N;
+    g.out_maxabs = out_maxabs; g.err_flag = c->err_flag;
+    g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
+    CUtensorMap mring, mv;
+    NB_TRY(make_plane_map(&mring, reinterpret_cast<const __nv_bfloat16 *>(fs->ring), rows_fused, static_cast<int64_t>(ring_kb) * kBlockK, kBlockM));
+    NB_TRY(make_plane_map(&mv, reinterpret_cast<const __nv_bfloat16 *>(w1.f16), w1.rows, w1.ldk, 256));
+    using L = SmemLayout2<2, 4>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NB_CUDA(cudaFuncSetAttribute(k_l1_fused<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    k_l1_fused<4><<<nctas, kFusedThreads, L::kTotal, c->stream>>>(mring, mv, g);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // conv2d_memory_fusion as an implicit GEMM (K6).  The reference materialises the im2col matrix
 // `image_flat` through ImageToChunks -> ImageChunksToBlock -> ImageBlockToMatrix

@@ -104,6 +104,16 @@ enum { kFmtBF16 = 0, kFmtF16 = 1 };
 int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, int nterms, int splits,
                    const GemmEpilogue &epi, int *Mpad, int *Npad, int *splits_used, int fmt = kFmtBF16);
 int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms);
+// fused layer 1 (fp64 inputs converted to fp16 inside the persistent GEMM through an L2-resident ring)
+struct FusedScratch {
+    __half *ring = nullptr;
+    size_t ring_bytes = 0;
+    int *flags = nullptr;
+    int flag_cap = 0;
+};
+int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, int cols, int row_base, int n_mtiles,
+                    const Planes &xp, const Planes &w1, int N, const float *bias_n, float *out, int64_t out_ld,
+                    float *out_maxabs, FusedScratch *fs);
 // conv2d as implicit GEMM: NHWC bf16 image (channels padded to cp, multiple of 64), kernel planes with K = (tap, channel)
 int launch_conv_implicit(Context *c, const __nv_bfloat16 *img_hi, const __nv_bfloat16 *img_lo, int n, int h, int w, int cp,
                          const Planes &ker, int kout, int k, int pad, int nterms, const float *bias, int relu, float *out);

@@ -349,3 +349,18 @@ def test_conv2d_implicit_gemm_vs_blocked_oracle(nb, oracle, shape):
             assert R.info()[:2] == (n * hout * wout, kout)
             want = np.maximum(refd, 0) if relu else refd
             assert np.abs(R.download_dense() - want).max() <= TOL[prec] * np.abs(refd).max(), (prec, relu)
+
+
+@pytest.mark.parametrize("shape", [(2400, 9000, 700, 50, 500), (2048, 8200, 300, 20, 1000)])
+def test_fused_layer1_kernel_vs_oracle(nb, oracle, shape):
+    """Shapes large enough for the fused layer-1 kernel (fp64 -> fp16 conversion inside the persistent 2-SM GEMM through
+    an L2-resident ring; whole 256-row tiles fused, left-over rows on the two-kernel path): labels and logits vs oracle."""
+    batch, feat, hid, lab, blk = shape
+    dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk)
+    _, ref_logits, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=4)
+    for _ in range(2):  # twice: the ring and its flags are reused across calls
+        dev["x"].invalidate_planes()
+        _, labels, stats = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PREC_F16)
+        assert np.array_equal(labels, ref_labels)
+        z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
+        assert rel(z, ref_logits.dense()) <= TOL["f16"]
