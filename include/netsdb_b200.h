@@ -86,6 +86,9 @@ int nb200_device_count(int *count);
 /* Launch everything on `cuda_stream` (a cudaStream_t) instead of the library's own stream. */
 int nb200_set_stream(void *cuda_stream);
 int nb200_synchronize(void);
+/* Tuning switches (process wide).  "fused_layer1" (default 1): run layer 1 of nb200_ff_inference_unit with the
+ * kernel that converts the fp64 inputs to fp16 inside the persistent GEMM; 0 = separate conversion and GEMM kernels. */
+int nb200_set_option(const char *key, int value);
 /* Number of kernels this library has launched since nb200_init (monotonic). */
 int64_t nb200_launch_count(void);
 

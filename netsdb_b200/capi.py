@@ -22,7 +22,7 @@ PRECISIONS = {"bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "fp64": PREC_FP64, "f16"
 # every symbol include/netsdb_b200.h declares (tests check the .so exports each one)
 EXPORTS = [
     "nb200_init", "nb200_shutdown", "nb200_last_error", "nb200_device_count", "nb200_set_stream",
-    "nb200_synchronize", "nb200_launch_count", "nb200_pin_pool", "nb200_unpin_pool", "nb200_set_create",
+    "nb200_synchronize", "nb200_launch_count", "nb200_set_option", "nb200_pin_pool", "nb200_unpin_pool", "nb200_set_create",
     "nb200_set_lookup", "nb200_set_destroy", "nb200_set_info", "nb200_upload_block", "nb200_upload_rect",
     "nb200_download_block", "nb200_download_rect", "nb200_set_fill_synth", "nb200_set_invalidate_planes",
     "nb200_set_exp_view", "nb200_set_rename",
@@ -66,6 +66,7 @@ def lib():
         L.nb200_device_count.argtypes = [ip]
         L.nb200_set_stream.argtypes = [vp]
         L.nb200_launch_count.restype = i64
+        L.nb200_set_option.argtypes = [C.c_char_p, i]
         L.nb200_pin_pool.argtypes = [vp, C.c_size_t]
         L.nb200_unpin_pool.argtypes = [vp]
         L.nb200_set_create.argtypes = [C.c_char_p, C.c_char_p, i, i, i, i, C.POINTER(vp)]
@@ -115,6 +116,10 @@ def synchronize():
 
 def set_stream(stream_ptr: int | None):
     check(lib().nb200_set_stream(C.c_void_p(stream_ptr or 0)))
+
+
+def set_option(key: str, value: int):
+    check(lib().nb200_set_option(key.encode(), int(value)))
 
 
 def launch_count() -> int:

@@ -23,6 +23,7 @@ void set_error(const char *fmt, ...) {
 }
 
 static Context *g_ctx = nullptr;
+static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default on)
 static std::mutex g_mu;
 static std::map<std::pair<std::string, std::string>, nb200_set *> g_sets;
 
@@ -288,6 +289,12 @@ int nb200_synchronize(void) {
 }
 
 int64_t nb200_launch_count(void) { return g_ctx ? g_ctx->launches : 0; }
+
+int nb200_set_option(const char *key, int value) {
+    if (key && !strcmp(key, "fused_layer1")) { g_opt_fused = value ? 1 : 0; return NB200_OK; }
+    set_error("set_option: unknown key");
+    return NB200_ERR_INVALID;
+}
 
 int nb200_pin_pool(void *base, size_t bytes) {
     NEED_CTX();
@@ -918,7 +925,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         // pipelined with the layer-1 GEMM chunk by chunk (tc_forward) and only the scale is picked here; measured on
         // B200 the two kernels do not overlap usefully (phase time = sum of both), so it is off by default.
         static const bool overlap = getenv("NB200_OVERLAP") && atoi(getenv("NB200_OVERLAP")) != 0;  // off by default, see DESIGN.md
-        static const bool fused = !(getenv("NB200_FUSED") && atoi(getenv("NB200_FUSED")) == 0);
+        const bool fused = g_opt_fused >= 0 ? g_opt_fused != 0 : !(getenv("NB200_FUSED") && atoi(getenv("NB200_FUSED")) == 0);
         PipeSrc pipe{inputs->f64, true, F, F, &inputs->rowp, fused ? &S.fused : nullptr};
         bool pipelined = false;
         if (fmt == kFmtF16) {

@@ -619,7 +619,7 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
 //
 // All CTAs must be resident at once (grid = 2 x pairs <= SM count, 1 CTA / SM); every wait is bounded.
 // ---------------------------------------------------------------------------------------------
-constexpr int kCvtWarps = 8;
+constexpr int kCvtWarps = 12;
 constexpr int kFusedThreads = kThreads + kCvtWarps * 32;  // 448
 // K blocks (of 64) per conversion super-slab are a run-time parameter (FusedArgs::super_kb)
 
@@ -663,6 +663,7 @@ __device__ __forceinline__ bool wait_flag_ge(const int *p, int target) {
     }
     return true;
 }
+
 
 template <int STAGES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFusedThreads, 1)
@@ -787,15 +788,15 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
         }
     } else {
         // ===== converter warps: this CTA's share of the rows, one 256-column super-slab at a time =====
-        const int cw = warp - 6;                        // 0..7
-        const int ct = threadIdx.x - kThreads;          // 0..255
+        const int cw = warp - 6;                        // 0..kCvtWarps-1
+        const int ct = threadIdx.x - kThreads;          // 0..kCvtWarps*32-1
         const int nctas = gridDim.x;
         const int rpc = (g.rows_fused + nctas - 1) / nctas;  // rows per CTA (<= 128 by construction)
         const int r_begin = blockIdx.x * rpc;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
         __shared__ int s_abort;                          // written by one thread, read by all after the barrier
         if (ct == 0) s_abort = 0;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kCvtWarps * 32) : "memory");
         float mx = 0.f;
         float ss_acc[16];                                // per-warp rows: rpc / 8 <= 16
 #pragma unroll
@@ -804,7 +805,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
         for (int S = 0; S < num_super && alive; S++) {
             if (S >= ring_super) {
                 if (ct == 0 && !wait_flag_ge(g.done + S - ring_super, npairs)) { atomicExch(g.err_flag, 405); s_abort = 1; }
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(kCvtWarps * 32) : "memory");
                 if (*reinterpret_cast<volatile int *>(&s_abort) != 0) alive = false;  // same value for all 256 threads
                 if (!alive) break;
             }
@@ -862,7 +863,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
             }
             asm volatile("fence.proxy.async;" ::: "memory");
             __threadfence();
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(kCvtWarps * 32) : "memory");
             if (ct == 0) atomicAdd(g.ready + S, 1);
         }
         // per-row sum of squares (error model) and the overflow check value
@@ -903,7 +904,7 @@ int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, i
     const int rows_fused = n_mtiles * 256;
     const int nctas = 2 * npairs;
     if ((rows_fused + nctas - 1) / nctas > 16 * kCvtWarps) { set_error("fused layer 1: too many rows per CTA"); return NB200_ERR_STATE; }
-    static int ring_kb_env = getenv("NB200_RING_KB") ? atoi(getenv("NB200_RING_KB")) : 48;
+    static int ring_kb_env = getenv("NB200_RING_KB") ? atoi(getenv("NB200_RING_KB")) : 32;
     const int ring_kb = (ring_kb_env / kSuperKb > 1 ? ring_kb_env / kSuperKb : 2) * kSuperKb;
     const size_t ring_bytes = static_cast<size_t>(rows_fused) * ring_kb * kBlockK * sizeof(__half);
     if (fs->ring_bytes < ring_bytes) {
