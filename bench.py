@@ -257,7 +257,7 @@ def run_b200(a):
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
         if (a.batch, a.features, a.hidden) == (10000, 597540, 1000) and a.precision in ("f16", "bf16"):
-            traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+            traffic = {k: v["dram_bytes_read"] + v["dram_bytes_write"] for k, v in tr.items() if isinstance(v, dict)}
     except Exception:
         pass
     fused_on = a.precision == "f16" and stats.get("splits1", 0) == 1
@@ -265,13 +265,15 @@ def run_b200(a):
     # the fused kernel reads the fp64 inputs once while it multiplies: it is bounded by the slower of the two
     rows_fused = (148 // 2 // ((a.hidden + 511) // 512)) * 256 if fused_on else a.batch
     rows_fused = min(rows_fused, a.batch // 256 * 256) if fused_on else a.batch
-    flops_k = 2.0 * rows_fused * a.hidden * a.features if fused_on else flops1
-    bytes_k = rows_fused * a.features * 8.0 + a.hidden * a.features * 2.0 if fused_on else None
+    # the event window around layer 1 also covers the left-over rows' two kernels, so all rows count
+    flops_k = flops1
+    bytes_k = a.batch * a.features * 8.0 + a.hidden * a.features * 2.0 if fused_on else None
     ach = flops_k / (k_ms / 1000.0) / 1e12 if k_ms > 0 else None
     roofline = dict(bound="tensor", kernel=("k_l1_fused<4> (layer 1: fp64->fp16 conversion inside the 2-SM tcgen05 GEMM)" if fused_on
                                             else "k_block_gemm_2sm<2,4> (layer 1)"),
                     achieved=ach, peak=peak_tf, unit="TFLOP/s",
-                    frac=(ach / peak_tf if ach else None), traffic=(None if fused_on else traffic), peak_source=which,
+                    frac=(ach / peak_tf if ach else None),
+                    traffic=((traffic or {}).get("k_l1_fused<4>" if fused_on else "k_block_gemm_2sm<2,4> (layer 1)")), peak_source=which,
                     algorithmic_flops_per_launch=flops_k,
                     hbm=(dict(algorithmic_bytes=bytes_k, achieved_gbs=bytes_k / (k_ms / 1e3) / 1e9, peak_gbs=hbm_peak,
                               frac=bytes_k / (k_ms / 1e3) / 1e9 / hbm_peak) if fused_on and k_ms > 0 else None),

@@ -797,7 +797,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
         __shared__ int s_abort;                          // written by one thread, read by all after the barrier
         if (ct == 0) s_abort = 0;
         asm volatile("bar.sync 1, %0;" ::"n"(kCvtWarps * 32) : "memory");
-        float mx = 0.f;
+        uint32_t ovf = 0;                                // any converted value overflowed fp16
         float ss_acc[16];                                // per-warp rows: rpc / 8 <= 16
 #pragma unroll
         for (int i = 0; i < 16; i++) ss_acc[i] = 0.f;
@@ -853,10 +853,12 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
 #pragma unroll
                     for (int e = 0; e < 4; e++) {
                         const float f0 = static_cast<float>(v[u][e].x), f1 = static_cast<float>(v[u][e].y);
-                        const float s0 = f0 * scale, s1 = f1 * scale;
-                        *reinterpret_cast<__half2 *>(dst + e * 64) = __floats2half2_rn(s0, s1);
-                        ss += f0 * f0 + f1 * f1;
-                        mx = fmaxf(mx, fmaxf(fabsf(s0), fabsf(s1)));
+                        const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
+                        *reinterpret_cast<__half2 *>(dst + e * 64) = h2;
+                        ss = fmaf(f0, f0, fmaf(f1, f1, ss));
+                        // overflow check on the packed result: an all-ones fp16 exponent (inf) in either half
+                        const uint32_t hb = *reinterpret_cast<const uint32_t *>(&h2);
+                        ovf |= ((hb & 0x7C00u) == 0x7C00u) | ((hb & 0x7C000000u) == 0x7C000000u);
                     }
                     ss_acc[i] += ss;
                 }
@@ -875,8 +877,9 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
             const long long row = static_cast<long long>(g.row_base) + rl;
             if (lane == 0 && i * kCvtWarps + cw < rpc && rl < g.rows_fused && row < g.rows_total) atomicAdd(g.row_sumsq + row, ss);
         }
-        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        if (lane == 0) atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), __float_as_uint(mx));
+        // the host compares maxscaled with 65504: report +inf when anything overflowed
+        if (__any_sync(0xffffffffu, ovf != 0) && lane == 0)
+            atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), 0x7F800000u);
     }
     tc_fence_before();
     cluster_sync_all();
