@@ -713,7 +713,8 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
                 const int s = kb % STAGES;
                 const uint32_t ph = (kb / STAGES) & 1;
                 if (kb % kSuperKb == 0) {
-                    if (!wait_flag_ge(g.ready + kb / kSuperKb, static_cast<int>(gridDim.x))) { atomicExch(g.err_flag, 404); break; }
+                    // only the 2 * tiles_n CTAs that share this M tile convert its rows
+                    if (!wait_flag_ge(g.ready + tile_m * num_super + kb / kSuperKb, 2 * g.tiles_n)) { atomicExch(g.err_flag, 404); break; }
                     asm volatile("fence.proxy.async;" ::: "memory");  // converters wrote the slab through the generic proxy
                 }
                 if (!mbar_wait(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 401); break; }
@@ -735,7 +736,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
                 if (!mbar_wait(&full_bar[s], ph)) { atomicExch(g.err_flag, 402); break; }
                 tc_fence_after();
                 // both CTAs' loads of this K block have landed: once the super-slab's last block is in, its ring slot is free
-                if (kb % kSuperKb == kSuperKb - 1 || kb == g.num_kb - 1) atomicAdd(g.done + kb / kSuperKb, 1);
+                if (kb % kSuperKb == kSuperKb - 1 || kb == g.num_kb - 1) atomicAdd(g.done + tile_m * num_super + kb / kSuperKb, 1);
                 const uint32_t sa = smem_u32(smem + s * L::kStageBytes);
                 const uint32_t sb = sa + kABytes;
                 const uint64_t da = umma_desc_k_sw128(sa);
@@ -790,9 +791,10 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
         // ===== converter warps: this CTA's share of the rows, one 256-column super-slab at a time =====
         const int cw = warp - 6;                        // 0..kCvtWarps-1
         const int ct = threadIdx.x - kThreads;          // 0..kCvtWarps*32-1
-        const int nctas = gridDim.x;
-        const int rpc = (g.rows_fused + nctas - 1) / nctas;  // rows per CTA (<= 128 by construction)
-        const int r_begin = blockIdx.x * rpc;
+        // the 256 rows of an M tile are converted by the 2 * tiles_n CTAs that consume it, so every handshake is
+        // local to that small group and the groups sweep K independently of one another
+        const int rpc = 256 / (2 * g.tiles_n);               // rows per CTA (64 or 128)
+        const int r_begin = tile_m * 256 + (tile_n * 2 + static_cast<int>(rank)) * rpc;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
         __shared__ int s_abort;                          // written by one thread, read by all after the barrier
         if (ct == 0) s_abort = 0;
@@ -804,7 +806,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
         bool alive = true;
         for (int S = 0; S < num_super && alive; S++) {
             if (S >= ring_super) {
-                if (ct == 0 && !wait_flag_ge(g.done + S - ring_super, npairs)) { atomicExch(g.err_flag, 405); s_abort = 1; }
+                if (ct == 0 && !wait_flag_ge(g.done + tile_m * num_super + S - ring_super, g.tiles_n)) { atomicExch(g.err_flag, 405); s_abort = 1; }
                 asm volatile("bar.sync 1, %0;" ::"n"(kCvtWarps * 32) : "memory");
                 if (*reinterpret_cast<volatile int *>(&s_abort) != 0) alive = false;  // same value for all 256 threads
                 if (!alive) break;
@@ -866,7 +868,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
             asm volatile("fence.proxy.async;" ::: "memory");
             __threadfence();
             asm volatile("bar.sync 1, %0;" ::"n"(kCvtWarps * 32) : "memory");
-            if (ct == 0) atomicAdd(g.ready + S, 1);
+            if (ct == 0) atomicAdd(g.ready + tile_m * num_super + S, 1);
         }
         // per-row sum of squares (error model) and the overflow check value
 #pragma unroll
@@ -906,7 +908,7 @@ int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, i
     const int num_super = (num_kb + kSuperKb - 1) / kSuperKb;
     const int rows_fused = n_mtiles * 256;
     const int nctas = 2 * npairs;
-    if ((rows_fused + nctas - 1) / nctas > 16 * kCvtWarps) { set_error("fused layer 1: too many rows per CTA"); return NB200_ERR_STATE; }
+    if (tiles_n > 2) { set_error("fused layer 1: more than 2 N tiles are not supported"); return NB200_ERR_STATE; }
     static int ring_kb_env = getenv("NB200_RING_KB") ? atoi(getenv("NB200_RING_KB")) : 32;
     const int ring_kb = (ring_kb_env / kSuperKb > 1 ? ring_kb_env / kSuperKb : 2) * kSuperKb;
     const size_t ring_bytes = static_cast<size_t>(rows_fused) * ring_kb * kBlockK * sizeof(__half);
@@ -918,20 +920,21 @@ int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, i
         fs->ring_bytes = ring_bytes;
     }
     NB_CUDA(cudaMemsetAsync(fs->ring, 0, ring_bytes, c->stream));  // rows beyond the batch must read as zero
-    if (fs->flag_cap < 2 * num_super) {
+    const int nflags = 2 * n_mtiles * num_super;  // ready[tile_m][S], done[tile_m][S]
+    if (fs->flag_cap < nflags) {
         cudaFree(fs->flags);
         fs->flags = nullptr;
         fs->flag_cap = 0;
-        NB_CUDA(cudaMalloc(&fs->flags, static_cast<size_t>(2 * num_super) * sizeof(int)));
-        fs->flag_cap = 2 * num_super;
+        NB_CUDA(cudaMalloc(&fs->flags, static_cast<size_t>(nflags) * sizeof(int)));
+        fs->flag_cap = nflags;
     }
-    NB_CUDA(cudaMemsetAsync(fs->flags, 0, static_cast<size_t>(2 * num_super) * sizeof(int), c->stream));
+    NB_CUDA(cudaMemsetAsync(fs->flags, 0, static_cast<size_t>(nflags) * sizeof(int), c->stream));
     // out_maxabs is NOT cleared here: the caller may already have folded the left-over rows' maximum into it
 
     FusedArgs g{};
     g.x = x; g.x_ld = x_ld; g.rows_total = rows_total; g.cols = cols; g.row_base = row_base; g.rows_fused = rows_fused;
     g.tiles_n = tiles_n; g.num_kb = num_kb; g.super_kb = kSuperKb; g.ring_kb = ring_kb; g.ring = fs->ring;
-    g.exp_x = xp.f16_exp; g.exp_v = w1.f16_exp; g.ready = fs->flags; g.done = fs->flags + num_super;
+    g.exp_x = xp.f16_exp; g.exp_v = w1.f16_exp; g.ready = fs->flags; g.done = fs->flags + n_mtiles * num_super;
     g.row_sumsq = xp.row_sumsq; g.maxscaled = xp.f16_maxscaled; g.out = out; g.out_ld = out_ld; g.bias_n = bias_n; g.N = N;
     g.out_maxabs = out_maxabs; g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
