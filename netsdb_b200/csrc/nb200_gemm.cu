@@ -680,7 +680,7 @@ k_l1_fused(const __grid_constant__ CUtensorMap map_ring, const __grid_constant__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
-    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int pair = blockIdx.x >> 1;
     const int tile_m = pair / g.tiles_n, tile_n = pair % g.tiles_n;
     const int kSuperKb = g.super_kb;
     const int num_super = (g.num_kb + kSuperKb - 1) / kSuperKb;

@@ -28,6 +28,8 @@ uint64_t seed_of_set(const std::string &n) {
     if (n == "b1") return 3;
     if (n == "wo") return 4;
     if (n == "bo") return 5;
+    if (n == "w2") return 6;
+    if (n == "b2") return 7;
     return 1000 + std::hash<std::string>()(n) % 1000000;
 }
 

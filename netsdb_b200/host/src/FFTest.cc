@@ -3,6 +3,7 @@
 // predicted labels and a few probabilities, so that the parity tests can compare against the oracle.
 //
 //   FFTest blockX blockY batch features neurons labels [dump.txt]
+//   NB200_FF_LAYERS=3 runs the 3-layer ff::inference (w1, w2, wo) instead of ff::inference_unit
 #include <chrono>
 #include <cstdio>
 
@@ -37,8 +38,15 @@ int main(int argc, char *argv[]) {
     ff::loadMatrix(pdbClient, "ff", "bo", numLabels, 1, block_x, 1, false, true, errMsg);
 
     const double dropout_rate = 0;  // the reference driver passes 0.5 drawn from a time-seeded rand(); parity needs 0
+    const bool three = getenv("NB200_FF_LAYERS") && atoi(getenv("NB200_FF_LAYERS")) == 3;
+    if (three) {
+        for (const char *s : {"w2", "b2", "y2"}) ff::createSet(pdbClient, "ff", s, s, 64);
+        ff::loadMatrix(pdbClient, "ff", "w2", numNeurons, numNeurons, block_x, block_x, false, false, errMsg);
+        ff::loadMatrix(pdbClient, "ff", "b2", numNeurons, 1, block_x, 1, false, true, errMsg);
+    }
     auto begin = std::chrono::high_resolution_clock::now();
-    ff::inference_unit(pdbClient, "ff", "w1", "wo", "inputs", "b1", "bo", "output", dropout_rate);
+    if (three) ff::inference(pdbClient, "ff", "w1", "w2", "wo", "inputs", "b1", "b2", "bo", "output", dropout_rate);
+    else ff::inference_unit(pdbClient, "ff", "w1", "wo", "inputs", "b1", "bo", "output", dropout_rate);
     auto end = std::chrono::high_resolution_clock::now();
     std::cout << "*****FFTest End-to-End Time Duration: ****" << std::chrono::duration<float>(end - begin).count() << " secs."
               << std::endl;

@@ -47,6 +47,71 @@ void cleanup(pdb::PDBClient &pdbClient, std::string database) {
     for (const char *s : {"inputs", "label", "w1", "b1", "wo", "bo", "y1", "yo", "output"}) pdbClient.removeSet(database, s, errMsg);
 }
 
+// One layer of the 3-layer pipeline as its own graph + executeComputations, as in the reference
+// (SimpleFF.cc:99-147 layer 1 with FFTransposeMult; :166-214, :231-275 the FFInputLayerJoin layers).
+static void run_layer(pdb::PDBClient &pdbClient, const std::string &database, bool first, const std::string &w,
+                      const std::string &in, const std::string &bias, bool last, double dropout_rate, const std::string &out,
+                      const char *jobName) {
+    using pdb::Computation;
+    using pdb::Handle;
+    using pdb::makeObject;
+    std::string errMsg;
+    const pdb::UseTemporaryAllocationBlock tempBlock{1024 * 1024 * 128};
+    Handle<Computation> readW = makeObject<FFMatrixBlockScanner>(database, w);
+    Handle<Computation> readIn = makeObject<FFMatrixBlockScanner>(database, in);
+    Handle<Computation> join;
+    if (first) join = makeObject<FFTransposeMult>();
+    else join = makeObject<FFInputLayerJoin>();
+    join->setInput(0, readW);
+    join->setInput(1, readIn);
+    Handle<Computation> agg = makeObject<FFAggMatrix>();
+    agg->setInput(join);
+    Handle<Computation> readB = makeObject<FFMatrixBlockScanner>(database, bias);
+    Handle<Computation> act;
+    if (last) act = makeObject<FFTransposeBiasSum>();
+    else act = makeObject<FFReluBiasSum>(dropout_rate);
+    act->setInput(0, agg);
+    act->setInput(1, readB);
+    Handle<Computation> writer = makeObject<FFMatrixWriter>(database, out);
+    writer->setInput(act);
+    auto t0 = std::chrono::high_resolution_clock::now();
+    if (!pdbClient.executeComputations(errMsg, jobName, false, writer)) {
+        std::cout << "Computation failed. Message was: " << errMsg << "\n";
+        exit(1);
+    }
+    std::cout << jobName << " Stage Time Duration: "
+              << std::chrono::duration<float>(std::chrono::high_resolution_clock::now() - t0).count() << " secs." << std::endl;
+}
+
+void inference_compute(pdb::PDBClient &pdbClient, std::string database, std::string w1, std::string w2, std::string wo,
+                       std::string inputs, std::string b1, std::string b2, std::string bo, double dropout_rate, bool) {
+    run_layer(pdbClient, database, true, w1, inputs, b1, false, dropout_rate, "y1", "inference-1");
+    run_layer(pdbClient, database, false, w2, "y1", b2, false, dropout_rate, "y2", "inference-2");
+    run_layer(pdbClient, database, false, wo, "y2", bo, true, dropout_rate, "yo", "inference-3");
+}
+
+void inference(pdb::PDBClient &pdbClient, std::string database, std::string w1, std::string w2, std::string wo, std::string inputs,
+               std::string b1, std::string b2, std::string bo, std::string output, double dropout_rate, bool enablePartition) {
+    using pdb::Computation;
+    using pdb::Handle;
+    using pdb::makeObject;
+    inference_compute(pdbClient, database, w1, w2, wo, inputs, b1, b2, bo, dropout_rate, enablePartition);
+    std::string errMsg;
+    const pdb::UseTemporaryAllocationBlock tempBlock{1024 * 1024 * 128};
+    Handle<Computation> readYo = makeObject<FFMatrixBlockScanner>(database, "yo");
+    Handle<Computation> expSum = makeObject<FFRowAggregate>();
+    expSum->setInput(readYo);
+    Handle<Computation> softmax = makeObject<FFOutputLayer>();
+    softmax->setInput(0, readYo);
+    softmax->setInput(1, expSum);
+    Handle<Computation> writeOut = makeObject<FFMatrixWriter>(database, output);
+    writeOut->setInput(softmax);
+    if (!pdbClient.executeComputations(errMsg, "inference-3", false, writeOut)) {
+        std::cout << "Computation failed. Message was: " << errMsg << "\n";
+        exit(1);
+    }
+}
+
 void inference_unit(pdb::PDBClient &pdbClient, std::string database, std::string w1, std::string wo, std::string inputs,
                     std::string b1, std::string bo, std::string output, double dropout_rate, bool) {
     using pdb::Computation;

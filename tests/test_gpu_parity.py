@@ -364,3 +364,29 @@ def test_fused_layer1_kernel_vs_oracle(nb, oracle, shape):
         assert np.array_equal(labels, ref_labels)
         z = nb.DeviceSet.lookup("ff", "__logits").download_dense()
         assert rel(z, ref_logits.dense()) <= TOL["f16"]
+
+
+@pytest.mark.parametrize("prec", ["bf16x3", "fp64"])
+def test_cpp_three_layer_inference(oracle, prec, tmp_path):
+    """ff::inference (SimpleFF.cc:94-329): three separately executed graphs writing y1, y2, yo, then the softmax graph,
+    each lowered to one block GEMM with its bias join fused; checked against the oracle's operators composed the same way."""
+    from netsdb_b200 import build
+
+    exe = build.build_host()["FFTest"]
+    blk, batch, feat, hid, lab = 50, 130, 220, 110, 9
+    dump = tmp_path / "dump3.txt"
+    r = _run([exe, str(blk), str(blk), str(batch), str(feat), str(hid), str(lab), str(dump)],
+             {"NB200_PRECISION": prec, "NB200_FF_LAYERS": "3"})
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    got = np.loadtxt(dump)
+    L = lambda rows, cols, seed, bc: oracle.load_matrix(oracle.synth_dense(rows, cols, seed), blk, bc)
+    X, W1, B1 = L(batch, feat, 1, blk), L(hid, feat, 2, blk), L(hid, 1, 3, 1)
+    WO, BO, W2, B2 = L(lab, hid, 4, blk), L(lab, 1, 5, 1), L(hid, hid, 6, blk), L(hid, 1, 7, 1)
+    y1 = oracle.relu_bias_sum(oracle.transpose_mult_agg(W1, X, 2), B1)
+    y2 = oracle.relu_bias_sum(oracle.input_layer_join_agg(W2, y1, 2), B2)
+    z = oracle.input_layer_join_agg(WO, y2, 2)
+    yo = oracle.transpose_bias_sum(z, BO, True)
+    probs = oracle.output_layer(yo, oracle.row_aggregate(yo)).dense()
+    assert np.isfinite(probs).all()
+    assert np.array_equal(got[:, 1].astype(np.int32), np.argmax(probs, axis=1))   # argmax of the `output` set read back
+    assert np.abs(got[:, 2] - probs[:, 0]).max() <= (1e-9 if prec == "fp64" else 1e-3)
