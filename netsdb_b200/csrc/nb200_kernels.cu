@@ -973,14 +973,16 @@ k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restri
 // from HBM exactly once as float4, kept in registers for the max / argmax / top-2 scan, the exp-sum and the
 // normalisation, and the probabilities leave as 16-byte stores.  exp is evaluated in fp32 (the logits are fp32
 // tensor-core results; their own error dominates) and widened to the fp64 output type of the reference.
-__global__ void __launch_bounds__(256)
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
 k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *__restrict__ probs, long long probs_ld,
                    int32_t *__restrict__ labels, float *__restrict__ gap, const int32_t *__restrict__ row_list,
                    int in_compact) {
-    constexpr int NV = 16;  // float4 per thread
-    __shared__ float s_m1[8], s_m2[8];
-    __shared__ double s_sum[8];
-    __shared__ int s_i1[8];
+    constexpr int NV = 4096 / THREADS;  // float4 per thread (covers 16,384 columns)
+    constexpr int NW = THREADS / 32;
+    __shared__ float s_m1[NW], s_m2[NW];
+    __shared__ double s_sum[NW];
+    __shared__ int s_i1[NW];
     __shared__ float b_m1;
     __shared__ double b_sum;
     const long long row = row_list ? row_list[blockIdx.x] : blockIdx.x;
@@ -989,14 +991,14 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
     float4 v[NV];
 #pragma unroll
     for (int i = 0; i < NV; i++) {
-        const int q = threadIdx.x + i * 256;
+        const int q = threadIdx.x + i * THREADS;
         v[i] = q < nvec ? __ldg(zr + q) : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
     }
     float m1 = -CUDART_INF_F, m2 = -CUDART_INF_F;
     int i1 = 0x7fffffff;
 #pragma unroll
     for (int i = 0; i < NV; i++) {
-        const int base = (threadIdx.x + i * 256) * 4;
+        const int base = (threadIdx.x + i * THREADS) * 4;
         const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
         for (int j = 0; j < 4; j++) {
@@ -1016,7 +1018,7 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
     if (threadIdx.x == 0) {
         float a1 = s_m1[0], a2 = s_m2[0];
         int ai = s_i1[0];
-        for (int k = 1; k < 8; k++) {
+        for (int k = 1; k < NW; k++) {
             const float om1 = s_m1[k], om2 = s_m2[k];
             const int oi1 = s_i1[k];
             if (om1 > a1 || (om1 == a1 && oi1 < ai)) { a2 = fmaxf(a1, om2); a1 = om1; ai = oi1; }
@@ -1040,7 +1042,7 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
     __syncthreads();
     if (threadIdx.x == 0) {
         double t = 0.0;
-        for (int k = 0; k < 8; k++) t += s_sum[k];
+        for (int k = 0; k < NW; k++) t += s_sum[k];
         b_sum = t;
     }
     __syncthreads();
@@ -1049,7 +1051,7 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
     const bool aligned = ((reinterpret_cast<uintptr_t>(pr) & 15) == 0);
 #pragma unroll
     for (int i = 0; i < NV; i++) {
-        const int q = threadIdx.x + i * 256;
+        const int q = threadIdx.x + i * THREADS;
         if (q < nvec) {
             const double a = v[i].x * inv, b = v[i].y * inv, cc = v[i].z * inv, d = v[i].w * inv;
             if (aligned) {
@@ -1068,7 +1070,10 @@ int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t row
     const int64_t n = row_list ? nrows_list : rows;
     if (n == 0 || cols == 0) return NB200_OK;
     if (!is_f64 && cols <= 16384 && (cols & 3) == 0 && (ld & 3) == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0) {
-        k_softmax_rows_reg<<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+        static const int thr = getenv("NB200_SOFTMAX_THREADS") ? atoi(getenv("NB200_SOFTMAX_THREADS")) : 512;
+        if (thr == 1024) k_softmax_rows_reg<1024><<<static_cast<unsigned>(n), 1024, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+        else if (thr == 256) k_softmax_rows_reg<256><<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+        else k_softmax_rows_reg<512><<<static_cast<unsigned>(n), 512, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
         NB_LAUNCH_CHECK(c);
         return NB200_OK;
     }
