@@ -44,6 +44,18 @@ def test_amazon14k_full_size_properties(nb, oracle):
     zs = nb.DeviceSet.lookup("ff", "__logits")
     got = np.stack([np.ascontiguousarray(zs.download_block(int(r) // blk, 0, blk, lab)[int(r) % blk]) for r in sample[:3]])
     assert np.abs(got - z[:3]).max() <= 2.5e-3 * np.abs(z).max()
+    # every one of the 10,000 labels against the device's own fp64 (DMMA) pipeline, which is checked against the
+    # oracle at oracle-sized shapes; plus the bf16x3 path as a third, independent arithmetic
+    z_f16 = zs.download_block(3, 0, blk, lab)
+    _, labels_x3, _ = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_BF16X3)
+    assert np.array_equal(labels, labels_x3)
+    _, labels_f64, _ = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_FP64)
+    assert np.array_equal(labels, labels_f64), f"{(labels != labels_f64).sum()} of {batch} labels differ from the fp64 pipeline"
+    z_f64 = nb.DeviceSet.lookup("ff", "__logits").download_block(3, 0, blk, lab)
+    assert np.abs(z_f16 - z_f64).max() <= 2.5e-3 * np.abs(z_f64).max()
+    z_f64_b4 = nb.DeviceSet.lookup("ff", "__logits").download_block(4, 0, blk, lab)
+    assert np.abs(z_f64_b4[242] - z[4]).max() <= 1e-9 * np.abs(z).max()   # row 4242 = sample[4]: fp64 device vs fp64 host
+    out, _, _ = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_F16)
     # probabilities: rows sum to one, argmax agrees with the labels, padding of the last label block is zero
     pblk = out.download_block(9, 14)                          # rows 9000..9999, labels 14000..14999 (588 real)
     assert (pblk[:, 588:] == 0).all() and (pblk >= 0).all()
