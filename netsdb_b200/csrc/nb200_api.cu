@@ -678,7 +678,7 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
         const int tiles_n = static_cast<int>(ceil_div(H, 512));
         int n_mtiles = (sms / 2) / tiles_n;
         if (n_mtiles > rows / 256) n_mtiles = rows / 256;
-        if (n_mtiles >= 8 && X.ldk >= 4096) {
+        if (n_mtiles >= 8 && X.ldk >= 4096 && tiles_n <= 2) {  // wider hidden layers take the two-kernel path
             const int rows_f = n_mtiles * 256;
             const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
             if (need > *y1_f32_bytes) {
@@ -930,10 +930,10 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         bool pipelined = false;
         if (fmt == kFmtF16) {
             if (!inputs->rowp.f16_valid && (overlap || fused) && static_cast<int64_t>(F) >= 8192) {
-                NB_TRY(prepare_convert_f16(c, inputs->f64, true, B, F, F, &inputs->rowp, 64, nullptr));
+                NB_TRY(prepare_convert_f16(c, inputs->f64, true, B, F, F, &inputs->rowp, 128, nullptr));
                 pipelined = true;
             } else {
-                NB_TRY(ensure_f16_row(c, inputs, 64));
+                NB_TRY(ensure_f16_row(c, inputs, 128));
             }
         } else {
             NB_TRY(ensure_rowp(c, inputs, lo));

@@ -162,10 +162,14 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 k_max_sampled(const T *__restrict__ src, long long ld, long long rows, long long cols, int stride,
               float *__restrict__ maxabs) {
+    // work item = (sampled row, 8192-column piece); grid-stride so that a handful of sampled rows still fills the GPU
+    const long long nsamp = (rows + stride - 1) / stride;
+    const long long pieces = (cols + 8191) / 8192;
     float mx = 0.f;
-    for (long long r = static_cast<long long>(blockIdx.x) * stride; r < rows; r += static_cast<long long>(gridDim.x) * stride) {
-        const T *srow = src + r * ld;
-        for (long long c = threadIdx.x; c < cols; c += 256) mx = fmaxf(mx, fabsf(static_cast<float>(srow[c])));
+    for (long long w = blockIdx.x; w < nsamp * pieces; w += gridDim.x) {
+        const T *srow = src + (w / pieces) * stride * ld;
+        const long long c0 = (w % pieces) * 8192, c1 = (c0 + 8192 < cols) ? c0 + 8192 : cols;
+        for (long long c = c0 + threadIdx.x; c < c1; c += 256) mx = fmaxf(mx, fabsf(static_cast<float>(srow[c])));
     }
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<unsigned int *>(maxabs), __float_as_uint(mx));
@@ -264,8 +268,8 @@ int prepare_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t ro
     if (!mx) {
         NB_CUDA(cudaMemsetAsync(p->maxabs, 0, sizeof(float), c->stream));
         const int stride = sample_stride > 1 ? sample_stride : 1;
-        const int64_t nsamp = ceil_div(rows, stride);
-        const unsigned blocks = static_cast<unsigned>(nsamp < 148 * 16 ? nsamp : 148 * 16);
+        const int64_t items = ceil_div(rows, stride) * ceil_div(cols, 8192);
+        const unsigned blocks = static_cast<unsigned>(items < 148 * 16 ? items : 148 * 16);
         if (src_is_f64) k_max_sampled<double><<<blocks, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, stride, p->maxabs);
         else k_max_sampled<float><<<blocks, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, stride, p->maxabs);
         NB_LAUNCH_CHECK(c);
@@ -973,11 +977,13 @@ k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restri
 // from HBM exactly once as float4, kept in registers for the max / argmax / top-2 scan, the exp-sum and the
 // normalisation, and the probabilities leave as 16-byte stores.  exp is evaluated in fp32 (the logits are fp32
 // tensor-core results; their own error dominates) and widened to the fp64 output type of the reference.
+// Persistent: each CTA walks over rows (stride gridDim.x) and loads the NEXT row's float4s before it starts the
+// reductions of the current one, so the three block-wide phases of a row overlap with the following row's HBM reads.
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
 k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *__restrict__ probs, long long probs_ld,
                    int32_t *__restrict__ labels, float *__restrict__ gap, const int32_t *__restrict__ row_list,
-                   int in_compact) {
+                   int in_compact, long long nrows) {
     constexpr int NV = 4096 / THREADS;  // float4 per thread (covers 16,384 columns)
     constexpr int NW = THREADS / 32;
     __shared__ float s_m1[NW], s_m2[NW];
@@ -985,82 +991,96 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
     __shared__ int s_i1[NW];
     __shared__ float b_m1;
     __shared__ double b_sum;
-    const long long row = row_list ? row_list[blockIdx.x] : blockIdx.x;
-    const float4 *zr = reinterpret_cast<const float4 *>(z + (in_compact ? static_cast<long long>(blockIdx.x) : row) * ld);
     const int nvec = cols >> 2;  // cols % 4 == 0 guaranteed by the launcher
-    float4 v[NV];
-#pragma unroll
-    for (int i = 0; i < NV; i++) {
-        const int q = threadIdx.x + i * THREADS;
-        v[i] = q < nvec ? __ldg(zr + q) : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
-    }
-    float m1 = -CUDART_INF_F, m2 = -CUDART_INF_F;
-    int i1 = 0x7fffffff;
-#pragma unroll
-    for (int i = 0; i < NV; i++) {
-        const int base = (threadIdx.x + i * THREADS) * 4;
-        const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            if (e[j] > m1) { m2 = m1; m1 = e[j]; i1 = base + j; }
-            else if (e[j] > m2) m2 = e[j];
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-        const float om1 = __shfl_xor_sync(0xffffffffu, m1, o), om2 = __shfl_xor_sync(0xffffffffu, m2, o);
-        const int oi1 = __shfl_xor_sync(0xffffffffu, i1, o);
-        if (om1 > m1 || (om1 == m1 && oi1 < i1)) { m2 = fmaxf(m1, om2); m1 = om1; i1 = oi1; }
-        else m2 = fmaxf(m2, om1);
-    }
+    const float4 ninf = make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    if (l == 0) { s_m1[w] = m1; s_m2[w] = m2; s_i1[w] = i1; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float a1 = s_m1[0], a2 = s_m2[0];
-        int ai = s_i1[0];
-        for (int k = 1; k < NW; k++) {
-            const float om1 = s_m1[k], om2 = s_m2[k];
-            const int oi1 = s_i1[k];
-            if (om1 > a1 || (om1 == a1 && oi1 < ai)) { a2 = fmaxf(a1, om2); a1 = om1; ai = oi1; }
-            else a2 = fmaxf(a2, om1);
+    auto load_row = [&](long long it, float4 (&dst)[NV]) {
+        const long long row = row_list ? row_list[it] : it;
+        const float4 *zr = reinterpret_cast<const float4 *>(z + (in_compact ? it : row) * ld);
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            const int q = threadIdx.x + i * THREADS;
+            dst[i] = q < nvec ? __ldg(zr + q) : ninf;
         }
-        b_m1 = a1;
-        if (labels) labels[row] = ai;
-        if (gap) gap[row] = a1 - a2;
-    }
-    __syncthreads();
-    if (!probs) return;
-    const float mx = b_m1;
-    double sum = 0.0;  // summed in fp64 so that the probabilities of a row add up to 1 to fp64 rounding
+    };
+    float4 v[NV], nv[NV];
+    long long it = blockIdx.x;
+    if (it < nrows) load_row(it, v);
+    for (; it < nrows; it += gridDim.x) {
+        const long long row = row_list ? row_list[it] : it;
+        const bool has_next = it + gridDim.x < nrows;
+        if (has_next) load_row(it + gridDim.x, nv);
+        float m1 = -CUDART_INF_F, m2 = -CUDART_INF_F;
+        int i1 = 0x7fffffff;
 #pragma unroll
-    for (int i = 0; i < NV; i++) {  // exp(-inf) = 0 for the out-of-range slots
-        v[i].x = __expf(v[i].x - mx); v[i].y = __expf(v[i].y - mx); v[i].z = __expf(v[i].z - mx); v[i].w = __expf(v[i].w - mx);
-        sum += (static_cast<double>(v[i].x) + static_cast<double>(v[i].y)) + (static_cast<double>(v[i].z) + static_cast<double>(v[i].w));
-    }
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (l == 0) s_sum[w] = sum;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int k = 0; k < NW; k++) t += s_sum[k];
-        b_sum = t;
-    }
-    __syncthreads();
-    const double inv = 1.0 / b_sum;
-    double *pr = probs + row * probs_ld;
-    const bool aligned = ((reinterpret_cast<uintptr_t>(pr) & 15) == 0);
+        for (int i = 0; i < NV; i++) {
+            const int base = (threadIdx.x + i * THREADS) * 4;
+            const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
-    for (int i = 0; i < NV; i++) {
-        const int q = threadIdx.x + i * THREADS;
-        if (q < nvec) {
-            const double a = v[i].x * inv, b = v[i].y * inv, cc = v[i].z * inv, d = v[i].w * inv;
-            if (aligned) {
-                *reinterpret_cast<double2 *>(pr + q * 4) = make_double2(a, b);
-                *reinterpret_cast<double2 *>(pr + q * 4 + 2) = make_double2(cc, d);
-            } else {
-                pr[q * 4] = a; pr[q * 4 + 1] = b; pr[q * 4 + 2] = cc; pr[q * 4 + 3] = d;
+            for (int j = 0; j < 4; j++) {
+                if (e[j] > m1) { m2 = m1; m1 = e[j]; i1 = base + j; }
+                else if (e[j] > m2) m2 = e[j];
             }
         }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float om1 = __shfl_xor_sync(0xffffffffu, m1, o), om2 = __shfl_xor_sync(0xffffffffu, m2, o);
+            const int oi1 = __shfl_xor_sync(0xffffffffu, i1, o);
+            if (om1 > m1 || (om1 == m1 && oi1 < i1)) { m2 = fmaxf(m1, om2); m1 = om1; i1 = oi1; }
+            else m2 = fmaxf(m2, om1);
+        }
+        if (l == 0) { s_m1[w] = m1; s_m2[w] = m2; s_i1[w] = i1; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float a1 = s_m1[0], a2 = s_m2[0];
+            int ai = s_i1[0];
+            for (int k = 1; k < NW; k++) {
+                const float om1 = s_m1[k], om2 = s_m2[k];
+                const int oi1 = s_i1[k];
+                if (om1 > a1 || (om1 == a1 && oi1 < ai)) { a2 = fmaxf(a1, om2); a1 = om1; ai = oi1; }
+                else a2 = fmaxf(a2, om1);
+            }
+            b_m1 = a1;
+            if (labels) labels[row] = ai;
+            if (gap) gap[row] = a1 - a2;
+        }
+        __syncthreads();
+        if (probs) {
+            const float mx = b_m1;
+            double sum = 0.0;  // summed in fp64 so that the probabilities of a row add up to 1 to fp64 rounding
+#pragma unroll
+            for (int i = 0; i < NV; i++) {  // exp(-inf) = 0 for the out-of-range slots
+                v[i].x = __expf(v[i].x - mx); v[i].y = __expf(v[i].y - mx); v[i].z = __expf(v[i].z - mx); v[i].w = __expf(v[i].w - mx);
+                sum += (static_cast<double>(v[i].x) + static_cast<double>(v[i].y)) + (static_cast<double>(v[i].z) + static_cast<double>(v[i].w));
+            }
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (l == 0) s_sum[w] = sum;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double t = 0.0;
+                for (int k = 0; k < NW; k++) t += s_sum[k];
+                b_sum = t;
+            }
+            __syncthreads();
+            const double inv = 1.0 / b_sum;
+            double *pr = probs + row * probs_ld;
+            const bool aligned = ((reinterpret_cast<uintptr_t>(pr) & 15) == 0);
+#pragma unroll
+            for (int i = 0; i < NV; i++) {
+                const int q = threadIdx.x + i * THREADS;
+                if (q < nvec) {
+                    const double a = v[i].x * inv, b = v[i].y * inv, cc = v[i].z * inv, d = v[i].w * inv;
+                    if (aligned) {
+                        *reinterpret_cast<double2 *>(pr + q * 4) = make_double2(a, b);
+                        *reinterpret_cast<double2 *>(pr + q * 4 + 2) = make_double2(cc, d);
+                    } else {
+                        pr[q * 4] = a; pr[q * 4 + 1] = b; pr[q * 4 + 2] = cc; pr[q * 4 + 3] = d;
+                    }
+                }
+            }
+        }
+        __syncthreads();  // b_m1 / b_sum / s_* are reused by the next row
+#pragma unroll
+        for (int i = 0; i < NV; i++) v[i] = nv[i];
     }
 }
 
@@ -1070,10 +1090,9 @@ int launch_softmax_rows(Context *c, const void *logits, bool is_f64, int64_t row
     const int64_t n = row_list ? nrows_list : rows;
     if (n == 0 || cols == 0) return NB200_OK;
     if (!is_f64 && cols <= 16384 && (cols & 3) == 0 && (ld & 3) == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0) {
-        static const int thr = getenv("NB200_SOFTMAX_THREADS") ? atoi(getenv("NB200_SOFTMAX_THREADS")) : 512;
-        if (thr == 1024) k_softmax_rows_reg<1024><<<static_cast<unsigned>(n), 1024, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
-        else if (thr == 256) k_softmax_rows_reg<256><<<static_cast<unsigned>(n), 256, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
-        else k_softmax_rows_reg<512><<<static_cast<unsigned>(n), 512, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact);
+        const int sms = c->sm_count > 0 ? c->sm_count : 148;
+        const unsigned grid = static_cast<unsigned>(n < 2 * sms ? n : 2 * sms);
+        k_softmax_rows_reg<1024><<<grid, 1024, 0, c->stream>>>((const float *)logits, ld, (int)cols, probs, probs_ld, labels, gap, row_list, in_compact, n);
         NB_LAUNCH_CHECK(c);
         return NB200_OK;
     }

@@ -390,3 +390,14 @@ def test_cpp_three_layer_inference(oracle, prec, tmp_path):
     assert np.isfinite(probs).all()
     assert np.array_equal(got[:, 1].astype(np.int32), np.argmax(probs, axis=1))   # argmax of the `output` set read back
     assert np.abs(got[:, 2] - probs[:, 0]).max() <= (1e-9 if prec == "fp64" else 1e-3)
+
+
+def test_wide_hidden_layer_takes_two_kernel_path(nb, oracle):
+    """hidden > 1,024 needs more than two 512-wide N tiles: the fused layer-1 kernel does not apply and the call must
+    fall back to conversion + split-K GEMM (and still match the oracle)."""
+    batch, feat, hid, lab, blk = 2100, 8300, 1100, 16, 500
+    dev, ora, _ = _ff_sets(nb, oracle, batch, feat, hid, lab, blk)
+    _, ref_logits, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=4)
+    _, labels, stats = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PREC_F16)
+    assert np.array_equal(labels, ref_labels) and stats["splits1"] > 1
+    assert rel(nb.DeviceSet.lookup("ff", "__logits").download_dense(), ref_logits.dense()) <= TOL["f16"]
