@@ -235,8 +235,11 @@ struct SmemLayout2 {
     static constexpr uint32_t kTotal = kBarOffset + (2 * STAGES + 1) * 8 + 16 + 1024;
 };
 
-template <int NSUB, int STAGES>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+// MC = true: clusters of 4 = two CTA pairs working on two adjacent M tiles of the SAME N tile; each CTA loads only half of
+// its share of the V tile and multicasts it to its counterpart in the other pair, which halves the V traffic from L2
+// (the L2 -> SM fabric saturates near 9.5 TB/s on this part and bounds the kernels that stream operands).
+template <int NSUB, int STAGES, bool MC>
+__global__ void __cluster_dims__(MC ? 4 : 2, 1, 1) __launch_bounds__(kThreads, 1)
 k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_constant__ CUtensorMap map_u_lo,
                  const __grid_constant__ CUtensorMap map_v_hi, const __grid_constant__ CUtensorMap map_v_lo,
                  const GemmArgs g) {
@@ -251,11 +254,20 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();
+    const uint32_t crank = cluster_ctarank();     // 0..1, or 0..3 with MC
+    const uint32_t rank = crank & 1;              // rank inside the CTA pair
+    const uint32_t pair_in_cluster = crank >> 1;  // 0 without MC
     const bool leader = rank == 0;
-    const int pair = blockIdx.x >> 1;
-    const int tile_m = pair / g.tiles_n;
-    const int tile_n = pair % g.tiles_n;
+    int tile_m, tile_n;
+    if (MC) {
+        const int cl = blockIdx.x >> 2;           // cluster index: (tile_m / 2, tile_n)
+        tile_n = cl % g.tiles_n;
+        tile_m = (cl / g.tiles_n) * 2 + static_cast<int>(pair_in_cluster);
+    } else {
+        const int pair = blockIdx.x >> 1;
+        tile_m = pair / g.tiles_n;
+        tile_n = pair % g.tiles_n;
+    }
     const int split = blockIdx.y + g.split_offset;
     const int kb0 = split * g.kb_per_split;
     const int kb1 = min(kb0 + g.kb_per_split, g.num_kb);
@@ -269,8 +281,8 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
             tma_prefetch_desc(&map_v_lo);
         }
         for (int s = 0; s < STAGES; s++) {
-            mbar_init(&full_bar[s], 2);   // leader's arrive.expect_tx + the peer's remote arrive
-            mbar_init(&empty_bar[s], 1);  // the leader's multicast commit
+            mbar_init(&full_bar[s], 2);            // leader's arrive.expect_tx + the peer's remote arrive
+            mbar_init(&empty_bar[s], MC ? 2 : 1);  // one multicast commit per pair that writes into this CTA's stage
         }
         mbar_init(tmem_full_bar, 1);
         fence_barrier_init();
@@ -298,11 +310,21 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
                 uint8_t *sa = smem + s * L::kStageBytes;
                 uint8_t *sb = sa + kABytes;
                 if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * L::kStageBytes);
-                else mbar_arrive_remote(&full_bar[s], 0);
+                else mbar_arrive_remote(&full_bar[s], crank & ~1u);  // the leader of MY pair
                 tma_load_2d_2sm(mu, &full_bar[s], sa, kb * kBlockK, tile_m * 256 + static_cast<int>(rank) * kBlockM,
                                 kEvictNormal);
-                tma_load_2d_2sm(mv, &full_bar[s], sb, kb * kBlockK, tile_n * BN + static_cast<int>(rank) * (BN / 2),
-                                kEvictLast);
+                if (!MC) {
+                    tma_load_2d_2sm(mv, &full_bar[s], sb, kb * kBlockK, tile_n * BN + static_cast<int>(rank) * (BN / 2),
+                                    kEvictLast);
+                } else {
+                    // my share of V is rows [rank*BN/2, +BN/2); I fetch one half of it (pair 0 the first, pair 1 the second)
+                    // and it lands in my stage and in the stage of the same-rank CTA of the other pair
+                    constexpr int kHalfRows = BN / 4;
+                    const uint16_t mask = static_cast<uint16_t>((1u << rank) | (1u << (rank + 2)));
+                    tma_load_2d_2sm_mc(mv, &full_bar[s], sb + pair_in_cluster * (kHalfRows * kBlockK * 2), kb * kBlockK,
+                                       tile_n * BN + static_cast<int>(rank) * (BN / 2) + static_cast<int>(pair_in_cluster) * kHalfRows,
+                                       mask, kEvictLast);
+                }
             }
         }
     } else if (warp == 1) {
@@ -326,9 +348,11 @@ k_block_gemm_2sm(const __grid_constant__ CUtensorMap map_u_hi, const __grid_cons
                         umma_f16_2sm(tmem_base + sub * 256, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
                     }
                 }
-                umma_commit_2sm(&empty_bar[s], 0x3);  // frees the slot in BOTH CTAs
+                // frees the slot in both CTAs of the pair -- and, with MC, tells the other pair (which writes half of
+                // our V tile) as well
+                umma_commit_2sm(&empty_bar[s], MC ? 0xF : 0x3);
             }
-            umma_commit_2sm(tmem_full_bar, 0x3);
+            umma_commit_2sm(tmem_full_bar, MC ? static_cast<uint16_t>(0x3u << (crank & ~1u)) : 0x3);
         }
     } else {
         // ===== epilogue warps (both CTAs drain their own 128 TMEM lanes) =====
@@ -461,17 +485,17 @@ int choose_splits(Context *c, int M, int N, int64_t ldk, int nterms) {
     return best;
 }
 
-template <int NSUB, int STAGES>
+template <int NSUB, int STAGES, bool MC>
 static int launch_impl_2sm(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
                            const CUtensorMap &mv_lo, const GemmArgs &g, int pair_tiles, int splits, cudaStream_t stream) {
     using L = SmemLayout2<NSUB, STAGES>;
     static bool attr_set = false;
     if (!attr_set) {
-        NB_CUDA(cudaFuncSetAttribute(k_block_gemm_2sm<NSUB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        NB_CUDA(cudaFuncSetAttribute(k_block_gemm_2sm<NSUB, STAGES, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
     }
-    dim3 grid(2 * pair_tiles, splits);
-    k_block_gemm_2sm<NSUB, STAGES><<<grid, kThreads, L::kTotal, stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
+    dim3 grid(2 * pair_tiles, splits);  // with MC pair_tiles is even: clusters of 4 CTAs
+    k_block_gemm_2sm<NSUB, STAGES, MC><<<grid, kThreads, L::kTotal, stream>>>(mu_hi, mu_lo, mv_hi, mv_lo, g);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     return NB200_OK;
@@ -535,7 +559,12 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     const int kind = pick_kernel(M, N, u.ldk);  // 0: 1-SM 128 x {128,256}; 1: 2-SM 256 x 256; 2: 2-SM 256 x 512
     const int BN = kind == 2 ? 512 : (kind == 1 ? 256 : ((N <= 128) ? 128 : 256));
     const int BM = kind == 0 ? kBlockM : 256;
-    const int tiles_m = static_cast<int>(ceil_div(M, BM)), tiles_n = static_cast<int>(ceil_div(N, BN));
+    int tiles_m = static_cast<int>(ceil_div(M, BM));
+    const int tiles_n = static_cast<int>(ceil_div(N, BN));
+    // V-tile multicast across two M tiles (clusters of 4) for the 2-SM kernels whenever there are at least two M tiles
+    static const bool mc_env = !(getenv("NB200_GEMM_MC") && atoi(getenv("NB200_GEMM_MC")) == 0);
+    const bool mc = mc_env && kind != 0 && tiles_m >= 2;
+    if (mc) tiles_m = (tiles_m + 1) & ~1;  // an odd last tile gets an all-padding partner
     const int Mpad = tiles_m * BM, Npad = tiles_n * BN;
     if (Mpad_out) *Mpad_out = Mpad;
     if (Npad_out) *Npad_out = Npad;
@@ -575,7 +604,7 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     const __nv_bfloat16 *v_hi = f16 ? reinterpret_cast<const __nv_bfloat16 *>(v.f16) : v.hi;
 
     CUtensorMap mu_hi, mu_lo, mv_hi, mv_lo;
-    const int v_box = kind == 0 ? BN : BN / 2;  // the 2-SM kernels load half of the V tile per CTA
+    const int v_box = kind == 0 ? BN : (mc ? BN / 4 : BN / 2);  // 2-SM: half of the V tile per CTA; with multicast a quarter
     NB_TRY(make_plane_map(&mu_hi, u_hi, u.rows, u.ldk, kBlockM));
     NB_TRY(make_plane_map(&mv_hi, v_hi, v.rows, v.ldk, v_box));
     if (nterms == 3) {
@@ -594,8 +623,10 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
         if (launch_splits <= 0) return NB200_OK;
     }
     cudaStream_t stream = epi.stream ? epi.stream : c->stream;
-    if (kind == 2) return launch_impl_2sm<2, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
-    if (kind == 1) return launch_impl_2sm<1, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    if (kind == 2 && mc) return launch_impl_2sm<2, 4, true>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    if (kind == 1 && mc) return launch_impl_2sm<1, 6, true>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    if (kind == 2) return launch_impl_2sm<2, 4, false>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
+    if (kind == 1) return launch_impl_2sm<1, 6, false>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
     if (BN == 256) return launch_impl<256, 4>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
     return launch_impl<128, 6>(c, mu_hi, mu_lo, mv_hi, mv_lo, g, tiles_m * tiles_n, launch_splits, stream);
 }

@@ -160,6 +160,17 @@ __device__ __forceinline__ void tma_load_2d_2sm(const CUtensorMap *m, uint64_t *
         "r"(c1), "l"(cache_hint)
         : "memory");
 }
+// the same, multicast: the box also lands (same CTA-relative offset) in every CTA of `cta_mask`, and each destination's
+// pair leader gets the complete_tx on its barrier
+__device__ __forceinline__ void tma_load_2d_2sm_mc(const CUtensorMap *m, uint64_t *bar, void *dst, int c0, int c1,
+                                                   uint16_t cta_mask, uint64_t cache_hint) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint "
+        "[%0], [%1, {%3, %4}], [%2], %5, %6;"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0),
+        "r"(c1), "h"(cta_mask), "l"(cache_hint)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_alloc_2sm(uint32_t *dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
                  "r"(ncols)
