@@ -47,6 +47,13 @@ typedef enum {
                                     on download of the `yo` view so that the device never overflows */
 } nb200_epilogue;
 
+/* Activation of nb200_sum_blocks = enum class SumActivation of the reference (LSTMThreeWaySum.h:12) plus "none". */
+typedef enum {
+    NB200_ACT_NONE = 0,    /* LSTMTwoSum (LSTMTwoSum.h:58-63): plain sum */
+    NB200_ACT_SIGMOID = 1, /* SumActivation::Sigmod: 1 / (1 + exp(-s))          (LSTMThreeWaySum.h:81)    */
+    NB200_ACT_TANH = 2     /* SumActivation::Tanh: (e^s - e^-s) / (e^s + e^-s)  (LSTMThreeWaySum.h:85-86) */
+} nb200_activation;
+
 /* Arithmetic of the block GEMM.  The reference is fp64 end to end (FFMatrixData.h:35-36). */
 typedef enum {
     NB200_PREC_BF16 = 0,   /* one tcgen05 kind::f16 pass, bf16 operands, fp32 TMEM accumulation        */
@@ -138,6 +145,17 @@ int nb200_set_invalidate_planes(nb200_set *s);
  * FFTransposeBiasSum.h:64-67).  `bias` must be (rows of C) x 1 (FFReluBiasSum.h:49-56). */
 int nb200_gemm_blocks(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision,
                       const char *db, const char *out_set, nb200_set **out);
+
+/* LSTMThreeWaySum / LSTMTwoSum (src/LSTM/headers/LSTMThreeWaySum.h:39-95, LSTMTwoSum.h:24-64): the join on equal
+ * (blockRow, blockCol) keys followed by out = act(a + b + c) per element, for whole sets at once.  b and c may be
+ * NULL (c NULL: LSTMTwoSum; both NULL: the activation mapped over a, which is the tanh LSTMHiddenState applies to its
+ * second input, LSTMHiddenState.h:44-47 -- LSTMHiddenState + FFAggMatrix is this call followed by
+ * nb200_gemm_blocks(NB200_OP_NN, o_t, tanh_c_t, ...)).  Shapes and block sizes of all inputs must be equal
+ * ("Block dimemsions mismatch!", LSTMThreeWaySum.h:58-65).  Inputs may be fp64 sets or fp32 results of the
+ * tensor-core GEMM; the sum and the activation are evaluated in fp64 and the result set holds fp64.  Out meta = a's
+ * (LSTMThreeWaySum.h:67-70). */
+int nb200_sum_blocks(nb200_set *a, nb200_set *b, nb200_set *c, int activation, const char *db, const char *out_set,
+                     nb200_set **out);
 
 /* FFRowAggregate + FFOutputLayer (FFRowAggregate.h:11-29, FFMatrixBlock.h:116-142,
  * FFOutputLayer.h:31-57 intended form) on a set of pre-exp logits (batch x labels):

@@ -45,6 +45,7 @@ HOST = os.path.join(HERE, "host")
 HOST_BIN = os.path.join(HOST, "bin")
 HOST_SRCS = [os.path.join(HOST, "src", f) for f in ("SimpleFF.cc", "FFMatrixUtil.cc")]
 REF_DRIVER = "/root/reference/src/tests/source/FFTest.cc"
+REF_LSTM_DRIVER = "/root/reference/src/tests/source/LSTMTest.cc"
 
 
 def build_host(force: bool = False) -> dict:
@@ -52,16 +53,19 @@ def build_host(force: bool = False) -> dict:
 
     FFTest          our driver in the shape of the reference's (adds a label dump for the parity tests)
     FFTest_netsdb   the reference's own, UNMODIFIED src/tests/source/FFTest.cc compiled in place against the
-                    shim headers (only where /root/reference exists; the binary travels to the GPU box)."""
+                    shim headers (only where /root/reference exists; the binary travels to the GPU box).
+    LSTMTest / LSTMTest_netsdb   the same pair for the LSTM cell (src/tests/source/LSTMTest.cc)."""
     build()
     os.makedirs(HOST_BIN, exist_ok=True)
     inc = ["-I" + os.path.join(HERE, "..", "include"), "-I" + os.path.join(HOST, "include")]
     common = ["/usr/bin/g++", "-std=c++17", "-O2", "-ffp-contract=off", *inc]
     link = ["-L" + HERE, "-lnetsdb_b200", "-Wl,-rpath,$ORIGIN/../.."]
     out = {}
-    targets = [("FFTest", os.path.join(HOST, "src", "FFTest.cc"))]
+    targets = [("FFTest", os.path.join(HOST, "src", "FFTest.cc")), ("LSTMTest", os.path.join(HOST, "src", "LSTMTest.cc"))]
     if os.path.exists(REF_DRIVER):
         targets.append(("FFTest_netsdb", REF_DRIVER))
+    if os.path.exists(REF_LSTM_DRIVER):
+        targets.append(("LSTMTest_netsdb", REF_LSTM_DRIVER))
     for name, main_src in targets:
         exe = os.path.join(HOST_BIN, name)
         deps = [main_src, *HOST_SRCS, LIB] + [os.path.join(HOST, "include", f) for f in os.listdir(os.path.join(HOST, "include"))]

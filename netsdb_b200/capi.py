@@ -28,7 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
-    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks",
 ]
 
 
@@ -83,6 +83,7 @@ def lib():
         L.nb200_set_rename.argtypes = [vp, C.c_char_p, C.c_char_p]
         L.nb200_gemm_blocks.argtypes = [i, vp, vp, i, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_softmax_rows.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(vp), vp]
+        L.nb200_sum_blocks.argtypes = [vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_ff_inference_unit.argtypes = [vp, vp, vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp), vp,
                                               C.POINTER(FFStats)]
         L.nb200_conv2d_image_flat.argtypes = [vp, i, i, i, i, i, i, i, i, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
@@ -215,6 +216,17 @@ def gemm_blocks(op: int, a: DeviceSet, b: DeviceSet, epilogue: int, bias: Device
     p = C.c_void_p()
     check(lib().nb200_gemm_blocks(op, a.ptr, b.ptr, epilogue, bias.ptr if bias else None, precision, _b(db),
                                   _b(out_set), C.byref(p)))
+    return DeviceSet(p)
+
+
+ACT_NONE, ACT_SIGMOID, ACT_TANH = 0, 1, 2
+
+
+def sum_blocks(a: DeviceSet, b: DeviceSet | None, c: DeviceSet | None, activation: int, db: str, out_set: str) -> DeviceSet:
+    """LSTMThreeWaySum / LSTMTwoSum / activation map (nb200_sum_blocks)."""
+    p = C.c_void_p()
+    check(lib().nb200_sum_blocks(a.ptr, b.ptr if b else None, c.ptr if c else None, activation, _b(db), _b(out_set),
+                                 C.byref(p)))
     return DeviceSet(p)
 
 

@@ -530,13 +530,18 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
         return NB200_ERR_INVALID;
     }
     // join predicate + per-pair dimension check (FFTransposeMult.h:38-39,61-65; FFInputLayerJoin.h:30-31,57-60)
-    const int K = a->total_cols;
+    const int Ka = a->total_cols;
     const int Kb = (op == NB200_OP_NT) ? b->total_cols : b->total_rows;
     const int bkA = a->block_cols, bkB = (op == NB200_OP_NT) ? b->block_cols : b->block_rows;
-    if (K != Kb || bkA != bkB) {
-        set_error("Block dimemsions mismatch! (K %d vs %d, block K %d vs %d)", K, Kb, bkA, bkB);
+    if (bkA != bkB) {  // the per-pair check of the projection lambda
+        set_error("Block dimemsions mismatch! (block K %d vs %d)", bkA, bkB);
         return NB200_ERR_SHAPE;
     }
+    // Total K extents may differ: the join simply finds no partner for the surplus column blocks of the longer
+    // operand (src/tests/source/LSTMTest.cc:470-480 multiplies a 128 x 500 set with a 128 x 500 set this way), and
+    // inside the last matched block the shorter operand's zero padding cancels the rest: the contraction runs over
+    // k < min(Ka, Kb).
+    const int K = Ka < Kb ? Ka : Kb;
     const int I = a->total_rows, J = (op == NB200_OP_NT) ? b->total_rows : b->total_cols;
     const int bI = a->block_rows, bJ = (op == NB200_OP_NT) ? b->block_rows : b->block_cols;
     if (epilogue != NB200_EPI_NONE) NB_TRY(bias_check(bias, I, epilogue == NB200_EPI_BIAS_RELU ? "ReluBiasSum" : "TransposeBiasSum"));
@@ -593,7 +598,7 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
     const Planes &V = transpose_out ? pa : pb;
     const int M = o->total_rows, N = o->total_cols;
     if (M == 0 || N == 0) { *out = o; return NB200_OK; }
-    const int splits = choose_splits(c, M, N, U.ldk, nterms);
+    const int splits = choose_splits(c, M, N, U.ldk < V.ldk ? U.ldk : V.ldk, nterms);
     int Mpad = 0, Npad = 0;
     if (splits == 1) {
         GemmEpilogue ge;
@@ -619,6 +624,45 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
 int nb200_gemm_blocks(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision, const char *db,
                       const char *out_set, nb200_set **out) {
     return gemm_blocks_impl(op, a, b, epilogue, bias, precision, db, out_set, out, 0);
+}
+
+int nb200_sum_blocks(nb200_set *a, nb200_set *b, nb200_set *cc, int activation, const char *db, const char *out_set,
+                     nb200_set **out) {
+    NEED_CTX();
+    if (!a || (!b && cc) || !db || !out_set || !out || activation < NB200_ACT_NONE || activation > NB200_ACT_TANH) {
+        set_error("sum_blocks: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    nb200_set *in[3] = {a, b, cc};
+    EwiseSrc src[3];
+    int nsrc = 0;
+    for (int i = 0; i < 3 && in[i]; i++, nsrc++) {
+        nb200_set *s = in[i];
+        if (s->view_of) { set_error("sum_blocks: %s:%s is a view", s->db.c_str(), s->name.c_str()); return NB200_ERR_INVALID; }
+        if (s->total_rows != a->total_rows || s->total_cols != a->total_cols || s->block_rows != a->block_rows ||
+            s->block_cols != a->block_cols) {
+            set_error("Block dimemsions mismatch! (%d x %d in blocks of %d x %d vs %d x %d in blocks of %d x %d)", a->total_rows,
+                      a->total_cols, a->block_rows, a->block_cols, s->total_rows, s->total_cols, s->block_rows, s->block_cols);
+            return NB200_ERR_SHAPE;
+        }
+        if (s->f64) src[i] = EwiseSrc{s->f64, nullptr, s->total_cols};
+        else if (s->f32) src[i] = EwiseSrc{nullptr, s->f32, s->f32_ld};
+        else { set_error("sum_blocks: set %s:%s holds no data", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
+    }
+    // the output may replace one of the inputs (same db:name): compute into fresh storage, then swap it in
+    const size_t n = static_cast<size_t>(a->total_rows) * a->total_cols;
+    double *res = nullptr;
+    NB_CUDA(cudaMalloc(&res, (n ? n : 1) * sizeof(double)));
+    const int tr = a->total_rows, tc = a->total_cols, br = a->block_rows, bc = a->block_cols;
+    int st = launch_sum_blocks(c, src, nsrc, activation, tr, tc, res);
+    if (st != NB200_OK) { cudaFree(res); return st; }
+    NB_CUDA(cudaStreamSynchronize(c->stream));  // make_set below may free an input that is being replaced
+    nb200_set *o = nullptr;
+    st = make_set(db, out_set, tr, tc, br, bc, &o);
+    if (st != NB200_OK) { cudaFree(res); return st; }
+    o->f64 = res;
+    *out = o;
+    return NB200_OK;
 }
 
 int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, nb200_set **out, int32_t *labels_host) {

@@ -547,16 +547,19 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
         set_error("block GEMM: fp16 operands missing (or asked for a split-precision pass)");
         return NB200_ERR_STATE;
     }
-    if ((!f16 && (!u.valid || !v.valid)) || u.ldk != v.ldk || u.ldk % kBlockK != 0) {
-        set_error("block GEMM: operand planes missing or K pitch mismatch (%lld vs %lld)", (long long)u.ldk,
+    if ((!f16 && (!u.valid || !v.valid)) || u.ldk % kBlockK != 0 || v.ldk % kBlockK != 0) {
+        set_error("block GEMM: operand planes missing or K pitch not a multiple of %d (%lld, %lld)", kBlockK, (long long)u.ldk,
                   (long long)v.ldk);
         return NB200_ERR_STATE;
     }
+    // operands whose K extents differ (a join that matches only the leading column blocks, see gemm_blocks): the
+    // planes are zero beyond their own extent, so the product over the shorter pitch is the product over min(Ka, Kb)
+    const int64_t ldk_eff = u.ldk < v.ldk ? u.ldk : v.ldk;
     if (nterms == 3 && (!u.lo_valid || !v.lo_valid)) {
         set_error("block GEMM: BF16X3 needs the residual planes");
         return NB200_ERR_STATE;
     }
-    const int kind = pick_kernel(M, N, u.ldk);  // 0: 1-SM 128 x {128,256}; 1: 2-SM 256 x 256; 2: 2-SM 256 x 512
+    const int kind = pick_kernel(M, N, ldk_eff);  // 0: 1-SM 128 x {128,256}; 1: 2-SM 256 x 256; 2: 2-SM 256 x 512
     const int BN = kind == 2 ? 512 : (kind == 1 ? 256 : ((N <= 128) ? 128 : 256));
     const int BM = kind == 0 ? kBlockM : 256;
     int tiles_m = static_cast<int>(ceil_div(M, BM));
@@ -568,7 +571,7 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     const int Mpad = tiles_m * BM, Npad = tiles_n * BN;
     if (Mpad_out) *Mpad_out = Mpad;
     if (Npad_out) *Npad_out = Npad;
-    const int num_kb = static_cast<int>(u.ldk / kBlockK);
+    const int num_kb = static_cast<int>(ldk_eff / kBlockK);
     if (splits < 1) splits = 1;
     if (splits > num_kb) splits = num_kb > 0 ? num_kb : 1;
     int per = static_cast<int>(ceil_div(num_kb, splits));

@@ -154,6 +154,12 @@ int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_
                                Planes *p);
 int launch_transpose_f32(Context *c, const float *src, int64_t rows, int64_t cols, int64_t ld, float *dst, int64_t dld);
 int launch_f64_to_f32(Context *c, const double *src, int64_t n, float *dst);
+struct EwiseSrc {  // one operand of an element-wise kernel: fp64 or fp32 storage with a row pitch
+    const double *d;
+    const float *f;
+    long long ld;
+};
+int launch_sum_blocks(Context *c, const EwiseSrc *src, int nsrc, int act, int64_t rows, int64_t cols, double *out);
 int launch_bias_relu_f32(Context *c, float *p, int64_t rows, int64_t cols, int64_t ld, const float *bias_n);
 int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
                       int64_t row_offset, int64_t total_cols);

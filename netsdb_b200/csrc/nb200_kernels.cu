@@ -603,6 +603,45 @@ int launch_f64_to_f32(Context *c, const double *src, int64_t n, float *dst) {
     return NB200_OK;
 }
 
+// LSTMThreeWaySum / LSTMTwoSum (src/LSTM/headers/LSTMThreeWaySum.h:76-95, LSTMTwoSum.h:58-63): out = act(a + b + c),
+// element-wise over equally shaped sets; every source is fp64 or fp32 (results of the tensor-core GEMMs), the sum and
+// the activation are evaluated in fp64 with the reference's own formulas.  HBM-bound: (8 or 4) x sources + 8 bytes
+// per element.
+__device__ __forceinline__ double ew_load(const EwiseSrc &s, long long r, long long c) {
+    return s.d ? s.d[r * s.ld + c] : static_cast<double>(s.f[r * s.ld + c]);
+}
+__global__ void __launch_bounds__(256)
+k_sum_blocks(EwiseSrc a, EwiseSrc b, EwiseSrc c, int nsrc, int act, long long rows, long long cols, double *__restrict__ out) {
+    const long long n = rows * cols;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / cols, col = i - r * cols;
+        double sum = ew_load(a, r, col);
+        if (nsrc > 1) sum = sum + ew_load(b, r, col);
+        if (nsrc > 2) sum = sum + ew_load(c, r, col);
+        double v = sum;
+        if (act == NB200_ACT_SIGMOID) {
+            v = 1.0 / (1.0 + exp(-1.0 * sum));                       // LSTMThreeWaySum.h:81
+        } else if (act == NB200_ACT_TANH) {
+            // :85-86 (exp(s) - exp(-s)) / (exp(s) + exp(-s)); that quotient is inf/inf beyond |s| = 709, where the
+            // function it spells is +-1
+            if (fabs(sum) > 350.0) v = copysign(1.0, sum);
+            else { const double ep = exp(sum), em = exp(-1.0 * sum); v = (ep - em) / (ep + em); }
+        }
+        out[i] = v;
+    }
+}
+int launch_sum_blocks(Context *c, const EwiseSrc *src, int nsrc, int act, int64_t rows, int64_t cols, double *out) {
+    const int64_t n = rows * cols;
+    if (n == 0) return NB200_OK;
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < sms * 8 ? ceil_div(n, 256) : sms * 8);
+    EwiseSrc z{};
+    k_sum_blocks<<<blocks, 256, 0, c->stream>>>(src[0], nsrc > 1 ? src[1] : z, nsrc > 2 ? src[2] : z, nsrc, act, rows, cols, out);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
 // Seeded generator; the test suite's CPU generator is defined to match it bit for bit (explicit _rn intrinsics
 // keep the compiler from contracting the multiply-add, which would change the rounding).
 __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {

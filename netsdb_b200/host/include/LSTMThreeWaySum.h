@@ -1,0 +1,3 @@
+// LSTMThreeWaySum.h -- same header name as src/LSTM/headers/LSTMThreeWaySum.h; the class lives in lstm_udfs.h
+#pragma once
+#include "lstm_udfs.h"

@@ -84,8 +84,14 @@ public:
     template <class T>
     bool sendData(std::pair<std::string, std::string> setAndDatabase, Handle<Vector<Handle<T>>> data, std::string &errMsg) {
         const std::string &set = setAndDatabase.first, &db = setAndDatabase.second;
+        int tr = 0, tc = 0;  // extents of the block grid, for blocks whose meta carry no totals
+        for (size_t i = 0; i < data->size(); i++) {
+            Handle<T> &b = (*data)[i];
+            tr = std::max(tr, (b->getBlockRowIndex() + 1) * b->getRowNums());
+            tc = std::max(tc, (b->getBlockColIndex() + 1) * b->getColNums());
+        }
         for (size_t i = 0; i < data->size(); i++)
-            if (!ok(nb200_host::ship_block(db, set, (*data)[i]), errMsg)) return false;
+            if (!ok(nb200_host::ship_block(db, set, (*data)[i], tr, tc), errMsg)) return false;
         return ok(nb200_synchronize(), errMsg);  // the caller reuses its allocation block after sendData
     }
 

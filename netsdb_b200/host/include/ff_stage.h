@@ -7,6 +7,8 @@
 //   FFAggMatrix(FFTransposeMult|FFInputLayerJoin(a, b))                          -> one block GEMM
 //   FFReluBiasSum(FFAggMatrix(join), bias) / FFTransposeBiasSum(..., bias)       -> the same GEMM with the bias join fused
 //   FFOutputLayer(x, FFRowAggregate(x))                                          -> row softmax
+//   LSTMThreeWaySum(x, y, z) / LSTMTwoSum(x, y)                                  -> one element-wise kernel
+//   FFAggMatrix(LSTMHiddenState(o, c))                                           -> tanh map + block GEMM
 //   the whole graph of ff::inference_unit (SimpleFF.cc:340-389)                  -> the fused stage with the
 //                                                                                   label-exact precision cascade
 // Anything else is rejected: there is no CPU fallback.
@@ -14,7 +16,7 @@
 #include <set>
 #include <sstream>
 
-#include "ff_udfs.h"
+#include "lstm_udfs.h"
 
 namespace nb200_host {
 
@@ -39,11 +41,17 @@ inline void ensure_init() {
 }
 
 // sendData for one FFMatrixBlock: the device set is created from the first block's meta
-inline int ship_block(const std::string &db, const std::string &set, pdb::Handle<FFMatrixBlock> &b) {
+// total_rows / total_cols: extents to use when the block's meta leaves them at -1 (LSTMTest.cc:63-110 builds its blocks
+// with the 4-argument constructor); the caller derives them from the block grid, i.e. the set is carried with its
+// padding, exactly as the reference carries it
+inline int ship_block(const std::string &db, const std::string &set, pdb::Handle<FFMatrixBlock> &b, int total_rows = -1,
+                      int total_cols = -1) {
     nb200_set *s = nullptr;
     if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) {
         // nominal block size = size of the first block sent (block (0,0) in ff::loadMatrix's order)
-        int st = nb200_set_create(db.c_str(), set.c_str(), b->getTotalRowNums(), b->getTotalColNums(), b->getRowNums(),
+        const int tr = b->getTotalRowNums() >= 0 ? b->getTotalRowNums() : total_rows;
+        const int tc = b->getTotalColNums() >= 0 ? b->getTotalColNums() : total_cols;
+        int st = nb200_set_create(db.c_str(), set.c_str(), tr, tc, b->getRowNums(),
                                   b->getColNums(), &s);
         if (st != NB200_OK) return st;
     }
@@ -115,9 +123,14 @@ private:
         pdb::Handle<pdb::Computation> join = agg->getIthInput(0);
         int op;
         if (as<FFTransposeMult>(join)) op = NB200_OP_NT;
-        else if (as<FFInputLayerJoin>(join)) op = NB200_OP_NN;
+        else if (as<FFInputLayerJoin>(join) || as<LSTMHiddenState>(join)) op = NB200_OP_NN;
         else throw std::runtime_error("FFAggMatrix over an unsupported join (no CPU fallback)");
         nb200_set *a = eval(join->getIthInput(0), db, ""), *b = eval(join->getIthInput(1), db, "");
+        if (as<LSTMHiddenState>(join)) {  // tanh of the second input (LSTMHiddenState.h:44-47), into a temporary: the
+            nb200_set *t = nullptr;       // reference overwrites its input page, which is not reproduced
+            check(nb200_sum_blocks(b, nullptr, nullptr, NB200_ACT_TANH, db.c_str(), tmp().c_str(), &t));
+            b = t;
+        }
         nb200_set *c = nullptr;
         check(nb200_gemm_blocks(op, a, b, epilogue, bias, precision_from_env(), db.c_str(), out.c_str(), &c));
         return c;
@@ -138,6 +151,20 @@ private:
             nb200_set *view = nullptr;
             check(nb200_set_exp_view(z, db.c_str(), out.c_str(), &view));  // the reference's yo holds exp(.)
             return view;
+        }
+        if (auto *s3 = as<LSTMThreeWaySum>(c)) {
+            nb200_set *x = eval(c->getIthInput(0), db, ""), *y = eval(c->getIthInput(1), db, ""), *z = eval(c->getIthInput(2), db, "");
+            nb200_set *o = nullptr;
+            const int act = s3->modifier == SumActivation::Sigmod ? NB200_ACT_SIGMOID
+                            : s3->modifier == SumActivation::Tanh ? NB200_ACT_TANH : -1;  // "Invalid modifier!" (:92-94)
+            check(nb200_sum_blocks(x, y, z, act, db.c_str(), out.c_str(), &o));
+            return o;
+        }
+        if (as<LSTMTwoSum>(c)) {
+            nb200_set *x = eval(c->getIthInput(0), db, ""), *y = eval(c->getIthInput(1), db, "");
+            nb200_set *o = nullptr;
+            check(nb200_sum_blocks(x, y, nullptr, NB200_ACT_NONE, db.c_str(), out.c_str(), &o));
+            return o;
         }
         if (as<FFOutputLayer>(c)) {
             auto *ra = as<FFRowAggregate>(c->getIthInput(1));

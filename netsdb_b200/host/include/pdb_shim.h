@@ -18,6 +18,7 @@
 // graphs of this path to calls into the CUDA library (ff_stage.h) and rejects anything else.
 #pragma once
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -131,6 +132,12 @@ template <class In1, class In2, class F> auto makeLambda(Handle<In1> a, Handle<I
     l.keep = std::make_shared<F>(std::move(f));
     return l;
 }
+template <class In1, class In2, class In3, class F>
+auto makeLambda(Handle<In1> a, Handle<In2> b, Handle<In3> c, F f) -> Lambda<decltype(f(a, b, c))> {
+    Lambda<decltype(f(a, b, c))> l("native_lambda");
+    l.keep = std::make_shared<F>(std::move(f));
+    return l;
+}
 #define makeLambdaFromMethod(VAR, METHOD) \
     (::pdb::Lambda<typename std::decay<decltype((VAR)->METHOD())>::type>(std::string("methodCall(") + #METHOD + ")"))
 #define makeLambdaFromMember(VAR, MEMBER) \
@@ -163,8 +170,17 @@ private:
     std::vector<Handle<Computation>> inputs;
 };
 
-template <class Out, class In1, class In2>
+// JoinComp<Out, In1, In2[, In3]> (lambdas/headers/JoinComp.h:44-45: up to five inputs there; the drivers of this
+// path use two and, for LSTMThreeWaySum, three)
+template <class Out, class In1, class In2, class In3 = void>
 class JoinComp : public Computation {
+public:
+    std::string getComputationType() override { return "JoinComp"; }
+    virtual Lambda<bool> getSelection(Handle<In1> in1, Handle<In2> in2, Handle<In3> in3) = 0;
+    virtual Lambda<Handle<Out>> getProjection(Handle<In1> in1, Handle<In2> in2, Handle<In3> in3) = 0;
+};
+template <class Out, class In1, class In2>
+class JoinComp<Out, In1, In2, void> : public Computation {
 public:
     std::string getComputationType() override { return "JoinComp"; }
     virtual Lambda<bool> getSelection(Handle<In1> in1, Handle<In2> in2) = 0;

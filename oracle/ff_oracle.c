@@ -515,6 +515,56 @@ nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_s
     return out;
 }
 
+/* ------------------------------------------------------------------ LSTM ----------------- */
+/* The two activations as LSTMThreeWaySum.h:79-90 writes them. */
+static double lstm_act(double s, int activation) {
+    if (activation == 1) return 1 / (1 + exp(-1 * s));                                /* Sigmod, :81 */
+    if (activation == 2) return (exp(s) - exp(-1 * s)) / (exp(s) + exp(-1 * s));      /* Tanh, :85-86 */
+    return s;                                                                         /* LSTMTwoSum.h:62 */
+}
+
+/* LSTMThreeWaySum (LSTMThreeWaySum.h:39-42 predicate: the three FFMatrixMeta keys are equal, i.e. same block row
+ * and column, FFMatrixMeta.h:34-37; :58-65 block dimensions must agree; :67-70 out meta = in1's; :76-95 the sum and
+ * its activation over the whole padded block) and, with c == NULL and activation 0, LSTMTwoSum (LSTMTwoSum.h:24-27
+ * same predicate on two inputs, :38-64).  With a alone it maps the activation over a set (the in-place tanh of
+ * LSTMHiddenState.h:44-47). */
+nbo_set *nbo_lstm_sum(const nbo_set *a, const nbo_set *b, const nbo_set *c, int activation) {
+    nbo_set *out = nbo_set_new();
+    for (int x = 0; x < a->n; x++) {
+        const nbo_block *ba = &a->blocks[x];
+        const nbo_block *bb = b ? nbo_set_find(b, ba->block_row, ba->block_col) : NULL;
+        const nbo_block *bc = c ? nbo_set_find(c, ba->block_row, ba->block_col) : NULL;
+        if ((b && !bb) || (c && !bc)) continue;                       /* inner join: no partner, no output */
+        if ((bb && (bb->rows != ba->rows || bb->cols != ba->cols)) || (bc && (bc->rows != ba->rows || bc->cols != ba->cols))) {
+            fprintf(stderr, "Block dimemsions mismatch!\n");
+            nbo_set_free(out);
+            return NULL;
+        }
+        nbo_block *o = set_add(out, ba->block_row, ba->block_col, ba->rows, ba->cols, ba->total_rows, ba->total_cols);
+        const size_t n = (size_t)ba->rows * ba->cols;
+        for (size_t i = 0; i < n; i++) {
+            double sum = ba->data[i];
+            if (bb) sum = sum + bb->data[i];
+            if (bc) sum = sum + bc->data[i];
+            o->data[i] = lstm_act(sum, activation);
+        }
+    }
+    return out;
+}
+
+/* LSTMHiddenState (LSTMHiddenState.h:24-27 predicate in1.blockCol == in2.blockRow; :44-47 tanh over every element
+ * of in2, padding included (tanh(0) = 0); :49-62 out = in1 * tanh(in2); out meta :35-38) followed by FFAggMatrix
+ * (LSTMTest.cc:538-543).  The reference overwrites in2's page in place and says so ("Does this modify the data if
+ * used elsewhere?"); a block probed by several in1 blocks would then be tanh'ed more than once.  The oracle rules
+ * for the intended single application and leaves in2 untouched (quirk Q8 in DESIGN.md). */
+nbo_set *nbo_lstm_hidden_state_agg(const nbo_set *o_t, const nbo_set *c_t, int threads) {
+    nbo_set *t = nbo_lstm_sum(c_t, NULL, NULL, 2);
+    if (!t) return NULL;
+    nbo_set *out = nbo_input_layer_join_agg(o_t, t, threads);
+    nbo_set_free(t);
+    return out;
+}
+
 /* ------------------------------------------------------------------ conv2d --------------- */
 
 /* Image::get_win_value (Image.h:36-57); h_slides/v_slides integer division (Image.h:26-32). */

@@ -94,6 +94,14 @@ nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_s
                                const nbo_set *b1, const nbo_set *bo, int threads,
                                nbo_set **logits_out, int32_t *labels);
 
+/* ---- LSTM cell operators (src/LSTM/headers, wired by src/tests/source/LSTMTest.cc:204-543) -------------- */
+/* LSTMThreeWaySum (LSTMThreeWaySum.h:39-95): out = act(a + b + c) per block with equal (blockRow, blockCol);
+ * activation 1 = Sigmod, 2 = Tanh (enum SumActivation, :12), 0 = none.  c == NULL: LSTMTwoSum (LSTMTwoSum.h:24-64).
+ * b == c == NULL: the activation mapped over a (the tanh of LSTMHiddenState.h:44-47). */
+nbo_set *nbo_lstm_sum(const nbo_set *a, const nbo_set *b, const nbo_set *c, int activation);
+/* LSTMHiddenState (LSTMHiddenState.h:24-62) + FFAggMatrix: out(i,j) = sum_k o_t(i,k) * tanh(c_t)(k,j). */
+nbo_set *nbo_lstm_hidden_state_agg(const nbo_set *o_t, const nbo_set *c_t, int threads);
+
 /* ---- conv2d_memory_fusion -------------------------------------------------------------- */
 /* Image -> image_flat: Image.h:26-57, ImageToChunks.h:43-102, ImageChunksToBlock.h:35-50,
  * ImageBlockToMatrix.h:46-73.  images: n x c x h x w row-major.  Row = img * windows + win,

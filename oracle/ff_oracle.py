@@ -66,6 +66,10 @@ def lib():
         L.nbo_transpose_bias_sum.argtypes = [vp, vp, i]
         L.nbo_row_aggregate.restype = vp
         L.nbo_row_aggregate.argtypes = [vp]
+        L.nbo_lstm_sum.restype = vp
+        L.nbo_lstm_sum.argtypes = [vp, vp, vp, i]
+        L.nbo_lstm_hidden_state_agg.restype = vp
+        L.nbo_lstm_hidden_state_agg.argtypes = [vp, vp, i]
         L.nbo_ff_inference_unit.restype = vp
         L.nbo_ff_inference_unit.argtypes = [vp, vp, vp, vp, vp, i, C.POINTER(vp), C.POINTER(C.c_int32)]
         L.nbo_image_flat.restype = vp
@@ -168,6 +172,69 @@ def ff_inference_unit(w1, wo, inputs, b1, bo, threads=1):
     out = lib().nbo_ff_inference_unit(w1.ptr, wo.ptr, inputs.ptr, b1.ptr, bo.ptr, threads, C.byref(logits),
                                       labels.ctypes.data_as(C.POINTER(C.c_int32)))
     return BlockSet(out), BlockSet(logits.value), labels
+
+
+SIGMOID, TANH = 1, 2  # enum SumActivation (LSTMThreeWaySum.h:12)
+
+
+def lstm_sum(a: BlockSet, b: BlockSet = None, c: BlockSet = None, activation: int = 0) -> BlockSet:
+    """LSTMThreeWaySum / LSTMTwoSum / activation map."""
+    return BlockSet(lib().nbo_lstm_sum(a.ptr, b.ptr if b is not None else None, c.ptr if c is not None else None, activation))
+
+
+def lstm_hidden_state_agg(o_t: BlockSet, c_t: BlockSet, threads=1) -> BlockSet:
+    return BlockSet(lib().nbo_lstm_hidden_state_agg(o_t.ptr, c_t.ptr, threads))
+
+
+def lstm_cell(p: dict, threads=1) -> dict:
+    """One LSTM step as src/tests/source/LSTMTest.cc wires it (:204-543).  p maps the reference's set names
+    (w_f u_f b_f w_i u_i b_i w_o u_o b_o w_c u_c b_c x_t h_t_1 c_t_1) to BlockSets; returns the sets the driver
+    writes: f_t i_t o_t c_t_temp c_t h_t.  Note that the driver combines gates and states with FFInputLayerJoin,
+    i.e. as matrix products (:470-510), not element-wise."""
+    def gate(w, u, b, act):
+        wx = input_layer_join_agg(p[w], p["x_t"], threads)        # :213-225
+        uh = input_layer_join_agg(p[u], p["h_t_1"], threads)      # :227-238
+        return lstm_sum(wx, uh, p[b], act)                         # :240-247
+    r = {}
+    r["f_t"] = gate("w_f", "u_f", "b_f", SIGMOID)
+    r["i_t"] = gate("w_i", "u_i", "b_i", SIGMOID)                 # :278-312
+    r["o_t"] = gate("w_o", "u_o", "b_o", SIGMOID)                 # :343-377
+    r["c_t_temp"] = gate("w_c", "u_c", "b_c", TANH)               # :408-440
+    fc = input_layer_join_agg(r["f_t"], p["c_t_1"], threads)      # :470-480
+    ic = input_layer_join_agg(r["i_t"], r["c_t_temp"], threads)   # :482-494
+    r["c_t"] = lstm_sum(fc, ic)                                   # :496-498 LSTMTwoSum
+    r["h_t"] = lstm_hidden_state_agg(r["o_t"], r["c_t"], threads)  # :528-543
+    return r
+
+
+def lstm_cell_numpy(d: dict, block: int = 0) -> dict:
+    """Dense fp64 evaluation of the same step (independent cross-check).
+
+    block = 0: zero-padding semantics -- a join of a (I x Ka) with b (Kb x J) keeps the matching block
+    columns/rows only, which with zero padding is the product over k < min(Ka, Kb).  This is what the reference
+    computes whenever every extent is a multiple of the block size.
+    block > 0: the reference as written for ragged extents -- every set is carried padded to whole blocks and
+    LSTMThreeWaySum applies its activation to the padding too (LSTMThreeWaySum.h:76-95 loops over I*J of the padded
+    block), so sigmoid(0) = 0.5 appears in the padding of f_t, i_t, o_t and leaks into c_t and h_t through the
+    products (quirk Q9)."""
+    def pad(a):
+        if not block:
+            return a
+        r, c = (-a.shape[0]) % block, (-a.shape[1]) % block
+        return np.pad(a, ((0, r), (0, c)))
+    def mm(a, b):
+        k = min(a.shape[1], b.shape[0])
+        return a[:, :k] @ b[:k, :]
+    sig = lambda s: 1.0 / (1.0 + np.exp(-s))
+    e = {k: pad(v) for k, v in d.items()}
+    r = {}
+    for g, act in (("f", sig), ("i", sig), ("o", sig), ("c", np.tanh)):
+        s = mm(e["w_" + g], e["x_t"]) + mm(e["u_" + g], e["h_t_1"]) + e["b_" + g]
+        r[{"f": "f_t", "i": "i_t", "o": "o_t", "c": "c_t_temp"}[g]] = act(s)
+    r["c_t"] = mm(r["f_t"], e["c_t_1"]) + mm(r["i_t"], r["c_t_temp"])
+    r["h_t"] = mm(r["o_t"], np.tanh(r["c_t"]))
+    L, B = d["b_f"].shape
+    return {k: v[:L, :B] for k, v in r.items()}
 
 
 def image_flat(images: np.ndarray, k: int, stride: int, padding: int, block_rows: int, block_cols: int) -> BlockSet:
