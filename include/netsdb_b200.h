@@ -208,6 +208,13 @@ int nb200_conv2d_fused(const double *images_host, int n, int c, int h, int w, co
                        const double *bias_host, int kout, int k, int padding, int relu, int precision,
                        int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out);
 
+/* ConvResultToChunks + ConvChunksToImage (ConvResultToChunks.h:42-103, ConvChunksToImage.h:34-72; the last two
+ * jobs of Conv2dMemFuseTest.cc): re-assemble the `result` matrix [(image, window), channel] into num_images images of
+ * z channels, each an x * y matrix in window order.  images_host receives num_images * z * x * y doubles (NCHW).
+ * The result set's rows must divide evenly among the images (the reference asserts it, :46) and x * y must equal
+ * that quotient; channels beyond the set's columns (z > total columns) are zero. */
+int nb200_conv2d_result_to_images(nb200_set *result, int num_images, int x, int y, int z, double *images_host);
+
 /* ---- allocation-free variant ----------------------------------------------------------------------
  * This entry point has no counterpart in the reference.
  *

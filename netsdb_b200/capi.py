@@ -28,7 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
-    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images",
 ]
 
 
@@ -90,6 +90,7 @@ def lib():
         L.nb200_conv2d_kernel_flat.argtypes = [vp, vp, i, i, i, i, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_conv2d_fused.argtypes = [vp, i, i, i, i, vp, vp, i, i, i, i, i, i, i, C.c_char_p, C.c_char_p,
                                          C.POINTER(vp)]
+        L.nb200_conv2d_result_to_images.argtypes = [vp, i, i, i, i, vp]
         L.nb200_ff_layer1_partial.argtypes = [vp, vp, i, vp, i64]
         L.nb200_ff_finish_from_layer1.argtypes = [vp, i64, i, vp, vp, vp, i, C.c_float, C.c_char_p, C.c_char_p, C.POINTER(vp), vp, ip]
         L.nb200_set_maxabs.argtypes = [vp, C.POINTER(C.c_float)]
@@ -217,6 +218,13 @@ def gemm_blocks(op: int, a: DeviceSet, b: DeviceSet, epilogue: int, bias: Device
     check(lib().nb200_gemm_blocks(op, a.ptr, b.ptr, epilogue, bias.ptr if bias else None, precision, _b(db),
                                   _b(out_set), C.byref(p)))
     return DeviceSet(p)
+
+
+def conv2d_result_to_images(result: DeviceSet, num_images: int, x: int, y: int, z: int) -> np.ndarray:
+    """ConvResultToChunks + ConvChunksToImage: the result matrix re-assembled as an (n, z, x, y) fp64 array."""
+    out = np.empty((num_images, z, x, y), dtype=np.float64)
+    check(lib().nb200_conv2d_result_to_images(result.ptr, num_images, x, y, z, _hostptr(out)))
+    return out
 
 
 ACT_NONE, ACT_SIGMOID, ACT_TANH = 0, 1, 2

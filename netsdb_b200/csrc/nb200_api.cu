@@ -1276,6 +1276,31 @@ int nb200_conv2d_kernel_flat(const double *kernels_host, const double *bias_host
     return NB200_OK;
 }
 
+int nb200_conv2d_result_to_images(nb200_set *result, int num_images, int x, int y, int z, double *images_host) {
+    NEED_CTX();
+    if (!result || !images_host || num_images <= 0 || x <= 0 || y <= 0 || z <= 0) {
+        set_error("conv2d_result_to_images: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    const int group = result->total_rows / num_images;
+    if (result->total_rows % num_images != 0 || static_cast<long long>(x) * y != group || result->total_cols > z) {
+        set_error("conv2d_result_to_images: %d rows do not split into %d images of %d x %d windows (or %d columns > %d channels)",
+                  result->total_rows, num_images, x, y, result->total_cols, z);
+        return NB200_ERR_SHAPE;
+    }
+    if (!result->f64 && !result->f32) { set_error("conv2d_result_to_images: set %s:%s holds no data", result->db.c_str(), result->name.c_str()); return NB200_ERR_STATE; }
+    const size_t n = static_cast<size_t>(num_images) * z * group;
+    double *dev = nullptr;
+    NB_CUDA(cudaMalloc(&dev, n * sizeof(double)));
+    int st = result->f64 ? launch_result_to_images(c, result->f64, true, result->total_cols, num_images, group, result->total_cols, z, dev)
+                         : launch_result_to_images(c, result->f32, false, result->f32_ld, num_images, group, result->total_cols, z, dev);
+    if (st == NB200_OK && (cudaMemcpyAsync(images_host, dev, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+                           cudaStreamSynchronize(c->stream) != cudaSuccess)) st = NB200_ERR_CUDA;
+    cudaFree(dev);
+    if (st == NB200_ERR_CUDA) set_error("conv2d_result_to_images: CUDA error %s", cudaGetErrorString(cudaGetLastError()));
+    return st;
+}
+
 int nb200_conv2d_fused(const double *images_host, int n, int ch, int h, int w, const double *kernels_host,
                        const double *bias_host, int kout, int k, int padding, int relu, int precision, int block_rows,
                        int block_cols, const char *db, const char *out_set, nb200_set **out) {

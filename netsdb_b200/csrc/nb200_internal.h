@@ -159,6 +159,7 @@ struct EwiseSrc {  // one operand of an element-wise kernel: fp64 or fp32 storag
     const float *f;
     long long ld;
 };
+int launch_result_to_images(Context *c, const void *src, bool src_is_f64, int64_t ld, int num_images, int group, int zsrc, int z, double *dst);
 int launch_sum_blocks(Context *c, const EwiseSrc *src, int nsrc, int act, int64_t rows, int64_t cols, double *out);
 int launch_bias_relu_f32(Context *c, float *p, int64_t rows, int64_t cols, int64_t ld, const float *bias_n);
 int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,

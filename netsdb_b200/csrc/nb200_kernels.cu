@@ -1244,6 +1244,36 @@ int launch_extract_to_f64(Context *c, const void *src, bool src_is_f64, int64_t 
     return NB200_OK;
 }
 
+// ConvResultToChunks + ConvChunksToImage (conv2d_memory_fusion/headers/ConvResultToChunks.h:42-103,
+// ConvChunksToImage.h:34-72): result[(image, window), channel] -> images[image][channel][window], a batched
+// transpose through a padded shared-memory tile (both sides coalesced); channels at or beyond zsrc (the set's columns)
+// are written as zero.  HBM-bound: 4 or 8 bytes in, 8 out per element.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_result_to_images(const T *__restrict__ src, long long ld, int group, int zsrc, int z, double *__restrict__ dst) {
+    __shared__ double tile[32][33];
+    const int img = blockIdx.z;
+    const int w0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int r = ty; r < 32; r += 8) {
+        const int w = w0 + r, c = c0 + tx;
+        tile[r][tx] = (w < group && c < zsrc) ? static_cast<double>(src[(static_cast<long long>(img) * group + w) * ld + c]) : 0.0;
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int c = c0 + r, w = w0 + tx;
+        if (c < z && w < group) dst[(static_cast<long long>(img) * z + c) * group + w] = tile[tx][r];
+    }
+}
+int launch_result_to_images(Context *c, const void *src, bool src_is_f64, int64_t ld, int num_images, int group, int zsrc, int z, double *dst) {
+    if (num_images == 0 || group == 0 || z == 0) return NB200_OK;
+    dim3 grid(static_cast<unsigned>(ceil_div(group, 32)), static_cast<unsigned>(ceil_div(z, 32)), num_images);
+    if (src_is_f64) k_result_to_images<double><<<grid, 256, 0, c->stream>>>((const double *)src, ld, group, zsrc, z, dst);
+    else k_result_to_images<float><<<grid, 256, 0, c->stream>>>((const float *)src, ld, group, zsrc, z, dst);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
 // im2col with the reference's column order and trailing 1.0 column
 // (Image.h:36-57 get_win_value, ImageToChunks.h:52,67,75-84,98)
 __global__ void k_im2col(const double *__restrict__ img, int n, int ch, int h, int w, int k, int stride, int padding,

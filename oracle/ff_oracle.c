@@ -633,3 +633,36 @@ nbo_set *nbo_kernel_flat(const double *kernels, const double *bias, int kout, in
         }
     return s;
 }
+
+/* ConvResultToChunks + ConvChunksToImage (conv2d_memory_fusion/headers/ConvResultToChunks.h:42-103,
+ * ConvChunksToImage.h:34-72): the `result` matrix (rows = image * group + window, columns = output channel) is cut
+ * column by column into chunks of at most `group` consecutive rows; a chunk goes to image floor(row / group), channel
+ * = its column, at offset row % group; ConvChunksToImage lays each channel out as an x * y matrix in window order.
+ * out: num_images x z x (x*y) doubles.  Padding rows / columns of the edge blocks are stripped (:62-67). */
+int nbo_conv_result_to_images(const nbo_set *result, int num_images, int x, int y, int z, double *out) {
+    if (result->n == 0) return -1;
+    const int total_rows = result->blocks[0].total_rows, total_cols = result->blocks[0].total_cols;
+    if (num_images <= 0 || total_rows % num_images != 0) return -1;                 /* the assert of :46 */
+    const int group = total_rows / num_images;
+    if (group != x * y || total_cols > z) return -1;
+    for (int b = 0; b < result->n; b++) {
+        const nbo_block *blk = &result->blocks[b];
+        const int origin_x = blk->block_row * blk->rows, origin_y = blk->block_col * blk->cols;
+        int real_x = total_rows - origin_x, real_y = total_cols - origin_y;
+        if (real_x > blk->rows) real_x = blk->rows;
+        if (real_y > blk->cols) real_y = blk->cols;
+        int image_id = origin_x / group, done = origin_x % group;
+        int left = group - done < real_x ? group - done : real_x;
+        int i = 0;
+        while (i < real_x) {
+            for (int j = 0; j < real_y; j++)
+                for (int pos = 0; pos < left; pos++)
+                    out[((size_t)image_id * z + (origin_y + j)) * group + done + pos] = blk->data[(size_t)(i + pos) * blk->cols + j];
+            i += left;
+            left = real_x - i < group ? real_x - i : group;
+            image_id++;
+            done = 0;
+        }
+    }
+    return 0;
+}

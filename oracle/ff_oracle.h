@@ -115,6 +115,10 @@ nbo_set *nbo_kernel_flat(const double *kernels, const double *bias, int kout, in
                          int block_rows, int block_cols);
 
 /* ---- misc ------------------------------------------------------------------------------ */
+/* ConvResultToChunks + ConvChunksToImage (ConvResultToChunks.h:42-103, ConvChunksToImage.h:34-72): result matrix
+ * [(image, window), channel] -> num_images x z channels x (x * y) window-ordered values.  0 on success. */
+int nbo_conv_result_to_images(const nbo_set *result, int num_images, int x, int y, int z, double *out);
+
 /* plain fp64 GEMM used by the pair products: C(MxN) = A(MxK) * B^T (B is NxK) if b_trans else
  * A(MxK) * B(KxN); all row-major. */
 void nbo_dgemm(int m, int n, int k, const double *a, int lda, const double *b, int ldb,

@@ -76,6 +76,7 @@ def lib():
         L.nbo_image_flat.argtypes = [d, i, i, i, i, i, i, i, i, i]
         L.nbo_kernel_flat.restype = vp
         L.nbo_kernel_flat.argtypes = [d, d, i, i, i, i, i]
+        L.nbo_conv_result_to_images.argtypes = [vp, i, i, i, i, d]
         L.nbo_dgemm.argtypes = [i, i, i, d, i, d, i, i, d, i]
         L.nbo_hw_threads.restype = i
         _lib = L
@@ -249,6 +250,14 @@ def kernel_flat(kernels: np.ndarray, bias: np.ndarray, block_rows: int, block_co
     kout, c, k, k2 = kernels.shape
     assert k == k2
     return BlockSet(lib().nbo_kernel_flat(_dptr(kernels), _dptr(bias), kout, c, k, block_rows, block_cols))
+
+
+def conv_result_to_images(result: BlockSet, num_images: int, x: int, y: int, z: int) -> np.ndarray:
+    """ConvResultToChunks + ConvChunksToImage: images as an (n, z, x, y) array."""
+    out = np.zeros((num_images, z, x, y), dtype=np.float64)
+    if lib().nbo_conv_result_to_images(result.ptr, num_images, x, y, z, _dptr(out)) != 0:
+        raise RuntimeError("conv_result_to_images: total rows not divisible by the number of images, or shape mismatch")
+    return out
 
 
 def dgemm(a: np.ndarray, b: np.ndarray, b_trans: bool) -> np.ndarray:

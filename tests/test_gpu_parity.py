@@ -351,6 +351,36 @@ def test_conv2d_implicit_gemm_vs_blocked_oracle(nb, oracle, shape):
             assert np.abs(R.download_dense() - want).max() <= TOL[prec] * np.abs(refd).max(), (prec, relu)
 
 
+@pytest.mark.parametrize("shape", [(2, 3, 20, 19, 5, 3, 0, 5), (3, 8, 17, 150, 40, 3, 1, 40), (2, 4, 9, 9, 3, 3, 0, 6)])
+def test_conv2d_result_to_images(nb, oracle, shape):
+    """ConvResultToChunks + ConvChunksToImage: the result matrix re-assembled into images (pure data movement: bit
+    exact against the oracle's chunk-by-chunk restatement and against the plain NCHW transpose)."""
+    n, c, h, w, kout, k, pad, z = shape
+    imgs = oracle.synth_dense(n * c, h * w, 41).reshape(n, c, h, w)
+    kern = oracle.synth_dense(kout * c, k * k, 42).reshape(kout, c, k, k)
+    bias = oracle.synth_dense(kout, 1, 43).reshape(kout)
+    hout, wout = h + 2 * pad - k + 1, w + 2 * pad - k + 1
+    ref = oracle.transpose_mult_agg(oracle.image_flat(imgs, k, 1, pad, 50, 64), oracle.kernel_flat(kern, bias, 64, 64), 4)
+    want = oracle.conv_result_to_images(ref, n, hout, wout, z)
+    R = nb.conv2d_fused(imgs, kern, bias, pad, False, nb.PREC_FP64, 50, 64)
+    got = nb.conv2d_result_to_images(R, n, hout, wout, z)
+    assert got.shape == (n, z, hout, wout)
+    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+    # the movement itself is exact: the device result matrix, transposed on the host, equals what the call returns
+    dense = R.download_dense()
+    plain = np.zeros((n, z, hout * wout))
+    plain[:, :kout] = dense.reshape(n, hout * wout, kout).transpose(0, 2, 1)
+    assert np.array_equal(got.reshape(n, z, -1), plain)
+    F = nb.conv2d_fused(imgs, kern, bias, pad, True, nb.PREC_BF16, 50, 64)  # fp32 result set
+    gf = nb.conv2d_result_to_images(F, n, hout, wout, z)
+    assert np.array_equal(gf.reshape(n, z, -1)[:, :kout], F.download_dense().reshape(n, hout * wout, kout).transpose(0, 2, 1))
+    with pytest.raises(nb.Nb200Error):
+        nb.conv2d_result_to_images(R, n, hout + 1, wout, z)
+    if kout > 1:
+        with pytest.raises(nb.Nb200Error):
+            nb.conv2d_result_to_images(R, n, hout, wout, kout - 1)
+
+
 @pytest.mark.parametrize("shape", [(2400, 9000, 700, 50, 500), (2048, 8200, 300, 20, 1000)])
 def test_fused_layer1_kernel_vs_oracle(nb, oracle, shape):
     """Shapes large enough for the fused layer-1 kernel (fp64 -> fp16 conversion inside the persistent 2-SM GEMM through

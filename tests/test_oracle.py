@@ -138,3 +138,18 @@ def test_word2vec_shape(oracle):
     w, x = oracle.synth_dense(6, 50, 9), oracle.synth_dense(11, 50, 10)
     out = oracle.transpose_mult_agg(oracle.load_matrix(w, 4, 16), oracle.load_matrix(x, 4, 16), 3)
     assert out.totals() == (6, 11) and np.allclose(out.dense(), w @ x.T, atol=1e-13)
+
+
+def test_conv_result_to_images(oracle):
+    """ConvResultToChunks + ConvChunksToImage restated chunk by chunk == the plain (image, window, channel) ->
+    (image, channel, window) transpose, for block shapes that split images and channels unevenly."""
+    rng = np.random.default_rng(1)
+    n, z, x, y = 3, 5, 4, 6
+    res = rng.normal(size=(n * x * y, z))
+    want = res.reshape(n, x * y, z).transpose(0, 2, 1).reshape(n, z, x, y)
+    for br, bc in ((7, 2), (24, 5), (10, 3), (100, 100), (1, 1)):
+        assert np.array_equal(oracle.conv_result_to_images(oracle.load_matrix(res, br, bc), n, x, y, z), want)
+    wide = oracle.conv_result_to_images(oracle.load_matrix(res, 7, 2), n, x, y, z + 2)  # more channels than columns
+    assert np.array_equal(wide[:, :z], want) and not wide[:, z:].any()
+    with pytest.raises(RuntimeError):
+        oracle.conv_result_to_images(oracle.load_matrix(res, 7, 2), 5, x, y, z)  # 72 rows do not split into 5 images
