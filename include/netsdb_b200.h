@@ -157,6 +157,23 @@ int nb200_gemm_blocks(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_se
 int nb200_sum_blocks(nb200_set *a, nb200_set *b, nb200_set *c, int activation, const char *db, const char *out_set,
                      nb200_set **out);
 
+/* One LSTM step as the reference's driver wires it (src/tests/source/LSTMTest.cc:204-543), in one call:
+ *   f_t = sigmoid(w_f.x_t + u_f.h_t_1 + b_f), i_t and o_t alike, c_t_temp = tanh(w_c.x_t + u_c.h_t_1 + b_c)
+ *       (FFInputLayerJoin + FFAggMatrix twice, LSTMThreeWaySum; :204-451)
+ *   c_t = f_t . c_t_1 + i_t . c_t_temp     (matrix products through FFInputLayerJoin, LSTMTwoSum; :470-498)
+ *   h_t = o_t . tanh(c_t)                  (LSTMHiddenState + FFAggMatrix; :528-543)
+ * Reads the 15 sets of `in`, creates (or replaces) sets f_t, i_t, o_t, c_t_temp, c_t, h_t in `db` (the driver's
+ * names), all fp64.  With BF16 / BF16X3 the eight gate products run as ONE tensor-core GEMM over K-concatenated
+ * operands ([w_f u_f; w_i u_i; w_o u_o; w_c u_c] . [x_t; h_t_1], the stacked weight operand is cached across steps
+ * until a weight set changes), the four LSTMThreeWaySum joins as one pass, and c_t's two products as one GEMM
+ * ([f_t | i_t] . [c_t_1; c_t_temp]); no device memory is allocated in steady state.  FP64 and F16 compose the
+ * per-operator entry points above.  Gate order in the arrays: forget, input, output, cell candidate. */
+typedef struct nb200_lstm_sets {
+    nb200_set *w[4], *u[4], *b[4];
+    nb200_set *x_t, *h_t_1, *c_t_1;
+} nb200_lstm_sets;
+int nb200_lstm_cell(const nb200_lstm_sets *in, int precision, const char *db);
+
 /* FFRowAggregate + FFOutputLayer (FFRowAggregate.h:11-29, FFMatrixBlock.h:116-142,
  * FFOutputLayer.h:31-57 intended form) on a set of pre-exp logits (batch x labels):
  * out[i,j] = exp(z[i,j]) / sum_j exp(z[i,j]), evaluated in the max-subtracted form.

@@ -28,7 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
-    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell",
 ]
 
 
@@ -41,6 +41,12 @@ class FFStats(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class LstmSets(C.Structure):
+    """nb200_lstm_sets: gate order forget, input, output, cell candidate."""
+    _fields_ = [("w", C.c_void_p * 4), ("u", C.c_void_p * 4), ("b", C.c_void_p * 4), ("x_t", C.c_void_p),
+                ("h_t_1", C.c_void_p), ("c_t_1", C.c_void_p)]
 
 
 class Nb200Error(RuntimeError):
@@ -83,6 +89,7 @@ def lib():
         L.nb200_set_rename.argtypes = [vp, C.c_char_p, C.c_char_p]
         L.nb200_gemm_blocks.argtypes = [i, vp, vp, i, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_softmax_rows.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(vp), vp]
+        L.nb200_lstm_cell.argtypes = [C.POINTER(LstmSets), i, C.c_char_p]
         L.nb200_sum_blocks.argtypes = [vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_ff_inference_unit.argtypes = [vp, vp, vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp), vp,
                                               C.POINTER(FFStats)]
@@ -236,6 +243,17 @@ def sum_blocks(a: DeviceSet, b: DeviceSet | None, c: DeviceSet | None, activatio
     check(lib().nb200_sum_blocks(a.ptr, b.ptr if b else None, c.ptr if c else None, activation, _b(db), _b(out_set),
                                  C.byref(p)))
     return DeviceSet(p)
+
+
+def lstm_cell(db: str, precision: int) -> dict:
+    """nb200_lstm_cell on the reference driver's set names in `db`; returns the six result sets."""
+    L = DeviceSet.lookup
+    a = LstmSets()
+    for k, g in enumerate("fioc"):
+        a.w[k], a.u[k], a.b[k] = L(db, "w_" + g).ptr.value, L(db, "u_" + g).ptr.value, L(db, "b_" + g).ptr.value
+    a.x_t, a.h_t_1, a.c_t_1 = L(db, "x_t").ptr.value, L(db, "h_t_1").ptr.value, L(db, "c_t_1").ptr.value
+    check(lib().nb200_lstm_cell(C.byref(a), precision, _b(db)))
+    return {n: L(db, n) for n in ("f_t", "i_t", "o_t", "c_t_temp", "c_t", "h_t")}
 
 
 def softmax_rows(logits: DeviceSet, db: str, out_set: str, want_labels: bool = True):

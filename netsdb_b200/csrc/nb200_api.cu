@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <string>
@@ -25,6 +26,8 @@ void set_error(const char *fmt, ...) {
 static Context *g_ctx = nullptr;
 static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default on)
 static std::mutex g_mu;
+static std::atomic<uint64_t> g_version{0};  // source of set versions: unique across sets, so a cache keyed on
+                                            // (pointer, version) cannot be fooled by a recycled address
 static std::map<std::pair<std::string, std::string>, nb200_set *> g_sets;
 
 Context *ctx() { return g_ctx; }
@@ -157,6 +160,7 @@ static int make_set(const char *db, const char *name, int tr, int tc, int br, in
     s->db = db; s->name = name;
     s->total_rows = tr; s->total_cols = tc; s->block_rows = br; s->block_cols = bc;
     s->view_exp = false; s->view_of = nullptr;
+    s->version = ++g_version;
     *out = s;
     return NB200_OK;
 }
@@ -248,10 +252,13 @@ int nb200_init(int device) {
     return NB200_OK;
 }
 
+static void release_lstm_scratch(void);
+
 int nb200_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (!g_ctx) return NB200_OK;
     cudaStreamSynchronize(g_ctx->stream);
+    release_lstm_scratch();
     for (auto &kv : g_sets) {
         free_set_storage(kv.second);
         delete kv.second;
@@ -353,6 +360,7 @@ int nb200_set_info(const nb200_set *s, int *total_rows, int *total_cols, int *bl
 }
 
 static void drop_derived(nb200_set *s) {
+    s->version = ++g_version;
     s->rowp.valid = s->rowp.lo_valid = s->rowp.f16_valid = false;
     s->colp.valid = s->colp.lo_valid = s->colp.f16_valid = false;
     if (s->f64 && s->f32) { cudaFree(s->f32); s->f32 = nullptr; }
@@ -663,6 +671,176 @@ int nb200_sum_blocks(nb200_set *a, nb200_set *b, nb200_set *cc, int activation, 
     o->f64 = res;
     *out = o;
     return NB200_OK;
+}
+
+// ---- LSTM step -----------------------------------------------------------------------------------
+namespace {
+struct LstmScratch {
+    nb200_set *w[4] = {}, *u[4] = {};
+    uint64_t ver[8] = {};
+    bool wu_lo = false, wu_valid = false;
+    Planes WU, XH, FI, CC, OP, TH;
+    float *G = nullptr, *C32 = nullptr;
+    double *T64 = nullptr;
+    size_t G_cap = 0, C_cap = 0, T_cap = 0;
+};
+LstmScratch g_lstm;
+
+int grow_bytes(void **p, size_t *have, size_t need) {
+    if (*have >= need) return NB200_OK;
+    cudaFree(*p);
+    *p = nullptr; *have = 0;
+    NB_CUDA(cudaMalloc(p, need ? need : 1));
+    *have = need;
+    return NB200_OK;
+}
+
+// P = U . V^T over K-major bf16 planes into an fp32 matrix (split-K + deterministic reduce when that is faster)
+int gemm_planes_f32(Context *c, const Planes &U, const Planes &V, int M, int N, int nterms, float *out, int64_t ld) {
+    if (M == 0 || N == 0) return NB200_OK;
+    const int splits = choose_splits(c, M, N, U.ldk < V.ldk ? U.ldk : V.ldk, nterms);
+    int Mpad = 0, Npad = 0;
+    GemmEpilogue ge;
+    if (splits == 1) {
+        ge.mode = 1; ge.out = out; ge.out_ld = ld;
+        return launch_gemm_tc(c, U, V, M, N, nterms, 1, ge, &Mpad, &Npad, nullptr, kFmtBF16);
+    }
+    int real_splits = splits;
+    NB_TRY(launch_gemm_tc(c, U, V, M, N, nterms, splits, ge, &Mpad, &Npad, &real_splits, kFmtBF16));
+    ReduceOut ro;
+    ro.f32 = out; ro.f32_ld = ld;
+    return launch_splitk_reduce(c, M, N, real_splits, Mpad, Npad, nullptr, nullptr, 0, ro);
+}
+
+// result set holding fp64: storage of an existing set of the same shape is reused (no cudaMalloc / cudaFree per step)
+int out_set_f64(const char *db, const char *name, int tr, int tc, int br, int bc, nb200_set **out) {
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto it = g_sets.find(std::make_pair(std::string(db), std::string(name)));
+        if (it != g_sets.end()) {
+            nb200_set *s = it->second;
+            if (s->f64 && !s->f32 && !s->view_of && s->total_rows == tr && s->total_cols == tc && s->block_rows == br &&
+                s->block_cols == bc) {
+                s->version = ++g_version;
+                s->rowp.valid = s->rowp.lo_valid = s->rowp.f16_valid = false;
+                s->colp.valid = s->colp.lo_valid = s->colp.f16_valid = false;
+                *out = s;
+                return NB200_OK;
+            }
+        }
+    }
+    NB_TRY(make_set(db, name, tr, tc, br, bc, out));
+    const size_t n = static_cast<size_t>(tr) * tc;
+    NB_CUDA(cudaMalloc(&(*out)->f64, (n ? n : 1) * sizeof(double)));
+    return NB200_OK;
+}
+}  // namespace
+
+static void release_lstm_scratch(void) {
+    for (Planes *p : {&g_lstm.WU, &g_lstm.XH, &g_lstm.FI, &g_lstm.CC, &g_lstm.OP, &g_lstm.TH}) free_planes(p);
+    cudaFree(g_lstm.G); cudaFree(g_lstm.C32); cudaFree(g_lstm.T64);
+    g_lstm = LstmScratch();
+}
+
+static int lstm_cell_composed(const nb200_lstm_sets *in, int precision, const char *db) {
+    static const char *gate_names[4] = {"f_t", "i_t", "o_t", "c_t_temp"};
+    nb200_set *gate[4] = {};
+    for (int g = 0; g < 4; g++) {
+        nb200_set *wx = nullptr, *uh = nullptr;
+        NB_TRY(gemm_blocks_impl(NB200_OP_NN, in->w[g], in->x_t, NB200_EPI_NONE, nullptr, precision, db, "__lstm_wx", &wx, 0));
+        NB_TRY(gemm_blocks_impl(NB200_OP_NN, in->u[g], in->h_t_1, NB200_EPI_NONE, nullptr, precision, db, "__lstm_uh", &uh, 0));
+        NB_TRY(nb200_sum_blocks(wx, uh, in->b[g], g == 3 ? NB200_ACT_TANH : NB200_ACT_SIGMOID, db, gate_names[g], &gate[g]));
+    }
+    nb200_set *fc = nullptr, *ic = nullptr, *c_t = nullptr, *th = nullptr, *h_t = nullptr;
+    NB_TRY(gemm_blocks_impl(NB200_OP_NN, gate[0], in->c_t_1, NB200_EPI_NONE, nullptr, precision, db, "__lstm_wx", &fc, 0));
+    NB_TRY(gemm_blocks_impl(NB200_OP_NN, gate[1], gate[3], NB200_EPI_NONE, nullptr, precision, db, "__lstm_uh", &ic, 0));
+    NB_TRY(nb200_sum_blocks(fc, ic, nullptr, NB200_ACT_NONE, db, "c_t", &c_t));
+    NB_TRY(nb200_sum_blocks(c_t, nullptr, nullptr, NB200_ACT_TANH, db, "__lstm_tanh_c_t", &th));
+    NB_TRY(gemm_blocks_impl(NB200_OP_NN, gate[2], th, NB200_EPI_NONE, nullptr, precision, db, "h_t", &h_t, 0));
+    return NB200_OK;
+}
+
+int nb200_lstm_cell(const nb200_lstm_sets *in, int precision, const char *db) {
+    NEED_CTX();
+    if (!in || !db || precision < 0 || precision > 3 || !in->x_t || !in->h_t_1 || !in->c_t_1) { set_error("lstm_cell: invalid arguments"); return NB200_ERR_INVALID; }
+    for (int g = 0; g < 4; g++)
+        if (!in->w[g] || !in->u[g] || !in->b[g]) { set_error("lstm_cell: invalid arguments"); return NB200_ERR_INVALID; }
+    const int L = in->w[0]->total_rows, D = in->w[0]->total_cols, B = in->x_t->total_cols;
+    const int br = in->w[0]->block_rows, bk = in->w[0]->block_cols, bc = in->x_t->block_cols;
+    // the fused path wants the textbook shapes; anything else (the driver's own ragged joins) goes operator by operator
+    bool regular = (precision == NB200_PREC_BF16 || precision == NB200_PREC_BF16X3) && L > 0 && D > 0 && B > 0 &&
+                   in->x_t->total_rows == D && in->x_t->f64 && in->x_t->block_rows == bk &&
+                   in->h_t_1->total_rows == L && in->h_t_1->total_cols == B && in->h_t_1->f64 && in->h_t_1->block_cols == bc &&
+                   in->c_t_1->total_rows == L && in->c_t_1->total_cols == B && in->c_t_1->f64 && in->c_t_1->block_cols == bc &&
+                   in->c_t_1->block_rows == bc;  // f_t's column blocks join c_t_1's row blocks
+    for (int g = 0; g < 4 && regular; g++) {
+        nb200_set *w = in->w[g], *u = in->u[g], *b = in->b[g];
+        regular = w->f64 && u->f64 && b->f64 && w->total_rows == L && w->total_cols == D && w->block_rows == br && w->block_cols == bk &&
+                  u->total_rows == L && u->total_cols == L && u->block_rows == br && u->block_cols == in->h_t_1->block_rows &&
+                  b->total_rows == L && b->total_cols == B && b->block_rows == br && b->block_cols == bc;
+    }
+    if (!regular) return lstm_cell_composed(in, precision, db);
+
+    LstmScratch &S = g_lstm;
+    const bool lo = precision == NB200_PREC_BF16X3;
+    const int nterms = lo ? 3 : 1;
+    const int64_t Dp = round_up(D, 64), Lp = round_up(L, 64);
+    // 1. stacked weight operand [w_g | u_g] for g = f, i, o, c: rebuilt only when a weight set changed
+    bool cached = S.wu_valid && (S.wu_lo || !lo) && S.WU.rows == 4ll * L && S.WU.ldk == Dp + Lp;
+    for (int g = 0; g < 4 && cached; g++)
+        cached = S.w[g] == in->w[g] && S.u[g] == in->u[g] && S.ver[g] == in->w[g]->version && S.ver[4 + g] == in->u[g]->version;
+    if (!cached) {
+        S.wu_valid = false;
+        NB_TRY(alloc_planes_raw(&S.WU, 4ll * L, Dp + Lp, lo));
+        for (int g = 0; g < 4; g++) {
+            NB_TRY(launch_convert_sub(c, in->w[g]->f64, D, L, D, false, &S.WU, static_cast<int64_t>(g) * L, 0, lo));
+            NB_TRY(launch_convert_sub(c, in->u[g]->f64, L, L, L, false, &S.WU, static_cast<int64_t>(g) * L, Dp, lo));
+            S.w[g] = in->w[g]; S.u[g] = in->u[g];
+            S.ver[g] = in->w[g]->version; S.ver[4 + g] = in->u[g]->version;
+        }
+        S.wu_lo = lo;
+        S.wu_valid = true;
+    }
+    // 2. [x_t; h_t_1] as the transposed operand, then every gate's W.x + U.h in one GEMM
+    NB_TRY(alloc_planes_raw(&S.XH, B, Dp + Lp, lo));
+    NB_TRY(launch_convert_sub(c, in->x_t->f64, B, D, B, true, &S.XH, 0, 0, lo));
+    NB_TRY(launch_convert_sub(c, in->h_t_1->f64, B, L, B, true, &S.XH, 0, Dp, lo));
+    NB_TRY(grow_bytes(reinterpret_cast<void **>(&S.G), &S.G_cap, static_cast<size_t>(4) * L * B * sizeof(float)));
+    NB_TRY(gemm_planes_f32(c, S.WU, S.XH, 4 * L, B, nterms, S.G, B));
+    // 3. the four LSTMThreeWaySum joins
+    nb200_set *f_t, *i_t, *o_t, *c_tmp, *c_t, *h_t;
+    NB_TRY(out_set_f64(db, "f_t", L, B, br, bc, &f_t));
+    NB_TRY(out_set_f64(db, "i_t", L, B, br, bc, &i_t));
+    NB_TRY(out_set_f64(db, "o_t", L, B, br, bc, &o_t));
+    NB_TRY(out_set_f64(db, "c_t_temp", L, B, br, bc, &c_tmp));
+    NB_TRY(launch_lstm_gates(c, S.G, B, L, B, in->b[0]->f64, in->b[1]->f64, in->b[2]->f64, in->b[3]->f64, f_t->f64, i_t->f64,
+                             o_t->f64, c_tmp->f64));
+    // 4. c_t = f_t . c_t_1 + i_t . c_t_temp: the joins match column blocks of the left with row blocks of the right,
+    //    i.e. contract over k < Kc = min(B, L); one GEMM over [f_t | i_t] and [c_t_1; c_t_temp]
+    const int Kc = B < L ? B : L;
+    const int64_t Kcp = round_up(Kc, 64);
+    NB_TRY(alloc_planes_raw(&S.FI, L, 2 * Kcp, lo));
+    NB_TRY(launch_convert_sub(c, f_t->f64, B, L, Kc, false, &S.FI, 0, 0, lo));
+    NB_TRY(launch_convert_sub(c, i_t->f64, B, L, Kc, false, &S.FI, 0, Kcp, lo));
+    NB_TRY(alloc_planes_raw(&S.CC, B, 2 * Kcp, lo));
+    NB_TRY(launch_convert_sub(c, in->c_t_1->f64, B, Kc, B, true, &S.CC, 0, 0, lo));
+    NB_TRY(launch_convert_sub(c, c_tmp->f64, B, Kc, B, true, &S.CC, 0, Kcp, lo));
+    NB_TRY(grow_bytes(reinterpret_cast<void **>(&S.C32), &S.C_cap, static_cast<size_t>(L) * B * sizeof(float)));
+    NB_TRY(gemm_planes_f32(c, S.FI, S.CC, L, B, nterms, S.C32, B));
+    NB_TRY(out_set_f64(db, "c_t", L, B, br, bc, &c_t));
+    EwiseSrc src{nullptr, S.C32, B};
+    NB_TRY(launch_sum_blocks(c, &src, 1, NB200_ACT_NONE, L, B, c_t->f64));
+    // 5. h_t = o_t . tanh(c_t)
+    NB_TRY(grow_bytes(reinterpret_cast<void **>(&S.T64), &S.T_cap, static_cast<size_t>(L) * B * sizeof(double)));
+    NB_TRY(launch_sum_blocks(c, &src, 1, NB200_ACT_TANH, L, B, S.T64));
+    NB_TRY(alloc_planes_raw(&S.OP, L, Kcp, lo));
+    NB_TRY(launch_convert_sub(c, o_t->f64, B, L, Kc, false, &S.OP, 0, 0, lo));
+    NB_TRY(alloc_planes_raw(&S.TH, B, Kcp, lo));
+    NB_TRY(launch_convert_sub(c, S.T64, B, Kc, B, true, &S.TH, 0, 0, lo));
+    NB_TRY(gemm_planes_f32(c, S.OP, S.TH, L, B, nterms, S.C32, B));
+    NB_TRY(out_set_f64(db, "h_t", L, B, br, bc, &h_t));
+    NB_TRY(launch_sum_blocks(c, &src, 1, NB200_ACT_NONE, L, B, h_t->f64));
+    return check_kernel_fault(c, "lstm_cell");
 }
 
 int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, nb200_set **out, int32_t *labels_host) {

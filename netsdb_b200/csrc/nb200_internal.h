@@ -160,6 +160,11 @@ struct EwiseSrc {  // one operand of an element-wise kernel: fp64 or fp32 storag
     long long ld;
 };
 int launch_result_to_images(Context *c, const void *src, bool src_is_f64, int64_t ld, int num_images, int group, int zsrc, int z, double *dst);
+int launch_convert_sub(Context *c, const double *src, int64_t ld, int64_t rows, int64_t cols, bool transposed, Planes *p,
+                       int64_t row_off, int64_t k_off, bool want_lo);
+int alloc_planes_raw(Planes *p, int64_t rows, int64_t k, bool want_lo);
+int launch_lstm_gates(Context *c, const float *g, int64_t g_ld, int L, int B, const double *bf, const double *bi,
+                      const double *bo, const double *bc, double *f_t, double *i_t, double *o_t, double *c_temp);
 int launch_sum_blocks(Context *c, const EwiseSrc *src, int nsrc, int act, int64_t rows, int64_t cols, double *out);
 int launch_bias_relu_f32(Context *c, float *p, int64_t rows, int64_t cols, int64_t ld, const float *bias_n);
 int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
@@ -213,6 +218,7 @@ struct nb200_set {
     int64_t f32_ld = 0;
     nb200::Planes rowp, colp;
     float *wo_rownorm_max = nullptr;  // device scalar derived from rowp.row_sumsq (error model)
+    uint64_t version = 0;          // bumped whenever the set's contents change (caches of derived operands)
     bool view_exp = false;         // downloads apply exp() (the `yo` view of the logits)
     nb200_set *view_of = nullptr;  // set whose storage a view reads
 };

@@ -66,7 +66,7 @@ template <typename T, bool WANT_LO>
 __global__ void __launch_bounds__(kCvtThreads)
 k_convert_planes(const T *__restrict__ src, long long ld, long long cols, __nv_bfloat16 *__restrict__ hi,
                  __nv_bfloat16 *__restrict__ lo, long long ldk, float *__restrict__ row_sumsq,
-                 float *__restrict__ maxabs) {
+                 float *__restrict__ maxabs, long long kext) {  // kext: K range written (a multiple of 4, <= ldk)
     __shared__ float sh[32];
     const long long row = blockIdx.x;
     const long long c0 = static_cast<long long>(blockIdx.y) * kCvtChunk + threadIdx.x * 4;
@@ -75,7 +75,7 @@ k_convert_planes(const T *__restrict__ src, long long ld, long long cols, __nv_b
 #pragma unroll
     for (int h = 0; h < kCvtPerThread / 4; h++) {
         const long long c = c0 + static_cast<long long>(h) * kCvtThreads * 4;
-        if (c >= ldk) continue;
+        if (c >= kext) continue;
         T v[4];
         if (c + 3 < cols && ((reinterpret_cast<uintptr_t>(srow + c) & (sizeof(T) * 2 - 1)) == 0)) {
             // two 16-byte (double) or one 16-byte (float) loads
@@ -137,11 +137,11 @@ int launch_convert_planes(Context *c, const void *src, bool src_is_f64, int64_t 
     dim3 grid(static_cast<unsigned>(rows), static_cast<unsigned>(ceil_div(p->ldk, kCvtChunk)));
     if (grid.y > 65535) { set_error("convert: K too large for one launch (%lld)", (long long)cols); return NB200_ERR_INVALID; }
     if (src_is_f64) {
-        if (want_lo) k_convert_planes<double, true><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
-        else k_convert_planes<double, false><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        if (want_lo) k_convert_planes<double, true><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
+        else k_convert_planes<double, false><<<grid, kCvtThreads, 0, c->stream>>>((const double *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
     } else {
-        if (want_lo) k_convert_planes<float, true><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
-        else k_convert_planes<float, false><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        if (want_lo) k_convert_planes<float, true><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
+        else k_convert_planes<float, false><<<grid, kCvtThreads, 0, c->stream>>>((const float *)src, ld, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
     }
     NB_LAUNCH_CHECK(c);
     p->valid = true;
@@ -309,7 +309,7 @@ template <typename T, bool WANT_LO>
 __global__ void __launch_bounds__(256)
 k_convert_planes_t(const T *__restrict__ src, long long ld, long long rows, long long cols,
                    __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo, long long ldk,
-                   float *__restrict__ row_sumsq, float *__restrict__ maxabs) {
+                   float *__restrict__ row_sumsq, float *__restrict__ maxabs, long long kext) {
     __shared__ T tile[32][33];
     const long long r0 = static_cast<long long>(blockIdx.y) * 32, c0 = static_cast<long long>(blockIdx.x) * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
@@ -329,7 +329,7 @@ k_convert_planes_t(const T *__restrict__ src, long long ld, long long rows, long
         float ss = f * f;
         mx = fmaxf(mx, fabsf(f));
         for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-        if (pc < cols && pr < ldk) {
+        if (pc < cols && pr < kext) {
             hi[pc * ldk + pr] = h;
             if (WANT_LO) lo[pc * ldk + pr] = l;
         }
@@ -349,11 +349,11 @@ int launch_convert_planes_t(Context *c, const void *src, bool src_is_f64, int64_
     dim3 grid(static_cast<unsigned>(ceil_div(cols, 32)), static_cast<unsigned>(ceil_div(p->ldk, 32)));
     if (grid.y > 65535) { set_error("transposing convert: source has too many rows (%lld)", (long long)rows); return NB200_ERR_INVALID; }
     if (src_is_f64) {
-        if (want_lo) k_convert_planes_t<double, true><<<grid, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
-        else k_convert_planes_t<double, false><<<grid, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        if (want_lo) k_convert_planes_t<double, true><<<grid, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
+        else k_convert_planes_t<double, false><<<grid, 256, 0, c->stream>>>((const double *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
     } else {
-        if (want_lo) k_convert_planes_t<float, true><<<grid, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
-        else k_convert_planes_t<float, false><<<grid, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs);
+        if (want_lo) k_convert_planes_t<float, true><<<grid, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
+        else k_convert_planes_t<float, false><<<grid, 256, 0, c->stream>>>((const float *)src, ld, rows, cols, p->hi, p->lo, p->ldk, p->row_sumsq, p->maxabs, p->ldk);
     }
     NB_LAUNCH_CHECK(c);
     p->valid = true;
@@ -361,6 +361,71 @@ int launch_convert_planes_t(Context *c, const void *src, bool src_is_f64, int64_
     return NB200_OK;
 }
 
+
+// Conversion of an fp64 matrix into a sub-range of wider operand planes (K-concatenated operands of the fused LSTM
+// step): plane rows [row_off, row_off + rows), K range [k_off, k_off + round_up(cols, 64)).  `transposed` reads a
+// (K x rows) source instead (plane[c][k_off + r] = src[r][c]).
+int launch_convert_sub(Context *c, const double *src, int64_t ld, int64_t rows, int64_t cols, bool transposed, Planes *p,
+                       int64_t row_off, int64_t k_off, bool want_lo) {
+    if (rows == 0 || cols == 0) return NB200_OK;
+    __nv_bfloat16 *hi = p->hi + row_off * p->ldk + k_off;
+    __nv_bfloat16 *lo = want_lo ? p->lo + row_off * p->ldk + k_off : nullptr;
+    if (!transposed) {
+        const int64_t kext = round_up(cols, 64);
+        dim3 grid(static_cast<unsigned>(rows), static_cast<unsigned>(ceil_div(kext, kCvtChunk)));
+        if (want_lo) k_convert_planes<double, true><<<grid, kCvtThreads, 0, c->stream>>>(src, ld, cols, hi, lo, p->ldk, nullptr, nullptr, kext);
+        else k_convert_planes<double, false><<<grid, kCvtThreads, 0, c->stream>>>(src, ld, cols, hi, lo, p->ldk, nullptr, nullptr, kext);
+    } else {  // here `rows` is the source's row count = K extent, `cols` its column count = plane rows
+        const int64_t kext = round_up(rows, 64);
+        dim3 grid(static_cast<unsigned>(ceil_div(cols, 32)), static_cast<unsigned>(ceil_div(kext, 32)));
+        if (want_lo) k_convert_planes_t<double, true><<<grid, 256, 0, c->stream>>>(src, ld, rows, cols, hi, lo, p->ldk, nullptr, nullptr, kext);
+        else k_convert_planes_t<double, false><<<grid, 256, 0, c->stream>>>(src, ld, rows, cols, hi, lo, p->ldk, nullptr, nullptr, kext);
+    }
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+int alloc_planes_raw(Planes *p, int64_t rows, int64_t k, bool want_lo) {
+    NB_TRY(alloc_planes(p, rows, k, want_lo));
+    p->valid = true;
+    p->lo_valid = want_lo;
+    return NB200_OK;
+}
+
+// The four LSTMThreeWaySum joins of one step in a single pass (src/LSTM/headers/LSTMThreeWaySum.h:76-95;
+// LSTMTest.cc:240-247, :305-312, :370-377, :435-440): g holds the stacked pre-activations [f; i; o; c] (4L x B, fp32,
+// W.x + U.h already summed by the K-concatenated GEMM), each gate adds its own bias matrix and applies sigmoid
+// (f, i, o) or tanh (c).
+__global__ void __launch_bounds__(256)
+k_lstm_gates(const float *__restrict__ g, long long g_ld, int L, int B, const double *__restrict__ bf,
+             const double *__restrict__ bi, const double *__restrict__ bo, const double *__restrict__ bc,
+             double *__restrict__ f_t, double *__restrict__ i_t, double *__restrict__ o_t, double *__restrict__ c_temp) {
+    const long long n = static_cast<long long>(L) * B;
+    for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < n;
+         e += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = e / B, col = e - r * B;
+        const double sf = static_cast<double>(g[r * g_ld + col]) + bf[e];
+        const double si = static_cast<double>(g[(r + L) * g_ld + col]) + bi[e];
+        const double so = static_cast<double>(g[(r + 2ll * L) * g_ld + col]) + bo[e];
+        const double sc = static_cast<double>(g[(r + 3ll * L) * g_ld + col]) + bc[e];
+        f_t[e] = 1.0 / (1.0 + exp(-1.0 * sf));
+        i_t[e] = 1.0 / (1.0 + exp(-1.0 * si));
+        o_t[e] = 1.0 / (1.0 + exp(-1.0 * so));
+        double t;
+        if (fabs(sc) > 350.0) t = copysign(1.0, sc);
+        else { const double ep = exp(sc), em = exp(-1.0 * sc); t = (ep - em) / (ep + em); }
+        c_temp[e] = t;
+    }
+}
+int launch_lstm_gates(Context *c, const float *g, int64_t g_ld, int L, int B, const double *bf, const double *bi,
+                      const double *bo, const double *bc, double *f_t, double *i_t, double *o_t, double *c_temp) {
+    const int64_t n = static_cast<int64_t>(L) * B;
+    if (n == 0) return NB200_OK;
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < sms * 8 ? ceil_div(n, 256) : sms * 8);
+    k_lstm_gates<<<blocks, 256, 0, c->stream>>>(g, g_ld, L, B, bf, bi, bo, bc, f_t, i_t, o_t, c_temp);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
 
 // Gather the listed rows of an fp64 matrix straight into compact bf16 hi/lo planes (the inputs of the
 // second cascade level): plane row i = source row list[i].

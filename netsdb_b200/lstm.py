@@ -16,8 +16,13 @@ GATES = (("f_t", "w_f", "u_f", "b_f", capi.ACT_SIGMOID),       # LSTMTest.cc:204
          ("c_t_temp", "w_c", "u_c", "b_c", capi.ACT_TANH))     # :401-451
 
 
+def lstm_cell_fused(db: str = "lstm", precision: str = "bf16x3") -> dict[str, capi.DeviceSet]:
+    """The same step through the single entry point nb200_lstm_cell (K-concatenated gate GEMM, fused gate pass)."""
+    return capi.lstm_cell(db, capi.PRECISIONS[precision])
+
+
 def lstm_cell(db: str = "lstm", precision: str = "fp64") -> dict[str, capi.DeviceSet]:
-    """Reads sets w_*/u_*/b_* (* in f i o c), x_t, h_t_1, c_t_1 of `db`; writes f_t i_t o_t c_t_temp c_t h_t."""
+    """Operator by operator, as the reference driver issues its jobs.  Reads sets w_*/u_*/b_* (* in f i o c), x_t, h_t_1, c_t_1 of `db`; writes f_t i_t o_t c_t_temp c_t h_t."""
     L = capi.DeviceSet.lookup
     prec = capi.PRECISIONS[precision]
     mm = lambda a, b, out: capi.gemm_blocks(capi.OP_NN, a, b, capi.EPI_NONE, None, prec, db, out)

@@ -146,6 +146,35 @@ def test_lstm_cell_against_oracle(nb, oracle, prec, shape):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("prec", ["bf16x3", "bf16", "fp64", "f16"])
+@pytest.mark.parametrize("shape", [(128, 256, 128, 32), (96, 200, 96, 32), (128, 192, 64, 32), (64, 100, 192, 64), (320, 700, 320, 64)])
+def test_lstm_cell_single_entry_point(nb, oracle, prec, shape):
+    """nb200_lstm_cell: K-concatenated gate GEMM + fused gate pass (bf16 / bf16x3), composed operators otherwise;
+    L != B exercises the joins over differing K extents (contraction over min(B, L))."""
+    from netsdb_b200 import lstm
+    L, D, B, bs = shape
+    d = make_inputs(L, D, B, 11)
+    want = oracle.lstm_cell({k: oracle.load_matrix(v, bs, bs) for k, v in d.items()}, threads=4)
+    sets = upload(nb, "lstm", d, bs)
+    for rep in range(2):  # the second call runs on the cached weight operand and the reused result sets
+        r = lstm.lstm_cell_fused("lstm", prec)
+        for k in OUT:
+            w, g = want[k].dense(), r[k].download_dense()
+            s = max(np.abs(w).max(), 1.0)
+            assert np.abs(g - w).max() <= TOL[prec] * s * (4 if k in ("c_t", "h_t") and prec != "fp64" else 1), (k, prec, rep)
+            assert r[k].info() == (L, B, bs, bs)
+    # a changed weight set invalidates the cached stacked operand
+    d["u_o"] = d["u_o"] * -1.0
+    sets["u_o"].upload_dense(np.ascontiguousarray(d["u_o"]))
+    want = oracle.lstm_cell({k: oracle.load_matrix(v, bs, bs) for k, v in d.items()}, threads=4)
+    r = lstm.lstm_cell_fused("lstm", prec)
+    for k in ("o_t", "h_t"):
+        w, g = want[k].dense(), r[k].download_dense()
+        assert np.abs(g - w).max() <= TOL[prec] * max(np.abs(w).max(), 1.0) * 4, (k, prec)
+    [s.destroy() for s in sets.values()]
+
+
+@pytest.mark.gpu
 def test_lstm_reference_driver_shape(nb, oracle):
     """LSTMTest.cc's sizes: the K extents of f_t (128 x 500) and c_t_1 (128 x 500) differ and the join keeps the
     leading column blocks only.  Gates and c_t equal the reference as written; h_t equals the zero-padding model."""
