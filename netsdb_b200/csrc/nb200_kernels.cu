@@ -833,6 +833,13 @@ __device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, do
                  : "d"(a), "d"(b));
 }
 
+// m16n8k4 (sm_90+): lane t, g = t / 4, q = t % 4 holds A[g][q], A[g+8][q]; B[q][g]; C[g][2q + {0,1}], C[g+8][2q + {0,1}].
+__device__ __forceinline__ void dmma_m16n8k4(double (&cfrag)[4], double a0, double a1, double b) {
+    asm volatile("mma.sync.aligned.m16n8k4.row.col.f64.f64.f64.f64 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
+                 : "+d"(cfrag[0]), "+d"(cfrag[1]), "+d"(cfrag[2]), "+d"(cfrag[3])
+                 : "d"(a0), "d"(a1), "d"(b));
+}
+
 // 128 threads = 4 warps arranged WARPS_M x WARPS_N, each warp computes a (8*MT) x 32 tile.
 template <int MT, int WARPS_M, int WARPS_N>
 __global__ void __launch_bounds__(128)
@@ -923,6 +930,88 @@ k_gemm_f64_mma(const double *__restrict__ u, long long u_ld, const double *__res
             }
 }
 
+// Skinny variant for the last cascade level (a handful of rows against all of W1): the kernel is a stream over V, so
+// what matters is bytes in flight.  16 x 128 tile, operands brought in by 16-byte cp.async into a 3-stage
+// shared-memory ring (zero fill past the ends), no register staging; sized for 3 CTAs per SM.  Needs 16-byte aligned rows (even pitches).
+__device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gsrc, int src_bytes) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+template <int STAGES, int BK, int BN>
+__global__ void __launch_bounds__(128)
+k_gemm_f64_mma_skinny(const double *__restrict__ u, long long u_ld, const double *__restrict__ v, long long v_ld, int M, int N,
+                      long long K, long long k_per_split, double *__restrict__ out, long long out_ld) {
+    constexpr int BM = 16, LDS = BK + 4, PIECES = BK / 2;  // 16-byte pieces per row
+    constexpr int NT = BN / 32;                            // n8 tiles per warp (4 warps side by side)
+    extern __shared__ __align__(16) double dyn_smem[];
+    double *su = dyn_smem;                         // [STAGES][BM * LDS]
+    double *sv = dyn_smem + STAGES * BM * LDS;     // [STAGES][BN * LDS]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long n0 = static_cast<long long>(blockIdx.x) * BN, m0 = static_cast<long long>(blockIdx.y) * BM;
+    const long long kbeg = static_cast<long long>(blockIdx.z) * k_per_split;
+    const long long kend = (kbeg + k_per_split < K) ? kbeg + k_per_split : K;
+    const int nk = kend > kbeg ? static_cast<int>((kend - kbeg + BK - 1) / BK) : 0;
+    double acc[NT][4];
+#pragma unroll
+    for (int j = 0; j < NT; j++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) acc[j][e] = 0.0;
+    // one stage = (BM + BN) rows x PIECES pieces of 16 bytes
+    auto issue = [&](int kb, int stage) {
+        const long long k0 = kbeg + static_cast<long long>(kb) * BK;
+#pragma unroll
+        for (int e = 0; e < ((BM + BN) * PIECES + 127) / 128; e++) {
+            const int idx = e * 128 + tid, r = idx / PIECES, piece = idx % PIECES;
+            if (r >= BM + BN) break;
+            const long long gk = k0 + piece * 2;
+            int bytes = 0;
+            if (gk < kend) bytes = (gk + 1 < kend) ? 16 : 8;
+            if (r < BM) {
+                const long long gm = m0 + r;
+                if (gm >= M) bytes = 0;
+                cp_async16_zfill(su + (stage * BM + r) * LDS + piece * 2, u + (bytes ? gm * u_ld + gk : 0), bytes);
+            } else {
+                const long long gn = n0 + (r - BM);
+                if (gn >= N) bytes = 0;
+                cp_async16_zfill(sv + (stage * BN + (r - BM)) * LDS + piece * 2, v + (bytes ? gn * v_ld + gk : 0), bytes);
+            }
+        }
+    };
+    for (int s = 0; s < STAGES - 1; s++) {
+        if (s < nk) issue(s, s);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int kb = 0; kb < nk; kb++) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 2) : "memory");
+        __syncthreads();  // stage kb has landed for everyone; stage kb-1's readers are done
+        if (kb + STAGES - 1 < nk) issue(kb + STAGES - 1, (kb + STAGES - 1) % STAGES);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const int st = kb % STAGES;
+        const double *pu = su + (st * BM + lane / 4) * LDS + lane % 4;
+        const double *pv = sv + (st * BN + warp * (8 * NT) + lane / 4) * LDS + lane % 4;
+#pragma unroll
+        for (int ks = 0; ks < BK; ks += 4) {
+            const double a0 = pu[ks], a1 = pu[8 * LDS + ks];
+            double b[NT];
+#pragma unroll
+            for (int j = 0; j < NT; j++) b[j] = pv[j * 8 * LDS + ks];
+#pragma unroll
+            for (int j = 0; j < NT; j++) dmma_m16n8k4(acc[j], a0, a1, b[j]);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NT; j++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const long long gm = m0 + (e >> 1) * 8 + lane / 4;
+            const long long gn = n0 + warp * (8 * NT) + j * 8 + 2 * (lane % 4) + (e & 1);
+            if (gm < M && gn < N) {
+                if (gridDim.z == 1) out[gm * out_ld + gn] = acc[j][e];
+                else atomicAdd(out + gm * out_ld + gn, acc[j][e]);
+            }
+        }
+}
+
 __global__ void k_bias_relu_f64(double *__restrict__ p, int M, int N, long long ld, const double *__restrict__ bias_m,
                                 const double *__restrict__ bias_n, int relu) {
     const long long n = static_cast<long long>(M) * N;
@@ -950,6 +1039,39 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
             const int64_t maxs = K / 2048;
             if (splits > maxs) splits = static_cast<int>(maxs);
             if (splits < 1) splits = 1;
+        }
+        // skinny + aligned: the cp.async streaming variant, 2 CTAs per SM, as many K splits as fill them
+        static const bool skinny_env = !(getenv("NB200_F64_SKINNY") && atoi(getenv("NB200_F64_SKINNY")) == 0);
+        const bool aligned = (u_sm % 2 == 0) && (v_sn % 2 == 0) && ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+        if (small && aligned && skinny_env && K >= 8192) {
+            static const int cfg = getenv("NB200_F64_CFG") ? atoi(getenv("NB200_F64_CFG")) : 0;
+            auto run = [&](auto kern, int BNs, int BKs, int ST, int ctas_per_sm) -> int {
+                const size_t smem = static_cast<size_t>(ST) * (16 + BNs) * (BKs + 4) * sizeof(double);
+                NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+                const int64_t tl = ceil_div(M, 16) * ceil_div(N, BNs);
+                int sp = static_cast<int>(ceil_div(static_cast<int64_t>(ctas_per_sm) * sms, tl));
+                if (sp > K / 2048) sp = static_cast<int>(K / 2048);
+                if (sp < 1) sp = 1;
+                const int64_t kp = round_up(ceil_div(K, sp), BKs);
+                sp = static_cast<int>(ceil_div(K, kp));
+                if (sp > 1) NB_CUDA(cudaMemset2DAsync(out, out_ld * sizeof(double), 0, static_cast<size_t>(N) * sizeof(double), M, c->stream));
+                dim3 g2(static_cast<unsigned>(ceil_div(N, BNs)), static_cast<unsigned>(ceil_div(M, 16)), sp);
+                kern<<<g2, 128, smem, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kp, out, out_ld);
+                return NB200_OK;
+            };
+            // measured on the Amazon shape (15 x 1000 x 597,540, tools/f64_skinny_bench.py): 16 x 64 tiles with BK = 32
+            // 1.145 ms, 16 x 128 with BK = 16 1.154 ms, register-staged kernel 1.277 ms; 16 x 32 tiles 1.8 - 2.0 ms.
+            // All sit at ~17 TFLOP/s of DMMA.8x8x4 (m16n8k4 lowers to two of them), not at the HBM roofline (0.73 ms).
+            if (cfg == 1) NB_TRY(run(k_gemm_f64_mma_skinny<3, 16, 128>, 128, 16, 3, 3));
+            else NB_TRY(run(k_gemm_f64_mma_skinny<3, 32, 64>, 64, 32, 3, 3));
+            NB_LAUNCH_CHECK(c);
+            if (e.bias_m || e.bias_n || e.relu) {
+                const int64_t n = static_cast<int64_t>(M) * N;
+                const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+                k_bias_relu_f64<<<blocks, 256, 0, c->stream>>>(out, M, N, out_ld, e.bias_m, e.bias_n, e.relu);
+                NB_LAUNCH_CHECK(c);
+            }
+            return NB200_OK;
         }
         const int64_t kper = round_up(ceil_div(K, splits), 16);
         splits = static_cast<int>(ceil_div(K, kper));

@@ -51,7 +51,8 @@ def test_block_upload_download_roundtrip(nb, oracle):
 
 
 @pytest.mark.parametrize("prec", ["fp64", "bf16x3", "bf16", "f16"])
-@pytest.mark.parametrize("shape", [(230, 310, 150, 100), (64, 128, 64, 64), (5, 7, 3, 4), (300, 2500, 129, 100)])
+@pytest.mark.parametrize("shape", [(230, 310, 150, 100), (64, 128, 64, 64), (5, 7, 3, 4), (300, 2500, 129, 100),
+                                   (12, 20002, 300, 1000), (16, 8222, 129, 100), (9, 9001, 40, 1000)])  # skinny: the streaming fp64 kernel
 def test_transpose_mult_and_input_layer_join(nb, oracle, prec, shape):
     I, K, J, blk = shape
     a, b = oracle.synth_dense(I, K, 11), oracle.synth_dense(J, K, 12)
