@@ -35,7 +35,10 @@ typedef enum {
 /* Join flavour: which reference JoinComp the block GEMM replaces. */
 typedef enum {
     NB200_OP_NT = 0, /* FFTransposeMult  (FFTransposeMult.h:38-39,80-92): C(i,j) = sum_k A(i,k) B(j,k)^T */
-    NB200_OP_NN = 1  /* FFInputLayerJoin (FFInputLayerJoin.h:30-31,72-86): C(i,j) = sum_k A(i,k) B(k,j)  */
+    NB200_OP_NN = 1, /* FFInputLayerJoin (FFInputLayerJoin.h:30-31,72-86): C(i,j) = sum_k A(i,k) B(k,j); also the LA DSL's
+                        LASillyMultiply1Join (sharedLibraries/headers/LASillyMultiply1Join.h:24-70) */
+    NB200_OP_TN = 2  /* LASillyTransposeMultiply1Join (LASillyTransposeMultiply1Join.h:24-70): predicate
+                        in1.blockRow == in2.blockRow, C(i,j) = sum_k A(k,i) B(k,j); no epilogue */
 } nb200_op;
 
 /* What is fused after the aggregation. */

@@ -46,6 +46,8 @@ HOST_BIN = os.path.join(HOST, "bin")
 HOST_SRCS = [os.path.join(HOST, "src", f) for f in ("SimpleFF.cc", "FFMatrixUtil.cc")]
 REF_DRIVER = "/root/reference/src/tests/source/FFTest.cc"
 REF_LSTM_DRIVER = "/root/reference/src/tests/source/LSTMTest.cc"
+REF_LA_DRIVERS = [("TestLA04_netsdb", "/root/reference/src/tests/source/TestLA04_Multiply.cc"),
+                  ("TestLA07_netsdb", "/root/reference/src/tests/source/TestLA07_TransposeMultiply_Gram.cc")]
 
 
 def build_host(force: bool = False) -> dict:
@@ -54,7 +56,9 @@ def build_host(force: bool = False) -> dict:
     FFTest          our driver in the shape of the reference's (adds a label dump for the parity tests)
     FFTest_netsdb   the reference's own, UNMODIFIED src/tests/source/FFTest.cc compiled in place against the
                     shim headers (only where /root/reference exists; the binary travels to the GPU box).
-    LSTMTest / LSTMTest_netsdb   the same pair for the LSTM cell (src/tests/source/LSTMTest.cc)."""
+    LSTMTest / LSTMTest_netsdb   the same pair for the LSTM cell (src/tests/source/LSTMTest.cc).
+    TestLA04_netsdb / TestLA07_netsdb   the LA DSL's multiply and Gram-matrix drivers (TestLA04_Multiply.cc,
+                    TestLA07_TransposeMultiply_Gram.cc), unmodified."""
     build()
     os.makedirs(HOST_BIN, exist_ok=True)
     inc = ["-I" + os.path.join(HERE, "..", "include"), "-I" + os.path.join(HOST, "include")]
@@ -66,6 +70,9 @@ def build_host(force: bool = False) -> dict:
         targets.append(("FFTest_netsdb", REF_DRIVER))
     if os.path.exists(REF_LSTM_DRIVER):
         targets.append(("LSTMTest_netsdb", REF_LSTM_DRIVER))
+    for name, src in REF_LA_DRIVERS:
+        if os.path.exists(src):
+            targets.append((name, src))
     for name, main_src in targets:
         exe = os.path.join(HOST_BIN, name)
         deps = [main_src, *HOST_SRCS, LIB] + [os.path.join(HOST, "include", f) for f in os.listdir(os.path.join(HOST, "include"))]

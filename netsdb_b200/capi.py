@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libnetsdb_b200.so")
 
 OK = 0
-OP_NT, OP_NN = 0, 1
+OP_NT, OP_NN, OP_TN = 0, 1, 2
 EPI_NONE, EPI_BIAS_RELU, EPI_BIAS_TRANSPOSE = 0, 1, 2
 PREC_BF16, PREC_BF16X3, PREC_FP64, PREC_F16 = 0, 1, 2, 3
 PRECISIONS = {"bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "fp64": PREC_FP64, "f16": PREC_F16}

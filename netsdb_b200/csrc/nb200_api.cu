@@ -532,15 +532,17 @@ static int bias_check(nb200_set *bias, int rows, const char *who) {
 static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision,
                             const char *db, const char *out_set, nb200_set **out, int extra_relu) {
     NEED_CTX();
-    if (!a || !b || !db || !out_set || !out || (op != NB200_OP_NT && op != NB200_OP_NN) || epilogue < 0 || epilogue > 2 ||
+    if (!a || !b || !db || !out_set || !out || (op != NB200_OP_NT && op != NB200_OP_NN && op != NB200_OP_TN) || (op == NB200_OP_TN && epilogue != NB200_EPI_NONE) || epilogue < 0 || epilogue > 2 ||
         precision < 0 || precision > 3) {
         set_error("gemm_blocks: invalid arguments");
         return NB200_ERR_INVALID;
     }
     // join predicate + per-pair dimension check (FFTransposeMult.h:38-39,61-65; FFInputLayerJoin.h:30-31,57-60)
-    const int Ka = a->total_cols;
+    // (LASillyTransposeMultiply1Join.h:24-33,44-47: there the rows of both operands are the contraction index)
+    const bool a_t = op == NB200_OP_TN;  // A enters transposed
+    const int Ka = a_t ? a->total_rows : a->total_cols;
     const int Kb = (op == NB200_OP_NT) ? b->total_cols : b->total_rows;
-    const int bkA = a->block_cols, bkB = (op == NB200_OP_NT) ? b->block_cols : b->block_rows;
+    const int bkA = a_t ? a->block_rows : a->block_cols, bkB = (op == NB200_OP_NT) ? b->block_cols : b->block_rows;
     if (bkA != bkB) {  // the per-pair check of the projection lambda
         set_error("Block dimemsions mismatch! (block K %d vs %d)", bkA, bkB);
         return NB200_ERR_SHAPE;
@@ -550,8 +552,8 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
     // inside the last matched block the shorter operand's zero padding cancels the rest: the contraction runs over
     // k < min(Ka, Kb).
     const int K = Ka < Kb ? Ka : Kb;
-    const int I = a->total_rows, J = (op == NB200_OP_NT) ? b->total_rows : b->total_cols;
-    const int bI = a->block_rows, bJ = (op == NB200_OP_NT) ? b->block_rows : b->block_cols;
+    const int I = a_t ? a->total_cols : a->total_rows, J = (op == NB200_OP_NT) ? b->total_rows : b->total_cols;
+    const int bI = a_t ? a->block_cols : a->block_rows, bJ = (op == NB200_OP_NT) ? b->block_rows : b->block_cols;
     if (epilogue != NB200_EPI_NONE) NB_TRY(bias_check(bias, I, epilogue == NB200_EPI_BIAS_RELU ? "ReluBiasSum" : "TransposeBiasSum"));
     const bool transpose_out = (epilogue == NB200_EPI_BIAS_TRANSPOSE);
     // output meta: FFTransposeMult.h:68-71 / FFInputLayerJoin.h:64-67 / FFTransposeBiasSum.h:64-67
@@ -567,7 +569,7 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
         F64Epilogue e;
         e.relu = relu;
         // element strides of A(i,k) and B'(j,k)
-        const int64_t a_sm = a->total_cols, a_sk = 1;
+        const int64_t a_sm = a_t ? 1 : a->total_cols, a_sk = a_t ? a->total_cols : 1;
         const int64_t b_sn = (op == NB200_OP_NT) ? b->total_cols : 1, b_sk = (op == NB200_OP_NT) ? 1 : b->total_cols;
         if (!transpose_out) {
             e.bias_m = bias ? bias->f64 : nullptr;
@@ -584,15 +586,17 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
     const bool lo = nterms == 3;
     const int fmt = (precision == NB200_PREC_F16) ? kFmtF16 : kFmtBF16;
     if (fmt == kFmtF16) {
-        NB_TRY(ensure_f16_row(c, a, 1));
+        if (a_t) NB_TRY(ensure_f16_col(c, a));
+        else NB_TRY(ensure_f16_row(c, a, 1));
         if (op == NB200_OP_NT) NB_TRY(ensure_f16_row(c, b, 1));
         else NB_TRY(ensure_f16_col(c, b));
     } else {
-        NB_TRY(ensure_rowp(c, a, lo));
+        if (a_t) NB_TRY(ensure_colp(c, a, lo));
+        else NB_TRY(ensure_rowp(c, a, lo));
         if (op == NB200_OP_NT) NB_TRY(ensure_rowp(c, b, lo));
         else NB_TRY(ensure_colp(c, b, lo));
     }
-    const Planes &pa = a->rowp;
+    const Planes &pa = a_t ? a->colp : a->rowp;
     const Planes &pb = (op == NB200_OP_NT) ? b->rowp : b->colp;
     const float *bias32 = nullptr;
     if (bias) {

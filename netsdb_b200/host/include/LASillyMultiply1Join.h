@@ -1,0 +1,3 @@
+// LASillyMultiply1Join.h -- same header name as sharedLibraries/headers/LASillyMultiply1Join.h; the class lives in la_udfs.h
+#pragma once
+#include "la_udfs.h"

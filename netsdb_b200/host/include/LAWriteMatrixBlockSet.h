@@ -1,0 +1,3 @@
+// LAWriteMatrixBlockSet.h -- same header name as sharedLibraries/headers/LAWriteMatrixBlockSet.h; the class lives in la_udfs.h
+#pragma once
+#include "la_udfs.h"

@@ -32,7 +32,7 @@ public:
         It(nb200_set *s, int idx, int n, int nbc) : s(s), idx(idx), n(n), nbc(nbc) {}
         bool operator!=(const It &o) const { return idx != o.idx; }
         void operator++() { idx++; }
-        Handle<T> operator*() const { return nb200_host::fetch_block(s, idx / nbc, idx % nbc); }
+        Handle<T> operator*() const { return nb200_host::fetch_block<T>(s, idx / nbc, idx % nbc); }
 
     private:
         nb200_set *s;
@@ -77,6 +77,7 @@ public:
         return true;
     }
     bool removeSet(const std::string &db, const std::string &set, std::string &) { return drop(db, set); }
+    bool deleteSet(std::string db, std::string set) { return drop(db, set); }  // mainClient/headers/PDBClient.h:253
     bool clearSet(const std::string &db, const std::string &set, const std::string &, std::string &) { return drop(db, set); }
     bool flushData(std::string &errMsg) { return ok(nb200_synchronize(), errMsg); }
 

@@ -16,6 +16,7 @@
 #include <set>
 #include <sstream>
 
+#include "la_udfs.h"
 #include "lstm_udfs.h"
 
 namespace nb200_host {
@@ -44,27 +45,35 @@ inline void ensure_init() {
 // total_rows / total_cols: extents to use when the block's meta leaves them at -1 (LSTMTest.cc:63-110 builds its blocks
 // with the 4-argument constructor); the caller derives them from the block grid, i.e. the set is carried with its
 // padding, exactly as the reference carries it
-inline int ship_block(const std::string &db, const std::string &set, pdb::Handle<FFMatrixBlock> &b, int total_rows = -1,
-                      int total_cols = -1) {
+template <class Block>
+inline int ship_block(const std::string &db, const std::string &set, pdb::Handle<Block> &b, int total_rows = -1, int total_cols = -1) {
     nb200_set *s = nullptr;
     if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) {
         // nominal block size = size of the first block sent (block (0,0) in ff::loadMatrix's order)
-        const int tr = b->getTotalRowNums() >= 0 ? b->getTotalRowNums() : total_rows;
-        const int tc = b->getTotalColNums() >= 0 ? b->getTotalColNums() : total_cols;
+        // FFMatrixMeta leaves unknown totals at -1, MatrixMeta at 0
+        const int tr = b->getTotalRowNums() > 0 ? b->getTotalRowNums() : total_rows;
+        const int tc = b->getTotalColNums() > 0 ? b->getTotalColNums() : total_cols;
         int st = nb200_set_create(db.c_str(), set.c_str(), tr, tc, b->getRowNums(),
                                   b->getColNums(), &s);
         if (st != NB200_OK) return st;
     }
-    return nb200_upload_block(s, b->getBlockRowIndex(), b->getBlockColIndex(), b->getValue().rawData->c_ptr(), b->getRowNums(),
+    return nb200_upload_block(s, b->getBlockRowIndex(), b->getBlockColIndex(), b->getRawDataHandle()->c_ptr(), b->getRowNums(),
                               b->getColNums());
 }
 
 // getSetIterator: re-wrap one device block as an FFMatrixBlock (full-size, zero padded, reference meta)
-inline pdb::Handle<FFMatrixBlock> fetch_block(nb200_set *s, int br, int bc) {
+template <class Block>
+inline pdb::Handle<Block> make_block(int br, int bc, int rows, int cols, int tr, int tc) { return pdb::makeObject<Block>(br, bc, rows, cols, tr, tc); }
+template <>
+inline pdb::Handle<FFMatrixBlock> make_block<FFMatrixBlock>(int br, int bc, int rows, int cols, int tr, int tc) {
+    return pdb::makeObject<FFMatrixBlock>(br, bc, rows, cols, tr, tc, false);
+}
+template <class Block = FFMatrixBlock>
+inline pdb::Handle<Block> fetch_block(nb200_set *s, int br, int bc) {
     int tr, tc, rows, cols;
     nb200_set_info(s, &tr, &tc, &rows, &cols);
-    pdb::Handle<FFMatrixBlock> out = pdb::makeObject<FFMatrixBlock>(br, bc, rows, cols, tr, tc, false);
-    if (nb200_download_block(s, br, bc, out->getValue().rawData->c_ptr(), rows, cols) != NB200_OK) {
+    pdb::Handle<Block> out = make_block<Block>(br, bc, rows, cols, tr, tc);
+    if (nb200_download_block(s, br, bc, out->getRawDataHandle()->c_ptr(), rows, cols) != NB200_OK) {
         std::cerr << nb200_last_error() << std::endl;
         exit(1);
     }
@@ -141,6 +150,17 @@ private:
         const std::string out = out_name.empty() ? tmp() : out_name;
         if (auto *scan = as<pdb::ScanSetBase>(c)) return lookup(scan->getDatabaseName(), scan->getSetName());
         if (as<FFAggMatrix>(c)) return lower_join(c, NB200_EPI_NONE, nullptr, db, out);
+        if (as<LASillyMultiply2Aggregate>(c)) {  // LA DSL: the same join + aggregation pair on MatrixBlock
+            pdb::Handle<pdb::Computation> join = c->getIthInput(0);
+            int op;
+            if (as<LASillyMultiply1Join>(join)) op = NB200_OP_NN;
+            else if (as<LASillyTransposeMultiply1Join>(join)) op = NB200_OP_TN;
+            else throw std::runtime_error("LASillyMultiply2Aggregate over an unsupported join (no CPU fallback)");
+            nb200_set *a = eval(join->getIthInput(0), db, ""), *b = eval(join->getIthInput(1), db, "");
+            nb200_set *o = nullptr;
+            check(nb200_gemm_blocks(op, a, b, NB200_EPI_NONE, nullptr, precision_from_env(), db.c_str(), out.c_str(), &o));
+            return o;
+        }
         if (auto *r = as<FFReluBiasSum>(c)) {
             dropout_must_be_zero(r);
             return lower_join(c->getIthInput(0), NB200_EPI_BIAS_RELU, eval(c->getIthInput(1), db, ""), db, out);

@@ -66,6 +66,8 @@ public:
     Handle &operator=(std::nullptr_t) { p.reset(); return *this; }
     const std::shared_ptr<T> &ptr() const { return p; }
     bool isNullPtr() const { return !p; }
+    // distance from the handle to its target (objectModel/headers/Handle.h:211); only ever printed by the drivers
+    int64_t getOffset() const { return reinterpret_cast<const char *>(p.get()) - reinterpret_cast<const char *>(this); }
 
 private:
     std::shared_ptr<T> p;
@@ -160,14 +162,18 @@ public:
     bool setInput(int slot, Handle<Computation> in) {
         if (static_cast<int>(inputs.size()) <= slot) inputs.resize(slot + 1);
         inputs[slot] = in;
+        if (in != nullptr) in->setNumConsumers(in->getNumConsumers() + 1);  // lambdas/headers/Computation.h:182
         return true;
     }
+    int getNumConsumers() { return numConsumers; }
+    void setNumConsumers(int n) { numConsumers = n; }
     int getNumInputs() const { return static_cast<int>(inputs.size()); }
     Handle<Computation> getIthInput(int i) const { return i < static_cast<int>(inputs.size()) ? inputs[i] : Handle<Computation>(); }
     void setAllocatorPolicy(int) {}
 
 private:
     std::vector<Handle<Computation>> inputs;
+    int numConsumers = 0;
 };
 
 // JoinComp<Out, In1, In2[, In3]> (lambdas/headers/JoinComp.h:44-45: up to five inputs there; the drivers of this

@@ -515,6 +515,26 @@ nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_s
     return out;
 }
 
+/* ------------------------------------------------------------------ LA DSL --------------- */
+/* LASillyTransposeMultiply1Join (sharedLibraries/headers/LASillyTransposeMultiply1Join.h:24-33 predicate
+ * in1.blockRow == in2.blockRow; :44-47 row counts must agree; :48-53 out block (in1.blockCol, in2.blockCol) of
+ * in1.colNums x in2.colNums, totals (in1.totalCols, in2.totalCols); product in1^T * in2) followed by
+ * LASillyMultiply2Aggregate (LASillyMultiply2Aggregate.h: key = block meta, value summed by MatrixData::operator+
+ * with the sum flag, MatrixData.h SumAggregate).  Restated as the block-wise transpose of `a` followed by the
+ * LASillyMultiply1Join shape (in1.blockCol == in2.blockRow, in1 * in2), which is FFInputLayerJoin's. */
+nbo_set *nbo_la_transpose_multiply_agg(const nbo_set *a, const nbo_set *b, int threads) {
+    nbo_set *at = nbo_set_new();
+    for (int x = 0; x < a->n; x++) {
+        const nbo_block *ba = &a->blocks[x];
+        nbo_block *o = set_add(at, ba->block_col, ba->block_row, ba->cols, ba->rows, ba->total_cols, ba->total_rows);
+        for (int i = 0; i < ba->rows; i++)
+            for (int j = 0; j < ba->cols; j++) o->data[(size_t)j * ba->rows + i] = ba->data[(size_t)i * ba->cols + j];
+    }
+    nbo_set *out = join_agg(at, b, 1, threads);
+    nbo_set_free(at);
+    return out;
+}
+
 /* ------------------------------------------------------------------ LSTM ----------------- */
 /* The two activations as LSTMThreeWaySum.h:79-90 writes them. */
 static double lstm_act(double s, int activation) {

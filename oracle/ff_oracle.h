@@ -94,6 +94,12 @@ nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_s
                                const nbo_set *b1, const nbo_set *bo, int threads,
                                nbo_set **logits_out, int32_t *labels);
 
+/* ---- LA DSL multiply joins on MatrixBlock (same block layout) --------------------------- */
+/* LASillyMultiply1Join + LASillyMultiply2Aggregate == nbo_input_layer_join_agg (same predicate and product,
+ * LASillyMultiply1Join.h:24-33, :44-70).  LASillyTransposeMultiply1Join + LASillyMultiply2Aggregate
+ * (LASillyTransposeMultiply1Join.h:24-70): out(i,j) = sum_k A(k,i) * B(k,j). */
+nbo_set *nbo_la_transpose_multiply_agg(const nbo_set *a, const nbo_set *b, int threads);
+
 /* ---- LSTM cell operators (src/LSTM/headers, wired by src/tests/source/LSTMTest.cc:204-543) -------------- */
 /* LSTMThreeWaySum (LSTMThreeWaySum.h:39-95): out = act(a + b + c) per block with equal (blockRow, blockCol);
  * activation 1 = Sigmod, 2 = Tanh (enum SumActivation, :12), 0 = none.  c == NULL: LSTMTwoSum (LSTMTwoSum.h:24-64).

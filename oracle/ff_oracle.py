@@ -56,7 +56,7 @@ def lib():
         L.nbo_load_matrix_synth.restype = vp
         L.nbo_load_matrix_synth.argtypes = [C.c_uint64, i, i, i, i]
         L.nbo_set_to_dense.argtypes = [vp, d, i, i]
-        for name in ("nbo_transpose_mult_agg", "nbo_input_layer_join_agg"):
+        for name in ("nbo_transpose_mult_agg", "nbo_input_layer_join_agg", "nbo_la_transpose_multiply_agg"):
             getattr(L, name).restype = vp
             getattr(L, name).argtypes = [vp, vp, i]
         for name in ("nbo_relu_bias_sum", "nbo_output_layer"):
@@ -147,6 +147,11 @@ def transpose_mult_agg(a: BlockSet, b: BlockSet, threads=1) -> BlockSet:
 
 def input_layer_join_agg(a: BlockSet, b: BlockSet, threads=1) -> BlockSet:
     return BlockSet(lib().nbo_input_layer_join_agg(a.ptr, b.ptr, threads))
+
+
+def la_transpose_multiply_agg(a: BlockSet, b: BlockSet, threads=1) -> BlockSet:
+    """LASillyTransposeMultiply1Join + LASillyMultiply2Aggregate: A^T . B."""
+    return BlockSet(lib().nbo_la_transpose_multiply_agg(a.ptr, b.ptr, threads))
 
 
 def relu_bias_sum(a: BlockSet, bias: BlockSet) -> BlockSet:
