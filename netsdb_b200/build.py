@@ -47,7 +47,8 @@ HOST_SRCS = [os.path.join(HOST, "src", f) for f in ("SimpleFF.cc", "FFMatrixUtil
 REF_DRIVER = "/root/reference/src/tests/source/FFTest.cc"
 REF_LSTM_DRIVER = "/root/reference/src/tests/source/LSTMTest.cc"
 REF_LA_DRIVERS = [("TestLA04_netsdb", "/root/reference/src/tests/source/TestLA04_Multiply.cc"),
-                  ("TestLA07_netsdb", "/root/reference/src/tests/source/TestLA07_TransposeMultiply_Gram.cc")]
+                  ("TestLA07_netsdb", "/root/reference/src/tests/source/TestLA07_TransposeMultiply_Gram.cc"),
+                  ("Word2Vec_netsdb", "/root/reference/src/word2vec/source/Word2Vec.cc")]
 
 
 def build_host(force: bool = False) -> dict:
@@ -58,7 +59,8 @@ def build_host(force: bool = False) -> dict:
                     shim headers (only where /root/reference exists; the binary travels to the GPU box).
     LSTMTest / LSTMTest_netsdb   the same pair for the LSTM cell (src/tests/source/LSTMTest.cc).
     TestLA04_netsdb / TestLA07_netsdb   the LA DSL's multiply and Gram-matrix drivers (TestLA04_Multiply.cc,
-                    TestLA07_TransposeMultiply_Gram.cc), unmodified."""
+                    TestLA07_TransposeMultiply_Gram.cc), unmodified.
+    Word2Vec_netsdb the word2vec embedding driver (src/word2vec/source/Word2Vec.cc), unmodified."""
     build()
     os.makedirs(HOST_BIN, exist_ok=True)
     inc = ["-I" + os.path.join(HERE, "..", "include"), "-I" + os.path.join(HOST, "include")]

@@ -21,6 +21,7 @@ void load_matrix_data(pdb::PDBClient &pdbClient, std::string path, std::string d
                       bool partitionByCol = true);
 void load_matrix_from_file(std::string path, std::vector<std::vector<double>> &matrix);
 void print_stats(pdb::PDBClient &pdbClient, std::string dbName, std::string setName);
+void print(pdb::PDBClient &pdbClient, std::string dbName, std::string setName);
 bool is_empty_set(pdb::PDBClient &pdbClient, pdb::CatalogClient &catalogClient, std::string dbName, std::string setName);
 uint64_t seed_of_set(const std::string &setName);
 double synth_value(uint64_t seed, uint64_t index);

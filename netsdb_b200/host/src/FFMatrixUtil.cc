@@ -122,6 +122,18 @@ void print_stats(pdb::PDBClient &pdbClient, std::string dbName, std::string setN
               << cols << std::endl;
 }
 
+// FFMatrixUtil.cc:388-415 of the reference: the set's totals from its first block, then the number of blocks (the
+// per-element dump is commented out there)
+void print(pdb::PDBClient &pdbClient, std::string dbName, std::string setName) {
+    int count = 0;
+    auto it = pdbClient.getSetIterator<FFMatrixBlock>(dbName, setName);
+    for (auto r : it) {
+        if (count == 0) std::cout << "[STATS] " << setName << " : " << r->getTotalRowNums() << " X " << r->getTotalColNums() << std::endl;
+        count++;
+    }
+    std::cout << "count = " << count << std::endl;
+}
+
 bool is_empty_set(pdb::PDBClient &pdbClient, pdb::CatalogClient &catalogClient, std::string dbName, std::string setName) {
     if (!catalogClient.setExists(dbName, setName)) return true;
     auto it = pdbClient.getSetIterator<FFMatrixBlock>(dbName, setName);

@@ -331,6 +331,25 @@ def test_k_sharded_variant_two_gpus():
     assert r.stdout.count("OK  k-sharded") == 3
 
 
+def test_unmodified_reference_word2vec_driver(tmp_path):
+    """netsDB's own src/word2vec/source/Word2Vec.cc compiled unmodified against the shim: loads `inputs` and
+    `weights0` from text files (ff::load_matrix_data), runs FFTransposeMult + FFAggMatrix through
+    executeComputations(errMsg, jobName, materializeHash, sink) and reports the shape of `outputs`."""
+    from netsdb_b200 import build
+
+    exe = os.path.join(build.HOST_BIN, "Word2Vec_netsdb")
+    if not os.path.exists(exe):
+        pytest.skip("reference driver was not built (no reference tree at build time)")
+    rng = np.random.default_rng(3)
+    for name, shape in (("inputs", (30, 400)), ("weights0", (20, 400))):
+        with open(tmp_path / f"{name}.txt", "w") as f:
+            f.write(f"{shape[0]}, {shape[1]}\n")
+            np.savetxt(f, rng.uniform(-1, 1, shape), fmt="%.17g")
+    r = _run([exe, "50", "50", "Y", "1", str(tmp_path)], {"NB200_PRECISION": "bf16x3"}, timeout=180)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "[STATS] outputs : 20 X 30" in r.stdout and "count = 1" in r.stdout  # embedding_dimension x batch, one block
+
+
 @pytest.mark.parametrize("shape", [(2, 3, 20, 19, 5, 3, 0), (3, 8, 17, 150, 40, 3, 1), (2, 64, 30, 30, 64, 3, 0),
                                    (1, 70, 12, 140, 130, 5, 2), (2, 3, 16, 16, 7, 7, 3)])
 def test_conv2d_implicit_gemm_vs_blocked_oracle(nb, oracle, shape):
