@@ -43,12 +43,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 HOST = os.path.join(HERE, "host")
 HOST_BIN = os.path.join(HOST, "bin")
-HOST_SRCS = [os.path.join(HOST, "src", f) for f in ("SimpleFF.cc", "FFMatrixUtil.cc")]
+HOST_SRCS = [os.path.join(HOST, "src", f) for f in ("SimpleFF.cc", "FFMatrixUtil.cc", "ImageUtils.cc")]
 REF_DRIVER = "/root/reference/src/tests/source/FFTest.cc"
 REF_LSTM_DRIVER = "/root/reference/src/tests/source/LSTMTest.cc"
 REF_LA_DRIVERS = [("TestLA04_netsdb", "/root/reference/src/tests/source/TestLA04_Multiply.cc"),
                   ("TestLA07_netsdb", "/root/reference/src/tests/source/TestLA07_TransposeMultiply_Gram.cc"),
-                  ("Word2Vec_netsdb", "/root/reference/src/word2vec/source/Word2Vec.cc")]
+                  ("Word2Vec_netsdb", "/root/reference/src/word2vec/source/Word2Vec.cc"),
+                  ("PipelinedConv2dMemFuseTest_netsdb", "/root/reference/src/tests/source/PipelinedConv2dMemFuseTest.cc")]
 
 
 def build_host(force: bool = False) -> dict:
@@ -67,7 +68,8 @@ def build_host(force: bool = False) -> dict:
     common = ["/usr/bin/g++", "-std=c++17", "-O2", "-ffp-contract=off", *inc]
     link = ["-L" + HERE, "-lnetsdb_b200", "-Wl,-rpath,$ORIGIN/../.."]
     out = {}
-    targets = [("FFTest", os.path.join(HOST, "src", "FFTest.cc")), ("LSTMTest", os.path.join(HOST, "src", "LSTMTest.cc"))]
+    targets = [("FFTest", os.path.join(HOST, "src", "FFTest.cc")), ("LSTMTest", os.path.join(HOST, "src", "LSTMTest.cc")),
+               ("Conv2dMemFuseTest", os.path.join(HOST, "src", "Conv2dMemFuseTest.cc"))]
     if os.path.exists(REF_DRIVER):
         targets.append(("FFTest_netsdb", REF_DRIVER))
     if os.path.exists(REF_LSTM_DRIVER):

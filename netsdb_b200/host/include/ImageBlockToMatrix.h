@@ -1,0 +1,3 @@
+// ImageBlockToMatrix.h -- same header name as src/conv2d_memory_fusion/headers/ImageBlockToMatrix.h; the class lives in conv_udfs.h
+#pragma once
+#include "conv_udfs.h"

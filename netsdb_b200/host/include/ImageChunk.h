@@ -1,0 +1,3 @@
+// ImageChunk.h -- same header name as src/conv2d_memory_fusion/headers/ImageChunk.h; the class lives in conv_udfs.h
+#pragma once
+#include "conv_udfs.h"

@@ -32,13 +32,19 @@ public:
         It(nb200_set *s, int idx, int n, int nbc) : s(s), idx(idx), n(n), nbc(nbc) {}
         bool operator!=(const It &o) const { return idx != o.idx; }
         void operator++() { idx++; }
-        Handle<T> operator*() const { return nb200_host::fetch_block<T>(s, idx / nbc, idx % nbc); }
+        It(const std::vector<Handle<T>> *host, int idx) : s(nullptr), idx(idx), n(0), nbc(1), host(host) {}
+        Handle<T> operator*() const {
+            if constexpr (std::is_base_of<conv2d_memory_fusion::Matrix3D, T>::value) return (*host)[idx];
+            else return nb200_host::fetch_block<T>(s, idx / nbc, idx % nbc);
+        }
 
     private:
         nb200_set *s;
         int idx, n, nbc;
+        const std::vector<Handle<T>> *host = nullptr;
     };
     SetIterator() {}
+    explicit SetIterator(const std::vector<Handle<T>> *records) : host(records) {}
     explicit SetIterator(nb200_set *s) : s(s) {
         if (s) {
             int tr, tc, br, bc;
@@ -47,12 +53,13 @@ public:
             nbc = (tc + bc - 1) / bc;
         }
     }
-    It begin() { return It(s, 0, nbr * nbc, nbc > 0 ? nbc : 1); }
-    It end() { return It(s, nbr * nbc, nbr * nbc, nbc > 0 ? nbc : 1); }
+    It begin() { return host ? It(host, 0) : It(s, 0, nbr * nbc, nbc > 0 ? nbc : 1); }
+    It end() { return host ? It(host, static_cast<int>(host->size())) : It(s, nbr * nbc, nbr * nbc, nbc > 0 ? nbc : 1); }
 
 private:
     nb200_set *s = nullptr;
     int nbr = 0, nbc = 0;
+    const std::vector<Handle<T>> *host = nullptr;
 };
 
 class PDBClient {
@@ -85,6 +92,13 @@ public:
     template <class T>
     bool sendData(std::pair<std::string, std::string> setAndDatabase, Handle<Vector<Handle<T>>> data, std::string &errMsg) {
         const std::string &set = setAndDatabase.first, &db = setAndDatabase.second;
+        if constexpr (std::is_base_of<conv2d_memory_fusion::Matrix3D, T>::value) {
+            // Image / Kernel records stay on the host until a job scans them (conv_stage.h)
+            auto &dst = nb200_host::host_sets<T>()[std::make_pair(db, set)];
+            for (size_t i = 0; i < data->size(); i++) dst.push_back((*data)[i]);
+            (void)errMsg;
+            return true;
+        } else {
         int tr = 0, tc = 0;  // extents of the block grid, for blocks whose meta carry no totals
         for (size_t i = 0; i < data->size(); i++) {
             Handle<T> &b = (*data)[i];
@@ -94,6 +108,7 @@ public:
         for (size_t i = 0; i < data->size(); i++)
             if (!ok(nb200_host::ship_block(db, set, (*data)[i], tr, tc), errMsg)) return false;
         return ok(nb200_synchronize(), errMsg);  // the caller reuses its allocation block after sendData
+        }
     }
 
     template <class... Sinks>
@@ -113,6 +128,11 @@ public:
 
     template <class T>
     SetIterator<T> getSetIterator(const std::string &db, const std::string &set) {
+        if constexpr (std::is_base_of<conv2d_memory_fusion::Matrix3D, T>::value) {
+            auto &m = nb200_host::host_sets<T>();
+            auto it = m.find(std::make_pair(db, set));
+            return it == m.end() ? SetIterator<T>() : SetIterator<T>(&it->second);
+        }
         nb200_set *s = nullptr;
         if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) return SetIterator<T>();
         return SetIterator<T>(s);
@@ -130,6 +150,7 @@ private:
         return false;
     }
     bool drop(const std::string &db, const std::string &set) {
+        nb200_host::host_set_drop(db, set);
         nb200_set *s = nullptr;
         if (nb200_set_lookup(db.c_str(), set.c_str(), &s) == NB200_OK) nb200_set_destroy(s);
         return true;

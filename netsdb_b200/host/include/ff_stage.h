@@ -16,6 +16,7 @@
 #include <set>
 #include <sstream>
 
+#include "conv_stage.h"
 #include "la_udfs.h"
 #include "lstm_udfs.h"
 
@@ -92,6 +93,7 @@ public:
                 auto *w = dynamic_cast<pdb::WriteSetBase *>(sink.ptr().get());
                 if (!w) throw std::runtime_error("sink is not a WriteUserSet");
                 if (try_inference_unit(w)) continue;
+                if (ConvStage::try_run(w)) continue;
                 eval(w->getIthInput(0), w->getDatabaseName(), w->getSetName());
             }
         } catch (const std::exception &e) {

@@ -100,6 +100,20 @@ private:
     std::vector<T> v;
 };
 
+// pdb::Map (builtInPDBObjects/headers/PDBMap.h): the slice the conv UDF types use
+template <class K, class V>
+class Map : public Object {
+public:
+    V &operator[](const K &k) { return m[k]; }
+    int count(const K &k) { return static_cast<int>(m.count(k)); }
+    size_t size() const { return m.size(); }
+    typename std::map<K, V>::iterator begin() { return m.begin(); }
+    typename std::map<K, V>::iterator end() { return m.end(); }
+
+private:
+    std::map<K, V> m;
+};
+
 using String = std::string;
 inline void makeObjectAllocatorBlock(size_t, bool) {}
 struct UseTemporaryAllocationBlock {

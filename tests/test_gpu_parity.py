@@ -401,6 +401,31 @@ def test_conv2d_result_to_images(nb, oracle, shape):
             nb.conv2d_result_to_images(R, n, hout, wout, kout - 1)
 
 
+@pytest.mark.parametrize("cfg", [(2, 3, 20, 19, 5, 3, 1, 0, 32, 32, "fp64"), (3, 4, 12, 12, 6, 3, 2, 1, 16, 10, "fp64"),
+                                 (2, 8, 17, 30, 40, 3, 1, 1, 64, 64, "bf16x3")])
+def test_cpp_conv2d_driver_through_netsdb_api(oracle, tmp_path, cfg):
+    """The C++ host shim for conv2d_memory_fusion: Conv2dMemFuseTest builds the reference's four jobs from its
+    Computation classes (KernelToChunks / ImageToChunks -> ImageChunksToBlock -> ImageBlockToMatrix [-> KernelBiasJoin],
+    FFTransposeMult + FFAggMatrix, ConvResultToChunks -> ImageChunksToBlock -> ConvChunksToImage) and the shim lowers
+    each job to the device; the re-assembled images are compared with the oracle's pipeline on the same data."""
+    from netsdb_b200 import build
+
+    exe = build.build_host()["Conv2dMemFuseTest"]
+    n, c, h, w, kout, k, stride, pad, bx, by, prec = cfg
+    r = _run([exe] + [str(v) for v in (n, c, h, w, kout, k, stride, pad, bx, by)] + [str(tmp_path)], {"NB200_PRECISION": prec}, timeout=120)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    imgs = oracle.synth_dense(n * c, h * w, 41).reshape(n, c, h, w)
+    kern = oracle.synth_dense(kout * c, k * k, 42).reshape(kout, c, k, k)
+    bias = oracle.synth_dense(kout, 1, 43).reshape(kout)
+    hout, wout = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    ref = oracle.transpose_mult_agg(oracle.image_flat(imgs, k, stride, pad, bx, by), oracle.kernel_flat(kern, bias, bx, by), 2)
+    want = oracle.conv_result_to_images(ref, n, hout, wout, kout)
+    got = np.loadtxt(tmp_path / "images.out.txt").reshape(n, kout, hout, wout)
+    assert np.abs(got - want).max() <= TOL[prec] * np.abs(want).max()
+    assert f"images={n}" in r.stdout
+    assert f"result ( {n * hout * wout} X {kout} )" in r.stdout
+
+
 @pytest.mark.parametrize("shape", [(2400, 9000, 700, 50, 500), (2048, 8200, 300, 20, 1000)])
 def test_fused_layer1_kernel_vs_oracle(nb, oracle, shape):
     """Shapes large enough for the fused layer-1 kernel (fp64 -> fp16 conversion inside the persistent 2-SM GEMM through
