@@ -86,6 +86,40 @@ def build_host(force: bool = False) -> dict:
     return out
 
 
+# The reference's one-line GET_V_TABLE(Type) sources, compiled unmodified into lib<Type>.so (the netsDB plugin ABI)
+HOST_LIBRARIES = os.path.join(HOST, "libraries")
+REF_UDF_SOURCES = {
+    "/root/reference/src/FF/source": ["FFMatrixMeta", "FFMatrixData", "FFMatrixBlock", "FFMatrixBlockScanner", "FFMatrixWriter",
+                                      "FFInputLayerJoin", "FFAggMatrix", "FFReluBiasSum", "FFTransposeMult", "FFTransposeBiasSum",
+                                      "FFRowAggregate", "FFOutputLayer"],
+    "/root/reference/src/LSTM/source": ["LSTMThreeWaySum", "LSTMTwoSum", "LSTMHiddenState"],
+    "/root/reference/src/conv2d_memory_fusion/source": ["Image", "Kernel", "ImageChunk", "ImageBlock", "ImageToChunks", "ImageChunksToBlock",
+                                                        "ImageBlockToMatrix", "KernelToChunks", "KernelBiasJoin", "ConvResultToChunks",
+                                                        "ConvChunksToImage"],
+    "/root/reference/src/sharedLibraries/source": ["MatrixMeta", "MatrixData", "MatrixBlock", "LAScanMatrixBlockSet", "LAWriteMatrixBlockSet",
+                                                   "LASillyMultiply1Join", "LASillyTransposeMultiply1Join", "LASillyMultiply2Aggregate"],
+}
+
+
+def build_udf_libraries(force: bool = False) -> list:
+    """lib<Type>.so for every type of the path, from the reference's own GET_V_TABLE sources (only where the reference
+    tree is present; the libraries travel with the repository snapshot like the other built binaries)."""
+    os.makedirs(HOST_LIBRARIES, exist_ok=True)
+    inc = ["-I" + os.path.join(HERE, "..", "include"), "-I" + os.path.join(HOST, "include")]
+    out = []
+    for src_dir, types in REF_UDF_SOURCES.items():
+        for t in types:
+            src = os.path.join(src_dir, t + ".cc")
+            lib = os.path.join(HOST_LIBRARIES, f"lib{t}.so")
+            if os.path.exists(src) and (force or not os.path.exists(lib) or os.path.getmtime(src) > os.path.getmtime(lib)
+                                        or os.path.getmtime(os.path.join(HOST, "include", "GetVTable.h")) > os.path.getmtime(lib)):
+                subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O2", "-shared", "-fPIC", *inc, src, "-o", lib])
+            if os.path.exists(lib):
+                out.append(lib)
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
     print(build_host(force="--force" in sys.argv))
+    print(len(build_udf_libraries(force="--force" in sys.argv)), "UDF libraries")

@@ -3,6 +3,7 @@
 // Calls return bool + errMsg like the reference's; nothing here computes on the host.
 #pragma once
 // the real PDBClient.h pulls these in transitively and the reference drivers rely on that
+#include <dlfcn.h>
 #include <unistd.h>
 
 #include <chrono>
@@ -70,7 +71,40 @@ public:
 
     bool createDatabase(const std::string &, std::string &) { return true; }
     bool removeDatabase(const std::string &, std::string &) { return true; }
-    bool registerType(const std::string &, std::string &) { return true; }  // UDF .so shipping: nothing to ship
+    // registerType (mainClient/headers/PDBClient.h:176-180): the reference ships the UDF's shared library to the catalog.
+    // In process there is nothing to ship; when the library exists (as given, under $NB200_LIBRARIES, or next to the
+    // driver: <exe dir>/../<path>) it is loaded and its plugin ABI checked -- getObjectTypeName / getObjectVTable /
+    // setAllGlobalVariables, GetVTable.h -- and a broken library fails the call.  A path that does not exist is accepted:
+    // the shim's types are compiled into the driver.
+    bool registerType(const std::string &fileContainingSharedLib, std::string &errMsg) {
+        std::vector<std::string> candidates{fileContainingSharedLib};
+        const std::string base = fileContainingSharedLib.substr(fileContainingSharedLib.find_last_of('/') + 1);
+        if (const char *e = getenv("NB200_LIBRARIES")) candidates.push_back(std::string(e) + "/" + base);
+        char self[4096];
+        const ssize_t len = readlink("/proc/self/exe", self, sizeof(self) - 1);
+        if (len > 0) {
+            std::string exe(self, len);
+            candidates.push_back(exe.substr(0, exe.find_last_of('/')) + "/../" + fileContainingSharedLib);
+        }
+        for (const std::string &path : candidates) {
+            if (access(path.c_str(), R_OK) != 0) continue;
+            void *h = dlopen(path.c_str(), RTLD_LOCAL | RTLD_LAZY);  // the flags of VTableMapCatalogLookup.cc:92
+            if (!h) { errMsg = std::string("registerType: ") + dlerror(); return false; }
+            typedef char *(*name_fn)();
+            typedef void *(*vtable_fn)();
+            typedef void (*globals_fn)(void *, void *, void *, void *);  // (Allocator *, VTableMap *, stackBase, stackEnd)
+            name_fn getName = reinterpret_cast<name_fn>(dlsym(h, "getObjectTypeName"));
+            vtable_fn getVTable = reinterpret_cast<vtable_fn>(dlsym(h, "getObjectVTable"));
+            globals_fn setGlobals = reinterpret_cast<globals_fn>(dlsym(h, "setAllGlobalVariables"));
+            if (!getName || !getVTable || !setGlobals) { errMsg = "registerType: " + path + " does not export the plugin ABI"; return false; }
+            setGlobals(nullptr, nullptr, nullptr, nullptr);
+            if (!getVTable()) { errMsg = "registerType: " + path + ": no vtable"; return false; }
+            registered[getName()] = path;
+            return true;
+        }
+        return true;
+    }
+    const std::map<std::string, std::string> &registeredTypes() const { return registered; }
     // the device set is sized when the first block arrives (sendData), as the reference's set is filled by sendData
     template <class T>
     bool createSet(const std::string &db, const std::string &set, std::string &, size_t = 0, const std::string & = "",
@@ -156,6 +190,7 @@ private:
         return true;
     }
     std::set<std::pair<std::string, std::string>> declared;
+    std::map<std::string, std::string> registered;  // type name -> library it was loaded from
 };
 
 }  // namespace pdb

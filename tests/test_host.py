@@ -67,3 +67,31 @@ def test_cpp_shim_drivers_compile():
     assert os.path.exists(exes["FFTest"])
     if os.path.exists(build.REF_DRIVER):
         assert os.path.exists(exes["FFTest_netsdb"])
+
+
+def test_udf_plugin_libraries_export_the_netsdb_abi():
+    """Every user type of the path as its own lib<Type>.so, built from the reference's unmodified one-line
+    GET_V_TABLE(Type) sources against the shim classes: the three extern "C" symbols a netsDB catalog / worker binds
+    (objectModel/headers/GetVTable.h:8-58) are there and answer."""
+    import ctypes as C
+    import glob
+
+    from netsdb_b200 import build
+
+    if os.path.exists("/root/reference"):
+        build.build_udf_libraries()
+    libs = sorted(glob.glob(os.path.join(build.HOST_LIBRARIES, "lib*.so")))
+    if not libs:
+        pytest.skip("UDF libraries were not built (no reference tree at build time)")
+    expected = {t for types in build.REF_UDF_SOURCES.values() for t in types}
+    assert {os.path.basename(p)[3:-3] for p in libs} == expected
+    for path in libs:
+        t = os.path.basename(path)[3:-3]
+        lib = C.CDLL(path, mode=getattr(os, "RTLD_LOCAL", 0) | os.RTLD_LAZY)
+        lib.getObjectTypeName.restype = C.c_char_p
+        lib.getObjectVTable.restype = C.c_void_p
+        lib.setAllGlobalVariables.argtypes = [C.c_void_p] * 4
+        lib.setAllGlobalVariables(None, None, None, None)
+        name = lib.getObjectTypeName().decode()
+        assert name in (t, "conv2d_memory_fusion::" + t), (path, name)
+        assert lib.getObjectVTable()
