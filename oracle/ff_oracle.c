@@ -1,6 +1,6 @@
 /*
- * ff_oracle.c -- see ff_oracle.h.  TEST INFRASTRUCTURE ONLY; PARITY UNPINNED (no reference
- * golden vectors exist and the reference cannot be built here).
+ * ff_oracle.c -- see ff_oracle.h.  TEST INFRASTRUCTURE ONLY.  Parity: pinned against the reference's own UDF
+ * headers compiled unmodified (oracle/ref, tests/test_oracle_pinned.py), not against a reference binary.
  *
  * Build: gcc -O3 -fopenmp -ffp-contract=off -shared -fPIC (oracle/Makefile).  The GEMM micro
  * kernels carry their own target attributes (AVX2+FMA / AVX-512) and are picked at run time,
@@ -85,6 +85,9 @@ static nbo_block *set_add(nbo_set *s, int br, int bc, int rows, int cols, int tr
     if (!b->data) { fprintf(stderr, "nbo: out of memory\n"); abort(); }
     return b;
 }
+
+/* exported for oracle/ref/ref_harness.cc, which converts the reference's FFMatrixBlocks into sets of this library */
+nbo_block *nbo_set_add_block(nbo_set *s, int br, int bc, int rows, int cols, int tr, int tc) { return set_add(s, br, bc, rows, cols, tr, tc); }
 
 static int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
@@ -512,6 +515,57 @@ nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_s
         free(best);
     }
     if (logits_out) *logits_out = logits; else nbo_set_free(logits);
+    return out;
+}
+
+/* ------------------------------------------------------------------ as written ----------- */
+/* The two UDFs whose bodies in this fork do not do what their declarations say, restated AS WRITTEN.
+ * They exist to pin this file against the reference's code where it is compiled (oracle/ref) and to document the
+ * quirks; the pipeline above uses the intended forms.
+ *
+ * FFTransposeBiasSum.h:64-104 as written: the output block is declared transposed -- (blockCol, blockRow), J x I,
+ * totals swapped -- and zero filled; only its first I elements receive in1[p] + in2[p] (both operands are mapped as
+ * I x 1, :73-84); then exp() runs over i * J + j for every (i, j) whose un-padded coordinate lies inside in1's totals
+ * (:94-104), so almost every in-range entry becomes exp(0) = 1. */
+nbo_set *nbo_transpose_bias_sum_as_written(const nbo_set *in, const nbo_set *bias) {
+    nbo_set *out = nbo_set_new();
+    for (int x = 0; x < in->n; x++) {
+        const nbo_block *a = &in->blocks[x];
+        for (int y = 0; y < bias->n; y++) {
+            const nbo_block *bb = &bias->blocks[y];
+            if (bb->block_row != a->block_row) continue;
+            if (a->rows != bb->rows || bb->cols != 1) { fprintf(stderr, "Block dimemsions mismatch!\n"); nbo_set_free(out); return NULL; }
+            const int I = a->rows, J = a->cols;
+            nbo_block *o = set_add(out, a->block_col, a->block_row, J, I, a->total_cols, a->total_rows);
+            for (int p = 0; p < I; p++) o->data[p] = a->data[p] + bb->data[p];
+            for (int i = 0; i < I; i++)
+                for (int j = 0; j < J; j++)
+                    if (a->block_row * I + i < a->total_rows && a->block_col * J + j < a->total_cols)
+                        o->data[(size_t)i * J + j] = exp(o->data[(size_t)i * J + j]);
+        }
+    }
+    return out;
+}
+/* FFOutputLayer.h:31-57 as written: out[i * I + j] = in1[i * I + j] / (1 + in1[i * I + j]) (stride I instead of J, and
+ * the row sum in2 is not used: "used to be in2Data[i]").  With I > J the reference writes past the end of the block;
+ * this restatement refuses such shapes. */
+nbo_set *nbo_output_layer_as_written(const nbo_set *in, const nbo_set *rowsum) {
+    nbo_set *out = nbo_set_new();
+    for (int x = 0; x < in->n; x++) {
+        const nbo_block *a = &in->blocks[x];
+        for (int y = 0; y < rowsum->n; y++) {
+            const nbo_block *rs = &rowsum->blocks[y];
+            if (rs->block_row != a->block_row) continue;
+            if (a->rows != rs->rows || rs->cols != 1 || a->rows > a->cols) { fprintf(stderr, "[FFOutputLayer] Cannot divide! Dimensions mismatch!\n"); nbo_set_free(out); return NULL; }
+            const int I = a->rows, J = a->cols;
+            nbo_block *o = set_add(out, a->block_row, a->block_col, I, J, a->total_rows, a->total_cols);
+            for (int i = 0; i < I; i++)
+                for (int j = 0; j < J; j++) {
+                    const size_t pos = (size_t)i * I + j;
+                    o->data[pos] = a->data[pos] / (1 + a->data[pos]);
+                }
+        }
+    }
     return out;
 }
 

@@ -6,12 +6,18 @@
  * bench.py's cpu_baseline / --impl reference legs may load it.  The product path
  * (libnetsdb_b200.so) never links, loads or calls anything in oracle/.
  *
- * PARITY UNPINNED: the reference ships no golden vectors, known-answer tests or fixtures for
- * this path and cannot be compiled here (its FF headers need Eigen 3,
- * which is absent, and the object model needs SCons-generated sources).  The oracle is
- * therefore a restatement of the UDF arithmetic, cross-checked against a dense numpy fp64
- * evaluation (oracle/ff_oracle.py) and hand-computable KATs (tests/golden/), not against
- * outputs of the reference binary.
+ * PARITY PINNED AGAINST THE REFERENCE'S OWN UDF CODE (not against a reference binary): the
+ * reference ships no golden vectors, known-answer tests or fixtures for this path (SURVEY.md
+ * section 4) and its build cannot run here (SCons-generated object model, Eigen 3 absent).  What
+ * does compile is the part that carries the arithmetic: netsDB's UDF headers, unmodified, from
+ * where they lie under /root/reference, around a stand-in object model and a plain-loop stand-in
+ * for the five Eigen expressions they use (oracle/ref/, `make -C oracle ref` ->
+ * oracle/_ref/libff_ref.so).  tests/test_oracle_pinned.py runs every operator of this file and
+ * the reference's own lambda bodies on the same blocks and compares keys, meta, padding and
+ * values (exact, or 1e-13 where a product's summation order differs); tests/golden/ref_pinned.npz
+ * holds vectors recorded from that code for machines without the reference tree.  Not pinned:
+ * Eigen's own dgemm summation order (third-party, unpinned version) and anything above the UDFs
+ * (planner, shuffle, multi-threaded arrival order).
  *
  * Each function cites the reference file:line it follows (paths relative to the netsDB tree).
  * Where this fork's debugging edits changed results the
@@ -51,6 +57,8 @@ void nbo_synth_dense(double *out, int64_t rows, int64_t cols, uint64_t seed);
 
 /* ---- sets ------------------------------------------------------------------------------ */
 nbo_set *nbo_set_new(void);
+/* appends a zero-filled block and returns it */
+nbo_block *nbo_set_add_block(nbo_set *s, int block_row, int block_col, int rows, int cols, int total_rows, int total_cols);
 void nbo_set_free(nbo_set *s);
 int nbo_set_size(const nbo_set *s);
 const nbo_block *nbo_set_get(const nbo_set *s, int i);
@@ -93,6 +101,11 @@ nbo_set *nbo_output_layer(const nbo_set *in, const nbo_set *rowsum);
 nbo_set *nbo_ff_inference_unit(const nbo_set *w1, const nbo_set *wo, const nbo_set *inputs,
                                const nbo_set *b1, const nbo_set *bo, int threads,
                                nbo_set **logits_out, int32_t *labels);
+
+/* The same two UDFs AS WRITTEN in this fork (quirks Q1, Q2): for pinning against the reference's code and for
+ * documentation only; see the comments at their definitions. */
+nbo_set *nbo_transpose_bias_sum_as_written(const nbo_set *in, const nbo_set *bias);
+nbo_set *nbo_output_layer_as_written(const nbo_set *in, const nbo_set *rowsum);
 
 /* ---- LA DSL multiply joins on MatrixBlock (same block layout) --------------------------- */
 /* LASillyMultiply1Join + LASillyMultiply2Aggregate == nbo_input_layer_join_agg (same predicate and product,

@@ -3,10 +3,11 @@
 TEST INFRASTRUCTURE ONLY -- imported by tests/, __graft_entry__.smoke() and bench.py's
 cpu_baseline / --impl reference legs; never by the product package (netsdb_b200/).
 
-PARITY UNPINNED: the reference (venkate5hgunda/netsdb) ships no golden vectors for the FF /
-conv2d_memory_fusion / word2vec path and cannot be built here (Eigen absent, SCons-generated
-sources).  The C oracle restates the UDF arithmetic (each function cites file:line in
-ff_oracle.h); this module cross-checks it against a dense numpy evaluation of
+PARITY: pinned against the reference's own UDF headers, compiled unmodified around stand-ins for the object model and
+Eigen (oracle/ref/ -> oracle/_ref/libff_ref.so, bound by oracle/ff_ref.py; tests/test_oracle_pinned.py and the vectors
+of tests/golden/ref_pinned.npz), not against a reference binary: the reference ships no golden vectors for this path
+and its build cannot run here.  The C oracle restates the UDF arithmetic (each function cites file:line in
+ff_oracle.h); this module also cross-checks it against a dense numpy evaluation of
 softmax(Wo . relu(W1 . X^T + b1) + bo)^T.
 """
 from __future__ import annotations
@@ -59,7 +60,7 @@ def lib():
         for name in ("nbo_transpose_mult_agg", "nbo_input_layer_join_agg", "nbo_la_transpose_multiply_agg"):
             getattr(L, name).restype = vp
             getattr(L, name).argtypes = [vp, vp, i]
-        for name in ("nbo_relu_bias_sum", "nbo_output_layer"):
+        for name in ("nbo_relu_bias_sum", "nbo_output_layer", "nbo_transpose_bias_sum_as_written", "nbo_output_layer_as_written"):
             getattr(L, name).restype = vp
             getattr(L, name).argtypes = [vp, vp]
         L.nbo_transpose_bias_sum.restype = vp
@@ -160,6 +161,16 @@ def relu_bias_sum(a: BlockSet, bias: BlockSet) -> BlockSet:
 
 def transpose_bias_sum(a: BlockSet, bias: BlockSet, apply_exp=True) -> BlockSet:
     return BlockSet(lib().nbo_transpose_bias_sum(a.ptr, bias.ptr, int(apply_exp)))
+
+
+def transpose_bias_sum_as_written(a: BlockSet, bias: BlockSet) -> BlockSet:
+    """FFTransposeBiasSum as this fork writes it (Q1); pinning / documentation only."""
+    return BlockSet(lib().nbo_transpose_bias_sum_as_written(a.ptr, bias.ptr))
+
+
+def output_layer_as_written(a: BlockSet, rowsum: BlockSet) -> BlockSet:
+    """FFOutputLayer as this fork writes it (Q2); pinning / documentation only."""
+    return BlockSet(lib().nbo_output_layer_as_written(a.ptr, rowsum.ptr))
 
 
 def row_aggregate(a: BlockSet) -> BlockSet:

@@ -20,6 +20,46 @@ def rel(a, b):
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
 
 
+def test_device_against_reference_goldens(nb):
+    """The device (fp64 path, through the C ABI) against vectors recorded from the REFERENCE'S OWN UDF code
+    (tests/golden/ref_pinned.npz, see tests/golden/make_golden_ref.py) -- no oracle in between."""
+    g = np.load(os.path.join(G, "ref_pinned.npz"))
+    fp64 = nb.PREC_FP64
+    close = lambda a, b: np.abs(a - b).max() <= 1e-12 * max(np.abs(b).max(), 1.0)
+
+    def dev(name, m, br=10, bc=10):
+        m = np.ascontiguousarray(m, dtype=np.float64)
+        s = nb.DeviceSet.create("gold", name, m.shape[0], m.shape[1], br, bc)
+        s.upload_dense(m)
+        return s
+
+    w1, x, b1, wo = dev("w1", g["ff_w1"]), dev("x", g["ff_x"]), dev("b1", g["ff_b1"], 10, 1), dev("wo", g["ff_wo"])
+    assert close(nb.gemm_blocks(nb.OP_NT, w1, x, nb.EPI_NONE, None, fp64, "gold", "y1pre").download_dense(), g["ff_y1pre"])
+    y1 = nb.gemm_blocks(nb.OP_NT, w1, x, nb.EPI_BIAS_RELU, b1, fp64, "gold", "y1")
+    assert close(y1.download_dense(), g["ff_y1"])
+    assert close(nb.gemm_blocks(nb.OP_NN, wo, y1, nb.EPI_NONE, None, fp64, "gold", "zpre").download_dense(), g["ff_zpre"])
+    wx = nb.gemm_blocks(nb.OP_NN, dev("lw", g["lstm_w"]), dev("lx", g["lstm_xt"]), nb.EPI_NONE, None, fp64, "gold", "wx")
+    uh = nb.gemm_blocks(nb.OP_NN, dev("lu", g["lstm_u"]), dev("lh", g["lstm_h"]), nb.EPI_NONE, None, fp64, "gold", "uh")
+    lb = dev("lb", g["lstm_b"])
+    assert close(nb.sum_blocks(wx, uh, lb, nb.ACT_SIGMOID, "gold", "gs").download_dense(), g["lstm_gate_sigmoid"])
+    assert close(nb.sum_blocks(wx, uh, lb, nb.ACT_TANH, "gold", "gt").download_dense(), g["lstm_gate_tanh"])
+    assert close(nb.sum_blocks(wx, uh, None, nb.ACT_NONE, "gold", "g2").download_dense(), g["lstm_two_sum"])
+    th = nb.sum_blocks(dev("lc", g["lstm_c"]), None, None, nb.ACT_TANH, "gold", "th")
+    assert close(nb.gemm_blocks(nb.OP_NN, dev("lo", g["lstm_w"][:10, :20]), th, nb.EPI_NONE, None, fp64, "gold", "hid").download_dense(), g["lstm_hidden"])
+    la_a, la_b = dev("la", g["la_a"]), dev("lbb", g["la_b"])
+    assert close(nb.gemm_blocks(nb.OP_TN, la_a, la_a, nb.EPI_NONE, None, fp64, "gold", "gram").download_dense(), g["la_gram"])
+    assert close(nb.gemm_blocks(nb.OP_TN, la_a, la_b, nb.EPI_NONE, None, fp64, "gold", "tn").download_dense(), g["la_tn"])
+    assert close(nb.gemm_blocks(nb.OP_NN, dev("lat", g["la_a"].T.copy()), la_b, nb.EPI_NONE, None, fp64, "gold", "nn").download_dense(), g["la_nn"])
+    assert np.array_equal(nb.conv2d_image_flat(g["conv_imgs"], 3, 1, 0, 7, 5).download_dense(), g["conv_image_flat"])
+    assert np.array_equal(nb.conv2d_image_flat(g["conv_imgs2"], 3, 2, 1, 16, 4).download_dense(), g["conv_image_flat2"])
+    kf = nb.conv2d_kernel_flat(g["conv_kern"], np.zeros(5), 7, 5)
+    assert np.array_equal(kf.download_dense(), g["conv_kernel_flat_nobias"])
+    res = nb.conv2d_fused(g["conv_imgs"], g["conv_kern"], np.zeros(5), 0, False, fp64, 7, 5)
+    assert close(res.download_dense(), g["conv_result_nobias"])
+    one = dev("one", g["conv_one_result"], 7, 2)
+    assert np.array_equal(nb.conv2d_result_to_images(one, 1, 4, 6, 5), g["conv_one_images"])
+
+
 def test_generator_bit_exact(nb, oracle):
     s = nb.DeviceSet.create("t", "gen", 37, 53, 10, 10)
     s.fill_synth(42)

@@ -1,8 +1,9 @@
 """CPU tests: the C oracle against the golden fixtures, numpy and its own invariants.
 
-The oracle restates the reference's UDF arithmetic (oracle/ff_oracle.h cites file:line); parity is
-UNPINNED against the reference binary (it ships no golden vectors and cannot be built here), so
-these tests pin it to hand-computed KATs and an independent numpy evaluation instead."""
+The oracle restates the reference's UDF arithmetic (oracle/ff_oracle.h cites file:line).  The reference ships no golden
+vectors and its build cannot run here; these tests pin the oracle to hand-computed KATs, to an independent numpy
+evaluation, and (test_reference_goldens) to vectors recorded from the reference's own UDF headers compiled unmodified
+(oracle/ref); tests/test_oracle_pinned.py compares against that code directly where it was built."""
 import os
 
 import numpy as np
@@ -153,3 +154,36 @@ def test_conv_result_to_images(oracle):
     assert np.array_equal(wide[:, :z], want) and not wide[:, z:].any()
     with pytest.raises(RuntimeError):
         oracle.conv_result_to_images(oracle.load_matrix(res, 7, 2), 5, x, y, z)  # 72 rows do not split into 5 images
+
+
+def test_reference_goldens(oracle):
+    """tests/golden/ref_pinned.npz was recorded from the REFERENCE'S OWN UDF code (oracle/_ref, netsDB's headers compiled
+    unmodified; tests/golden/make_golden_ref.py).  The restatement must reproduce every vector: exactly where no product
+    is involved, within summation-order noise (1e-13 of the scale) otherwise."""
+    g = np.load(os.path.join(G, "ref_pinned.npz"))
+    S = lambda m, br=10, bc=10: oracle.load_matrix(np.ascontiguousarray(m), br, bc)
+    close = lambda a, b: np.abs(a - b).max() <= 1e-13 * max(np.abs(b).max(), 1.0)
+    y1pre = oracle.transpose_mult_agg(S(g["ff_w1"]), S(g["ff_x"]), 2)
+    assert close(y1pre.dense(), g["ff_y1pre"])
+    y1 = oracle.relu_bias_sum(y1pre, S(g["ff_b1"], 10, 1))
+    assert close(y1.dense(), g["ff_y1"])
+    zpre = oracle.input_layer_join_agg(S(g["ff_wo"]), y1, 2)
+    assert close(zpre.dense(), g["ff_zpre"])
+    assert close(oracle.transpose_bias_sum_as_written(zpre, S(g["ff_bo"], 10, 1)).dense(), g["ff_yo_as_written"])
+    assert close(oracle.row_aggregate(S(np.abs(g["ff_x"]))).dense(), g["ff_rowsum"])
+    wx = oracle.input_layer_join_agg(S(g["lstm_w"]), S(g["lstm_xt"]), 2)
+    uh = oracle.input_layer_join_agg(S(g["lstm_u"]), S(g["lstm_h"]), 2)
+    assert close(oracle.lstm_sum(wx, uh, S(g["lstm_b"]), oracle.SIGMOID).dense(), g["lstm_gate_sigmoid"])
+    assert close(oracle.lstm_sum(wx, uh, S(g["lstm_b"]), oracle.TANH).dense(), g["lstm_gate_tanh"])
+    assert close(oracle.lstm_sum(wx, uh).dense(), g["lstm_two_sum"])
+    assert close(oracle.lstm_hidden_state_agg(S(g["lstm_w"][:10, :20]), S(g["lstm_c"]), 2).dense(), g["lstm_hidden"])
+    assert close(oracle.la_transpose_multiply_agg(S(g["la_a"]), S(g["la_a"]), 2).dense(), g["la_gram"])
+    assert close(oracle.la_transpose_multiply_agg(S(g["la_a"]), S(g["la_b"]), 2).dense(), g["la_tn"])
+    assert close(oracle.input_layer_join_agg(S(g["la_a"].T.copy()), S(g["la_b"]), 2).dense(), g["la_nn"])
+    imf = oracle.image_flat(g["conv_imgs"], 3, 1, 0, 7, 5)
+    assert np.array_equal(imf.dense(), g["conv_image_flat"])
+    kf = oracle.kernel_flat(g["conv_kern"], np.zeros(5), 7, 5)
+    assert np.array_equal(kf.dense(), g["conv_kernel_flat_nobias"])
+    assert close(oracle.transpose_mult_agg(imf, kf, 2).dense(), g["conv_result_nobias"])
+    assert np.array_equal(oracle.image_flat(g["conv_imgs2"], 3, 2, 1, 16, 4).dense(), g["conv_image_flat2"])
+    assert np.array_equal(oracle.conv_result_to_images(S(g["conv_one_result"], 7, 2), 1, 4, 6, 5), g["conv_one_images"])
