@@ -566,8 +566,9 @@ int launch_gemm_tc(Context *c, const Planes &u, const Planes &v, int M, int N, i
     const int tiles_n = static_cast<int>(ceil_div(N, BN));
     // V-tile multicast across two M tiles (clusters of 4) for the 2-SM kernels whenever there are at least two M tiles
     static const bool mc_env = !(getenv("NB200_GEMM_MC") && atoi(getenv("NB200_GEMM_MC")) == 0);
-    const bool mc = mc_env && kind != 0 && tiles_m >= 2;
-    if (mc) tiles_m = (tiles_m + 1) & ~1;  // an odd last tile gets an all-padding partner
+    // (an odd tile count gets an all-padding partner tile: only worth it when that is a small fraction of the work)
+    const bool mc = mc_env && kind != 0 && tiles_m >= 2 && (tiles_m % 2 == 0 || tiles_m >= 9);
+    if (mc) tiles_m = (tiles_m + 1) & ~1;
     const int Mpad = tiles_m * BM, Npad = tiles_n * BN;
     if (Mpad_out) *Mpad_out = Mpad;
     if (Npad_out) *Npad_out = Npad;
