@@ -131,13 +131,15 @@ class Clocks:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
-        self.idx, self.rows, self.proc = gpu_index, [], None
+    def __init__(self, gpu_indices):
+        """One poller (on rank 0) for all GPUs of the job: eight ranks each running their own nvidia-smi loop would only
+        add driver-lock traffic to the timed region."""
+        self.idx, self.rows, self.proc = ",".join(str(i) for i in gpu_indices), [], None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "100", "-i", self.idx], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
@@ -215,8 +217,9 @@ def run_b200(a):
     for _ in range(max(a.warmup, 3)):
         step()
     barrier()
-    clocks = Clocks(local)
-    clocks.start()
+    clocks = Clocks(range(world) if rank == 0 else [])
+    if rank == 0:
+        clocks.start()
     time.sleep(0.3)
     l0 = capi.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -49,7 +49,8 @@ REF_LSTM_DRIVER = "/root/reference/src/tests/source/LSTMTest.cc"
 REF_LA_DRIVERS = [("TestLA04_netsdb", "/root/reference/src/tests/source/TestLA04_Multiply.cc"),
                   ("TestLA07_netsdb", "/root/reference/src/tests/source/TestLA07_TransposeMultiply_Gram.cc"),
                   ("Word2Vec_netsdb", "/root/reference/src/word2vec/source/Word2Vec.cc"),
-                  ("PipelinedConv2dMemFuseTest_netsdb", "/root/reference/src/tests/source/PipelinedConv2dMemFuseTest.cc")]
+                  ("PipelinedConv2dMemFuseTest_netsdb", "/root/reference/src/tests/source/PipelinedConv2dMemFuseTest.cc"),
+                  ("FFTestWithoutDeduplication_netsdb", "/root/reference/src/tests/source/FFTestWithoutDeduplication.cc")]
 
 
 def build_host(force: bool = False) -> dict:

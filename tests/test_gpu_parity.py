@@ -355,6 +355,19 @@ def test_unmodified_reference_driver_runs(tmp_path):
     assert "count=3" in r.stdout  # 120 rows / 50 = 3 row blocks x 1 column block of the output set
 
 
+def test_unmodified_reference_driver_with_sizes():
+    """netsDB's src/tests/source/FFTestWithoutDeduplication.cc (sizes, database name and reload flag from the command
+    line; the driver bench.py's configuration can be run with) unmodified through the shim."""
+    from netsdb_b200 import build
+
+    exe = os.path.join(build.HOST_BIN, "FFTestWithoutDeduplication_netsdb")
+    if not os.path.exists(exe):
+        pytest.skip("reference driver was not built (no reference tree at build time)")
+    r = _run([exe, "50", "50", "130", "220", "90", "7", "ffnd", "Y"], {"NB200_DROPOUT_AS_ZERO": "1", "NB200_PRECISION": "f16"}, timeout=120)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "*****FFTest End-to-End Time Duration" in r.stdout
+
+
 def test_k_sharded_variant_two_gpus():
     """K-sharded layer 1 + NCCL reduce-scatter (the fallback for weights larger than one GPU's HBM) against the oracle;
     needs two visible GPUs, so it is skipped on the single-GPU test box (run under `gpurun --gpus 2`)."""
