@@ -26,11 +26,16 @@ void set_error(const char *fmt, ...) {
 static Context *g_ctx = nullptr;
 static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default on)
 static std::mutex g_mu;
+// Serialises the entry points: the library keeps one compute stream, one split-K workspace and one set of scratch buffers per
+// process, so calls from netsDB's pipeline threads (one per hash partition, work/source/PDBWorkerQueue.cc:163) run one at a
+// time on the device.  Recursive because entry points compose (nb200_lstm_cell -> gemm_blocks -> ...).
+static std::recursive_mutex g_api_mu;
 static std::atomic<uint64_t> g_version{0};  // source of set versions: unique across sets, so a cache keyed on
                                             // (pointer, version) cannot be fooled by a recycled address
 static std::map<std::pair<std::string, std::string>, nb200_set *> g_sets;
 
 Context *ctx() { return g_ctx; }
+std::recursive_mutex &api_mutex() { return g_api_mu; }
 
 int ensure_ws(Context *c, size_t bytes) {
     if (bytes <= c->ws_bytes) return NB200_OK;
@@ -96,6 +101,7 @@ static void free_set_storage(nb200_set *s) {
 }
 
 #define NEED_CTX_RAW()                                          \
+    std::lock_guard<std::recursive_mutex> _api_lock(::nb200::api_mutex()); \
     Context *c = ::nb200::ctx();                                \
     if (!c) {                                                   \
         ::nb200::set_error("nb200_init has not been called");   \
@@ -208,6 +214,7 @@ int nb200_device_count(int *count) {
 }
 
 int nb200_init(int device) {
+    std::lock_guard<std::recursive_mutex> api_lock(g_api_mu);
     std::lock_guard<std::mutex> lk(g_mu);
     if (g_ctx) {
         if (g_ctx->device == device) return NB200_OK;
@@ -255,6 +262,7 @@ int nb200_init(int device) {
 static void release_lstm_scratch(void);
 
 int nb200_shutdown(void) {
+    std::lock_guard<std::recursive_mutex> api_lock(g_api_mu);
     std::lock_guard<std::mutex> lk(g_mu);
     if (!g_ctx) return NB200_OK;
     cudaStreamSynchronize(g_ctx->stream);

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <mutex>
 #include <string>
 
 #include "../../include/netsdb_b200.h"
@@ -60,7 +61,9 @@ struct Context {
     bool main_dirty = true;        // compute-stream work queued since the copy streams last waited for it
 };
 int wait_uploads(Context *c);      // make the compute stream wait for every queued upload
-Context *ctx();                                   // nullptr before nb200_init
+Context *ctx();
+                                   // nullptr before nb200_init
+std::recursive_mutex &api_mutex();  // held by every entry point for its whole duration
 int ensure_ws(Context *c, size_t bytes);          // grows c->ws
 int check_kernel_fault(Context *c, const char *what);  // syncs the stream and reads err_flag
 

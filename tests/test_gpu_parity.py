@@ -368,6 +368,39 @@ def test_unmodified_reference_driver_with_sizes():
     assert "*****FFTest End-to-End Time Duration" in r.stdout
 
 
+def test_concurrent_callers_are_serialised(nb, oracle):
+    """netsDB runs one pipeline thread per hash partition, all calling UDFs at once (threading).  The
+    library serialises its entry points, so concurrent calls from several threads give the same results as sequential
+    ones (ctypes releases the GIL during the calls)."""
+    import threading
+
+    I, K, J, blk = 300, 2500, 129, 100
+    mats = [(oracle.synth_dense(I, K, 50 + t), oracle.synth_dense(J, K, 60 + t)) for t in range(4)]
+    sets = []
+    for t, (a, b) in enumerate(mats):
+        A = nb.DeviceSet.create("thr", f"a{t}", I, K, blk, blk); A.upload_dense(a)
+        B = nb.DeviceSet.create("thr", f"b{t}", J, K, blk, blk); B.upload_dense(b)
+        sets.append((A, B))
+    out, errs = [None] * 4, []
+
+    def work(t):
+        try:
+            for rep in range(3):
+                C = nb.gemm_blocks(nb.OP_NT, sets[t][0], sets[t][1], nb.EPI_NONE, None, nb.PREC_BF16X3 if t % 2 else nb.PREC_FP64,
+                                   "thr", f"c{t}")
+                out[t] = C.download_dense()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(4)]
+    [th.start() for th in threads]
+    [th.join() for th in threads]
+    assert not errs, errs
+    for t, (a, b) in enumerate(mats):
+        want = a @ b.T
+        assert np.abs(out[t] - want).max() <= (TOL["bf16x3"] if t % 2 else TOL["fp64"]) * np.abs(want).max(), t
+
+
 def test_k_sharded_variant_two_gpus():
     """K-sharded layer 1 + NCCL reduce-scatter (the fallback for weights larger than one GPU's HBM) against the oracle;
     needs two visible GPUs, so it is skipped on the single-GPU test box (run under `gpurun --gpus 2`)."""
