@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--hidden", type=int, default=1000)
     ap.add_argument("--labels", type=int, default=14588)
     ap.add_argument("--block", type=int, default=1000)
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the baseline sample")
@@ -363,21 +363,34 @@ def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):
             off += rows * cols
     oh = out_host.numpy().reshape(a.batch, a.labels)
 
-    def step():
+    # Two input sets, used alternately: while step i computes on one, the blocks of step i + 1 are already on their way
+    # into the other (nb200_upload_commit makes the computation wait for its own set only).  Every step's inputs still
+    # cross PCIe inside the timed region, and every step's labels and `output` set come back to the host.
+    x2 = capi.DeviceSet.create("ff", "inputs_b", a.batch, a.features, blk, blk)
+    bufs = [x, x2]
+
+    def upload(dst):
         for i, j, view in blocks:
-            capi.check(capi.lib().nb200_upload_block(x.ptr, i, j, view.ctypes.data, view.shape[0], view.shape[1]))
-        out, labels, _ = capi.ff_inference_unit(w1, wo, x, b1, bo, prec, "ff", "output")
-        capi.check(capi.lib().nb200_download_rect(out.ptr, 0, 0, oh.ctypes.data, a.batch, a.labels, a.labels))
+            capi.check(capi.lib().nb200_upload_block(dst.ptr, i, j, view.ctypes.data, view.shape[0], view.shape[1]))
+        dst.upload_commit()
+
+    def run(n_steps):
+        upload(bufs[0])
+        labels = None
+        for k in range(n_steps):
+            if k + 1 < n_steps:
+                upload(bufs[(k + 1) % 2])
+            out, labels, _ = capi.ff_inference_unit(w1, wo, bufs[k % 2], b1, bo, prec, "ff", "output")
+            capi.check(capi.lib().nb200_download_rect(out.ptr, 0, 0, oh.ctypes.data, a.batch, a.labels, a.labels))
         return labels
 
-    step()
+    run(2)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s = torch.cuda.current_stream()
     t0 = time.perf_counter()
     e0.record(s)
-    for _ in range(a.e2e_steps):
-        step()
+    run(a.e2e_steps)
     e1.record(s)
     barrier()
     wall = (time.perf_counter() - t0) * 1000.0
@@ -389,7 +402,8 @@ def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):
     v = world * a.batch / (ms / a.e2e_steps / 1000.0)
     return dict(value=v, unit=UNIT, h2d_bytes_per_step=in_bytes, d2h_bytes_per_step=out_bytes + a.batch * 4,
                 ms_per_step=ms / a.e2e_steps, steps=a.e2e_steps,
-                note="inputs uploaded as fp64 FFMatrixBlocks from pinned host memory every step; weights model-resident")
+                note="inputs uploaded as fp64 FFMatrixBlocks from pinned host memory every step into two alternating sets (the next "
+                     "step's transfer runs under the current step's computation); weights model-resident")
 
 
 if __name__ == "__main__":

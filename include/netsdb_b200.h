@@ -120,6 +120,13 @@ int nb200_set_info(const nb200_set *s, int *total_rows, int *total_cols, int *bl
  * row-major rows x cols (full-size zero-padded edge blocks as ff::loadMatrix builds them,
  * FFMatrixUtil.cc:245-302, or trimmed ones).  Padding beyond totalRows/totalCols is dropped. */
 int nb200_upload_block(nb200_set *s, int block_row, int block_col, const double *host, int rows, int cols);
+/* Marks the end of the uploads queued so far into `set`.  Uploads are asynchronous (two copy streams); an entry point that
+ * reads a set first makes the compute stream wait for them -- for ALL queued uploads by default.  After a commit,
+ * nb200_ff_inference_unit and nb200_download_* wait only for the uploads of the sets they read, so a caller can queue the
+ * next batch into a second set and have its transfer run under the computation of the current one (netsDB's pipeline
+ * does the same with its page-circular buffer, storage/headers/PageCircularBuffer.h).  A later upload into the set
+ * withdraws the commit. */
+int nb200_upload_commit(nb200_set *set);
 /* Arbitrary rectangle (row-granular sharding across GPUs): element (r,c) of the rectangle is
  * host[r*ld + c] and lands at (row0 + r, col0 + c) of the set. */
 int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int rows, int cols, int64_t ld);

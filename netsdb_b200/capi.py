@@ -28,7 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
-    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell", "nb200_upload_commit",
 ]
 
 
@@ -184,6 +184,10 @@ class DeviceSet:
         assert rect.dtype == np.float64 and rect.ndim == 2 and rect.strides[1] == 8
         check(lib().nb200_upload_rect(self.ptr, row0, col0, _hostptr(rect), rect.shape[0], rect.shape[1],
                                       rect.strides[0] // 8))
+
+    def upload_commit(self):
+        """nb200_upload_commit: readers of this set wait for its uploads only."""
+        check(lib().nb200_upload_commit(self.ptr))
 
     def upload_dense(self, dense: np.ndarray):
         """ff::loadMatrix analogue: send the matrix block by block (full-size zero-padded blocks)."""

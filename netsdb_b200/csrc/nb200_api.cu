@@ -70,6 +70,20 @@ int wait_uploads(Context *c) {
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->up_ev[i], 0));
     }
     c->uploads_pending = false;
+    c->up_epoch++;
+    return NB200_OK;
+}
+
+// Order the compute stream after the uploads of ONE set.  With a commit fence (nb200_upload_commit) only that set's
+// copies are waited for, so uploads queued behind them -- the next batch into another set -- keep running under the
+// computation; without one this falls back to waiting for everything.
+int wait_set_uploads(Context *c, nb200_set *s) {
+    if (!s) return NB200_OK;
+    if (s->view_of) s = s->view_of;
+    if (s->up_epoch != c->up_epoch) return NB200_OK;  // nothing uploaded since the compute stream last waited
+    if (!s->up_fenced) return wait_uploads(c);
+    for (int i = 0; i < 2; i++) NB_CUDA(cudaStreamWaitEvent(c->stream, s->up_fence[i], 0));
+    s->up_epoch = 0;
     return NB200_OK;
 }
 
@@ -93,6 +107,8 @@ static void free_planes(Planes *p) {
 }
 
 static void free_set_storage(nb200_set *s) {
+    for (auto &e : s->up_fence) { if (e) cudaEventDestroy(e); e = nullptr; }
+    s->up_fenced = false; s->up_epoch = 0;
     cudaFree(s->f64); s->f64 = nullptr;
     cudaFree(s->f32); s->f32 = nullptr;
     cudaFree(s->wo_rownorm_max); s->wo_rownorm_max = nullptr;
@@ -417,6 +433,19 @@ int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int 
                                   static_cast<size_t>(vc) * sizeof(double), vr, cudaMemcpyHostToDevice, cs));
     }
     c->uploads_pending = true;
+    s->up_epoch = c->up_epoch;
+    s->up_fenced = false;
+    return NB200_OK;
+}
+
+int nb200_upload_commit(nb200_set *s) {
+    NEED_CTX_RAW();
+    if (!s || s->view_of) { set_error("upload_commit: invalid set"); return NB200_ERR_INVALID; }
+    for (int i = 0; i < 2; i++) {
+        if (!s->up_fence[i]) NB_CUDA(cudaEventCreateWithFlags(&s->up_fence[i], cudaEventDisableTiming));
+        NB_CUDA(cudaEventRecord(s->up_fence[i], c->copy[i]));
+    }
+    s->up_fenced = true;
     return NB200_OK;
 }
 
@@ -429,7 +458,9 @@ int nb200_upload_block(nb200_set *s, int block_row, int block_col, const double 
 }
 
 int nb200_download_rect(nb200_set *s, int row0, int col0, double *host, int rows, int cols, int64_t ld) {
-    NEED_CTX();
+    NEED_CTX_RAW();
+    NB_TRY(wait_set_uploads(c, s));  // only this set's uploads: a download of results must not wait for the next batch's
+    c->main_dirty = true;
     if (!s || !host || row0 < 0 || col0 < 0 || rows < 0 || cols < 0 || ld < cols) {
         set_error("download: invalid arguments");
         return NB200_ERR_INVALID;
@@ -1060,11 +1091,15 @@ static int grow(double **p, size_t *have, size_t need) {
 int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb200_set *b1, nb200_set *bo, int precision,
                             const char *db, const char *out_set, nb200_set **out, int32_t *labels_host,
                             nb200_ff_stats *stats) {
-    NEED_CTX();
+    NEED_CTX_RAW();
     if (!w1 || !wo || !inputs || !b1 || !bo || !db || !out_set || !out || precision < 0 || precision > 3) {
         set_error("ff_inference_unit: invalid arguments");
         return NB200_ERR_INVALID;
     }
+    // wait for the uploads of the five operand sets only (see nb200_upload_commit): the next batch may already be on its
+    // way into another set
+    for (nb200_set *s : {w1, wo, inputs, b1, bo}) NB_TRY(wait_set_uploads(c, s));
+    c->main_dirty = true;
     const int B = inputs->total_rows, F = inputs->total_cols, H = w1->total_rows, Lb = wo->total_rows;
     // FFTransposeMult predicate/dimension check (w1 x inputs), FFInputLayerJoin (wo x y1)
     if (w1->total_cols != F || w1->block_cols != inputs->block_cols) { set_error("Block dimemsions mismatch! (w1 vs inputs)"); return NB200_ERR_SHAPE; }

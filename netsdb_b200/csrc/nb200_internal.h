@@ -58,9 +58,12 @@ struct Context {
     cudaEvent_t main_ev = nullptr;
     int up_next = 0;
     bool uploads_pending = false;  // work queued on the copy streams that the compute stream has not waited for
+    uint64_t up_epoch = 1;         // advanced by every wait on ALL uploads: a set with set->up_epoch == up_epoch has
+                                   // uploads the compute stream has not waited for yet
     bool main_dirty = true;        // compute-stream work queued since the copy streams last waited for it
 };
 int wait_uploads(Context *c);      // make the compute stream wait for every queued upload
+int wait_set_uploads(Context *c, nb200_set *s);  // ... for the uploads of one set (its commit fence when it has one)
 Context *ctx();
                                    // nullptr before nb200_init
 std::recursive_mutex &api_mutex();  // held by every entry point for its whole duration
@@ -222,6 +225,11 @@ struct nb200_set {
     nb200::Planes rowp, colp;
     float *wo_rownorm_max = nullptr;  // device scalar derived from rowp.row_sumsq (error model)
     uint64_t version = 0;          // bumped whenever the set's contents change (caches of derived operands)
+    // uploads: epoch of the context when the set was last written by an upload, and (after nb200_upload_commit) events
+    // that mark the end of its uploads on the two copy streams, so that a reader can wait for THIS set only
+    uint64_t up_epoch = 0;
+    cudaEvent_t up_fence[2] = {nullptr, nullptr};
+    bool up_fenced = false;
     bool view_exp = false;         // downloads apply exp() (the `yo` view of the logits)
     nb200_set *view_of = nullptr;  // set whose storage a view reads
 };

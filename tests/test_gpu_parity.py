@@ -368,6 +368,44 @@ def test_unmodified_reference_driver_with_sizes():
     assert "*****FFTest End-to-End Time Duration" in r.stdout
 
 
+def test_upload_commit_overlaps_next_batch(nb, oracle):
+    """Double-buffered inputs: the blocks of batch B are queued (and committed) while batch A is evaluated, the results
+    of A are downloaded while B's transfer may still be running, then B is evaluated.  Labels and probabilities of both
+    batches equal the oracle's, repeatedly, and a late upload withdraws the commit."""
+    batch, feat, hid, lab, blk = 1200, 8200, 300, 20, 1000
+    dev, ora, dense = _ff_sets(nb, oracle, batch, feat, hid, lab, blk)
+    xb = oracle.synth_dense(batch, feat, 77)
+    ref = {}
+    for name, xd in (("a", dense["x"]), ("b", xb)):
+        out, _, labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], oracle.load_matrix(xd, blk, blk), ora["b1"], ora["bo"], threads=4)
+        ref[name] = (labels, out.dense())
+    A, B = dev["x"], nb.DeviceSet.create("ff", "inputs_b", batch, feat, blk, blk)
+    host = {"a": oracle.load_matrix(dense["x"], blk, blk), "b": oracle.load_matrix(xb, blk, blk)}
+
+    def send(dst, name):
+        for br, bc, _, _, arr in host[name].blocks():
+            dst.upload_block(br, bc, np.ascontiguousarray(arr))
+        dst.upload_commit()
+
+    send(A, "a")
+    for rep in range(3):
+        send(B, "b")                                                    # in flight while A is evaluated
+        out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], A, dev["b1"], dev["bo"], nb.PREC_F16)
+        assert np.array_equal(labels, ref["a"][0]), rep
+        assert np.abs(out.download_dense() - ref["a"][1]).max() < 5e-2  # fp16 logits; the labels above are the exact check
+        send(A, "a")                                                    # in flight while B is evaluated
+        out, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], B, dev["b1"], dev["bo"], nb.PREC_F16)
+        assert np.array_equal(labels, ref["b"][0]), rep
+        assert np.abs(out.download_dense() - ref["b"][1]).max() < 5e-2
+    # an upload after the commit withdraws it: the reader falls back to waiting for everything and sees the new data
+    B.upload_commit()
+    for br, bc, _, _, arr in host["a"].blocks():
+        B.upload_block(br, bc, np.ascontiguousarray(arr))
+    _, labels, _ = nb.ff_inference_unit(dev["w1"], dev["wo"], B, dev["b1"], dev["bo"], nb.PREC_F16)
+    assert np.array_equal(labels, ref["a"][0])
+    B.destroy()
+
+
 def test_concurrent_callers_are_serialised(nb, oracle):
     """netsDB runs one pipeline thread per hash partition, all calling UDFs at once (threading).  The
     library serialises its entry points, so concurrent calls from several threads give the same results as sequential
