@@ -450,7 +450,7 @@ def test_k_sharded_variant_two_gpus():
         pytest.skip("needs 2 GPUs")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-              "--master-port", "29547", os.path.join(root, "tools", "ksharded_check.py")], {}, timeout=600)
+              "--master-port", "29547", os.path.join(root, "tests", "tools", "ksharded_check.py")], {}, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("OK  k-sharded") == 3
 

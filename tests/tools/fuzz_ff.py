@@ -1,10 +1,11 @@
 """Random-shape sweep of nb200_ff_inference_unit (all precisions; shapes on both sides of the fused-kernel and split-K
 thresholds) against a dense numpy fp64 evaluation: labels must be identical, logits inside the precision's bound."""
+import os
 import sys
 
 import numpy as np
 
-sys.path.insert(0, ".")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from netsdb_b200 import capi
 from oracle import ff_oracle as fo  # checker only
 

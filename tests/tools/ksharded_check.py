@@ -1,5 +1,5 @@
 """torchrun script: K-sharded FF inference on WORLD_SIZE GPUs against the CPU oracle (rank 0 checks).
-    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/ksharded_check.py"""
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/tools/ksharded_check.py"""
 import os
 import sys
 
@@ -7,7 +7,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from netsdb_b200 import capi  # noqa: E402
 from netsdb_b200.ksharded import col_shard, ff_inference_k_sharded  # noqa: E402
 from oracle import ff_oracle as fo  # noqa: E402  (the checker; this is a test tool)

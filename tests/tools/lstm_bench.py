@@ -1,12 +1,13 @@
 """Times one LSTM step (netsdb_b200.lstm.lstm_cell: the graph of src/tests/source/LSTMTest.cc) with all sets resident
 on the device, and the CPU oracle on the same sizes.  Device time by CUDA events on the library's stream."""
+import os
 import sys
 import time
 
 import numpy as np
 import torch
 
-sys.path.insert(0, ".")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from netsdb_b200 import capi, lstm
 
 L, D, B, bs = (int(a) for a in sys.argv[1:5]) if len(sys.argv) >= 5 else (2048, 4096, 2048, 1024)
