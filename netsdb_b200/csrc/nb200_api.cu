@@ -815,7 +815,8 @@ int nb200_lstm_cell(const nb200_lstm_sets *in, int precision, const char *db) {
                    in->x_t->total_rows == D && in->x_t->f64 && in->x_t->block_rows == bk &&
                    in->h_t_1->total_rows == L && in->h_t_1->total_cols == B && in->h_t_1->f64 && in->h_t_1->block_cols == bc &&
                    in->c_t_1->total_rows == L && in->c_t_1->total_cols == B && in->c_t_1->f64 && in->c_t_1->block_cols == bc &&
-                   in->c_t_1->block_rows == bc;  // f_t's column blocks join c_t_1's row blocks
+                   in->c_t_1->block_rows == bc &&  // f_t's column blocks join c_t_1's row blocks
+                   br == bc;  // ... and i_t's / o_t's join c_t_temp's / c_t's, whose row blocks are br tall (else the reference exits: composed path)
     for (int g = 0; g < 4 && regular; g++) {
         nb200_set *w = in->w[g], *u = in->u[g], *b = in->b[g];
         regular = w->f64 && u->f64 && b->f64 && w->total_rows == L && w->total_cols == D && w->block_rows == br && w->block_cols == bk &&

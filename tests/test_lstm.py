@@ -175,6 +175,30 @@ def test_lstm_cell_single_entry_point(nb, oracle, prec, shape):
 
 
 @pytest.mark.gpu
+def test_lstm_cell_block_mismatch_is_the_references_error(nb):
+    """i_t (column blocks as wide as x_t's) joins c_t_temp (row blocks as tall as w's): unequal block sizes trip the
+    per-pair dimension check of FFInputLayerJoin in the reference (exit(1)); same error here, on every precision."""
+    from netsdb_b200 import lstm
+    L, D, B = 64, 96, 64
+    d = make_inputs(L, D, B, 12)
+    sets = {}
+    for k, v in d.items():
+        # weights and biases in 32-row blocks, x_t / h_t_1 / c_t_1 columns in blocks of 16
+        br = 32 if k[0] in "wub" else (32 if k != "x_t" else 32)
+        bc = 16 if (k[0] == "b" or k in ("x_t", "h_t_1", "c_t_1")) else 32
+        if k == "c_t_1":
+            br = 16
+        s = nb.DeviceSet.create("lstm", k, v.shape[0], v.shape[1], br, bc)
+        s.upload_dense(np.ascontiguousarray(v))
+        sets[k] = s
+    for prec in ("bf16x3", "fp64"):
+        with pytest.raises(nb.Nb200Error) as e:
+            lstm.lstm_cell_fused("lstm", prec)
+        assert "Block dimemsions mismatch" in str(e.value)
+    [s.destroy() for s in sets.values()]
+
+
+@pytest.mark.gpu
 def test_lstm_reference_driver_shape(nb, oracle):
     """LSTMTest.cc's sizes: the K extents of f_t (128 x 500) and c_t_1 (128 x 500) differ and the join keeps the
     leading column blocks only.  Gates and c_t equal the reference as written; h_t equals the zero-padding model."""
