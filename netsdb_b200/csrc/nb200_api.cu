@@ -41,11 +41,11 @@ int ensure_ws(Context *c, size_t bytes) {
     if (bytes <= c->ws_bytes) return NB200_OK;
     if (c->ws) {
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        cudaFree(c->ws);
+        nb_free(c->ws);
         c->ws = nullptr;
         c->ws_bytes = 0;
     }
-    NB_CUDA(cudaMalloc(&c->ws, bytes));
+    NB_CUDA(nb_malloc(&c->ws, bytes));
     c->ws_bytes = bytes;
     return NB200_OK;
 }
@@ -54,11 +54,11 @@ static int ensure_stage(Context *c, size_t bytes) {
     if (bytes <= c->stage_bytes) return NB200_OK;
     if (c->stage) {
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        cudaFree(c->stage);
+        nb_free(c->stage);
         c->stage = nullptr;
         c->stage_bytes = 0;
     }
-    NB_CUDA(cudaMalloc(&c->stage, bytes));
+    NB_CUDA(nb_malloc(&c->stage, bytes));
     c->stage_bytes = bytes;
     return NB200_OK;
 }
@@ -101,17 +101,19 @@ int check_kernel_fault(Context *c, const char *what) {
 }
 
 static void free_planes(Planes *p) {
-    cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
-    cudaFree(p->f16); cudaFree(p->f16_exp); cudaFree(p->f16_maxscaled);
+    nb_free(p->hi); nb_free(p->lo); nb_free(p->row_sumsq); nb_free(p->maxabs);
+    nb_free(p->f16); nb_free(p->f16_exp); nb_free(p->f16_maxscaled);
     *p = Planes();
 }
 
 static void free_set_storage(nb200_set *s) {
+    // uploads still in flight into this set must land before its storage can be handed to someone else
+    if (Context *c0 = ctx()) { if (s->up_epoch == c0->up_epoch && c0->uploads_pending) wait_uploads(c0); }
     for (auto &e : s->up_fence) { if (e) cudaEventDestroy(e); e = nullptr; }
     s->up_fenced = false; s->up_epoch = 0;
-    cudaFree(s->f64); s->f64 = nullptr;
-    cudaFree(s->f32); s->f32 = nullptr;
-    cudaFree(s->wo_rownorm_max); s->wo_rownorm_max = nullptr;
+    nb_free(s->f64); s->f64 = nullptr;
+    nb_free(s->f32); s->f32 = nullptr;
+    nb_free(s->wo_rownorm_max); s->wo_rownorm_max = nullptr;
     free_planes(&s->rowp);
     free_planes(&s->colp);
 }
@@ -136,7 +138,7 @@ static void free_set_storage(nb200_set *s) {
 static int ensure_f64(Context *c, nb200_set *s) {
     if (s->f64) return NB200_OK;
     const size_t n = static_cast<size_t>(s->total_rows) * s->total_cols;
-    NB_CUDA(cudaMalloc(&s->f64, (n ? n : 1) * sizeof(double)));
+    NB_CUDA(nb_malloc(&s->f64, (n ? n : 1) * sizeof(double)));
     NB_CUDA(cudaMemsetAsync(s->f64, 0, (n ? n : 1) * sizeof(double), c->stream));
     return NB200_OK;
 }
@@ -144,7 +146,7 @@ static int ensure_f32(Context *c, nb200_set *s) {
     if (s->f32) return NB200_OK;
     if (!s->f64) { set_error("set %s:%s holds no data", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
     const size_t n = static_cast<size_t>(s->total_rows) * s->total_cols;
-    NB_CUDA(cudaMalloc(&s->f32, (n ? n : 1) * sizeof(float)));
+    NB_CUDA(nb_malloc(&s->f32, (n ? n : 1) * sizeof(float)));
     s->f32_ld = s->total_cols;
     return launch_f64_to_f32(c, s->f64, static_cast<int64_t>(n), s->f32);
 }
@@ -207,11 +209,11 @@ static int ensure_f16_col(Context *c, nb200_set *s) {
     NB_TRY(ensure_f32(c, s));
     float *t = nullptr;  // transposed fp32 copy, then a plain conversion
     const size_t n = static_cast<size_t>(s->total_rows) * s->total_cols;
-    NB_CUDA(cudaMalloc(&t, (n ? n : 1) * sizeof(float)));
+    NB_CUDA(nb_malloc(&t, (n ? n : 1) * sizeof(float)));
     int st = launch_transpose_f32(c, s->f32, s->total_rows, s->total_cols, s->f32_ld, t, s->total_rows);
     if (st == NB200_OK) st = launch_convert_f16(c, t, false, s->total_cols, s->total_rows, s->total_rows, &s->colp, 1, nullptr);
     cudaStreamSynchronize(c->stream);
-    cudaFree(t);
+    nb_free(t);
     return st;
 }
 
@@ -255,7 +257,7 @@ int nb200_init(int device) {
     c->sm_count = prop.multiProcessorCount;
     NB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
-    NB_CUDA(cudaMalloc(&c->err_flag, sizeof(int)));
+    NB_CUDA(nb_malloc(&c->err_flag, sizeof(int)));
     NB_CUDA(cudaMemset(c->err_flag, 0, sizeof(int)));
     NB_CUDA(cudaMallocHost(&c->err_flag_host, sizeof(int)));
     for (auto &e : c->ev) NB_CUDA(cudaEventCreate(&e));
@@ -288,9 +290,9 @@ int nb200_shutdown(void) {
         delete kv.second;
     }
     g_sets.clear();
-    cudaFree(g_ctx->ws);
-    cudaFree(g_ctx->stage);
-    cudaFree(g_ctx->err_flag);
+    nb_free(g_ctx->ws);
+    nb_free(g_ctx->stage);
+    nb_free(g_ctx->err_flag);
     cudaFreeHost(g_ctx->err_flag_host);
     for (auto &e : g_ctx->ev) cudaEventDestroy(e);
     for (auto &e : g_ctx->chunk_ev) cudaEventDestroy(e);
@@ -299,10 +301,11 @@ int nb200_shutdown(void) {
     for (auto &st : g_ctx->copy) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
     for (auto &e : g_ctx->up_ev) cudaEventDestroy(e);
     cudaEventDestroy(g_ctx->main_ev);
-    cudaFree(g_ctx->up_stage[0]); cudaFree(g_ctx->up_stage[1]);
+    nb_free(g_ctx->up_stage[0]); nb_free(g_ctx->up_stage[1]);
     cudaStreamDestroy(g_ctx->own_stream);
     delete g_ctx;
     g_ctx = nullptr;
+    pool_release_all();
     return NB200_OK;
 }
 
@@ -387,7 +390,7 @@ static void drop_derived(nb200_set *s) {
     s->version = ++g_version;
     s->rowp.valid = s->rowp.lo_valid = s->rowp.f16_valid = false;
     s->colp.valid = s->colp.lo_valid = s->colp.f16_valid = false;
-    if (s->f64 && s->f32) { cudaFree(s->f32); s->f32 = nullptr; }
+    if (s->f64 && s->f32) { nb_free(s->f32); s->f32 = nullptr; }
 }
 
 int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int rows, int cols, int64_t ld) {
@@ -419,10 +422,10 @@ int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int 
         // contiguous H2D of the host rows into a staging slot, then de-block on the device
         if (c->up_bytes[slot] < block_bytes) {
             NB_CUDA(cudaStreamSynchronize(cs));
-            cudaFree(c->up_stage[slot]);
+            nb_free(c->up_stage[slot]);
             c->up_stage[slot] = nullptr;
             c->up_bytes[slot] = 0;
-            NB_CUDA(cudaMalloc(&c->up_stage[slot], block_bytes));
+            NB_CUDA(nb_malloc(&c->up_stage[slot], block_bytes));
             c->up_bytes[slot] = block_bytes;
         }
         NB_CUDA(cudaMemcpyAsync(c->up_stage[slot], host, block_bytes, cudaMemcpyHostToDevice, cs));
@@ -604,7 +607,7 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
 
     if (precision == NB200_PREC_FP64) {
         if (!a->f64 || !b->f64 || (bias && !bias->f64)) { set_error("gemm_blocks(FP64): inputs hold no fp64 data"); return NB200_ERR_STATE; }
-        NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+        NB_CUDA(nb_malloc(&o->f64, (on ? on : 1) * sizeof(double)));
         F64Epilogue e;
         e.relu = relu;
         // element strides of A(i,k) and B'(j,k)
@@ -642,7 +645,7 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
         NB_TRY(ensure_f32(c, bias));
         bias32 = bias->f32;
     }
-    NB_CUDA(cudaMalloc(&o->f32, (on ? on : 1) * sizeof(float)));
+    NB_CUDA(nb_malloc(&o->f32, (on ? on : 1) * sizeof(float)));
     o->f32_ld = o->total_cols;
     // P is always the logical output: roles are swapped for the transposing epilogue
     const Planes &U = transpose_out ? pb : pa;
@@ -703,14 +706,14 @@ int nb200_sum_blocks(nb200_set *a, nb200_set *b, nb200_set *cc, int activation, 
     // the output may replace one of the inputs (same db:name): compute into fresh storage, then swap it in
     const size_t n = static_cast<size_t>(a->total_rows) * a->total_cols;
     double *res = nullptr;
-    NB_CUDA(cudaMalloc(&res, (n ? n : 1) * sizeof(double)));
+    NB_CUDA(nb_malloc(&res, (n ? n : 1) * sizeof(double)));
     const int tr = a->total_rows, tc = a->total_cols, br = a->block_rows, bc = a->block_cols;
     int st = launch_sum_blocks(c, src, nsrc, activation, tr, tc, res);
-    if (st != NB200_OK) { cudaFree(res); return st; }
+    if (st != NB200_OK) { nb_free(res); return st; }
     NB_CUDA(cudaStreamSynchronize(c->stream));  // make_set below may free an input that is being replaced
     nb200_set *o = nullptr;
     st = make_set(db, out_set, tr, tc, br, bc, &o);
-    if (st != NB200_OK) { cudaFree(res); return st; }
+    if (st != NB200_OK) { nb_free(res); return st; }
     o->f64 = res;
     *out = o;
     return NB200_OK;
@@ -731,9 +734,9 @@ LstmScratch g_lstm;
 
 int grow_bytes(void **p, size_t *have, size_t need) {
     if (*have >= need) return NB200_OK;
-    cudaFree(*p);
+    nb_free(*p);
     *p = nullptr; *have = 0;
-    NB_CUDA(cudaMalloc(p, need ? need : 1));
+    NB_CUDA(nb_malloc(p, need ? need : 1));
     *have = need;
     return NB200_OK;
 }
@@ -774,14 +777,14 @@ int out_set_f64(const char *db, const char *name, int tr, int tc, int br, int bc
     }
     NB_TRY(make_set(db, name, tr, tc, br, bc, out));
     const size_t n = static_cast<size_t>(tr) * tc;
-    NB_CUDA(cudaMalloc(&(*out)->f64, (n ? n : 1) * sizeof(double)));
+    NB_CUDA(nb_malloc(&(*out)->f64, (n ? n : 1) * sizeof(double)));
     return NB200_OK;
 }
 }  // namespace
 
 static void release_lstm_scratch(void) {
     for (Planes *p : {&g_lstm.WU, &g_lstm.XH, &g_lstm.FI, &g_lstm.CC, &g_lstm.OP, &g_lstm.TH}) free_planes(p);
-    cudaFree(g_lstm.G); cudaFree(g_lstm.C32); cudaFree(g_lstm.T64);
+    nb_free(g_lstm.G); nb_free(g_lstm.C32); nb_free(g_lstm.T64);
     g_lstm = LstmScratch();
 }
 
@@ -895,9 +898,9 @@ int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, n
     NB_TRY(make_set(db, out_set, logits->total_rows, logits->total_cols, logits->block_rows, logits->block_cols, &o));
     const int64_t rows = o->total_rows, cols = o->total_cols;
     const size_t on = static_cast<size_t>(rows) * cols;
-    NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+    NB_CUDA(nb_malloc(&o->f64, (on ? on : 1) * sizeof(double)));
     int32_t *labels = nullptr;
-    NB_CUDA(cudaMalloc(&labels, (rows ? rows : 1) * sizeof(int32_t)));
+    NB_CUDA(nb_malloc(&labels, (rows ? rows : 1) * sizeof(int32_t)));
     int st;
     if (src->f64) st = launch_softmax_rows(c, src->f64, true, rows, cols, src->total_cols, o->f64, cols, labels, nullptr, nullptr, 0, 0);
     else if (src->f32) st = launch_softmax_rows(c, src->f32, false, rows, cols, src->f32_ld, o->f64, cols, labels, nullptr, nullptr, 0, 0);
@@ -905,7 +908,7 @@ int nb200_softmax_rows(nb200_set *logits, const char *db, const char *out_set, n
     if (st == NB200_OK && labels_host && rows)
         if (cudaMemcpyAsync(labels_host, labels, rows * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
     cudaStreamSynchronize(c->stream);
-    cudaFree(labels);
+    nb_free(labels);
     if (st != NB200_OK) return st;
     *out = o;
     return NB200_OK;
@@ -948,10 +951,10 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
             const int rows_f = n_mtiles * 256;
             const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
             if (need > *y1_f32_bytes) {
-                cudaFree(*y1_f32);
+                nb_free(*y1_f32);
                 *y1_f32 = nullptr;
                 *y1_f32_bytes = 0;
-                NB_CUDA(cudaMalloc(y1_f32, need));
+                NB_CUDA(nb_malloc(y1_f32, need));
                 *y1_f32_bytes = need;
             }
             NB_CUDA(cudaMemsetAsync(y1_max, 0, sizeof(float), c->stream));
@@ -1021,10 +1024,10 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
         // fp16: un-scale the partial sums, keep y1 in fp32 for a moment to learn its maximum, then pick its scale
         const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
         if (need > *y1_f32_bytes) {
-            cudaFree(*y1_f32);
+            nb_free(*y1_f32);
             *y1_f32 = nullptr;
             *y1_f32_bytes = 0;
-            NB_CUDA(cudaMalloc(y1_f32, need));
+            NB_CUDA(nb_malloc(y1_f32, need));
             *y1_f32_bytes = need;
         }
         r1.f32 = *y1_f32; r1.f32_ld = H;
@@ -1081,10 +1084,10 @@ static FFScratch g_ff;
 
 static int grow(double **p, size_t *have, size_t need) {
     if (need <= *have) return NB200_OK;
-    cudaFree(*p);
+    nb_free(*p);
     *p = nullptr;
     *have = 0;
-    NB_CUDA(cudaMalloc(p, need));
+    NB_CUDA(nb_malloc(p, need));
     *have = need;
     return NB200_OK;
 }
@@ -1131,21 +1134,21 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     NB_TRY(make_set(db, out_set, B, Lb, inputs->block_rows, wo->block_rows, &o));
     const size_t on = static_cast<size_t>(B) * Lb;
     if (reuse_out) o->f64 = reuse_out;
-    else NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
+    else NB_CUDA(nb_malloc(&o->f64, (on ? on : 1) * sizeof(double)));
     if (reuse_logits) { zset->f32 = reuse_logits; zset->f32_ld = Lb; }
 
     FFScratch &S = g_ff;
     if (S.cap_rows < B) {
-        cudaFree(S.labels); cudaFree(S.gap); cudaFree(S.list);
-        NB_CUDA(cudaMalloc(&S.labels, (B ? B : 1) * sizeof(int32_t)));
-        NB_CUDA(cudaMalloc(&S.gap, (B ? B : 1) * sizeof(float)));
-        NB_CUDA(cudaMalloc(&S.list, (B ? B : 1) * sizeof(int32_t)));
+        nb_free(S.labels); nb_free(S.gap); nb_free(S.list);
+        NB_CUDA(nb_malloc(&S.labels, (B ? B : 1) * sizeof(int32_t)));
+        NB_CUDA(nb_malloc(&S.gap, (B ? B : 1) * sizeof(float)));
+        NB_CUDA(nb_malloc(&S.list, (B ? B : 1) * sizeof(int32_t)));
         S.cap_rows = B;
     }
     if (!S.count) {
-        NB_CUDA(cudaMalloc(&S.count, sizeof(int)));
+        NB_CUDA(nb_malloc(&S.count, sizeof(int)));
         NB_CUDA(cudaMallocHost(&S.count_host, sizeof(int)));
-        NB_CUDA(cudaMalloc(&S.y1_max, sizeof(float)));
+        NB_CUDA(nb_malloc(&S.y1_max, sizeof(float)));
         NB_CUDA(cudaMallocHost(&S.host_scalars, 4 * sizeof(float)));
     }
     cudaEvent_t *ev = c->ev;
@@ -1162,8 +1165,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     if (precision == NB200_PREC_FP64) {
         // exact path: everything in fp64 DFMA
         NB_TRY(grow(&S.y1g, &S.y1g_bytes, static_cast<size_t>(B) * H * sizeof(double)));
-        if (zset->f32) { cudaFree(zset->f32); zset->f32 = nullptr; }
-        NB_CUDA(cudaMalloc(&zset->f64, on * sizeof(double)));
+        if (zset->f32) { nb_free(zset->f32); zset->f32 = nullptr; }
+        NB_CUDA(nb_malloc(&zset->f64, on * sizeof(double)));
         NB_CUDA(cudaEventRecord(ev[1], c->stream));
         F64Epilogue e1; e1.bias_n = b1->f64; e1.relu = 1;
         NB_TRY(launch_gemm_f64(c, inputs->f64, F, 1, w1->f64, F, 1, B, H, F, S.y1g, H, e1));
@@ -1188,7 +1191,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         }
         NB_TRY(ensure_f32(c, b1));
         NB_TRY(ensure_f32(c, bo));
-        if (!wo->wo_rownorm_max) NB_CUDA(cudaMalloc(&wo->wo_rownorm_max, sizeof(float)));
+        if (!wo->wo_rownorm_max) NB_CUDA(nb_malloc(&wo->wo_rownorm_max, sizeof(float)));
         NB_TRY(launch_max_rownorm(c, wo->rowp.row_sumsq, Lb, wo->wo_rownorm_max));
         NB_CUDA(cudaEventRecord(ev[0], c->stream));
         // query side: de-blocked fp64 inputs -> 16-bit operand planes.  With NB200_OVERLAP=1 the fp16 conversion is
@@ -1209,7 +1212,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
             NB_TRY(ensure_rowp(c, inputs, lo));
         }
         NB_CUDA(cudaEventRecord(ev[1], c->stream));
-        if (!zset->f32) NB_CUDA(cudaMalloc(&zset->f32, on * sizeof(float)));
+        if (!zset->f32) NB_CUDA(nb_malloc(&zset->f32, on * sizeof(float)));
         zset->f32_ld = Lb;
         // level 1 on every row
         NB_TRY(tc_forward(c, inputs->rowp, B, nterms, fmt, w1, wo, b1->f32, bo->f32, &S.y1, &S.y1_f32, &S.y1_f32_bytes, S.y1_max,
@@ -1236,8 +1239,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         if ((precision == NB200_PREC_BF16 || precision == NB200_PREC_F16) && n1 > 0) {
             // level 2: bf16x3 on the undecided rows only (gathered straight from the fp64 inputs)
             if (S.list2_cap < B) {
-                cudaFree(S.list2);
-                NB_CUDA(cudaMalloc(&S.list2, static_cast<size_t>(B) * sizeof(int32_t)));
+                nb_free(S.list2);
+                NB_CUDA(nb_malloc(&S.list2, static_cast<size_t>(B) * sizeof(int32_t)));
                 S.list2_cap = B;
             }
             NB_CUDA(cudaMemsetAsync(S.count, 0, sizeof(int), c->stream));
@@ -1247,10 +1250,10 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
                 NB_TRY(launch_gather_convert_rows(c, inputs->f64, F, F, S.list + r0, R, &S.xsub));
                 const size_t need = static_cast<size_t>(R) * Lb * sizeof(float);
                 if (need > S.logits_sub_bytes) {
-                    cudaFree(S.logits_sub);
+                    nb_free(S.logits_sub);
                     S.logits_sub = nullptr;
                     S.logits_sub_bytes = 0;
-                    NB_CUDA(cudaMalloc(&S.logits_sub, need));
+                    NB_CUDA(nb_malloc(&S.logits_sub, need));
                     S.logits_sub_bytes = need;
                 }
                 int dummy = 0;
@@ -1374,8 +1377,8 @@ int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb
     yo->view_exp = true;
     NB_TRY(make_set(db, out_set, rows, Lb, b1->block_rows, wo->block_rows, &o));
     const size_t on = static_cast<size_t>(rows) * Lb;
-    NB_CUDA(cudaMalloc(&o->f64, (on ? on : 1) * sizeof(double)));
-    NB_CUDA(cudaMalloc(&zset->f32, (on ? on : 1) * sizeof(float)));
+    NB_CUDA(nb_malloc(&o->f64, (on ? on : 1) * sizeof(double)));
+    NB_CUDA(nb_malloc(&zset->f32, (on ? on : 1) * sizeof(float)));
     zset->f32_ld = Lb;
     *out = o;
     if (undecided_rows) *undecided_rows = 0;
@@ -1390,10 +1393,10 @@ int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb
     FFScratch &S = g_ff;
     const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
     if (need > S.y1_f32_bytes) {
-        cudaFree(S.y1_f32);
+        nb_free(S.y1_f32);
         S.y1_f32 = nullptr;
         S.y1_f32_bytes = 0;
-        NB_CUDA(cudaMalloc(&S.y1_f32, need));
+        NB_CUDA(nb_malloc(&S.y1_f32, need));
         S.y1_f32_bytes = need;
     }
     NB_CUDA(cudaMemcpy2DAsync(S.y1_f32, static_cast<size_t>(H) * sizeof(float), y1pre_dev, static_cast<size_t>(ld) * sizeof(float),
@@ -1416,10 +1419,10 @@ int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb
         NB_TRY(launch_splitk_reduce(c, rows, Lb, used, Mpad, Npad, nullptr, bo->f32, 0, r2));
     }
     if (S.cap_rows < rows) {
-        cudaFree(S.labels); cudaFree(S.gap); cudaFree(S.list);
-        NB_CUDA(cudaMalloc(&S.labels, static_cast<size_t>(rows) * sizeof(int32_t)));
-        NB_CUDA(cudaMalloc(&S.gap, static_cast<size_t>(rows) * sizeof(float)));
-        NB_CUDA(cudaMalloc(&S.list, static_cast<size_t>(rows) * sizeof(int32_t)));
+        nb_free(S.labels); nb_free(S.gap); nb_free(S.list);
+        NB_CUDA(nb_malloc(&S.labels, static_cast<size_t>(rows) * sizeof(int32_t)));
+        NB_CUDA(nb_malloc(&S.gap, static_cast<size_t>(rows) * sizeof(float)));
+        NB_CUDA(nb_malloc(&S.list, static_cast<size_t>(rows) * sizeof(int32_t)));
         S.cap_rows = rows;
     }
     NB_TRY(launch_softmax_rows(c, zset->f32, false, rows, Lb, Lb, o->f64, Lb, S.labels, S.gap, nullptr, 0, 0));
@@ -1427,18 +1430,18 @@ int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb
     if (undecided_rows && ld > H && w1_maxabs > 0.f) {
         // same near-tie criterion as the fused stage, with the globally reduced ||x_r||^2 and max |w1|
         if (!S.count) {
-            NB_CUDA(cudaMalloc(&S.count, sizeof(int)));
+            NB_CUDA(nb_malloc(&S.count, sizeof(int)));
             NB_CUDA(cudaMallocHost(&S.count_host, sizeof(int)));
-            NB_CUDA(cudaMalloc(&S.y1_max, sizeof(float)));
+            NB_CUDA(nb_malloc(&S.y1_max, sizeof(float)));
             NB_CUDA(cudaMallocHost(&S.host_scalars, 4 * sizeof(float)));
         }
         float *xs = nullptr;
-        NB_CUDA(cudaMalloc(&xs, static_cast<size_t>(rows + 1) * sizeof(float)));
+        NB_CUDA(nb_malloc(&xs, static_cast<size_t>(rows + 1) * sizeof(float)));
         int st = NB200_OK;
         if (cudaMemcpy2DAsync(xs, sizeof(float), y1pre_dev + H, static_cast<size_t>(ld) * sizeof(float), sizeof(float), rows,
                               cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
         if (st == NB200_OK && cudaMemcpyAsync(xs + rows, &w1_maxabs, sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
-        if (!wo->wo_rownorm_max && st == NB200_OK && cudaMalloc(&wo->wo_rownorm_max, sizeof(float)) != cudaSuccess) st = NB200_ERR_CUDA;
+        if (!wo->wo_rownorm_max && st == NB200_OK && nb_malloc(&wo->wo_rownorm_max, sizeof(float)) != cudaSuccess) st = NB200_ERR_CUDA;
         if (st == NB200_OK) st = launch_max_rownorm(c, wo->rowp.row_sumsq, Lb, wo->wo_rownorm_max);
         if (st == NB200_OK && cudaMemsetAsync(S.count, 0, sizeof(int), c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
         if (st == NB200_OK)
@@ -1446,7 +1449,7 @@ int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb
                                   prec_unit(precision), 4.0f, S.list, S.count, rows, nullptr);
         if (st == NB200_OK && cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
         cudaStreamSynchronize(c->stream);
-        cudaFree(xs);
+        nb_free(xs);
         if (st != NB200_OK) return st;
         *undecided_rows = *S.count_host;
     }
@@ -1468,12 +1471,12 @@ int nb200_conv2d_image_flat(const double *images_host, int n, int ch, int h, int
     NB_TRY(ensure_f64(c, o));
     const size_t ib = static_cast<size_t>(n) * ch * h * w * sizeof(double);
     double *dimg = nullptr;
-    NB_CUDA(cudaMalloc(&dimg, ib));
+    NB_CUDA(nb_malloc(&dimg, ib));
     int st = NB200_OK;
     if (cudaMemcpyAsync(dimg, images_host, ib, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
     if (st == NB200_OK) st = launch_im2col(c, dimg, n, ch, h, w, k, stride, padding, o->f64, o->total_cols);
     cudaStreamSynchronize(c->stream);
-    cudaFree(dimg);
+    nb_free(dimg);
     if (st != NB200_OK) return st;
     *out = o;
     return NB200_OK;
@@ -1517,12 +1520,12 @@ int nb200_conv2d_result_to_images(nb200_set *result, int num_images, int x, int 
     if (!result->f64 && !result->f32) { set_error("conv2d_result_to_images: set %s:%s holds no data", result->db.c_str(), result->name.c_str()); return NB200_ERR_STATE; }
     const size_t n = static_cast<size_t>(num_images) * z * group;
     double *dev = nullptr;
-    NB_CUDA(cudaMalloc(&dev, n * sizeof(double)));
+    NB_CUDA(nb_malloc(&dev, n * sizeof(double)));
     int st = result->f64 ? launch_result_to_images(c, result->f64, true, result->total_cols, num_images, group, result->total_cols, z, dev)
                          : launch_result_to_images(c, result->f32, false, result->f32_ld, num_images, group, result->total_cols, z, dev);
     if (st == NB200_OK && (cudaMemcpyAsync(images_host, dev, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
                            cudaStreamSynchronize(c->stream) != cudaSuccess)) st = NB200_ERR_CUDA;
-    cudaFree(dev);
+    nb_free(dev);
     if (st == NB200_ERR_CUDA) set_error("conv2d_result_to_images: CUDA error %s", cudaGetErrorString(cudaGetLastError()));
     return st;
 }
@@ -1563,18 +1566,18 @@ int nb200_conv2d_fused(const double *images_host, int n, int ch, int h, int w, c
     int st = make_set(db, out_set, n * hout * wout, kout, block_rows, block_cols, &o);
     auto cleanup = [&]() {
         cudaStreamSynchronize(c->stream);
-        cudaFree(dimg); cudaFree(dker); cudaFree(dbias); cudaFree(ihi); cudaFree(ilo);
+        nb_free(dimg); nb_free(dker); nb_free(dbias); nb_free(ihi); nb_free(ilo);
         free_planes(&kp);
     };
 #define CONV_TRY(x) do { if (st == NB200_OK && (x) != cudaSuccess) { set_error("conv2d_fused: %s failed", #x); st = NB200_ERR_CUDA; } } while (0)
-    CONV_TRY(cudaMalloc(&dimg, img_elems * sizeof(double)));
-    CONV_TRY(cudaMalloc(&dker, static_cast<size_t>(kout) * ch * k * k * sizeof(double)));
-    CONV_TRY(cudaMalloc(&dbias, static_cast<size_t>(kout) * sizeof(float)));
-    CONV_TRY(cudaMalloc(&ihi, nhwc_elems * sizeof(__nv_bfloat16)));
-    if (nterms == 3) CONV_TRY(cudaMalloc(&ilo, nhwc_elems * sizeof(__nv_bfloat16)));
+    CONV_TRY(nb_malloc(&dimg, img_elems * sizeof(double)));
+    CONV_TRY(nb_malloc(&dker, static_cast<size_t>(kout) * ch * k * k * sizeof(double)));
+    CONV_TRY(nb_malloc(&dbias, static_cast<size_t>(kout) * sizeof(float)));
+    CONV_TRY(nb_malloc(&ihi, nhwc_elems * sizeof(__nv_bfloat16)));
+    if (nterms == 3) CONV_TRY(nb_malloc(&ilo, nhwc_elems * sizeof(__nv_bfloat16)));
     const size_t on = static_cast<size_t>(n) * hout * wout * kout;
     if (st == NB200_OK) {
-        CONV_TRY(cudaMalloc(&o->f32, (on ? on : 1) * sizeof(float)));
+        CONV_TRY(nb_malloc(&o->f32, (on ? on : 1) * sizeof(float)));
         o->f32_ld = kout;
     }
     std::vector<float> bias32(kout);

@@ -955,19 +955,19 @@ int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, i
     const int ring_kb = (ring_kb_env / kSuperKb > 1 ? ring_kb_env / kSuperKb : 2) * kSuperKb;
     const size_t ring_bytes = static_cast<size_t>(rows_fused) * ring_kb * kBlockK * sizeof(__half);
     if (fs->ring_bytes < ring_bytes) {
-        cudaFree(fs->ring);
+        nb_free(fs->ring);
         fs->ring = nullptr;
         fs->ring_bytes = 0;
-        NB_CUDA(cudaMalloc(&fs->ring, ring_bytes));
+        NB_CUDA(nb_malloc(&fs->ring, ring_bytes));
         fs->ring_bytes = ring_bytes;
     }
     NB_CUDA(cudaMemsetAsync(fs->ring, 0, ring_bytes, c->stream));  // rows beyond the batch must read as zero
     const int nflags = 2 * n_mtiles * num_super;  // ready[tile_m][S], done[tile_m][S]
     if (fs->flag_cap < nflags) {
-        cudaFree(fs->flags);
+        nb_free(fs->flags);
         fs->flags = nullptr;
         fs->flag_cap = 0;
-        NB_CUDA(cudaMalloc(&fs->flags, static_cast<size_t>(nflags) * sizeof(int)));
+        NB_CUDA(nb_malloc(&fs->flags, static_cast<size_t>(nflags) * sizeof(int)));
         fs->flag_cap = nflags;
     }
     NB_CUDA(cudaMemsetAsync(fs->flags, 0, static_cast<size_t>(nflags) * sizeof(int), c->stream));

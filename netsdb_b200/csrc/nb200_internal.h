@@ -67,6 +67,12 @@ int wait_set_uploads(Context *c, nb200_set *s);  // ... for the uploads of one s
 Context *ctx();
                                    // nullptr before nb200_init
 std::recursive_mutex &api_mutex();  // held by every entry point for its whole duration
+// caching device allocator (nb200_pool.cu): every device allocation of the library goes through these
+cudaError_t pool_malloc(void **p, size_t bytes);
+cudaError_t pool_free(void *p);
+void pool_release_all();
+template <class T> inline cudaError_t nb_malloc(T **p, size_t bytes) { return pool_malloc(reinterpret_cast<void **>(p), bytes); }
+inline cudaError_t nb_free(void *p) { return pool_free(p); }
 int ensure_ws(Context *c, size_t bytes);          // grows c->ws
 int check_kernel_fault(Context *c, const char *what);  // syncs the stream and reads err_flag
 

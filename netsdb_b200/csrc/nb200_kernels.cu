@@ -114,17 +114,17 @@ k_convert_planes(const T *__restrict__ src, long long ld, long long cols, __nv_b
 static int alloc_planes(Planes *p, int64_t rows, int64_t k, bool want_lo) {
     const int64_t ldk = round_up(k, 64);
     if ((p->hi || p->f16) && (p->cap_rows < rows || p->ldk != ldk)) {
-        cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
-        cudaFree(p->f16); cudaFree(p->f16_exp); cudaFree(p->f16_maxscaled);
+        nb_free(p->hi); nb_free(p->lo); nb_free(p->row_sumsq); nb_free(p->maxabs);
+        nb_free(p->f16); nb_free(p->f16_exp); nb_free(p->f16_maxscaled);
         *p = Planes();
     }
     if (!p->hi && !p->f16) p->cap_rows = rows;
     p->rows = rows; p->k = k; p->ldk = ldk;
     const size_t bytes = static_cast<size_t>(p->cap_rows ? p->cap_rows : 1) * ldk * sizeof(__nv_bfloat16);
-    if (!p->hi) NB_CUDA(cudaMalloc(&p->hi, bytes));
-    if (want_lo && !p->lo) NB_CUDA(cudaMalloc(&p->lo, bytes));
-    if (!p->row_sumsq) NB_CUDA(cudaMalloc(&p->row_sumsq, static_cast<size_t>(p->cap_rows ? p->cap_rows : 1) * sizeof(float)));
-    if (!p->maxabs) NB_CUDA(cudaMalloc(&p->maxabs, sizeof(float)));
+    if (!p->hi) NB_CUDA(nb_malloc(&p->hi, bytes));
+    if (want_lo && !p->lo) NB_CUDA(nb_malloc(&p->lo, bytes));
+    if (!p->row_sumsq) NB_CUDA(nb_malloc(&p->row_sumsq, static_cast<size_t>(p->cap_rows ? p->cap_rows : 1) * sizeof(float)));
+    if (!p->maxabs) NB_CUDA(nb_malloc(&p->maxabs, sizeof(float)));
     return NB200_OK;
 }
 
@@ -245,18 +245,18 @@ int prepare_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t ro
                         int sample_stride, const float *known_maxabs) {
     const int64_t ldk = round_up(cols, 64);
     if ((p->hi || p->f16) && (p->cap_rows < rows || p->ldk != ldk)) {
-        cudaFree(p->hi); cudaFree(p->lo); cudaFree(p->row_sumsq); cudaFree(p->maxabs);
-        cudaFree(p->f16); cudaFree(p->f16_exp); cudaFree(p->f16_maxscaled);
+        nb_free(p->hi); nb_free(p->lo); nb_free(p->row_sumsq); nb_free(p->maxabs);
+        nb_free(p->f16); nb_free(p->f16_exp); nb_free(p->f16_maxscaled);
         *p = Planes();
     }
     if (!p->hi && !p->f16) p->cap_rows = rows;
     p->rows = rows; p->k = cols; p->ldk = ldk;
     const size_t cap = static_cast<size_t>(p->cap_rows ? p->cap_rows : 1);
-    if (!p->f16) NB_CUDA(cudaMalloc(&p->f16, cap * ldk * sizeof(__half)));
-    if (!p->f16_exp) NB_CUDA(cudaMalloc(&p->f16_exp, sizeof(int)));
-    if (!p->f16_maxscaled) NB_CUDA(cudaMalloc(&p->f16_maxscaled, sizeof(float)));
-    if (!p->row_sumsq) NB_CUDA(cudaMalloc(&p->row_sumsq, cap * sizeof(float)));
-    if (!p->maxabs) NB_CUDA(cudaMalloc(&p->maxabs, sizeof(float)));
+    if (!p->f16) NB_CUDA(nb_malloc(&p->f16, cap * ldk * sizeof(__half)));
+    if (!p->f16_exp) NB_CUDA(nb_malloc(&p->f16_exp, sizeof(int)));
+    if (!p->f16_maxscaled) NB_CUDA(nb_malloc(&p->f16_maxscaled, sizeof(float)));
+    if (!p->row_sumsq) NB_CUDA(nb_malloc(&p->row_sumsq, cap * sizeof(float)));
+    if (!p->maxabs) NB_CUDA(nb_malloc(&p->maxabs, sizeof(float)));
     NB_CUDA(cudaMemsetAsync(p->row_sumsq, 0, static_cast<size_t>(rows ? rows : 1) * sizeof(float), c->stream));
     NB_CUDA(cudaMemsetAsync(p->f16_maxscaled, 0, sizeof(float), c->stream));
     p->f16_valid = true;
