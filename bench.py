@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--hidden", type=int, default=1000)
     ap.add_argument("--labels", type=int, default=14588)
     ap.add_argument("--block", type=int, default=1000)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every GPU gets its own --batch rows (default); strong: the --batch rows are row-sharded over the GPUs (config C3)")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -189,6 +191,15 @@ def run_b200(a):
 
         dist = dist_mod
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # strong scaling (BASELINE config C3): the same batch, row-sharded contiguously over the ranks (netsdb_b200/shard.py)
+    row0 = rank * a.batch
+    total_rows = world * a.batch
+    if a.scaling == "strong":
+        from netsdb_b200.shard import row_shard
+
+        total_rows = a.batch
+        row0, a.batch = row_shard(total_rows, world, rank)
+    a.total_rows = total_rows
     capi.init(local)
     stream = torch.cuda.current_stream()
     capi.set_stream(stream.cuda_stream)
@@ -207,7 +218,7 @@ def run_b200(a):
     b1 = DS.create("ff", "b1", a.hidden, 1, blk, 1); b1.fill_synth(3)
     wo = DS.create("ff", "wo", a.labels, a.hidden, blk, blk); wo.fill_synth(4)
     bo = DS.create("ff", "bo", a.labels, 1, blk, 1); bo.fill_synth(5)
-    x = DS.create("ff", "inputs", a.batch, a.features, blk, blk); x.fill_synth(1, row_offset=rank * a.batch)
+    x = DS.create("ff", "inputs", a.batch, a.features, blk, blk); x.fill_synth(1, row_offset=row0)
     capi.synchronize()
 
     def step():
@@ -242,7 +253,7 @@ def run_b200(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     ms_per_step = ms / a.steps
-    value = world * a.batch / (ms_per_step / 1000.0)
+    value = total_rows / (ms_per_step / 1000.0)
     stats = {k: v / a.steps for k, v in agg.items()}
 
     # --- roofline of the dominant kernel: the layer-1 tcgen05 block GEMM ---
@@ -314,7 +325,7 @@ def run_b200(a):
 
     if rank == 0:
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=a.steps, warmup=max(a.warmup, 3),
-                    ms_per_step=ms_per_step, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    ms_per_step=ms_per_step, higher_is_better=True, scaling=a.scaling, vs_baseline=None,
                     dtype={"bf16": "bf16", "f16": "f16", "bf16x3": "bf16x3 (bf16 hi/lo split, fp32 accumulate)", "fp64": "f64"}[a.precision],
                     data="synthetic",
                     config=dict(workload=workload_name(a), parallelism=f"row-sharded dp{world}, weights replicated",
@@ -399,7 +410,7 @@ def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    v = world * a.batch / (ms / a.e2e_steps / 1000.0)
+    v = a.total_rows / (ms / a.e2e_steps / 1000.0)
     return dict(value=v, unit=UNIT, h2d_bytes_per_step=in_bytes, d2h_bytes_per_step=out_bytes + a.batch * 4,
                 ms_per_step=ms / a.e2e_steps, steps=a.e2e_steps,
                 note="inputs uploaded as fp64 FFMatrixBlocks from pinned host memory every step into two alternating sets (the next "
