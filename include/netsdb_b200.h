@@ -10,6 +10,13 @@
  *
  * There is no CPU fallback: if no sm_100 device is present nb200_init fails.
  *
+ * Threads and memory: one device per process (nb200_init after the worker's fork()).  Entry points may be called from
+ * any number of threads -- netsDB runs one pipeline thread per hash partition -- and are served one at a time (a
+ * process-wide lock: every call already fills the device).  Device memory comes from a caching allocator inside the
+ * library; the fused stages (nb200_ff_inference_unit, nb200_lstm_cell) allocate nothing in steady state.  Uploads are
+ * asynchronous: a source block must stay unmodified until nb200_synchronize() or the next call that returns data to the
+ * host (see nb200_pin_pool / nb200_upload_commit).
+ *
  * Paths in the citations are relative to the netsDB tree (venkate5hgunda/netsdb).
  */
 #ifndef NETSDB_B200_H
