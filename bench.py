@@ -191,8 +191,9 @@ def run_b200(a):
 
         dist = dist_mod
         # rank 0 prints ONE line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION goes to stdout) out of it
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # (the banner is printed at VERSION and above, WARN included; INFO is left alone: somebody asked for it)
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+            del os.environ["NCCL_DEBUG"]
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     # strong scaling (BASELINE config C3): the same batch, row-sharded contiguously over the ranks (netsdb_b200/shard.py)
     row0 = rank * a.batch
