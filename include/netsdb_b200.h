@@ -153,6 +153,23 @@ int nb200_set_rename(nb200_set *s, const char *db, const char *set);
 /* Drop the derived bf16 operand planes of a set (they are rebuilt from the fp64 data on next use). */
 int nb200_set_invalidate_planes(nb200_set *s);
 
+/* ---- fp16 side format ("a binary/bf16 side-format to cut the fp64 transfer and conversion cost") ----
+ * An input set can be kept, next to its fp64 FFMatrixBlocks, as what the tensor cores consume: one fp16 operand plane
+ * (row-major, row pitch ldk = total_cols rounded up to a multiple of 64, values x * 2^exp), the exponent and the per-row
+ * sums of squares of the error model.  nb200_set_export_f16 produces it on the device from a resident fp64 set (done once,
+ * at load time) and writes it to host memory; nb200_set_import_f16 brings a set into HBM from that format alone -- a
+ * quarter of the bytes over PCIe and no conversion -- asynchronously on the upload streams (nb200_upload_commit applies).
+ * nb200_ff_inference_unit(NB200_PREC_F16) accepts such a set as `inputs`; for the label-exact cascade it reads the fp64
+ * rows of the few undecided inputs straight out of the host blocks (zero-copy over PCIe), so `host_blocks` -- the
+ * row-major grid of pointers to the set's fp64 blocks, ceil(rows / block_rows) x ceil(cols / block_cols) entries -- must
+ * point into pinned, device-visible memory (nb200_pin_pool / cudaHostAlloc) and stay valid while the set is in use.
+ * edge_ld = row pitch of the blocks in the last block column (block_cols for zero-padded blocks, the remaining columns
+ * for trimmed ones).  The caller's plane, row_sumsq and pointer arrays must stay unmodified until nb200_synchronize()
+ * or the next call that returns data to the host. */
+int nb200_set_export_f16(nb200_set *set, void *plane_host, int64_t ldk, int *exp_out, float *row_sumsq_host);
+int nb200_set_import_f16(nb200_set *set, const void *plane_host, int64_t ldk, int exp, const float *row_sumsq_host,
+                         const double *const *host_blocks, int edge_ld);
+
 /* ---- operators ------------------------------------------------------------------------------- */
 /* JoinComp + ClusterAggregateComp as ONE block GEMM: FFTransposeMult|FFInputLayerJoin followed by
  * FFAggMatrix (FFAggMatrix.h:11-35; ClusterAggregateComp.h:40-344), optionally with the next

@@ -28,7 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
-    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell", "nb200_upload_commit",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell", "nb200_upload_commit", "nb200_set_export_f16", "nb200_set_import_f16",
 ]
 
 
@@ -90,6 +90,8 @@ def lib():
         L.nb200_gemm_blocks.argtypes = [i, vp, vp, i, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_softmax_rows.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(vp), vp]
         L.nb200_lstm_cell.argtypes = [C.POINTER(LstmSets), i, C.c_char_p]
+        L.nb200_set_export_f16.argtypes = [vp, vp, i64, C.POINTER(C.c_int), vp]
+        L.nb200_set_import_f16.argtypes = [vp, vp, i64, i, vp, vp, i]
         L.nb200_sum_blocks.argtypes = [vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
         L.nb200_ff_inference_unit.argtypes = [vp, vp, vp, vp, vp, i, C.c_char_p, C.c_char_p, C.POINTER(vp), vp,
                                               C.POINTER(FFStats)]
@@ -184,6 +186,27 @@ class DeviceSet:
         assert rect.dtype == np.float64 and rect.ndim == 2 and rect.strides[1] == 8
         check(lib().nb200_upload_rect(self.ptr, row0, col0, _hostptr(rect), rect.shape[0], rect.shape[1],
                                       rect.strides[0] // 8))
+
+    def f16_ldk(self) -> int:
+        return (self.info()[1] + 63) // 64 * 64
+
+    def export_f16(self, plane: np.ndarray | None = None, row_sumsq: np.ndarray | None = None):
+        """nb200_set_export_f16: (plane uint16[rows, ldk], exponent, row_sumsq float32[rows]) of a resident fp64 set."""
+        rows, ldk = self.info()[0], self.f16_ldk()
+        plane = np.empty((rows, ldk), dtype=np.uint16) if plane is None else plane
+        row_sumsq = np.empty(rows, dtype=np.float32) if row_sumsq is None else row_sumsq
+        e = C.c_int()
+        check(lib().nb200_set_export_f16(self.ptr, _hostptr(plane), ldk, C.byref(e), _hostptr(row_sumsq)))
+        return plane, e.value, row_sumsq
+
+    def import_f16(self, plane: np.ndarray, exp: int, row_sumsq: np.ndarray, block_ptrs: np.ndarray, edge_ld: int):
+        """nb200_set_import_f16: block_ptrs = uint64 array of the addresses of the set's fp64 host blocks (row-major block
+        grid, pinned memory).  All arrays must stay alive and unmodified until the next synchronising call."""
+        assert plane.dtype == np.uint16 and plane.flags["C_CONTIGUOUS"] and row_sumsq.dtype == np.float32
+        assert block_ptrs.dtype == np.uint64 and block_ptrs.flags["C_CONTIGUOUS"]
+        self._keep = (plane, row_sumsq, block_ptrs)
+        check(lib().nb200_set_import_f16(self.ptr, _hostptr(plane), plane.shape[1], int(exp), _hostptr(row_sumsq),
+                                         _hostptr(block_ptrs), int(edge_ld)))
 
     def upload_commit(self):
         """nb200_upload_commit: readers of this set wait for its uploads only."""

@@ -114,6 +114,7 @@ static void free_set_storage(nb200_set *s) {
     nb_free(s->f64); s->f64 = nullptr;
     nb_free(s->f32); s->f32 = nullptr;
     nb_free(s->wo_rownorm_max); s->wo_rownorm_max = nullptr;
+    nb_free(s->hb_dev); s->hb_dev = nullptr; s->hb_host.clear(); s->side_format = false;
     free_planes(&s->rowp);
     free_planes(&s->colp);
 }
@@ -449,6 +450,83 @@ int nb200_upload_commit(nb200_set *s) {
         NB_CUDA(cudaEventRecord(s->up_fence[i], c->copy[i]));
     }
     s->up_fenced = true;
+    return NB200_OK;
+}
+
+// ---- fp16 side format ---------------------------------------------------------------------------
+int nb200_set_export_f16(nb200_set *s, void *plane_host, int64_t ldk, int *exp_out, float *row_sumsq_host) {
+    NEED_CTX();
+    if (!s || !plane_host || !exp_out || !row_sumsq_host || s->view_of) { set_error("set_export_f16: invalid arguments"); return NB200_ERR_INVALID; }
+    if (ldk != round_up(s->total_cols, 64)) {
+        set_error("set_export_f16: ldk must be %lld (columns rounded up to a multiple of 64)", (long long)round_up(s->total_cols, 64));
+        return NB200_ERR_INVALID;
+    }
+    s->rowp.f16_valid = false;            // always from the exact maximum: this is the persistent copy
+    NB_TRY(ensure_f16_row(c, s, 1));
+    const size_t rows = static_cast<size_t>(s->total_rows);
+    NB_CUDA(cudaMemcpyAsync(plane_host, s->rowp.f16, rows * ldk * sizeof(__half), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(exp_out, s->rowp.f16_exp, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(row_sumsq_host, s->rowp.row_sumsq, rows * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB200_OK;
+}
+
+int nb200_set_import_f16(nb200_set *s, const void *plane_host, int64_t ldk, int exp, const float *row_sumsq_host,
+                         const double *const *host_blocks, int edge_ld) {
+    NEED_CTX_RAW();
+    if (!s || !plane_host || !row_sumsq_host || !host_blocks || s->view_of || edge_ld <= 0 || edge_ld > s->block_cols) {
+        set_error("set_import_f16: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    if (ldk != round_up(s->total_cols, 64)) {
+        set_error("set_import_f16: ldk must be %lld (columns rounded up to a multiple of 64)", (long long)round_up(s->total_cols, 64));
+        return NB200_ERR_INVALID;
+    }
+    const int n_rb = (s->total_rows + s->block_rows - 1) / s->block_rows, n_cb = (s->total_cols + s->block_cols - 1) / s->block_cols;
+    // the cascade's kernels dereference these pointers: they must be pinned host memory the device can see
+    for (int i = 0; i < n_rb * n_cb; i += (n_rb * n_cb > 1 ? n_rb * n_cb - 1 : 1)) {
+        cudaPointerAttributes at{};
+        if (!host_blocks[i] || cudaPointerGetAttributes(&at, host_blocks[i]) != cudaSuccess || at.type != cudaMemoryTypeHost ||
+            at.devicePointer != static_cast<const void *>(host_blocks[i])) {
+            cudaGetLastError();
+            set_error("set_import_f16: the fp64 host blocks must lie in pinned, device-visible memory (nb200_pin_pool / cudaHostAlloc)");
+            return NB200_ERR_INVALID;
+        }
+    }
+    if (s->f64) {  // the set now lives on the device in its side format only
+        if (s->up_epoch == c->up_epoch && c->uploads_pending) NB_TRY(wait_uploads(c));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        nb_free(s->f64); s->f64 = nullptr;
+    }
+    if (s->f32) { nb_free(s->f32); s->f32 = nullptr; }
+    drop_derived(s);
+    NB_TRY(alloc_f16_plane(c, &s->rowp, s->total_rows, s->total_cols));
+    if (!s->hb_dev) NB_CUDA(nb_malloc(&s->hb_dev, static_cast<size_t>(n_rb) * n_cb * sizeof(double *)));
+    s->hb_host.assign(host_blocks, host_blocks + static_cast<size_t>(n_rb) * n_cb);
+    s->hb_edge_ld = edge_ld;
+    s->hb_exp = exp;
+    c->main_dirty = true;  // (the plane may have been handed out by the allocator a moment ago)
+    NB_CUDA(cudaEventRecord(c->main_ev, c->stream));
+    for (auto &st : c->copy) NB_CUDA(cudaStreamWaitEvent(st, c->main_ev, 0));
+    c->main_dirty = false;
+    // the plane in pieces of 256 MB, alternating between the two upload streams like block uploads do
+    const size_t total = static_cast<size_t>(s->total_rows) * ldk * sizeof(__half), piece = size_t(256) << 20;
+    for (size_t off = 0; off < total; off += piece) {
+        const size_t n = total - off < piece ? total - off : piece;
+        NB_CUDA(cudaMemcpyAsync(reinterpret_cast<char *>(s->rowp.f16) + off, static_cast<const char *>(plane_host) + off, n,
+                                cudaMemcpyHostToDevice, c->copy[c->up_next]));
+        c->up_next ^= 1;
+    }
+    cudaStream_t cs = c->copy[0];
+    NB_CUDA(cudaMemcpyAsync(s->rowp.row_sumsq, row_sumsq_host, static_cast<size_t>(s->total_rows) * sizeof(float), cudaMemcpyHostToDevice, cs));
+    NB_CUDA(cudaMemcpyAsync(s->rowp.f16_exp, &s->hb_exp, sizeof(int), cudaMemcpyHostToDevice, cs));
+    NB_CUDA(cudaMemsetAsync(s->rowp.f16_maxscaled, 0, sizeof(float), cs));
+    NB_CUDA(cudaMemcpyAsync(s->hb_dev, s->hb_host.data(), s->hb_host.size() * sizeof(double *), cudaMemcpyHostToDevice, cs));
+    s->rowp.f16_valid = true;
+    s->side_format = true;
+    c->uploads_pending = true;
+    s->up_epoch = c->up_epoch;
+    s->up_fenced = false;
     return NB200_OK;
 }
 
@@ -1110,7 +1188,15 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
     if (wo->total_cols != H || wo->block_cols != w1->block_rows) { set_error("Block dimemsions mismatch! (wo vs y1)"); return NB200_ERR_SHAPE; }
     NB_TRY(bias_check(b1, H, "ReluBiasSum"));
     NB_TRY(bias_check(bo, Lb, "TransposeBiasSum"));
-    if (!w1->f64 || !wo->f64 || !inputs->f64 || !b1->f64 || !bo->f64) { set_error("ff_inference_unit: an input set holds no data"); return NB200_ERR_STATE; }
+    const bool side = inputs->side_format && inputs->rowp.f16_valid && inputs->hb_dev;  // resident in its fp16 side format only
+    if (!w1->f64 || !wo->f64 || (!inputs->f64 && !side) || !b1->f64 || !bo->f64) { set_error("ff_inference_unit: an input set holds no data"); return NB200_ERR_STATE; }
+    if (side && !inputs->f64 && precision != NB200_PREC_F16) {
+        set_error("ff_inference_unit: a set imported in the fp16 side format can only be evaluated with NB200_PREC_F16");
+        return NB200_ERR_INVALID;
+    }
+    const HostBlocks hb{inputs->hb_dev, inputs->block_rows, inputs->block_cols,
+                        (inputs->total_cols + inputs->block_cols - 1) / inputs->block_cols, inputs->hb_edge_ld};
+    const bool from_host = side && !inputs->f64;
 
     const int64_t launches0 = c->launches;
     // a repeated call replaces its result sets: take over their buffers instead of freeing and re-allocating
@@ -1247,7 +1333,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
             const int chunk2 = 8192;
             for (int r0 = 0; r0 < n1; r0 += chunk2) {
                 const int R = std::min(chunk2, n1 - r0);
-                NB_TRY(launch_gather_convert_rows(c, inputs->f64, F, F, S.list + r0, R, &S.xsub));
+                if (from_host) NB_TRY(launch_gather_convert_rows_hb(c, hb, F, S.list + r0, R, &S.xsub));
+                else NB_TRY(launch_gather_convert_rows(c, inputs->f64, F, F, S.list + r0, R, &S.xsub));
                 const size_t need = static_cast<size_t>(R) * Lb * sizeof(float);
                 if (need > S.logits_sub_bytes) {
                     nb_free(S.logits_sub);
@@ -1278,7 +1365,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
             NB_TRY(grow(&S.xg, &S.xg_bytes, static_cast<size_t>(chunk) * F * sizeof(double)));
             NB_TRY(grow(&S.y1g, &S.y1g_bytes, static_cast<size_t>(chunk) * H * sizeof(double)));
             NB_TRY(grow(&S.zg, &S.zg_bytes, static_cast<size_t>(chunk) * Lb * sizeof(double)));
-            NB_TRY(launch_gather_rows_f64(c, inputs->f64, F, F, final_list + r0, R, S.xg));
+            if (from_host) NB_TRY(launch_gather_rows_f64_hb(c, hb, F, final_list + r0, R, S.xg));
+            else NB_TRY(launch_gather_rows_f64(c, inputs->f64, F, F, final_list + r0, R, S.xg));
             F64Epilogue e1; e1.bias_n = b1->f64; e1.relu = 1;
             NB_TRY(launch_gemm_f64(c, S.xg, F, 1, w1->f64, F, 1, R, H, F, S.y1g, H, e1));
             F64Epilogue e2; e2.bias_n = bo->f64;

@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/netsdb_b200.h"
 
@@ -177,6 +178,19 @@ int launch_convert_sub(Context *c, const double *src, int64_t ld, int64_t rows, 
 int alloc_planes_raw(Planes *p, int64_t rows, int64_t k, bool want_lo);
 int launch_lstm_gates(Context *c, const float *g, int64_t g_ld, int L, int B, const double *bf, const double *bi,
                       const double *bo, const double *bc, double *f_t, double *i_t, double *o_t, double *c_temp);
+// The fp64 blocks of a set as they lie in (pinned, device-visible) HOST memory: a row-major grid of block pointers.
+// Kernels read single rows out of them over PCIe (zero-copy) for the label-exact cascade of a set that is resident on
+// the device only in its fp16 side format.
+struct HostBlocks {
+    const double *const *blocks;  // device array of n_rb x n_cb host pointers
+    int block_rows, block_cols;   // nominal block size
+    int n_cb;                     // block columns
+    int edge_ld;                  // row pitch of the blocks of the LAST block column (block_cols when padded, the
+                                  // remaining columns when trimmed); all other blocks have pitch block_cols
+};
+int launch_gather_convert_rows_hb(Context *c, const HostBlocks &hb, int64_t cols, const int32_t *list, int n, Planes *p);
+int launch_gather_rows_f64_hb(Context *c, const HostBlocks &hb, int64_t cols, const int32_t *list, int n, double *dst);
+int alloc_f16_plane(Context *c, Planes *p, int64_t rows, int64_t cols);  // storage of an fp16 operand plane, no conversion
 int launch_sum_blocks(Context *c, const EwiseSrc *src, int nsrc, int act, int64_t rows, int64_t cols, double *out);
 int launch_bias_relu_f32(Context *c, float *p, int64_t rows, int64_t cols, int64_t ld, const float *bias_n);
 int launch_synth_fill(Context *c, double *dst, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
@@ -236,6 +250,11 @@ struct nb200_set {
     uint64_t up_epoch = 0;
     cudaEvent_t up_fence[2] = {nullptr, nullptr};
     bool up_fenced = false;
+    // fp16 side format (nb200_set_import_f16): no fp64 copy on the device, rows are fetched from the host blocks on demand
+    const double **hb_dev = nullptr;
+    std::vector<const double *> hb_host;  // the pointer table as given (kept: its upload is asynchronous)
+    int hb_edge_ld = 0, hb_exp = 0;
+    bool side_format = false;
     bool view_exp = false;         // downloads apply exp() (the `yo` view of the logits)
     nb200_set *view_of = nullptr;  // set whose storage a view reads
 };

@@ -241,6 +241,25 @@ k_convert_f16(const T *__restrict__ src, long long ld, long long rows, long long
     if (threadIdx.x == 0 && maxscaled) atomicMax(reinterpret_cast<unsigned int *>(maxscaled), __float_as_uint(mx));
 }
 
+int alloc_f16_plane(Context *c, Planes *p, int64_t rows, int64_t cols) {
+    const int64_t ldk = round_up(cols, 64);
+    if ((p->hi || p->f16) && (p->cap_rows < rows || p->ldk != ldk)) {
+        nb_free(p->hi); nb_free(p->lo); nb_free(p->row_sumsq); nb_free(p->maxabs);
+        nb_free(p->f16); nb_free(p->f16_exp); nb_free(p->f16_maxscaled);
+        *p = Planes();
+    }
+    if (!p->hi && !p->f16) p->cap_rows = rows;
+    p->rows = rows; p->k = cols; p->ldk = ldk;
+    const size_t cap = static_cast<size_t>(p->cap_rows ? p->cap_rows : 1);
+    if (!p->f16) NB_CUDA(nb_malloc(&p->f16, cap * ldk * sizeof(__half)));
+    if (!p->f16_exp) NB_CUDA(nb_malloc(&p->f16_exp, sizeof(int)));
+    if (!p->f16_maxscaled) NB_CUDA(nb_malloc(&p->f16_maxscaled, sizeof(float)));
+    if (!p->row_sumsq) NB_CUDA(nb_malloc(&p->row_sumsq, cap * sizeof(float)));
+    if (!p->maxabs) NB_CUDA(nb_malloc(&p->maxabs, sizeof(float)));
+    (void)c;
+    return NB200_OK;
+}
+
 int prepare_convert_f16(Context *c, const void *src, bool src_is_f64, int64_t rows, int64_t cols, int64_t ld, Planes *p,
                         int sample_stride, const float *known_maxabs) {
     const int64_t ldk = round_up(cols, 64);
@@ -451,6 +470,50 @@ int launch_gather_convert_rows(Context *c, const double *src, int64_t ld, int64_
     const int64_t chunks = ceil_div(p->ldk, kCvtThreads * 4);
     dim3 grid(n, static_cast<unsigned>(chunks < 64 ? chunks : 64));
     k_gather_convert_rows<<<grid, kCvtThreads, 0, c->stream>>>(src, ld, cols, list, p->hi, p->lo, p->ldk);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+// The same two gathers for a set whose fp64 data live in HOST blocks (side format): the listed rows are read straight
+// out of pinned host memory over PCIe, one block-column segment at a time (each warp reads contiguous runs).
+__device__ __forceinline__ double hb_at(const HostBlocks &hb, long long r, long long cidx) {
+    const int bcol = static_cast<int>(cidx / hb.block_cols);
+    const double *blk = hb.blocks[(r / hb.block_rows) * hb.n_cb + bcol];
+    const long long ld = (bcol == hb.n_cb - 1) ? hb.edge_ld : hb.block_cols;
+    return blk[(r % hb.block_rows) * ld + (cidx - static_cast<long long>(bcol) * hb.block_cols)];
+}
+__global__ void __launch_bounds__(kCvtThreads)
+k_gather_convert_rows_hb(HostBlocks hb, long long cols, const int32_t *__restrict__ list, __nv_bfloat16 *__restrict__ hi,
+                         __nv_bfloat16 *__restrict__ lo, long long ldk) {
+    const long long i = blockIdx.x, r = list[i];
+    for (long long c = (static_cast<long long>(blockIdx.y) * kCvtThreads + threadIdx.x) * 4; c < ldk;
+         c += static_cast<long long>(gridDim.y) * kCvtThreads * 4) {
+        __nv_bfloat16 h4[4], l4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) split_bf16<double>((c + j < cols) ? hb_at(hb, r, c + j) : 0.0, h4[j], l4[j]);
+        *reinterpret_cast<uint2 *>(hi + i * ldk + c) = *reinterpret_cast<uint2 *>(h4);
+        *reinterpret_cast<uint2 *>(lo + i * ldk + c) = *reinterpret_cast<uint2 *>(l4);
+    }
+}
+int launch_gather_convert_rows_hb(Context *c, const HostBlocks &hb, int64_t cols, const int32_t *list, int n, Planes *p) {
+    NB_TRY(alloc_planes(p, n, cols, true));
+    p->valid = p->lo_valid = true;
+    if (n == 0) return NB200_OK;
+    const int64_t chunks = ceil_div(p->ldk, kCvtThreads * 4);
+    dim3 grid(n, static_cast<unsigned>(chunks < 64 ? chunks : 64));
+    k_gather_convert_rows_hb<<<grid, kCvtThreads, 0, c->stream>>>(hb, cols, list, p->hi, p->lo, p->ldk);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+__global__ void k_gather_rows_f64_hb(HostBlocks hb, long long cols, const int32_t *__restrict__ list, double *__restrict__ dst) {
+    const long long r = list[blockIdx.y];
+    for (long long j = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; j < cols;
+         j += static_cast<long long>(gridDim.x) * blockDim.x)
+        dst[static_cast<long long>(blockIdx.y) * cols + j] = hb_at(hb, r, j);
+}
+int launch_gather_rows_f64_hb(Context *c, const HostBlocks &hb, int64_t cols, const int32_t *list, int n, double *dst) {
+    if (n == 0 || cols == 0) return NB200_OK;
+    dim3 grid(static_cast<unsigned>(ceil_div(cols, 256) < 64 ? ceil_div(cols, 256) : 64), n);
+    k_gather_rows_f64_hb<<<grid, 256, 0, c->stream>>>(hb, cols, list, dst);
     NB_LAUNCH_CHECK(c);
     return NB200_OK;
 }

@@ -406,6 +406,52 @@ def test_upload_commit_overlaps_next_batch(nb, oracle):
     B.destroy()
 
 
+@pytest.mark.parametrize("trim", [False, True])
+def test_fp16_side_format_inputs(nb, oracle, trim):
+    """the inputs kept as an fp16 operand plane next to their fp64 blocks.  Exported once from the resident
+    fp64 set, imported into a set that holds NO fp64 data on the device, evaluated with the label-exact cascade whose
+    undecided rows are read straight out of the pinned host blocks (zero-padded or trimmed edge blocks).  Labels equal the
+    oracle's and the fp64-resident run's; logits are bit-identical to that run's first level."""
+    import torch
+
+    batch, feat, hid, lab, blk = 1300, 8300, 300, 40, 1000
+    dev, ora, dense = _ff_sets(nb, oracle, batch, feat, hid, lab, blk, wo_scale=0.02)  # small wo: many near ties
+    _, _, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=4)
+    plane, e, ss = dev["x"].export_f16()
+    _, labels_res, st_res = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PREC_F16)
+    z_res = nb.DeviceSet.lookup("ff", "__logits").download_dense()
+    assert np.array_equal(labels_res, ref_labels)
+    # the fp64 blocks in pinned host memory, as a netsDB page would hold them
+    n_rb, n_cb = -(-batch // blk), -(-feat // blk)
+    pinned, ptrs = [], np.zeros(n_rb * n_cb, dtype=np.uint64)
+    for i in range(n_rb):
+        for j in range(n_cb):
+            rows = min(blk, batch - i * blk) if trim else blk
+            cols = min(blk, feat - j * blk) if trim else blk
+            t = torch.zeros(rows * cols, dtype=torch.float64).pin_memory()
+            b = t.numpy().reshape(rows, cols)
+            src = dense["x"][i * blk:i * blk + rows, j * blk:j * blk + cols]
+            b[:src.shape[0], :src.shape[1]] = src
+            pinned.append(t)
+            ptrs[i * n_cb + j] = b.ctypes.data
+    edge_ld = (feat - (n_cb - 1) * blk) if trim else blk
+    S = nb.DeviceSet.create("ff", "inputs_side", batch, feat, blk, blk)
+    pp = torch.from_numpy(plane.view(np.int16)).pin_memory().numpy().view(np.uint16)
+    for rep in range(2):
+        S.import_f16(pp, e, ss, ptrs, edge_ld)
+        S.upload_commit()
+        out, labels, st = nb.ff_inference_unit(dev["w1"], dev["wo"], S, dev["b1"], dev["bo"], nb.PREC_F16)
+        assert np.array_equal(labels, ref_labels), (labels != ref_labels).sum()
+        assert st["relevel_rows"] == st_res["relevel_rows"] > 0  # the cascade ran, on rows fetched from the host blocks
+        assert np.array_equal(nb.DeviceSet.lookup("ff", "__logits").download_dense(), z_res)
+    with pytest.raises(nb.Nb200Error):  # no fp64 on the device: only the fp16 evaluation is possible
+        nb.ff_inference_unit(dev["w1"], dev["wo"], S, dev["b1"], dev["bo"], nb.PREC_BF16X3)
+    unpinned = np.zeros(n_rb * n_cb, dtype=np.uint64) + np.uint64(np.zeros(8).ctypes.data)
+    with pytest.raises(nb.Nb200Error):  # host blocks the device cannot see
+        S.import_f16(pp, e, ss, unpinned, edge_ld)
+    S.destroy()
+
+
 def test_concurrent_callers_are_serialised(nb, oracle):
     """netsDB runs one pipeline thread per hash partition, all calling UDFs at once (threading).  The
     library serialises its entry points, so concurrent calls from several threads give the same results as sequential
