@@ -415,10 +415,70 @@ def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     v = a.total_rows / (ms / a.e2e_steps / 1000.0)
+    x2.destroy()
+    side = None
+    try:
+        side = run_e2e_side_format(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, blocks, oh, n_cb)
+    except Exception as e:  # noqa: BLE001 -- an extra, never the headline
+        side = dict(value=None, note=f"failed: {e!r}")
     return dict(value=v, unit=UNIT, h2d_bytes_per_step=in_bytes, d2h_bytes_per_step=out_bytes + a.batch * 4,
-                ms_per_step=ms / a.e2e_steps, steps=a.e2e_steps,
+                ms_per_step=ms / a.e2e_steps, steps=a.e2e_steps, side_format=side,
                 note="inputs uploaded as fp64 FFMatrixBlocks from pinned host memory every step into two alternating sets (the next "
                      "step's transfer runs under the current step's computation); weights model-resident")
+
+
+def run_e2e_side_format(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, blocks, oh, n_cb):
+    """Extra, not the headline: the same end-to-end step when the host also keeps the inputs in the
+    library's fp16 side format (exported once, untimed, like netsDB's load phase).  Per step the fp16 plane crosses PCIe
+    (a quarter of the bytes, no conversion on the device) into one of two alternating sets; the label-exact cascade reads
+    the fp64 rows of the undecided inputs straight out of the pinned host blocks."""
+    import numpy as np
+
+    if a.precision != "f16":
+        return None
+    ldk = x.f16_ldk()
+    plane = torch.empty(a.batch * ldk, dtype=torch.int16).pin_memory().numpy().view(np.uint16).reshape(a.batch, ldk)
+    ss = torch.empty(a.batch, dtype=torch.float32).pin_memory().numpy()
+    _, e, _ = x.export_f16(plane, ss)
+    ptrs = np.array([view.ctypes.data for _, _, view in blocks], dtype=np.uint64)
+    edge_ld = blocks[n_cb - 1][2].shape[1]
+    bufs = [capi.DeviceSet.create("ff", "inputs_s0", a.batch, a.features, a.block, a.block),
+            capi.DeviceSet.create("ff", "inputs_s1", a.batch, a.features, a.block, a.block)]
+
+    def upload(dst):
+        dst.import_f16(plane, e, ss, ptrs, edge_ld)
+        dst.upload_commit()
+
+    def run(n_steps):
+        upload(bufs[0])
+        labels = None
+        for k in range(n_steps):
+            if k + 1 < n_steps:
+                upload(bufs[(k + 1) % 2])
+            out, labels, st = capi.ff_inference_unit(w1, wo, bufs[k % 2], b1, bo, prec, "ff", "output")
+            capi.check(capi.lib().nb200_download_rect(out.ptr, 0, 0, oh.ctypes.data, a.batch, a.labels, a.labels))
+        return labels, st
+
+    ref_labels = capi.ff_inference_unit(w1, wo, x, b1, bo, prec, "ff", "output")[1]
+    labels, _ = run(2)
+    same = bool(np.array_equal(labels, ref_labels))
+    barrier()
+    t0 = time.perf_counter()
+    _, st = run(a.e2e_steps)
+    capi.synchronize()
+    barrier()
+    ms = (time.perf_counter() - t0) * 1000.0
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    for b in bufs:
+        b.destroy()
+    return dict(value=a.total_rows / (ms / a.e2e_steps / 1000.0), unit=UNIT, ms_per_step=ms / a.e2e_steps,
+                h2d_bytes_per_step=int(plane.nbytes + ss.nbytes), labels_equal_fp64_resident_run=same,
+                rows_fetched_from_host_blocks=int(st["relevel_rows"]),
+                note="inputs cross PCIe as the fp16 side-format plane (exported once, untimed); undecided rows of the "
+                     "label-exact cascade are read as fp64 from the pinned host blocks (zero-copy)")
 
 
 if __name__ == "__main__":
