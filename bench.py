@@ -283,16 +283,17 @@ def run_b200(a):
     # the fused kernel reads the fp64 inputs once while it multiplies: it is bounded by the slower of the two
     rows_fused = (148 // 2 // ((a.hidden + 511) // 512)) * 256 if fused_on else a.batch
     rows_fused = min(rows_fused, a.batch // 256 * 256) if fused_on else a.batch
-    # the event window around layer 1 also covers the left-over rows' two kernels, so all rows count
-    flops_k = flops1
-    bytes_k = a.batch * a.features * 8.0 + a.hidden * a.features * 2.0 if fused_on else None
+    # ms_gemm1_kernel is the event window around the dominant kernel alone: with the fused kernel that is k_l1_fused on
+    # its rows_fused rows (the left-over rows' two kernels are outside it), otherwise the block GEMM on all rows
+    flops_k = 2.0 * rows_fused * a.hidden * a.features
+    bytes_k = rows_fused * a.features * 8.0 + a.hidden * a.features * 2.0 if fused_on else None
     ach = flops_k / (k_ms / 1000.0) / 1e12 if k_ms > 0 else None
     roofline = dict(bound="tensor", kernel=("k_l1_fused<4> (layer 1: fp64->fp16 conversion inside the 2-SM tcgen05 GEMM)" if fused_on
                                             else "k_block_gemm_2sm<2,4> (layer 1)"),
                     achieved=ach, peak=peak_tf, unit="TFLOP/s",
                     frac=(ach / peak_tf if ach else None),
                     traffic=((traffic or {}).get("k_l1_fused<4>" if fused_on else "k_block_gemm_2sm<2,4> (layer 1)")), peak_source=which,
-                    algorithmic_flops_per_launch=flops_k,
+                    algorithmic_flops_per_launch=flops_k, rows_per_launch=int(rows_fused), ms_per_launch=k_ms,
                     hbm=(dict(algorithmic_bytes=bytes_k, achieved_gbs=bytes_k / (k_ms / 1e3) / 1e9, peak_gbs=hbm_peak,
                               frac=bytes_k / (k_ms / 1e3) / 1e9 / hbm_peak) if fused_on and k_ms > 0 else None),
                     executed_over_useful=3 if a.precision == "bf16x3" else 1)

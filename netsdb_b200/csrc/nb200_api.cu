@@ -1053,6 +1053,7 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
                 rl.out_maxabs = y1_max;  // cleared and set here; the fused kernel folds its own maximum in afterwards
                 NB_TRY(launch_splitk_reduce(c, rows - rows_f, H, used, mp, np, nullptr, b1, 1, rl));
             }
+            if (k0) NB_CUDA(cudaEventRecord(k0, c->stream));  // the kernel-only window (ms_gemm1_kernel) is the fused kernel's
             NB_TRY(launch_l1_fused(c, static_cast<const double *>(pipe->src), pipe->ld, rows, static_cast<int>(pipe->cols), 0, n_mtiles,
                                    *pipe->planes, w1->rowp, H, b1, *y1_f32, H, y1_max, pipe->fused));
             pipe->planes->f16_valid = false;  // the full fp16 plane of the inputs was never materialised
