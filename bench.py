@@ -360,7 +360,10 @@ def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):
         avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
     except Exception:
         avail = 0
-    if avail < (in_bytes + out_bytes) * world * 1.3:
+    fits = torch.tensor([1 if avail >= (in_bytes + out_bytes) * world * 1.3 else 0], device="cuda")
+    if dist is not None:
+        dist.all_reduce(fits, op=dist.ReduceOp.MIN)  # one decision for all ranks (they share the host)
+    if int(fits.item()) == 0:
         return dict(value=None, unit=UNIT, h2d_bytes_per_step=in_bytes, d2h_bytes_per_step=out_bytes,
                     note=f"skipped: host has {avail >> 30} GiB available, needs {(in_bytes + out_bytes) * world >> 30} GiB pinned")
     # pinned host pool holding the inputs as the reference stores them: one row-major fp64 buffer per FFMatrixBlock
@@ -438,6 +441,17 @@ def run_e2e_side_format(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, 
     if a.precision != "f16":
         return None
     ldk = x.f16_ldk()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    try:  # every rank pins another copy of the inputs (a quarter of their size): never push the host out of memory
+        avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+    except Exception:
+        avail = 0
+    need = a.batch * ldk * 2 * world
+    ok = torch.tensor([1 if avail >= need * 1.5 + (32 << 30) else 0], device="cuda")
+    if dist is not None:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks take the same decision
+    if int(ok.item()) == 0:
+        return dict(value=None, note=f"skipped: host has {avail >> 30} GiB available, the pinned side-format copies need {need >> 30} GiB")
     plane = torch.empty(a.batch * ldk, dtype=torch.int16).pin_memory().numpy().view(np.uint16).reshape(a.batch, ldk)
     ss = torch.empty(a.batch, dtype=torch.float32).pin_memory().numpy()
     _, e, _ = x.export_f16(plane, ss)
