@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnetsdb_b200.so")
-SOURCES = ["nb200_api.cu", "nb200_gemm.cu", "nb200_kernels.cu", "nb200_pool.cu"]
+SOURCES = ["nb200_api.cu", "nb200_gemm.cu", "nb200_l1stream.cu", "nb200_kernels.cu", "nb200_pool.cu"]
 HEADERS = ["nb200_internal.h", "nb200_ptx.cuh", os.path.join("..", "..", "include", "netsdb_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",

@@ -24,7 +24,12 @@ void set_error(const char *fmt, ...) {
 }
 
 static Context *g_ctx = nullptr;
-static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default on)
+static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default 2); 0 separate kernels, 1 ring kernel, 2 stream kernel
+static int fused_mode() {
+    if (g_opt_fused >= 0) return g_opt_fused;
+    static const int env = getenv("NB200_FUSED") ? atoi(getenv("NB200_FUSED")) : 2;
+    return env < 0 ? 0 : (env > 2 ? 2 : env);
+}
 static std::mutex g_mu;
 // Serialises the entry points: the library keeps one compute stream, one split-K workspace and one set of scratch buffers per
 // process, so calls from netsDB's pipeline threads (one per hash partition, work/source/PDBWorkerQueue.cc:163) run one at a
@@ -279,6 +284,7 @@ int nb200_init(int device) {
 }
 
 static void release_lstm_scratch(void);
+static void release_ff_scratch(void);
 
 int nb200_shutdown(void) {
     std::lock_guard<std::recursive_mutex> api_lock(g_api_mu);
@@ -286,6 +292,7 @@ int nb200_shutdown(void) {
     if (!g_ctx) return NB200_OK;
     cudaStreamSynchronize(g_ctx->stream);
     release_lstm_scratch();
+    release_ff_scratch();
     for (auto &kv : g_sets) {
         free_set_storage(kv.second);
         delete kv.second;
@@ -326,7 +333,7 @@ int nb200_synchronize(void) {
 int64_t nb200_launch_count(void) { return g_ctx ? g_ctx->launches : 0; }
 
 int nb200_set_option(const char *key, int value) {
-    if (key && !strcmp(key, "fused_layer1")) { g_opt_fused = value ? 1 : 0; return NB200_OK; }
+    if (key && !strcmp(key, "fused_layer1")) { g_opt_fused = value < 0 ? -1 : (value > 2 ? 2 : value); return NB200_OK; }
     set_error("set_option: unknown key");
     return NB200_ERR_INVALID;
 }
@@ -1005,6 +1012,7 @@ struct PipeSrc {
     int64_t ld, cols;
     Planes *planes;
     FusedScratch *fused;  // non-null: use the fused conversion + GEMM kernel (fp64 source, fp16 operands)
+    L1StreamScratch *stream = nullptr;  // non-null: prefer the cluster kernel of nb200_l1stream.cu where the shape suits it
 };
 static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt, nb200_set *w1, nb200_set *wo, const float *b1,
                       const float *bo, Planes *y1, float **y1_f32, size_t *y1_f32_bytes, float *y1_max, float *logits,
@@ -1018,7 +1026,29 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
     if (k0) NB_CUDA(cudaEventRecord(k0, c->stream));
     const int want_splits = choose_splits(c, rows, H, X.ldk, nterms);
     bool fused_done = false;
-    if (pipe && pipe->fused && f16 && pipe->is_f64) {
+    int fused_slots = 1;
+    if (pipe && pipe->fused && pipe->stream && f16 && pipe->is_f64 && X.ldk >= 4096 &&
+        l1_stream_supported(static_cast<const double *>(pipe->src), pipe->ld, pipe->cols, H, w1->rowp)) {
+        // Streamed layer 1: the whole batch through the cluster kernel (conversion inside, K split in waves), then one
+        // pass that sums the partial tiles and applies FFReluBiasSum.
+        const size_t need = static_cast<size_t>(rows) * H * sizeof(float);
+        if (need > *y1_f32_bytes) {
+            nb_free(*y1_f32);
+            *y1_f32 = nullptr;
+            *y1_f32_bytes = 0;
+            NB_CUDA(nb_malloc(y1_f32, need));
+            *y1_f32_bytes = need;
+        }
+        if (k0) NB_CUDA(cudaEventRecord(k0, c->stream));
+        NB_TRY(launch_l1_stream(c, static_cast<const double *>(pipe->src), pipe->ld, rows, static_cast<int>(pipe->cols),
+                                pipe->planes->f16_exp, pipe->planes->row_sumsq, pipe->planes->f16_maxscaled, w1->rowp, H, pipe->stream));
+        if (k1) NB_CUDA(cudaEventRecord(k1, c->stream));
+        NB_TRY(launch_l1_stream_reduce(c, *pipe->stream, rows, H, b1, 1, pipe->planes->f16_exp, w1->rowp.f16_exp, *y1_f32, H, y1_max));
+        pipe->planes->f16_valid = false;  // the fp16 plane of the inputs was never materialised
+        fused_done = true;
+        fused_slots = pipe->stream->plan.max_slots;
+        k1 = nullptr;                     // recorded above: the kernel-only window excludes the reduction
+    } else if (pipe && pipe->fused && f16 && pipe->is_f64) {
         // Fused layer 1: as many whole 256-row tiles as there are SM pairs go through the persistent kernel that
         // converts fp64 -> fp16 inside the GEMM; the left-over rows take the two-kernel path first.
         const int sms = c->sm_count > 0 ? c->sm_count : 148;
@@ -1063,7 +1093,7 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
     }
     if (fused_done) {
         if (k1) NB_CUDA(cudaEventRecord(k1, c->stream));
-        *splits1 = 1;
+        *splits1 = fused_slots;
         NB_TRY(launch_convert_f16(c, *y1_f32, false, rows, H, H, y1, 1, y1_max));
         if (after_l1) NB_CUDA(cudaEventRecord(after_l1, c->stream));
     } else if (!pipe || pipe->fused) {
@@ -1158,8 +1188,21 @@ struct FFScratch {  // reused across calls
     float *y1_max = nullptr;
     float *host_scalars = nullptr;  // pinned: [0] = largest scaled |x| of the inputs' fp16 conversion
     FusedScratch fused;             // ring + flags of the fused layer-1 kernel
+    L1StreamScratch l1s;            // wave plan of the streamed layer-1 kernel
 };
 static FFScratch g_ff;
+
+// nb200_shutdown: nothing of the fused stage's scratch may outlive the context (a later nb200_init may bind another device)
+static void release_ff_scratch(void) {
+    FFScratch &S = g_ff;
+    for (Planes *p : {&S.y1, &S.xsub, &S.y1sub}) free_planes(p);
+    nb_free(S.logits); nb_free(S.labels); nb_free(S.gap); nb_free(S.list); nb_free(S.count); nb_free(S.xg); nb_free(S.y1g);
+    nb_free(S.zg); nb_free(S.logits_sub); nb_free(S.list2); nb_free(S.y1_f32); nb_free(S.y1_max);
+    nb_free(S.fused.ring); nb_free(S.fused.flags); nb_free(S.l1s.dev);
+    if (S.count_host) cudaFreeHost(S.count_host);
+    if (S.host_scalars) cudaFreeHost(S.host_scalars);
+    S = FFScratch();
+}
 
 static int grow(double **p, size_t *have, size_t need) {
     if (need <= *have) return NB200_OK;
@@ -1285,8 +1328,8 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         // pipelined with the layer-1 GEMM chunk by chunk (tc_forward) and only the scale is picked here; measured on
         // B200 the two kernels do not overlap usefully (phase time = sum of both), so it is off by default.
         static const bool overlap = getenv("NB200_OVERLAP") && atoi(getenv("NB200_OVERLAP")) != 0;  // off by default, see DESIGN.md
-        const bool fused = g_opt_fused >= 0 ? g_opt_fused != 0 : !(getenv("NB200_FUSED") && atoi(getenv("NB200_FUSED")) == 0);
-        PipeSrc pipe{inputs->f64, true, F, F, &inputs->rowp, fused ? &S.fused : nullptr};
+        const bool fused = fused_mode() != 0;
+        PipeSrc pipe{inputs->f64, true, F, F, &inputs->rowp, fused ? &S.fused : nullptr, fused_mode() == 2 ? &S.l1s : nullptr};
         bool pipelined = false;
         if (fmt == kFmtF16) {
             if (!inputs->rowp.f16_valid && (overlap || fused) && static_cast<int64_t>(F) >= 8192) {
@@ -1416,6 +1459,26 @@ int nb200_ff_layer1_partial(nb200_set *w1, nb200_set *inputs, int precision, flo
     const int fmt = precision == NB200_PREC_F16 ? kFmtF16 : kFmtBF16;
     if (fmt == kFmtF16) {
         NB_TRY(ensure_f16_row(c, w1, 1));
+        if (fused_mode() == 2 && inputs->f64 && !inputs->rowp.f16_valid && Fs >= 4096 &&
+            l1_stream_supported(inputs->f64, Fs, Fs, H, w1->rowp)) {
+            // the shard's fp64 blocks go through the cluster kernel as they are (no fp16 plane of the inputs)
+            NB_TRY(prepare_convert_f16(c, inputs->f64, true, B, Fs, Fs, &inputs->rowp, 64, nullptr));
+            NB_TRY(launch_l1_stream(c, inputs->f64, Fs, B, Fs, inputs->rowp.f16_exp, inputs->rowp.row_sumsq,
+                                    inputs->rowp.f16_maxscaled, w1->rowp, H, &g_ff.l1s));
+            NB_TRY(launch_l1_stream_reduce(c, g_ff.l1s, B, H, nullptr, 0, inputs->rowp.f16_exp, w1->rowp.f16_exp, partial_dev, ld, nullptr));
+            inputs->rowp.f16_valid = false;
+            if (ld > H)
+                NB_CUDA(cudaMemcpy2DAsync(partial_dev + H, static_cast<size_t>(ld) * sizeof(float), inputs->rowp.row_sumsq, sizeof(float),
+                                          sizeof(float), B, cudaMemcpyDeviceToDevice, c->stream));
+            float mx = 0.f;
+            NB_CUDA(cudaMemcpyAsync(&mx, inputs->rowp.f16_maxscaled, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            if (!(mx < 65504.f)) {
+                set_error("ff_layer1_partial: an input overflowed the sampled fp16 scale; use NB200_PREC_BF16 or BF16X3");
+                return NB200_ERR_STATE;
+            }
+            return check_kernel_fault(c, "ff_layer1_partial");
+        }
         NB_TRY(ensure_f16_row(c, inputs, 64));
     } else {
         NB_TRY(ensure_rowp(c, w1, nterms == 3));

@@ -127,6 +127,30 @@ struct FusedScratch {
 int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, int cols, int row_base, int n_mtiles,
                     const Planes &xp, const Planes &w1, int N, const float *bias_n, float *out, int64_t out_ld,
                     float *out_maxabs, FusedScratch *fs);
+// streamed layer 1 (nb200_l1stream.cu): fp64 inputs converted inside the clusters that consume them, (M tile, K range)
+// segments laid out in waves; fp32 partial tiles go to ctx->ws and launch_l1_stream_reduce sums them
+struct L1StreamSeg { int tile, kb0, kb1, slot; };
+struct L1StreamPlan {
+    std::vector<L1StreamSeg> segs;   // [clusters][max_seg], each cluster's list ends at the first empty segment
+    std::vector<int> tile_slots;     // partial tiles per cluster tile
+    int clusters = 0, max_seg = 0, max_slots = 1;
+};
+struct L1StreamScratch {
+    L1StreamPlan plan;
+    int plan_rows = -1, plan_kb = -1, plan_g = -1, plan_mt = -1;
+    unsigned char *dev = nullptr;    // device copy of the plan
+    size_t dev_bytes = 0;
+    const L1StreamSeg *seg_dev = nullptr;
+    const int *slots_dev = nullptr;
+    int tile_rows = 0;
+    long long slot_stride = 0;
+};
+int plan_l1_stream(int tiles, int num_kb, int clusters, L1StreamPlan *plan);
+bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1);
+int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,
+                     float *maxscaled, const Planes &w1, int N, L1StreamScratch *sc);
+int launch_l1_stream_reduce(Context *c, const L1StreamScratch &sc, int rows, int N, const float *bias_n, int relu,
+                            const int *exp_u, const int *exp_v, float *out, int64_t out_ld, float *out_maxabs);
 // conv2d as implicit GEMM: NHWC bf16 image (channels padded to cp, multiple of 64), kernel planes with K = (tap, channel)
 int launch_conv_implicit(Context *c, const __nv_bfloat16 *img_hi, const __nv_bfloat16 *img_lo, int n, int h, int w, int cp,
                          const Planes &ker, int kout, int k, int pad, int nterms, const float *bias, int relu, float *out);

@@ -1,0 +1,651 @@
+// nb200_l1stream.cu -- layer 1 of ff::inference_unit as ONE kernel: FFTransposeMult + FFAggMatrix over the fp64
+// `inputs` blocks as they lie in HBM, converted to fp16 on the way into the tensor cores.
+//
+// Replaces, for the first join of FF/source/SimpleFF.cc:331-364: the per-pair Eigen GEMM of
+// FF/headers/FFTransposeMult.h:80-92 and the keyed sum of queryExecution/headers/CombinedShuffleSink.h:112-144 /
+// AggregationProcessor.cc:131-156 (the reference hash-partitions the pair products by blockColIndex,
+// FFMatrixBlock.h:151-156, i.e. it splits K across workers and merges; the K split below is the same idea inside
+// one GPU).
+//
+// Why a second fused kernel: the first one (k_l1_fused, nb200_gemm.cu) passes the fp16 copy of X through a ring in
+// global memory, so every X element crosses the L2 -> SM fabric three times (fp64 once, fp16 once per N half) and the
+// kernel sits on that fabric's limit (~6.4 KB / clock, profiles/r01_ncu_final_summary.txt).  Here a CLUSTER owns a
+// 256*MT x 1024 output tile: every X element is read from HBM once, converted once, and handed to the CTA that
+// needs the same rows for the other half of the hidden layer through distributed shared memory; with MT = 2 the
+// W1 tile is multicast to the two M tiles of the cluster (W1's fp16 plane lives in this GPU's memory).  Fabric bytes
+// per launch on the Amazon shape: 47.8 GB (X) + 24 GB (W1, MT = 2) against 117 GB before.
+//
+// Cluster of 4*MT CTAs, rank = 4*mt + 2*nh + c:
+//   pair (mt, nh) = CTAs {c = 0, 1} issues tcgen05.mma.cta_group::2, M = 256 rows of X, N = 2 x 256 of hidden half nh
+//   CTA (mt, nh, c) holds A rows [128c, 128c + 128) of M tile mt.  It converts rows [64nh, 64nh + 64) of those itself
+//   (8 converter warps: LDG.256 fp64 -> fp16 -> 128B-swizzled st.shared) and receives the other 64 from
+//   CTA (mt, 1 - nh, c) as one 8 KB cp.async.bulk smem -> DSMEM copy per K block.
+//   W1: CTA (mt, nh, c) owns rows nh*512 + c*256 + {0..255}; with MT = 2 it fetches the 128-row chunk `mt` and
+//   multicasts it to CTA (1 - mt, nh, c).
+//
+// Work is split over clusters as (M tile, K range) segments laid out in waves (host: plan_l1_stream) so that all
+// clusters of a wave sweep the same K ranges together -- W1 comes out of L2, not HBM -- and no SM idles when the
+// tile count is not a multiple of the cluster count (row shards of 5,000 / 2,500 / 1,250 rows keep every cluster
+// busy).  A segment's accumulator (TMEM, fp32) is written to workspace slot `slot`; k_l1s_reduce sums the slots of
+// a tile in index order (deterministic) and applies 2^-(ex+ev), bias and ReLU (FFReluBiasSum.h:63-71).
+//
+// Every wait is bounded: a protocol error becomes err_flag != 0 (NB200_ERR_KERNEL), never a hung GPU.
+#include "nb200_internal.h"
+#include "nb200_ptx.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+namespace nb200 {
+namespace {
+
+constexpr int kBK = 64;             // K block: 64 fp16 = one 128-byte swizzle row
+constexpr int kUK = 16;             // K of one tcgen05.mma kind::f16
+constexpr int kST = 4;              // shared-memory stages
+constexpr int kCvtWarps = 8;
+constexpr int kWarpCvt0 = 7;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 manager, 7.. converters
+constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 480
+constexpr uint32_t kATile = 128 * kBK * 2;   // 16 KB: 128 rows of X
+constexpr uint32_t kBTile = 256 * kBK * 2;   // 32 KB: two 128-row chunks of W1
+constexpr uint32_t kStage = kATile + kBTile;
+constexpr uint32_t kXHalf = 64 * kBK * 2;    // 8 KB: the 64 rows one CTA converts
+constexpr uint32_t kBarOff = kST * kStage;
+constexpr uint32_t kSmemTotal = kBarOff + (4 * kST + 2) * 8 + 16 + 1024;
+constexpr int kDepth = 2;           // K blocks of fp64 loads in flight per converter thread
+constexpr int kWsLd = 1024;         // fp32 partial tiles: [slot][row][1024]
+
+struct Seg { int tile, kb0, kb1, slot; };
+
+struct L1SArgs {
+    const double *x;        // [rows_total x cols] fp64, pitch x_ld (multiple of 4, base 32-byte aligned)
+    long long x_ld;
+    int rows_total, cols;
+    const int *exp_x;       // fp16 scale exponent of X (device)
+    float *row_sumsq;       // [rows_total], accumulated with atomics (error model of the near-tie cascade); may be null
+    float *maxscaled;       // receives +inf if a converted value overflowed fp16
+    float *ws;              // fp32 partial tiles
+    long long ws_slot_stride;
+    const Seg *sched;       // [clusters][max_seg], a cluster's list ends at the first kb0 >= kb1
+    int max_seg;
+    int *err_flag;
+    unsigned int idesc;
+    int debug;              // experiments: 1 = converters skip the HBM loads, 2 = no MMAs, 4 = no DSMEM copy
+};
+
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ bool mbar_wait_cluster(uint64_t *bar, uint32_t parity) {
+    if (mbar_try_wait_cluster(bar, parity)) return true;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_cluster(bar, parity)) {
+        if (clock64() - t0 > (1ll << 30)) return false;
+    }
+    return true;
+}
+__device__ __forceinline__ bool mbar_wait_b(uint64_t *bar, uint32_t parity) {  // bounded, CTA scope
+    if (mbar_try_wait(bar, parity)) return true;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > (1ll << 30)) return false;
+    }
+    return true;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_remote_release(uint64_t *bar, uint32_t cta) {
+    const uint32_t ra = mapa_u32(smem_u32(bar), cta);
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
+}
+// 8 KB (or any multiple of 16 bytes) from this CTA's shared memory to the same offset of CTA `cta`; completes the
+// bytes on THAT CTA's mbarrier `bar`
+__device__ __forceinline__ void dsmem_bulk_copy(void *dst_same_offset, const void *src, uint32_t bytes, uint64_t *bar,
+                                                uint32_t cta) {
+    const uint32_t rd = mapa_u32(smem_u32(dst_same_offset), cta);
+    const uint32_t rb = mapa_u32(smem_u32(bar), cta);
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(rd), "r"(smem_u32(src)), "r"(bytes), "r"(rb)
+                 : "memory");
+}
+__device__ __forceinline__ void ldg256(const double *p, double (&v)[4]) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.f64 {%0, %1, %2, %3}, [%4];"
+                 : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+                 : "l"(p));
+}
+
+template <int MT>
+__global__ void __cluster_dims__(4 * MT, 1, 1) __launch_bounds__(kThreadsL1S, 1)
+k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
+    constexpr int CS = 4 * MT;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + kBarOff);  // leader: W1 landed + both CTAs' A tiles complete
+    uint64_t *empty_bar = full_bar + kST;    // every CTA: all pairs of the cluster have consumed stage s
+    uint64_t *xfull_bar = empty_bar + kST;   // every CTA: the partner's 64 rows have landed
+    uint64_t *cdone_bar = xfull_bar + kST;   // every CTA: own converters have written their 64 rows
+    uint64_t *tmem_full_bar = cdone_bar + kST;
+    uint64_t *tmem_empty_bar = tmem_full_bar + 1;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const uint32_t c = crank & 1, nh = (crank >> 1) & 1, mt = crank >> 2;
+    const uint32_t leader_rank = crank & ~1u;
+    const bool leader = c == 0;
+    const int cluster_id = blockIdx.x / CS;
+    const Seg *my = g.sched + static_cast<long long>(cluster_id) * g.max_seg;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_w);
+        for (int s = 0; s < kST; s++) {
+            mbar_init(&full_bar[s], 4);         // leader's expect_tx arrive, peer producer, two managers
+            mbar_init(&empty_bar[s], 2 * MT);   // one multicast commit per pair of the cluster
+            mbar_init(&xfull_bar[s], 1);
+            mbar_init(&cdone_bar[s], kCvtWarps);
+        }
+        mbar_init(tmem_full_bar, 1);
+        mbar_init(tmem_empty_bar, 8);           // 4 epilogue warps of each CTA of the pair
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_2sm(tmem_slot, 512);
+        tmem_relinquish_2sm();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== W1 producer (one thread per CTA) =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            bool ok = true;
+            for (int si = 0; si < g.max_seg && ok; si++) {
+                const Seg sg = my[si];
+                if (sg.kb0 >= sg.kb1) break;
+                for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
+                    const uint32_t s = it % kST, ph = (it / kST) & 1;
+                    if (!mbar_wait_b(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 501); ok = false; break; }
+                    uint8_t *sb = smem + s * kStage + kATile;
+                    if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * kBTile);
+                    else mbar_arrive_remote(&full_bar[s], leader_rank);
+                    const int wrow = static_cast<int>(nh) * 512 + static_cast<int>(c) * 256;
+                    if (MT == 1) {
+                        tma_load_2d_2sm(&map_w, &full_bar[s], sb, kb * kBK, wrow, kEvictLast);  // box of 256 rows
+                    } else {
+                        const uint16_t mask = static_cast<uint16_t>((1u << crank) | (1u << (crank ^ 4u)));
+                        tma_load_2d_2sm_mc(&map_w, &full_bar[s], sb + mt * (128 * kBK * 2), kb * kBK,
+                                           wrow + static_cast<int>(mt) * 128, mask, kEvictLast);  // box of 128 rows
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one thread of each pair's leader =====
+        if (leader && lane == 0) {
+            uint32_t it = 0;
+            bool ok = true;
+            for (int si = 0; si < g.max_seg && ok; si++) {
+                const Seg sg = my[si];
+                if (sg.kb0 >= sg.kb1) break;
+                if (si > 0) {  // the epilogue of the previous segment must have drained TMEM
+                    if (!mbar_wait_cluster(tmem_empty_bar, (si - 1) & 1)) { atomicExch(g.err_flag, 502); ok = false; break; }
+                    tc_fence_after();
+                }
+                for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
+                    const uint32_t s = it % kST, ph = (it / kST) & 1;
+                    if (!mbar_wait_cluster(&full_bar[s], ph)) { atomicExch(g.err_flag, 503); ok = false; break; }
+                    tc_fence_after();
+                    if (!(g.debug & 2)) {
+                        const uint32_t sa = smem_u32(smem + s * kStage);
+                        const uint32_t sb = sa + kATile;
+                        const uint64_t da = umma_desc_k_sw128(sa);
+#pragma unroll
+                        for (int k = 0; k < kBK / kUK; k++) {
+#pragma unroll
+                            for (int sub = 0; sub < 2; sub++) {
+                                const uint64_t db = umma_desc_k_sw128(sb + sub * (128 * kBK * 2));
+                                umma_f16_2sm(tmem_base + sub * 256, da + 2 * k, db + 2 * k, g.idesc,
+                                             (kb > sg.kb0 || k > 0) ? 1u : 0u);
+                            }
+                        }
+                    }
+                    umma_commit_2sm(&empty_bar[s], static_cast<uint16_t>((1u << CS) - 1));
+                }
+                if (ok) umma_commit_2sm(tmem_full_bar, static_cast<uint16_t>(0x3u << leader_rank));
+            }
+        }
+    } else if (warp < 6) {
+        // ===== epilogue: TMEM -> fp32 partial tile in the workspace =====
+        const int q = warp & 3;
+        bool ok = true;
+        for (int si = 0; si < g.max_seg && ok; si++) {
+            const Seg sg = my[si];
+            if (sg.kb0 >= sg.kb1) break;
+            ok = mbar_wait_b(tmem_full_bar, si & 1);
+            if (!ok && lane == 0) atomicExch(g.err_flag, 504);
+            ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+            if (!ok) break;
+            tc_fence_after();
+            const long long row = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + q * 32 + lane;
+            float *dst_row = g.ws + sg.slot * g.ws_slot_stride + row * kWsLd + nh * 512;
+            const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+            for (int cc = 0; cc < 16; cc++) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(lane_addr + cc * 32, r);
+                tmem_ld_wait();
+                const int sub = cc >> 3, j = (cc & 7) * 32;
+                const int tcol = (j < 128) ? sub * 128 + j : 256 + sub * 128 + (j - 128);
+                float *dst = dst_row + tcol;
+#pragma unroll
+                for (int jj = 0; jj < 32; jj += 4)
+                    *reinterpret_cast<uint4 *>(dst + jj) = make_uint4(r[jj], r[jj + 1], r[jj + 2], r[jj + 3]);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (leader) mbar_arrive(tmem_empty_bar);
+                else mbar_arrive_remote_release(tmem_empty_bar, leader_rank);
+            }
+        }
+    } else if (warp == 6) {
+        // ===== manager: ships this CTA's 64 converted rows to the partner and reports the A tile complete =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            bool ok = true;
+            const uint32_t partner = crank ^ 2u;
+            for (int si = 0; si < g.max_seg && ok; si++) {
+                const Seg sg = my[si];
+                if (sg.kb0 >= sg.kb1) break;
+                for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
+                    const uint32_t s = it % kST, ph = (it / kST) & 1;
+                    if (!(g.debug & 4)) mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
+                    else mbar_arrive(&xfull_bar[s]);
+                    if (!mbar_wait_b(&cdone_bar[s], ph)) { atomicExch(g.err_flag, 505); ok = false; break; }
+                    uint8_t *mine = smem + s * kStage + nh * kXHalf;
+                    if (!(g.debug & 4)) dsmem_bulk_copy(mine, mine, kXHalf, &xfull_bar[s], partner);
+                    if (!mbar_wait_cluster(&xfull_bar[s], ph)) { atomicExch(g.err_flag, 506); ok = false; break; }
+                    if (leader) mbar_arrive(&full_bar[s]);
+                    else mbar_arrive_remote_release(&full_bar[s], leader_rank);
+                }
+            }
+        }
+    } else {
+        // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major =====
+        const int ct = threadIdx.x - kWarpCvt0 * 32;   // 0..255
+        const int chunk = ct & 7;                      // 8 doubles = 64 bytes of the 512-byte row segment
+        const int r = ct >> 3;                         // rows r and r + 32 of the 64
+        const float scale = exp2f(static_cast<float>(*g.exp_x));
+        // loader cursor (runs kDepth K blocks ahead of the converting cursor)
+        int l_si = 0, l_kb = 0, l_kb1 = 0;
+        const double *l_p[2] = {nullptr, nullptr};
+        bool l_in[2] = {false, false};
+        auto l_open = [&]() {
+            while (l_si < g.max_seg) {
+                const Seg sg = my[l_si];
+                if (sg.kb0 >= sg.kb1) { l_si = g.max_seg; break; }
+                l_kb = sg.kb0; l_kb1 = sg.kb1;
+                const long long row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + r;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const long long row = row0 + 32 * h;
+                    l_in[h] = row < g.rows_total;
+                    l_p[h] = g.x + (l_in[h] ? row : 0) * g.x_ld + chunk * 8;
+                }
+                return;
+            }
+            l_kb = 0; l_kb1 = 0;
+        };
+        auto l_issue = [&](double (&v)[2][8]) {
+            if (l_kb >= l_kb1) {
+#pragma unroll
+                for (int h = 0; h < 2; h++)
+#pragma unroll
+                    for (int e = 0; e < 8; e++) v[h][e] = 0.0;
+                return;
+            }
+            const long long col = static_cast<long long>(l_kb) * kBK + chunk * 8;
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                if (l_in[h] && col + 8 <= g.cols && !(g.debug & 1)) {
+                    double a[4], b[4];
+                    ldg256(l_p[h] + static_cast<long long>(l_kb) * kBK, a);
+                    ldg256(l_p[h] + static_cast<long long>(l_kb) * kBK + 4, b);
+#pragma unroll
+                    for (int e = 0; e < 4; e++) { v[h][e] = a[e]; v[h][4 + e] = b[e]; }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 8; e++)
+                        v[h][e] = (l_in[h] && col + e < g.cols) ? ((g.debug & 1) ? 0.25 : l_p[h][static_cast<long long>(l_kb) * kBK + e]) : 0.0;
+                }
+            }
+            if (++l_kb >= l_kb1) { l_si++; l_open(); }
+        };
+        l_open();
+        double buf[kDepth][2][8];
+#pragma unroll
+        for (int d = 0; d < kDepth; d++) l_issue(buf[d]);
+
+        uint32_t it = 0;
+        uint32_t ovf = 0;
+        bool ok = true;
+        // converting cursor: walks the same (segment, K block) sequence as the loader, kDepth items behind it; item i
+        // lives in buf[i % kDepth] whatever the segment lengths are
+        int c_si = 0, c_kb = 0, c_kb1 = 0;
+        long long c_row0 = 0;
+        float ss[2] = {0.f, 0.f};
+        auto c_open = [&]() -> bool {
+            if (c_si >= g.max_seg) return false;
+            const Seg sg = my[c_si];
+            if (sg.kb0 >= sg.kb1) return false;
+            c_kb = sg.kb0; c_kb1 = sg.kb1;
+            c_row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + r;
+            ss[0] = 0.f; ss[1] = 0.f;
+            return true;
+        };
+        bool more = c_open();
+        while (more && ok) {
+#pragma unroll
+            for (int d = 0; d < kDepth; d++) {
+                if (more && ok) {
+                    const uint32_t s = it % kST, ph = (it / kST) & 1;
+                    int w_ok = 1;
+                    if (lane == 0) {
+                        w_ok = mbar_wait_b(&empty_bar[s], ph ^ 1) ? 1 : 0;
+                        if (!w_ok) atomicExch(g.err_flag, 507);
+                    }
+                    w_ok = __shfl_sync(0xffffffffu, w_ok, 0);
+                    if (!w_ok) { ok = false; continue; }
+                    const uint32_t dst = smem_u32(smem + s * kStage + nh * kXHalf + r * 128 + ((chunk ^ (r & 7)) << 4));
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        uint32_t pk[4];
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const float f0 = static_cast<float>(buf[d][h][2 * e]), f1 = static_cast<float>(buf[d][h][2 * e + 1]);
+                            ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
+                            const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
+                            pk[e] = *reinterpret_cast<const uint32_t *>(&h2);
+                            ovf |= ((pk[e] & 0x7C00u) == 0x7C00u) | ((pk[e] & 0x7C000000u) == 0x7C000000u);
+                        }
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + h * (32 * 128)), "r"(pk[0]), "r"(pk[1]),
+                                     "r"(pk[2]), "r"(pk[3])
+                                     : "memory");
+                    }
+                    fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&cdone_bar[s]);
+                    l_issue(buf[d]);            // refill the buffer just consumed
+                    it++;
+                    if (++c_kb >= c_kb1) {
+                        // per-row sum of squares of this segment's K range: the 8 chunk lanes of a row are adjacent
+                        if (g.row_sumsq != nullptr) {
+#pragma unroll
+                            for (int h = 0; h < 2; h++) {
+                                float v = ss[h];
+                                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                                const long long row = c_row0 + 32 * h;
+                                if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
+                            }
+                        }
+                        c_si++;
+                        more = c_open();
+                    }
+                }
+            }
+        }
+        if (__any_sync(0xffffffffu, ovf != 0) && lane == 0 && g.maxscaled != nullptr)
+            atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), 0x7F800000u);
+    }
+    tc_fence_before();
+    cluster_sync_all();   // nobody leaves while a peer may still read its shared memory or TMEM
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2sm(tmem_base, 512);
+    }
+}
+
+// out[row][col] = relu?(sum over the tile's slots * 2^-(ex+ev) + bias[col]); block = one row, 256 threads x 4 columns
+__global__ void __launch_bounds__(256)
+k_l1s_reduce(const float *__restrict__ ws, long long slot_stride, const int *__restrict__ tile_slots, int tile_rows, int N,
+             const float *__restrict__ bias_n, int relu, const int *__restrict__ exp_u, const int *__restrict__ exp_v,
+             float *__restrict__ out, long long out_ld, float *__restrict__ out_maxabs) {
+    __shared__ float sh[8];
+    const long long m = blockIdx.x;
+    const int n0 = threadIdx.x * 4;
+    const int slots = tile_slots[m / tile_rows];
+    const float oscale = exp_u ? exp2f(-static_cast<float>(*exp_u + *exp_v)) : 1.f;
+    float mx = 0.f;
+    if (n0 < N) {
+        const float *p = ws + m * kWsLd + n0;
+        float4 acc = *reinterpret_cast<const float4 *>(p);
+        for (int s = 1; s < slots; s++) {
+            const float4 t = *reinterpret_cast<const float4 *>(p + s * slot_stride);
+            acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
+        float v[4] = {acc.x * oscale, acc.y * oscale, acc.z * oscale, acc.w * oscale};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (n0 + j < N) {
+                if (bias_n) v[j] += bias_n[n0 + j];
+                if (relu) v[j] = fmaxf(v[j], 0.f);
+                out[m * out_ld + n0 + j] = v[j];
+                mx = fmaxf(mx, fabsf(v[j]));
+            }
+        }
+    }
+    if (out_maxabs) {
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = mx;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < 8; w++) mx = fmaxf(mx, sh[w]);
+            atomicMax(reinterpret_cast<unsigned int *>(out_maxabs), __float_as_uint(mx));
+        }
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+int make_w_map(CUtensorMap *m, const void *base, int64_t rows, int64_t ldk, int box_rows) {
+    static EncodeTiledFn enc = nullptr;
+    if (!enc) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess) {
+            set_error("cuTensorMapEncodeTiled not available from the driver");
+            return NB200_ERR_CUDA;
+        }
+        enc = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(ldk), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ldk) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(kBK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (l1 stream, rows=%lld ldk=%lld)", (int)r, (long long)rows,
+                  (long long)ldk);
+        return NB200_ERR_CUDA;
+    }
+    return NB200_OK;
+}
+
+template <int MT>
+int max_clusters(int *out) {
+    static int cached = -1;
+    if (cached < 0) {
+        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(4 * MT * 64);
+        cfg.blockDim = dim3(kThreadsL1S);
+        cfg.dynamicSmemBytes = kSmemTotal;
+        cudaLaunchAttribute at{};
+        at.id = cudaLaunchAttributeClusterDimension;
+        at.val.clusterDim.x = 4 * MT; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+        cfg.attrs = &at;
+        cfg.numAttrs = 1;
+        int n = 0;
+        NB_CUDA(cudaOccupancyMaxActiveClusters(&n, k_l1_stream<MT>, &cfg));
+        cached = n;
+    }
+    *out = cached;
+    return NB200_OK;
+}
+
+}  // namespace
+
+// ---- the wave plan ---------------------------------------------------------------------------------
+// `tiles` cluster tiles x `num_kb` K blocks over `G` clusters.  A wave takes T tiles and gives each S = G / T
+// clusters, each a contiguous K range; cost of a wave = ceil(num_kb / S) + a fixed part (pipeline fill, TMEM flush).
+// The split (T per wave) minimising the sum is found by dynamic programming over the remaining tile count.
+int plan_l1_stream(int tiles, int num_kb, int G, L1StreamPlan *plan) {
+    plan->segs.clear();
+    plan->tile_slots.assign(tiles > 0 ? tiles : 1, 1);
+    plan->clusters = 0;
+    plan->max_seg = 0;
+    plan->max_slots = 1;
+    if (tiles <= 0 || num_kb <= 0 || G <= 0) return NB200_OK;
+    const int max_split = std::max(1, num_kb / 8);  // a K range shorter than 8 blocks is all prologue
+    const double fixed = 12.0;                      // K-block equivalents per segment
+    std::vector<double> best(tiles + 1, 0.0);
+    std::vector<int> take(tiles + 1, 0);
+    for (int R = 1; R <= tiles; R++) {
+        best[R] = 1e30;
+        for (int T = 1; T <= std::min(R, G); T++) {
+            const int S = std::min(G / T, max_split);
+            const double cost = static_cast<double>((num_kb + S - 1) / S) + fixed + best[R - T];
+            if (cost < best[R] - 1e-9) { best[R] = cost; take[R] = T; }
+        }
+    }
+    std::vector<std::vector<L1StreamSeg>> per(G);
+    int t0 = 0;
+    for (int R = tiles; R > 0;) {
+        const int T = take[R];
+        int S = std::min(G / T, max_split);
+        const int per_kb = (num_kb + S - 1) / S;
+        S = (num_kb + per_kb - 1) / per_kb;          // no empty K range
+        for (int j = 0; j < T; j++) {
+            plan->tile_slots[t0 + j] = S;
+            for (int sp = 0; sp < S; sp++) {
+                // split-major cluster order: the T clusters of one K range are neighbours and sweep it together
+                const int gidx = sp * T + j;
+                per[gidx].push_back(L1StreamSeg{t0 + j, sp * per_kb, std::min((sp + 1) * per_kb, num_kb), sp});
+            }
+        }
+        plan->max_slots = std::max(plan->max_slots, S);
+        t0 += T;
+        R -= T;
+    }
+    for (int gi = 0; gi < G; gi++)
+        if (!per[gi].empty()) {
+            plan->clusters = gi + 1;
+            plan->max_seg = std::max(plan->max_seg, static_cast<int>(per[gi].size()));
+        }
+    plan->max_seg += 1;  // terminator
+    plan->segs.assign(static_cast<size_t>(plan->clusters) * plan->max_seg, L1StreamSeg{0, 0, 0, 0});
+    for (int gi = 0; gi < plan->clusters; gi++)
+        for (size_t j = 0; j < per[gi].size(); j++) plan->segs[static_cast<size_t>(gi) * plan->max_seg + j] = per[gi][j];
+    return NB200_OK;
+}
+
+static_assert(sizeof(L1StreamSeg) == sizeof(Seg), "plan segments are handed to the kernel as they are");
+
+bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1) {
+    return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && (x_ld & 3) == 0 &&
+           (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
+}
+
+template <int MT>
+static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,
+                                 float *maxscaled, const Planes &w1, L1StreamScratch *sc, int debug) {
+    int G = 0;
+    NB_TRY(max_clusters<MT>(&G));
+    if (G < 1) { set_error("l1 stream: no cluster of %d CTAs fits this device", 4 * MT); return NB200_ERR_STATE; }
+    static const int g_env = getenv("NB200_L1S_CLUSTERS") ? atoi(getenv("NB200_L1S_CLUSTERS")) : 0;
+    if (g_env > 0 && g_env < G) G = g_env;
+    const int tile_rows = 256 * MT;
+    const int tiles = static_cast<int>(ceil_div(rows, tile_rows));
+    const int num_kb = static_cast<int>(w1.ldk / kBK);
+    if (sc->plan_rows != rows || sc->plan_kb != num_kb || sc->plan_g != G || sc->plan_mt != MT) {
+        NB_TRY(plan_l1_stream(tiles, num_kb, G, &sc->plan));
+        const size_t sb = sc->plan.segs.size() * sizeof(L1StreamSeg), tb = sc->plan.tile_slots.size() * sizeof(int);
+        if (sc->dev_bytes < sb + tb) {
+            nb_free(sc->dev);
+            sc->dev = nullptr;
+            sc->dev_bytes = 0;
+            NB_CUDA(nb_malloc(&sc->dev, sb + tb));
+            sc->dev_bytes = sb + tb;
+        }
+        // (pageable source: the copy is staged before the call returns, so the vectors may change afterwards)
+        NB_CUDA(cudaMemcpyAsync(sc->dev, sc->plan.segs.data(), sb, cudaMemcpyHostToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(sc->dev + sb, sc->plan.tile_slots.data(), tb, cudaMemcpyHostToDevice, c->stream));
+        sc->seg_dev = reinterpret_cast<const L1StreamSeg *>(sc->dev);
+        sc->slots_dev = reinterpret_cast<const int *>(sc->dev + sb);
+        sc->plan_rows = rows; sc->plan_kb = num_kb; sc->plan_g = G; sc->plan_mt = MT;
+    }
+    const long long slot_stride = static_cast<long long>(tiles) * tile_rows * kWsLd;
+    NB_TRY(ensure_ws(c, static_cast<size_t>(sc->plan.max_slots) * slot_stride * sizeof(float)));
+    sc->tile_rows = tile_rows;
+    sc->slot_stride = slot_stride;
+
+    L1SArgs g{};
+    g.x = x; g.x_ld = x_ld; g.rows_total = rows; g.cols = cols; g.exp_x = exp_x; g.row_sumsq = row_sumsq; g.maxscaled = maxscaled;
+    g.ws = c->ws; g.ws_slot_stride = slot_stride; g.sched = reinterpret_cast<const Seg *>(sc->seg_dev); g.max_seg = sc->plan.max_seg;
+    g.err_flag = c->err_flag;
+    g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
+    g.debug = debug;
+    CUtensorMap mw;
+    NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
+    k_l1_stream<MT><<<sc->plan.clusters * 4 * MT, kThreadsL1S, kSmemTotal, c->stream>>>(mw, g);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,
+                     float *maxscaled, const Planes &w1, int N, L1StreamScratch *sc) {
+    if (!l1_stream_supported(x, x_ld, cols, N, w1)) { set_error("l1 stream: shape not supported"); return NB200_ERR_STATE; }
+    static const int mt_env = getenv("NB200_L1S_MT") ? atoi(getenv("NB200_L1S_MT")) : 0;
+    static const int debug = getenv("NB200_L1S_DEBUG") ? atoi(getenv("NB200_L1S_DEBUG")) : 0;
+    int mt = mt_env;
+    if (mt != 1 && mt != 2) {
+        // MT = 2 halves the W1 traffic but works in 512-row tiles: take it unless its padding costs more than that
+        const int64_t pad1 = ceil_div(rows, 256) * 256, pad2 = ceil_div(rows, 512) * 512;
+        mt = (pad2 * 10 <= pad1 * 12) ? 2 : 1;
+    }
+    if (mt == 2) return launch_l1_stream_impl<2>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    return launch_l1_stream_impl<1>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+}
+
+int launch_l1_stream_reduce(Context *c, const L1StreamScratch &sc, int rows, int N, const float *bias_n, int relu,
+                            const int *exp_u, const int *exp_v, float *out, int64_t out_ld, float *out_maxabs) {
+    if (out_maxabs) NB_CUDA(cudaMemsetAsync(out_maxabs, 0, sizeof(float), c->stream));
+    k_l1s_reduce<<<rows, 256, 0, c->stream>>>(c->ws, sc.slot_stride, sc.slots_dev, sc.tile_rows, N, bias_n, relu, exp_u, exp_v,
+                                              out, out_ld, out_maxabs);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+}  // namespace nb200
