@@ -34,6 +34,7 @@
 #include "nb200_ptx.cuh"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -603,6 +604,10 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
         sc->seg_dev = reinterpret_cast<const L1StreamSeg *>(sc->dev);
         sc->slots_dev = reinterpret_cast<const int *>(sc->dev + sb);
         sc->plan_rows = rows; sc->plan_kb = num_kb; sc->plan_g = G; sc->plan_mt = MT;
+        static const bool verbose = getenv("NB200_L1S_VERBOSE") != nullptr;
+        if (verbose)
+            fprintf(stderr, "[l1 stream] MT=%d rows=%d tiles=%d num_kb=%d resident clusters=%d used=%d max_seg=%d max_slots=%d\n", MT, rows,
+                    tiles, num_kb, G, sc->plan.clusters, sc->plan.max_seg - 1, sc->plan.max_slots);
     }
     const long long slot_stride = static_cast<long long>(tiles) * tile_rows * kWsLd;
     NB_TRY(ensure_ws(c, static_cast<size_t>(sc->plan.max_slots) * slot_stride * sizeof(float)));
