@@ -52,7 +52,7 @@ constexpr uint32_t kBTile = 256 * kBK * 2;   // 32 KB: two 128-row chunks of W1
 constexpr uint32_t kStage = kATile + kBTile;
 constexpr uint32_t kXHalf = 64 * kBK * 2;    // 8 KB: the 64 rows one CTA converts
 constexpr uint32_t kBarOff = kST * kStage;
-constexpr uint32_t kSmemTotal = kBarOff + (4 * kST + 2) * 8 + 16 + 1024;
+constexpr uint32_t kSmemTotal = kBarOff + (3 * kST + 2) * 8 + 16 + 1024;
 constexpr int kDepth = 2;           // K blocks of fp64 loads in flight per converter thread
 constexpr int kWsLd = 1024;         // fp32 partial tiles: [slot][row][1024]
 
@@ -71,7 +71,9 @@ struct L1SArgs {
     int max_seg;
     int *err_flag;
     unsigned int idesc;
-    int debug;              // experiments: 1 = converters skip the HBM loads, 2 = no MMAs, 4 = no DSMEM copy
+    int debug;              // experiments: 1 = converters skip the HBM loads, 2 = no MMAs, 4 = no DSMEM copy, 8 = no proxy fence
+    int relay;              // 1: a c = 1 CTA's incoming rows are signalled on its own barrier and relayed to the pair leader
+    int pf_dist;            // L2 prefetch distance of the converters in K blocks (0 = off)
 };
 
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t *bar, uint32_t parity) {
@@ -110,12 +112,12 @@ __device__ __forceinline__ void mbar_arrive_remote_release(uint64_t *bar, uint32
     const uint32_t ra = mapa_u32(smem_u32(bar), cta);
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
 }
-// 8 KB (or any multiple of 16 bytes) from this CTA's shared memory to the same offset of CTA `cta`; completes the
-// bytes on THAT CTA's mbarrier `bar`
-__device__ __forceinline__ void dsmem_bulk_copy(void *dst_same_offset, const void *src, uint32_t bytes, uint64_t *bar,
-                                                uint32_t cta) {
-    const uint32_t rd = mapa_u32(smem_u32(dst_same_offset), cta);
-    const uint32_t rb = mapa_u32(smem_u32(bar), cta);
+// bytes (a multiple of 16) from this CTA's shared memory to the same offset of CTA `dst_cta`; they complete on the
+// mbarrier at `bar`'s offset in CTA `bar_cta` (which may differ from the destination CTA)
+__device__ __forceinline__ void dsmem_bulk_copy2(void *dst_same_offset, const void *src, uint32_t bytes, uint64_t *bar,
+                                                 uint32_t dst_cta, uint32_t bar_cta) {
+    const uint32_t rd = mapa_u32(smem_u32(dst_same_offset), dst_cta);
+    const uint32_t rb = mapa_u32(smem_u32(bar), bar_cta);
     asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(rd), "r"(smem_u32(src)), "r"(bytes), "r"(rb)
                  : "memory");
@@ -134,9 +136,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + kBarOff);  // leader: W1 landed + both CTAs' A tiles complete
     uint64_t *empty_bar = full_bar + kST;    // every CTA: all pairs of the cluster have consumed stage s
-    uint64_t *xfull_bar = empty_bar + kST;   // every CTA: the partner's 64 rows have landed
-    uint64_t *cdone_bar = xfull_bar + kST;   // every CTA: own converters have written their 64 rows
-    uint64_t *tmem_full_bar = cdone_bar + kST;
+    uint64_t *xfull_bar = empty_bar + kST;   // relay mode, c = 1 CTAs: the partner's 64 rows have landed
+    uint64_t *tmem_full_bar = xfull_bar + kST;
     uint64_t *tmem_empty_bar = tmem_full_bar + 1;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty_bar + 1);
 
@@ -151,10 +152,10 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < kST; s++) {
-            mbar_init(&full_bar[s], 4);         // leader's expect_tx arrive, peer producer, two managers
+            // leader's expect_tx arrive + peer producer + the 8 converter warps of both CTAs (+ the peer's relay)
+            mbar_init(&full_bar[s], 2 + 2 * kCvtWarps + (g.relay ? 1 : 0));
             mbar_init(&empty_bar[s], 2 * MT);   // one multicast commit per pair of the cluster
             mbar_init(&xfull_bar[s], 1);
-            mbar_init(&cdone_bar[s], kCvtWarps);
         }
         mbar_init(tmem_full_bar, 1);
         mbar_init(tmem_empty_bar, 8);           // 4 epilogue warps of each CTA of the pair
@@ -181,7 +182,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                     const uint32_t s = it % kST, ph = (it / kST) & 1;
                     if (!mbar_wait_b(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 501); ok = false; break; }
                     uint8_t *sb = smem + s * kStage + kATile;
-                    if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * kBTile);
+                    // W1 of both CTAs + the rows the partner pair ships in (those of the c = 1 CTA arrive via its relay)
+                    if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * kBTile + ((g.debug & 4) ? 0 : (g.relay ? kXHalf : 2 * kXHalf)));
                     else mbar_arrive_remote(&full_bar[s], leader_rank);
                     const int wrow = static_cast<int>(nh) * 512 + static_cast<int>(c) * 256;
                     if (MT == 1) {
@@ -264,32 +266,27 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             }
         }
     } else if (warp == 6) {
-        // ===== manager: ships this CTA's 64 converted rows to the partner and reports the A tile complete =====
-        if (lane == 0) {
+        // ===== relay (only in relay mode, only the c = 1 CTA): rows shipped in by the partner -> pair leader's barrier =====
+        if (lane == 0 && g.relay && !leader && !(g.debug & 4)) {
             uint32_t it = 0;
             bool ok = true;
-            const uint32_t partner = crank ^ 2u;
             for (int si = 0; si < g.max_seg && ok; si++) {
                 const Seg sg = my[si];
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kST, ph = (it / kST) & 1;
-                    if (!(g.debug & 4)) mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
-                    else mbar_arrive(&xfull_bar[s]);
-                    if (!mbar_wait_b(&cdone_bar[s], ph)) { atomicExch(g.err_flag, 505); ok = false; break; }
-                    uint8_t *mine = smem + s * kStage + nh * kXHalf;
-                    if (!(g.debug & 4)) dsmem_bulk_copy(mine, mine, kXHalf, &xfull_bar[s], partner);
+                    mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
                     if (!mbar_wait_cluster(&xfull_bar[s], ph)) { atomicExch(g.err_flag, 506); ok = false; break; }
-                    if (leader) mbar_arrive(&full_bar[s]);
-                    else mbar_arrive_remote_release(&full_bar[s], leader_rank);
+                    mbar_arrive_remote(&full_bar[s], leader_rank);
                 }
             }
         }
     } else {
         // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major =====
-        const int ct = threadIdx.x - kWarpCvt0 * 32;   // 0..255
-        const int chunk = ct & 7;                      // 8 doubles = 64 bytes of the 512-byte row segment
-        const int r = ct >> 3;                         // rows r and r + 32 of the 64
+        const int cw = warp - kWarpCvt0;               // 0..7: this warp owns rows [8cw, 8cw + 8) = one 1 KB swizzle atom
+        const int chunk = lane & 7;                    // 8 doubles = 64 bytes of the 512-byte row segment
+        const int r = cw * 8 + (lane >> 3);            // rows r and r + 4 of the CTA's 64
+        const uint32_t partner = crank ^ 2u;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
         // loader cursor (runs kDepth K blocks ahead of the converting cursor)
         int l_si = 0, l_kb = 0, l_kb1 = 0;
@@ -303,7 +300,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 const long long row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + r;
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
-                    const long long row = row0 + 32 * h;
+                    const long long row = row0 + 4 * h;
                     l_in[h] = row < g.rows_total;
                     l_p[h] = g.x + (l_in[h] ? row : 0) * g.x_ld + chunk * 8;
                 }
@@ -320,6 +317,16 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 return;
             }
             const long long col = static_cast<long long>(l_kb) * kBK + chunk * 8;
+            if (g.pf_dist > 0 && chunk == 0 && l_kb + g.pf_dist < l_kb1) {
+                // warm L2 with the 512-byte row segments this warp will load pf_dist K blocks from now
+                const long long pcol = static_cast<long long>(l_kb + g.pf_dist) * kBK;
+                if (pcol + kBK <= g.cols) {
+#pragma unroll
+                    for (int h = 0; h < 2; h++)
+                        if (l_in[h])
+                            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(l_p[h] + pcol), "r"(512u) : "memory");
+                }
+            }
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 if (l_in[h] && col + 8 <= g.cols && !(g.debug & 1)) {
@@ -371,7 +378,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                     }
                     w_ok = __shfl_sync(0xffffffffu, w_ok, 0);
                     if (!w_ok) { ok = false; continue; }
-                    const uint32_t dst = smem_u32(smem + s * kStage + nh * kXHalf + r * 128 + ((chunk ^ (r & 7)) << 4));
+                    uint8_t *atom = smem + s * kStage + nh * kXHalf + cw * 1024;   // rows [8cw, 8cw + 8)
+                    const int rl = lane >> 3;                                     // row inside the atom: rl and rl + 4
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
                         uint32_t pk[4];
@@ -383,13 +391,24 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                             pk[e] = *reinterpret_cast<const uint32_t *>(&h2);
                             ovf |= ((pk[e] & 0x7C00u) == 0x7C00u) | ((pk[e] & 0x7C000000u) == 0x7C000000u);
                         }
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + h * (32 * 128)), "r"(pk[0]), "r"(pk[1]),
-                                     "r"(pk[2]), "r"(pk[3])
+                        const int ra = rl + 4 * h;
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(atom) + ra * 128 + ((chunk ^ ra) << 4)),
+                                     "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
                                      : "memory");
                     }
-                    fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
+                    if (!(g.debug & 8)) fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&cdone_bar[s]);
+                    if (lane == 0) {
+                        // ship the atom to the CTA that needs the same rows for the other half of the hidden layer; the
+                        // bytes complete on that pair's leader barrier (relay mode: on a c = 1 destination's own barrier)
+                        if (!(g.debug & 4)) {
+                            if (g.relay && !leader) dsmem_bulk_copy2(atom, atom, 1024, &xfull_bar[s], partner, partner);
+                            else dsmem_bulk_copy2(atom, atom, 1024, &full_bar[s], partner, partner & ~1u);
+                        }
+                        // ... and tell my own pair's leader that these 8 rows are in place
+                        if (leader) mbar_arrive(&full_bar[s]);
+                        else mbar_arrive_remote(&full_bar[s], leader_rank);
+                    }
                     l_issue(buf[d]);            // refill the buffer just consumed
                     it++;
                     if (++c_kb >= c_kb1) {
@@ -401,7 +420,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                                 v += __shfl_xor_sync(0xffffffffu, v, 1);
                                 v += __shfl_xor_sync(0xffffffffu, v, 2);
                                 v += __shfl_xor_sync(0xffffffffu, v, 4);
-                                const long long row = c_row0 + 32 * h;
+                                const long long row = c_row0 + 4 * h;
                                 if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
                             }
                         }
@@ -528,7 +547,7 @@ int plan_l1_stream(int tiles, int num_kb, int G, L1StreamPlan *plan) {
     plan->max_slots = 1;
     if (tiles <= 0 || num_kb <= 0 || G <= 0) return NB200_OK;
     const int max_split = std::max(1, num_kb / 8);  // a K range shorter than 8 blocks is all prologue
-    const double fixed = 12.0;                      // K-block equivalents per segment
+    const double fixed = 100.0;                     // K-block equivalents per wave: pipeline fill, TMEM flush, W1 re-read
     std::vector<double> best(tiles + 1, 0.0);
     std::vector<int> take(tiles + 1, 0);
     for (int R = 1; R <= tiles; R++) {
@@ -620,6 +639,10 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
     g.debug = debug;
+    static const int relay_env = getenv("NB200_L1S_RELAY") ? atoi(getenv("NB200_L1S_RELAY")) : 0;
+    static const int pf_env = getenv("NB200_L1S_PF") ? atoi(getenv("NB200_L1S_PF")) : 0;
+    g.relay = relay_env;
+    g.pf_dist = pf_env;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
     k_l1_stream<MT><<<sc->plan.clusters * 4 * MT, kThreadsL1S, kSmemTotal, c->stream>>>(mw, g);
