@@ -43,17 +43,16 @@ namespace {
 
 constexpr int kBK = 64;             // K block: 64 fp16 = one 128-byte swizzle row
 constexpr int kUK = 16;             // K of one tcgen05.mma kind::f16
-constexpr int kST = 4;              // shared-memory stages
+constexpr int kSA = 8;              // shared-memory slots for X tiles (long chain: convert, DSMEM hand-off, relay)
+constexpr int kSB = 3;              // ... for W1 tiles (TMA out of L2)
 constexpr int kCvtWarps = 8;
-constexpr int kWarpCvt0 = 7;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 manager, 7.. converters
+constexpr int kWarpCvt0 = 7;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 relay, 7.. converters
 constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 480
 constexpr uint32_t kATile = 128 * kBK * 2;   // 16 KB: 128 rows of X
 constexpr uint32_t kBTile = 256 * kBK * 2;   // 32 KB: two 128-row chunks of W1
-constexpr uint32_t kStage = kATile + kBTile;
 constexpr uint32_t kXHalf = 64 * kBK * 2;    // 8 KB: the 64 rows one CTA converts
-constexpr uint32_t kBarOff = kST * kStage;
-constexpr uint32_t kSmemTotal = kBarOff + (3 * kST + 2) * 8 + 16 + 1024;
-constexpr int kDepth = 2;           // K blocks of fp64 loads in flight per converter thread
+constexpr uint32_t kBarOff = kSA * kATile + kSB * kBTile;   // 224 KB
+constexpr uint32_t kSmemTotal = kBarOff + (3 * kSA + 2 * kSB + 2) * 8 + 16 + 1024;
 constexpr int kWsLd = 1024;         // fp32 partial tiles: [slot][row][1024]
 
 struct Seg { int tile, kb0, kb1, slot; };
@@ -131,13 +130,16 @@ __device__ __forceinline__ void ldg256(const double *p, double (&v)[4]) {
 template <int MT>
 __global__ void __cluster_dims__(4 * MT, 1, 1) __launch_bounds__(kThreadsL1S, 1)
 k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
-    constexpr int CS = 4 * MT;
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + kBarOff);  // leader: W1 landed + both CTAs' A tiles complete
-    uint64_t *empty_bar = full_bar + kST;    // every CTA: all pairs of the cluster have consumed stage s
-    uint64_t *xfull_bar = empty_bar + kST;   // relay mode, c = 1 CTAs: the partner's 64 rows have landed
-    uint64_t *tmem_full_bar = xfull_bar + kST;
+    uint8_t *a_ring = smem;                      // kSA x 16 KB: X tiles (fp16, 128B-swizzled K-major)
+    uint8_t *b_ring = smem + kSA * kATile;       // kSB x 32 KB: W1 tiles
+    uint64_t *a_full = reinterpret_cast<uint64_t *>(smem + kBarOff);  // leader: both CTAs' A tiles of K block `it` complete
+    uint64_t *a_empty = a_full + kSA;     // every CTA: both pairs that share these X rows have consumed A slot s
+    uint64_t *xfull_bar = a_empty + kSA;  // c = 1 CTAs: the partner's 64 rows have landed (relayed to the leader)
+    uint64_t *b_full = xfull_bar + kSA;   // leader: W1 tile landed in both CTAs
+    uint64_t *b_empty = b_full + kSB;     // every CTA: all pairs that share this W1 tile have consumed B slot s
+    uint64_t *tmem_full_bar = b_empty + kSB;
     uint64_t *tmem_empty_bar = tmem_full_bar + 1;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty_bar + 1);
 
@@ -146,16 +148,20 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     const uint32_t c = crank & 1, nh = (crank >> 1) & 1, mt = crank >> 2;
     const uint32_t leader_rank = crank & ~1u;
     const bool leader = c == 0;
-    const int cluster_id = blockIdx.x / CS;
+    const int cluster_id = blockIdx.x / (4 * MT);
     const Seg *my = g.sched + static_cast<long long>(cluster_id) * g.max_seg;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
-        for (int s = 0; s < kST; s++) {
-            // leader's expect_tx arrive + peer producer + the 8 converter warps of both CTAs (+ the peer's relay)
-            mbar_init(&full_bar[s], 2 + 2 * kCvtWarps + (g.relay ? 1 : 0));
-            mbar_init(&empty_bar[s], 2 * MT);   // one multicast commit per pair of the cluster
+        for (int s = 0; s < kSA; s++) {
+            // per K block 4 converter warps of each CTA of the pair write this slot, plus the c = 1 CTA's relay
+            mbar_init(&a_full[s], 2 * (kCvtWarps / 2) + ((g.debug & 4) ? 0 : 1));
+            mbar_init(&a_empty[s], 2);          // the pairs (mt, 0) and (mt, 1)
             mbar_init(&xfull_bar[s], 1);
+        }
+        for (int s = 0; s < kSB; s++) {
+            mbar_init(&b_full[s], 2);           // leader's expect_tx arrive + the peer producer
+            mbar_init(&b_empty[s], MT);         // the pairs (0, nh) .. (MT - 1, nh)
         }
         mbar_init(tmem_full_bar, 1);
         mbar_init(tmem_empty_bar, 8);           // 4 epilogue warps of each CTA of the pair
@@ -179,18 +185,17 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 const Seg sg = my[si];
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
-                    const uint32_t s = it % kST, ph = (it / kST) & 1;
-                    if (!mbar_wait_b(&empty_bar[s], ph ^ 1)) { atomicExch(g.err_flag, 501); ok = false; break; }
-                    uint8_t *sb = smem + s * kStage + kATile;
-                    // W1 of both CTAs + the rows the partner pair ships in (those of the c = 1 CTA arrive via its relay)
-                    if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * kBTile + ((g.debug & 4) ? 0 : (g.relay ? kXHalf : 2 * kXHalf)));
-                    else mbar_arrive_remote(&full_bar[s], leader_rank);
+                    const uint32_t s = it % kSB, ph = (it / kSB) & 1;
+                    if (!mbar_wait_b(&b_empty[s], ph ^ 1)) { atomicExch(g.err_flag, 501); ok = false; break; }
+                    uint8_t *sb = b_ring + s * kBTile;
+                    if (leader) mbar_arrive_expect_tx(&b_full[s], 2 * kBTile);
+                    else mbar_arrive_remote(&b_full[s], leader_rank);
                     const int wrow = static_cast<int>(nh) * 512 + static_cast<int>(c) * 256;
                     if (MT == 1) {
-                        tma_load_2d_2sm(&map_w, &full_bar[s], sb, kb * kBK, wrow, kEvictLast);  // box of 256 rows
+                        tma_load_2d_2sm(&map_w, &b_full[s], sb, kb * kBK, wrow, kEvictLast);  // box of 256 rows
                     } else {
                         const uint16_t mask = static_cast<uint16_t>((1u << crank) | (1u << (crank ^ 4u)));
-                        tma_load_2d_2sm_mc(&map_w, &full_bar[s], sb + mt * (128 * kBK * 2), kb * kBK,
+                        tma_load_2d_2sm_mc(&map_w, &b_full[s], sb + mt * (128 * kBK * 2), kb * kBK,
                                            wrow + static_cast<int>(mt) * 128, mask, kEvictLast);  // box of 128 rows
                     }
                 }
@@ -201,6 +206,9 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         if (leader && lane == 0) {
             uint32_t it = 0;
             bool ok = true;
+            // who shares my X rows (same mt) and who shares my W1 tile (same nh)
+            const uint16_t mask_a = static_cast<uint16_t>(0xFu << (4 * mt));
+            const uint16_t mask_b = static_cast<uint16_t>((MT == 1 ? 0x3u : 0x33u) << (2 * nh));
             for (int si = 0; si < g.max_seg && ok; si++) {
                 const Seg sg = my[si];
                 if (sg.kb0 >= sg.kb1) break;
@@ -209,12 +217,13 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                     tc_fence_after();
                 }
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
-                    const uint32_t s = it % kST, ph = (it / kST) & 1;
-                    if (!mbar_wait_cluster(&full_bar[s], ph)) { atomicExch(g.err_flag, 503); ok = false; break; }
+                    const uint32_t sa_i = it % kSA, pha = (it / kSA) & 1, sb_i = it % kSB, phb = (it / kSB) & 1;
+                    if (!mbar_wait_cluster(&b_full[sb_i], phb)) { atomicExch(g.err_flag, 503); ok = false; break; }
+                    if (!mbar_wait_cluster(&a_full[sa_i], pha)) { atomicExch(g.err_flag, 508); ok = false; break; }
                     tc_fence_after();
                     if (!(g.debug & 2)) {
-                        const uint32_t sa = smem_u32(smem + s * kStage);
-                        const uint32_t sb = sa + kATile;
+                        const uint32_t sa = smem_u32(a_ring + sa_i * kATile);
+                        const uint32_t sb = smem_u32(b_ring + sb_i * kBTile);
                         const uint64_t da = umma_desc_k_sw128(sa);
 #pragma unroll
                         for (int k = 0; k < kBK / kUK; k++) {
@@ -226,7 +235,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                             }
                         }
                     }
-                    umma_commit_2sm(&empty_bar[s], static_cast<uint16_t>((1u << CS) - 1));
+                    umma_commit_2sm(&b_empty[sb_i], mask_b);
+                    umma_commit_2sm(&a_empty[sa_i], mask_a);
                 }
                 if (ok) umma_commit_2sm(tmem_full_bar, static_cast<uint16_t>(0x3u << leader_rank));
             }
@@ -266,166 +276,145 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             }
         }
     } else if (warp == 6) {
-        // ===== relay (only in relay mode, only the c = 1 CTA): rows shipped in by the partner -> pair leader's barrier =====
-        if (lane == 0 && g.relay && !leader && !(g.debug & 4)) {
+        // ===== relay (c = 1 CTA only): the rows the partner shipped in -> the pair leader's barrier.  A bulk copy into
+        // shared memory can only signal a barrier of the CTA it writes to (measured: with the barrier in a third CTA the
+        // bytes never complete), and the MMA thread can only wait on its own CTA's barriers. =====
+        if (lane == 0 && !leader && !(g.debug & 4)) {
             uint32_t it = 0;
             bool ok = true;
             for (int si = 0; si < g.max_seg && ok; si++) {
                 const Seg sg = my[si];
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
-                    const uint32_t s = it % kST, ph = (it / kST) & 1;
+                    const uint32_t s = it % kSA, ph = (it / kSA) & 1;
                     mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
                     if (!mbar_wait_cluster(&xfull_bar[s], ph)) { atomicExch(g.err_flag, 506); ok = false; break; }
-                    mbar_arrive_remote(&full_bar[s], leader_rank);
+                    mbar_arrive_remote(&a_full[s], leader_rank);
                 }
             }
         }
     } else {
-        // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major =====
-        const int cw = warp - kWarpCvt0;               // 0..7: this warp owns rows [8cw, 8cw + 8) = one 1 KB swizzle atom
-        const int chunk = lane & 7;                    // 8 doubles = 64 bytes of the 512-byte row segment
-        const int r = cw * 8 + (lane >> 3);            // rows r and r + 4 of the CTA's 64
+        // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major.
+        // Two groups of 4 warps take alternate K blocks; a warp owns 16 rows (two 1 KB swizzle atoms), a lane one
+        // 64-byte chunk of rows rl, rl + 4, rl + 8, rl + 12. =====
+        const int cw = warp - kWarpCvt0;               // 0..7
+        const int grp = cw >> 2, wq = cw & 3;
+        const int chunk = lane & 7;
+        const int rl = lane >> 3;
         const uint32_t partner = crank ^ 2u;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
-        // loader cursor (runs kDepth K blocks ahead of the converting cursor)
-        int l_si = 0, l_kb = 0, l_kb1 = 0;
-        const double *l_p[2] = {nullptr, nullptr};
-        bool l_in[2] = {false, false};
-        auto l_open = [&]() {
-            while (l_si < g.max_seg) {
-                const Seg sg = my[l_si];
-                if (sg.kb0 >= sg.kb1) { l_si = g.max_seg; break; }
-                l_kb = sg.kb0; l_kb1 = sg.kb1;
-                const long long row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + r;
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const long long row = row0 + 4 * h;
-                    l_in[h] = row < g.rows_total;
-                    l_p[h] = g.x + (l_in[h] ? row : 0) * g.x_ld + chunk * 8;
-                }
-                return;
-            }
-            l_kb = 0; l_kb1 = 0;
+        struct Cur { int si, kb, kb1; long long row0; bool valid; };
+        auto open = [&](Cur &u) {
+            u.valid = false;
+            if (u.si >= g.max_seg) return;
+            const Seg sg = my[u.si];
+            if (sg.kb0 >= sg.kb1) return;
+            u.kb = sg.kb0; u.kb1 = sg.kb1; u.valid = true;
+            u.row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + wq * 16 + rl;
         };
-        auto l_issue = [&](double (&v)[2][8]) {
-            if (l_kb >= l_kb1) {
+        auto advance = [&](Cur &u) {
+            if (!u.valid) return;
+            if (++u.kb >= u.kb1) { u.si++; open(u); }
+        };
+        auto issue = [&](const Cur &u, double (&v)[4][8]) {
+            if (!u.valid) return;
+            const long long col = static_cast<long long>(u.kb) * kBK + chunk * 8;
+            if (g.pf_dist > 0 && chunk == 0 && u.kb + g.pf_dist < u.kb1 && col + (g.pf_dist + 1) * kBK <= g.cols) {
 #pragma unroll
-                for (int h = 0; h < 2; h++)
-#pragma unroll
-                    for (int e = 0; e < 8; e++) v[h][e] = 0.0;
-                return;
-            }
-            const long long col = static_cast<long long>(l_kb) * kBK + chunk * 8;
-            if (g.pf_dist > 0 && chunk == 0 && l_kb + g.pf_dist < l_kb1) {
-                // warm L2 with the 512-byte row segments this warp will load pf_dist K blocks from now
-                const long long pcol = static_cast<long long>(l_kb + g.pf_dist) * kBK;
-                if (pcol + kBK <= g.cols) {
-#pragma unroll
-                    for (int h = 0; h < 2; h++)
-                        if (l_in[h])
-                            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(l_p[h] + pcol), "r"(512u) : "memory");
-                }
+                for (int h = 0; h < 4; h++)
+                    if (u.row0 + 4 * h < g.rows_total)
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g.x + (u.row0 + 4 * h) * g.x_ld + col + g.pf_dist * kBK),
+                                     "r"(512u)
+                                     : "memory");
             }
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-                if (l_in[h] && col + 8 <= g.cols && !(g.debug & 1)) {
+            for (int h = 0; h < 4; h++) {
+                const long long row = u.row0 + 4 * h;
+                const bool in = row < g.rows_total;
+                const double *p = g.x + (in ? row : 0) * g.x_ld + col;
+                if (in && col + 8 <= g.cols && !(g.debug & 1)) {
                     double a[4], b[4];
-                    ldg256(l_p[h] + static_cast<long long>(l_kb) * kBK, a);
-                    ldg256(l_p[h] + static_cast<long long>(l_kb) * kBK + 4, b);
+                    ldg256(p, a);
+                    ldg256(p + 4, b);
 #pragma unroll
                     for (int e = 0; e < 4; e++) { v[h][e] = a[e]; v[h][4 + e] = b[e]; }
                 } else {
 #pragma unroll
-                    for (int e = 0; e < 8; e++)
-                        v[h][e] = (l_in[h] && col + e < g.cols) ? ((g.debug & 1) ? 0.25 : l_p[h][static_cast<long long>(l_kb) * kBK + e]) : 0.0;
+                    for (int e = 0; e < 8; e++) v[h][e] = (in && col + e < g.cols) ? ((g.debug & 1) ? 0.25 : p[e]) : 0.0;
                 }
             }
-            if (++l_kb >= l_kb1) { l_si++; l_open(); }
         };
-        l_open();
-        double buf[kDepth][2][8];
-#pragma unroll
-        for (int d = 0; d < kDepth; d++) l_issue(buf[d]);
-
-        uint32_t it = 0;
+        Cur lc{0, 0, 0, 0, false}, cc{0, 0, 0, 0, false};
+        open(lc);
+        open(cc);
+        if (grp == 1) { advance(lc); advance(cc); }
+        double buf[4][8];
+        issue(lc, buf);
+        advance(lc); advance(lc);
+        uint32_t it = grp;
         uint32_t ovf = 0;
+        float ss[4] = {0.f, 0.f, 0.f, 0.f};
         bool ok = true;
-        // converting cursor: walks the same (segment, K block) sequence as the loader, kDepth items behind it; item i
-        // lives in buf[i % kDepth] whatever the segment lengths are
-        int c_si = 0, c_kb = 0, c_kb1 = 0;
-        long long c_row0 = 0;
-        float ss[2] = {0.f, 0.f};
-        auto c_open = [&]() -> bool {
-            if (c_si >= g.max_seg) return false;
-            const Seg sg = my[c_si];
-            if (sg.kb0 >= sg.kb1) return false;
-            c_kb = sg.kb0; c_kb1 = sg.kb1;
-            c_row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + r;
-            ss[0] = 0.f; ss[1] = 0.f;
-            return true;
-        };
-        bool more = c_open();
-        while (more && ok) {
+        while (cc.valid && ok) {
+            const uint32_t s = it % kSA, ph = (it / kSA) & 1;
+            int w_ok = 1;
+            if (lane == 0) {
+                w_ok = mbar_wait_b(&a_empty[s], ph ^ 1) ? 1 : 0;
+                if (!w_ok) atomicExch(g.err_flag, 507);
+            }
+            w_ok = __shfl_sync(0xffffffffu, w_ok, 0);
+            if (!w_ok) { ok = false; break; }
+            uint8_t *atoms = a_ring + s * kATile + nh * kXHalf + wq * 2048;   // rows [16wq, 16wq + 16) of my 64
 #pragma unroll
-            for (int d = 0; d < kDepth; d++) {
-                if (more && ok) {
-                    const uint32_t s = it % kST, ph = (it / kST) & 1;
-                    int w_ok = 1;
-                    if (lane == 0) {
-                        w_ok = mbar_wait_b(&empty_bar[s], ph ^ 1) ? 1 : 0;
-                        if (!w_ok) atomicExch(g.err_flag, 507);
+            for (int h = 0; h < 4; h++) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    if (g.debug & 16) {  // experiment: no conversion arithmetic at all
+                        pk[e] = static_cast<uint32_t>(__double2hiint(buf[h][2 * e])) ^ static_cast<uint32_t>(__double2loint(buf[h][2 * e + 1]));
+                        continue;
                     }
-                    w_ok = __shfl_sync(0xffffffffu, w_ok, 0);
-                    if (!w_ok) { ok = false; continue; }
-                    uint8_t *atom = smem + s * kStage + nh * kXHalf + cw * 1024;   // rows [8cw, 8cw + 8)
-                    const int rl = lane >> 3;                                     // row inside the atom: rl and rl + 4
+                    const float f0 = static_cast<float>(buf[h][2 * e]), f1 = static_cast<float>(buf[h][2 * e + 1]);
+                    ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
+                    const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
+                    pk[e] = *reinterpret_cast<const uint32_t *>(&h2);
+                    ovf |= ((pk[e] & 0x7C00u) == 0x7C00u) | ((pk[e] & 0x7C000000u) == 0x7C000000u);
+                }
+                const int ra = rl + 4 * h;   // 0..15: row inside the warp's two atoms
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(atoms) + ra * 128 + ((chunk ^ (ra & 7)) << 4)),
+                             "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                             : "memory");
+            }
+            if (!(g.debug & 8)) fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
+            __syncwarp();
+            if (lane == 0) {
+                // ship the 16 rows to the CTA that needs them for the other half of the hidden layer (bytes complete on
+                // a barrier of THAT CTA: a_full if it is a leader, else its relay barrier) ...
+                if (!(g.debug & 4)) dsmem_bulk_copy2(atoms, atoms, 2048, leader ? &a_full[s] : &xfull_bar[s], partner, partner);
+                // ... and tell my own pair's leader that they are in place here
+                // (in the leader CTA the same arrival announces the 2 KB the partner's twin of this warp ships in)
+                if (leader && !(g.debug & 4)) mbar_arrive_expect_tx(&a_full[s], 2048);
+                else if (leader) mbar_arrive(&a_full[s]);
+                else mbar_arrive_remote(&a_full[s], leader_rank);
+            }
+            issue(lc, buf);            // this group's next K block
+            advance(lc); advance(lc);
+            const int si_before = cc.si;
+            const long long row0_before = cc.row0;
+            advance(cc); advance(cc);
+            it += 2;
+            if (!cc.valid || cc.si != si_before) {
+                // per-row sum of squares of the K blocks this group converted in that segment (8 chunk lanes per row)
+                if (g.row_sumsq != nullptr) {
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        uint32_t pk[4];
-#pragma unroll
-                        for (int e = 0; e < 4; e++) {
-                            const float f0 = static_cast<float>(buf[d][h][2 * e]), f1 = static_cast<float>(buf[d][h][2 * e + 1]);
-                            ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
-                            const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
-                            pk[e] = *reinterpret_cast<const uint32_t *>(&h2);
-                            ovf |= ((pk[e] & 0x7C00u) == 0x7C00u) | ((pk[e] & 0x7C000000u) == 0x7C000000u);
-                        }
-                        const int ra = rl + 4 * h;
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(atom) + ra * 128 + ((chunk ^ ra) << 4)),
-                                     "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
-                                     : "memory");
-                    }
-                    if (!(g.debug & 8)) fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
-                    __syncwarp();
-                    if (lane == 0) {
-                        // ship the atom to the CTA that needs the same rows for the other half of the hidden layer; the
-                        // bytes complete on that pair's leader barrier (relay mode: on a c = 1 destination's own barrier)
-                        if (!(g.debug & 4)) {
-                            if (g.relay && !leader) dsmem_bulk_copy2(atom, atom, 1024, &xfull_bar[s], partner, partner);
-                            else dsmem_bulk_copy2(atom, atom, 1024, &full_bar[s], partner, partner & ~1u);
-                        }
-                        // ... and tell my own pair's leader that these 8 rows are in place
-                        if (leader) mbar_arrive(&full_bar[s]);
-                        else mbar_arrive_remote(&full_bar[s], leader_rank);
-                    }
-                    l_issue(buf[d]);            // refill the buffer just consumed
-                    it++;
-                    if (++c_kb >= c_kb1) {
-                        // per-row sum of squares of this segment's K range: the 8 chunk lanes of a row are adjacent
-                        if (g.row_sumsq != nullptr) {
-#pragma unroll
-                            for (int h = 0; h < 2; h++) {
-                                float v = ss[h];
-                                v += __shfl_xor_sync(0xffffffffu, v, 1);
-                                v += __shfl_xor_sync(0xffffffffu, v, 2);
-                                v += __shfl_xor_sync(0xffffffffu, v, 4);
-                                const long long row = c_row0 + 4 * h;
-                                if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
-                            }
-                        }
-                        c_si++;
-                        more = c_open();
+                    for (int h = 0; h < 4; h++) {
+                        float v = ss[h];
+                        v += __shfl_xor_sync(0xffffffffu, v, 1);
+                        v += __shfl_xor_sync(0xffffffffu, v, 2);
+                        v += __shfl_xor_sync(0xffffffffu, v, 4);
+                        const long long row = row0_before + 4 * h;
+                        if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
+                        ss[h] = 0.f;
                     }
                 }
             }
