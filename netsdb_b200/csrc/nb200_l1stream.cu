@@ -666,3 +666,22 @@ int launch_l1_stream_reduce(Context *c, const L1StreamScratch &sc, int rows, int
 }
 
 }  // namespace nb200
+
+// Test hook (not part of the public ABI, needs no device): the wave plan as flat ints, 5 per segment
+// (cluster, tile, kb0, kb1, slot); returns the segment count, or -1 when `cap` ints do not hold them.
+extern "C" int nb200_debug_plan_l1(int tiles, int num_kb, int clusters, int *out, int cap, int *tile_slots) {
+    nb200::L1StreamPlan plan;
+    if (nb200::plan_l1_stream(tiles, num_kb, clusters, &plan) != NB200_OK) return -1;
+    int n = 0;
+    for (int g = 0; g < plan.clusters; g++)
+        for (int j = 0; j < plan.max_seg; j++) {
+            const nb200::L1StreamSeg &sg = plan.segs[static_cast<size_t>(g) * plan.max_seg + j];
+            if (sg.kb0 >= sg.kb1) break;
+            if (5 * (n + 1) > cap) return -1;
+            out[5 * n] = g; out[5 * n + 1] = sg.tile; out[5 * n + 2] = sg.kb0; out[5 * n + 3] = sg.kb1; out[5 * n + 4] = sg.slot;
+            n++;
+        }
+    if (tile_slots)
+        for (int t = 0; t < tiles; t++) tile_slots[t] = plan.tile_slots[t];
+    return n;
+}

@@ -95,3 +95,35 @@ def test_udf_plugin_libraries_export_the_netsdb_abi():
         name = lib.getObjectTypeName().decode()
         assert name in (t, "conv2d_memory_fusion::" + t), (path, name)
         assert lib.getObjectVTable()
+
+
+def test_l1_stream_wave_plan_covers_every_tile_once():
+    """Host logic of the streamed layer-1 kernel (nb200_l1stream.cu: plan_l1_stream): every (tile, K block) is covered by
+    exactly one segment, a tile's partial slots are 0..S-1 with S = tile_slots[tile], and no plan is much worse than the
+    ideal tiles * K / clusters (the row-shard sizes of BASELINE config 3 included)."""
+    import ctypes as C
+
+    import numpy as np
+
+    from netsdb_b200 import build
+
+    L = C.CDLL(build.build())
+    L.nb200_debug_plan_l1.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+    for tiles, num_kb, G in ((20, 9337, 15), (40, 9337, 33), (10, 9337, 15), (5, 9337, 15), (3, 9337, 15), (5, 9337, 33),
+                             (1, 65, 15), (7, 40, 4), (64, 100, 15), (1, 3, 8), (2, 9, 33)):
+        out = np.zeros(5 * 4096, dtype=np.int32)
+        slots = np.zeros(tiles, dtype=np.int32)
+        n = L.nb200_debug_plan_l1(tiles, num_kb, G, out.ctypes.data, out.size, slots.ctypes.data)
+        assert n > 0
+        segs = out[:5 * n].reshape(n, 5)
+        cover = np.zeros((tiles, num_kb), dtype=np.int32)
+        per_cluster = np.zeros(G, dtype=np.int64)
+        for g, t, k0, k1, slot in segs:
+            assert 0 <= g < G and 0 <= t < tiles and 0 <= k0 < k1 <= num_kb and 0 <= slot < slots[t]
+            cover[t, k0:k1] += 1
+            per_cluster[g] += k1 - k0
+        assert (cover == 1).all(), (tiles, num_kb, G)
+        for t in range(tiles):
+            assert sorted(s[4] for s in segs if s[1] == t) == list(range(slots[t]))
+        ideal = tiles * num_kb / G
+        assert per_cluster.max() <= max(1.35 * ideal + 110 * (1 + tiles // G), num_kb / max(1, min(G, num_kb // 8)) + 1), (tiles, num_kb, G, per_cluster.max(), ideal)
