@@ -43,8 +43,8 @@ namespace {
 
 constexpr int kBK = 64;             // K block: 64 fp16 = one 128-byte swizzle row
 constexpr int kUK = 16;             // K of one tcgen05.mma kind::f16
-constexpr int kSA = 8;              // shared-memory slots for X tiles (long chain: convert, DSMEM hand-off, relay)
-constexpr int kSB = 3;              // ... for W1 tiles (TMA out of L2)
+constexpr int kSA = 6;              // shared-memory slots for X tiles (chain: convert, DSMEM hand-off, relay)
+constexpr int kSB = 4;              // ... for W1 tiles (TMA out of L2: ~1.4 us from slot free to tile landed)
 constexpr int kCvtWarps = 8;
 constexpr int kWarpCvt0 = 7;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 relay, 7.. converters
 constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 480
@@ -71,8 +71,6 @@ struct L1SArgs {
     int *err_flag;
     unsigned int idesc;
     int debug;              // experiments: 1 = converters skip the HBM loads, 2 = no MMAs, 4 = no DSMEM copy, 8 = no proxy fence
-    int relay;              // 1: a c = 1 CTA's incoming rows are signalled on its own barrier and relayed to the pair leader
-    int pf_dist;            // L2 prefetch distance of the converters in K blocks (0 = off)
 };
 
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t *bar, uint32_t parity) {
@@ -319,14 +317,6 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         auto issue = [&](const Cur &u, double (&v)[4][8]) {
             if (!u.valid) return;
             const long long col = static_cast<long long>(u.kb) * kBK + chunk * 8;
-            if (g.pf_dist > 0 && chunk == 0 && u.kb + g.pf_dist < u.kb1 && col + (g.pf_dist + 1) * kBK <= g.cols) {
-#pragma unroll
-                for (int h = 0; h < 4; h++)
-                    if (u.row0 + 4 * h < g.rows_total)
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g.x + (u.row0 + 4 * h) * g.x_ld + col + g.pf_dist * kBK),
-                                     "r"(512u)
-                                     : "memory");
-            }
 #pragma unroll
             for (int h = 0; h < 4; h++) {
                 const long long row = u.row0 + 4 * h;
@@ -357,6 +347,26 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         bool ok = true;
         while (cc.valid && ok) {
             const uint32_t s = it % kSA, ph = (it / kSA) & 1;
+            // convert as soon as the loads land and put this group's next K block in flight right away: the registers
+            // are the landing zone, so the only way to keep HBM busy is to never sit on an empty buffer
+            uint32_t pk[4][4];
+#pragma unroll
+            for (int h = 0; h < 4; h++) {
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    if (g.debug & 16) {  // experiment: no conversion arithmetic at all
+                        pk[h][e] = static_cast<uint32_t>(__double2hiint(buf[h][2 * e])) ^ static_cast<uint32_t>(__double2loint(buf[h][2 * e + 1]));
+                        continue;
+                    }
+                    const float f0 = static_cast<float>(buf[h][2 * e]), f1 = static_cast<float>(buf[h][2 * e + 1]);
+                    ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
+                    const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
+                    pk[h][e] = *reinterpret_cast<const uint32_t *>(&h2);
+                    ovf |= ((pk[h][e] & 0x7C00u) == 0x7C00u) | ((pk[h][e] & 0x7C000000u) == 0x7C000000u);
+                }
+            }
+            issue(lc, buf);            // this group's next K block
+            advance(lc); advance(lc);
             int w_ok = 1;
             if (lane == 0) {
                 w_ok = mbar_wait_b(&a_empty[s], ph ^ 1) ? 1 : 0;
@@ -367,22 +377,9 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             uint8_t *atoms = a_ring + s * kATile + nh * kXHalf + wq * 2048;   // rows [16wq, 16wq + 16) of my 64
 #pragma unroll
             for (int h = 0; h < 4; h++) {
-                uint32_t pk[4];
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    if (g.debug & 16) {  // experiment: no conversion arithmetic at all
-                        pk[e] = static_cast<uint32_t>(__double2hiint(buf[h][2 * e])) ^ static_cast<uint32_t>(__double2loint(buf[h][2 * e + 1]));
-                        continue;
-                    }
-                    const float f0 = static_cast<float>(buf[h][2 * e]), f1 = static_cast<float>(buf[h][2 * e + 1]);
-                    ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
-                    const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
-                    pk[e] = *reinterpret_cast<const uint32_t *>(&h2);
-                    ovf |= ((pk[e] & 0x7C00u) == 0x7C00u) | ((pk[e] & 0x7C000000u) == 0x7C000000u);
-                }
                 const int ra = rl + 4 * h;   // 0..15: row inside the warp's two atoms
                 asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(atoms) + ra * 128 + ((chunk ^ (ra & 7)) << 4)),
-                             "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                             "r"(pk[h][0]), "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
                              : "memory");
             }
             if (!(g.debug & 8)) fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
@@ -397,8 +394,6 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 else if (leader) mbar_arrive(&a_full[s]);
                 else mbar_arrive_remote(&a_full[s], leader_rank);
             }
-            issue(lc, buf);            // this group's next K block
-            advance(lc); advance(lc);
             const int si_before = cc.si;
             const long long row0_before = cc.row0;
             advance(cc); advance(cc);
@@ -628,10 +623,6 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
     g.debug = debug;
-    static const int relay_env = getenv("NB200_L1S_RELAY") ? atoi(getenv("NB200_L1S_RELAY")) : 0;
-    static const int pf_env = getenv("NB200_L1S_PF") ? atoi(getenv("NB200_L1S_PF")) : 0;
-    g.relay = relay_env;
-    g.pf_dist = pf_env;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
     k_l1_stream<MT><<<sc->plan.clusters * 4 * MT, kThreadsL1S, kSmemTotal, c->stream>>>(mw, g);

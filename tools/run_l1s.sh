@@ -4,9 +4,9 @@ for mt in 2 1; do
   echo "=== parity MT=$mt"
   NB200_L1S_MT=$mt timeout 300 python tools/l1s_check.py parity 2>&1 | grep -E "mode=2|PARITY|rror|fault"
 done
-for cfg in "2 0 0" "2 0 8" "2 0 16" "2 1 0" "2 16 8" "2 17 0" "2 19 0" "2 4 8" "1 0 0" "1 0 8"; do
+for cfg in "2 0" "2 1" "2 16" "2 17" "2 19" "2 2" "2 4" "1 0" "1 1" "1 19"; do
   set -- $cfg
-  echo "=== amazon MT=$1 DEBUG=$2 PF=$3"
-  NB200_L1S_MT=$1 NB200_L1S_DEBUG=$2 NB200_L1S_PF=$3 timeout 300 python tools/l1s_check.py amazon 2>&1 | grep -E "rep=2|rror|fault" | sed -E 's/ms_convert.*ms_gemm1_kernel/k1/; s/refined.*//'
+  echo "=== amazon MT=$1 DEBUG=$2"
+  NB200_L1S_MT=$1 NB200_L1S_DEBUG=$2 timeout 300 python tools/l1s_check.py amazon 2>&1 | grep -E "rep=2|rror|fault" | sed -E 's/ms_convert.*ms_gemm1_kernel/k1/; s/refined.*//'
 done
-} > gpurun_out/l1s_v4.log 2>&1
+} > gpurun_out/l1s_v5.log 2>&1
