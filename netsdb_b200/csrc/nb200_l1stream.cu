@@ -43,16 +43,15 @@ namespace {
 
 constexpr int kBK = 64;             // K block: 64 fp16 = one 128-byte swizzle row
 constexpr int kUK = 16;             // K of one tcgen05.mma kind::f16
-constexpr int kSA = 6;              // shared-memory slots for X tiles (chain: convert, DSMEM hand-off, relay)
-constexpr int kSB = 4;              // ... for W1 tiles (TMA out of L2: ~1.4 us from slot free to tile landed)
+// shared-memory slots: SA for X tiles (chain: convert, DSMEM hand-off, relay), SB for W1 tiles (TMA out of L2: ~2 us from
+// slot free to tile landed); SA * 16 KB + SB * 32 KB = 224 KB
 constexpr int kCvtWarps = 8;
-constexpr int kWarpCvt0 = 7;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 relay, 7.. converters
-constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 480
+constexpr int kWarpCvt0 = 8;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 relay, 7 manager, 8.. converters
+constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 512
 constexpr uint32_t kATile = 128 * kBK * 2;   // 16 KB: 128 rows of X
 constexpr uint32_t kBTile = 256 * kBK * 2;   // 32 KB: two 128-row chunks of W1
 constexpr uint32_t kXHalf = 64 * kBK * 2;    // 8 KB: the 64 rows one CTA converts
-constexpr uint32_t kBarOff = kSA * kATile + kSB * kBTile;   // 224 KB
-constexpr uint32_t kSmemTotal = kBarOff + (3 * kSA + 2 * kSB + 2) * 8 + 16 + 1024;
+constexpr uint32_t smem_total(int sa, int sb) { return sa * kATile + sb * kBTile + (4 * sa + 2 * sb + 2) * 8 + 16 + 1024; }
 constexpr int kWsLd = 1024;         // fp32 partial tiles: [slot][row][1024]
 
 struct Seg { int tile, kb0, kb1, slot; };
@@ -125,17 +124,18 @@ __device__ __forceinline__ void ldg256(const double *p, double (&v)[4]) {
                  : "l"(p));
 }
 
-template <int MT>
+template <int MT, int kSA, int kSB>
 __global__ void __cluster_dims__(4 * MT, 1, 1) __launch_bounds__(kThreadsL1S, 1)
 k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t *a_ring = smem;                      // kSA x 16 KB: X tiles (fp16, 128B-swizzled K-major)
     uint8_t *b_ring = smem + kSA * kATile;       // kSB x 32 KB: W1 tiles
-    uint64_t *a_full = reinterpret_cast<uint64_t *>(smem + kBarOff);  // leader: both CTAs' A tiles of K block `it` complete
+    uint64_t *a_full = reinterpret_cast<uint64_t *>(smem + kSA * kATile + kSB * kBTile);  // leader: both CTAs' A tiles of K block `it` complete
     uint64_t *a_empty = a_full + kSA;     // every CTA: both pairs that share these X rows have consumed A slot s
-    uint64_t *xfull_bar = a_empty + kSA;  // c = 1 CTAs: the partner's 64 rows have landed (relayed to the leader)
-    uint64_t *b_full = xfull_bar + kSA;   // leader: W1 tile landed in both CTAs
+    uint64_t *xfull_bar = a_empty + kSA;  // every CTA: the partner's 64 rows have landed (the relay tells the leader)
+    uint64_t *cdone_bar = xfull_bar + kSA;  // every CTA: this CTA's converters have written their 64 rows
+    uint64_t *b_full = cdone_bar + kSA;   // leader: W1 tile landed in both CTAs
     uint64_t *b_empty = b_full + kSB;     // every CTA: all pairs that share this W1 tile have consumed B slot s
     uint64_t *tmem_full_bar = b_empty + kSB;
     uint64_t *tmem_empty_bar = tmem_full_bar + 1;
@@ -152,10 +152,11 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < kSA; s++) {
-            // per K block 4 converter warps of each CTA of the pair write this slot, plus the c = 1 CTA's relay
-            mbar_init(&a_full[s], 2 * (kCvtWarps / 2) + ((g.debug & 4) ? 0 : 1));
+            // per K block: the manager of each CTA of the pair (own 64 rows in place) and its relay (partner's 64 rows)
+            mbar_init(&a_full[s], (g.debug & 4) ? 2 : 4);
             mbar_init(&a_empty[s], 2);          // the pairs (mt, 0) and (mt, 1)
             mbar_init(&xfull_bar[s], 1);
+            mbar_init(&cdone_bar[s], kCvtWarps / 2);   // the 4 converter warps that take this K block
         }
         for (int s = 0; s < kSB; s++) {
             mbar_init(&b_full[s], 2);           // leader's expect_tx arrive + the peer producer
@@ -274,10 +275,10 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             }
         }
     } else if (warp == 6) {
-        // ===== relay (c = 1 CTA only): the rows the partner shipped in -> the pair leader's barrier.  A bulk copy into
-        // shared memory can only signal a barrier of the CTA it writes to (measured: with the barrier in a third CTA the
-        // bytes never complete), and the MMA thread can only wait on its own CTA's barriers. =====
-        if (lane == 0 && !leader && !(g.debug & 4)) {
+        // ===== relay: the rows the partner shipped in -> the pair leader's barrier.  A bulk copy into shared memory can
+        // only signal a barrier of the CTA it writes to (measured: with the barrier in a third CTA the bytes never
+        // complete), and the MMA thread can only wait on its own CTA's barriers. =====
+        if (lane == 0 && !(g.debug & 4)) {
             uint32_t it = 0;
             bool ok = true;
             for (int si = 0; si < g.max_seg && ok; si++) {
@@ -287,7 +288,31 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                     const uint32_t s = it % kSA, ph = (it / kSA) & 1;
                     mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
                     if (!mbar_wait_cluster(&xfull_bar[s], ph)) { atomicExch(g.err_flag, 506); ok = false; break; }
-                    mbar_arrive_remote(&a_full[s], leader_rank);
+                    if (leader) mbar_arrive(&a_full[s]);
+                    else mbar_arrive_remote(&a_full[s], leader_rank);
+                }
+            }
+        }
+    } else if (warp == 7) {
+        // ===== manager: once this CTA's converters have written their 64 rows of a K block, make them visible to the
+        // async proxy (tcgen05.mma and the bulk copy read shared memory through it), ship them to the CTA that needs
+        // the same rows for the other half of the hidden layer, and tell the pair leader.  The fence lives here and
+        // not in the converter warps: there it would wait for the fp64 loads they keep in flight. =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            bool ok = true;
+            const uint32_t partner = crank ^ 2u;
+            for (int si = 0; si < g.max_seg && ok; si++) {
+                const Seg sg = my[si];
+                if (sg.kb0 >= sg.kb1) break;
+                for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
+                    const uint32_t s = it % kSA, ph = (it / kSA) & 1;
+                    if (!mbar_wait_b(&cdone_bar[s], ph)) { atomicExch(g.err_flag, 505); ok = false; break; }
+                    if (!(g.debug & 8)) fence_proxy_async_smem();
+                    uint8_t *mine = a_ring + s * kATile + nh * kXHalf;
+                    if (!(g.debug & 4)) dsmem_bulk_copy2(mine, mine, kXHalf, &xfull_bar[s], partner, partner);
+                    if (leader) mbar_arrive(&a_full[s]);
+                    else mbar_arrive_remote(&a_full[s], leader_rank);
                 }
             }
         }
@@ -299,7 +324,6 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         const int grp = cw >> 2, wq = cw & 3;
         const int chunk = lane & 7;
         const int rl = lane >> 3;
-        const uint32_t partner = crank ^ 2u;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
         struct Cur { int si, kb, kb1; long long row0; bool valid; };
         auto open = [&](Cur &u) {
@@ -382,18 +406,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                              "r"(pk[h][0]), "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
                              : "memory");
             }
-            if (!(g.debug & 8)) fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.mma / the bulk copy
             __syncwarp();
-            if (lane == 0) {
-                // ship the 16 rows to the CTA that needs them for the other half of the hidden layer (bytes complete on
-                // a barrier of THAT CTA: a_full if it is a leader, else its relay barrier) ...
-                if (!(g.debug & 4)) dsmem_bulk_copy2(atoms, atoms, 2048, leader ? &a_full[s] : &xfull_bar[s], partner, partner);
-                // ... and tell my own pair's leader that they are in place here
-                // (in the leader CTA the same arrival announces the 2 KB the partner's twin of this warp ships in)
-                if (leader && !(g.debug & 4)) mbar_arrive_expect_tx(&a_full[s], 2048);
-                else if (leader) mbar_arrive(&a_full[s]);
-                else mbar_arrive_remote(&a_full[s], leader_rank);
-            }
+            if (lane == 0) mbar_arrive(&cdone_bar[s]);   // (release: the warp's stores are ordered before it)
             const int si_before = cc.si;
             const long long row0_before = cc.row0;
             advance(cc); advance(cc);
@@ -495,22 +509,22 @@ int make_w_map(CUtensorMap *m, const void *base, int64_t rows, int64_t ldk, int 
     return NB200_OK;
 }
 
-template <int MT>
+template <int MT, int SA, int SB>
 int max_clusters(int *out) {
     static int cached = -1;
     if (cached < 0) {
-        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(4 * MT * 64);
         cfg.blockDim = dim3(kThreadsL1S);
-        cfg.dynamicSmemBytes = kSmemTotal;
+        cfg.dynamicSmemBytes = smem_total(SA, SB);
         cudaLaunchAttribute at{};
         at.id = cudaLaunchAttributeClusterDimension;
         at.val.clusterDim.x = 4 * MT; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
         cfg.attrs = &at;
         cfg.numAttrs = 1;
         int n = 0;
-        NB_CUDA(cudaOccupancyMaxActiveClusters(&n, k_l1_stream<MT>, &cfg));
+        NB_CUDA(cudaOccupancyMaxActiveClusters(&n, k_l1_stream<MT, SA, SB>, &cfg));
         cached = n;
     }
     *out = cached;
@@ -580,11 +594,11 @@ bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, con
            (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
 }
 
-template <int MT>
+template <int MT, int SA, int SB>
 static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,
                                  float *maxscaled, const Planes &w1, L1StreamScratch *sc, int debug) {
     int G = 0;
-    NB_TRY(max_clusters<MT>(&G));
+    NB_TRY((max_clusters<MT, SA, SB>(&G)));
     if (G < 1) { set_error("l1 stream: no cluster of %d CTAs fits this device", 4 * MT); return NB200_ERR_STATE; }
     static const int g_env = getenv("NB200_L1S_CLUSTERS") ? atoi(getenv("NB200_L1S_CLUSTERS")) : 0;
     if (g_env > 0 && g_env < G) G = g_env;
@@ -625,7 +639,7 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     g.debug = debug;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
-    k_l1_stream<MT><<<sc->plan.clusters * 4 * MT, kThreadsL1S, kSmemTotal, c->stream>>>(mw, g);
+    k_l1_stream<MT, SA, SB><<<sc->plan.clusters * 4 * MT, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     return NB200_OK;
@@ -642,8 +656,13 @@ int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int co
         const int64_t pad1 = ceil_div(rows, 256) * 256, pad2 = ceil_div(rows, 512) * 512;
         mt = (pad2 * 10 <= pad1 * 12) ? 2 : 1;
     }
-    if (mt == 2) return launch_l1_stream_impl<2>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
-    return launch_l1_stream_impl<1>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    static const int ring_env = getenv("NB200_L1S_RING") ? atoi(getenv("NB200_L1S_RING")) : 64;   // SA * 10 + SB
+    if (ring_env == 45) {
+        if (mt == 2) return launch_l1_stream_impl<2, 4, 5>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+        return launch_l1_stream_impl<1, 4, 5>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    }
+    if (mt == 2) return launch_l1_stream_impl<2, 6, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    return launch_l1_stream_impl<1, 6, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
 }
 
 int launch_l1_stream_reduce(Context *c, const L1StreamScratch &sc, int rows, int N, const float *bias_n, int relu,
