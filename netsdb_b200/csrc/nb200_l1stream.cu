@@ -45,9 +45,9 @@ constexpr int kBK = 64;             // K block: 64 fp16 = one 128-byte swizzle r
 constexpr int kUK = 16;             // K of one tcgen05.mma kind::f16
 // shared-memory slots: SA for X tiles (chain: convert, DSMEM hand-off, relay), SB for W1 tiles (TMA out of L2: ~2 us from
 // slot free to tile landed); SA * 16 KB + SB * 32 KB = 224 KB
-constexpr int kCvtWarps = 8;
+constexpr int kCvtWarps = 16;
 constexpr int kWarpCvt0 = 8;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 relay, 7 manager, 8.. converters
-constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 512
+constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 768
 constexpr uint32_t kATile = 128 * kBK * 2;   // 16 KB: 128 rows of X
 constexpr uint32_t kBTile = 256 * kBK * 2;   // 32 KB: two 128-row chunks of W1
 constexpr uint32_t kXHalf = 64 * kBK * 2;    // 8 KB: the 64 rows one CTA converts
@@ -69,7 +69,7 @@ struct L1SArgs {
     int max_seg;
     int *err_flag;
     unsigned int idesc;
-    int debug;              // experiments: 1 = converters skip the HBM loads, 2 = no MMAs, 4 = no DSMEM copy, 8 = no proxy fence
+    int debug;              // experiments: 2 = no MMAs, 4 = no DSMEM copy, 8 = no proxy fence
 };
 
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t *bar, uint32_t parity) {
@@ -156,7 +156,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             mbar_init(&a_full[s], (g.debug & 4) ? 2 : 4);
             mbar_init(&a_empty[s], 2);          // the pairs (mt, 0) and (mt, 1)
             mbar_init(&xfull_bar[s], 1);
-            mbar_init(&cdone_bar[s], kCvtWarps / 2);   // the 4 converter warps that take this K block
+            mbar_init(&cdone_bar[s], kCvtWarps / 2);   // the 8 converter warps that take this K block
         }
         for (int s = 0; s < kSB; s++) {
             mbar_init(&b_full[s], 2);           // leader's expect_tx arrive + the peer producer
@@ -318,117 +318,114 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         }
     } else {
         // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major.
-        // Two groups of 4 warps take alternate K blocks; a warp owns 16 rows (two 1 KB swizzle atoms), a lane one
-        // 64-byte chunk of rows rl, rl + 4, rl + 8, rl + 12. =====
-        const int cw = warp - kWarpCvt0;               // 0..7
-        const int grp = cw >> 2, wq = cw & 3;
+        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), a lane one 64-byte
+        // chunk of rows rl and rl + 4.  The registers are the landing zone of the HBM stream (128 bytes per lane, 64 KB
+        // per SM), so a buffer is re-issued the moment it has been converted; many light warps rather than few heavy
+        // ones because the loop is a chain of dependent conversions (measured: 8 warps sat in dependency stalls). =====
+        const int cw = warp - kWarpCvt0;               // 0..15
+        const int grp = cw >> 3, wq = cw & 7;
         const int chunk = lane & 7;
         const int rl = lane >> 3;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
-        struct Cur { int si, kb, kb1; long long row0; bool valid; };
+        const int row_in_tile = static_cast<int>(mt * 256 + c * 128 + nh * 64) + wq * 8 + rl;
+        struct Cur { int si, kb, kb1, in; const double *p0; };   // valid while kb < kb1; in: bit h = row rl + 4h exists
         auto open = [&](Cur &u) {
-            u.valid = false;
+            u.kb = 0; u.kb1 = 0;
             if (u.si >= g.max_seg) return;
             const Seg sg = my[u.si];
             if (sg.kb0 >= sg.kb1) return;
-            u.kb = sg.kb0; u.kb1 = sg.kb1; u.valid = true;
-            u.row0 = static_cast<long long>(sg.tile) * (256 * MT) + mt * 256 + c * 128 + nh * 64 + wq * 16 + rl;
+            u.kb = sg.kb0; u.kb1 = sg.kb1;
+            const int row0 = sg.tile * (256 * MT) + row_in_tile;
+            u.in = (row0 < g.rows_total ? 1 : 0) | (row0 + 4 < g.rows_total ? 2 : 0);
+            u.p0 = g.x + static_cast<long long>(u.in ? row0 : 0) * g.x_ld + chunk * 8;
         };
         auto advance = [&](Cur &u) {
-            if (!u.valid) return;
+            if (u.kb >= u.kb1) return;
             if (++u.kb >= u.kb1) { u.si++; open(u); }
         };
-        auto issue = [&](const Cur &u, double (&v)[4][8]) {
-            if (!u.valid) return;
-            const long long col = static_cast<long long>(u.kb) * kBK + chunk * 8;
+        auto load_row = [&](const double *p, bool in, int kb, double (&v)[8]) {
+            const long long col = static_cast<long long>(kb) * kBK;
+            if (in && col + chunk * 8 + 8 <= g.cols) {
+                double a[4], b[4];
+                ldg256(p + col, a);
+                ldg256(p + col + 4, b);
 #pragma unroll
-            for (int h = 0; h < 4; h++) {
-                const long long row = u.row0 + 4 * h;
-                const bool in = row < g.rows_total;
-                const double *p = g.x + (in ? row : 0) * g.x_ld + col;
-                if (in && col + 8 <= g.cols && !(g.debug & 1)) {
-                    double a[4], b[4];
-                    ldg256(p, a);
-                    ldg256(p + 4, b);
+                for (int e = 0; e < 4; e++) { v[e] = a[e]; v[4 + e] = b[e]; }
+            } else {
 #pragma unroll
-                    for (int e = 0; e < 4; e++) { v[h][e] = a[e]; v[h][4 + e] = b[e]; }
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 8; e++) v[h][e] = (in && col + e < g.cols) ? ((g.debug & 1) ? 0.25 : p[e]) : 0.0;
-                }
+                for (int e = 0; e < 8; e++) v[e] = (in && col + chunk * 8 + e < g.cols) ? p[col + e] : 0.0;
             }
         };
-        Cur lc{0, 0, 0, 0, false}, cc{0, 0, 0, 0, false};
+        auto issue = [&](const Cur &u, double (&v)[2][8]) {
+            if (u.kb >= u.kb1) return;
+            load_row(u.p0, (u.in & 1) != 0, u.kb, v[0]);
+            load_row(u.p0 + 4 * g.x_ld, (u.in & 2) != 0, u.kb, v[1]);
+        };
+        Cur lc{0, 0, 0, 0, nullptr};
         open(lc);
-        open(cc);
-        if (grp == 1) { advance(lc); advance(cc); }
-        double buf[4][8];
+        if (grp == 1) advance(lc);
+        Cur cc = lc;
+        double buf[2][8];
         issue(lc, buf);
         advance(lc); advance(lc);
         uint32_t it = grp;
-        uint32_t ovf = 0;
-        float ss[4] = {0.f, 0.f, 0.f, 0.f};
+        __half2 hmax = __floats2half2_rn(0.f, 0.f);   // running max |x * 2^e| (fp16 overflow check)
+        float ss[2] = {0.f, 0.f};
         bool ok = true;
-        while (cc.valid && ok) {
+        while (cc.kb < cc.kb1 && ok) {
             const uint32_t s = it % kSA, ph = (it / kSA) & 1;
-            // convert as soon as the loads land and put this group's next K block in flight right away: the registers
-            // are the landing zone, so the only way to keep HBM busy is to never sit on an empty buffer
-            uint32_t pk[4][4];
+            uint32_t pk[2][4];
 #pragma unroll
-            for (int h = 0; h < 4; h++) {
+            for (int h = 0; h < 2; h++) {
 #pragma unroll
                 for (int e = 0; e < 4; e++) {
-                    if (g.debug & 16) {  // experiment: no conversion arithmetic at all
-                        pk[h][e] = static_cast<uint32_t>(__double2hiint(buf[h][2 * e])) ^ static_cast<uint32_t>(__double2loint(buf[h][2 * e + 1]));
-                        continue;
-                    }
                     const float f0 = static_cast<float>(buf[h][2 * e]), f1 = static_cast<float>(buf[h][2 * e + 1]);
                     ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
                     const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
+                    hmax = __hmax2(hmax, __habs2(h2));
                     pk[h][e] = *reinterpret_cast<const uint32_t *>(&h2);
-                    ovf |= ((pk[h][e] & 0x7C00u) == 0x7C00u) | ((pk[h][e] & 0x7C000000u) == 0x7C000000u);
                 }
             }
-            issue(lc, buf);            // this group's next K block
+            issue(lc, buf);            // this group's next K block goes in flight before anything else happens
             advance(lc); advance(lc);
-            int w_ok = 1;
-            if (lane == 0) {
-                w_ok = mbar_wait_b(&a_empty[s], ph ^ 1) ? 1 : 0;
-                if (!w_ok) atomicExch(g.err_flag, 507);
+            if (!mbar_wait_b(&a_empty[s], ph ^ 1)) {   // every lane polls: no broadcast needed
+                if (lane == 0) atomicExch(g.err_flag, 507);
+                ok = false;
+                break;
             }
-            w_ok = __shfl_sync(0xffffffffu, w_ok, 0);
-            if (!w_ok) { ok = false; break; }
-            uint8_t *atoms = a_ring + s * kATile + nh * kXHalf + wq * 2048;   // rows [16wq, 16wq + 16) of my 64
+            const uint32_t atom = smem_u32(a_ring + s * kATile + nh * kXHalf + wq * 1024);   // rows [8wq, 8wq + 8) of my 64
 #pragma unroll
-            for (int h = 0; h < 4; h++) {
-                const int ra = rl + 4 * h;   // 0..15: row inside the warp's two atoms
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(atoms) + ra * 128 + ((chunk ^ (ra & 7)) << 4)),
-                             "r"(pk[h][0]), "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
+            for (int h = 0; h < 2; h++) {
+                const int ra = rl + 4 * h;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + ra * 128 + ((chunk ^ ra) << 4)), "r"(pk[h][0]),
+                             "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
                              : "memory");
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&cdone_bar[s]);   // (release: the warp's stores are ordered before it)
             const int si_before = cc.si;
-            const long long row0_before = cc.row0;
             advance(cc); advance(cc);
             it += 2;
-            if (!cc.valid || cc.si != si_before) {
+            if (cc.kb >= cc.kb1 || cc.si != si_before) {
                 // per-row sum of squares of the K blocks this group converted in that segment (8 chunk lanes per row)
                 if (g.row_sumsq != nullptr) {
 #pragma unroll
-                    for (int h = 0; h < 4; h++) {
+                    for (int h = 0; h < 2; h++) {
                         float v = ss[h];
                         v += __shfl_xor_sync(0xffffffffu, v, 1);
                         v += __shfl_xor_sync(0xffffffffu, v, 2);
                         v += __shfl_xor_sync(0xffffffffu, v, 4);
-                        const long long row = row0_before + 4 * h;
+                        const int row = my[si_before].tile * (256 * MT) + row_in_tile + 4 * h;
                         if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
                         ss[h] = 0.f;
                     }
                 }
             }
         }
-        if (__any_sync(0xffffffffu, ovf != 0) && lane == 0 && g.maxscaled != nullptr)
+        // an fp16 infinity anywhere means the sampled scale let an input overflow: report +inf
+        const uint32_t hm = *reinterpret_cast<const uint32_t *>(&hmax);
+        const bool ovf = (hm & 0x7FFFu) >= 0x7C00u || ((hm >> 16) & 0x7FFFu) >= 0x7C00u;
+        if (__any_sync(0xffffffffu, ovf) && lane == 0 && g.maxscaled != nullptr)
             atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), 0x7F800000u);
     }
     tc_fence_before();
