@@ -47,8 +47,9 @@ def gather_labels(local_labels, total_rows: int, world: int, rank: int, dist=Non
 
     sizes = [row_shard(total_rows, world, r)[1] for r in range(world)]
     mx = max(sizes)
-    buf = torch.full((mx,), -1, dtype=torch.int32)
-    buf[: sizes[rank]] = torch.as_tensor(np.asarray(local_labels, dtype=np.int32))
-    out = [torch.empty(mx, dtype=torch.int32) for _ in range(world)]
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"   # NCCL moves device tensors only
+    buf = torch.full((mx,), -1, dtype=torch.int32, device=dev)
+    buf[: sizes[rank]] = torch.as_tensor(np.asarray(local_labels, dtype=np.int32)).to(dev)
+    out = [torch.empty(mx, dtype=torch.int32, device=dev) for _ in range(world)]
     dist.all_gather(out, buf)
-    return np.concatenate([o[:n].numpy() for o, n in zip(out, sizes)])
+    return np.concatenate([o[:n].cpu().numpy() for o, n in zip(out, sizes)])
