@@ -289,7 +289,9 @@ int nb200_conv2d_result_to_images(nb200_set *result, int num_images, int x, int 
  *  - the first call on a device looks up the scratch array's device address and sets kernel attributes;
  *    make that first call before any stream capture.
  *  - all calls share the one array, which still holds the previous call's data: calls whose GPU work
- *    can overlap (different streams, different threads) race and must be serialised by the caller. */
+ *    can overlap (different streams, different threads) race and must be serialised by the caller.
+ *  - the call returns before the work has run, so a fault inside the kernels (a pipeline barrier that timed
+ *    out) cannot come back as a status: in that case every element of C is NaN once the stream has drained. */
 #define NB200_NOALLOC_SCRATCH_BYTES (64u << 20)
 int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, const double *b_dev, int64_t ldb, int I, int J,
                                  int K, double *c_dev, int64_t ldc, void *cuda_stream);

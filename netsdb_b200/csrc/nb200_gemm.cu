@@ -19,6 +19,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 namespace nb200 {
 
@@ -1203,9 +1204,10 @@ int launch_conv_implicit(Context *c, const __nv_bfloat16 *img_hi, const __nv_bfl
 // address.  The device address comes from cudaGetSymbolAddress, once per device with that device
 // current (first call = set-up; do it before any stream capture).  Device code may name the array
 // directly, as k_na_reduce does.  The array is shared by all calls and keeps the last call's contents:
-// nothing in it needs to start at zero except the fault word (cleared per call), because every split
-// overwrites its whole partial tile and the conversion rewrites the K padding; calls whose GPU work
-// overlaps race on it.
+// nothing in it needs to start at zero except the fault word in its last 256 bytes (cleared per call), because
+// every split overwrites its whole partial tile and the conversion rewrites the K padding; calls whose GPU work
+// overlaps race on it.  A kernel-internal fault (a pipeline barrier that timed out) sets the fault word and the
+// reduction then fills C with NaN instead of summing stale partial tiles: the caller sees it without a query.
 // ---------------------------------------------------------------------------------------------
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NB200_NOALLOC_SCRATCH_BYTES];
 
@@ -1222,17 +1224,17 @@ __global__ void __launch_bounds__(256)
 k_na_reduce(unsigned long long partial_off, long long split_stride, int ws_ld, int splits, int M, int N,
             double *__restrict__ out, long long out_ld) {
     const float *ws = reinterpret_cast<const float *>(g_noalloc_scratch + partial_off);
+    const int fault = *reinterpret_cast<const int *>(g_noalloc_scratch + (NB200_NOALLOC_SCRATCH_BYTES - 256));
     const long long m = blockIdx.x;
     for (int n = blockIdx.y * 256 + threadIdx.x; n < N; n += gridDim.y * 256) {
         float acc = 0.f;
         for (int s = 0; s < splits; s++) acc += ws[s * split_stride + m * ws_ld + n];
-        out[m * out_ld + n] = static_cast<double>(acc);
+        // the GEMM skipped its stores if a barrier wait timed out: never hand back sums of stale tiles
+        out[m * out_ld + n] = fault != 0 ? __longlong_as_double(0x7FF8000000000000ll) : static_cast<double>(acc);
     }
 }
 
 }  // namespace nb200
-
-#include <mutex>
 
 extern "C" int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, const double *b_dev, int64_t ldb, int I,
                                             int J, int K, double *c_dev, int64_t ldc, void *cuda_stream) {
@@ -1288,7 +1290,7 @@ extern "C" int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, co
     __nv_bfloat16 *pa = reinterpret_cast<__nv_bfloat16 *>(base);
     __nv_bfloat16 *pb = reinterpret_cast<__nv_bfloat16 *>(base + a_bytes);
     float *partial = reinterpret_cast<float *>(base + a_bytes + b_bytes);
-    int *fault = reinterpret_cast<int *>(base + a_bytes + b_bytes + p_bytes);
+    int *fault = reinterpret_cast<int *>(base + (NB200_NOALLOC_SCRATCH_BYTES - 256));  // fixed place: k_na_reduce reads it by name
     NB_CUDA(cudaMemsetAsync(fault, 0, sizeof(int), stream));  // the one word that must start at zero
     const unsigned chunks = static_cast<unsigned>(ceil_div(ldk, 256) < 32 ? ceil_div(ldk, 256) : 32);
     k_na_convert<<<dim3(I, chunks), 256, 0, stream>>>(a_dev, lda, K, pa, static_cast<int>(ldk));
@@ -1310,6 +1312,3 @@ extern "C" int nb200_transpose_mult_noalloc(const double *a_dev, int64_t lda, co
     NB_CUDA(cudaGetLastError());
     return NB200_OK;
 }
-
-namespace nb200 {
-}  // namespace nb200

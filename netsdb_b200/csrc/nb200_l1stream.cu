@@ -70,6 +70,7 @@ struct L1SArgs {
     int *err_flag;
     unsigned int idesc;
     int debug;              // experiments: 2 = no MMAs, 4 = no DSMEM copy, 8 = no proxy fence
+    unsigned long long *prof;   // experiments: per-CTA cycle counters [cta][16] (null = off)
 };
 
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t *bar, uint32_t parity) {
@@ -148,6 +149,11 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     const bool leader = c == 0;
     const int cluster_id = blockIdx.x / (4 * MT);
     const Seg *my = g.sched + static_cast<long long>(cluster_id) * g.max_seg;
+    // cycle accounting (experiments): slot 0 producer b_empty, 1 mma b_full, 2 mma a_full, 3 relay xfull, 4 manager cdone,
+    // 5 converter warp 0 a_empty, 6 converter warp 0 total, 7 converter warp 8 a_empty, 8 converter warp 8 total, 9 mma total
+    unsigned long long *prof = g.prof ? g.prof + static_cast<long long>(blockIdx.x) * 16 : nullptr;
+    unsigned long long t_acc = 0, t_acc2 = 0, t_cvt_issue = 0;
+#define L1S_TIMED(acc, expr) [&]() { const long long _t0 = prof ? clock64() : 0; const bool _r = (expr); if (prof) acc += clock64() - _t0; return _r; }()
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
@@ -185,7 +191,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kSB, ph = (it / kSB) & 1;
-                    if (!mbar_wait_b(&b_empty[s], ph ^ 1)) { atomicExch(g.err_flag, 501); ok = false; break; }
+                    if (!L1S_TIMED(t_acc, mbar_wait_b(&b_empty[s], ph ^ 1))) { atomicExch(g.err_flag, 501); ok = false; break; }
                     uint8_t *sb = b_ring + s * kBTile;
                     if (leader) mbar_arrive_expect_tx(&b_full[s], 2 * kBTile);
                     else mbar_arrive_remote(&b_full[s], leader_rank);
@@ -203,6 +209,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     } else if (warp == 1) {
         // ===== MMA issuer: one thread of each pair's leader =====
         if (leader && lane == 0) {
+            const long long t_mma0 = prof ? clock64() : 0;
             uint32_t it = 0;
             bool ok = true;
             // who shares my X rows (same mt) and who shares my W1 tile (same nh)
@@ -217,8 +224,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 }
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t sa_i = it % kSA, pha = (it / kSA) & 1, sb_i = it % kSB, phb = (it / kSB) & 1;
-                    if (!mbar_wait_cluster(&b_full[sb_i], phb)) { atomicExch(g.err_flag, 503); ok = false; break; }
-                    if (!mbar_wait_cluster(&a_full[sa_i], pha)) { atomicExch(g.err_flag, 508); ok = false; break; }
+                    if (!L1S_TIMED(t_acc, mbar_wait_cluster(&b_full[sb_i], phb))) { atomicExch(g.err_flag, 503); ok = false; break; }
+                    if (!L1S_TIMED(t_acc2, mbar_wait_cluster(&a_full[sa_i], pha))) { atomicExch(g.err_flag, 508); ok = false; break; }
                     tc_fence_after();
                     if (!(g.debug & 2)) {
                         const uint32_t sa = smem_u32(a_ring + sa_i * kATile);
@@ -239,6 +246,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 }
                 if (ok) umma_commit_2sm(tmem_full_bar, static_cast<uint16_t>(0x3u << leader_rank));
             }
+            if (prof) prof[9] = clock64() - t_mma0;
         }
     } else if (warp < 6) {
         // ===== epilogue: TMEM -> fp32 partial tile in the workspace =====
@@ -287,7 +295,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kSA, ph = (it / kSA) & 1;
                     mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
-                    if (!mbar_wait_cluster(&xfull_bar[s], ph)) { atomicExch(g.err_flag, 506); ok = false; break; }
+                    if (!L1S_TIMED(t_acc, mbar_wait_cluster(&xfull_bar[s], ph))) { atomicExch(g.err_flag, 506); ok = false; break; }
                     if (leader) mbar_arrive(&a_full[s]);
                     else mbar_arrive_remote(&a_full[s], leader_rank);
                 }
@@ -307,7 +315,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kSA, ph = (it / kSA) & 1;
-                    if (!mbar_wait_b(&cdone_bar[s], ph)) { atomicExch(g.err_flag, 505); ok = false; break; }
+                    if (!L1S_TIMED(t_acc, mbar_wait_b(&cdone_bar[s], ph))) { atomicExch(g.err_flag, 505); ok = false; break; }
                     if (!(g.debug & 8)) fence_proxy_async_smem();
                     uint8_t *mine = a_ring + s * kATile + nh * kXHalf;
                     if (!(g.debug & 4)) dsmem_bulk_copy2(mine, mine, kXHalf, &xfull_bar[s], partner, partner);
@@ -372,8 +380,10 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         __half2 hmax = __floats2half2_rn(0.f, 0.f);   // running max |x * 2^e| (fp16 overflow check)
         float ss[2] = {0.f, 0.f};
         bool ok = true;
+        const long long t_loop0 = prof ? clock64() : 0;
         while (cc.kb < cc.kb1 && ok) {
             const uint32_t s = it % kSA, ph = (it / kSA) & 1;
+            const long long tA = prof ? clock64() : 0;
             uint32_t pk[2][4];
 #pragma unroll
             for (int h = 0; h < 2; h++) {
@@ -386,9 +396,12 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                     pk[h][e] = *reinterpret_cast<const uint32_t *>(&h2);
                 }
             }
+            const long long tB = prof ? clock64() : 0;
             issue(lc, buf);            // this group's next K block goes in flight before anything else happens
             advance(lc); advance(lc);
-            if (!mbar_wait_b(&a_empty[s], ph ^ 1)) {   // every lane polls: no broadcast needed
+            const long long tC = prof ? clock64() : 0;
+            if (prof) { t_acc2 += tB - tA; t_cvt_issue += tC - tB; }
+            if (!L1S_TIMED(t_acc, mbar_wait_b(&a_empty[s], ph ^ 1))) {   // every lane polls: no broadcast needed
                 if (lane == 0) atomicExch(g.err_flag, 507);
                 ok = false;
                 break;
@@ -422,11 +435,20 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 }
             }
         }
+        if (prof && lane == 0 && (warp == kWarpCvt0 || warp == kWarpCvt0 + 8)) prof[warp == kWarpCvt0 ? 6 : 8] = clock64() - t_loop0;
         // an fp16 infinity anywhere means the sampled scale let an input overflow: report +inf
         const uint32_t hm = *reinterpret_cast<const uint32_t *>(&hmax);
         const bool ovf = (hm & 0x7FFFu) >= 0x7C00u || ((hm >> 16) & 0x7FFFu) >= 0x7C00u;
         if (__any_sync(0xffffffffu, ovf) && lane == 0 && g.maxscaled != nullptr)
             atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), 0x7F800000u);
+    }
+    if (prof && lane == 0) {
+        if (warp == 0) prof[0] = t_acc;
+        if (warp == 1) { prof[1] = t_acc; prof[2] = t_acc2; }
+        if (warp == 6) prof[3] = t_acc;
+        if (warp == 7) prof[4] = t_acc;
+        if (warp == kWarpCvt0) { prof[5] = t_acc; prof[10] = t_acc2; prof[11] = t_cvt_issue; }
+        if (warp == kWarpCvt0 + 8) prof[7] = t_acc;
     }
     tc_fence_before();
     cluster_sync_all();   // nobody leaves while a peer may still read its shared memory or TMEM
@@ -634,11 +656,30 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
     g.debug = debug;
+    static unsigned long long *prof_dev = nullptr;
+    static const bool prof_on = getenv("NB200_L1S_PROF") != nullptr;
+    const int nctas = sc->plan.clusters * 4 * MT;
+    if (prof_on && !prof_dev) NB_CUDA(cudaMalloc(&prof_dev, 1024 * 16 * sizeof(unsigned long long)));
+    if (prof_on) NB_CUDA(cudaMemsetAsync(prof_dev, 0, 1024 * 16 * sizeof(unsigned long long), c->stream));
+    g.prof = prof_on ? prof_dev : nullptr;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
     k_l1_stream<MT, SA, SB><<<sc->plan.clusters * 4 * MT, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
     c->launches++;
     NB_CUDA(cudaGetLastError());
+    if (prof_on) {   // experiments only: synchronises
+        std::vector<unsigned long long> h(static_cast<size_t>(nctas) * 16);
+        NB_CUDA(cudaMemcpyAsync(h.data(), prof_dev, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        static const char *names[12] = {"producer wait b_empty", "mma wait b_full", "mma wait a_full", "relay wait xfull", "manager wait cdone",
+                                        "cvt w0 wait a_empty", "cvt w0 loop total", "cvt w8 wait a_empty", "cvt w8 loop total", "mma loop total",
+                                        "cvt w0 load stall+convert", "cvt w0 issue loads"};
+        for (int k = 0; k < 12; k++) {
+            double sum = 0, mx = 0; int n = 0;
+            for (int b = 0; b < nctas; b++) { const double v = static_cast<double>(h[static_cast<size_t>(b) * 16 + k]); if (v > 0) { sum += v; n++; if (v > mx) mx = v; } }
+            fprintf(stderr, "[l1 stream prof] %-24s mean %.3f Mcycles over %d CTAs, max %.3f\n", names[k], n ? sum / n / 1e6 : 0.0, n, mx / 1e6);
+        }
+    }
     return NB200_OK;
 }
 

@@ -47,13 +47,38 @@ def test_no_alloc_product_matches_regular_entry_point_twice_in_a_row(nb):
         b = rng.uniform(-0.5, 0.5, size=(J, K))
         ref = _regular(nb, a, b, blk)
         got = _call(nb, torch, a, b)
-        assert np.isfinite(got).all()
+        assert np.isfinite(got).all()   # (a kernel-internal fault would have filled C with NaN)
+        exact = a @ b.T                 # independent of the library: fp64 on the host
+        assert np.abs(got - exact).max() / np.abs(exact).max() <= TOL_BF16, (I, J, K)
         err = np.abs(got - ref).max() / np.abs(ref).max()
         assert err <= TOL_BF16, (I, J, K, err)
         # same arithmetic (one bf16 pass, fp32 accumulate): the two paths differ only in summation order
         assert err <= 1e-5, err
         # and a repeat of the very same call reproduces its own result exactly
         assert np.array_equal(_call(nb, torch, a, b), got)
+
+
+def test_no_alloc_padded_pitches_on_a_side_stream(nb):
+    """Operands and result that are windows of larger device buffers (lda, ldb, ldc wider than the logical
+    matrices), queued on a stream of the caller's; J <= 128 takes the narrow-tile kernel."""
+    import torch
+
+    rng = np.random.default_rng(9)
+    I, J, K = 200, 96, 700
+    big_a = rng.uniform(-0.5, 0.5, size=(I, K + 13))
+    big_b = rng.uniform(-0.5, 0.5, size=(J, K + 40))
+    ta, tb = torch.from_numpy(big_a).cuda(), torch.from_numpy(big_b).cuda()
+    tc = torch.full((I, J + 7), float("nan"), dtype=torch.float64, device="cuda")
+    side = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    for _ in range(2):
+        nb.check(nb.lib().nb200_transpose_mult_noalloc(C.c_void_p(ta.data_ptr()), K + 13, C.c_void_p(tb.data_ptr()), K + 40,
+                                                      I, J, K, C.c_void_p(tc.data_ptr()), J + 7, C.c_void_p(side.cuda_stream)))
+        side.synchronize()
+        got = tc.cpu().numpy()
+        exact = big_a[:, :K] @ big_b[:, :K].T
+        assert np.abs(got[:, :J] - exact).max() / np.abs(exact).max() <= TOL_BF16
+        assert np.isnan(got[:, J:]).all()   # nothing written beyond the logical width
 
 
 def test_no_alloc_rejects_sizes_beyond_the_fixed_scratch(nb):
