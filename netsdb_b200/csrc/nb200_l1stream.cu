@@ -57,7 +57,7 @@ constexpr int kWsLd = 1024;         // fp32 partial tiles: [slot][row][1024]
 struct Seg { int tile, kb0, kb1, slot; };
 
 struct L1SArgs {
-    const double *x;        // [rows_total x cols] fp64, pitch x_ld (multiple of 4, base 32-byte aligned)
+    const double *x;        // [rows_total x cols] fp64, pitch x_ld
     long long x_ld;
     int rows_total, cols;
     const int *exp_x;       // fp16 scale exponent of X (device)
@@ -119,12 +119,16 @@ __device__ __forceinline__ void dsmem_bulk_copy2(void *dst_same_offset, const vo
                  ::"r"(rd), "r"(smem_u32(src)), "r"(bytes), "r"(rb)
                  : "memory");
 }
-__device__ __forceinline__ void ldg256(const double *p, double (&v)[4]) {
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.f64 {%0, %1, %2, %3}, [%4];"
-                 : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
-                 : "l"(p));
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
 }
-
+__device__ __forceinline__ uint32_t ldg_hi(const uint32_t *p, uint64_t pol) {   // streamed once: keep it out of W1's way in L2
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+    return v;
+}
 template <int MT, int kSA, int kSB>
 __global__ void __cluster_dims__(4 * MT, 1, 1) __launch_bounds__(kThreadsL1S, 1)
 k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
@@ -326,114 +330,120 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         }
     } else {
         // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major.
-        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), a lane one 64-byte
-        // chunk of rows rl and rl + 4.  The registers are the landing zone of the HBM stream (128 bytes per lane, 64 KB
-        // per SM), so a buffer is re-issued the moment it has been converted; many light warps rather than few heavy
-        // ones because the loop is a chain of dependent conversions (measured: 8 warps sat in dependency stalls). =====
+        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), lane l the
+        // elements l and l + 32 of each.
+        // The registers are the landing zone of the HBM stream, and HBM needs ~100 KB per SM in flight (latency under
+        // load ~1.5 us x 53 GB/s per SM) -- more than the register file can hold as fp64.  An fp16 operand only needs the
+        // top 11 mantissa bits, which all sit in the HIGH word of a double: each lane loads just the high words (32-bit
+        // loads at an 8-byte stride; a warp instruction still consumes whole 32-byte sectors, so HBM and L2 traffic are
+        // unchanged), which doubles the bytes in flight per register and lets every warp keep TWO K blocks in flight.
+        // Operand value = RN_fp16(2^e * x with the low 32 mantissa bits cleared): at most 2^-20 relative before the
+        // rounding; nb200_kernels.cu's standalone conversion uses the same definition. =====
         const int cw = warp - kWarpCvt0;               // 0..15
         const int grp = cw >> 3, wq = cw & 7;
-        const int chunk = lane & 7;
-        const int rl = lane >> 3;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
-        const int row_in_tile = static_cast<int>(mt * 256 + c * 128 + nh * 64) + wq * 8 + rl;
-        struct Cur { int si, kb, kb1, in; const double *p0; };   // valid while kb < kb1; in: bit h = row rl + 4h exists
+        const int row_in_tile = static_cast<int>(mt * 256 + c * 128 + nh * 64) + wq * 8;
+        const uint64_t pol = policy_evict_first();
+        struct Cur { int si, kb, kb1, row0; };   // valid while kb < kb1
         auto open = [&](Cur &u) {
             u.kb = 0; u.kb1 = 0;
             if (u.si >= g.max_seg) return;
             const Seg sg = my[u.si];
             if (sg.kb0 >= sg.kb1) return;
             u.kb = sg.kb0; u.kb1 = sg.kb1;
-            const int row0 = sg.tile * (256 * MT) + row_in_tile;
-            u.in = (row0 < g.rows_total ? 1 : 0) | (row0 + 4 < g.rows_total ? 2 : 0);
-            u.p0 = g.x + static_cast<long long>(u.in ? row0 : 0) * g.x_ld + chunk * 8;
+            u.row0 = sg.tile * (256 * MT) + row_in_tile;
         };
-        auto advance = [&](Cur &u) {
-            if (u.kb >= u.kb1) return;
-            if (++u.kb >= u.kb1) { u.si++; open(u); }
-        };
-        auto load_row = [&](const double *p, bool in, int kb, double (&v)[8]) {
-            const long long col = static_cast<long long>(kb) * kBK;
-            if (in && col + chunk * 8 + 8 <= g.cols) {
-                double a[4], b[4];
-                ldg256(p + col, a);
-                ldg256(p + col + 4, b);
+        auto advance2 = [&](Cur &u) {   // two K blocks on: this group's next item
 #pragma unroll
-                for (int e = 0; e < 4; e++) { v[e] = a[e]; v[4 + e] = b[e]; }
-            } else {
-#pragma unroll
-                for (int e = 0; e < 8; e++) v[e] = (in && col + chunk * 8 + e < g.cols) ? p[col + e] : 0.0;
+            for (int k = 0; k < 2; k++) {
+                if (u.kb >= u.kb1) return;
+                if (++u.kb >= u.kb1) { u.si++; open(u); }
             }
         };
-        auto issue = [&](const Cur &u, double (&v)[2][8]) {
+        auto issue = [&](const Cur &u, uint32_t (&v)[16]) {
             if (u.kb >= u.kb1) return;
-            load_row(u.p0, (u.in & 1) != 0, u.kb, v[0]);
-            load_row(u.p0 + 4 * g.x_ld, (u.in & 2) != 0, u.kb, v[1]);
+            const long long col = static_cast<long long>(u.kb) * kBK + lane;
+            const bool in0 = col < g.cols, in1 = col + 32 < g.cols;
+            const uint32_t *p = reinterpret_cast<const uint32_t *>(g.x + static_cast<long long>(u.row0) * g.x_ld + col) + 1;   // high word
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                const bool row_in = u.row0 + r < g.rows_total;
+                v[2 * r] = 0u; v[2 * r + 1] = 0u;
+                if (row_in && in0) v[2 * r] = ldg_hi(p, pol);
+                if (row_in && in1) v[2 * r + 1] = ldg_hi(p + 64, pol);
+                p += 2 * g.x_ld;
+            }
         };
-        Cur lc{0, 0, 0, 0, nullptr};
+        Cur lc{0, 0, 0, 0};
         open(lc);
-        if (grp == 1) advance(lc);
+        if (grp == 1) { if (lc.kb < lc.kb1 && ++lc.kb >= lc.kb1) { lc.si++; open(lc); } }
         Cur cc = lc;
-        double buf[2][8];
-        issue(lc, buf);
-        advance(lc); advance(lc);
+        uint32_t bufA[16], bufB[16];
+        issue(lc, bufA); advance2(lc);
+        issue(lc, bufB); advance2(lc);
         uint32_t it = grp;
         __half2 hmax = __floats2half2_rn(0.f, 0.f);   // running max |x * 2^e| (fp16 overflow check)
-        float ss[2] = {0.f, 0.f};
+        float ss[8];
+#pragma unroll
+        for (int r = 0; r < 8; r++) ss[r] = 0.f;
         bool ok = true;
         const long long t_loop0 = prof ? clock64() : 0;
-        while (cc.kb < cc.kb1 && ok) {
+        // byte offset of this lane's 4-byte store inside a 128-byte row, before the swizzle: even lanes write k = l, l + 1
+        // (from the neighbour), odd lanes k = l + 31, l + 32
+        const int kpair = (lane & 1) ? lane + 31 : lane;
+        const uint32_t sel = (lane & 1) ? 0x3276u : 0x5410u;   // PRMT: odd: (partner.hi, own.hi), even: (own.lo, partner.lo)
+        auto step = [&](uint32_t (&buf)[16]) {
             const uint32_t s = it % kSA, ph = (it / kSA) & 1;
             const long long tA = prof ? clock64() : 0;
-            uint32_t pk[2][4];
+            uint32_t pk[8];
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const float f0 = static_cast<float>(buf[h][2 * e]), f1 = static_cast<float>(buf[h][2 * e + 1]);
-                    ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
-                    const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
-                    hmax = __hmax2(hmax, __habs2(h2));
-                    pk[h][e] = *reinterpret_cast<const uint32_t *>(&h2);
-                }
+            for (int r = 0; r < 8; r++) {
+                const float f0 = hi_to_f32(buf[2 * r]), f1 = hi_to_f32(buf[2 * r + 1]);
+                ss[r] = fmaf(f0, f0, fmaf(f1, f1, ss[r]));
+                const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);   // (k = l, k = l + 32)
+                hmax = __hmax2(hmax, __habs2(h2));
+                const uint32_t w = *reinterpret_cast<const uint32_t *>(&h2);
+                const uint32_t wp = __shfl_xor_sync(0xffffffffu, w, 1);
+                pk[r] = (lane & 1) ? __byte_perm(wp, w, sel) : __byte_perm(w, wp, sel);
             }
             const long long tB = prof ? clock64() : 0;
-            issue(lc, buf);            // this group's next K block goes in flight before anything else happens
-            advance(lc); advance(lc);
+            issue(lc, buf);            // refill this buffer: the K block two of this group's items ahead
+            advance2(lc);
             const long long tC = prof ? clock64() : 0;
             if (prof) { t_acc2 += tB - tA; t_cvt_issue += tC - tB; }
             if (!L1S_TIMED(t_acc, mbar_wait_b(&a_empty[s], ph ^ 1))) {   // every lane polls: no broadcast needed
                 if (lane == 0) atomicExch(g.err_flag, 507);
                 ok = false;
-                break;
+                return;
             }
             const uint32_t atom = smem_u32(a_ring + s * kATile + nh * kXHalf + wq * 1024);   // rows [8wq, 8wq + 8) of my 64
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int ra = rl + 4 * h;
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + ra * 128 + ((chunk ^ ra) << 4)), "r"(pk[h][0]),
-                             "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
+            for (int r = 0; r < 8; r++)
+                asm volatile("st.shared.b32 [%0], %1;" ::"r"(atom + r * 128 + ((((kpair >> 3) ^ r) << 4) | ((kpair & 7) << 1))), "r"(pk[r])
                              : "memory");
-            }
             __syncwarp();
             if (lane == 0) mbar_arrive(&cdone_bar[s]);   // (release: the warp's stores are ordered before it)
-            const int si_before = cc.si;
-            advance(cc); advance(cc);
+            const int si_before = cc.si, row0_before = cc.row0;
+            advance2(cc);
             it += 2;
             if (cc.kb >= cc.kb1 || cc.si != si_before) {
-                // per-row sum of squares of the K blocks this group converted in that segment (8 chunk lanes per row)
+                // per-row sum of squares of the K blocks this group converted in that segment
                 if (g.row_sumsq != nullptr) {
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        float v = ss[h];
-                        v += __shfl_xor_sync(0xffffffffu, v, 1);
-                        v += __shfl_xor_sync(0xffffffffu, v, 2);
-                        v += __shfl_xor_sync(0xffffffffu, v, 4);
-                        const int row = my[si_before].tile * (256 * MT) + row_in_tile + 4 * h;
-                        if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
-                        ss[h] = 0.f;
+                    for (int r = 0; r < 8; r++) {
+                        float v = ss[r];
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                        if (lane == 0 && row0_before + r < g.rows_total) atomicAdd(g.row_sumsq + row0_before + r, v);
+                        ss[r] = 0.f;
                     }
                 }
             }
+        };
+        while (cc.kb < cc.kb1 && ok) {
+            step(bufA);
+            if (!(cc.kb < cc.kb1 && ok)) break;
+            step(bufB);
         }
         if (prof && lane == 0 && (warp == kWarpCvt0 || warp == kWarpCvt0 + 8)) prof[warp == kWarpCvt0 ? 6 : 8] = clock64() - t_loop0;
         // an fp16 infinity anywhere means the sampled scale let an input overflow: report +inf
@@ -609,8 +619,8 @@ int plan_l1_stream(int tiles, int num_kb, int G, L1StreamPlan *plan) {
 static_assert(sizeof(L1StreamSeg) == sizeof(Seg), "plan segments are handed to the kernel as they are");
 
 bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1) {
-    return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && (x_ld & 3) == 0 &&
-           (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
+    return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && x_ld >= cols &&
+           (reinterpret_cast<uintptr_t>(x) & 7) == 0 && cols >= 8 * kBK;
 }
 
 template <int MT, int SA, int SB>
