@@ -6,7 +6,6 @@
 //   * fp64 DFMA GEMM used for the exact path and for re-evaluating near-tie rows         (K9)
 //   * seeded generator, transposes, im2col (ImageToChunks.h:43-102), gather/scatter.
 #include "nb200_internal.h"
-#include "nb200_ptx.cuh"
 
 #include <cfloat>
 #include <cstdlib>
@@ -227,9 +226,7 @@ k_convert_f16(const T *__restrict__ src, long long ld, long long rows, long long
             __half h4[4];
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                // fp64 sources: the operand definition of nb200_ptx.cuh (hi_to_f32), shared with the streamed layer-1 kernel
-                const float f = sizeof(T) == 8 ? hi_to_f32(static_cast<uint32_t>(__double2hiint(static_cast<double>(v[h][j]))))
-                                               : static_cast<float>(v[h][j]);
+                const float f = static_cast<float>(v[h][j]);
                 const float sc = f * scale;  // exact (power of two) unless it overflows
                 h4[j] = __float2half_rn(sc);
                 ss += f * f;

@@ -55,9 +55,10 @@ constexpr uint32_t smem_total(int sa, int sb) { return sa * kATile + sb * kBTile
 constexpr int kWsLd = 1024;         // fp32 partial tiles: [slot][row][1024]
 
 struct Seg { int tile, kb0, kb1, slot; };
+__constant__ long long c_wait_limit = 1ll << 30;   // cycles a bounded wait may take (profilers replay kernels far slower)
 
 struct L1SArgs {
-    const double *x;        // [rows_total x cols] fp64, pitch x_ld
+    const double *x;        // [rows_total x cols] fp64, pitch x_ld (multiple of 4, base 32-byte aligned)
     long long x_ld;
     int rows_total, cols;
     const int *exp_x;       // fp16 scale exponent of X (device)
@@ -73,30 +74,39 @@ struct L1SArgs {
     unsigned long long *prof;   // experiments: per-CTA cycle counters [cta][16] (null = off)
 };
 
-__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t *bar, uint32_t parity) {
+// All shared-memory addresses in this kernel are 32-bit shared-window addresses computed once from one base: a generic
+// pointer would be converted again (S2UR + ULEA) wherever the compiler chose to rematerialise it, inside the hot loops.
+__device__ __forceinline__ bool try_wait_u(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ bool try_wait_cluster_u(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
-__device__ __forceinline__ bool mbar_wait_cluster(uint64_t *bar, uint32_t parity) {
-    if (mbar_try_wait_cluster(bar, parity)) return true;
+__device__ __forceinline__ bool wait_u(uint32_t bar, uint32_t parity) {  // bounded, CTA scope
+    if (try_wait_u(bar, parity)) return true;
     const long long t0 = clock64();
-    while (!mbar_try_wait_cluster(bar, parity)) {
-        if (clock64() - t0 > (1ll << 30)) return false;
+    while (!try_wait_u(bar, parity)) {
+        if (clock64() - t0 > c_wait_limit) return false;
     }
     return true;
 }
-__device__ __forceinline__ bool mbar_wait_b(uint64_t *bar, uint32_t parity) {  // bounded, CTA scope
-    if (mbar_try_wait(bar, parity)) return true;
+__device__ __forceinline__ bool wait_cluster_u(uint32_t bar, uint32_t parity) {  // bounded, cluster-scope acquire
+    if (try_wait_cluster_u(bar, parity)) return true;
     const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > (1ll << 30)) return false;
+    while (!try_wait_cluster_u(bar, parity)) {
+        if (clock64() - t0 > c_wait_limit) return false;
     }
     return true;
 }
@@ -105,48 +115,76 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t cta) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
     return r;
 }
-__device__ __forceinline__ void mbar_arrive_remote_release(uint64_t *bar, uint32_t cta) {
-    const uint32_t ra = mapa_u32(smem_u32(bar), cta);
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
+__device__ __forceinline__ void init_u(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-// bytes (a multiple of 16) from this CTA's shared memory to the same offset of CTA `dst_cta`; they complete on the
-// mbarrier at `bar`'s offset in CTA `bar_cta` (which may differ from the destination CTA)
-__device__ __forceinline__ void dsmem_bulk_copy2(void *dst_same_offset, const void *src, uint32_t bytes, uint64_t *bar,
-                                                 uint32_t dst_cta, uint32_t bar_cta) {
-    const uint32_t rd = mapa_u32(smem_u32(dst_same_offset), dst_cta);
-    const uint32_t rb = mapa_u32(smem_u32(bar), bar_cta);
+__device__ __forceinline__ void arrive_u(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void arrive_expect_tx_u(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void arrive_remote_u(uint32_t bar, uint32_t cta) {   // same offset in CTA `cta` (no fence emitted)
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(mapa_u32(bar, cta)) : "memory");
+}
+__device__ __forceinline__ void arrive_remote_release_u(uint32_t bar, uint32_t cta) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(mapa_u32(bar, cta)) : "memory");
+}
+// bytes (a multiple of 16) from this CTA's shared memory to the same offset of CTA `cta`; they complete on the mbarrier at
+// `bar`'s offset in THAT CTA (a barrier in a third CTA never sees them: measured)
+__device__ __forceinline__ void dsmem_bulk_copy_u(uint32_t addr, uint32_t bytes, uint32_t bar, uint32_t cta) {
     asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(rd), "r"(smem_u32(src)), "r"(bytes), "r"(rb)
+                 ::"r"(mapa_u32(addr, cta)), "r"(addr), "r"(bytes), "r"(mapa_u32(bar, cta))
                  : "memory");
 }
-__device__ __forceinline__ uint64_t policy_evict_first() {
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
+__device__ __forceinline__ void tma_w_2sm_u(const CUtensorMap *m, uint32_t bar, uint32_t dst, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+        "[%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "l"(kEvictLast)
+        : "memory");
 }
-__device__ __forceinline__ uint32_t ldg_hi(const uint32_t *p, uint64_t pol) {   // streamed once: keep it out of W1's way in L2
-    uint32_t v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
-    return v;
+__device__ __forceinline__ void tma_w_2sm_mc_u(const CUtensorMap *m, uint32_t bar, uint32_t dst, int c0, int c1, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint "
+        "[%0], [%1, {%3, %4}], [%2], %5, %6;"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "h"(mask), "l"(kEvictLast)
+        : "memory");
 }
-template <int MT, int kSA, int kSB>
+__device__ __forceinline__ void commit_2sm_u(uint32_t bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"(cta_mask) : "memory");
+}
+__device__ __forceinline__ void ldg256(const double *p, double (&v)[4]) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.f64 {%0, %1, %2, %3}, [%4];"
+                 : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+                 : "l"(p));
+}
+
+template <int MT, int kSA, int kSB, bool PROF>
 __global__ void __cluster_dims__(4 * MT, 1, 1) __launch_bounds__(kThreadsL1S, 1)
 k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t *a_ring = smem;                      // kSA x 16 KB: X tiles (fp16, 128B-swizzled K-major)
-    uint8_t *b_ring = smem + kSA * kATile;       // kSB x 32 KB: W1 tiles
-    uint64_t *a_full = reinterpret_cast<uint64_t *>(smem + kSA * kATile + kSB * kBTile);  // leader: both CTAs' A tiles of K block `it` complete
-    uint64_t *a_empty = a_full + kSA;     // every CTA: both pairs that share these X rows have consumed A slot s
-    uint64_t *xfull_bar = a_empty + kSA;  // every CTA: the partner's 64 rows have landed (the relay tells the leader)
-    uint64_t *cdone_bar = xfull_bar + kSA;  // every CTA: this CTA's converters have written their 64 rows
-    uint64_t *b_full = cdone_bar + kSA;   // leader: W1 tile landed in both CTAs
-    uint64_t *b_empty = b_full + kSB;     // every CTA: all pairs that share this W1 tile have consumed B slot s
-    uint64_t *tmem_full_bar = b_empty + kSB;
-    uint64_t *tmem_empty_bar = tmem_full_bar + 1;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty_bar + 1);
+    uint32_t sbase, tid;
+    asm volatile("mov.u32 %0, %1;" : "=r"(sbase) : "r"(smem_u32(smem)));   // opaque: never rematerialised
+    // the thread index, taken once THROUGH A SHUFFLE: ptxas rematerialises a plain read of %tid.x as an S2R wherever it is
+    // short of registers, and inside the hot loops an S2R queues behind the loads in flight (measured: a third of the
+    // converters' time)
+    asm volatile("{\n\t.reg .u32 t, l;\n\tmov.u32 t, %%tid.x;\n\tmov.u32 l, %%laneid;\n\tshfl.sync.idx.b32 %0, t, l, 0x1f, 0xffffffff;\n\t}" : "=r"(tid));
+    const uint32_t a_ring = sbase;                      // kSA x 16 KB: X tiles (fp16, 128B-swizzled K-major)
+    const uint32_t b_ring = sbase + kSA * kATile;       // kSB x 32 KB: W1 tiles
+    const uint32_t a_full = sbase + kSA * kATile + kSB * kBTile;  // leader: both CTAs' A tiles of K block `it` complete
+    const uint32_t a_empty = a_full + 8 * kSA;    // every CTA: both pairs that share these X rows have consumed A slot s
+    const uint32_t xfull_bar = a_empty + 8 * kSA; // every CTA: the partner's 64 rows have landed (the relay tells the leader)
+    const uint32_t cdone_bar = xfull_bar + 8 * kSA;  // every CTA: this CTA's converters have written their 64 rows
+    const uint32_t b_full = cdone_bar + 8 * kSA;  // leader: W1 tile landed in both CTAs
+    const uint32_t b_empty = b_full + 8 * kSB;    // every CTA: all pairs that share this W1 tile have consumed B slot s
+    const uint32_t tmem_full_bar = b_empty + 8 * kSB;
+    const uint32_t tmem_empty_bar = tmem_full_bar + 8;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + kSA * kATile + kSB * kBTile + (4 * kSA + 2 * kSB + 2) * 8);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = static_cast<int>(tid >> 5), lane = static_cast<int>(tid & 31);
     const uint32_t crank = cluster_ctarank();
     const uint32_t c = crank & 1, nh = (crank >> 1) & 1, mt = crank >> 2;
     const uint32_t leader_rank = crank & ~1u;
@@ -155,25 +193,25 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     const Seg *my = g.sched + static_cast<long long>(cluster_id) * g.max_seg;
     // cycle accounting (experiments): slot 0 producer b_empty, 1 mma b_full, 2 mma a_full, 3 relay xfull, 4 manager cdone,
     // 5 converter warp 0 a_empty, 6 converter warp 0 total, 7 converter warp 8 a_empty, 8 converter warp 8 total, 9 mma total
-    unsigned long long *prof = g.prof ? g.prof + static_cast<long long>(blockIdx.x) * 16 : nullptr;
+    unsigned long long *const prof = PROF ? g.prof + static_cast<long long>(blockIdx.x) * 16 : nullptr;
     unsigned long long t_acc = 0, t_acc2 = 0, t_cvt_issue = 0;
-#define L1S_TIMED(acc, expr) [&]() { const long long _t0 = prof ? clock64() : 0; const bool _r = (expr); if (prof) acc += clock64() - _t0; return _r; }()
+#define L1S_TIMED(acc, expr) [&]() { const long long _t0 = PROF ? clock64() : 0; const bool _r = (expr); if (PROF) acc += clock64() - _t0; return _r; }()
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < kSA; s++) {
             // per K block: the manager of each CTA of the pair (own 64 rows in place) and its relay (partner's 64 rows)
-            mbar_init(&a_full[s], (g.debug & 4) ? 2 : 4);
-            mbar_init(&a_empty[s], 2);          // the pairs (mt, 0) and (mt, 1)
-            mbar_init(&xfull_bar[s], 1);
-            mbar_init(&cdone_bar[s], kCvtWarps / 2);   // the 8 converter warps that take this K block
+            init_u(a_full + 8 * s, (g.debug & 4) ? 2 : 4);
+            init_u(a_empty + 8 * s, 2);          // the pairs (mt, 0) and (mt, 1)
+            init_u(xfull_bar + 8 * s, 1);
+            init_u(cdone_bar + 8 * s, kCvtWarps / 2);   // the 8 converter warps that take this K block
         }
         for (int s = 0; s < kSB; s++) {
-            mbar_init(&b_full[s], 2);           // leader's expect_tx arrive + the peer producer
-            mbar_init(&b_empty[s], MT);         // the pairs (0, nh) .. (MT - 1, nh)
+            init_u(b_full + 8 * s, 2);           // leader's expect_tx arrive + the peer producer
+            init_u(b_empty + 8 * s, MT);         // the pairs (0, nh) .. (MT - 1, nh)
         }
-        mbar_init(tmem_full_bar, 1);
-        mbar_init(tmem_empty_bar, 8);           // 4 epilogue warps of each CTA of the pair
+        init_u(tmem_full_bar, 1);
+        init_u(tmem_empty_bar, 8);           // 4 epilogue warps of each CTA of the pair
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -195,17 +233,16 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kSB, ph = (it / kSB) & 1;
-                    if (!L1S_TIMED(t_acc, mbar_wait_b(&b_empty[s], ph ^ 1))) { atomicExch(g.err_flag, 501); ok = false; break; }
-                    uint8_t *sb = b_ring + s * kBTile;
-                    if (leader) mbar_arrive_expect_tx(&b_full[s], 2 * kBTile);
-                    else mbar_arrive_remote(&b_full[s], leader_rank);
+                    if (!L1S_TIMED(t_acc, wait_u(b_empty + 8 * s, ph ^ 1))) { atomicExch(g.err_flag, 501); ok = false; break; }
+                    const uint32_t sb = b_ring + s * kBTile;
+                    if (leader) arrive_expect_tx_u(b_full + 8 * s, 2 * kBTile);
+                    else arrive_remote_u(b_full + 8 * s, leader_rank);
                     const int wrow = static_cast<int>(nh) * 512 + static_cast<int>(c) * 256;
                     if (MT == 1) {
-                        tma_load_2d_2sm(&map_w, &b_full[s], sb, kb * kBK, wrow, kEvictLast);  // box of 256 rows
+                        tma_w_2sm_u(&map_w, b_full + 8 * s, sb, kb * kBK, wrow);  // box of 256 rows
                     } else {
                         const uint16_t mask = static_cast<uint16_t>((1u << crank) | (1u << (crank ^ 4u)));
-                        tma_load_2d_2sm_mc(&map_w, &b_full[s], sb + mt * (128 * kBK * 2), kb * kBK,
-                                           wrow + static_cast<int>(mt) * 128, mask, kEvictLast);  // box of 128 rows
+                        tma_w_2sm_mc_u(&map_w, b_full + 8 * s, sb + mt * (128 * kBK * 2), kb * kBK, wrow + static_cast<int>(mt) * 128, mask);  // box of 128 rows
                     }
                 }
             }
@@ -213,7 +250,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
     } else if (warp == 1) {
         // ===== MMA issuer: one thread of each pair's leader =====
         if (leader && lane == 0) {
-            const long long t_mma0 = prof ? clock64() : 0;
+            const long long t_mma0 = PROF ? clock64() : 0;
             uint32_t it = 0;
             bool ok = true;
             // who shares my X rows (same mt) and who shares my W1 tile (same nh)
@@ -223,17 +260,17 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 const Seg sg = my[si];
                 if (sg.kb0 >= sg.kb1) break;
                 if (si > 0) {  // the epilogue of the previous segment must have drained TMEM
-                    if (!mbar_wait_cluster(tmem_empty_bar, (si - 1) & 1)) { atomicExch(g.err_flag, 502); ok = false; break; }
+                    if (!wait_cluster_u(tmem_empty_bar, (si - 1) & 1)) { atomicExch(g.err_flag, 502); ok = false; break; }
                     tc_fence_after();
                 }
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t sa_i = it % kSA, pha = (it / kSA) & 1, sb_i = it % kSB, phb = (it / kSB) & 1;
-                    if (!L1S_TIMED(t_acc, mbar_wait_cluster(&b_full[sb_i], phb))) { atomicExch(g.err_flag, 503); ok = false; break; }
-                    if (!L1S_TIMED(t_acc2, mbar_wait_cluster(&a_full[sa_i], pha))) { atomicExch(g.err_flag, 508); ok = false; break; }
+                    if (!L1S_TIMED(t_acc, wait_cluster_u(b_full + 8 * sb_i, phb))) { atomicExch(g.err_flag, 503); ok = false; break; }
+                    if (!L1S_TIMED(t_acc2, wait_cluster_u(a_full + 8 * sa_i, pha))) { atomicExch(g.err_flag, 508); ok = false; break; }
                     tc_fence_after();
                     if (!(g.debug & 2)) {
-                        const uint32_t sa = smem_u32(a_ring + sa_i * kATile);
-                        const uint32_t sb = smem_u32(b_ring + sb_i * kBTile);
+                        const uint32_t sa = a_ring + sa_i * kATile;
+                        const uint32_t sb = b_ring + sb_i * kBTile;
                         const uint64_t da = umma_desc_k_sw128(sa);
 #pragma unroll
                         for (int k = 0; k < kBK / kUK; k++) {
@@ -245,12 +282,12 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                             }
                         }
                     }
-                    umma_commit_2sm(&b_empty[sb_i], mask_b);
-                    umma_commit_2sm(&a_empty[sa_i], mask_a);
+                    commit_2sm_u(b_empty + 8 * sb_i, mask_b);
+                    commit_2sm_u(a_empty + 8 * sa_i, mask_a);
                 }
-                if (ok) umma_commit_2sm(tmem_full_bar, static_cast<uint16_t>(0x3u << leader_rank));
+                if (ok) commit_2sm_u(tmem_full_bar, static_cast<uint16_t>(0x3u << leader_rank));
             }
-            if (prof) prof[9] = clock64() - t_mma0;
+            if (PROF) prof[9] = clock64() - t_mma0;
         }
     } else if (warp < 6) {
         // ===== epilogue: TMEM -> fp32 partial tile in the workspace =====
@@ -259,7 +296,7 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         for (int si = 0; si < g.max_seg && ok; si++) {
             const Seg sg = my[si];
             if (sg.kb0 >= sg.kb1) break;
-            ok = mbar_wait_b(tmem_full_bar, si & 1);
+            ok = wait_u(tmem_full_bar, si & 1);
             if (!ok && lane == 0) atomicExch(g.err_flag, 504);
             ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
             if (!ok) break;
@@ -282,8 +319,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                if (leader) mbar_arrive(tmem_empty_bar);
-                else mbar_arrive_remote_release(tmem_empty_bar, leader_rank);
+                if (leader) arrive_u(tmem_empty_bar);
+                else arrive_remote_release_u(tmem_empty_bar, leader_rank);
             }
         }
     } else if (warp == 6) {
@@ -298,10 +335,10 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kSA, ph = (it / kSA) & 1;
-                    mbar_arrive_expect_tx(&xfull_bar[s], kXHalf);
-                    if (!L1S_TIMED(t_acc, mbar_wait_cluster(&xfull_bar[s], ph))) { atomicExch(g.err_flag, 506); ok = false; break; }
-                    if (leader) mbar_arrive(&a_full[s]);
-                    else mbar_arrive_remote(&a_full[s], leader_rank);
+                    arrive_expect_tx_u(xfull_bar + 8 * s, kXHalf);
+                    if (!L1S_TIMED(t_acc, wait_cluster_u(xfull_bar + 8 * s, ph))) { atomicExch(g.err_flag, 506); ok = false; break; }
+                    if (leader) arrive_u(a_full + 8 * s);
+                    else arrive_remote_u(a_full + 8 * s, leader_rank);
                 }
             }
         }
@@ -319,140 +356,133 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 if (sg.kb0 >= sg.kb1) break;
                 for (int kb = sg.kb0; kb < sg.kb1; kb++, it++) {
                     const uint32_t s = it % kSA, ph = (it / kSA) & 1;
-                    if (!L1S_TIMED(t_acc, mbar_wait_b(&cdone_bar[s], ph))) { atomicExch(g.err_flag, 505); ok = false; break; }
+                    if (!L1S_TIMED(t_acc, wait_u(cdone_bar + 8 * s, ph))) { atomicExch(g.err_flag, 505); ok = false; break; }
                     if (!(g.debug & 8)) fence_proxy_async_smem();
-                    uint8_t *mine = a_ring + s * kATile + nh * kXHalf;
-                    if (!(g.debug & 4)) dsmem_bulk_copy2(mine, mine, kXHalf, &xfull_bar[s], partner, partner);
-                    if (leader) mbar_arrive(&a_full[s]);
-                    else mbar_arrive_remote(&a_full[s], leader_rank);
+                    if (!(g.debug & 4)) dsmem_bulk_copy_u(a_ring + s * kATile + nh * kXHalf, kXHalf, xfull_bar + 8 * s, partner);
+                    if (leader) arrive_u(a_full + 8 * s);
+                    else arrive_remote_u(a_full + 8 * s, leader_rank);
                 }
             }
         }
     } else {
         // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major.
-        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), lane l the
-        // elements l and l + 32 of each.
-        // The registers are the landing zone of the HBM stream, and HBM needs ~100 KB per SM in flight (latency under
-        // load ~1.5 us x 53 GB/s per SM) -- more than the register file can hold as fp64.  An fp16 operand only needs the
-        // top 11 mantissa bits, which all sit in the HIGH word of a double: each lane loads just the high words (32-bit
-        // loads at an 8-byte stride; a warp instruction still consumes whole 32-byte sectors, so HBM and L2 traffic are
-        // unchanged), which doubles the bytes in flight per register and lets every warp keep TWO K blocks in flight.
-        // Operand value = RN_fp16(2^e * x with the low 32 mantissa bits cleared): at most 2^-20 relative before the
-        // rounding; nb200_kernels.cu's standalone conversion uses the same definition. =====
+        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), a lane one 64-byte
+        // chunk of rows rl and rl + 4.  The registers are the landing zone of the HBM stream (128 bytes per lane, 64 KB
+        // per SM), so a buffer is re-issued the moment it has been converted; many light warps rather than few heavy
+        // ones because the loop is a chain of dependent conversions (measured: 8 warps sat in dependency stalls). =====
         const int cw = warp - kWarpCvt0;               // 0..15
         const int grp = cw >> 3, wq = cw & 7;
+        const int chunk = lane & 7;
+        const int rl = lane >> 3;
         const float scale = exp2f(static_cast<float>(*g.exp_x));
-        const int row_in_tile = static_cast<int>(mt * 256 + c * 128 + nh * 64) + wq * 8;
-        const uint64_t pol = policy_evict_first();
-        struct Cur { int si, kb, kb1, row0; };   // valid while kb < kb1
+        const int row_in_tile = static_cast<int>(mt * 256 + c * 128 + nh * 64) + wq * 8 + rl;
+        struct Cur { int si, kb, kb1, in; const double *p0; };   // valid while kb < kb1; in: bit h = row rl + 4h exists
         auto open = [&](Cur &u) {
             u.kb = 0; u.kb1 = 0;
             if (u.si >= g.max_seg) return;
             const Seg sg = my[u.si];
             if (sg.kb0 >= sg.kb1) return;
             u.kb = sg.kb0; u.kb1 = sg.kb1;
-            u.row0 = sg.tile * (256 * MT) + row_in_tile;
+            const int row0 = sg.tile * (256 * MT) + row_in_tile;
+            u.in = (row0 < g.rows_total ? 1 : 0) | (row0 + 4 < g.rows_total ? 2 : 0);
+            u.p0 = g.x + static_cast<long long>(u.in ? row0 : 0) * g.x_ld + chunk * 8;
         };
-        auto advance2 = [&](Cur &u) {   // two K blocks on: this group's next item
-#pragma unroll
-            for (int k = 0; k < 2; k++) {
-                if (u.kb >= u.kb1) return;
-                if (++u.kb >= u.kb1) { u.si++; open(u); }
-            }
-        };
-        auto issue = [&](const Cur &u, uint32_t (&v)[16]) {
+        auto advance = [&](Cur &u) {
             if (u.kb >= u.kb1) return;
-            const long long col = static_cast<long long>(u.kb) * kBK + lane;
-            const bool in0 = col < g.cols, in1 = col + 32 < g.cols;
-            const uint32_t *p = reinterpret_cast<const uint32_t *>(g.x + static_cast<long long>(u.row0) * g.x_ld + col) + 1;   // high word
+            if (++u.kb >= u.kb1) { u.si++; open(u); }
+        };
+        auto load_row = [&](const double *p, bool in, int kb, double (&v)[8]) {
+            const long long col = static_cast<long long>(kb) * kBK;
+            if (in && col + chunk * 8 + 8 <= g.cols) {
+                double a[4], b[4];
+                ldg256(p + col, a);
+                ldg256(p + col + 4, b);
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const bool row_in = u.row0 + r < g.rows_total;
-                v[2 * r] = 0u; v[2 * r + 1] = 0u;
-                if (row_in && in0) v[2 * r] = ldg_hi(p, pol);
-                if (row_in && in1) v[2 * r + 1] = ldg_hi(p + 64, pol);
-                p += 2 * g.x_ld;
+                for (int e = 0; e < 4; e++) { v[e] = a[e]; v[4 + e] = b[e]; }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; e++) v[e] = (in && col + chunk * 8 + e < g.cols) ? p[col + e] : 0.0;
             }
         };
-        Cur lc{0, 0, 0, 0};
+        auto issue = [&](const Cur &u, double (&v)[2][8]) {
+            if (u.kb >= u.kb1) return;
+            load_row(u.p0, (u.in & 1) != 0, u.kb, v[0]);
+            load_row(u.p0 + 4 * g.x_ld, (u.in & 2) != 0, u.kb, v[1]);
+        };
+        Cur lc{0, 0, 0, 0, nullptr};
         open(lc);
-        if (grp == 1) { if (lc.kb < lc.kb1 && ++lc.kb >= lc.kb1) { lc.si++; open(lc); } }
+        if (grp == 1) advance(lc);
         Cur cc = lc;
-        uint32_t bufA[16], bufB[16];
-        issue(lc, bufA); advance2(lc);
-        issue(lc, bufB); advance2(lc);
+        double buf[2][8];
+        issue(lc, buf);
+        advance(lc); advance(lc);
         uint32_t it = grp;
         __half2 hmax = __floats2half2_rn(0.f, 0.f);   // running max |x * 2^e| (fp16 overflow check)
-        float ss[8];
-#pragma unroll
-        for (int r = 0; r < 8; r++) ss[r] = 0.f;
+        float ss[2] = {0.f, 0.f};
         bool ok = true;
-        const long long t_loop0 = prof ? clock64() : 0;
-        // byte offset of this lane's 4-byte store inside a 128-byte row, before the swizzle: even lanes write k = l, l + 1
-        // (from the neighbour), odd lanes k = l + 31, l + 32
-        const int kpair = (lane & 1) ? lane + 31 : lane;
-        const uint32_t sel = (lane & 1) ? 0x3276u : 0x5410u;   // PRMT: odd: (partner.hi, own.hi), even: (own.lo, partner.lo)
-        auto step = [&](uint32_t (&buf)[16]) {
+        const long long t_loop0 = PROF ? clock64() : 0;
+        while (cc.kb < cc.kb1 && ok) {
             const uint32_t s = it % kSA, ph = (it / kSA) & 1;
-            const long long tA = prof ? clock64() : 0;
-            uint32_t pk[8];
+            const long long tA = PROF ? clock64() : 0;
+            uint32_t pk[2][4];
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const float f0 = hi_to_f32(buf[2 * r]), f1 = hi_to_f32(buf[2 * r + 1]);
-                ss[r] = fmaf(f0, f0, fmaf(f1, f1, ss[r]));
-                const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);   // (k = l, k = l + 32)
-                hmax = __hmax2(hmax, __habs2(h2));
-                const uint32_t w = *reinterpret_cast<const uint32_t *>(&h2);
-                const uint32_t wp = __shfl_xor_sync(0xffffffffu, w, 1);
-                pk[r] = (lane & 1) ? __byte_perm(wp, w, sel) : __byte_perm(w, wp, sel);
+            for (int h = 0; h < 2; h++) {
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float f0 = static_cast<float>(buf[h][2 * e]), f1 = static_cast<float>(buf[h][2 * e + 1]);
+                    ss[h] = fmaf(f0, f0, fmaf(f1, f1, ss[h]));
+                    const __half2 h2 = __floats2half2_rn(f0 * scale, f1 * scale);
+                    hmax = __hmax2(hmax, __habs2(h2));
+                    pk[h][e] = *reinterpret_cast<const uint32_t *>(&h2);
+                }
             }
-            const long long tB = prof ? clock64() : 0;
-            issue(lc, buf);            // refill this buffer: the K block two of this group's items ahead
-            advance2(lc);
-            const long long tC = prof ? clock64() : 0;
-            if (prof) { t_acc2 += tB - tA; t_cvt_issue += tC - tB; }
-            if (!L1S_TIMED(t_acc, mbar_wait_b(&a_empty[s], ph ^ 1))) {   // every lane polls: no broadcast needed
+            const long long tB = PROF ? clock64() : 0;
+            issue(lc, buf);            // this group's next K block goes in flight before anything else happens
+            advance(lc); advance(lc);
+            const long long tC = PROF ? clock64() : 0;
+            if (PROF) { t_acc2 += tB - tA; t_cvt_issue += tC - tB; }
+            if (!L1S_TIMED(t_acc, wait_u(a_empty + 8 * s, ph ^ 1))) {   // every lane polls: no broadcast needed
                 if (lane == 0) atomicExch(g.err_flag, 507);
                 ok = false;
-                return;
+                break;
             }
-            const uint32_t atom = smem_u32(a_ring + s * kATile + nh * kXHalf + wq * 1024);   // rows [8wq, 8wq + 8) of my 64
+            const uint32_t atom = a_ring + s * kATile + nh * kXHalf + wq * 1024;   // rows [8wq, 8wq + 8) of my 64
 #pragma unroll
-            for (int r = 0; r < 8; r++)
-                asm volatile("st.shared.b32 [%0], %1;" ::"r"(atom + r * 128 + ((((kpair >> 3) ^ r) << 4) | ((kpair & 7) << 1))), "r"(pk[r])
+            for (int h = 0; h < 2; h++) {
+                const int ra = rl + 4 * h;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + ra * 128 + ((chunk ^ ra) << 4)), "r"(pk[h][0]),
+                             "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
                              : "memory");
+            }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&cdone_bar[s]);   // (release: the warp's stores are ordered before it)
-            const int si_before = cc.si, row0_before = cc.row0;
-            advance2(cc);
+            if (lane == 0) arrive_u(cdone_bar + 8 * s);   // (release: the warp's stores are ordered before it)
+            const int si_before = cc.si;
+            advance(cc); advance(cc);
             it += 2;
             if (cc.kb >= cc.kb1 || cc.si != si_before) {
-                // per-row sum of squares of the K blocks this group converted in that segment
+                // per-row sum of squares of the K blocks this group converted in that segment (8 chunk lanes per row)
                 if (g.row_sumsq != nullptr) {
 #pragma unroll
-                    for (int r = 0; r < 8; r++) {
-                        float v = ss[r];
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                        if (lane == 0 && row0_before + r < g.rows_total) atomicAdd(g.row_sumsq + row0_before + r, v);
-                        ss[r] = 0.f;
+                    for (int h = 0; h < 2; h++) {
+                        float v = ss[h];
+                        v += __shfl_xor_sync(0xffffffffu, v, 1);
+                        v += __shfl_xor_sync(0xffffffffu, v, 2);
+                        v += __shfl_xor_sync(0xffffffffu, v, 4);
+                        const int row = my[si_before].tile * (256 * MT) + row_in_tile + 4 * h;
+                        if (chunk == 0 && row < g.rows_total) atomicAdd(g.row_sumsq + row, v);
+                        ss[h] = 0.f;
                     }
                 }
             }
-        };
-        while (cc.kb < cc.kb1 && ok) {
-            step(bufA);
-            if (!(cc.kb < cc.kb1 && ok)) break;
-            step(bufB);
         }
-        if (prof && lane == 0 && (warp == kWarpCvt0 || warp == kWarpCvt0 + 8)) prof[warp == kWarpCvt0 ? 6 : 8] = clock64() - t_loop0;
+        if (PROF && lane == 0 && (warp == kWarpCvt0 || warp == kWarpCvt0 + 8)) prof[warp == kWarpCvt0 ? 6 : 8] = clock64() - t_loop0;
         // an fp16 infinity anywhere means the sampled scale let an input overflow: report +inf
         const uint32_t hm = *reinterpret_cast<const uint32_t *>(&hmax);
         const bool ovf = (hm & 0x7FFFu) >= 0x7C00u || ((hm >> 16) & 0x7FFFu) >= 0x7C00u;
         if (__any_sync(0xffffffffu, ovf) && lane == 0 && g.maxscaled != nullptr)
             atomicMax(reinterpret_cast<unsigned int *>(g.maxscaled), 0x7F800000u);
     }
-    if (prof && lane == 0) {
+    if (PROF && lane == 0) {
         if (warp == 0) prof[0] = t_acc;
         if (warp == 1) { prof[1] = t_acc; prof[2] = t_acc2; }
         if (warp == 6) prof[3] = t_acc;
@@ -540,9 +570,10 @@ int make_w_map(CUtensorMap *m, const void *base, int64_t rows, int64_t ldk, int 
 
 template <int MT, int SA, int SB>
 int max_clusters(int *out) {
+    constexpr bool PROF = false;
     static int cached = -1;
     if (cached < 0) {
-        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
+        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(4 * MT * 64);
         cfg.blockDim = dim3(kThreadsL1S);
@@ -553,7 +584,7 @@ int max_clusters(int *out) {
         cfg.attrs = &at;
         cfg.numAttrs = 1;
         int n = 0;
-        NB_CUDA(cudaOccupancyMaxActiveClusters(&n, k_l1_stream<MT, SA, SB>, &cfg));
+        NB_CUDA(cudaOccupancyMaxActiveClusters(&n, k_l1_stream<MT, SA, SB, PROF>, &cfg));
         cached = n;
     }
     *out = cached;
@@ -619,8 +650,8 @@ int plan_l1_stream(int tiles, int num_kb, int G, L1StreamPlan *plan) {
 static_assert(sizeof(L1StreamSeg) == sizeof(Seg), "plan segments are handed to the kernel as they are");
 
 bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1) {
-    return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && x_ld >= cols &&
-           (reinterpret_cast<uintptr_t>(x) & 7) == 0 && cols >= 8 * kBK;
+    return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && (x_ld & 3) == 0 &&
+           (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
 }
 
 template <int MT, int SA, int SB>
@@ -666,6 +697,14 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
     g.debug = debug;
+    static bool limit_set = false;
+    if (!limit_set) {
+        limit_set = true;
+        if (const char *e = getenv("NB200_WAIT_LOG2")) {
+            const long long lim = 1ll << atoi(e);
+            NB_CUDA(cudaMemcpyToSymbol(c_wait_limit, &lim, sizeof(lim)));
+        }
+    }
     static unsigned long long *prof_dev = nullptr;
     static const bool prof_on = getenv("NB200_L1S_PROF") != nullptr;
     const int nctas = sc->plan.clusters * 4 * MT;
@@ -674,7 +713,13 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     g.prof = prof_on ? prof_dev : nullptr;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
-    k_l1_stream<MT, SA, SB><<<sc->plan.clusters * 4 * MT, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
+    if (prof_on) {
+        static bool attr = false;
+        if (!attr) { NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB))); attr = true; }
+        k_l1_stream<MT, SA, SB, true><<<nctas, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
+    } else {
+        k_l1_stream<MT, SA, SB, false><<<nctas, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
+    }
     c->launches++;
     NB_CUDA(cudaGetLastError());
     if (prof_on) {   // experiments only: synchronises
@@ -703,11 +748,6 @@ int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int co
         // MT = 2 halves the W1 traffic but works in 512-row tiles: take it unless its padding costs more than that
         const int64_t pad1 = ceil_div(rows, 256) * 256, pad2 = ceil_div(rows, 512) * 512;
         mt = (pad2 * 10 <= pad1 * 12) ? 2 : 1;
-    }
-    static const int ring_env = getenv("NB200_L1S_RING") ? atoi(getenv("NB200_L1S_RING")) : 64;   // SA * 10 + SB
-    if (ring_env == 45) {
-        if (mt == 2) return launch_l1_stream_impl<2, 4, 5>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
-        return launch_l1_stream_impl<1, 4, 5>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
     }
     if (mt == 2) return launch_l1_stream_impl<2, 6, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
     return launch_l1_stream_impl<1, 6, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);

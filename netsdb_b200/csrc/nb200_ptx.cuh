@@ -200,20 +200,6 @@ __device__ __forceinline__ void umma_commit_2sm(uint64_t *bar, uint16_t cta_mask
         : "memory");
 }
 
-// ---- fp64 -> fp16 operand definition ------------------------------------------------------------
-// An fp16 operand keeps 11 mantissa bits; they all sit in the HIGH word of a double.  Every conversion of fp64 data to
-// the fp16 operand format goes through this function, so the streamed layer-1 kernel (which loads only the high words,
-// nb200_l1stream.cu) and the standalone conversion produce identical planes: value = RN_fp16(2^e * x with the low 32
-// mantissa bits cleared), i.e. at most 2^-20 relative before the rounding.
-// the high word of a double -> the float with the same sign, exponent and top 20 mantissa bits (exact); magnitudes
-// below 2^-126 give +-0, above 2^127 (and inf / nan) +-inf
-__device__ __forceinline__ float hi_to_f32(uint32_t hi) {
-    const uint32_t a = hi & 0x7FFFFFFFu;
-    uint32_t t = (a << 3) - 0xC0000000u;           // (e11 - 896) << 23 | m20 << 3, modulo 2^32
-    t = a < (897u << 20) ? 0u : t;
-    t = a >= (1151u << 20) ? 0x7F800000u : t;
-    return __uint_as_float(t | (hi & 0x80000000u));
-}
 // ---- descriptors ----------------------------------------------------------------------------
 // Shared-memory matrix descriptor for a K-major bf16 tile laid out by TMA with SWIZZLE_128B:
 // rows of 128 bytes (64 bf16), 8-row groups 1024 bytes apart.  Fields (PTX ISA "matrix
