@@ -43,8 +43,10 @@ namespace {
 
 constexpr int kBK = 64;             // K block: 64 fp16 = one 128-byte swizzle row
 constexpr int kUK = 16;             // K of one tcgen05.mma kind::f16
-// shared-memory slots: SA for X tiles (chain: convert, DSMEM hand-off, relay), SB for W1 tiles (TMA out of L2: ~2 us from
-// slot free to tile landed); SA * 16 KB + SB * 32 KB = 224 KB
+// Shared-memory slots: SA for X tiles (chain: convert, DSMEM hand-off, relay), SB for W1 tiles (TMA out of L2: ~2 us from
+// slot free to tile landed).  4 + 4 slots = 192 KB and NOT more: what the CTA leaves of the SM's 228 KB is the L1, and the L1
+// is where the converters' global loads land.  Beyond a 196 KB carve-out nothing is left, and a CTA per SM then streams
+// this access pattern at 3.9 TB/s instead of 6.2 TB/s (tools/hbm_pattern_bench.cu, profiles/r02_hbm_pattern.txt).
 constexpr int kCvtWarps = 16;
 constexpr int kWarpCvt0 = 8;        // warps: 0 W1 producer, 1 MMA, 2..5 epilogue, 6 relay, 7 manager, 8.. converters
 constexpr int kThreadsL1S = (kWarpCvt0 + kCvtWarps) * 32;  // 768
@@ -437,8 +439,10 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 }
             }
             const long long tB = PROF ? clock64() : 0;
-            issue(lc, buf);            // this group's next K block goes in flight before anything else happens
-            advance(lc); advance(lc);
+            if (!(g.debug & 32)) {
+                issue(lc, buf);            // this group's next K block goes in flight before anything else happens
+                advance(lc); advance(lc);
+            }
             const long long tC = PROF ? clock64() : 0;
             if (PROF) { t_acc2 += tB - tA; t_cvt_issue += tC - tB; }
             if (!L1S_TIMED(t_acc, wait_u(a_empty + 8 * s, ph ^ 1))) {   // every lane polls: no broadcast needed
@@ -456,6 +460,10 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             }
             __syncwarp();
             if (lane == 0) arrive_u(cdone_bar + 8 * s);   // (release: the warp's stores are ordered before it)
+            if (g.debug & 32) {            // experiment: loads after the stores
+                issue(lc, buf);
+                advance(lc); advance(lc);
+            }
             const int si_before = cc.si;
             advance(cc); advance(cc);
             it += 2;
@@ -749,8 +757,8 @@ int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int co
         const int64_t pad1 = ceil_div(rows, 256) * 256, pad2 = ceil_div(rows, 512) * 512;
         mt = (pad2 * 10 <= pad1 * 12) ? 2 : 1;
     }
-    if (mt == 2) return launch_l1_stream_impl<2, 6, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
-    return launch_l1_stream_impl<1, 6, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    if (mt == 2) return launch_l1_stream_impl<2, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    return launch_l1_stream_impl<1, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
 }
 
 int launch_l1_stream_reduce(Context *c, const L1StreamScratch &sc, int rows, int N, const float *bias_n, int relu,

@@ -137,13 +137,14 @@ int main(int argc, char **argv) {
     cudaEvent_t a, b;
     cudaEventCreate(&a); cudaEventCreate(&b);
     const double gb = (double)rows * num_kb * 512 / 1e9;
-    const int pad = 160 * 1024;
+    const int pad = (argc > 2 ? atoi(argv[2]) : 160) * 1024;   // dynamic shared memory per CTA: what is left is the L1
+    const bool regs_only = argc > 3;
     CK(cudaFuncSetAttribute(k_regs<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pad));
     CK(cudaFuncSetAttribute(k_regs<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, pad));
     CK(cudaFuncSetAttribute(k_regs<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, pad));
     auto report = [&](const char *name, float ms) { printf("%-58s %7.3f ms  %6.0f GB/s\n", name, ms, gb / ms * 1e3); fflush(stdout); };
     for (int rpl : {2, 4, 8}) {
-        for (int mode = 0; mode < 4; mode++) {
+        for (int mode = 0; mode < (regs_only ? 1 : 4); mode++) {
             for (int pf : {8, 32}) {
                 if (mode == 0 && pf != 8) continue;
                 float best = 1e9;
@@ -163,6 +164,7 @@ int main(int argc, char **argv) {
             }
         }
     }
+    if (regs_only) return 0;
     // TMA
     void *fp = nullptr;
     cudaDriverEntryPointQueryResult q;
