@@ -368,10 +368,12 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
         }
     } else {
         // ===== converters: rows [64nh, 64nh + 64) of this CTA's 128, fp64 -> fp16, 128B-swizzled K-major.
-        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), a lane one 64-byte
-        // chunk of rows rl and rl + 4.  The registers are the landing zone of the HBM stream (128 bytes per lane, 64 KB
-        // per SM), so a buffer is re-issued the moment it has been converted; many light warps rather than few heavy
-        // ones because the loop is a chain of dependent conversions (measured: 8 warps sat in dependency stalls). =====
+        // Two groups of 8 warps take alternate K blocks; a warp owns 8 rows (one 1 KB swizzle atom), a lane the elements
+        // [4c, 4c + 4) and [32 + 4c, 32 + 4c + 4) of rows rl and rl + 4 (c = lane & 7): each warp-wide 256-bit load then
+        // covers 256 contiguous bytes of 4 rows -- 8 full lines, half the tag lookups of a 64-bytes-per-lane split.  The
+        // registers are the landing zone of the HBM stream (128 bytes per lane, 64 KB per SM), so a buffer is re-issued
+        // the moment it has been converted; many light warps rather than few heavy ones because the loop is a chain of
+        // dependent conversions (measured: 8 warps sat in dependency stalls). =====
         const int cw = warp - kWarpCvt0;               // 0..15
         const int grp = cw >> 3, wq = cw & 7;
         const int chunk = lane & 7;
@@ -387,23 +389,26 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
             u.kb = sg.kb0; u.kb1 = sg.kb1;
             const int row0 = sg.tile * (256 * MT) + row_in_tile;
             u.in = (row0 < g.rows_total ? 1 : 0) | (row0 + 4 < g.rows_total ? 2 : 0);
-            u.p0 = g.x + static_cast<long long>(u.in ? row0 : 0) * g.x_ld + chunk * 8;
+            u.p0 = g.x + static_cast<long long>(u.in ? row0 : 0) * g.x_ld + chunk * 4;
         };
         auto advance = [&](Cur &u) {
             if (u.kb >= u.kb1) return;
             if (++u.kb >= u.kb1) { u.si++; open(u); }
         };
-        auto load_row = [&](const double *p, bool in, int kb, double (&v)[8]) {
+        auto load_row = [&](const double *p, bool in, int kb, double (&v)[8]) {   // v[0..3]: k = 4c.., v[4..7]: k = 32 + 4c..
             const long long col = static_cast<long long>(kb) * kBK;
-            if (in && col + chunk * 8 + 8 <= g.cols) {
+            if (in && col + kBK <= g.cols) {
                 double a[4], b[4];
                 ldg256(p + col, a);
-                ldg256(p + col + 4, b);
+                ldg256(p + col + 32, b);
 #pragma unroll
                 for (int e = 0; e < 4; e++) { v[e] = a[e]; v[4 + e] = b[e]; }
             } else {
 #pragma unroll
-                for (int e = 0; e < 8; e++) v[e] = (in && col + chunk * 8 + e < g.cols) ? p[col + e] : 0.0;
+                for (int e = 0; e < 4; e++) {
+                    v[e] = (in && col + chunk * 4 + e < g.cols) ? p[col + e] : 0.0;
+                    v[4 + e] = (in && col + 32 + chunk * 4 + e < g.cols) ? p[col + 32 + e] : 0.0;
+                }
             }
         };
         auto issue = [&](const Cur &u, double (&v)[2][8]) {
@@ -439,10 +444,8 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
                 }
             }
             const long long tB = PROF ? clock64() : 0;
-            if (!(g.debug & 32)) {
-                issue(lc, buf);            // this group's next K block goes in flight before anything else happens
-                advance(lc); advance(lc);
-            }
+            issue(lc, buf);            // this group's next K block goes in flight before anything else happens
+            advance(lc); advance(lc);      // (measured: issuing after the stores instead costs 4 %)
             const long long tC = PROF ? clock64() : 0;
             if (PROF) { t_acc2 += tB - tA; t_cvt_issue += tC - tB; }
             if (!L1S_TIMED(t_acc, wait_u(a_empty + 8 * s, ph ^ 1))) {   // every lane polls: no broadcast needed
@@ -454,16 +457,13 @@ k_l1_stream(const __grid_constant__ CUtensorMap map_w, const L1SArgs g) {
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int ra = rl + 4 * h;
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + ra * 128 + ((chunk ^ ra) << 4)), "r"(pk[h][0]),
-                             "r"(pk[h][1]), "r"(pk[h][2]), "r"(pk[h][3])
-                             : "memory");
+                // k = 4c.. sits in 16-byte chunk c / 2 of the row, k = 32 + 4c.. in chunk 4 + c / 2 (128B swizzle: chunk ^ row)
+                const uint32_t row_addr = atom + ra * 128 + ((chunk & 1) << 3);
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(row_addr + (((chunk >> 1) ^ ra) << 4)), "r"(pk[h][0]), "r"(pk[h][1]) : "memory");
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(row_addr + ((((chunk >> 1) + 4) ^ ra) << 4)), "r"(pk[h][2]), "r"(pk[h][3]) : "memory");
             }
             __syncwarp();
             if (lane == 0) arrive_u(cdone_bar + 8 * s);   // (release: the warp's stores are ordered before it)
-            if (g.debug & 32) {            // experiment: loads after the stores
-                issue(lc, buf);
-                advance(lc); advance(lc);
-            }
             const int si_before = cc.si;
             advance(cc); advance(cc);
             it += 2;
