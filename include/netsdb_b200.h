@@ -103,8 +103,14 @@ int nb200_device_count(int *count);
 /* Launch everything on `cuda_stream` (a cudaStream_t) instead of the library's own stream. */
 int nb200_set_stream(void *cuda_stream);
 int nb200_synchronize(void);
-/* Tuning switches (process wide).  "fused_layer1" (default 1): run layer 1 of nb200_ff_inference_unit with the
- * kernel that converts the fp64 inputs to fp16 inside the persistent GEMM; 0 = separate conversion and GEMM kernels. */
+/* Tuning switches (process wide).
+ *  "fused_layer1": how layer 1 of nb200_ff_inference_unit(NB200_PREC_F16) runs on long feature vectors.  2 (default): the
+ *      cluster kernel that converts the fp64 inputs inside the CTAs that consume them and splits K in waves, so that any
+ *      number of rows (a row shard of 1,250 as well as 10,000) fills the device; 1: the round-1 kernel that passes the
+ *      converted inputs through a ring in L2 (whole 256-row tiles only); 0: separate conversion and GEMM kernels;
+ *      -1: back to the default.  Shapes a kernel does not cover fall through to the next one.
+ *  "l1_stream_mt": cluster shape of the default kernel, 1 (4 CTAs, 256 rows) or 2 (8 CTAs, 512 rows, W1 multicast); 0
+ *      (default) picks by the padding the row count would need. */
 int nb200_set_option(const char *key, int value);
 /* Number of kernels this library has launched since nb200_init (monotonic). */
 int64_t nb200_launch_count(void);

@@ -334,6 +334,7 @@ int64_t nb200_launch_count(void) { return g_ctx ? g_ctx->launches : 0; }
 
 int nb200_set_option(const char *key, int value) {
     if (key && !strcmp(key, "fused_layer1")) { g_opt_fused = value < 0 ? -1 : (value > 2 ? 2 : value); return NB200_OK; }
+    if (key && !strcmp(key, "l1_stream_mt")) { g_l1_stream_mt = (value == 1 || value == 2) ? value : 0; return NB200_OK; }
     set_error("set_option: unknown key");
     return NB200_ERR_INVALID;
 }

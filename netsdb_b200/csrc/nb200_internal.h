@@ -145,6 +145,7 @@ struct L1StreamScratch {
     int tile_rows = 0;
     long long slot_stride = 0;
 };
+extern int g_l1_stream_mt;
 int plan_l1_stream(int tiles, int num_kb, int clusters, L1StreamPlan *plan);
 bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1);
 int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,

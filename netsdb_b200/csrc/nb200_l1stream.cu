@@ -657,6 +657,8 @@ int plan_l1_stream(int tiles, int num_kb, int G, L1StreamPlan *plan) {
 
 static_assert(sizeof(L1StreamSeg) == sizeof(Seg), "plan segments are handed to the kernel as they are");
 
+int g_l1_stream_mt = 0;   // nb200_set_option("l1_stream_mt"): 0 = choose by padding, 1 / 2 = force the cluster shape
+
 bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1) {
     return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && (x_ld & 3) == 0 &&
            (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
@@ -750,6 +752,10 @@ int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int co
                      float *maxscaled, const Planes &w1, int N, L1StreamScratch *sc) {
     if (!l1_stream_supported(x, x_ld, cols, N, w1)) { set_error("l1 stream: shape not supported"); return NB200_ERR_STATE; }
     static const int mt_env = getenv("NB200_L1S_MT") ? atoi(getenv("NB200_L1S_MT")) : 0;
+    if (g_l1_stream_mt == 1 || g_l1_stream_mt == 2) {
+        if (g_l1_stream_mt == 2) return launch_l1_stream_impl<2, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, 0);
+        return launch_l1_stream_impl<1, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, 0);
+    }
     static const int debug = getenv("NB200_L1S_DEBUG") ? atoi(getenv("NB200_L1S_DEBUG")) : 0;
     int mt = mt_env;
     if (mt != 1 && mt != 2) {
