@@ -66,6 +66,90 @@ def test_amazon14k_full_size_properties(nb, oracle):
         s.destroy()
 
 
+def test_amazon14k_all_labels_against_the_cpu_oracle(nb, oracle):
+    """BASELINE config 2 in full against the ORACLE, not against the device's own fp64 path: all 10,000 labels of the F16
+    cascade (streamed layer 1, near-tie rows re-evaluated) equal the labels of oracle.ff_inference_unit -- the CPU
+    restatement of FFTransposeMult / FFAggMatrix / FFReluBiasSum / FFInputLayerJoin / FFTransposeBiasSum / FFRowAggregate
+    / FFOutputLayer (SimpleFF.cc:331-424) -- run in 1,000-row slabs on the host's threads from the same seeded blocks
+    (the device generator is bit-identical to the oracle's: test_generator_bit_exact), and the logits of a slab stay
+    inside the fp16 bound."""
+    batch, feat, hid, lab, blk = 10000, 597540, 1000, 14588, 1000
+    DS = nb.DeviceSet
+    w1 = DS.create("ff", "w1", hid, feat, blk, blk); w1.fill_synth(2)
+    b1 = DS.create("ff", "b1", hid, 1, blk, 1); b1.fill_synth(3)
+    wo = DS.create("ff", "wo", lab, hid, blk, blk); wo.fill_synth(4)
+    bo = DS.create("ff", "bo", lab, 1, blk, 1); bo.fill_synth(5)
+    x = DS.create("ff", "inputs", batch, feat, blk, blk); x.fill_synth(1)
+    _, labels, stats = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_F16)
+    assert stats["splits1"] >= 1
+    z_dev = nb.DeviceSet.lookup("ff", "__logits").download_block(7, 0, blk, lab)     # rows 7000..7999
+    threads = oracle.hw_threads()
+    W1 = oracle.load_matrix(w1.download_dense(), blk, blk)
+    B1 = oracle.load_matrix(b1.download_dense(), blk, 1)
+    WO = oracle.load_matrix(wo.download_dense(), blk, blk)
+    BO = oracle.load_matrix(bo.download_dense(), blk, 1)
+    slab = np.empty((blk, feat), dtype=np.float64)
+    ref = np.empty(batch, dtype=np.int32)
+    for i in range(batch // blk):
+        nb.check(nb.lib().nb200_download_rect(x.ptr, i * blk, 0, slab.ctypes.data, blk, feat, feat))
+        X = oracle.load_matrix(slab, blk, blk)
+        _, ref_logits, ref_labels = oracle.ff_inference_unit(W1, WO, X, B1, BO, threads=threads)
+        ref[i * blk:(i + 1) * blk] = ref_labels
+        if i == 7:
+            zr = ref_logits.dense()
+            assert np.abs(z_dev - zr).max() <= 2.5e-3 * np.abs(zr).max()
+    assert np.array_equal(labels, ref), f"{int((labels != ref).sum())} of {batch} labels differ from the CPU oracle"
+    for s in (w1, x):
+        s.destroy()
+
+
+def test_near_tie_band_on_100k_rows(nb, oracle):
+    """How safe is the near-tie filter?  102,400 synthetic rows (4,160 features, hidden 1,000, 600 labels): the RAW
+    single-pass fp16 labels (block GEMMs + softmax through the per-operator entry points: no cascade) against the fp64
+    labels.  Every row whose raw label is wrong must lie inside the band that the cascade re-evaluates
+    (gap < 4 eps_r, eps_r the norm-based estimate of DESIGN.md section 3, recomputed here in numpy from fp64 data), the
+    cascade's own labels must equal the fp64 labels on all rows, and the report says how close to the edge the flips come."""
+    batch, feat, hid, lab, blk = 102400, 4160, 1000, 600, 1040
+    DS = nb.DeviceSet
+    w1 = DS.create("band", "w1", hid, feat, blk, blk); w1.fill_synth(12)
+    b1 = DS.create("band", "b1", hid, 1, blk, 1); b1.fill_synth(13)
+    wo = DS.create("band", "wo", lab, hid, blk, blk); wo.fill_synth(14)
+    bo = DS.create("band", "bo", lab, 1, blk, 1); bo.fill_synth(15)
+    x = DS.create("band", "inputs", batch, feat, blk, blk); x.fill_synth(11)
+    # truth: the fp64 pipeline (oracle-checked at oracle sizes) -- logits and labels
+    _, lab64, _ = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_FP64, "band", "out64")
+    z = nb.DeviceSet.lookup("band", "__logits").download_dense()
+    assert np.array_equal(lab64, np.argmax(z, axis=1))
+    top2 = np.partition(z, lab - 2, axis=1)[:, lab - 2:]
+    gap = top2[:, 1] - top2[:, 0]
+    # the cascade
+    _, lab16, st = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_F16, "band", "out16")
+    assert np.array_equal(lab16, lab64), f"{int((lab16 != lab64).sum())} labels of the cascade differ from fp64"
+    # raw single-pass fp16 labels, operator by operator (FFTransposeMult+FFAggMatrix+FFReluBiasSum, FFInputLayerJoin+...+FFTransposeBiasSum)
+    y1 = nb.gemm_blocks(nb.OP_NT, w1, x, nb.EPI_BIAS_RELU, b1, nb.PREC_F16, "band", "y1")
+    zraw = nb.gemm_blocks(nb.OP_NN, wo, y1, nb.EPI_BIAS_TRANSPOSE, bo, nb.PREC_F16, "band", "zraw")
+    _, raw = nb.softmax_rows(zraw, "band", "praw")
+    # eps_r = u (|y1_r| max|wo| + |x_r| max|w1| max_l |wo_l|), u = 2^-11
+    X = x.download_dense()
+    xn = np.sqrt((X ** 2).sum(axis=1)); del X
+    W1 = w1.download_dense(); w1max = np.abs(W1).max(); del W1
+    WO = wo.download_dense(); womax = np.abs(WO).max(); wonorm = np.sqrt((WO ** 2).sum(axis=1)).max()
+    _, _, _ = nb.ff_inference_unit(w1, wo, x, b1, bo, nb.PREC_FP64, "band", "out64")   # y1 in fp64 = relu(z1): recompute its norms
+    Y1 = nb.gemm_blocks(nb.OP_NT, w1, x, nb.EPI_BIAS_RELU, b1, nb.PREC_FP64, "band", "y1f").download_dense()   # hidden x batch
+    yn = np.sqrt((Y1 ** 2).sum(axis=0)); del Y1
+    eps = 2.0 ** -11 * (yn * womax + xn * w1max * wonorm)
+    flipped = raw != lab64
+    ratio = gap / eps
+    n_band = int((ratio < 4).sum())
+    print(f"near-tie band: {int(flipped.sum())} raw fp16 labels of {batch} differ from fp64; {n_band} rows inside 4 eps "
+          f"(cascade re-ran {st['relevel_rows']}); flips with gap in [2,4) eps: {int((flipped & (ratio >= 2) & (ratio < 4)).sum())}; "
+          f"largest gap/eps among flips: {ratio[flipped].max() if flipped.any() else 0:.3f}")
+    assert not (flipped & (ratio >= 4)).any(), f"{int((flipped & (ratio >= 4)).sum())} wrong raw labels OUTSIDE the 4 eps band"
+    assert not (flipped & (ratio >= 2)).any() or ratio[flipped].max() < 4      # (the edge of the band is never reached)
+    for s_ in (w1, x):
+        s_.destroy()
+
+
 def test_word2vec_reference_shape(nb, oracle):
     """Word2Vec.cc:106-109: vocab 1,000,000, dim 500, batch 100 (the reference's own size), 1,000 x 1,000 blocks."""
     dim, vocab, batch, blk = 500, 1000000, 100, 1000
