@@ -1047,7 +1047,7 @@ static int tc_forward(Context *c, const Planes &X, int rows, int nterms, int fmt
         NB_TRY(launch_l1_stream_reduce(c, *pipe->stream, rows, H, b1, 1, pipe->planes->f16_exp, w1->rowp.f16_exp, *y1_f32, H, y1_max));
         pipe->planes->f16_valid = false;  // the fp16 plane of the inputs was never materialised
         fused_done = true;
-        fused_slots = pipe->stream->plan.max_slots;
+        fused_slots = pipe->stream->max_slots();
         k1 = nullptr;                     // recorded above: the kernel-only window excludes the reduction
     } else if (pipe && pipe->fused && f16 && pipe->is_f64) {
         // Fused layer 1: as many whole 256-row tiles as there are SM pairs go through the persistent kernel that
@@ -1199,7 +1199,7 @@ static void release_ff_scratch(void) {
     for (Planes *p : {&S.y1, &S.xsub, &S.y1sub}) free_planes(p);
     nb_free(S.logits); nb_free(S.labels); nb_free(S.gap); nb_free(S.list); nb_free(S.count); nb_free(S.xg); nb_free(S.y1g);
     nb_free(S.zg); nb_free(S.logits_sub); nb_free(S.list2); nb_free(S.y1_f32); nb_free(S.y1_max);
-    nb_free(S.fused.ring); nb_free(S.fused.flags); nb_free(S.l1s.dev);
+    nb_free(S.fused.ring); nb_free(S.fused.flags); nb_free(S.l1s.part[0].dev); nb_free(S.l1s.part[1].dev);
     if (S.count_host) cudaFreeHost(S.count_host);
     if (S.host_scalars) cudaFreeHost(S.host_scalars);
     S = FFScratch();

@@ -135,15 +135,20 @@ struct L1StreamPlan {
     std::vector<int> tile_slots;     // partial tiles per cluster tile
     int clusters = 0, max_seg = 0, max_slots = 1;
 };
-struct L1StreamScratch {
+struct L1StreamPart {                // one launch: rows [row0, row0 + rows) through the kernel with cluster shape mt
     L1StreamPlan plan;
     int plan_rows = -1, plan_kb = -1, plan_g = -1, plan_mt = -1;
     unsigned char *dev = nullptr;    // device copy of the plan
     size_t dev_bytes = 0;
     const L1StreamSeg *seg_dev = nullptr;
     const int *slots_dev = nullptr;
-    int tile_rows = 0;
-    long long slot_stride = 0;
+    int row0 = 0, rows = 0, mt = 0, tile_rows = 0;
+    long long slot_stride = 0, ws_off = 0;   // in floats
+};
+struct L1StreamScratch {
+    L1StreamPart part[2];
+    int nparts = 0;
+    int max_slots() const { int m = 1; for (int i = 0; i < nparts; i++) m = part[i].plan.max_slots > m ? part[i].plan.max_slots : m; return m; }
 };
 extern int g_l1_stream_mt;
 int plan_l1_stream(int tiles, int num_kb, int clusters, L1StreamPlan *plan);

@@ -664,46 +664,45 @@ bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, con
            (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
 }
 
-template <int MT, int SA, int SB>
-static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,
-                                 float *maxscaled, const Planes &w1, L1StreamScratch *sc, int debug) {
-    int G = 0;
-    NB_TRY((max_clusters<MT, SA, SB>(&G)));
-    if (G < 1) { set_error("l1 stream: no cluster of %d CTAs fits this device", 4 * MT); return NB200_ERR_STATE; }
-    static const int g_env = getenv("NB200_L1S_CLUSTERS") ? atoi(getenv("NB200_L1S_CLUSTERS")) : 0;
-    if (g_env > 0 && g_env < G) G = g_env;
+// One part of a launch: `rows` rows starting at row `row0` of the batch, through the kernel with cluster shape MT.
+template <int MT>
+static int prepare_part(Context *c, L1StreamPart *pt, int row0, int rows, int num_kb, int G) {
     const int tile_rows = 256 * MT;
     const int tiles = static_cast<int>(ceil_div(rows, tile_rows));
-    const int num_kb = static_cast<int>(w1.ldk / kBK);
-    if (sc->plan_rows != rows || sc->plan_kb != num_kb || sc->plan_g != G || sc->plan_mt != MT) {
-        NB_TRY(plan_l1_stream(tiles, num_kb, G, &sc->plan));
-        const size_t sb = sc->plan.segs.size() * sizeof(L1StreamSeg), tb = sc->plan.tile_slots.size() * sizeof(int);
-        if (sc->dev_bytes < sb + tb) {
-            nb_free(sc->dev);
-            sc->dev = nullptr;
-            sc->dev_bytes = 0;
-            NB_CUDA(nb_malloc(&sc->dev, sb + tb));
-            sc->dev_bytes = sb + tb;
+    if (pt->plan_rows != rows || pt->plan_kb != num_kb || pt->plan_g != G || pt->plan_mt != MT) {
+        NB_TRY(plan_l1_stream(tiles, num_kb, G, &pt->plan));
+        const size_t sb = pt->plan.segs.size() * sizeof(L1StreamSeg), tb = pt->plan.tile_slots.size() * sizeof(int);
+        if (pt->dev_bytes < sb + tb) {
+            nb_free(pt->dev);
+            pt->dev = nullptr;
+            pt->dev_bytes = 0;
+            NB_CUDA(nb_malloc(&pt->dev, sb + tb));
+            pt->dev_bytes = sb + tb;
         }
         // (pageable source: the copy is staged before the call returns, so the vectors may change afterwards)
-        NB_CUDA(cudaMemcpyAsync(sc->dev, sc->plan.segs.data(), sb, cudaMemcpyHostToDevice, c->stream));
-        NB_CUDA(cudaMemcpyAsync(sc->dev + sb, sc->plan.tile_slots.data(), tb, cudaMemcpyHostToDevice, c->stream));
-        sc->seg_dev = reinterpret_cast<const L1StreamSeg *>(sc->dev);
-        sc->slots_dev = reinterpret_cast<const int *>(sc->dev + sb);
-        sc->plan_rows = rows; sc->plan_kb = num_kb; sc->plan_g = G; sc->plan_mt = MT;
+        NB_CUDA(cudaMemcpyAsync(pt->dev, pt->plan.segs.data(), sb, cudaMemcpyHostToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(pt->dev + sb, pt->plan.tile_slots.data(), tb, cudaMemcpyHostToDevice, c->stream));
+        pt->seg_dev = reinterpret_cast<const L1StreamSeg *>(pt->dev);
+        pt->slots_dev = reinterpret_cast<const int *>(pt->dev + sb);
+        pt->plan_rows = rows; pt->plan_kb = num_kb; pt->plan_g = G; pt->plan_mt = MT;
         static const bool verbose = getenv("NB200_L1S_VERBOSE") != nullptr;
         if (verbose)
-            fprintf(stderr, "[l1 stream] MT=%d rows=%d tiles=%d num_kb=%d resident clusters=%d used=%d max_seg=%d max_slots=%d\n", MT, rows,
-                    tiles, num_kb, G, sc->plan.clusters, sc->plan.max_seg - 1, sc->plan.max_slots);
+            fprintf(stderr, "[l1 stream] MT=%d rows=%d (from row %d) tiles=%d num_kb=%d clusters=%d used=%d max_seg=%d max_slots=%d\n", MT,
+                    rows, row0, tiles, num_kb, G, pt->plan.clusters, pt->plan.max_seg - 1, pt->plan.max_slots);
     }
-    const long long slot_stride = static_cast<long long>(tiles) * tile_rows * kWsLd;
-    NB_TRY(ensure_ws(c, static_cast<size_t>(sc->plan.max_slots) * slot_stride * sizeof(float)));
-    sc->tile_rows = tile_rows;
-    sc->slot_stride = slot_stride;
+    pt->row0 = row0; pt->rows = rows; pt->mt = MT;
+    pt->tile_rows = tile_rows;
+    pt->slot_stride = static_cast<long long>(tiles) * tile_rows * kWsLd;
+    return NB200_OK;
+}
 
+template <int MT, int SA, int SB>
+static int launch_part(Context *c, const L1StreamPart &pt, const double *x, int64_t x_ld, int cols, const int *exp_x, float *row_sumsq,
+                       float *maxscaled, const Planes &w1, int debug, cudaStream_t stream) {
     L1SArgs g{};
-    g.x = x; g.x_ld = x_ld; g.rows_total = rows; g.cols = cols; g.exp_x = exp_x; g.row_sumsq = row_sumsq; g.maxscaled = maxscaled;
-    g.ws = c->ws; g.ws_slot_stride = slot_stride; g.sched = reinterpret_cast<const Seg *>(sc->seg_dev); g.max_seg = sc->plan.max_seg;
+    g.x = x + static_cast<long long>(pt.row0) * x_ld; g.x_ld = x_ld; g.rows_total = pt.rows; g.cols = cols; g.exp_x = exp_x;
+    g.row_sumsq = row_sumsq ? row_sumsq + pt.row0 : nullptr; g.maxscaled = maxscaled;
+    g.ws = c->ws + pt.ws_off; g.ws_slot_stride = pt.slot_stride; g.sched = reinterpret_cast<const Seg *>(pt.seg_dev); g.max_seg = pt.plan.max_seg;
     g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(256, 256) & ~((7u << 7) | (7u << 10));  // fp16 operands
     g.debug = debug;
@@ -717,25 +716,26 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     }
     static unsigned long long *prof_dev = nullptr;
     static const bool prof_on = getenv("NB200_L1S_PROF") != nullptr;
-    const int nctas = sc->plan.clusters * 4 * MT;
+    const int nctas = pt.plan.clusters * 4 * MT;
     if (prof_on && !prof_dev) NB_CUDA(cudaMalloc(&prof_dev, 1024 * 16 * sizeof(unsigned long long)));
-    if (prof_on) NB_CUDA(cudaMemsetAsync(prof_dev, 0, 1024 * 16 * sizeof(unsigned long long), c->stream));
+    if (prof_on) NB_CUDA(cudaMemsetAsync(prof_dev, 0, 1024 * 16 * sizeof(unsigned long long), stream));
     g.prof = prof_on ? prof_dev : nullptr;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
-    if (prof_on) {
-        static bool attr = false;
-        if (!attr) { NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB))); attr = true; }
-        k_l1_stream<MT, SA, SB, true><<<nctas, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
-    } else {
-        k_l1_stream<MT, SA, SB, false><<<nctas, kThreadsL1S, smem_total(SA, SB), c->stream>>>(mw, g);
+    static bool attr_set = false;
+    if (!attr_set) {
+        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
+        NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
+        attr_set = true;
     }
+    if (prof_on) k_l1_stream<MT, SA, SB, true><<<nctas, kThreadsL1S, smem_total(SA, SB), stream>>>(mw, g);
+    else k_l1_stream<MT, SA, SB, false><<<nctas, kThreadsL1S, smem_total(SA, SB), stream>>>(mw, g);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     if (prof_on) {   // experiments only: synchronises
         std::vector<unsigned long long> h(static_cast<size_t>(nctas) * 16);
-        NB_CUDA(cudaMemcpyAsync(h.data(), prof_dev, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
+        NB_CUDA(cudaMemcpyAsync(h.data(), prof_dev, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+        NB_CUDA(cudaStreamSynchronize(stream));
         static const char *names[12] = {"producer wait b_empty", "mma wait b_full", "mma wait a_full", "relay wait xfull", "manager wait cdone",
                                         "cvt w0 wait a_empty", "cvt w0 loop total", "cvt w8 wait a_empty", "cvt w8 loop total", "mma loop total",
                                         "cvt w0 load stall+convert", "cvt w0 issue loads"};
@@ -748,32 +748,79 @@ static int launch_l1_stream_impl(Context *c, const double *x, int64_t x_ld, int 
     return NB200_OK;
 }
 
+// The batch goes through one launch.  Clusters of 8 (MT = 2: W1 multicast, least fabric traffic) only fit 15 times on the
+// 148 SMs (GPC sizes), which leaves 28 SMs idle.  Tried and off by default (NB200_L1S_DUAL=1): sending the tail of the batch
+// to a second, concurrent launch of the 4-CTA kernel sized for those SMs -- the two launches share nothing, but the second
+// one is not placed beside the 8-CTA clusters and runs after them: 16.1 ms against 11.0 ms (profiles/r02_l1stream_dual.txt).
 int launch_l1_stream(Context *c, const double *x, int64_t x_ld, int rows, int cols, const int *exp_x, float *row_sumsq,
                      float *maxscaled, const Planes &w1, int N, L1StreamScratch *sc) {
     if (!l1_stream_supported(x, x_ld, cols, N, w1)) { set_error("l1 stream: shape not supported"); return NB200_ERR_STATE; }
     static const int mt_env = getenv("NB200_L1S_MT") ? atoi(getenv("NB200_L1S_MT")) : 0;
-    if (g_l1_stream_mt == 1 || g_l1_stream_mt == 2) {
-        if (g_l1_stream_mt == 2) return launch_l1_stream_impl<2, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, 0);
-        return launch_l1_stream_impl<1, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, 0);
-    }
     static const int debug = getenv("NB200_L1S_DEBUG") ? atoi(getenv("NB200_L1S_DEBUG")) : 0;
-    int mt = mt_env;
-    if (mt != 1 && mt != 2) {
+    static const int g_env = getenv("NB200_L1S_CLUSTERS") ? atoi(getenv("NB200_L1S_CLUSTERS")) : 0;
+    static const int dual_env = getenv("NB200_L1S_DUAL") ? atoi(getenv("NB200_L1S_DUAL")) : 0;
+    int mt = (g_l1_stream_mt == 1 || g_l1_stream_mt == 2) ? g_l1_stream_mt : mt_env;
+    const bool forced = mt == 1 || mt == 2;
+    if (!forced) {
         // MT = 2 halves the W1 traffic but works in 512-row tiles: take it unless its padding costs more than that
         const int64_t pad1 = ceil_div(rows, 256) * 256, pad2 = ceil_div(rows, 512) * 512;
         mt = (pad2 * 10 <= pad1 * 12) ? 2 : 1;
     }
-    if (mt == 2) return launch_l1_stream_impl<2, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
-    return launch_l1_stream_impl<1, 4, 4>(c, x, x_ld, rows, cols, exp_x, row_sumsq, maxscaled, w1, sc, debug);
+    const int num_kb = static_cast<int>(w1.ldk / kBK);
+    int G2 = 0, G1 = 0;
+    NB_TRY((max_clusters<2, 4, 4>(&G2)));
+    NB_TRY((max_clusters<1, 4, 4>(&G1)));
+    if (g_env > 0) { G2 = std::min(G2, g_env); G1 = std::min(G1, g_env); }
+    if ((mt == 2 && G2 < 1) || (mt == 1 && G1 < 1)) { set_error("l1 stream: no cluster of %d CTAs fits this device", 4 * mt); return NB200_ERR_STATE; }
+    const int sms = c->sm_count > 0 ? c->sm_count : 148;
+    const int spare = (sms - 8 * G2) / 4;   // 4-CTA clusters that fit beside the 8-CTA ones
+    sc->nparts = 1;
+    if (mt == 2 && !forced && dual_env && spare >= 2 && rows >= 4096) {
+        // rows in proportion to the SMs each launch gets; the first part in whole 512-row tiles
+        int rows_b = static_cast<int>(static_cast<int64_t>(rows) * (4 * spare) / (8 * G2 + 4 * spare));
+        int rows_a = static_cast<int>(ceil_div(rows - rows_b, 512) * 512);
+        if (rows_a >= rows) rows_a = rows;
+        rows_b = rows - rows_a;
+        NB_TRY(prepare_part<2>(c, &sc->part[0], 0, rows_a, num_kb, G2));
+        if (rows_b > 0) {
+            NB_TRY(prepare_part<1>(c, &sc->part[1], rows_a, rows_b, num_kb, spare));
+            sc->nparts = 2;
+        }
+    } else if (mt == 2) {
+        NB_TRY(prepare_part<2>(c, &sc->part[0], 0, rows, num_kb, G2));
+    } else {
+        NB_TRY(prepare_part<1>(c, &sc->part[0], 0, rows, num_kb, G1));
+    }
+    long long ws_floats = 0;
+    for (int i = 0; i < sc->nparts; i++) {
+        sc->part[i].ws_off = ws_floats;
+        ws_floats += static_cast<long long>(sc->part[i].plan.max_slots) * sc->part[i].slot_stride;
+    }
+    NB_TRY(ensure_ws(c, static_cast<size_t>(ws_floats) * sizeof(float)));
+    if (sc->nparts == 2) NB_CUDA(cudaEventRecord(c->join_ev[3], c->stream));   // fork point: everything queued so far
+    if (sc->part[0].mt == 2) NB_TRY((launch_part<2, 4, 4>(c, sc->part[0], x, x_ld, cols, exp_x, row_sumsq, maxscaled, w1, debug, c->stream)));
+    else NB_TRY((launch_part<1, 4, 4>(c, sc->part[0], x, x_ld, cols, exp_x, row_sumsq, maxscaled, w1, debug, c->stream)));
+    if (sc->nparts == 2) {
+        cudaStream_t side = c->aux[1];
+        NB_CUDA(cudaStreamWaitEvent(side, c->join_ev[3], 0));
+        NB_TRY((launch_part<1, 4, 4>(c, sc->part[1], x, x_ld, cols, exp_x, row_sumsq, maxscaled, w1, debug, side)));
+        NB_CUDA(cudaEventRecord(c->chunk_ev[63], side));
+        NB_CUDA(cudaStreamWaitEvent(c->stream, c->chunk_ev[63], 0));            // join: the reduction needs both
+    }
+    return NB200_OK;
 }
 
 int launch_l1_stream_reduce(Context *c, const L1StreamScratch &sc, int rows, int N, const float *bias_n, int relu,
                             const int *exp_u, const int *exp_v, float *out, int64_t out_ld, float *out_maxabs) {
+    (void)rows;
     if (out_maxabs) NB_CUDA(cudaMemsetAsync(out_maxabs, 0, sizeof(float), c->stream));
-    k_l1s_reduce<<<rows, 256, 0, c->stream>>>(c->ws, sc.slot_stride, sc.slots_dev, sc.tile_rows, N, bias_n, relu, exp_u, exp_v,
-                                              out, out_ld, out_maxabs);
-    c->launches++;
-    NB_CUDA(cudaGetLastError());
+    for (int i = 0; i < sc.nparts; i++) {
+        const L1StreamPart &pt = sc.part[i];
+        k_l1s_reduce<<<pt.rows, 256, 0, c->stream>>>(c->ws + pt.ws_off, pt.slot_stride, pt.slots_dev, pt.tile_rows, N, bias_n, relu, exp_u,
+                                                     exp_v, out + static_cast<long long>(pt.row0) * out_ld, out_ld, out_maxabs);
+        c->launches++;
+        NB_CUDA(cudaGetLastError());
+    }
     return NB200_OK;
 }
 
