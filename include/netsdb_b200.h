@@ -109,6 +109,10 @@ int nb200_synchronize(void);
  *      number of rows (a row shard of 1,250 as well as 10,000) fills the device; 1: the round-1 kernel that passes the
  *      converted inputs through a ring in L2 (whole 256-row tiles only); 0: separate conversion and GEMM kernels;
  *      -1: back to the default.  Shapes a kernel does not cover fall through to the next one.
+ *  "near_tie_tau_x10" (default 25): width of the near-tie band in tenths of eps_r, the norm-based estimate of a row's
+ *      low-precision logit error.  Rows whose top-2 logit gap is below tau * eps_r are re-evaluated
+ *      at the next precision level.  Measured on 102,400 rows (tests/test_gpu_fullsize.py): every raw fp16 label that
+ *      differs from fp64 has gap < 0.77 eps_r, so 2.5 leaves a factor of three; 40 restores round 1's band.
  *  "l1_stream_mt": cluster shape of the default kernel, 1 (4 CTAs, 256 rows) or 2 (8 CTAs, 512 rows, W1 multicast); 0
  *      (default) picks by the padding the row count would need. */
 int nb200_set_option(const char *key, int value);

@@ -25,6 +25,7 @@ void set_error(const char *fmt, ...) {
 
 static Context *g_ctx = nullptr;
 static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default 2); 0 separate kernels, 1 ring kernel, 2 stream kernel
+static int g_opt_tau_x10 = 25;  // near-tie band in units of 0.1 eps_r (nb200_set_option "near_tie_tau_x10")
 static int fused_mode() {
     if (g_opt_fused >= 0) return g_opt_fused;
     static const int env = getenv("NB200_FUSED") ? atoi(getenv("NB200_FUSED")) : 2;
@@ -334,6 +335,7 @@ int64_t nb200_launch_count(void) { return g_ctx ? g_ctx->launches : 0; }
 
 int nb200_set_option(const char *key, int value) {
     if (key && !strcmp(key, "fused_layer1")) { g_opt_fused = value < 0 ? -1 : (value > 2 ? 2 : value); return NB200_OK; }
+    if (key && !strcmp(key, "near_tie_tau_x10")) { g_opt_tau_x10 = value < 5 ? 5 : (value > 160 ? 160 : value); return NB200_OK; }
     if (key && !strcmp(key, "l1_stream_mt")) { g_l1_stream_mt = (value == 1 || value == 2) ? value : 0; return NB200_OK; }
     set_error("set_option: unknown key");
     return NB200_ERR_INVALID;
@@ -1353,7 +1355,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         NB_TRY(launch_softmax_rows(c, zset->f32, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, nullptr, 0, 0));
         NB_CUDA(cudaMemsetAsync(S.count, 0, sizeof(int), c->stream));
         NB_TRY(launch_flag_rows(c, B, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs, wo->rowp.maxabs,
-                                wo->wo_rownorm_max, prec_unit(precision), 4.0f, S.list, S.count, B, nullptr));
+                                wo->wo_rownorm_max, prec_unit(precision), 0.1f * g_opt_tau_x10, S.list, S.count, B, nullptr));
         NB_CUDA(cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         if (fmt == kFmtF16)
             NB_CUDA(cudaMemcpyAsync(S.host_scalars, inputs->rowp.f16_maxscaled, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
@@ -1367,7 +1369,9 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         int n1 = std::min(*S.count_host, B);
         const int32_t *final_list = S.list;
         refined = n1;
-        if ((precision == NB200_PREC_BF16 || precision == NB200_PREC_F16) && n1 > 0) {
+        // (a handful of undecided rows go straight to the fp64 level: both levels stream all of W1 once, and the fp64 kernel
+        // handles up to 16 rows in that one pass)
+        if ((precision == NB200_PREC_BF16 || precision == NB200_PREC_F16) && n1 > 16) {
             // level 2: bf16x3 on the undecided rows only (gathered straight from the fp64 inputs)
             if (S.list2_cap < B) {
                 nb_free(S.list2);
@@ -1394,7 +1398,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
                 NB_TRY(launch_scatter_rows_f32(c, S.logits_sub, Lb, Lb, S.list + r0, R, zset->f32, Lb));
                 NB_TRY(launch_softmax_rows(c, S.logits_sub, false, B, Lb, Lb, o->f64, Lb, S.labels, S.gap, S.list + r0, R, 1));
                 NB_TRY(launch_flag_rows(c, R, S.gap, inputs->rowp.row_sumsq, S.y1.row_sumsq, w1->rowp.maxabs,
-                                        wo->rowp.maxabs, wo->wo_rownorm_max, prec_unit(NB200_PREC_BF16X3), 4.0f, S.list2,
+                                        wo->rowp.maxabs, wo->wo_rownorm_max, prec_unit(NB200_PREC_BF16X3), 0.1f * g_opt_tau_x10, S.list2,
                                         S.count, B, S.list + r0));
             }
             NB_CUDA(cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -1599,7 +1603,7 @@ int nb200_ff_finish_from_layer1(const float *y1pre_dev, int64_t ld, int rows, nb
         if (st == NB200_OK && cudaMemsetAsync(S.count, 0, sizeof(int), c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
         if (st == NB200_OK)
             st = launch_flag_rows(c, rows, S.gap, xs, S.y1.row_sumsq, xs + rows, wo->rowp.maxabs, wo->wo_rownorm_max,
-                                  prec_unit(precision), 4.0f, S.list, S.count, rows, nullptr);
+                                  prec_unit(precision), 0.1f * g_opt_tau_x10, S.list, S.count, rows, nullptr);
         if (st == NB200_OK && cudaMemcpyAsync(S.count_host, S.count, sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) st = NB200_ERR_CUDA;
         cudaStreamSynchronize(c->stream);
         nb_free(xs);

@@ -1107,10 +1107,18 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
         static const bool skinny_env = !(getenv("NB200_F64_SKINNY") && atoi(getenv("NB200_F64_SKINNY")) == 0);
         const bool aligned = (u_sm % 2 == 0) && (v_sn % 2 == 0) && ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
         if (small && aligned && skinny_env && K >= 8192) {
-            static const int cfg = getenv("NB200_F64_CFG") ? atoi(getenv("NB200_F64_CFG")) : 0;
+            static const int cfg = getenv("NB200_F64_CFG") ? atoi(getenv("NB200_F64_CFG")) : 1;
             auto run = [&](auto kern, int BNs, int BKs, int ST, int ctas_per_sm) -> int {
                 const size_t smem = static_cast<size_t>(ST) * (16 + BNs) * (BKs + 4) * sizeof(double);
                 NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+                // What the resident CTAs leave of the SM's 228 KB is the L1, and the L1 is where global loads land: three
+                // 69 KB CTAs leave none and the stream over W1 stops at ~4.2 TB/s.  Two CTAs per SM (carve-out 164 KB,
+                // 64 KB of L1) stream faster than three.
+                static const int carve = getenv("NB200_F64_CARVEOUT") ? atoi(getenv("NB200_F64_CARVEOUT")) : 72;
+                if (carve > 0) NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+                static const int cps_env = getenv("NB200_F64_CTAS") ? atoi(getenv("NB200_F64_CTAS")) : 0;
+                if (cps_env > 0) ctas_per_sm = cps_env;
+                else if (carve > 0) ctas_per_sm = static_cast<int>((228 * 1024 * carve / 100) / (smem + 1024));
                 const int64_t tl = ceil_div(M, 16) * ceil_div(N, BNs);
                 int sp = static_cast<int>(ceil_div(static_cast<int64_t>(ctas_per_sm) * sms, tl));
                 if (sp > K / 2048) sp = static_cast<int>(K / 2048);
@@ -1122,9 +1130,10 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
                 kern<<<g2, 128, smem, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kp, out, out_ld);
                 return NB200_OK;
             };
-            // measured on the Amazon shape (15 x 1000 x 597,540, tools/f64_skinny_bench.py): 16 x 64 tiles with BK = 32
-            // 1.145 ms, 16 x 128 with BK = 16 1.154 ms, register-staged kernel 1.277 ms; 16 x 32 tiles 1.8 - 2.0 ms.
-            // All sit at ~17 TFLOP/s of DMMA.8x8x4 (m16n8k4 lowers to two of them), not at the HBM roofline (0.73 ms).
+            // measured on the Amazon shape (15 x 1000 x 597,540, tools/f64_skinny_bench.py, profiles/r02_f64_skinny.txt):
+            // with three CTAs per SM and no L1 left 16 x 64 / BK = 32 takes 1.13 ms, 16 x 128 / BK = 16 1.15 ms; with a
+            // 72 % carve-out (two CTAs per SM, 64 KB of L1) 16 x 128 / BK = 16 takes 1.01 ms = 4.7 TB/s of W1 and
+            // 19 TFLOP/s of DMMA.8x8x4 (m16n8k4 lowers to two of them); the HBM roofline is 0.73 ms.
             if (cfg == 1) NB_TRY(run(k_gemm_f64_mma_skinny<3, 16, 128>, 128, 16, 3, 3));
             else NB_TRY(run(k_gemm_f64_mma_skinny<3, 32, 64>, 64, 32, 3, 3));
             NB_LAUNCH_CHECK(c);
