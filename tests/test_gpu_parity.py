@@ -417,6 +417,7 @@ def test_fp16_side_format_inputs(nb, oracle, trim):
     batch, feat, hid, lab, blk = 1300, 8300, 300, 40, 1000
     dev, ora, dense = _ff_sets(nb, oracle, batch, feat, hid, lab, blk, wo_scale=0.02)  # small wo: many near ties
     _, _, ref_labels = oracle.ff_inference_unit(ora["w1"], ora["wo"], ora["x"], ora["b1"], ora["bo"], threads=4)
+    nb.set_option("near_tie_tau_x10", 80)  # a wide band: more than 16 undecided rows, so that BOTH levels fetch rows from the host
     plane, e, ss = dev["x"].export_f16()
     _, labels_res, st_res = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PREC_F16)
     z_res = nb.DeviceSet.lookup("ff", "__logits").download_dense()
@@ -442,7 +443,8 @@ def test_fp16_side_format_inputs(nb, oracle, trim):
         S.upload_commit()
         out, labels, st = nb.ff_inference_unit(dev["w1"], dev["wo"], S, dev["b1"], dev["bo"], nb.PREC_F16)
         assert np.array_equal(labels, ref_labels), (labels != ref_labels).sum()
-        assert st["relevel_rows"] == st_res["relevel_rows"] > 0  # the cascade ran, on rows fetched from the host blocks
+        assert st["relevel_rows"] == st_res["relevel_rows"] > 16  # the cascade ran, on rows fetched from the host blocks
+        assert st["refined_rows"] == st_res["refined_rows"]
         assert np.array_equal(nb.DeviceSet.lookup("ff", "__logits").download_dense(), z_res)
     with pytest.raises(nb.Nb200Error):  # no fp64 on the device: only the fp16 evaluation is possible
         nb.ff_inference_unit(dev["w1"], dev["wo"], S, dev["b1"], dev["bo"], nb.PREC_BF16X3)
@@ -450,6 +452,7 @@ def test_fp16_side_format_inputs(nb, oracle, trim):
     with pytest.raises(nb.Nb200Error):  # host blocks the device cannot see
         S.import_f16(pp, e, ss, unpinned, edge_ld)
     S.destroy()
+    nb.set_option("near_tie_tau_x10", 25)
 
 
 def test_concurrent_callers_are_serialised(nb, oracle):

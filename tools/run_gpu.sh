@@ -1,2 +1,1 @@
-for cfg in "0 0" "86 0" "72 0" "72 3" "58 0" "43 0"; do set -- $cfg; echo "carveout=$1 ctas=$2"; NB200_F64_CARVEOUT=$1 NB200_F64_CTAS=$2 timeout 200 python tools/f64_skinny_bench.py 2>&1 | tail -1; done > gpurun_out/f64_skinny.log 2>&1
-for cfg in "72 0" "58 0"; do set -- $cfg; echo "CFG=1 carveout=$1 ctas=$2"; NB200_F64_CFG=1 NB200_F64_CARVEOUT=$1 NB200_F64_CTAS=$2 timeout 200 python tools/f64_skinny_bench.py 2>&1 | tail -1; done >> gpurun_out/f64_skinny.log 2>&1
+timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -5 gpurun_out/pytest_gpu.log
