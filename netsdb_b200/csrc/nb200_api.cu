@@ -428,7 +428,8 @@ int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int 
     cudaStream_t cs = c->copy[slot];
     double *dst = s->f64 + static_cast<size_t>(row0) * s->total_cols + col0;
     const size_t dpitch = static_cast<size_t>(s->total_cols) * sizeof(double);
-    const size_t block_bytes = static_cast<size_t>(vr) * ld * sizeof(double);
+    // (the rectangle's last row only guarantees vc elements: never read the ld - vc doubles after it)
+    const size_t block_bytes = (static_cast<size_t>(vr - 1) * ld + vc) * sizeof(double);
     if (block_bytes >= (1u << 20) && dpitch != static_cast<size_t>(ld) * sizeof(double)) {
         // contiguous H2D of the host rows into a staging slot, then de-block on the device
         if (c->up_bytes[slot] < block_bytes) {

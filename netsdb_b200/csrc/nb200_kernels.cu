@@ -1224,8 +1224,10 @@ k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restri
     const T NEG = static_cast<T>(-CUDART_INF);
     T m1 = NEG, m2 = NEG;
     int i1 = 0x7fffffff;
+    int bad = 0;  // a NaN / inf logit: comparisons skip it, so the gap would look healthy -- report the row as undecided
     for (int j = threadIdx.x; j < cols; j += 256) {
         const T v = zr[j];
+        bad |= !(v < static_cast<T>(CUDART_INF));   // NaN or +inf
         if (v > m1) { m2 = m1; m1 = v; i1 = j; }
         else if (v > m2) m2 = v;
     }
@@ -1238,7 +1240,7 @@ k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restri
     }
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
     if (l == 0) { s_m1[w] = m1; s_m2[w] = m2; s_i1[w] = i1; }
-    __syncthreads();
+    const int any_bad = __syncthreads_or(bad);
     if (threadIdx.x == 0) {
         T a1 = s_m1[0], a2 = s_m2[0];
         int ai = s_i1[0];
@@ -1250,7 +1252,7 @@ k_softmax_rows(const T *__restrict__ z, long long ld, int cols, double *__restri
         }
         b_m1 = a1;
         if (labels) labels[row] = ai;
-        if (gap) gap[row] = static_cast<float>(a1 - a2);
+        if (gap) gap[row] = any_bad ? __int_as_float(0x7fc00000) : static_cast<float>(a1 - a2);
     }
     __syncthreads();
     if (!probs) return;
@@ -1310,12 +1312,14 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
         if (PREFETCH) { if (has_next) load_row(it + gridDim.x, reinterpret_cast<float4 (&)[NV]>(nv)); }
         float m1 = -CUDART_INF_F, m2 = -CUDART_INF_F;
         int i1 = 0x7fffffff;
+        int bad = 0;   // a NaN / +inf logit: comparisons skip a NaN, so the gap would look healthy -- report the row as undecided
 #pragma unroll
         for (int i = 0; i < NV; i++) {
             const int base = (threadIdx.x + i * THREADS) * 4;
             const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
             for (int j = 0; j < 4; j++) {
+                bad |= !(e[j] < CUDART_INF_F);
                 if (e[j] > m1) { m2 = m1; m1 = e[j]; i1 = base + j; }
                 else if (e[j] > m2) m2 = e[j];
             }
@@ -1327,7 +1331,7 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
             else m2 = fmaxf(m2, om1);
         }
         if (l == 0) { s_m1[w] = m1; s_m2[w] = m2; s_i1[w] = i1; }
-        __syncthreads();
+        const int any_bad = __syncthreads_or(bad);
         if (threadIdx.x == 0) {
             float a1 = s_m1[0], a2 = s_m2[0];
             int ai = s_i1[0];
@@ -1339,7 +1343,7 @@ k_softmax_rows_reg(const float *__restrict__ z, long long ld, int cols, double *
             }
             b_m1 = a1;
             if (labels) labels[row] = ai;
-            if (gap) gap[row] = a1 - a2;
+            if (gap) gap[row] = any_bad ? __int_as_float(0x7fc00000) : a1 - a2;
         }
         __syncthreads();
         if (probs) {

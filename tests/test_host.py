@@ -127,3 +127,31 @@ def test_l1_stream_wave_plan_covers_every_tile_once():
             assert sorted(s[4] for s in segs if s[1] == t) == list(range(slots[t]))
         ideal = tiles * num_kb / G
         assert per_cluster.max() <= max(1.35 * ideal + 110 * (1 + tiles // G), num_kb / max(1, min(G, num_kb // 8)) + 1), (tiles, num_kb, G, per_cluster.max(), ideal)
+
+
+def test_reference_side_stub_compiles_against_the_reference_headers():
+    """INTEGRATION.md section 2 / SURVEY 8f-1 (the reachable part): netsdb_b200/host/reference_side/FFGpuStage.h is a real
+    file, written against netsDB's own FFMatrixBlock.h and the C ABI only; `make -C oracle ref` compiles it with the
+    reference's unmodified header wherever the reference tree is mounted.  The object must reference exactly the entry
+    points the stub claims to bind."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    obj = os.path.join(root, "oracle", "_ref", "ffgpustage_check.o")
+    if os.path.exists("/root/reference/src/FF/headers/FFMatrixBlock.h"):
+        subprocess.check_call(["make", "-C", os.path.join(root, "oracle"), "_ref/ffgpustage_check.o"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(obj):
+        import pytest
+
+        pytest.skip("no reference tree here and no prebuilt object")
+    und = subprocess.run(["nm", "-u", obj], capture_output=True, text=True).stdout
+    for sym in ("nb200_upload_block", "nb200_download_block", "nb200_set_info", "nb200_set_create", "nb200_set_lookup",
+                "nb200_ff_inference_unit", "nb200_last_error"):
+        assert sym in und, sym
+    header = open(os.path.join(root, "include", "netsdb_b200.h")).read()
+    stub = open(os.path.join(root, "netsdb_b200", "host", "reference_side", "FFGpuStage.h")).read()
+    import re
+
+    for sym in set(re.findall(r"\b(nb200_[a-z0-9_]+)\(", stub)):
+        assert re.search(r"\b" + sym + r"\(", header), f"{sym} is not declared in the public header"
