@@ -356,6 +356,15 @@ def run_b200(a):
         weak = dict(value=rw["value"], unit=UNIT, ms_per_step=round(rw["ms_per_step"], 3), rows_per_gpu=full_batch,
                     note="independent replicas, 3 steps: every rank runs its own full batch (no communication to scale)")
 
+    # --- N > 1: the K-sharded variant (a weight set larger than one GPU's HBM): every rank a column shard of `inputs` and
+    # `w1`, one NCCL reduce-scatter of the layer-1 partials over NVLink, the rest row-local (netsdb_b200/ksharded.py) ---
+    ksh = None
+    if world > 1 and a.precision == "f16":
+        try:
+            ksh = run_ksharded(a, capi, torch, dist, barrier, np, rank, world, b1, wo, bo, prec, full_batch, head["labels"], row0)
+        except Exception as ex:  # an extra, never the headline
+            ksh = dict(value=None, note=f"failed: {ex!r}")
+
     # --- e2e: host blocks -> device -> labels + output blocks back, through the public C ABI ---
     e2e = None
     if not a.no_e2e:
@@ -385,12 +394,83 @@ def run_b200(a):
                                 labels="near-tie rows (top-2 gap inside a 4-sigma band of the low-precision error) are re-evaluated in bf16x3 and then fp64",
                                 precision=a.precision),
                     clocks=clk, e2e=e2e, gpu_launches=int(launches), roofline=roofline, two_kernel_path=two_kernel,
-                    precision_variants=variants, weak_replicas=weak, strong_check=labels_check, cpu_baseline=cpu,
+                    precision_variants=variants, weak_replicas=weak, strong_check=labels_check, ksharded=ksh, cpu_baseline=cpu,
                     breakdown_ms={k: round(v, 4) for k, v in stats.items()})
         print(json.dumps(line), flush=True)
     capi.shutdown()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def run_ksharded(a, capi, torch, dist, barrier, np, rank, world, b1, wo, bo, prec, full_batch, row_labels, row0):
+    """Extra key at N > 1: the same batch with K (the feature axis) sharded instead of the rows."""
+    from netsdb_b200.ksharded import col_shard, ff_inference_k_sharded
+    from netsdb_b200.shard import gather_labels
+
+    blk = a.block
+    c0, nc = col_shard(a.features, blk, world, rank)
+    DS = capi.DeviceSet
+    # the shard of the same synthetic matrices: column c of the full matrix is element row * features + c0 + c of the
+    # generator's stream, which a set of nc columns cannot address -- so generate full-width slabs and copy the columns
+    xs = DS.create("ffk", "inputs", full_batch, nc, blk, blk)
+    ws = DS.create("ffk", "w1", a.hidden, nc, blk, blk)
+    slab_rows = 500
+    for (dst, seed, rows) in ((ws, 2, a.hidden), (xs, 1, full_batch)):
+        tmp = DS.create("ffk", "__slab", slab_rows, a.features, blk, blk)
+        host = np.empty((slab_rows, nc), dtype=np.float64)
+        for r0 in range(0, rows, slab_rows):
+            n = min(slab_rows, rows - r0)
+            tmp.fill_synth(seed, row_offset=r0)
+            capi.check(capi.lib().nb200_download_rect(tmp.ptr, 0, c0, host.ctypes.data, n, nc, nc))
+            capi.check(capi.lib().nb200_upload_rect(dst.ptr, r0, 0, host.ctypes.data, n, nc, nc))
+            capi.synchronize()
+        tmp.destroy()
+    times, coll = [], []
+    out = labels = und = None
+    for it in range(5):
+        xs.invalidate_planes()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        tm = {}
+        out, labels, und, r0 = ff_inference_k_sharded(dist, torch, rank, world, ws, xs, b1, wo, bo, prec, "ffk", "output", timing=tm)
+        e1.record()
+        barrier()
+        if it >= 2:
+            t = torch.tensor([e0.elapsed_time(e1), tm.get("collective_ms", 0.0)], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            times.append(float(t[0].item())); coll.append(float(t[1].item()))
+    # labels of the K-sharded run (rows split by the reduce-scatter) against the row-sharded run's
+    mine_rows = len(labels)
+    allk = np.concatenate(_all_gather_var(torch, dist, labels, world))
+    allr = gather_labels(row_labels, full_batch, world, rank, dist)
+    undt = torch.tensor([und], device="cuda", dtype=torch.int64)
+    dist.all_reduce(undt)
+    ndiff = int((allk[:full_batch] != allr).sum())
+    xs.destroy(); ws.destroy()
+    ms, cms = sum(times) / len(times), sum(coll) / len(coll)
+    payload = full_batch * (a.hidden + 1) * 4
+    return dict(value=full_batch / (ms / 1e3), unit=UNIT, ms_per_step=round(ms, 3), collective="reduce_scatter (NCCL over NVLink)",
+                collective_ms=round(cms, 3), payload_bytes_per_rank=payload,
+                bus_gbs=round(payload * (world - 1) / world / (cms / 1e3) / 1e9, 1) if cms > 0 else None,
+                labels_differing_from_row_sharded=ndiff, undecided_rows_reported=int(undt.item()),
+                labels_ok=bool(ndiff <= int(undt.item())), rows_on_rank0=mine_rows,
+                note="3 timed steps; the label-exact cascade is not available in this variant (the fp64 rows are sharded): label "
+                     "differences must lie inside the reported undecided set")
+
+
+def _all_gather_var(torch, dist, arr, world):
+    import numpy as np
+
+    n = torch.tensor([len(arr)], device="cuda", dtype=torch.int64)
+    ns = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(ns, n)
+    mx = int(max(int(v.item()) for v in ns))
+    buf = torch.full((mx,), -1, dtype=torch.int32, device="cuda")
+    buf[:len(arr)] = torch.as_tensor(np.asarray(arr, dtype=np.int32)).cuda()
+    outs = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(outs, buf)
+    return [o[:int(k.item())].cpu().numpy() for o, k in zip(outs, ns)]
 
 
 def run_e2e(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, world):

@@ -27,8 +27,9 @@ def col_shard(total_cols: int, block_cols: int, world: int, rank: int) -> tuple[
 
 
 def ff_inference_k_sharded(dist, torch, rank: int, world: int, w1_shard, inputs_shard, b1, wo, bo, precision: int,
-                           db: str = "ff", out_set: str = "output"):
-    """Returns (output DeviceSet holding this rank's rows, labels of this rank's rows, undecided row count, row0)."""
+                           db: str = "ff", out_set: str = "output", timing: dict | None = None):
+    """Returns (output DeviceSet holding this rank's rows, labels of this rank's rows, undecided row count, row0).
+    `timing` (optional) receives the device time of the collective in ms (CUDA events on the current stream) and its payload."""
     B = inputs_shard.info()[0]
     H = w1_shard.info()[0]
     Bp = (B + world - 1) // world * world                      # reduce-scatter wants equal chunks: pad the batch
@@ -41,6 +42,10 @@ def ff_inference_k_sharded(dist, torch, rank: int, world: int, w1_shard, inputs_
     rows_per = Bp // world
     mine = torch.empty((rows_per, H + 1), dtype=torch.float32, device="cuda")
     wmax = torch.tensor([mx.value], dtype=torch.float32, device="cuda")
+    ev = None
+    if timing is not None and torch.cuda.is_available():
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record()
     if world > 1:
         if dist.get_backend() == "nccl":
             dist.reduce_scatter_tensor(mine, partial, op=dist.ReduceOp.SUM)     # the one data-path collective
@@ -50,7 +55,12 @@ def ff_inference_k_sharded(dist, torch, rank: int, world: int, w1_shard, inputs_
         dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
     else:
         mine.copy_(partial)
+    if ev is not None:
+        ev[1].record()
     torch.cuda.synchronize()
+    if ev is not None:
+        timing["collective_ms"] = ev[0].elapsed_time(ev[1])
+        timing["payload_bytes"] = int(partial.numel() * 4)
     row0 = rank * rows_per
     rows = max(0, min(B, row0 + rows_per) - row0)
     labels = np.empty(rows, dtype=np.int32)

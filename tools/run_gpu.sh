@@ -1,1 +1,1 @@
-timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -5 gpurun_out/pytest_gpu.log
+timeout 600 python -m pytest tests/test_gpu_housekeeping.py -x -q > gpurun_out/pytest_hk.log 2>&1; tail -15 gpurun_out/pytest_hk.log

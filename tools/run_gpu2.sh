@@ -1,3 +1,4 @@
-set -x
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 --no-e2e > gpurun_out/bench_n2.json 2> gpurun_out/bench_n2.err; tail -c 2500 gpurun_out/bench_n2.json; tail -5 gpurun_out/bench_n2.err
-timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "k_sharded" > gpurun_out/pytest_ksh.log 2>&1; tail -5 gpurun_out/pytest_ksh.log
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 --no-e2e > gpurun_out/bench_n2.json 2> gpurun_out/bench_n2.err; python3 -c "
+import json
+d=json.loads(open('gpurun_out/bench_n2.json').read().strip().splitlines()[-1])
+print({k:d[k] for k in ('value','ms_per_step','scaling')}); print(d['ksharded']); print(d['weak_replicas']); print(d['strong_check']); print(d['breakdown_ms'])"; tail -5 gpurun_out/bench_n2.err
