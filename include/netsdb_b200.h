@@ -10,9 +10,10 @@
  *
  * There is no CPU fallback: if no sm_100 device is present nb200_init fails.
  *
- * Threads and memory: one device per process (nb200_init after the worker's fork()).  Entry points may be called from
- * any number of threads -- netsDB runs one pipeline thread per hash partition -- and are served one at a time (a
- * process-wide lock: every call already fills the device).  Device memory comes from a caching allocator inside the
+ * Threads and memory: any number of devices per process (nb200_init / nb200_init_devices after the worker's fork(); a
+ * thread picks its device with nb200_use_device).  Entry points may be called from any number of threads -- netsDB runs one
+ * pipeline thread per hash partition --; calls onto the same device are served one at a time (a per-device lock: every call
+ * already fills the device), calls onto different devices run concurrently.  Device memory comes from a caching allocator inside the
  * library; the fused stages (nb200_ff_inference_unit, nb200_lstm_cell) allocate nothing in steady state.  Uploads are
  * asynchronous: a source block must stay unmodified until nb200_synchronize() or the next call that returns data to the
  * host (see nb200_pin_pool / nb200_upload_commit).
@@ -94,9 +95,21 @@ typedef struct {
 } nb200_ff_stats;
 
 /* ---- lifetime ------------------------------------------------------------------------------ */
-/* Bind the calling process to CUDA device `device` (lazily creates the context; call after
- * fork(), cf. mainServer/source/WorkerMain.cc:107).  Idempotent for the same device. */
+/* Create the library's context on CUDA device `device` (call after fork(), cf. mainServer/source/WorkerMain.cc:107) and make
+ * the CALLING THREAD work on it.  Idempotent; may be called for several devices.
+ *
+ * One process can drive all GPUs of a box: netsDB's backend runs `numThreads` pipeline threads in one process
+ * (conf/headers/Configuration.h:52-53, work/source/PDBWorkerQueue.cc:163).  Every device has its own context, sets (the
+ * (db, set) namespace is per device), scratch, allocator pool and lock; a thread works on the device it chose last
+ * (nb200_init / nb200_use_device; thread-local), and threads on different devices never wait for one another.  A set can
+ * only be passed to entry points by a thread that works on the set's device.  For config C3 each thread uploads its row
+ * shard of `inputs` (nb200_upload_rect) and the replicated weights to its own device and calls nb200_ff_inference_unit. */
 int nb200_init(int device);
+/* nb200_init for each of devices[0..n), then nb200_use_device(devices[0]). */
+int nb200_init_devices(const int *devices, int n);
+/* The calling thread works on `device` (already initialised) from now on. */
+int nb200_use_device(int device);
+int nb200_current_device(int *device);
 int nb200_shutdown(void);
 const char *nb200_last_error(void);
 int nb200_device_count(int *count);

@@ -22,7 +22,7 @@ PRECISIONS = {"bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "fp64": PREC_FP64, "f16"
 # every symbol include/netsdb_b200.h declares (tests check the .so exports each one)
 EXPORTS = [
     "nb200_init", "nb200_shutdown", "nb200_last_error", "nb200_device_count", "nb200_set_stream",
-    "nb200_synchronize", "nb200_launch_count", "nb200_set_option", "nb200_pin_pool", "nb200_unpin_pool", "nb200_set_create",
+    "nb200_synchronize", "nb200_init_devices", "nb200_use_device", "nb200_current_device", "nb200_launch_count", "nb200_set_option", "nb200_pin_pool", "nb200_unpin_pool", "nb200_set_create",
     "nb200_set_lookup", "nb200_set_destroy", "nb200_set_info", "nb200_upload_block", "nb200_upload_rect",
     "nb200_download_block", "nb200_download_rect", "nb200_set_fill_synth", "nb200_set_invalidate_planes",
     "nb200_set_exp_view", "nb200_set_rename",
@@ -115,6 +115,16 @@ def check(status: int):
 
 def init(device: int = 0):
     check(lib().nb200_init(device))
+
+
+def init_devices(devices):
+    arr = (C.c_int * len(devices))(*devices)
+    check(lib().nb200_init_devices(arr, len(devices)))
+
+
+def use_device(device: int):
+    """The calling thread works on `device` from now on (thread-local)."""
+    check(lib().nb200_use_device(device))
 
 
 def shutdown():

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <initializer_list>
 #include <map>
 #include <mutex>
 #include <string>
@@ -23,7 +24,24 @@ void set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
-static Context *g_ctx = nullptr;
+// ---- devices --------------------------------------------------------------------------------------
+// One Context per device.  netsDB runs `numThreads` pipeline threads inside ONE backend process (conf/headers/
+// Configuration.h:52-53, work/source/PDBWorkerQueue.cc:163): every thread picks the device it works on (nb200_init or
+// nb200_use_device, thread-local), and each device has its own context, sets, scratch, allocator pool and lock, so
+// threads on different devices never wait for one another.  A thread that never chose uses the first device initialised.
+constexpr int kMaxDev = 16;
+struct DeviceState {
+    Context *ctx = nullptr;
+    std::recursive_mutex mu;   // serialises the entry points of THIS device (they compose: recursive)
+    std::map<std::pair<std::string, std::string>, nb200_set *> sets;
+    void *ff = nullptr, *lstm = nullptr;   // FFScratch / LstmScratch, created on first use
+};
+static DeviceState g_dev[kMaxDev];
+static int g_default_dev = -1;
+static thread_local int tls_dev = -1;
+static int cur_dev() { return tls_dev >= 0 ? tls_dev : g_default_dev; }
+static DeviceState &cur_state() { const int d = cur_dev(); return g_dev[d >= 0 ? d : 0]; }
+#define g_sets (cur_state().sets)
 static int g_opt_fused = -1;  // -1: from the environment (NB200_FUSED, default 2); 0 separate kernels, 1 ring kernel, 2 stream kernel
 static int g_opt_tau_x10 = 25;  // near-tie band in units of 0.1 eps_r (nb200_set_option "near_tie_tau_x10")
 static int fused_mode() {
@@ -31,17 +49,14 @@ static int fused_mode() {
     static const int env = getenv("NB200_FUSED") ? atoi(getenv("NB200_FUSED")) : 2;
     return env < 0 ? 0 : (env > 2 ? 2 : env);
 }
-static std::mutex g_mu;
-// Serialises the entry points: the library keeps one compute stream, one split-K workspace and one set of scratch buffers per
-// process, so calls from netsDB's pipeline threads (one per hash partition, work/source/PDBWorkerQueue.cc:163) run one at a
-// time on the device.  Recursive because entry points compose (nb200_lstm_cell -> gemm_blocks -> ...).
-static std::recursive_mutex g_api_mu;
+static std::mutex g_mu;   // the registry of devices and the per-device set maps
+// Every entry point holds its device's lock for its whole duration: a device keeps one compute stream, one split-K workspace
+// and one set of scratch buffers, so calls from several pipeline threads onto the SAME device run one at a time.
 static std::atomic<uint64_t> g_version{0};  // source of set versions: unique across sets, so a cache keyed on
                                             // (pointer, version) cannot be fooled by a recycled address
-static std::map<std::pair<std::string, std::string>, nb200_set *> g_sets;
 
-Context *ctx() { return g_ctx; }
-std::recursive_mutex &api_mutex() { return g_api_mu; }
+Context *ctx() { const int d = cur_dev(); return d >= 0 ? g_dev[d].ctx : nullptr; }
+std::recursive_mutex &api_mutex() { return cur_state().mu; }
 
 int ensure_ws(Context *c, size_t bytes) {
     if (bytes <= c->ws_bytes) return NB200_OK;
@@ -131,7 +146,8 @@ static void free_set_storage(nb200_set *s) {
     if (!c) {                                                   \
         ::nb200::set_error("nb200_init has not been called");   \
         return NB200_ERR_STATE;                                 \
-    }
+    }                                                           \
+    cudaSetDevice(c->device);   /* the calling thread may have worked on another device before */
 // every entry point that reads or writes set data on the compute stream first orders itself after queued uploads
 #define NEED_CTX()                                              \
     NEED_CTX_RAW()                                              \
@@ -140,6 +156,17 @@ static void free_set_storage(nb200_set *s) {
         if (_w != NB200_OK) return _w;                          \
         c->main_dirty = true;                                   \
     }
+
+// a set can only be used by a thread that works on the set's device
+static int same_device(Context *c, std::initializer_list<const nb200_set *> sets) {
+    for (const nb200_set *s : sets)
+        if (s && s->device != c->device) {
+            set_error("set %s:%s lives on device %d but the calling thread works on device %d (nb200_use_device)", s->db.c_str(),
+                      s->name.c_str(), s->device, c->device);
+            return NB200_ERR_STATE;
+        }
+    return NB200_OK;
+}
 
 // ---- derived representations ------------------------------------------------------------------
 static int ensure_f64(Context *c, nb200_set *s) {
@@ -189,6 +216,7 @@ static int make_set(const char *db, const char *name, int tr, int tc, int br, in
         g_sets[key] = s;
     }
     s->db = db; s->name = name;
+    s->device = cur_dev();
     s->total_rows = tr; s->total_cols = tc; s->block_rows = br; s->block_cols = bc;
     s->view_exp = false; s->view_of = nullptr;
     s->version = ++g_version;
@@ -239,18 +267,17 @@ int nb200_device_count(int *count) {
 }
 
 int nb200_init(int device) {
-    std::lock_guard<std::recursive_mutex> api_lock(g_api_mu);
     std::lock_guard<std::mutex> lk(g_mu);
-    if (g_ctx) {
-        if (g_ctx->device == device) return NB200_OK;
-        set_error("nb200_init: already bound to device %d (one device per process)", g_ctx->device);
-        return NB200_ERR_STATE;
-    }
     int n = 0;
     NB_CUDA(cudaGetDeviceCount(&n));
-    if (device < 0 || device >= n) {
+    if (device < 0 || device >= n || device >= kMaxDev) {
         set_error("nb200_init: device %d out of range (%d visible); there is no CPU fallback", device, n);
         return NB200_ERR_INVALID;
+    }
+    if (g_dev[device].ctx) {   // idempotent; the calling thread now works on this device
+        tls_dev = device;
+        NB_CUDA(cudaSetDevice(device));
+        return NB200_OK;
     }
     NB_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
@@ -280,41 +307,77 @@ int nb200_init(int device) {
     for (auto &st : c->copy) NB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     for (auto &e : c->up_ev) NB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     NB_CUDA(cudaEventCreateWithFlags(&c->main_ev, cudaEventDisableTiming));
-    g_ctx = c;
+    g_dev[device].ctx = c;
+    if (g_default_dev < 0) g_default_dev = device;
+    tls_dev = device;
+    return NB200_OK;
+}
+
+int nb200_init_devices(const int *devices, int n) {
+    if (!devices || n <= 0) { set_error("nb200_init_devices: invalid arguments"); return NB200_ERR_INVALID; }
+    for (int i = 0; i < n; i++) NB_TRY(nb200_init(devices[i]));
+    return nb200_use_device(devices[0]);
+}
+
+int nb200_use_device(int device) {
+    if (device < 0 || device >= kMaxDev || !g_dev[device].ctx) {
+        set_error("nb200_use_device: device %d has not been initialised (nb200_init / nb200_init_devices)", device);
+        return NB200_ERR_STATE;
+    }
+    tls_dev = device;
+    NB_CUDA(cudaSetDevice(device));
+    return NB200_OK;
+}
+
+int nb200_current_device(int *device) {
+    if (!device) return NB200_ERR_INVALID;
+    *device = cur_dev();
     return NB200_OK;
 }
 
 static void release_lstm_scratch(void);
 static void release_ff_scratch(void);
 
-int nb200_shutdown(void) {
-    std::lock_guard<std::recursive_mutex> api_lock(g_api_mu);
-    std::lock_guard<std::mutex> lk(g_mu);
-    if (!g_ctx) return NB200_OK;
-    cudaStreamSynchronize(g_ctx->stream);
+static void shutdown_device(int d) {
+    DeviceState &D = g_dev[d];
+    Context *c = D.ctx;
+    if (!c) return;
+    std::lock_guard<std::recursive_mutex> api_lock(D.mu);
+    const int saved = tls_dev;
+    tls_dev = d;                       // the scratch / set accessors below address THIS device
+    cudaSetDevice(d);
+    cudaStreamSynchronize(c->stream);
     release_lstm_scratch();
     release_ff_scratch();
-    for (auto &kv : g_sets) {
+    for (auto &kv : D.sets) {
         free_set_storage(kv.second);
         delete kv.second;
     }
-    g_sets.clear();
-    nb_free(g_ctx->ws);
-    nb_free(g_ctx->stage);
-    nb_free(g_ctx->err_flag);
-    cudaFreeHost(g_ctx->err_flag_host);
-    for (auto &e : g_ctx->ev) cudaEventDestroy(e);
-    for (auto &e : g_ctx->chunk_ev) cudaEventDestroy(e);
-    for (auto &e : g_ctx->join_ev) cudaEventDestroy(e);
-    for (auto &st : g_ctx->aux) cudaStreamDestroy(st);
-    for (auto &st : g_ctx->copy) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
-    for (auto &e : g_ctx->up_ev) cudaEventDestroy(e);
-    cudaEventDestroy(g_ctx->main_ev);
-    nb_free(g_ctx->up_stage[0]); nb_free(g_ctx->up_stage[1]);
-    cudaStreamDestroy(g_ctx->own_stream);
-    delete g_ctx;
-    g_ctx = nullptr;
-    pool_release_all();
+    D.sets.clear();
+    nb_free(c->ws);
+    nb_free(c->stage);
+    nb_free(c->err_flag);
+    cudaFreeHost(c->err_flag_host);
+    for (auto &e : c->ev) cudaEventDestroy(e);
+    for (auto &e : c->chunk_ev) cudaEventDestroy(e);
+    for (auto &e : c->join_ev) cudaEventDestroy(e);
+    for (auto &st : c->aux) cudaStreamDestroy(st);
+    for (auto &st : c->copy) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    for (auto &e : c->up_ev) cudaEventDestroy(e);
+    cudaEventDestroy(c->main_ev);
+    nb_free(c->up_stage[0]); nb_free(c->up_stage[1]);
+    cudaStreamDestroy(c->own_stream);
+    delete c;
+    D.ctx = nullptr;
+    pool_release_all();                // this device's cached blocks
+    tls_dev = saved;
+}
+
+int nb200_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int d = 0; d < kMaxDev; d++) shutdown_device(d);
+    g_default_dev = -1;
+    tls_dev = -1;
     return NB200_OK;
 }
 
@@ -331,7 +394,7 @@ int nb200_synchronize(void) {
     return NB200_OK;
 }
 
-int64_t nb200_launch_count(void) { return g_ctx ? g_ctx->launches : 0; }
+int64_t nb200_launch_count(void) { Context *c = ctx(); return c ? c->launches : 0; }
 
 int nb200_set_option(const char *key, int value) {
     if (key && !strcmp(key, "fused_layer1")) { g_opt_fused = value < 0 ? -1 : (value > 2 ? 2 : value); return NB200_OK; }
@@ -411,6 +474,7 @@ int nb200_upload_rect(nb200_set *s, int row0, int col0, const double *host, int 
         return NB200_ERR_INVALID;
     }
     if (s->view_of) { set_error("upload: %s:%s is a read-only view", s->db.c_str(), s->name.c_str()); return NB200_ERR_STATE; }
+    NB_TRY(same_device(c, {s}));
     if (!s->f64) {  // first block of the set: allocate + zero on the compute stream
         NB_TRY(ensure_f64(c, s));
         c->main_dirty = true;
@@ -551,6 +615,7 @@ int nb200_upload_block(nb200_set *s, int block_row, int block_col, const double 
 
 int nb200_download_rect(nb200_set *s, int row0, int col0, double *host, int rows, int cols, int64_t ld) {
     NEED_CTX_RAW();
+    NB_TRY(same_device(c, {s}));
     NB_TRY(wait_set_uploads(c, s));  // only this set's uploads: a download of results must not wait for the next batch's
     c->main_dirty = true;
     if (!s || !host || row0 < 0 || col0 < 0 || rows < 0 || cols < 0 || ld < cols) {
@@ -668,6 +733,7 @@ static int gemm_blocks_impl(int op, nb200_set *a, nb200_set *b, int epilogue, nb
         set_error("gemm_blocks: invalid arguments");
         return NB200_ERR_INVALID;
     }
+    NB_TRY(same_device(c, {a, b, bias}));
     // join predicate + per-pair dimension check (FFTransposeMult.h:38-39,61-65; FFInputLayerJoin.h:30-31,57-60)
     // (LASillyTransposeMultiply1Join.h:24-33,44-47: there the rows of both operands are the contraction index)
     const bool a_t = op == NB200_OP_TN;  // A enters transposed
@@ -819,7 +885,8 @@ struct LstmScratch {
     double *T64 = nullptr;
     size_t G_cap = 0, C_cap = 0, T_cap = 0;
 };
-LstmScratch g_lstm;
+static LstmScratch &lstm_ref() { DeviceState &D = cur_state(); if (!D.lstm) D.lstm = new LstmScratch(); return *static_cast<LstmScratch *>(D.lstm); }
+#define g_lstm (lstm_ref())
 
 int grow_bytes(void **p, size_t *have, size_t need) {
     if (*have >= need) return NB200_OK;
@@ -1194,7 +1261,8 @@ struct FFScratch {  // reused across calls
     FusedScratch fused;             // ring + flags of the fused layer-1 kernel
     L1StreamScratch l1s;            // wave plan of the streamed layer-1 kernel
 };
-static FFScratch g_ff;
+static FFScratch &ff_ref() { DeviceState &D = cur_state(); if (!D.ff) D.ff = new FFScratch(); return *static_cast<FFScratch *>(D.ff); }
+#define g_ff (ff_ref())
 
 // nb200_shutdown: nothing of the fused stage's scratch may outlive the context (a later nb200_init may bind another device)
 static void release_ff_scratch(void) {
@@ -1226,6 +1294,7 @@ int nb200_ff_inference_unit(nb200_set *w1, nb200_set *wo, nb200_set *inputs, nb2
         set_error("ff_inference_unit: invalid arguments");
         return NB200_ERR_INVALID;
     }
+    NB_TRY(same_device(c, {w1, wo, inputs, b1, bo}));
     // wait for the uploads of the five operand sets only (see nb200_upload_commit): the next batch may already be on its
     // way into another set
     for (nb200_set *s : {w1, wo, inputs, b1, bo}) NB_TRY(wait_set_uploads(c, s));

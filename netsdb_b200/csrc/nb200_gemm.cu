@@ -490,7 +490,8 @@ template <int NSUB, int STAGES, bool MC>
 static int launch_impl_2sm(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
                            const CUtensorMap &mv_lo, const GemmArgs &g, int pair_tiles, int splits, cudaStream_t stream) {
     using L = SmemLayout2<NSUB, STAGES>;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};   // function attributes are per device
+    bool &attr_set = attr_set_dev[c->device & 15];
     if (!attr_set) {
         NB_CUDA(cudaFuncSetAttribute(k_block_gemm_2sm<NSUB, STAGES, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
@@ -529,7 +530,8 @@ template <int BN, int STAGES>
 static int launch_impl(Context *c, const CUtensorMap &mu_hi, const CUtensorMap &mu_lo, const CUtensorMap &mv_hi,
                        const CUtensorMap &mv_lo, const GemmArgs &g, int tiles, int splits, cudaStream_t stream) {
     using L = SmemLayout<BN, STAGES>;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};   // function attributes are per device
+    bool &attr_set = attr_set_dev[c->device & 15];
     if (!attr_set) {
         NB_CUDA(cudaFuncSetAttribute(k_block_gemm<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
@@ -986,7 +988,8 @@ int launch_l1_fused(Context *c, const double *x, int64_t x_ld, int rows_total, i
     NB_TRY(make_plane_map(&mring, reinterpret_cast<const __nv_bfloat16 *>(fs->ring), rows_fused, static_cast<int64_t>(ring_kb) * kBlockK, kBlockM));
     NB_TRY(make_plane_map(&mv, reinterpret_cast<const __nv_bfloat16 *>(w1.f16), w1.rows, w1.ldk, 256));
     using L = SmemLayout2<2, 4>;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};   // function attributes are per device
+    bool &attr_set = attr_set_dev[c->device & 15];
     if (!attr_set) {
         NB_CUDA(cudaFuncSetAttribute(k_l1_fused<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
@@ -1153,7 +1156,8 @@ template <int BN, int STAGES>
 static int launch_conv_impl(Context *c, const CUtensorMap &ih, const CUtensorMap &il, const CUtensorMap &kh,
                             const CUtensorMap &kl, const ConvArgs &g, int tiles) {
     using L = SmemLayout<BN, STAGES>;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};   // function attributes are per device
+    bool &attr_set = attr_set_dev[c->device & 15];
     if (!attr_set) {
         NB_CUDA(cudaFuncSetAttribute(k_conv_implicit<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;

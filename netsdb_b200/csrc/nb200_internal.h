@@ -268,6 +268,7 @@ int launch_im2col(Context *c, const double *images, int n, int ch, int h, int w,
 //   colp   bf16 planes with rows = logical cols, K = logical rows
 struct nb200_set {
     std::string db, name;
+    int device = -1;               // the device the set lives on (a thread must work on it: nb200_use_device)
     int total_rows = 0, total_cols = 0, block_rows = 0, block_cols = 0;
     double *f64 = nullptr;
     float *f32 = nullptr;

@@ -579,7 +579,10 @@ int make_w_map(CUtensorMap *m, const void *base, int64_t rows, int64_t ldk, int 
 template <int MT, int SA, int SB>
 int max_clusters(int *out) {
     constexpr bool PROF = false;
-    static int cached = -1;
+    static int cached_dev[16] = {-1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1};   // per device: attributes are
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int &cached = cached_dev[dev & 15];
     if (cached < 0) {
         NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
         cudaLaunchConfig_t cfg{};
@@ -722,7 +725,8 @@ static int launch_part(Context *c, const L1StreamPart &pt, const double *x, int6
     g.prof = prof_on ? prof_dev : nullptr;
     CUtensorMap mw;
     NB_TRY(make_w_map(&mw, w1.f16, w1.rows, w1.ldk, MT == 1 ? 256 : 128));
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};   // function attributes are per device
+    bool &attr_set = attr_set_dev[c->device & 15];
     if (!attr_set) {
         NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));
         NB_CUDA(cudaFuncSetAttribute(k_l1_stream<MT, SA, SB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(SA, SB)));

@@ -20,62 +20,86 @@ namespace nb200 {
 
 namespace {
 constexpr size_t kMaxPooled = size_t(2) << 30;   // larger blocks (the 47.8 GB input sets) go straight to the driver
-constexpr size_t kMaxCached = size_t(16) << 30;  // bytes kept in the free lists
-std::mutex g_pool_mu;
-std::multimap<size_t, void *> g_free;            // size -> block
-std::unordered_map<void *, size_t> g_size;       // every live or cached block of the pool -> its true size
-size_t g_cached = 0;
+constexpr size_t kMaxCached = size_t(16) << 30;  // bytes kept in the free lists, per device
+constexpr int kMaxDev = 16;
+struct Pool {                                    // one per device: a block is only ever handed out on the device it lives on
+    std::mutex mu;
+    std::multimap<size_t, void *> free_blocks;   // size -> block
+    std::unordered_map<void *, size_t> size;     // every live or cached block of the pool -> its true size
+    size_t cached = 0;
+};
+Pool g_pool[kMaxDev];
 
-void trim_locked() {
-    for (auto &kv : g_free) {
-        g_size.erase(kv.second);
+Pool &current_pool() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return g_pool[d >= 0 && d < kMaxDev ? d : 0];
+}
+
+void trim_locked(Pool &P) {
+    for (auto &kv : P.free_blocks) {
+        P.size.erase(kv.second);
         cudaFree(kv.second);
     }
-    g_free.clear();
-    g_cached = 0;
+    P.free_blocks.clear();
+    P.cached = 0;
 }
 }  // namespace
 
 cudaError_t pool_malloc(void **p, size_t bytes) {
     const size_t sz = bytes < 512 ? 512 : (bytes + 511) / 512 * 512;
-    std::lock_guard<std::mutex> lk(g_pool_mu);
+    Pool &P = current_pool();
+    std::lock_guard<std::mutex> lk(P.mu);
     if (sz <= kMaxPooled) {
-        auto it = g_free.lower_bound(sz);
-        if (it != g_free.end() && it->first <= sz + sz / 8) {  // at most 12.5 % larger than asked for
+        auto it = P.free_blocks.lower_bound(sz);
+        if (it != P.free_blocks.end() && it->first <= sz + sz / 8) {  // at most 12.5 % larger than asked for
             *p = it->second;
-            g_cached -= it->first;
-            g_free.erase(it);
+            P.cached -= it->first;
+            P.free_blocks.erase(it);
             return cudaSuccess;
         }
     }
     cudaError_t e = cudaMalloc(p, sz);
     if (e == cudaErrorMemoryAllocation) {  // give the cached blocks back and try once more
         cudaGetLastError();
-        trim_locked();
+        trim_locked(P);
         e = cudaMalloc(p, sz);
     }
-    if (e == cudaSuccess) g_size[*p] = sz;
+    if (e == cudaSuccess) P.size[*p] = sz;
     return e;
 }
 
 cudaError_t pool_free(void *p) {
     if (!p) return cudaSuccess;
-    std::lock_guard<std::mutex> lk(g_pool_mu);
-    auto it = g_size.find(p);
-    if (it == g_size.end()) return cudaFree(p);  // not ours (never happens for library allocations)
+    // the owning pool: the current device's in all but exotic cases (a set destroyed from a thread working elsewhere)
+    Pool *owner = nullptr;
+    {
+        Pool &P = current_pool();
+        std::lock_guard<std::mutex> lk(P.mu);
+        if (P.size.count(p)) owner = &P;
+    }
+    for (int d = 0; d < kMaxDev && !owner; d++) {
+        std::lock_guard<std::mutex> lk(g_pool[d].mu);
+        if (g_pool[d].size.count(p)) owner = &g_pool[d];
+    }
+    if (!owner) return cudaFree(p);  // not ours (never happens for library allocations)
+    std::lock_guard<std::mutex> lk(owner->mu);
+    auto it = owner->size.find(p);
+    if (it == owner->size.end()) return cudaFree(p);
     const size_t sz = it->second;
-    if (sz <= kMaxPooled && g_cached + sz <= kMaxCached) {
-        g_free.emplace(sz, p);
-        g_cached += sz;
+    if (sz <= kMaxPooled && owner->cached + sz <= kMaxCached) {
+        owner->free_blocks.emplace(sz, p);
+        owner->cached += sz;
         return cudaSuccess;
     }
-    g_size.erase(it);
+    owner->size.erase(it);
     return cudaFree(p);
 }
 
-void pool_release_all() {
-    std::lock_guard<std::mutex> lk(g_pool_mu);
-    trim_locked();
+void pool_release_all() {   // the current device's cached blocks
+    Pool &P = current_pool();
+    std::lock_guard<std::mutex> lk(P.mu);
+    trim_locked(P);
 }
 
 }  // namespace nb200
