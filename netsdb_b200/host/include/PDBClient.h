@@ -34,8 +34,10 @@ public:
         bool operator!=(const It &o) const { return idx != o.idx; }
         void operator++() { idx++; }
         It(const std::vector<Handle<T>> *host, int idx) : s(nullptr), idx(idx), n(0), nbc(1), host(host) {}
+        It(const std::pair<std::string, std::string> *names, int idx, int nbc) : s(nullptr), idx(idx), n(0), nbc(nbc), names(names) {}
         Handle<T> operator*() const {
             if constexpr (std::is_base_of<conv2d_memory_fusion::Matrix3D, T>::value) return (*host)[idx];
+            else if (names) return nb200_host::fetch_block_sharded<T>(names->first, names->second, idx / nbc, idx % nbc);
             else return nb200_host::fetch_block<T>(s, idx / nbc, idx % nbc);
         }
 
@@ -43,6 +45,7 @@ public:
         nb200_set *s;
         int idx, n, nbc;
         const std::vector<Handle<T>> *host = nullptr;
+        const std::pair<std::string, std::string> *names = nullptr;   // a set whose rows are spread over several devices
     };
     SetIterator() {}
     explicit SetIterator(const std::vector<Handle<T>> *records) : host(records) {}
@@ -54,13 +57,27 @@ public:
             nbc = (tc + bc - 1) / bc;
         }
     }
-    It begin() { return host ? It(host, 0) : It(s, 0, nbr * nbc, nbc > 0 ? nbc : 1); }
-    It end() { return host ? It(host, static_cast<int>(host->size())) : It(s, nbr * nbc, nbr * nbc, nbc > 0 ? nbc : 1); }
+    // a row-sharded set (NB200_DEVICES > 1): the block grid spans the rows of all devices
+    SetIterator(const std::string &db, const std::string &set, int total_rows, int total_cols, int br, int bc)
+        : names(db, set), sharded(true) {
+        nbr = (total_rows + br - 1) / br;
+        nbc = (total_cols + bc - 1) / bc;
+    }
+    It begin() {
+        if (sharded) return It(&names, 0, nbc > 0 ? nbc : 1);
+        return host ? It(host, 0) : It(s, 0, nbr * nbc, nbc > 0 ? nbc : 1);
+    }
+    It end() {
+        if (sharded) return It(&names, nbr * nbc, nbc > 0 ? nbc : 1);
+        return host ? It(host, static_cast<int>(host->size())) : It(s, nbr * nbc, nbr * nbc, nbc > 0 ? nbc : 1);
+    }
 
 private:
     nb200_set *s = nullptr;
     int nbr = 0, nbc = 0;
     const std::vector<Handle<T>> *host = nullptr;
+    std::pair<std::string, std::string> names;
+    bool sharded = false;
 };
 
 class PDBClient {
@@ -120,7 +137,7 @@ public:
     bool removeSet(const std::string &db, const std::string &set, std::string &) { return drop(db, set); }
     bool deleteSet(std::string db, std::string set) { return drop(db, set); }  // mainClient/headers/PDBClient.h:253
     bool clearSet(const std::string &db, const std::string &set, const std::string &, std::string &) { return drop(db, set); }
-    bool flushData(std::string &errMsg) { return ok(nb200_synchronize(), errMsg); }
+    bool flushData(std::string &errMsg) { return sync_all(errMsg); }
 
     // NOTE the (set, db) order of the pair, as in the reference (FFMatrixUtil.cc:110-111)
     template <class T>
@@ -141,7 +158,7 @@ public:
         }
         for (size_t i = 0; i < data->size(); i++)
             if (!ok(nb200_host::ship_block(db, set, (*data)[i], tr, tc), errMsg)) return false;
-        return ok(nb200_synchronize(), errMsg);  // the caller reuses its allocation block after sendData
+        return sync_all(errMsg);  // the caller reuses its allocation block after sendData
         }
     }
 
@@ -168,6 +185,20 @@ public:
             return it == m.end() ? SetIterator<T>() : SetIterator<T>(&it->second);
         }
         nb200_set *s = nullptr;
+        if (nb200_host::num_devices() > 1 && nb200_host::sharded_sets().count(std::make_pair(db, set))) {
+            int tr = 0, tc = 0, br = 1, bc = 1;
+            for (int d = 0; d < nb200_host::num_devices(); d++) {
+                nb200_use_device(d);
+                int r = 0;
+                if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK || nb200_set_info(s, &r, &tc, &br, &bc) != NB200_OK) {
+                    nb200_use_device(0);
+                    return SetIterator<T>();
+                }
+                tr += r;
+            }
+            nb200_use_device(0);
+            return SetIterator<T>(db, set, tr, tc, br, bc);
+        }
         if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) return SetIterator<T>();
         return SetIterator<T>(s);
     }
@@ -183,10 +214,24 @@ private:
         errMsg = nb200_last_error();
         return false;
     }
+    static bool sync_all(std::string &errMsg) {
+        bool good = true;
+        for (int d = 0; d < nb200_host::num_devices(); d++) {
+            if (nb200_host::num_devices() > 1) nb200_use_device(d);
+            good = ok(nb200_synchronize(), errMsg) && good;
+        }
+        if (nb200_host::num_devices() > 1) nb200_use_device(0);
+        return good;
+    }
     bool drop(const std::string &db, const std::string &set) {
         nb200_host::host_set_drop(db, set);
-        nb200_set *s = nullptr;
-        if (nb200_set_lookup(db.c_str(), set.c_str(), &s) == NB200_OK) nb200_set_destroy(s);
+        for (int d = 0; d < nb200_host::num_devices(); d++) {
+            if (nb200_host::num_devices() > 1) nb200_use_device(d);
+            nb200_set *s = nullptr;
+            if (nb200_set_lookup(db.c_str(), set.c_str(), &s) == NB200_OK) nb200_set_destroy(s);
+        }
+        if (nb200_host::num_devices() > 1) nb200_use_device(0);
+        nb200_host::sharded_sets().erase(std::make_pair(db, set));
         return true;
     }
     std::set<std::pair<std::string, std::string>> declared;

@@ -13,8 +13,10 @@
 //                                                                                   label-exact precision cascade
 // Anything else is rejected: there is no CPU fallback.
 #pragma once
+#include <mutex>
 #include <set>
 #include <sstream>
+#include <thread>
 
 #include "conv_stage.h"
 #include "la_udfs.h"
@@ -31,13 +33,50 @@ inline int precision_from_env() {
     return NB200_PREC_BF16;
 }
 
+// ---- several GPUs from one client process (NB200_DEVICES=n) -------------------------------------------------------
+// The reference partitions a set over the workers of the cluster (CombinedShuffleSink.h:95-98); here the batch rows of
+// the sets named in NB200_SHARD_SETS (default "inputs") are split contiguously over n devices and every other set is
+// replicated, so that each device runs the whole graph on its rows with no exchange.  The (db, set)
+// namespace of the library is per device: the same lowering code runs once per device, on its own thread.
+inline int &num_devices() { static int n = 1; return n; }
+inline std::set<std::pair<std::string, std::string>> &sharded_sets() { static std::set<std::pair<std::string, std::string>> s; return s; }
+inline bool shard_by_name(const std::string &set) {
+    static std::set<std::string> names = [] {
+        std::set<std::string> n;
+        const char *e = getenv("NB200_SHARD_SETS");
+        std::stringstream ss(e ? e : "inputs");
+        std::string t;
+        while (std::getline(ss, t, ',')) if (!t.empty()) n.insert(t);
+        return n;
+    }();
+    return names.count(set) != 0;
+}
+// contiguous row shard of device d: sizes differ by at most one (netsdb_b200/shard.py row_shard)
+inline void row_shard(int total, int world, int d, int *row0, int *rows) {
+    const int base = total / world, extra = total % world;
+    *rows = base + (d < extra ? 1 : 0);
+    *row0 = d * base + std::min(d, extra);
+}
+inline void die_on(int st) {
+    if (st != NB200_OK) {
+        std::cerr << nb200_last_error() << std::endl;  // reference convention: print and exit(1)
+        exit(1);
+    }
+}
+
 inline void ensure_init() {
     static bool done = false;
     if (done) return;
     const char *d = getenv("NB200_DEVICE");
-    if (nb200_init(d ? atoi(d) : 0) != NB200_OK) {
-        std::cerr << nb200_last_error() << std::endl;  // reference convention: print and exit(1)
-        exit(1);
+    const char *nd = getenv("NB200_DEVICES");
+    const int n = nd ? atoi(nd) : 1;
+    if (n > 1) {
+        std::vector<int> devs;
+        for (int i = 0; i < n; i++) devs.push_back(i);
+        die_on(nb200_init_devices(devs.data(), n));
+        num_devices() = n;
+    } else {
+        die_on(nb200_init(d ? atoi(d) : 0));
     }
     done = true;
 }
@@ -47,7 +86,41 @@ inline void ensure_init() {
 // with the 4-argument constructor); the caller derives them from the block grid, i.e. the set is carried with its
 // padding, exactly as the reference carries it
 template <class Block>
+inline int ship_block_one(const std::string &db, const std::string &set, pdb::Handle<Block> &b, int total_rows, int total_cols);
+template <class Block>
 inline int ship_block(const std::string &db, const std::string &set, pdb::Handle<Block> &b, int total_rows = -1, int total_cols = -1) {
+    const int n = num_devices();
+    if (n == 1) return ship_block_one(db, set, b, total_rows, total_cols);
+    int st = NB200_OK;
+    if (!shard_by_name(set)) {                       // replicated: the same block to every device
+        for (int d = 0; d < n && st == NB200_OK; d++) {
+            st = nb200_use_device(d);
+            if (st == NB200_OK) st = ship_block_one(db, set, b, total_rows, total_cols);
+        }
+    } else {                                         // row-sharded: each device gets its rows of the block
+        const int tr = b->getTotalRowNums() > 0 ? b->getTotalRowNums() : total_rows;
+        const int tc = b->getTotalColNums() > 0 ? b->getTotalColNums() : total_cols;
+        const int R = b->getRowNums(), C = b->getColNums();
+        const int blo = b->getBlockRowIndex() * R, bhi = std::min(blo + R, tr);
+        sharded_sets().insert(std::make_pair(db, set));
+        for (int d = 0; d < n && st == NB200_OK; d++) {
+            int r0, nr;
+            row_shard(tr, n, d, &r0, &nr);
+            const int lo = std::max(blo, r0), hi = std::min(bhi, r0 + nr);
+            st = nb200_use_device(d);
+            if (st != NB200_OK) break;
+            nb200_set *s = nullptr;
+            if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) st = nb200_set_create(db.c_str(), set.c_str(), nr, tc, R, C, &s);
+            if (st == NB200_OK && hi > lo)
+                st = nb200_upload_rect(s, lo - r0, b->getBlockColIndex() * C, b->getRawDataHandle()->c_ptr() + static_cast<size_t>(lo - blo) * C,
+                                       hi - lo, C, C);
+        }
+    }
+    nb200_use_device(0);
+    return st;
+}
+template <class Block>
+inline int ship_block_one(const std::string &db, const std::string &set, pdb::Handle<Block> &b, int total_rows, int total_cols) {
     nb200_set *s = nullptr;
     if (nb200_set_lookup(db.c_str(), set.c_str(), &s) != NB200_OK) {
         // nominal block size = size of the first block sent (block (0,0) in ff::loadMatrix's order)
@@ -81,12 +154,82 @@ inline pdb::Handle<Block> fetch_block(nb200_set *s, int br, int bc) {
     return out;
 }
 
+// one block of a row-sharded set, assembled from the devices that hold its rows
+template <class Block = FFMatrixBlock>
+inline pdb::Handle<Block> fetch_block_sharded(const std::string &db, const std::string &set, int br, int bc) {
+    const int n = num_devices();
+    std::vector<nb200_set *> sets(n, nullptr);
+    std::vector<int> rows_of(n, 0);
+    int tr = 0, tc = 0, R = 0, C = 0;
+    for (int d = 0; d < n; d++) {
+        die_on(nb200_use_device(d));
+        die_on(nb200_set_lookup(db.c_str(), set.c_str(), &sets[d]));
+        int r, c, rr, cc;
+        die_on(nb200_set_info(sets[d], &r, &c, &rr, &cc));
+        rows_of[d] = r; tr += r; tc = c; R = rr; C = cc;
+    }
+    nb200_use_device(0);
+    pdb::Handle<Block> out = make_block<Block>(br, bc, R, C, tr, tc);   // allocated before any device work (zeroed)
+    const int blo = br * R, bhi = std::min(blo + R, tr);
+    int off = 0;
+    for (int d = 0; d < n; d++) {
+        const int lo = std::max(blo, off), hi = std::min(bhi, off + rows_of[d]);
+        if (hi > lo) {
+            die_on(nb200_use_device(d));
+            die_on(nb200_download_rect(sets[d], lo - off, bc * C, out->getRawDataHandle()->c_ptr() + static_cast<size_t>(lo - blo) * C, hi - lo,
+                                       C, C));
+        }
+        off += rows_of[d];
+    }
+    nb200_use_device(0);
+    return out;
+}
+
 class FusedStage {
 public:
     std::vector<int32_t> labels;
     nb200_ff_stats stats{};
 
+    // several devices: the same lowering once per device, each on its own thread and its own (db, set) namespace
     bool run(const std::string &jobName, const std::vector<pdb::Handle<pdb::Computation>> &sinks, std::string &errMsg) {
+        const int n = num_devices();
+        if (n == 1) return run_one(jobName, sinks, errMsg);
+        // outputs of a job that scans a sharded set are sharded themselves (every stage of the path is row-local)
+        bool touches_sharded = false;
+        std::vector<std::pair<std::string, std::string>> outs;
+        for (auto &sink : sinks) {
+            auto *w = dynamic_cast<pdb::WriteSetBase *>(sink.ptr().get());
+            if (!w) { errMsg = "sink is not a WriteUserSet"; return false; }
+            outs.push_back(std::make_pair(w->getDatabaseName(), w->getSetName()));
+            touches_sharded |= scans_sharded(sink);
+        }
+        if (per_device.size() != static_cast<size_t>(n)) per_device.assign(n, nullptr);
+        std::vector<std::string> errs(n);
+        std::vector<char> oks(n, 1);
+        std::vector<std::thread> th;
+        for (int d = 0; d < n; d++)
+            th.emplace_back([&, d] {
+                if (nb200_use_device(d) != NB200_OK) { errs[d] = nb200_last_error(); oks[d] = 0; return; }
+                if (!per_device[d]) per_device[d] = std::make_shared<FusedStage>();
+                oks[d] = per_device[d]->run_one(jobName, sinks, errs[d]) ? 1 : 0;
+            });
+        for (auto &t : th) t.join();
+        nb200_use_device(0);
+        for (int d = 0; d < n; d++)
+            if (!oks[d]) { errMsg = "device " + std::to_string(d) + ": " + errs[d]; return false; }
+        if (touches_sharded) {
+            for (auto &o : outs) sharded_sets().insert(o);
+            labels.clear();
+            for (int d = 0; d < n; d++) labels.insert(labels.end(), per_device[d]->labels.begin(), per_device[d]->labels.end());
+        } else {
+            labels = per_device[0]->labels;
+        }
+        stats = per_device[0]->stats;
+        for (int d = 1; d < n; d++) if (per_device[d]->stats.ms_total > stats.ms_total) stats = per_device[d]->stats;
+        return true;
+    }
+
+    bool run_one(const std::string &jobName, const std::vector<pdb::Handle<pdb::Computation>> &sinks, std::string &errMsg) {
         (void)jobName;
         try {
             for (auto &sink : sinks) {
@@ -106,6 +249,16 @@ public:
 private:
     int tmp_id = 0;
     std::map<std::string, std::string> fused_output_of;  // db:yo-set -> pending fused `output` set name
+    std::vector<std::shared_ptr<FusedStage>> per_device;  // several devices: one lowering state per device
+
+    static bool scans_sharded(const pdb::Handle<pdb::Computation> &c) {
+        if (c == nullptr) return false;
+        if (auto *scan = dynamic_cast<pdb::ScanSetBase *>(c.ptr().get()))
+            return sharded_sets().count(std::make_pair(scan->getDatabaseName(), scan->getSetName())) != 0;
+        for (int i = 0; i < c->getNumInputs(); i++)
+            if (scans_sharded(c->getIthInput(i))) return true;
+        return false;
+    }
 
     static void check(int st) {
         if (st != NB200_OK) throw std::runtime_error(nb200_last_error());

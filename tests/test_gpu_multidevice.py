@@ -57,3 +57,40 @@ def test_two_devices_from_two_threads_of_one_process(nb):
     with pytest.raises(nb.Nb200Error):
         nb.ff_inference_unit(full[0], full[1], foreign[1], full[3], full[4], nb.PREC_F16, "md", "bad")
     nb.use_device(0)
+
+
+def test_cpp_driver_shards_inputs_over_two_devices(oracle, tmp_path):
+    """The C++ host shim with NB200_DEVICES=2: PDBClient::sendData splits the rows of `inputs` over the devices (row
+    granular: a block can straddle two devices) and replicates the other sets, executeComputations lowers the graph once
+    per device on its own thread, getSetIterator assembles the blocks of `output` from the devices that hold their rows.
+    The same FFTest driver, the same oracle check as on one device."""
+    import os
+    import subprocess
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from netsdb_b200 import build
+
+    exe = build.build_host()["FFTest"]
+    blk, batch, feat, hid, lab = 100, 250, 640, 300, 12     # 250 rows / 2 = 125: block row 1 straddles the two devices
+    ref = None
+    for ndev in (2, 1):
+        dump = tmp_path / f"dump{ndev}.txt"
+        env = dict(os.environ, NB200_PRECISION="f16", NB200_DEVICES=str(ndev))
+        r = subprocess.run([exe, str(blk), str(blk), str(batch), str(feat), str(hid), str(lab), str(dump)], env=env,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        got = np.loadtxt(dump)
+        if ref is None:
+            X = oracle.load_matrix(oracle.synth_dense(batch, feat, 1), blk, blk)
+            W1 = oracle.load_matrix(oracle.synth_dense(hid, feat, 2), blk, blk)
+            B1 = oracle.load_matrix(oracle.synth_dense(hid, 1, 3), blk, 1)
+            WO = oracle.load_matrix(oracle.synth_dense(lab, hid, 4), blk, blk)
+            BO = oracle.load_matrix(oracle.synth_dense(lab, 1, 5), blk, 1)
+            ref_out, _, ref_labels = oracle.ff_inference_unit(W1, WO, X, B1, BO, threads=2)
+            ref = (ref_out.dense(), ref_labels)
+        assert np.array_equal(got[:, 0].astype(np.int32), ref[1]), ndev      # fused stage's labels, concatenated over devices
+        assert np.array_equal(got[:, 1].astype(np.int32), ref[1]), ndev      # argmax of the `output` set read back
+        assert np.abs(got[:, 2] - ref[0][:, 0]).max() <= 1e-2

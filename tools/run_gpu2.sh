@@ -1,4 +1,2 @@
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 --no-e2e > gpurun_out/bench_n2.json 2> gpurun_out/bench_n2.err; python3 -c "
-import json
-d=json.loads(open('gpurun_out/bench_n2.json').read().strip().splitlines()[-1])
-print({k:d[k] for k in ('value','ms_per_step','scaling')}); print(d['ksharded']); print(d['weak_replicas']); print(d['strong_check']); print(d['breakdown_ms'])"; tail -5 gpurun_out/bench_n2.err
+timeout 900 python -m pytest tests/test_gpu_multidevice.py tests/test_gpu_housekeeping.py tests/test_gpu_l1stream.py -x -q > gpurun_out/pytest_md.log 2>&1; tail -15 gpurun_out/pytest_md.log
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_lstm.py tests/test_la.py tests/test_zz_no_alloc.py -x -q > gpurun_out/pytest_md2.log 2>&1; tail -5 gpurun_out/pytest_md2.log
