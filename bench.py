@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the baseline sample")
+    ap.add_argument("--config", default="c2", choices=["c2", "c4", "c5"],
+                    help="c2 (default): the Amazon-14K FF shape (C3 with --gpus N); c4: conv2d_memory_fusion; c5: word2vec (bench_configs.py)")
     return ap.parse_args()
 
 
@@ -625,7 +627,11 @@ def run_e2e_side_format(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, 
 
 if __name__ == "__main__":
     args = parse()
-    if args.impl == "reference":
+    if args.config != "c2":
+        import bench_configs
+
+        (bench_configs.run_c4 if args.config == "c4" else bench_configs.run_c5)(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)

@@ -282,6 +282,17 @@ int nb200_conv2d_fused(const double *images_host, int n, int c, int h, int w, co
                        const double *bias_host, int kout, int k, int padding, int relu, int precision,
                        int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out);
 
+/* The `img` set of the reference's driver (a set of Image records, conv2d_memory_fusion/headers/Image.h;
+ * PipelinedConv2dMemFuseTest.cc:99-107 loads it, the `image_ops` job scans it) resident on the device: NCHW fp64 as sent,
+ * plus the NHWC operand planes of the implicit GEMM, derived on first use and kept with the set. */
+int nb200_conv2d_images_create(const double *images_host, int n, int c, int h, int w, const char *db, const char *set,
+                               nb200_set **out);
+/* nb200_conv2d_fused on a resident image set: nothing crosses PCIe but the kernels and the bias.  kernel_ms (optional)
+ * receives the device time of the implicit-GEMM launch. */
+int nb200_conv2d_fused_from_set(nb200_set *images, const double *kernels_host, const double *bias_host, int kout, int k,
+                                int padding, int relu, int precision, int block_rows, int block_cols, const char *db,
+                                const char *out_set, nb200_set **out, float *kernel_ms);
+
 /* ConvResultToChunks + ConvChunksToImage (ConvResultToChunks.h:42-103, ConvChunksToImage.h:34-72; the last two
  * jobs of Conv2dMemFuseTest.cc): re-assemble the `result` matrix [(image, window), channel] into num_images images of
  * z channels, each an x * y matrix in window order.  images_host receives num_images * z * x * y doubles (NCHW).

@@ -27,7 +27,7 @@ EXPORTS = [
     "nb200_download_block", "nb200_download_rect", "nb200_set_fill_synth", "nb200_set_invalidate_planes",
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
-    "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_transpose_mult_noalloc",
+    "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_conv2d_images_create", "nb200_conv2d_fused_from_set", "nb200_transpose_mult_noalloc",
     "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell", "nb200_upload_commit", "nb200_set_export_f16", "nb200_set_import_f16",
 ]
 
@@ -100,6 +100,8 @@ def lib():
         L.nb200_conv2d_fused.argtypes = [vp, i, i, i, i, vp, vp, i, i, i, i, i, i, i, C.c_char_p, C.c_char_p,
                                          C.POINTER(vp)]
         L.nb200_conv2d_result_to_images.argtypes = [vp, i, i, i, i, vp]
+        L.nb200_conv2d_images_create.argtypes = [vp, i, i, i, i, C.c_char_p, C.c_char_p, C.POINTER(vp)]
+        L.nb200_conv2d_fused_from_set.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, C.c_char_p, C.c_char_p, C.POINTER(vp), C.POINTER(C.c_float)]
         L.nb200_ff_layer1_partial.argtypes = [vp, vp, i, vp, i64]
         L.nb200_ff_finish_from_layer1.argtypes = [vp, i64, i, vp, vp, vp, i, C.c_float, C.c_char_p, C.c_char_p, C.POINTER(vp), vp, ip]
         L.nb200_set_maxabs.argtypes = [vp, C.POINTER(C.c_float)]
@@ -346,3 +348,32 @@ def conv2d_fused(images: np.ndarray, kernels: np.ndarray, bias: np.ndarray, padd
     check(lib().nb200_conv2d_fused(_hostptr(images), n, c_, h, w, _hostptr(kernels), _hostptr(bias), kout, k, padding,
                                    int(relu), precision, block_rows, block_cols, _b(db), _b(out_set), C.byref(p)))
     return DeviceSet(p)
+
+
+_last_kernel_ms = 0.0
+
+
+def conv2d_images_create(images: np.ndarray, db: str = "conv2d", set_name: str = "img") -> DeviceSet:
+    images = np.ascontiguousarray(images, dtype=np.float64)
+    n, c, h, w = images.shape
+    p = C.c_void_p()
+    check(lib().nb200_conv2d_images_create(_hostptr(images), n, c, h, w, _b(db), _b(set_name), C.byref(p)))
+    return DeviceSet(p)
+
+
+def conv2d_fused_from_set(images: DeviceSet, kernels: np.ndarray, bias: np.ndarray, padding: int, relu: bool, precision: int,
+                          block_rows: int, block_cols: int, db: str = "conv2d", out_set: str = "result") -> DeviceSet:
+    global _last_kernel_ms
+    kernels = np.ascontiguousarray(kernels, dtype=np.float64)
+    bias = np.ascontiguousarray(bias, dtype=np.float64)
+    kout, _, k, _ = kernels.shape
+    p = C.c_void_p()
+    ms = C.c_float(0)
+    check(lib().nb200_conv2d_fused_from_set(images.ptr, _hostptr(kernels), _hostptr(bias), kout, k, padding, int(relu), precision,
+                                            block_rows, block_cols, _b(db), _b(out_set), C.byref(p), C.byref(ms)))
+    _last_kernel_ms = ms.value
+    return DeviceSet(p)
+
+
+def last_kernel_ms() -> float:
+    return _last_kernel_ms

@@ -138,6 +138,7 @@ static void free_set_storage(nb200_set *s) {
     nb_free(s->hb_dev); s->hb_dev = nullptr; s->hb_host.clear(); s->side_format = false;
     free_planes(&s->rowp);
     free_planes(&s->colp);
+    nb_free(s->img_hi); nb_free(s->img_lo); s->img_hi = s->img_lo = nullptr; s->img_n = 0;
 }
 
 #define NEED_CTX_RAW()                                          \
@@ -1757,6 +1758,47 @@ int nb200_conv2d_result_to_images(nb200_set *result, int num_images, int x, int 
     return st;
 }
 
+// the conv2d job on NHWC bf16 image planes: kernel planes, bias, the implicit-GEMM launch; result set (n * hout * wout) x kout
+static int conv2d_fused_planes(Context *c, const __nv_bfloat16 *ihi, const __nv_bfloat16 *ilo, int n, int ch, int h, int w, int cp,
+                               const double *kernels_host, const double *bias_host, int kout, int k, int padding, int relu, int nterms,
+                               int block_rows, int block_cols, const char *db, const char *out_set, nb200_set **out, float *kernel_ms) {
+    const int hout = h + 2 * padding - k + 1, wout = w + 2 * padding - k + 1;
+    double *dker = nullptr;
+    float *dbias = nullptr;
+    Planes kp;
+    nb200_set *o = nullptr;
+    int st = make_set(db, out_set, n * hout * wout, kout, block_rows, block_cols, &o);
+    const size_t on = static_cast<size_t>(n) * hout * wout * kout;
+    const size_t kelems = static_cast<size_t>(kout) * ch * k * k;
+    std::vector<float> bias32(kout);
+    for (int i = 0; i < kout; i++) bias32[i] = static_cast<float>(bias_host[i]);
+    if (st == NB200_OK && (nb_malloc(&dker, kelems * sizeof(double)) != cudaSuccess || nb_malloc(&dbias, static_cast<size_t>(kout) * sizeof(float)) != cudaSuccess ||
+                           nb_malloc(&o->f32, (on ? on : 1) * sizeof(float)) != cudaSuccess)) {
+        set_error("conv2d: out of device memory");
+        st = NB200_ERR_NOMEM;
+    }
+    if (st == NB200_OK) {
+        o->f32_ld = kout;
+        if (cudaMemcpyAsync(dker, kernels_host, kelems * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+            cudaMemcpyAsync(dbias, bias32.data(), static_cast<size_t>(kout) * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) {
+            set_error("conv2d: kernel upload failed");
+            st = NB200_ERR_CUDA;
+        }
+    }
+    if (st == NB200_OK) st = launch_kernel_to_planes(c, dker, kout, ch, k, cp, &kp, nterms == 3);
+    if (st == NB200_OK && kernel_ms) cudaEventRecord(c->ev[6], c->stream);
+    if (st == NB200_OK) st = launch_conv_implicit(c, ihi, ilo, n, h, w, cp, kp, kout, k, padding, nterms, dbias, relu, o->f32);
+    if (st == NB200_OK && kernel_ms) cudaEventRecord(c->ev[7], c->stream);
+    if (st == NB200_OK) st = check_kernel_fault(c, "conv2d_fused");
+    cudaStreamSynchronize(c->stream);   // bias32 / the caller's kernels were read asynchronously
+    if (st == NB200_OK && kernel_ms) cudaEventElapsedTime(kernel_ms, c->ev[6], c->ev[7]);
+    nb_free(dker); nb_free(dbias);
+    free_planes(&kp);
+    if (st != NB200_OK) return st;
+    *out = o;
+    return NB200_OK;
+}
+
 int nb200_conv2d_fused(const double *images_host, int n, int ch, int h, int w, const double *kernels_host,
                        const double *bias_host, int kout, int k, int padding, int relu, int precision, int block_rows,
                        int block_cols, const char *db, const char *out_set, nb200_set **out) {
@@ -1785,42 +1827,69 @@ int nb200_conv2d_fused(const double *images_host, int n, int ch, int h, int w, c
     const int nterms = precision == NB200_PREC_BF16X3 ? 3 : 1;
     const int cp = static_cast<int>(round_up(ch, 64));
     const size_t img_elems = static_cast<size_t>(n) * ch * h * w, nhwc_elems = static_cast<size_t>(n) * h * w * cp;
-    double *dimg = nullptr, *dker = nullptr;
-    float *dbias = nullptr;
+    double *dimg = nullptr;
     __nv_bfloat16 *ihi = nullptr, *ilo = nullptr;
-    Planes kp;
-    nb200_set *o = nullptr;
-    int st = make_set(db, out_set, n * hout * wout, kout, block_rows, block_cols, &o);
-    auto cleanup = [&]() {
-        cudaStreamSynchronize(c->stream);
-        nb_free(dimg); nb_free(dker); nb_free(dbias); nb_free(ihi); nb_free(ilo);
-        free_planes(&kp);
-    };
-#define CONV_TRY(x) do { if (st == NB200_OK && (x) != cudaSuccess) { set_error("conv2d_fused: %s failed", #x); st = NB200_ERR_CUDA; } } while (0)
-    CONV_TRY(nb_malloc(&dimg, img_elems * sizeof(double)));
-    CONV_TRY(nb_malloc(&dker, static_cast<size_t>(kout) * ch * k * k * sizeof(double)));
-    CONV_TRY(nb_malloc(&dbias, static_cast<size_t>(kout) * sizeof(float)));
-    CONV_TRY(nb_malloc(&ihi, nhwc_elems * sizeof(__nv_bfloat16)));
-    if (nterms == 3) CONV_TRY(nb_malloc(&ilo, nhwc_elems * sizeof(__nv_bfloat16)));
-    const size_t on = static_cast<size_t>(n) * hout * wout * kout;
-    if (st == NB200_OK) {
-        CONV_TRY(nb_malloc(&o->f32, (on ? on : 1) * sizeof(float)));
-        o->f32_ld = kout;
+    int st = NB200_OK;
+    if (nb_malloc(&dimg, img_elems * sizeof(double)) != cudaSuccess || nb_malloc(&ihi, nhwc_elems * sizeof(__nv_bfloat16)) != cudaSuccess ||
+        (nterms == 3 && nb_malloc(&ilo, nhwc_elems * sizeof(__nv_bfloat16)) != cudaSuccess)) {
+        set_error("conv2d_fused: out of device memory");
+        st = NB200_ERR_NOMEM;
     }
-    std::vector<float> bias32(kout);
-    for (int i = 0; i < kout; i++) bias32[i] = static_cast<float>(bias_host[i]);
-    CONV_TRY(cudaMemcpyAsync(dimg, images_host, img_elems * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    CONV_TRY(cudaMemcpyAsync(dker, kernels_host, static_cast<size_t>(kout) * ch * k * k * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    CONV_TRY(cudaMemcpyAsync(dbias, bias32.data(), static_cast<size_t>(kout) * sizeof(float), cudaMemcpyHostToDevice, c->stream));
-#undef CONV_TRY
+    if (st == NB200_OK && cudaMemcpyAsync(dimg, images_host, img_elems * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) {
+        set_error("conv2d_fused: image upload failed");
+        st = NB200_ERR_CUDA;
+    }
     if (st == NB200_OK) st = launch_nchw_to_nhwc_planes(c, dimg, n, ch, h, w, cp, ihi, ilo);
-    if (st == NB200_OK) st = launch_kernel_to_planes(c, dker, kout, ch, k, cp, &kp, nterms == 3);
-    if (st == NB200_OK) st = launch_conv_implicit(c, ihi, ilo, n, h, w, cp, kp, kout, k, padding, nterms, dbias, relu, o->f32);
-    if (st == NB200_OK) st = check_kernel_fault(c, "conv2d_fused");
-    cleanup();
-    if (st != NB200_OK) return st;
-    *out = o;
+    if (st == NB200_OK)
+        st = conv2d_fused_planes(c, ihi, ilo, n, ch, h, w, cp, kernels_host, bias_host, kout, k, padding, relu, nterms, block_rows, block_cols, db,
+                                 out_set, out, nullptr);
+    cudaStreamSynchronize(c->stream);
+    nb_free(dimg); nb_free(ihi); nb_free(ilo);
+    return st;
+}
+
+// The reference keeps the images as a set of Image records (conv2d_memory_fusion/headers/Image.h) that the `image_ops` job
+// scans (PipelinedConv2dMemFuseTest.cc:136-180).  nb200_conv2d_images_create is that set on the device: the NCHW fp64 data
+// as they were sent, plus -- derived on first use and kept until the set changes -- the NHWC bf16 operand planes the
+// implicit GEMM reads.  A conv2d job on a resident image set then moves nothing but the result.
+int nb200_conv2d_images_create(const double *images_host, int n, int ch, int h, int w, const char *db, const char *set, nb200_set **out) {
+    NEED_CTX();
+    if (!images_host || n <= 0 || ch <= 0 || h <= 0 || w <= 0 || !db || !set || !out) { set_error("conv2d_images_create: invalid arguments"); return NB200_ERR_INVALID; }
+    nb200_set *s = nullptr;
+    NB_TRY(make_set(db, set, n * ch * h, w, h, w, &s));   // as a matrix: one (h x w) block per (image, channel)
+    const size_t elems = static_cast<size_t>(n) * ch * h * w;
+    NB_CUDA(nb_malloc(&s->f64, elems * sizeof(double)));
+    NB_CUDA(cudaMemcpyAsync(s->f64, images_host, elems * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));             // the caller's buffer is free again
+    s->img_n = n; s->img_c = ch; s->img_h = h; s->img_w = w;
+    *out = s;
     return NB200_OK;
+}
+
+int nb200_conv2d_fused_from_set(nb200_set *images, const double *kernels_host, const double *bias_host, int kout, int k, int padding,
+                                int relu, int precision, int block_rows, int block_cols, const char *db, const char *out_set,
+                                nb200_set **out, float *kernel_ms) {
+    NEED_CTX();
+    if (!images || images->img_n <= 0 || !images->f64 || !kernels_host || !bias_host || kout <= 0 || kout > 256 || k <= 0 || padding < 0 || !db ||
+        !out_set || !out || precision == NB200_PREC_FP64 || precision < 0 || precision > 3) {
+        set_error("conv2d_fused_from_set: invalid arguments (an image set of nb200_conv2d_images_create, kout <= 256, a tensor-core precision)");
+        return NB200_ERR_INVALID;
+    }
+    NB_TRY(same_device(c, {images}));
+    const int n = images->img_n, ch = images->img_c, h = images->img_h, w = images->img_w;
+    if (h + 2 * padding - k + 1 <= 0 || w + 2 * padding - k + 1 <= 0) { set_error("conv2d_fused_from_set: kernel larger than image"); return NB200_ERR_SHAPE; }
+    const int nterms = precision == NB200_PREC_BF16X3 ? 3 : 1;
+    const int cp = static_cast<int>(round_up(ch, 64));
+    const size_t nhwc = static_cast<size_t>(n) * h * w * cp;
+    if (!images->img_hi || (nterms == 3 && !images->img_lo)) {   // derive the operand planes once
+        nb_free(images->img_hi); nb_free(images->img_lo);
+        images->img_hi = images->img_lo = nullptr;
+        NB_CUDA(nb_malloc(&images->img_hi, nhwc * sizeof(__nv_bfloat16)));
+        NB_CUDA(nb_malloc(&images->img_lo, nhwc * sizeof(__nv_bfloat16)));
+        NB_TRY(launch_nchw_to_nhwc_planes(c, images->f64, n, ch, h, w, cp, images->img_hi, images->img_lo));
+    }
+    return conv2d_fused_planes(c, images->img_hi, nterms == 3 ? images->img_lo : nullptr, n, ch, h, w, cp, kernels_host, bias_host, kout, k, padding,
+                               relu, nterms, block_rows, block_cols, db, out_set, out, kernel_ms);
 }
 
 }  // extern "C"

@@ -286,6 +286,9 @@ struct nb200_set {
     std::vector<const double *> hb_host;  // the pointer table as given (kept: its upload is asynchronous)
     int hb_edge_ld = 0, hb_exp = 0;
     bool side_format = false;
+    // an image set (nb200_conv2d_images_create): NCHW fp64 in f64, NHWC bf16 operand planes derived on first use
+    int img_n = 0, img_c = 0, img_h = 0, img_w = 0;
+    __nv_bfloat16 *img_hi = nullptr, *img_lo = nullptr;
     bool view_exp = false;         // downloads apply exp() (the `yo` view of the logits)
     nb200_set *view_of = nullptr;  // set whose storage a view reads
 };

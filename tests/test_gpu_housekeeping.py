@@ -88,3 +88,24 @@ def test_shutdown_releases_the_fused_stage_and_init_starts_clean(oracle):
     b = run()
     assert np.array_equal(a, b)
     # (the session fixture `nb`, if another test created it, stays valid: init is idempotent for the same device)
+
+
+def test_conv2d_on_a_resident_image_set_equals_the_host_image_call(nb, oracle):
+    """nb200_conv2d_images_create + nb200_conv2d_fused_from_set (the reference's `img` set resident on the device, the conv2d
+    job of PipelinedConv2dMemFuseTest.cc:249-273 on it) against nb200_conv2d_fused on host images and against the oracle's
+    image_flat x kernel_flat block GEMM; twice, so that the cached operand planes are used."""
+    rng = np.random.default_rng(7)
+    n, c, h, w, kout, k = 3, 5, 20, 17, 6, 3
+    imgs = rng.uniform(-0.5, 0.5, size=(n, c, h, w))
+    kern = rng.uniform(-0.5, 0.5, size=(kout, c, k, k))
+    bias = rng.uniform(-0.5, 0.5, size=kout)
+    ref = oracle.transpose_mult_agg(oracle.image_flat(imgs, k, 1, 1, 50, 50), oracle.kernel_flat(kern, bias, 50, 50), 2).dense()
+    iset = nb.conv2d_images_create(imgs, "convset", "img")
+    for prec, tol in (("bf16x3", 1e-4), ("bf16", 2e-2)):
+        host_call = nb.conv2d_fused(imgs, kern, bias, 1, False, nb.PRECISIONS[prec], 50, 50, "convset", "r_host").download_dense()
+        for _ in range(2):
+            got = nb.conv2d_fused_from_set(iset, kern, bias, 1, False, nb.PRECISIONS[prec], 50, 50, "convset", "r_set").download_dense()
+            assert np.array_equal(got, host_call)
+            assert np.abs(got - ref).max() <= tol * np.abs(ref).max()
+        assert nb.last_kernel_ms() > 0
+    iset.destroy()
