@@ -1137,19 +1137,305 @@ k_conv_implicit(const __grid_constant__ CUtensorMap map_img_hi, const __grid_con
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Persistent form of the implicit GEMM (single-term precisions).  One CTA per SM walks a contiguous run of
+// output rows (tile = up to 128 output positions of one output row; order image, 128-wide segment, row), and:
+//   * the filter planes (taps x channel blocks x BN x 128 B) are loaded into shared memory ONCE per CTA;
+//   * each INPUT row is loaded once per CTA and used for all k x k taps: a ring slot holds 128 + k - 1 pixels of
+//     one input row (64 channels = one 128-byte swizzle row per pixel), the k horizontal taps are k operand
+//     descriptors whose start address is moved by 128 B per tap (the 128-byte swizzle is a function of the
+//     shared-memory address bits, so a view shifted by whole rows stays consistent with what TMA wrote), and
+//     the k vertical taps are the k most recent slots.  Moving to the next output row loads one new input row:
+//     the image crosses L2 -> SM about once instead of k*k times;
+//   * accumulators rotate through up to four TMEM slots so the epilogue of one tile runs under the MMAs of the
+//     next ones; the epilogue adds bias (+ ReLU), stages 32-column chunks in swizzled shared memory and writes
+//     them with TMA stores (rows past wout and columns past kout are clipped by the tensor map).
+// ---------------------------------------------------------------------------------------------
+struct ConvPArgs {
+    int hout, wout, k, pad, cblocks, kout, wsegs;
+    int tiles;        // n * wsegs * hout
+    int rb;           // ring depth in row units (one unit = one input row x 64 channels)
+    int row_bytes;    // bytes TMA delivers per unit = (128 + k - 1) * 128
+    int row_stride;   // ring slot pitch (row_bytes rounded up to 1024)
+    int ker_bytes;    // taps * cblocks * BN * 128
+    const float *bias;
+    int relu;
+    int *err_flag;
+    unsigned int idesc;
+    int base_off;     // 1: put the row shift into the descriptor's base-offset field as well
+};
+constexpr int kConvStageBytes = 128 * 128;   // one 32-column fp32 chunk of a tile
+constexpr int kConvMaxRing = 16;
+
+__device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ bool bar_red_or_named(int id, int nthreads, bool pred) {
+    uint32_t r;
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.u32 q, %3, 0;\n\t"
+        "bar.red.or.pred p, %1, %2, q;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(r)
+        : "r"(id), "r"(nthreads), "r"(static_cast<uint32_t>(pred))
+        : "memory");
+    return r != 0;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+k_conv_persist(const __grid_constant__ CUtensorMap map_img, const __grid_constant__ CUtensorMap map_ker,
+               const __grid_constant__ CUtensorMap map_out, const ConvPArgs g) {
+    constexpr int NACC = (512 / BN) < 4 ? (512 / BN) : 4;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t *s_ker = smem;
+    uint8_t *s_ring = s_ker + g.ker_bytes;
+    uint8_t *s_stage = s_ring + g.rb * g.row_stride;
+    float *s_bias = reinterpret_cast<float *>(s_stage + 2 * kConvStageBytes);
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(s_bias + BN);
+    uint64_t *empty_bar = full_bar + kConvMaxRing;
+    uint64_t *ker_bar = empty_bar + kConvMaxRing;
+    uint64_t *tmem_full = ker_bar + 1;
+    uint64_t *tmem_empty = tmem_full + NACC;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + NACC);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t0 = static_cast<int>(static_cast<long long>(blockIdx.x) * g.tiles / gridDim.x);
+    const int t1 = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * g.tiles / gridDim.x);
+    const int taps = g.k * g.k;
+    const int units = g.k * g.cblocks;   // row units one tile reads
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_img);
+        tma_prefetch_desc(&map_ker);
+        tma_prefetch_desc(&map_out);
+        for (int s = 0; s < g.rb; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(ker_bar, 1);
+        for (int a = 0; a < NACC; a++) {
+            mbar_init(&tmem_full[a], 1);
+            mbar_init(&tmem_empty[a], 128);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(ker_bar, static_cast<uint32_t>(g.ker_bytes));
+            for (int kb = 0; kb < taps * g.cblocks; kb++)
+                tma_load_2d(&map_ker, ker_bar, s_ker + static_cast<size_t>(kb) * BN * 128, kb * kBlockK, 0, kEvictLast);
+            int seq = 0;
+            bool ok = true;
+            for (int t = t0; t < t1 && ok; t++) {
+                const int ho = t % g.hout, seg = (t / g.hout) % g.wsegs, img = t / (g.hout * g.wsegs);
+                const bool cont = t > t0 && ho > 0;
+                for (int fi = cont ? g.k - 1 : 0; fi < g.k && ok; fi++)
+                    for (int cb = 0; cb < g.cblocks; cb++, seq++) {
+                        const int slot = seq % g.rb;
+                        const uint32_t ph = (seq / g.rb) & 1;
+                        if (!mbar_wait(&empty_bar[slot], ph ^ 1)) { atomicExch(g.err_flag, 311); ok = false; break; }
+                        mbar_arrive_expect_tx(&full_bar[slot], static_cast<uint32_t>(g.row_bytes));
+                        tma_load_4d(&map_img, &full_bar[slot], s_ring + static_cast<size_t>(slot) * g.row_stride, cb * kBlockK,
+                                    seg * kBlockM - g.pad, ho - g.pad + fi, img, kEvictNormal);
+                    }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            bool ok = mbar_wait(ker_bar, 0);
+            if (!ok) atomicExch(g.err_flag, 312);
+            const uint32_t ker_base = smem_u32(s_ker), ring_base = smem_u32(s_ring);
+            int s = 0;
+            for (int t = t0; t < t1 && ok; t++) {
+                const int i = t - t0;
+                const int ho = t % g.hout;
+                if (i > 0) s += (ho > 0) ? g.cblocks : units;
+                const int acc = i % NACC;
+                const uint32_t aph = (i / NACC) & 1;
+                if (!mbar_wait(&tmem_empty[acc], aph ^ 1)) { atomicExch(g.err_flag, 313); break; }
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                uint32_t accum = 0;
+                for (int fi = 0; fi < g.k && ok; fi++)
+                    for (int cb = 0; cb < g.cblocks; cb++) {
+                        const int seq = s + fi * g.cblocks + cb;
+                        const int slot = seq % g.rb;
+                        if (!mbar_wait(&full_bar[slot], (seq / g.rb) & 1)) { atomicExch(g.err_flag, 314); ok = false; break; }
+                        tc_fence_after();
+                        const uint32_t a_base = ring_base + slot * g.row_stride;
+                        for (int fj = 0; fj < g.k; fj++) {
+                            const int kb = (fi * g.k + fj) * g.cblocks + cb;
+                            uint64_t da = umma_desc_k_sw128(a_base + fj * 128);
+                            if (g.base_off) da |= static_cast<uint64_t>(fj & 7) << 49;
+                            const uint64_t db = umma_desc_k_sw128(ker_base + kb * BN * 128);
+#pragma unroll
+                            for (int kk = 0; kk < kBlockK / kUmmaK; kk++) {
+                                umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, g.idesc, accum);
+                                accum = 1;
+                            }
+                        }
+                    }
+                if (!ok) break;
+                if (t + 1 < t1) {   // units the next tile no longer reads go back to the producer once these MMAs are done
+                    const int rel = (ho + 1 < g.hout) ? g.cblocks : units;
+                    for (int u = 0; u < rel; u++) umma_commit(&empty_bar[(s + u) % g.rb]);
+                }
+                umma_commit(&tmem_full[acc]);
+            }
+        }
+    } else {
+        const int et = threadIdx.x - 64;    // 0..127
+        const int q = warp & 3;             // the TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;        // row of the tile = output position wo0 + r
+        for (int cidx = et; cidx < BN; cidx += 128) s_bias[cidx] = (g.bias && cidx < g.kout) ? g.bias[cidx] : 0.f;
+        bar_sync_named(1, 128);
+        const int nchunks = (g.kout + 31) / 32;
+        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        const uint32_t stage_u = smem_u32(s_stage);
+        uint32_t chunk_ctr = 0;
+        for (int t = t0; t < t1; t++) {
+            const int i = t - t0;
+            const int ho = t % g.hout, seg = (t / g.hout) % g.wsegs, img = t / (g.hout * g.wsegs);
+            const int acc = i % NACC;
+            bool ok = mbar_wait(&tmem_full[acc], (i / NACC) & 1);
+            if (!ok) atomicExch(g.err_flag, 315);
+            ok = !bar_red_or_named(1, 128, !ok);   // all 128 threads leave together if any of them timed out
+            tc_fence_after();
+            if (!ok) break;
+            for (int c = 0; c < nchunks; c++, chunk_ctr++) {
+                const uint32_t buf = chunk_ctr & 1;
+                if (et == 0) bulk_wait_group_read<1>();   // the store that last read this buffer is done with it
+                bar_sync_named(1, 128);
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(lane_addr + acc * BN + c * 32, v);
+                tmem_ld_wait();
+                if (c == nchunks - 1) {
+                    tc_fence_before();
+                    mbar_arrive(&tmem_empty[acc]);
+                }
+                const uint32_t row_u = stage_u + buf * kConvStageBytes + r * 128;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    float f[4];
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        f[e] = __uint_as_float(v[4 * j + e]) + s_bias[c * 32 + 4 * j + e];
+                        if (g.relu) f[e] = fmaxf(f[e], 0.f);
+                    }
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_u + ((j ^ (r & 7)) << 4)), "f"(f[0]), "f"(f[1]),
+                                 "f"(f[2]), "f"(f[3])
+                                 : "memory");
+                }
+                fence_proxy_async_smem();
+                bar_sync_named(1, 128);
+                if (et == 0) {
+                    tma_store_3d(&map_out, s_stage + buf * kConvStageBytes, c * 32, seg * kBlockM, img * g.hout + ho);
+                    bulk_commit_group();
+                }
+            }
+        }
+        if (et == 0) bulk_wait_group<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 // NHWC bf16 image: dims {Cp, W, H, N}; box {64, 128, 1, 1}; out-of-range coordinates (the padding) read as zero
-static int make_image_map(CUtensorMap *m, const __nv_bfloat16 *base, int n, int h, int w, int cp) {
+static int make_image_map(CUtensorMap *m, const __nv_bfloat16 *base, int n, int h, int w, int cp, int box_pixels = kBlockM) {
     EncodeTiledFn enc = get_encode();
     if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return NB200_ERR_CUDA; }
     cuuint64_t dims[4] = {(cuuint64_t)cp, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
     cuuint64_t strides[3] = {(cuuint64_t)cp * 2, (cuuint64_t)w * cp * 2, (cuuint64_t)h * w * cp * 2};
-    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)kBlockM, 1, 1};
+    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)box_pixels, 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16 *>(base), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (image) failed with CUresult %d", (int)r); return NB200_ERR_CUDA; }
     return NB200_OK;
+}
+
+// fp32 result as a 3-D tensor {kout, wout, n*hout}: box {32 columns, 128 positions, 1 output row}, 128-byte swizzle
+static int make_conv_out_map(CUtensorMap *m, float *out, int kout, int wout, long long rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return NB200_ERR_CUDA; }
+    cuuint64_t dims[3] = {(cuuint64_t)kout, (cuuint64_t)wout, (cuuint64_t)rows};
+    cuuint64_t strides[2] = {(cuuint64_t)kout * 4, (cuuint64_t)wout * kout * 4};
+    cuuint32_t box[3] = {32, (cuuint32_t)kBlockM, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (conv result) failed with CUresult %d", (int)r); return NB200_ERR_CUDA; }
+    return NB200_OK;
+}
+
+template <int BN>
+static int launch_conv_persist_impl(Context *c, const CUtensorMap &im, const CUtensorMap &km, const CUtensorMap &om, const ConvPArgs &g,
+                                    size_t smem_bytes, int grid) {
+    static size_t attr_bytes_dev[16] = {};   // function attributes are per device
+    size_t &attr_bytes = attr_bytes_dev[c->device & 15];
+    if (attr_bytes < smem_bytes) {
+        NB_CUDA(cudaFuncSetAttribute(k_conv_persist<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_bytes)));
+        attr_bytes = smem_bytes;
+    }
+    k_conv_persist<BN><<<grid, kThreads, smem_bytes, c->stream>>>(im, km, om, g);
+    c->launches++;
+    NB_CUDA(cudaGetLastError());
+    return NB200_OK;
+}
+
+// returns NB200_OK and *done = true when the persistent kernel took the job
+static int try_conv_persist(Context *c, const __nv_bfloat16 *img_hi, int n, int h, int w, int cp, const Planes &ker, int kout, int k, int pad,
+                            const float *bias, int relu, float *out, int BN, bool *done) {
+    *done = false;
+    static const int mode = [] { const char *e = getenv("NB200_CONV_PERSIST"); return e ? atoi(e) : 1; }();   // 0 off, 1 on, 2 on + base-offset field
+    const int hout = h + 2 * pad - k + 1, wout = w + 2 * pad - k + 1;
+    if (!mode || k > 8 || (kout & 3) || (reinterpret_cast<uintptr_t>(out) & 15)) return NB200_OK;
+    ConvPArgs g{};
+    g.hout = hout; g.wout = wout; g.k = k; g.pad = pad; g.cblocks = cp / 64; g.kout = kout;
+    g.wsegs = static_cast<int>(ceil_div(wout, kBlockM));
+    const long long tiles = static_cast<long long>(n) * g.wsegs * hout;
+    if (tiles > (1ll << 30)) return NB200_OK;
+    g.tiles = static_cast<int>(tiles);
+    const int box_pixels = kBlockM + k - 1;
+    g.row_bytes = box_pixels * 128;
+    g.row_stride = static_cast<int>(round_up(g.row_bytes, 1024));
+    g.ker_bytes = k * k * g.cblocks * BN * 128;
+    const size_t fixed = static_cast<size_t>(g.ker_bytes) + 2 * kConvStageBytes + BN * 4 + (2 * kConvMaxRing + 1 + 8) * 8 + 16 + 1024;
+    const size_t budget = 227 * 1024;
+    const int units = k * g.cblocks;
+    if (fixed + static_cast<size_t>(units + g.cblocks) * g.row_stride > budget) return NB200_OK;   // filter or row window too large
+    g.rb = static_cast<int>(std::min<size_t>(kConvMaxRing, (budget - fixed) / g.row_stride));
+    g.rb = std::min(g.rb, units + 4 * g.cblocks);   // a window plus four rows ahead is plenty
+    g.bias = bias; g.relu = relu; g.err_flag = c->err_flag;
+    g.idesc = umma_idesc_bf16(kBlockM, BN);
+    g.base_off = mode == 2;
+    CUtensorMap im, km, om;
+    NB_TRY(make_image_map(&im, img_hi, n, h, w, cp, box_pixels));
+    NB_TRY(make_plane_map(&km, ker.hi, ker.rows, ker.ldk, BN));
+    NB_TRY(make_conv_out_map(&om, out, kout, wout, static_cast<long long>(n) * hout));
+    const size_t smem_bytes = fixed + static_cast<size_t>(g.rb) * g.row_stride;
+    const int grid = static_cast<int>(std::min<long long>(tiles, c->sm_count > 0 ? c->sm_count : 148));
+    *done = true;
+    if (BN == 64) return launch_conv_persist_impl<64>(c, im, km, om, g, smem_bytes, grid);
+    if (BN == 128) return launch_conv_persist_impl<128>(c, im, km, om, g, smem_bytes, grid);
+    return launch_conv_persist_impl<256>(c, im, km, om, g, smem_bytes, grid);
 }
 
 template <int BN, int STAGES>
@@ -1182,6 +1468,11 @@ int launch_conv_implicit(Context *c, const __nv_bfloat16 *img_hi, const __nv_bfl
     g.nterms = nterms; g.out = out; g.bias = bias; g.relu = relu; g.err_flag = c->err_flag;
     const int BN = kout <= 64 ? 64 : (kout <= 128 ? 128 : 256);
     g.idesc = umma_idesc_bf16(kBlockM, BN);
+    if (nterms == 1) {
+        bool done = false;
+        NB_TRY(try_conv_persist(c, img_hi, n, h, w, cp, ker, kout, k, pad, bias, relu, out, BN, &done));
+        if (done) return NB200_OK;
+    }
     CUtensorMap ih, il, kh, kl;
     NB_TRY(make_image_map(&ih, img_hi, n, h, w, cp));
     NB_TRY(make_plane_map(&kh, ker.hi, ker.rows, ker.ldk, BN));

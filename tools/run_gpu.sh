@@ -1,1 +1,6 @@
-timeout 600 python -m pytest tests/test_gpu_housekeeping.py -x -q > gpurun_out/pytest_hk.log 2>&1; tail -15 gpurun_out/pytest_hk.log
+for m in 0 1 2; do
+  NB200_CONV_PERSIST=$m timeout 300 python tools/conv_check.py > gpurun_out/conv_check_$m.log 2>&1; echo "mode $m rc=$?"; tail -12 gpurun_out/conv_check_$m.log
+done
+for m in 0 1 2; do
+  NB200_CONV_PERSIST=$m timeout 300 python tools/conv_check.py c4 > gpurun_out/conv_c4_$m.log 2>&1; echo "c4 mode $m rc=$?"; tail -4 gpurun_out/conv_c4_$m.log
+done
