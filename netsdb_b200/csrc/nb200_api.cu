@@ -1786,9 +1786,9 @@ static int conv2d_fused_planes(Context *c, const __nv_bfloat16 *ihi, const __nv_
         }
     }
     if (st == NB200_OK) st = launch_kernel_to_planes(c, dker, kout, ch, k, cp, &kp, nterms == 3);
-    if (st == NB200_OK && kernel_ms) cudaEventRecord(c->ev[6], c->stream);
+    if (kernel_ms) { c->time_ev0 = c->ev[6]; c->time_ev1 = c->ev[7]; }   // recorded right around the kernel launch
     if (st == NB200_OK) st = launch_conv_implicit(c, ihi, ilo, n, h, w, cp, kp, kout, k, padding, nterms, dbias, relu, o->f32);
-    if (st == NB200_OK && kernel_ms) cudaEventRecord(c->ev[7], c->stream);
+    c->time_ev0 = c->time_ev1 = nullptr;
     if (st == NB200_OK) st = check_kernel_fault(c, "conv2d_fused");
     cudaStreamSynchronize(c->stream);   // bias32 / the caller's kernels were read asynchronously
     if (st == NB200_OK && kernel_ms) cudaEventElapsedTime(kernel_ms, c->ev[6], c->ev[7]);

@@ -1144,12 +1144,16 @@ k_conv_implicit(const __grid_constant__ CUtensorMap map_img_hi, const __grid_con
 //   * each INPUT row is loaded once per CTA and used for all k x k taps: a ring slot holds 128 + k - 1 pixels of
 //     one input row (64 channels = one 128-byte swizzle row per pixel), the k horizontal taps are k operand
 //     descriptors whose start address is moved by 128 B per tap (the 128-byte swizzle is a function of the
-//     shared-memory address bits, so a view shifted by whole rows stays consistent with what TMA wrote), and
-//     the k vertical taps are the k most recent slots.  Moving to the next output row loads one new input row:
-//     the image crosses L2 -> SM about once instead of k*k times;
+//     shared-memory address bits, so a view shifted by whole rows stays consistent with what TMA wrote: measured,
+//     the descriptor's base-offset field stays 0), and the k vertical taps are the k most recent slots.  Moving
+//     to the next output row loads one new input row: the image crosses L2 -> SM about once instead of k*k times;
 //   * accumulators rotate through up to four TMEM slots so the epilogue of one tile runs under the MMAs of the
-//     next ones; the epilogue adds bias (+ ReLU), stages 32-column chunks in swizzled shared memory and writes
-//     them with TMA stores (rows past wout and columns past kout are clipped by the tensor map).
+//     next ones; two groups of four epilogue warps take alternate 32-column chunks of a tile: bias (+ ReLU),
+//     swizzled staging in shared memory, one TMA store per chunk (rows past wout and columns past kout are
+//     clipped by the tensor map).
+// The MMA warp runs its loop warp-uniformly (one elected lane issues): descriptors are built with 32-bit adds on
+// their low word, ring slots and phases are tracked incrementally, no division in the loop -- a first version
+// whose single thread spent ~5,000 cycles per tile on address arithmetic was bound by exactly that.
 // ---------------------------------------------------------------------------------------------
 struct ConvPArgs {
     int hout, wout, k, pad, cblocks, kout, wsegs;
@@ -1162,10 +1166,11 @@ struct ConvPArgs {
     int relu;
     int *err_flag;
     unsigned int idesc;
-    int base_off;     // 1: put the row shift into the descriptor's base-offset field as well
+    int debug;        // development: 1 no result stores, 2 no MMAs
 };
 constexpr int kConvStageBytes = 128 * 128;   // one 32-column fp32 chunk of a tile
 constexpr int kConvMaxRing = 16;
+constexpr int kConvThreads = 352;            // warp 0 TMA, warps 1-2 MMA, warps 3..6 and 7..10 the two epilogue groups
 
 __device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -1184,8 +1189,23 @@ __device__ __forceinline__ bool bar_red_or_named(int id, int nthreads, bool pred
     return r != 0;
 }
 
+// tcgen05.mma with both descriptors given as (low word, shared high word); executed by the whole (converged) warp,
+// one elected lane issues -- the operands then stay in uniform registers
+__device__ __forceinline__ void umma_f16_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                              uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\t.reg .b64 da, db;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 template <int BN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kConvThreads, 1)
 k_conv_persist(const __grid_constant__ CUtensorMap map_img, const __grid_constant__ CUtensorMap map_ker,
                const __grid_constant__ CUtensorMap map_out, const ConvPArgs g) {
     constexpr int NACC = (512 / BN) < 4 ? (512 / BN) : 4;
@@ -1218,7 +1238,7 @@ k_conv_persist(const __grid_constant__ CUtensorMap map_img, const __grid_constan
         mbar_init(ker_bar, 1);
         for (int a = 0; a < NACC; a++) {
             mbar_init(&tmem_full[a], 1);
-            mbar_init(&tmem_empty[a], 128);
+            mbar_init(&tmem_empty[a], 256);
         }
         fence_barrier_init();
     }
@@ -1236,117 +1256,160 @@ k_conv_persist(const __grid_constant__ CUtensorMap map_img, const __grid_constan
             mbar_arrive_expect_tx(ker_bar, static_cast<uint32_t>(g.ker_bytes));
             for (int kb = 0; kb < taps * g.cblocks; kb++)
                 tma_load_2d(&map_ker, ker_bar, s_ker + static_cast<size_t>(kb) * BN * 128, kb * kBlockK, 0, kEvictLast);
-            int seq = 0;
+            int slot = 0;
+            uint32_t ph = 0;
             bool ok = true;
             for (int t = t0; t < t1 && ok; t++) {
                 const int ho = t % g.hout, seg = (t / g.hout) % g.wsegs, img = t / (g.hout * g.wsegs);
                 const bool cont = t > t0 && ho > 0;
                 for (int fi = cont ? g.k - 1 : 0; fi < g.k && ok; fi++)
-                    for (int cb = 0; cb < g.cblocks; cb++, seq++) {
-                        const int slot = seq % g.rb;
-                        const uint32_t ph = (seq / g.rb) & 1;
+                    for (int cb = 0; cb < g.cblocks; cb++) {
                         if (!mbar_wait(&empty_bar[slot], ph ^ 1)) { atomicExch(g.err_flag, 311); ok = false; break; }
                         mbar_arrive_expect_tx(&full_bar[slot], static_cast<uint32_t>(g.row_bytes));
                         tma_load_4d(&map_img, &full_bar[slot], s_ring + static_cast<size_t>(slot) * g.row_stride, cb * kBlockK,
-                                    seg * kBlockM - g.pad, ho - g.pad + fi, img, kEvictNormal);
+                                    seg * kBlockM - g.pad, ho - g.pad + fi, img, kEvictFirst);
+                        if (++slot == g.rb) { slot = 0; ph ^= 1; }
                     }
             }
         }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            bool ok = mbar_wait(ker_bar, 0);
-            if (!ok) atomicExch(g.err_flag, 312);
-            const uint32_t ker_base = smem_u32(s_ker), ring_base = smem_u32(s_ring);
-            int s = 0;
-            for (int t = t0; t < t1 && ok; t++) {
-                const int i = t - t0;
-                const int ho = t % g.hout;
-                if (i > 0) s += (ho > 0) ? g.cblocks : units;
-                const int acc = i % NACC;
-                const uint32_t aph = (i / NACC) & 1;
-                if (!mbar_wait(&tmem_empty[acc], aph ^ 1)) { atomicExch(g.err_flag, 313); break; }
+    } else if (warp == 1 || warp == 2) {
+        // two MMA warps take alternate tiles (a single warp spends ~60 cycles of its own instruction stream per
+        // tcgen05.mma, twice what the tensor pipe needs for a 128 x 64 x 16 step).  Warp-uniform loop, one elected lane issues.
+        const int mw = warp - 1;
+        bool ok = mbar_wait(ker_bar, 0);
+        if (!ok && lane == 0) atomicExch(g.err_flag, 312);
+        tc_fence_after();
+        constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version 1, SWIZZLE_128B
+        const uint32_t ker_lo = ((smem_u32(s_ker) >> 4) & 0x3FFFu) | (1u << 16);
+        const uint32_t ring_lo = ((smem_u32(s_ring) >> 4) & 0x3FFFu) | (1u << 16);
+        const uint32_t slot_step = static_cast<uint32_t>(g.row_stride) >> 4;
+        constexpr uint32_t kb_step = (BN * 128) >> 4;
+        const uint32_t tap_step = g.cblocks * kb_step;
+        int slot = 0;           // ring slot and phase of the tile's first row unit
+        uint32_t ph = 0;
+        int ho = t0 % g.hout;
+        int acc = 0;
+        uint32_t aph = 0;
+        for (int t = t0; t < t1 && ok; t++) {
+            const bool last_row = ho + 1 == g.hout;
+            {   // both warps wait for every row unit once, in load order (a parity wait on a slot is only meaningful while
+                // the slot's previous use is known to be complete), whichever warp multiplies the tile
+                const int first_new = (t > t0 && ho > 0) ? units - g.cblocks : 0;
+                int us = slot;
+                uint32_t up = ph;
+                for (int u = 0; u < units; u++) {
+                    if (u >= first_new && !mbar_wait(&full_bar[us], up)) { if (lane == 0) atomicExch(g.err_flag, 314); ok = false; break; }
+                    if (++us == g.rb) { us = 0; up ^= 1; }
+                }
+                if (!ok) break;
+            }
+            if (((t - t0) & 1) == mw) {
+                if (!mbar_wait(&tmem_empty[acc], aph ^ 1)) { if (lane == 0) atomicExch(g.err_flag, 313); break; }
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 uint32_t accum = 0;
-                for (int fi = 0; fi < g.k && ok; fi++)
-                    for (int cb = 0; cb < g.cblocks; cb++) {
-                        const int seq = s + fi * g.cblocks + cb;
-                        const int slot = seq % g.rb;
-                        if (!mbar_wait(&full_bar[slot], (seq / g.rb) & 1)) { atomicExch(g.err_flag, 314); ok = false; break; }
-                        tc_fence_after();
-                        const uint32_t a_base = ring_base + slot * g.row_stride;
-                        for (int fj = 0; fj < g.k; fj++) {
-                            const int kb = (fi * g.k + fj) * g.cblocks + cb;
-                            uint64_t da = umma_desc_k_sw128(a_base + fj * 128);
-                            if (g.base_off) da |= static_cast<uint64_t>(fj & 7) << 49;
-                            const uint64_t db = umma_desc_k_sw128(ker_base + kb * BN * 128);
+                int us = slot;
+                uint32_t b_lo = ker_lo;
+                if (!(g.debug & 2)) {
+                    for (int fi = 0; fi < g.k; fi++) {
+                        for (int cb = 0; cb < g.cblocks; cb++) {
+                            uint32_t aj = ring_lo + us * slot_step;
+                            uint32_t bj = b_lo + cb * kb_step;
+                            for (int fj = 0; fj < g.k; fj++) {
 #pragma unroll
-                            for (int kk = 0; kk < kBlockK / kUmmaK; kk++) {
-                                umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, g.idesc, accum);
-                                accum = 1;
+                                for (int kk = 0; kk < kBlockK / kUmmaK; kk++) {
+                                    umma_f16_lohi(d_tmem, aj + 2 * kk, bj + 2 * kk, desc_hi, g.idesc, accum);
+                                    accum = 1;
+                                }
+                                aj += 8;          // next horizontal tap: one pixel = 128 B further
+                                bj += tap_step;
                             }
+                            if (++us == g.rb) us = 0;
                         }
+                        b_lo += g.k * tap_step;
                     }
-                if (!ok) break;
-                if (t + 1 < t1) {   // units the next tile no longer reads go back to the producer once these MMAs are done
-                    const int rel = (ho + 1 < g.hout) ? g.cblocks : units;
-                    for (int u = 0; u < rel; u++) umma_commit(&empty_bar[(s + u) % g.rb]);
                 }
-                umma_commit(&tmem_full[acc]);
+                if (lane == 0) umma_commit(&tmem_full[acc]);
+                __syncwarp();
             }
+            slot += last_row ? units : g.cblocks;
+            if (slot >= g.rb) { slot -= g.rb; ph ^= 1; }
+            ho = last_row ? 0 : ho + 1;
+            if (++acc == NACC) { acc = 0; aph ^= 1; }
         }
     } else {
-        const int et = threadIdx.x - 64;    // 0..127
-        const int q = warp & 3;             // the TMEM lane quarter this warp may read
-        const int r = q * 32 + lane;        // row of the tile = output position wo0 + r
-        for (int cidx = et; cidx < BN; cidx += 128) s_bias[cidx] = (g.bias && cidx < g.kout) ? g.bias[cidx] : 0.f;
-        bar_sync_named(1, 128);
+        const int ew = warp - 3;                  // epilogue warp 0..7
+        const int grp = ew >> 2;                  // epilogue group: chunks grp, grp + 2, ...
+        const int gt = (ew & 3) * 32 + lane;      // thread within the group
+        const int q = warp & 3;                   // the TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;              // row of the tile = output position wo0 + r
+        for (int cidx = ew * 32 + lane; cidx < BN; cidx += 256) s_bias[cidx] = (g.bias && cidx < g.kout) ? g.bias[cidx] : 0.f;
+        bar_sync_named(3, 256);
         const int nchunks = (g.kout + 31) / 32;
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-        const uint32_t stage_u = smem_u32(s_stage);
-        uint32_t chunk_ctr = 0;
+        uint8_t *stage = s_stage + grp * kConvStageBytes;
+        const uint32_t row_u = smem_u32(stage) + r * 128;
+        const int bar_id = 1 + grp;
+        int ho = t0 % g.hout, seg = (t0 / g.hout) % g.wsegs, img = t0 / (g.hout * g.wsegs);
+        int acc = 0;
+        uint32_t aph = 0;
+        int slot = 0;
         for (int t = t0; t < t1; t++) {
-            const int i = t - t0;
-            const int ho = t % g.hout, seg = (t / g.hout) % g.wsegs, img = t / (g.hout * g.wsegs);
-            const int acc = i % NACC;
-            bool ok = mbar_wait(&tmem_full[acc], (i / NACC) & 1);
+            bool ok = mbar_wait(&tmem_full[acc], aph);
             if (!ok) atomicExch(g.err_flag, 315);
-            ok = !bar_red_or_named(1, 128, !ok);   // all 128 threads leave together if any of them timed out
+            ok = !bar_red_or_named(bar_id, 128, !ok);   // the whole group leaves together if any thread timed out
             tc_fence_after();
             if (!ok) break;
-            for (int c = 0; c < nchunks; c++, chunk_ctr++) {
-                const uint32_t buf = chunk_ctr & 1;
-                if (et == 0) bulk_wait_group_read<1>();   // the store that last read this buffer is done with it
-                bar_sync_named(1, 128);
+            // this tile and, seen earlier in order, every tile before it are complete: the row units no later tile reads go
+            // back to the producer (the MMA warps cannot do it with tcgen05.commit, which only covers the issuing warp's MMAs)
+            const int step = (ho + 1 == g.hout) ? units : g.cblocks;
+            if (grp == 0 && gt == 0 && t + 1 < t1) {
+                int rs = slot;
+                for (int u = 0; u < step; u++) {
+                    mbar_arrive(&empty_bar[rs]);
+                    if (++rs == g.rb) rs = 0;
+                }
+            }
+            slot += step;
+            if (slot >= g.rb) slot -= g.rb;
+            for (int c = grp; c < nchunks; c += 2) {
                 uint32_t v[32];
                 tmem_ld_32x32b_x32(lane_addr + acc * BN + c * 32, v);
                 tmem_ld_wait();
-                if (c == nchunks - 1) {
-                    tc_fence_before();
-                    mbar_arrive(&tmem_empty[acc]);
-                }
-                const uint32_t row_u = stage_u + buf * kConvStageBytes + r * 128;
+                float f[32];
+                const float4 *b4 = reinterpret_cast<const float4 *>(s_bias + c * 32);
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
-                    float f[4];
-#pragma unroll
-                    for (int e = 0; e < 4; e++) {
-                        f[e] = __uint_as_float(v[4 * j + e]) + s_bias[c * 32 + 4 * j + e];
-                        if (g.relu) f[e] = fmaxf(f[e], 0.f);
-                    }
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_u + ((j ^ (r & 7)) << 4)), "f"(f[0]), "f"(f[1]),
-                                 "f"(f[2]), "f"(f[3])
-                                 : "memory");
+                    const float4 bb = b4[j];
+                    f[4 * j] = __uint_as_float(v[4 * j]) + bb.x;
+                    f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + bb.y;
+                    f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + bb.z;
+                    f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + bb.w;
                 }
-                fence_proxy_async_smem();
-                bar_sync_named(1, 128);
-                if (et == 0) {
-                    tma_store_3d(&map_out, s_stage + buf * kConvStageBytes, c * 32, seg * kBlockM, img * g.hout + ho);
+                if (g.relu) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) f[j] = fmaxf(f[j], 0.f);
+                }
+                if (gt == 0) bulk_wait_group_read<0>();   // the group's previous store is done reading the staging buffer
+                bar_sync_named(bar_id, 128);
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_u + ((j ^ (r & 7)) << 4)), "f"(f[4 * j]),
+                                 "f"(f[4 * j + 1]), "f"(f[4 * j + 2]), "f"(f[4 * j + 3])
+                                 : "memory");
+                bar_sync_named(bar_id, 128);
+                if (gt == 0 && !(g.debug & 1)) {
+                    fence_proxy_async_smem();   // by the issuing thread, after the barrier that ordered the group's writes before it
+                    tma_store_3d(&map_out, stage, c * 32, seg * kBlockM, img * g.hout + ho);
                     bulk_commit_group();
                 }
             }
+            tc_fence_before();
+            mbar_arrive(&tmem_empty[acc]);
+            if (++acc == NACC) { acc = 0; aph ^= 1; }
+            if (++ho == g.hout) { ho = 0; if (++seg == g.wsegs) { seg = 0; img++; } }
         }
-        if (et == 0) bulk_wait_group<0>();
+        if (gt == 0) bulk_wait_group<0>();
     }
     tc_fence_before();
     __syncthreads();
@@ -1394,7 +1457,9 @@ static int launch_conv_persist_impl(Context *c, const CUtensorMap &im, const CUt
         NB_CUDA(cudaFuncSetAttribute(k_conv_persist<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_bytes)));
         attr_bytes = smem_bytes;
     }
-    k_conv_persist<BN><<<grid, kThreads, smem_bytes, c->stream>>>(im, km, om, g);
+    if (c->time_ev0) cudaEventRecord(c->time_ev0, c->stream);
+    k_conv_persist<BN><<<grid, kConvThreads, smem_bytes, c->stream>>>(im, km, om, g);
+    if (c->time_ev1) cudaEventRecord(c->time_ev1, c->stream);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     return NB200_OK;
@@ -1404,7 +1469,7 @@ static int launch_conv_persist_impl(Context *c, const CUtensorMap &im, const CUt
 static int try_conv_persist(Context *c, const __nv_bfloat16 *img_hi, int n, int h, int w, int cp, const Planes &ker, int kout, int k, int pad,
                             const float *bias, int relu, float *out, int BN, bool *done) {
     *done = false;
-    static const int mode = [] { const char *e = getenv("NB200_CONV_PERSIST"); return e ? atoi(e) : 1; }();   // 0 off, 1 on, 2 on + base-offset field
+    static const int mode = [] { const char *e = getenv("NB200_CONV_PERSIST"); return e ? atoi(e) : 1; }();   // 0: tile-per-CTA kernel
     const int hout = h + 2 * pad - k + 1, wout = w + 2 * pad - k + 1;
     if (!mode || k > 8 || (kout & 3) || (reinterpret_cast<uintptr_t>(out) & 15)) return NB200_OK;
     ConvPArgs g{};
@@ -1425,7 +1490,8 @@ static int try_conv_persist(Context *c, const __nv_bfloat16 *img_hi, int n, int 
     g.rb = std::min(g.rb, units + 4 * g.cblocks);   // a window plus four rows ahead is plenty
     g.bias = bias; g.relu = relu; g.err_flag = c->err_flag;
     g.idesc = umma_idesc_bf16(kBlockM, BN);
-    g.base_off = mode == 2;
+    static const int dbg = [] { const char *e = getenv("NB200_CONV_DEBUG"); return e ? atoi(e) : 0; }();
+    g.debug = dbg;
     CUtensorMap im, km, om;
     NB_TRY(make_image_map(&im, img_hi, n, h, w, cp, box_pixels));
     NB_TRY(make_plane_map(&km, ker.hi, ker.rows, ker.ldk, BN));
@@ -1448,7 +1514,9 @@ static int launch_conv_impl(Context *c, const CUtensorMap &ih, const CUtensorMap
         NB_CUDA(cudaFuncSetAttribute(k_conv_implicit<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
     }
+    if (c->time_ev0) cudaEventRecord(c->time_ev0, c->stream);
     k_conv_implicit<BN, STAGES><<<tiles, kThreads, L::kTotal, c->stream>>>(ih, il, kh, kl, g);
+    if (c->time_ev1) cudaEventRecord(c->time_ev1, c->stream);
     c->launches++;
     NB_CUDA(cudaGetLastError());
     return NB200_OK;

@@ -46,6 +46,7 @@ struct Context {
     size_t stage_bytes = 0;
     int64_t launches = 0;
     cudaEvent_t ev[8] = {};
+    cudaEvent_t time_ev0 = nullptr, time_ev1 = nullptr;   // when set: recorded right around the next timed kernel launch
     // K-chunk pipelining of layer 1: conversion of chunk j+1 runs beside the GEMM of chunk j
     cudaStream_t aux[3] = {};        // [0] conversion, [1],[2] alternating GEMM streams
     cudaEvent_t chunk_ev[64] = {};   // conversion of chunk j done

@@ -2,8 +2,7 @@
 
 python tools/conv_check.py            shapes with padding, several 128-wide segments, >64 channels, 64/128/256 filters
 python tools/conv_check.py c4         the conv2d_memory_fusion bench shape (64 x 64ch x 112 x 112, 3x3, 64 filters): kernel time
-Environment (read once per process): NB200_CONV_PERSIST=0 (tile-per-CTA kernel) | 1 (persistent kernel) | 2 (persistent,
-row shift also in the descriptor's base-offset field).
+Environment (read once per process): NB200_CONV_PERSIST=0 (tile-per-CTA kernel) | 1 (persistent kernel) .
 """
 import os
 import sys
