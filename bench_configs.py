@@ -83,6 +83,16 @@ def run_c4(a):
     err = float(np.abs(got[idx] - ref).max() / np.abs(ref).max())
     peak_tf, peak_hbm, src = _peaks()
     alg_bytes = n * h * w * c * 2.0 + n * hout * wout * kout * 4.0   # bf16 NHWC image read once + fp32 result written once
+    traffic = None   # DRAM bytes per launch from the committed ncu capture, while the kernel source is the one profiled
+    try:
+        import hashlib
+        root = os.path.dirname(os.path.abspath(__file__))
+        tj = json.load(open(os.path.join(root, "profiles", "r02_traffic_conv.json")))
+        sha = hashlib.sha256(open(os.path.join(root, "netsdb_b200", "csrc", "nb200_gemm.cu"), "rb").read()).hexdigest()[:16]
+        if tj.get("kernel_source_sha16") == sha:
+            traffic = tj["k_conv_persist"]["dram_bytes_read"] + tj["k_conv_persist"]["dram_bytes_write"]
+    except (OSError, KeyError, ValueError):
+        pass
     cpu = None
     if not a.no_cpu_baseline:
         from oracle import ff_oracle as fo
@@ -103,8 +113,9 @@ def run_c4(a):
                 e2e=dict(value=n / (e_ms / 1e3), unit="images/s", h2d_bytes_per_step=int(imgs.nbytes), d2h_bytes_per_step=int(out_host.nbytes),
                          ms_per_step=e_ms, note="pinned fp64 NCHW images in, fp64 result blocks out, every step"),
                 gpu_launches=int(launches),
-                roofline=dict(bound="hbm", kernel="k_conv_implicit (4-D TMA implicit GEMM, bias + ReLU epilogue)", achieved=alg_bytes / (k_ms / 1e3) / 1e9,
-                              peak=peak_hbm, unit="GB/s", frac=alg_bytes / (k_ms / 1e3) / 1e9 / peak_hbm, traffic=None, peak_source=src,
+                roofline=dict(bound="hbm", kernel="k_conv_persist (persistent 4-D TMA implicit GEMM: filter planes resident, each input row loaded once, bias + ReLU + TMA-store epilogue)",
+                              achieved=alg_bytes / (k_ms / 1e3) / 1e9,
+                              peak=peak_hbm, unit="GB/s", frac=alg_bytes / (k_ms / 1e3) / 1e9 / peak_hbm, traffic=traffic, peak_source=src,
                               ms_per_launch=k_ms, tensor_tflops=flops / (k_ms / 1e3) / 1e12, tensor_frac=flops / (k_ms / 1e3) / 1e12 / peak_tf),
                 cpu_baseline=cpu, parity_sample_rel_err=err)
     print(json.dumps(line), flush=True)
@@ -168,7 +179,7 @@ def run_c5(a):
                             l2="the slab (80 GB) exceeds L2, no flush needed",
                             logit_tolerance=f"sampled outputs within {err:.1e} of max|result| of fp64 numpy (bound 2.5e-3 for f16)"),
                 e2e=None, gpu_launches=int(launches),
-                roofline=dict(bound="hbm", kernel="layer-1 path of nb200_ff_layer1_partial (fp64 -> fp16 conversion + block GEMM)", achieved=alg_bytes / (ms / 1e3) / 1e9,
+                roofline=dict(bound="hbm", kernel="nb200_ff_layer1_partial: k_l1_stream (fp64 inputs streamed once, converted in registers, tcgen05 cta_group::2; the hidden half past dim 500 multiplies zero rows) + k_l1s_reduce", achieved=alg_bytes / (ms / 1e3) / 1e9,
                               peak=peak_hbm, unit="GB/s", frac=alg_bytes / (ms / 1e3) / 1e9 / peak_hbm, traffic=None, peak_source=src,
                               tensor_tflops=flops / (ms / 1e3) / 1e12, tensor_frac=flops / (ms / 1e3) / 1e12 / peak_tf),
                 cpu_baseline=None, parity_sample_rel_err=err,

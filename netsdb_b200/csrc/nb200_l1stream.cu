@@ -662,8 +662,13 @@ static_assert(sizeof(L1StreamSeg) == sizeof(Seg), "plan segments are handed to t
 
 int g_l1_stream_mt = 0;   // nb200_set_option("l1_stream_mt"): 0 = choose by padding, 1 / 2 = force the cluster shape
 
+// Hidden sizes in (256, 512] leave the second hidden half of every cluster multiplying zero rows (the TMA boxes of W1 rows
+// >= N are zero-filled): wasted tensor work, but the kernel is bound by streaming X and still beats the separate conversion
+// + GEMM kernels there (word2vec, dim 500: 16.7 ms against 23.7 ms per 10,000 x 1,000,000 slab).  NB200_L1S_MIN_N moves
+// the lower bound for measurements.
 bool l1_stream_supported(const double *x, int64_t x_ld, int64_t cols, int N, const Planes &w1) {
-    return N > 512 && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && (x_ld & 3) == 0 &&
+    static const int min_n = [] { const char *e = getenv("NB200_L1S_MIN_N"); return e ? atoi(e) : 256; }();
+    return N > min_n && N <= 1024 && w1.f16_valid && w1.ldk % kBK == 0 && w1.ldk >= cols && (x_ld & 3) == 0 &&
            (reinterpret_cast<uintptr_t>(x) & 31) == 0 && cols >= 8 * kBK;
 }
 

@@ -36,7 +36,8 @@ def _sets(nb, oracle, batch, feat, hid, lab, blk):
 
 
 @pytest.mark.parametrize("mt", [1, 2])
-@pytest.mark.parametrize("shape", [(1250, 8256, 1000, 40, 1000), (300, 8228, 1000, 17, 500), (2600, 4160, 1024, 9, 520), (5, 4100, 600, 7, 100)])
+@pytest.mark.parametrize("shape", [(1250, 8256, 1000, 40, 1000), (300, 8228, 1000, 17, 500), (2600, 4160, 1024, 9, 520), (5, 4100, 600, 7, 100),
+                                   (900, 8200, 500, 12, 1000), (640, 4608, 300, 33, 512)])
 def test_inference_unit_through_the_stream_kernel_vs_oracle(stream_opts, oracle, shape, mt):
     nb = stream_opts
     batch, feat, hid, lab, blk = shape

@@ -2,6 +2,8 @@
 (the DRAM bytes per launch that bench.py reports as roofline.traffic while the kernel's source is the one profiled).
 
 python tools/make_ncu_digest.py gpurun_out/r02_l1stream.ncu-rep r02_ncu_l1stream
+python tools/make_ncu_digest.py gpurun_out/conv_persist.ncu-rep r02_ncu_conv_persist conv     (the C4 conv2d kernel ->
+                                                                                              profiles/r02_traffic_conv.json)
 """
 import csv
 import hashlib
@@ -33,6 +35,19 @@ def main():
     unit = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Tbyte": 1e12}
     rd = float(m["dram__bytes_read.sum"][0].replace(",", "")) * unit[m["dram__bytes_read.sum"][1]]
     wr = float(m["dram__bytes_write.sum"][0].replace(",", "")) * unit[m["dram__bytes_write.sum"][1]]
+    conv = len(sys.argv) > 3 and sys.argv[3] == "conv"
+    if conv:
+        alg = 64 * 112 * 112 * 64 * 2.0 + 64 * 110 * 110 * 64 * 4.0
+        lines += ["", f"DRAM bytes per launch: read {rd / 1e6:.1f} MB + write {wr / 1e6:.1f} MB = {(rd + wr) / 1e6:.1f} MB; algorithmic (bf16 NHWC image "
+                  f"once + fp32 result once) {alg / 1e6:.1f} MB -> {(rd + wr) / alg:.3f} x (part of the result is still in L2 when the kernel ends)"]
+        open(os.path.join(ROOT, "profiles", name + "_summary.txt"), "w").write("\n".join(lines) + "\n")
+        src = open(os.path.join(ROOT, "netsdb_b200", "csrc", "nb200_gemm.cu"), "rb").read()
+        json.dump({"kernel_source_sha16": hashlib.sha256(src).hexdigest()[:16], "report": os.path.basename(rep),
+                   "workload": "conv2d_memory_fusion C4: 64 x 64ch x 112 x 112, 3x3, 64 filters, bf16",
+                   "k_conv_persist": {"dram_bytes_read": rd, "dram_bytes_write": wr, "algorithmic_bytes": alg}},
+                  open(os.path.join(ROOT, "profiles", "r02_traffic_conv.json"), "w"), indent=1)
+        print("\n".join(lines))
+        return
     alg = 10000 * 597540 * 8.0 + 1000 * 597540 * 2.0
     lines += ["", f"DRAM bytes per launch: read {rd / 1e9:.2f} GB + write {wr / 1e9:.3f} GB = {(rd + wr) / 1e9:.2f} GB; algorithmic "
               f"(X fp64 once + W1 fp16 once) {alg / 1e9:.2f} GB -> {(rd + wr) / alg:.3f} x",
