@@ -203,6 +203,23 @@ int nb200_set_import_f16(nb200_set *set, const void *plane_host, int64_t ldk, in
 int nb200_gemm_blocks(int op, nb200_set *a, nb200_set *b, int epilogue, nb200_set *bias, int precision,
                       const char *db, const char *out_set, nb200_set **out);
 
+/* FullyConnectedNetwork (src/FF_proj/headers/FullyConnectedNetwork.h:62-123; driver src/tests/source/FCProjTest.cc:88-97)
+ * and SemanticClassifier (src/word2vec/headers/SemanticClassifier.h:43-141): a SelectionComp<FFMatrixBlock, FFMatrixBlock>
+ * whose projection runs a two-layer network on every block of the input set.  The block's raw buffer (block_rows x
+ * block_cols, zero-padded at the set's edges) is viewed as a row-major features x batch matrix x0 -- whatever the block's
+ * own shape; it must hold at least features * batch values -- and
+ *     y0 = relu(w0 x0 + b0)                   w0: hidden x features, row-major, b0: hidden
+ *     out = outLabel(sigmoid(w1 y0 + b1))     w1: labels x hidden, b1: labels; 1 where 1 / (1 + exp(-z)) > 0.5, else 0
+ * is written as a labels x batch block with the input block's (blockRow, blockCol): the output set has
+ * ceil(rows / block_rows) * labels rows and ceil(cols / block_cols) * batch columns in labels x batch blocks.  (The
+ * reference stamps each output block's totalRows / totalCols with labels / batch (SemanticClassifier) or leaves them at
+ * -1 (FullyConnectedNetwork); a set here has one pair of totals.)  FullyConnectedNetwork draws its weights from
+ * std::random_device in its constructor and SemanticClassifier uses all-ones: both are host arrays here.  Evaluated in
+ * fp64 (tensor-core DMMA): the output is a thresholded sign.  The input may be an fp64 set or the fp32 result of a
+ * tensor-core GEMM (the FFAggMatrix below SemanticClassifier in TestSemanticClassifier.cc:108-124). */
+int nb200_udf_dense2(nb200_set *in, int features, int batch, int hidden, int labels, const double *w0_host, const double *b0_host,
+                     const double *w1_host, const double *b1_host, const char *db, const char *out_set, nb200_set **out);
+
 /* LSTMThreeWaySum / LSTMTwoSum (src/LSTM/headers/LSTMThreeWaySum.h:39-95, LSTMTwoSum.h:24-64): the join on equal
  * (blockRow, blockCol) keys followed by out = act(a + b + c) per element, for whole sets at once.  b and c may be
  * NULL (c NULL: LSTMTwoSum; both NULL: the activation mapped over a, which is the tanh LSTMHiddenState applies to its

@@ -50,7 +50,9 @@ REF_LA_DRIVERS = [("TestLA04_netsdb", "/root/reference/src/tests/source/TestLA04
                   ("TestLA07_netsdb", "/root/reference/src/tests/source/TestLA07_TransposeMultiply_Gram.cc"),
                   ("Word2Vec_netsdb", "/root/reference/src/word2vec/source/Word2Vec.cc"),
                   ("PipelinedConv2dMemFuseTest_netsdb", "/root/reference/src/tests/source/PipelinedConv2dMemFuseTest.cc"),
-                  ("FFTestWithoutDeduplication_netsdb", "/root/reference/src/tests/source/FFTestWithoutDeduplication.cc")]
+                  ("FFTestWithoutDeduplication_netsdb", "/root/reference/src/tests/source/FFTestWithoutDeduplication.cc"),
+                  ("FCProjTest_netsdb", "/root/reference/src/tests/source/FCProjTest.cc"),
+                  ("TestSemanticClassifier_netsdb", "/root/reference/src/word2vec/source/TestSemanticClassifier.cc")]
 
 
 def build_host(force: bool = False) -> dict:
@@ -62,7 +64,9 @@ def build_host(force: bool = False) -> dict:
     LSTMTest / LSTMTest_netsdb   the same pair for the LSTM cell (src/tests/source/LSTMTest.cc).
     TestLA04_netsdb / TestLA07_netsdb   the LA DSL's multiply and Gram-matrix drivers (TestLA04_Multiply.cc,
                     TestLA07_TransposeMultiply_Gram.cc), unmodified.
-    Word2Vec_netsdb the word2vec embedding driver (src/word2vec/source/Word2Vec.cc), unmodified."""
+    Word2Vec_netsdb the word2vec embedding driver (src/word2vec/source/Word2Vec.cc), unmodified.
+    FCProjTest_netsdb / TestSemanticClassifier_netsdb   the drivers of the two network-in-a-SelectionComp UDFs
+                    (src/tests/source/FCProjTest.cc, src/word2vec/source/TestSemanticClassifier.cc), unmodified."""
     build()
     os.makedirs(HOST_BIN, exist_ok=True)
     inc = ["-I" + os.path.join(HERE, "..", "include"), "-I" + os.path.join(HOST, "include")]
@@ -94,6 +98,8 @@ REF_UDF_SOURCES = {
                                       "FFInputLayerJoin", "FFAggMatrix", "FFReluBiasSum", "FFTransposeMult", "FFTransposeBiasSum",
                                       "FFRowAggregate", "FFOutputLayer"],
     "/root/reference/src/LSTM/source": ["LSTMThreeWaySum", "LSTMTwoSum", "LSTMHiddenState"],
+    "/root/reference/src/FF_proj/source": ["FullyConnectedNetwork"],
+    "/root/reference/src/word2vec/source": ["SemanticClassifier"],
     "/root/reference/src/conv2d_memory_fusion/source": ["Image", "Kernel", "ImageChunk", "ImageBlock", "ImageToChunks", "ImageChunksToBlock",
                                                         "ImageBlockToMatrix", "KernelToChunks", "KernelBiasJoin", "ConvResultToChunks",
                                                         "ConvChunksToImage"],

@@ -28,7 +28,7 @@ EXPORTS = [
     "nb200_set_exp_view", "nb200_set_rename",
     "nb200_gemm_blocks", "nb200_softmax_rows", "nb200_ff_inference_unit", "nb200_conv2d_image_flat",
     "nb200_conv2d_kernel_flat", "nb200_conv2d_fused", "nb200_conv2d_images_create", "nb200_conv2d_fused_from_set", "nb200_transpose_mult_noalloc",
-    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_conv2d_result_to_images", "nb200_lstm_cell", "nb200_upload_commit", "nb200_set_export_f16", "nb200_set_import_f16",
+    "nb200_ff_layer1_partial", "nb200_ff_finish_from_layer1", "nb200_set_maxabs", "nb200_sum_blocks", "nb200_udf_dense2", "nb200_conv2d_result_to_images", "nb200_lstm_cell", "nb200_upload_commit", "nb200_set_export_f16", "nb200_set_import_f16",
 ]
 
 
@@ -271,6 +271,20 @@ def conv2d_result_to_images(result: DeviceSet, num_images: int, x: int, y: int, 
     out = np.empty((num_images, z, x, y), dtype=np.float64)
     check(lib().nb200_conv2d_result_to_images(result.ptr, num_images, x, y, z, _hostptr(out)))
     return out
+
+
+def udf_dense2(a: DeviceSet, features: int, batch: int, w0: np.ndarray, b0: np.ndarray, w1: np.ndarray, b1: np.ndarray,
+               db: str = "ff", out_set: str = "output") -> DeviceSet:
+    """FullyConnectedNetwork / SemanticClassifier (nb200_udf_dense2): the two-layer network inside one SelectionComp."""
+    w0 = np.ascontiguousarray(w0, dtype=np.float64); b0 = np.ascontiguousarray(b0, dtype=np.float64)
+    w1 = np.ascontiguousarray(w1, dtype=np.float64); b1 = np.ascontiguousarray(b1, dtype=np.float64)
+    hidden, labels = w0.shape[0], w1.shape[0]
+    if w0.shape != (hidden, features) or w1.shape != (labels, hidden) or b0.size != hidden or b1.size != labels:
+        raise ValueError("udf_dense2: weight shapes do not match (hidden x features, hidden, labels x hidden, labels)")
+    p = C.c_void_p()
+    check(lib().nb200_udf_dense2(a.ptr, features, batch, hidden, labels, _hostptr(w0), _hostptr(b0), _hostptr(w1), _hostptr(b1),
+                                 _b(db), _b(out_set), C.byref(p)))
+    return DeviceSet(p)
 
 
 ACT_NONE, ACT_SIGMOID, ACT_TANH = 0, 1, 2

@@ -875,6 +875,67 @@ int nb200_sum_blocks(nb200_set *a, nb200_set *b, nb200_set *cc, int activation, 
     return NB200_OK;
 }
 
+// ---- the networks that live inside one SelectionComp ------------------------------------------------
+// FullyConnectedNetwork (FF_proj/headers/FullyConnectedNetwork.h:62-123, driver tests/source/FCProjTest.cc:88-97) and
+// SemanticClassifier (word2vec/headers/SemanticClassifier.h:43-141) map every FFMatrixBlock of a set through a two-layer
+// network held by the computation object: x0 = the block's raw buffer viewed as features x batch,
+// y0 = relu(w0 x0 + b0), out = outLabel(sigmoid(w1 y0 + b1)), a labels x batch block with the input's block indices.
+// Here all blocks go through two fp64 tensor-core GEMMs at once (the blocks side by side along the batch axis):
+// fp64 because the result is a thresholded sign and the layers are tiny (word2vec: 500 -> 16 -> 1).
+int nb200_udf_dense2(nb200_set *in, int features, int batch, int hidden, int labels, const double *w0_host, const double *b0_host,
+                     const double *w1_host, const double *b1_host, const char *db, const char *out_set, nb200_set **out) {
+    NEED_CTX();
+    if (!in || features <= 0 || batch <= 0 || hidden <= 0 || labels <= 0 || !w0_host || !b0_host || !w1_host || !b1_host || !db || !out_set || !out) {
+        set_error("udf_dense2: invalid arguments");
+        return NB200_ERR_INVALID;
+    }
+    NB_TRY(same_device(c, {in}));
+    if (in->view_of || (!in->f64 && !in->f32)) { set_error("udf_dense2: the input set holds no data (or is a view)"); return NB200_ERR_STATE; }
+    if (static_cast<int64_t>(in->block_rows) * in->block_cols < static_cast<int64_t>(features) * batch) {
+        set_error("udf_dense2: a %d x %d block holds fewer than features x batch = %d x %d values", in->block_rows, in->block_cols, features, batch);
+        return NB200_ERR_SHAPE;
+    }
+    NB_TRY(wait_set_uploads(c, in));
+    const int nbr = static_cast<int>(ceil_div(in->total_rows, in->block_rows)), nbc = static_cast<int>(ceil_div(in->total_cols, in->block_cols));
+    const int64_t M = static_cast<int64_t>(nbr) * nbc * batch;
+    if (M > (1 << 30)) { set_error("udf_dense2: too many rows"); return NB200_ERR_SHAPE; }
+    double *xt = nullptr, *y0 = nullptr, *z = nullptr, *w0 = nullptr, *w1 = nullptr, *b0 = nullptr, *b1 = nullptr, *res = nullptr;
+    const size_t on = static_cast<size_t>(nbr) * labels * nbc * batch;
+    int st = NB200_OK;
+    auto fail = [&](int code) { nb_free(xt); nb_free(y0); nb_free(z); nb_free(w0); nb_free(w1); nb_free(b0); nb_free(b1); nb_free(res); return code; };
+    if (nb_malloc(&xt, (M ? M : 1) * features * sizeof(double)) != cudaSuccess || nb_malloc(&y0, (M ? M : 1) * hidden * sizeof(double)) != cudaSuccess ||
+        nb_malloc(&z, (M ? M : 1) * labels * sizeof(double)) != cudaSuccess || nb_malloc(&w0, static_cast<size_t>(hidden) * features * sizeof(double)) != cudaSuccess ||
+        nb_malloc(&w1, static_cast<size_t>(labels) * hidden * sizeof(double)) != cudaSuccess || nb_malloc(&b0, hidden * sizeof(double)) != cudaSuccess ||
+        nb_malloc(&b1, labels * sizeof(double)) != cudaSuccess || nb_malloc(&res, (on ? on : 1) * sizeof(double)) != cudaSuccess) {
+        set_error("udf_dense2: out of device memory");
+        return fail(NB200_ERR_NOMEM);
+    }
+    if (cudaMemcpyAsync(w0, w0_host, static_cast<size_t>(hidden) * features * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+        cudaMemcpyAsync(b0, b0_host, hidden * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+        cudaMemcpyAsync(w1, w1_host, static_cast<size_t>(labels) * hidden * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+        cudaMemcpyAsync(b1, b1_host, labels * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) {
+        set_error("udf_dense2: weight upload failed");
+        return fail(NB200_ERR_CUDA);
+    }
+    st = launch_udf_gather(c, in->f64 ? static_cast<const void *>(in->f64) : in->f32, in->f64 != nullptr, in->f64 ? in->total_cols : in->f32_ld, in->total_rows, in->total_cols, in->block_rows, in->block_cols, nbr, nbc, features, batch, xt);
+    F64Epilogue e0; e0.bias_n = b0; e0.relu = 1;
+    if (st == NB200_OK) st = launch_gemm_f64(c, xt, features, 1, w0, features, 1, static_cast<int>(M), hidden, features, y0, hidden, e0);
+    F64Epilogue e1; e1.bias_n = b1;
+    if (st == NB200_OK) st = launch_gemm_f64(c, y0, hidden, 1, w1, hidden, 1, static_cast<int>(M), labels, hidden, z, labels, e1);
+    if (st == NB200_OK) st = launch_udf_labels(c, z, labels, batch, nbr, nbc, res, static_cast<int64_t>(nbc) * batch);
+    if (st == NB200_OK) st = check_kernel_fault(c, "udf_dense2");
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess && st == NB200_OK) { set_error("udf_dense2: stream synchronisation failed"); st = NB200_ERR_CUDA; }
+    if (st != NB200_OK) return fail(st);
+    nb200_set *o = nullptr;
+    st = make_set(db, out_set, nbr * labels, nbc * batch, labels, batch, &o);   // may replace (and free) the input
+    if (st != NB200_OK) return fail(st);
+    o->f64 = res;
+    res = nullptr;
+    fail(NB200_OK);
+    *out = o;
+    return NB200_OK;
+}
+
 // ---- LSTM step -----------------------------------------------------------------------------------
 namespace {
 struct LstmScratch {

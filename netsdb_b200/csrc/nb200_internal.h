@@ -255,6 +255,9 @@ int launch_extract_to_f64(Context *c, const void *src, bool src_is_f64, int64_t 
                           int cols, int valid_rows, int valid_cols, double *dst, int64_t dst_ld, int apply_exp);
 int launch_scatter_rows(Context *c, const double *src, int64_t cols, const int32_t *list, int n, float *dst_f32,
                         int64_t dst_ld);
+int launch_udf_gather(Context *c, const void *src, bool src_is_f64, int64_t ld, int total_rows, int total_cols, int br, int bc, int nbr, int nbc,
+                      int features, int batch, double *xt);
+int launch_udf_labels(Context *c, const double *zt, int labels, int batch, int nbr, int nbc, double *dst, int64_t dst_ld);
 int launch_im2col(Context *c, const double *images, int n, int ch, int h, int w, int k, int stride, int padding,
                   double *out, int64_t out_ld);
 

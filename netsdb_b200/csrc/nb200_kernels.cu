@@ -1517,6 +1517,57 @@ int launch_extract_to_f64(Context *c, const void *src, bool src_is_f64, int64_t 
     return NB200_OK;
 }
 
+// FullyConnectedNetwork / SemanticClassifier (FF_proj/headers/FullyConnectedNetwork.h:62-123,
+// word2vec/headers/SemanticClassifier.h:43-141) view the raw buffer of a (zero-padded) block as a row-major
+// features x batch matrix, whatever the block's own shape.  k_udf_gather writes that view, for every block of the set,
+// as rows of a K-contiguous operand: xt[(b * batch + n) * features + f] = raw_b[f * batch + n], where raw_b[i] is element
+// (i / block_cols, i % block_cols) of block b = (bi, bj) of the de-blocked set (0 in the padding).
+template <typename T>
+__global__ void k_udf_gather(const T *__restrict__ src, long long ld, int total_rows, int total_cols, int br, int bc, int nbc,
+                             int features, int batch, long long n_total, double *__restrict__ xt) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n_total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int f = static_cast<int>(i % features);
+        const long long bn = i / features;
+        const int n = static_cast<int>(bn % batch), b = static_cast<int>(bn / batch);
+        const long long raw = static_cast<long long>(f) * batch + n;
+        const int r = static_cast<int>(raw / bc), cc = static_cast<int>(raw % bc);
+        const long long gr = static_cast<long long>(b / nbc) * br + r, gc = static_cast<long long>(b % nbc) * bc + cc;
+        xt[i] = (gr < total_rows && gc < total_cols) ? static_cast<double>(src[gr * ld + gc]) : 0.0;
+    }
+}
+// y1 = outLabel(sigmoid(z)) written as the labels x batch block (bi, bj) of the output set (FullyConnectedNetwork.cc:13-24:
+// sigmoid(x) = 1 / (1 + exp(-x)), outLabel(x) = x > 0.5 ? 1 : 0, both evaluated in fp64 as the reference does)
+__global__ void k_udf_labels(const double *__restrict__ zt, int labels, int batch, int nbc, long long n_total, double *__restrict__ dst,
+                             long long dst_ld) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n_total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int l = static_cast<int>(i % labels);
+        const long long bn = i / labels;
+        const int n = static_cast<int>(bn % batch), b = static_cast<int>(bn / batch);
+        const double sg = 1 / (1 + exp(-zt[i]));
+        dst[(static_cast<long long>(b / nbc) * labels + l) * dst_ld + static_cast<long long>(b % nbc) * batch + n] = sg > 0.5 ? 1.0 : 0.0;
+    }
+}
+int launch_udf_gather(Context *c, const void *src, bool src_is_f64, int64_t ld, int total_rows, int total_cols, int br, int bc, int nbr, int nbc,
+                      int features, int batch, double *xt) {
+    const int64_t n = static_cast<int64_t>(nbr) * nbc * batch * features;
+    if (n == 0) return NB200_OK;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+    if (src_is_f64) k_udf_gather<double><<<blocks, 256, 0, c->stream>>>(static_cast<const double *>(src), ld, total_rows, total_cols, br, bc, nbc, features, batch, n, xt);
+    else k_udf_gather<float><<<blocks, 256, 0, c->stream>>>(static_cast<const float *>(src), ld, total_rows, total_cols, br, bc, nbc, features, batch, n, xt);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+int launch_udf_labels(Context *c, const double *zt, int labels, int batch, int nbr, int nbc, double *dst, int64_t dst_ld) {
+    const int64_t n = static_cast<int64_t>(nbr) * nbc * batch * labels;
+    if (n == 0) return NB200_OK;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+    k_udf_labels<<<blocks, 256, 0, c->stream>>>(zt, labels, batch, nbc, n, dst, dst_ld);
+    NB_LAUNCH_CHECK(c);
+    return NB200_OK;
+}
+
 // ConvResultToChunks + ConvChunksToImage (conv2d_memory_fusion/headers/ConvResultToChunks.h:42-103,
 // ConvChunksToImage.h:34-72): result[(image, window), channel] -> images[image][channel][window], a batched
 // transpose through a padded shared-memory tile (both sides coalesced); channels at or beyond zsrc (the set's columns)

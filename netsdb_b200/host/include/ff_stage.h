@@ -9,6 +9,7 @@
 //   FFOutputLayer(x, FFRowAggregate(x))                                          -> row softmax
 //   LSTMThreeWaySum(x, y, z) / LSTMTwoSum(x, y)                                  -> one element-wise kernel
 //   FFAggMatrix(LSTMHiddenState(o, c))                                           -> tanh map + block GEMM
+//   FullyConnectedNetwork(x) / SemanticClassifier(x)                             -> nb200_udf_dense2 (two fp64 GEMMs)
 //   the whole graph of ff::inference_unit (SimpleFF.cc:340-389)                  -> the fused stage with the
 //                                                                                   label-exact precision cascade
 // Anything else is rejected: there is no CPU fallback.
@@ -21,6 +22,7 @@
 #include "conv_stage.h"
 #include "la_udfs.h"
 #include "lstm_udfs.h"
+#include "net_udfs.h"
 
 namespace nb200_host {
 
@@ -339,6 +341,28 @@ private:
             nb200_set *x = eval(c->getIthInput(0), db, ""), *y = eval(c->getIthInput(1), db, "");
             nb200_set *o = nullptr;
             check(nb200_sum_blocks(x, y, nullptr, NB200_ACT_NONE, db.c_str(), out.c_str(), &o));
+            return o;
+        }
+        if (auto *net = as<FullyConnectedNetwork>(c)) {
+            nb200_set *x = eval(c->getIthInput(0), db, "");
+            int br = 0;
+            nb200_set_info(x, nullptr, nullptr, &br, nullptr);
+            if (static_cast<uint32_t>(br) != net->sizeBatch)   // FullyConnectedNetwork.h:69-72 (the reference exits)
+                throw std::runtime_error("batch size doesn't match: " + std::to_string(net->sizeBatch) + ", " + std::to_string(br));
+            nb200_set *o = nullptr;
+            check(nb200_udf_dense2(x, net->numFeatures, static_cast<int>(net->sizeBatch), net->numNeurons, net->numLabels, net->weights1.data(),
+                                   net->bias1.data(), net->weights2.data(), net->bias2.data(), db.c_str(), out.c_str(), &o));
+            return o;
+        }
+        if (auto *net = as<SemanticClassifier>(c)) {
+            nb200_set *x = eval(c->getIthInput(0), db, "");
+            int bc = 0;
+            nb200_set_info(x, nullptr, nullptr, nullptr, &bc);   // sizeBatch = inNumCol (SemanticClassifier.h:57)
+            const std::vector<double> w0(static_cast<size_t>(net->sizeDense0) * net->sizeEmbed, 1.0), b0(net->sizeDense0, 1.0),
+                w1(static_cast<size_t>(net->sizeDense1) * net->sizeDense0, 1.0), b1(net->sizeDense1, 1.0);
+            nb200_set *o = nullptr;
+            check(nb200_udf_dense2(x, static_cast<int>(net->sizeEmbed), bc, static_cast<int>(net->sizeDense0), static_cast<int>(net->sizeDense1),
+                                   w0.data(), b0.data(), w1.data(), b1.data(), db.c_str(), out.c_str(), &o));
             return o;
         }
         if (as<FFOutputLayer>(c)) {

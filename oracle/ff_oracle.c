@@ -404,6 +404,45 @@ nbo_set *nbo_relu_bias_sum(const nbo_set *in, const nbo_set *bias) {
     return out;
 }
 
+/* FullyConnectedNetwork (FF_proj/headers/FullyConnectedNetwork.h:62-123) and SemanticClassifier
+ * (word2vec/headers/SemanticClassifier.h:43-141): a SelectionComp that runs a whole two-layer network on every block.
+ * The block's raw buffer is viewed as a row-major features x batch matrix x0 (whatever the block's own row/column
+ * counts say: :75-77 / :77-79), then
+ *     y0 = relu(w0 * x0 + b0)            w0: hidden x features, row-major             (:90-92 / :95-97)
+ *     y1 = outLabel(sigmoid(w1 * y0 + b1))   w1: labels x hidden; sigmoid(x) = 1 / (1 + exp(-x)), outLabel(x) = x > 0.5
+ *                                                                                      (:105-108 / :114-117; .cc:13-24)
+ * and the result is a labels x batch block with the input's block indices (:111-113 / :120-123).  Its totals are what the
+ * FFMatrixBlock constructor used leaves: the block's own size in SemanticClassifier (7 arguments, with_totals = 1), the
+ * FFMatrixMeta defaults -1 / -1 in FullyConnectedNetwork (5 arguments, FFMatrixMeta.h:11-12; with_totals = 0).  Products accumulate over k in
+ * increasing order.  A block with fewer than features * batch values is refused (the UDF would read past it). */
+nbo_set *nbo_udf_dense2(const nbo_set *in, int features, int batch, int hidden, int labels, const double *w0, const double *b0,
+                        const double *w1, const double *b1, int with_totals) {
+    nbo_set *out = nbo_set_new();
+    double *y0 = (double *)malloc((size_t)hidden * batch * sizeof(double));
+    for (int x = 0; x < in->n; x++) {
+        const nbo_block *a = &in->blocks[x];
+        if ((size_t)a->rows * a->cols < (size_t)features * batch) { fprintf(stderr, "block smaller than features x batch\n"); free(y0); nbo_set_free(out); return NULL; }
+        for (int h = 0; h < hidden; h++)
+            for (int n = 0; n < batch; n++) {
+                double s = 0.0;
+                for (int f = 0; f < features; f++) s += w0[(size_t)h * features + f] * a->data[(size_t)f * batch + n];
+                s += b0[h];
+                y0[(size_t)h * batch + n] = s > 0.0 ? s : 0.0;
+            }
+        nbo_block *o = set_add(out, a->block_row, a->block_col, labels, batch, with_totals ? labels : -1, with_totals ? batch : -1);
+        for (int l = 0; l < labels; l++)
+            for (int n = 0; n < batch; n++) {
+                double s = 0.0;
+                for (int h = 0; h < hidden; h++) s += w1[(size_t)l * hidden + h] * y0[(size_t)h * batch + n];
+                s += b1[l];
+                const double sg = 1 / (1 + exp(-s));
+                o->data[(size_t)l * batch + n] = sg > 0.5 ? 1.0 : 0.0;
+            }
+    }
+    free(y0);
+    return out;
+}
+
 /* FFTransposeBiasSum, intended semantics (Q1): out block (in.blockCol, in.blockRow) of J x I,
  * totals swapped (FFTransposeBiasSum.h:64-67); value = in[i,j] + bias[i] (the `colwise() +`
  * of :84) written transposed; exp() only where the un-padded coordinates are in range

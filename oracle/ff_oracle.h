@@ -90,6 +90,11 @@ nbo_set *nbo_relu_bias_sum(const nbo_set *in, const nbo_set *bias);
  * out = exp(in + bias[row])^T on the un-padded region, 0 elsewhere.  apply_exp = 0 returns the
  * pre-exp logits (used to define labels when exp overflows). */
 nbo_set *nbo_transpose_bias_sum(const nbo_set *in, const nbo_set *bias, int apply_exp);
+/* FullyConnectedNetwork (FF_proj/headers/FullyConnectedNetwork.h:62-123) / SemanticClassifier
+ * (word2vec/headers/SemanticClassifier.h:43-141): per block, raw buffer viewed as features x batch;
+ * out block = outLabel(sigmoid(w1 * relu(w0 * x + b0) + b1)), labels x batch, same block indices. */
+nbo_set *nbo_udf_dense2(const nbo_set *in, int features, int batch, int hidden, int labels, const double *w0, const double *b0,
+                        const double *w1, const double *b1, int with_totals);
 /* FFRowAggregate (FFRowAggregate.h:21-28; FFMatrixBlock.h:116-142). */
 nbo_set *nbo_row_aggregate(const nbo_set *in);
 /* FFOutputLayer, intended semantics (FFOutputLayer.h:21-22, :31-57: in1[i,j] / in2[i]). */

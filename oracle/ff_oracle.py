@@ -67,6 +67,8 @@ def lib():
         L.nbo_transpose_bias_sum.argtypes = [vp, vp, i]
         L.nbo_row_aggregate.restype = vp
         L.nbo_row_aggregate.argtypes = [vp]
+        L.nbo_udf_dense2.restype = vp
+        L.nbo_udf_dense2.argtypes = [vp, i, i, i, i, d, d, d, d, i]
         L.nbo_lstm_sum.restype = vp
         L.nbo_lstm_sum.argtypes = [vp, vp, vp, i]
         L.nbo_lstm_hidden_state_agg.restype = vp
@@ -157,6 +159,19 @@ def la_transpose_multiply_agg(a: BlockSet, b: BlockSet, threads=1) -> BlockSet:
 
 def relu_bias_sum(a: BlockSet, bias: BlockSet) -> BlockSet:
     return BlockSet(lib().nbo_relu_bias_sum(a.ptr, bias.ptr))
+
+
+def udf_dense2(a: BlockSet, features, batch, w0, b0, w1, b1, with_totals=True) -> BlockSet:
+    """FullyConnectedNetwork / SemanticClassifier: the two-layer network those SelectionComps run on every block."""
+    w0 = np.ascontiguousarray(w0, dtype=np.float64); b0 = np.ascontiguousarray(b0, dtype=np.float64)
+    w1 = np.ascontiguousarray(w1, dtype=np.float64); b1 = np.ascontiguousarray(b1, dtype=np.float64)
+    hidden, labels = w0.shape[0], w1.shape[0]
+    assert w0.shape == (hidden, features) and w1.shape == (labels, hidden) and b0.size == hidden and b1.size == labels
+    dp = lambda x: x.ctypes.data_as(C.POINTER(C.c_double))
+    p = lib().nbo_udf_dense2(a.ptr, features, batch, hidden, labels, dp(w0), dp(b0), dp(w1), dp(b1), int(with_totals))
+    if not p:
+        raise ValueError("udf_dense2: a block is smaller than features x batch")
+    return BlockSet(p)
 
 
 def transpose_bias_sum(a: BlockSet, bias: BlockSet, apply_exp=True) -> BlockSet:

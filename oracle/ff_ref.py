@@ -56,6 +56,10 @@ def lib():
         L.ref_kernel_flat.restype = vp
         L.ref_kernel_flat.argtypes = [d, vp, i, i, i, i, i, i]
         L.ref_conv_result_to_images.argtypes = [vp, i, i, i, i, d]
+        L.ref_fully_connected.restype = vp
+        L.ref_fully_connected.argtypes = [vp, i, i, i, i, d, d, d, d]
+        L.ref_semantic_classifier.restype = vp
+        L.ref_semantic_classifier.argtypes = [vp, i, i, i]
         _lib = L
     return _lib
 
@@ -150,3 +154,18 @@ def conv_result_to_images(result, n: int, x: int, y: int, z: int) -> np.ndarray:
     if got < 0:
         raise RuntimeError("conv_result_to_images: image index out of range")
     return out
+
+
+def fully_connected(a, features: int, labels: int, hidden: int, batch: int):
+    """FullyConnectedNetwork constructed as FCProjTest.cc does; returns (output set, w0, b0, w1, b1) -- the weights the
+    reference drew from std::random_device for this run."""
+    w0, b0 = np.empty((hidden, features)), np.empty(hidden)
+    w1, b1 = np.empty((labels, hidden)), np.empty(labels)
+    with _quiet():
+        out = _set(lib().ref_fully_connected(a.ptr, features, labels, hidden, batch, _d(w0), _d(b0), _d(w1), _d(b1)))
+    return out, w0, b0, w1, b1
+
+
+def semantic_classifier(a, size_embed: int, dense0: int, dense1: int):
+    with _quiet():
+        return _set(lib().ref_semantic_classifier(a.ptr, size_embed, dense0, dense1))

@@ -9,6 +9,8 @@
  *                   ImageBlockToMatrix.h KernelToChunks.h KernelBiasJoin.h ConvResultToChunks.h ConvChunksToImage.h
  *   src/sharedLibraries/headers: MatrixBlock.h MatrixData.h MatrixMeta.h LASillyMultiply1Join.h
  *                   LASillyTransposeMultiply1Join.h LASillyMultiply2Aggregate.h
+ *   src/FF_proj: headers/FullyConnectedNetwork.h + source/FullyConnectedNetwork.cc (sigmoid, relu, outLabel, randomGen);
+ *   src/word2vec/headers: SemanticClassifier.h (its .cc defines the same three functions again, so only one is compiled)
  * Two of their dependencies are stood in for (see those files): netsDB's object model (pdbmin/pdb_min.h: handles,
  * vectors, lambdas evaluated in place) and Eigen 3 (minieigen: plain-loop products and row sums).
  *
@@ -45,6 +47,14 @@
 #include "LASillyMultiply1Join.h"
 #include "LASillyMultiply2Aggregate.h"
 #include "LASillyTransposeMultiply1Join.h"
+/* the network's weights are private members filled from std::random_device: the harness has to read them to hand the
+ * same weights to the restatement, hence the keyword trick around this one include */
+#include <functional>
+#include <random>
+#define private public
+#include "FullyConnectedNetwork.cc"
+#undef private
+#include "SemanticClassifier.h"
 
 extern "C" {
 #include "../ff_oracle.h"
@@ -268,6 +278,27 @@ int ref_conv_result_to_images(const nbo_set *result, int n, int x, int y, int z,
         }
     }
     return static_cast<int>(imgs.size());
+}
+
+/* FullyConnectedNetwork (FCProjTest.cc:88-97): constructed as the driver does (random weights), run over the set; the
+ * weights it drew are copied out (w0: hidden x features, b0, w1: labels x hidden, b1) */
+nbo_set *ref_fully_connected(const nbo_set *in, int features, int labels, int hidden, int batch, double *w0, double *b0, double *w1,
+                             double *b1) {
+    FullyConnectedNetwork net(features, labels, hidden, (uint32_t)batch);
+    memcpy(w0, net.weights1->c_ptr(), (size_t)features * hidden * sizeof(double));
+    memcpy(b0, net.bias1->c_ptr(), (size_t)hidden * sizeof(double));
+    memcpy(w1, net.weights2->c_ptr(), (size_t)hidden * labels * sizeof(double));
+    memcpy(b1, net.bias2->c_ptr(), (size_t)labels * sizeof(double));
+    Set<FFMatrixBlock> xs = ff_blocks(in);
+    Set<FFMatrixBlock> out = run_select<FFMatrixBlock>(net, xs);
+    return to_nbo(out);
+}
+/* SemanticClassifier (TestSemanticClassifier.cc): weights and biases are the all-ones vectors the projection builds */
+nbo_set *ref_semantic_classifier(const nbo_set *in, int size_embed, int dense0, int dense1) {
+    SemanticClassifier net((uint32_t)size_embed, (uint32_t)dense0, (uint32_t)dense1);
+    Set<FFMatrixBlock> xs = ff_blocks(in);
+    Set<FFMatrixBlock> out = run_select<FFMatrixBlock>(net, xs);
+    return to_nbo(out);
 }
 
 }  /* extern "C" */

@@ -59,5 +59,15 @@ g.update(conv_imgs2=imgs2, conv_image_flat2=fr.image_flat(imgs2, 3, 2, 1, 16, 4)
 one = rng.normal(size=(24, 5))
 g.update(conv_one_result=one, conv_one_images=fr.conv_result_to_images(S(one, 7, 2), 1, 4, 6, 5))
 
+# the two networks that live inside one SelectionComp: FullyConnectedNetwork (weights drawn by the reference's own
+# constructor, read back out of the object) and SemanticClassifier (all-ones weights)
+fc_x = rng.uniform(-2, 2, size=(3 * 6, 2 * 10))                      # 3 x 2 blocks of batch 6 x features 10
+fc_out, fc_w0, fc_b0, fc_w1, fc_b1 = fr.fully_connected(S(fc_x, 6, 10), 10, 3, 7, 6)
+g.update(fc_x=fc_x, fc_w0=fc_w0, fc_b0=fc_b0, fc_w1=fc_w1, fc_b1=fc_b1,
+         fc_out=np.stack([b[4] for b in sorted(fc_out.blocks(), key=lambda b: (b[0], b[1]))]))
+sc_x = rng.uniform(-1, 0.6, size=(12, 3 * 5))                        # embedding 12, three blocks of batch 5
+sc_out = fr.semantic_classifier(S(sc_x, 12, 5), 12, 4, 2)
+g.update(sc_x=sc_x, sc_out=np.stack([b[4] for b in sorted(sc_out.blocks(), key=lambda b: (b[0], b[1]))]))
+
 np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_pinned.npz"), **g)
 print("wrote", len(g), "arrays")

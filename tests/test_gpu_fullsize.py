@@ -165,4 +165,35 @@ def test_word2vec_reference_shape(nb, oracle):
         assert out.info() == (dim, batch, blk, blk)
         got = out.download_dense()[np.arange(0, dim, 50)][:, idx]
         assert np.abs(got - ref).max() <= tol * np.abs(ref).max() * 4
+    # SemanticClassifier on top (TestSemanticClassifier.cc:108-124: embedding 500, dense 16, 1; the batch is the block's
+    # column count, 1,000, of which 100 columns are real): labels of the sampled batch rows against fp64 numpy of the
+    # fp32 embedding the device holds
+    rng = np.random.default_rng(9)
+    w0, b0 = rng.uniform(-0.5, 0.5, size=(16, dim)), rng.uniform(-0.5, 0.5, size=16)
+    w1, b1 = rng.uniform(-0.5, 0.5, size=(1, 16)), rng.uniform(-0.5, 0.5, size=1)
+    emb = out.download_dense()                                  # dim x batch
+    lab = nb.udf_dense2(out, dim, blk, w0, b0, w1, b1, "word2vec", "labels")
+    assert lab.info() == (1, blk, 1, blk)
+    z = w1 @ np.maximum(w0 @ emb + b0[:, None], 0.0) + b1[:, None]
+    want = (1 / (1 + np.exp(-z)) > 0.5).astype(np.float64)
+    sure = np.abs(z[0]) > 1e-9
+    got = lab.download_dense()[0, :batch]
+    assert np.array_equal(got[sure], want[0][sure]) and 0 < got.mean() < 1
     W.destroy(), X.destroy()
+
+
+def test_unmodified_reference_semantic_classifier_driver():
+    """netsDB's own src/word2vec/source/TestSemanticClassifier.cc compiled unmodified against the shim, at the sizes it
+    hard-codes (batch 100, vocab 1,000,000, embedding 500): FFTransposeMult + FFAggMatrix lowered to one block GEMM,
+    SemanticClassifier to nb200_udf_dense2, `labels` read back by ff::print_stats."""
+    import os
+    import subprocess
+
+    from netsdb_b200 import build
+
+    exe = os.path.join(build.HOST_BIN, "TestSemanticClassifier_netsdb")
+    if not os.path.exists(exe):
+        pytest.skip("reference driver was not built (no reference tree at build time)")
+    r = subprocess.run([exe, "1000", "1000", "Y"], env=dict(os.environ, NB200_PRECISION="f16"), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "[STATS] labels : 1 X 1000" in r.stdout and "count = 1" in r.stdout   # sizeDense1 x (block columns), one block

@@ -58,6 +58,11 @@ def test_device_against_reference_goldens(nb):
     assert close(res.download_dense(), g["conv_result_nobias"])
     one = dev("one", g["conv_one_result"], 7, 2)
     assert np.array_equal(nb.conv2d_result_to_images(one, 1, 4, 6, 5), g["conv_one_images"])
+    # FullyConnectedNetwork / SemanticClassifier: the output set holds the labels x batch blocks side by side
+    fc = nb.udf_dense2(dev("fcx", g["fc_x"], 6, 10), 10, 6, g["fc_w0"], g["fc_b0"], g["fc_w1"], g["fc_b1"], "gold", "fc").download_dense()
+    assert np.array_equal(fc.reshape(3, 3, 2, 6).transpose(0, 2, 1, 3).reshape(6, 3, 6), g["fc_out"])
+    sc = nb.udf_dense2(dev("scx", g["sc_x"], 12, 5), 12, 5, np.ones((4, 12)), np.ones(4), np.ones((2, 4)), np.ones(2), "gold", "sc").download_dense()
+    assert np.array_equal(sc.reshape(1, 2, 3, 5).transpose(0, 2, 1, 3).reshape(3, 2, 5), g["sc_out"])
 
 
 def test_generator_bit_exact(nb, oracle):
@@ -649,3 +654,48 @@ def test_wide_hidden_layer_takes_two_kernel_path(nb, oracle):
     _, labels, stats = nb.ff_inference_unit(dev["w1"], dev["wo"], dev["x"], dev["b1"], dev["bo"], nb.PREC_F16)
     assert np.array_equal(labels, ref_labels) and stats["splits1"] > 1
     assert rel(nb.DeviceSet.lookup("ff", "__logits").download_dense(), ref_logits.dense()) <= TOL["f16"]
+
+
+@pytest.mark.parametrize("cfg", [(6, 10, 7, 3, 3, 2), (100, 500, 16, 1, 1, 4), (64, 300, 128, 10, 2, 3), (33, 77, 40, 5, 5, 1)])
+def test_udf_networks_vs_oracle(nb, oracle, cfg):
+    """nb200_udf_dense2 = FullyConnectedNetwork / SemanticClassifier (a two-layer network inside one SelectionComp) against
+    the oracle's restatement, block by block; edge blocks of the input set are zero-padded as the reference's loader
+    leaves them (the set is not a whole number of blocks in the last case)."""
+    batch, feat, hid, lab, nbr, nbc = cfg
+    rng = np.random.default_rng(batch + feat)
+    rows, cols = nbr * batch - (3 if nbr > 2 else 0), nbc * feat
+    x = rng.uniform(-1, 1, size=(rows, cols))
+    w0, b0 = rng.uniform(-0.5, 0.5, size=(hid, feat)), rng.uniform(-0.5, 0.5, size=hid)
+    w1, b1 = rng.uniform(-0.5, 0.5, size=(lab, hid)), rng.uniform(-0.5, 0.5, size=lab)
+    ref = oracle.udf_dense2(oracle.load_matrix(x, batch, feat), feat, batch, w0, b0, w1, b1)
+    d = nb.DeviceSet.create("udf", "x", rows, cols, batch, feat)
+    d.upload_dense(x)
+    got = nb.udf_dense2(d, feat, batch, w0, b0, w1, b1, "udf", "labels")
+    assert got.info() == (nbr * lab, nbc * batch, lab, batch)
+    dense = got.download_dense()
+    n = 0
+    for br, bc, _, _, arr in ref.blocks():
+        assert np.array_equal(dense[br * lab:(br + 1) * lab, bc * batch:(bc + 1) * batch], arr), (br, bc)
+        n += 1
+    assert n == nbr * nbc and 0 < dense.mean() < 1
+    with pytest.raises(nb.Nb200Error):   # a block with fewer than features x batch values: the UDF would read past it
+        nb.udf_dense2(d, feat + 1, batch, np.zeros((hid, feat + 1)), b0, w1, b1, "udf", "bad")
+
+
+def test_unmodified_reference_network_drivers():
+    """netsDB's own FCProjTest.cc (FullyConnectedNetwork) and TestSemanticClassifier.cc (FFTransposeMult + FFAggMatrix +
+    SemanticClassifier) compiled unmodified against the shim and run through executeComputations."""
+    from netsdb_b200 import build
+
+    fc, sc = os.path.join(build.HOST_BIN, "FCProjTest_netsdb"), os.path.join(build.HOST_BIN, "TestSemanticClassifier_netsdb")
+    if not os.path.exists(fc) or not os.path.exists(sc):
+        pytest.skip("reference drivers were not built (no reference tree at build time)")
+    # the UDF insists on block rows == batch and views the block as features x batch: one 50 x 40 block (the driver ends
+    # with sleep(20))
+    r = _run([fc, "50", "40", "50", "40", "16", "2", "Y"], {"NB200_FC_SEED": "7"}, timeout=240)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "End-to-End Time Duration" in r.stdout
+    pairs = [ln for ln in r.stdout.splitlines() if ln.count(",") == 1 and set(ln.replace(" ", "")) <= set("01,")]
+    assert len(pairs) >= 2      # the driver prints the first two values of each output row: labels, all 0 or 1
+    r = _run([fc, "50", "40", "60", "40", "16", "2", "Y"], {"NB200_FC_SEED": "7"}, timeout=240)
+    assert r.returncode != 0 and "batch size doesn't match" in (r.stdout + r.stderr)   # FullyConnectedNetwork.h:69-72

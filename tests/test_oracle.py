@@ -187,3 +187,8 @@ def test_reference_goldens(oracle):
     assert close(oracle.transpose_mult_agg(imf, kf, 2).dense(), g["conv_result_nobias"])
     assert np.array_equal(oracle.image_flat(g["conv_imgs2"], 3, 2, 1, 16, 4).dense(), g["conv_image_flat2"])
     assert np.array_equal(oracle.conv_result_to_images(S(g["conv_one_result"], 7, 2), 1, 4, 6, 5), g["conv_one_images"])
+    stack = lambda s: np.stack([b[4] for b in sorted(s.blocks(), key=lambda b: (b[0], b[1]))])
+    fc = oracle.udf_dense2(S(g["fc_x"], 6, 10), 10, 6, g["fc_w0"], g["fc_b0"], g["fc_w1"], g["fc_b1"], with_totals=False)
+    assert np.array_equal(stack(fc), g["fc_out"])                  # FullyConnectedNetwork, the weights the reference drew
+    sc = oracle.udf_dense2(S(g["sc_x"], 12, 5), 12, 5, np.ones((4, 12)), np.ones(4), np.ones((2, 4)), np.ones(2))
+    assert np.array_equal(stack(sc), g["sc_out"])                  # SemanticClassifier

@@ -164,3 +164,28 @@ def test_conv_result_to_images_single_image(ref, oracle, cfg):
     assert np.array_equal(oracle.conv_result_to_images(s, 1, x, y, z), ref.conv_result_to_images(s, 1, x, y, z))
     exact = oracle.load_matrix(res, br, z)  # one column block that holds exactly the z columns
     assert not ref.conv_result_to_images(exact, 1, x, y, z).any()
+
+
+@pytest.mark.parametrize("cfg", [(6, 10, 7, 3, 3, 2), (4, 33, 16, 1, 1, 5), (16, 8, 5, 2, 2, 1)])
+def test_fully_connected_network(ref, oracle, cfg):
+    """FullyConnectedNetwork (FF_proj/headers/FullyConnectedNetwork.h): the reference's constructor draws the weights from
+    std::random_device; the harness reads them out of the object and the restatement gets the same ones.  Labels are
+    thresholded signs, so the two agree exactly unless a pre-activation is within rounding of 0."""
+    batch, feat, hid, lab, nbr, nbc = cfg
+    x = np.random.default_rng(batch * feat).uniform(-2, 2, size=(nbr * batch, nbc * feat))
+    a = oracle.load_matrix(x, batch, feat)
+    out, w0, b0, w1, b1 = ref.fully_connected(a, feat, lab, hid, batch)
+    assert np.abs(w0).min() >= 1e-4 and np.abs(w0).max() <= 0.5   # FullyConnectedNetwork.cc:32-33
+    same_sets(out, oracle.udf_dense2(a, feat, batch, w0, b0, w1, b1, with_totals=False), what="FullyConnectedNetwork")
+    vals = np.concatenate([b[4].ravel() for b in out.blocks()])
+    assert set(np.unique(vals)) <= {0.0, 1.0} and 0 < vals.mean() < 1   # both labels occur: the comparison is not vacuous
+
+
+def test_semantic_classifier(ref, oracle):
+    """SemanticClassifier (word2vec/headers/SemanticClassifier.h): all-ones weights and biases, batch = the block's
+    column count, totals of the result block = its own size."""
+    E, B = 12, 5
+    x = np.random.default_rng(5).uniform(-1, 0.6, size=(E, 3 * B))
+    a = oracle.load_matrix(x, E, B)
+    same_sets(ref.semantic_classifier(a, E, 4, 2), oracle.udf_dense2(a, E, B, np.ones((4, E)), np.ones(4), np.ones((2, 4)), np.ones(2)),
+              what="SemanticClassifier")

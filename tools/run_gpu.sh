@@ -1,3 +1,2 @@
-timeout 900 python -m pytest tests/test_gpu_l1stream.py tests/test_gpu_housekeeping.py -x -q > gpurun_out/pytest_l1s.log 2>&1; tail -5 gpurun_out/pytest_l1s.log
-timeout 600 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; tail -8 gpurun_out/smoke.log
-timeout 900 python bench.py --config c5 --steps 5 --warmup 3 > gpurun_out/bench_c5.json 2> gpurun_out/bench_c5.err; tail -c 600 gpurun_out/bench_c5.json; tail -3 gpurun_out/bench_c5.err
+timeout 1200 python -m pytest tests/test_gpu_parity.py -x -q -k "udf or goldens or network" > gpurun_out/pytest_udf.log 2>&1; tail -15 gpurun_out/pytest_udf.log
+timeout 1500 python -m pytest tests/test_gpu_fullsize.py -x -q -k "word2vec or semantic" > gpurun_out/pytest_udf2.log 2>&1; tail -15 gpurun_out/pytest_udf2.log
