@@ -196,4 +196,4 @@ def test_unmodified_reference_semantic_classifier_driver():
         pytest.skip("reference driver was not built (no reference tree at build time)")
     r = subprocess.run([exe, "1000", "1000", "Y"], env=dict(os.environ, NB200_PRECISION="f16"), capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
-    assert "[STATS] labels : 1 X 1000" in r.stdout and "count = 1" in r.stdout   # sizeDense1 x (block columns), one block
+    assert "labels ( 1 X 1000 ) (1 ) : Each block size: 1 X 1000" in r.stdout   # ff::print_stats: sizeDense1 x (block columns), one block
