@@ -1,1 +1,2 @@
-timeout 600 python tools/cascade_probe.py 2>&1 | tail -12
+timeout 1500 python bench.py > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; tail -c 300 gpurun_out/bench_n1.json; tail -2 gpurun_out/bench_n1.err
+timeout 600 python bench.py --config c4 --steps 10 --warmup 3 > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err; tail -c 300 gpurun_out/bench_c4.json
