@@ -878,7 +878,7 @@ k_gemm_f64(const double *__restrict__ u, long long u_sm, long long u_sk, const d
             const long long gm = m0 + tm * 4 + i, gn = n0 + tn * 4 + j;
             if (gm < M && gn < N) {
                 if (gridDim.z == 1) out[gm * out_ld + gn] = acc[i][j];
-                else atomicAdd(out + gm * out_ld + gn, acc[i][j]);
+                else out[(static_cast<long long>(blockIdx.z) * M + gm) * out_ld + gn] = acc[i][j];   // split slab (summed in order by k_f64_sum_splits)
             }
         }
 }
@@ -887,7 +887,7 @@ k_gemm_f64(const double *__restrict__ u, long long u_sm, long long u_sk, const d
 // fp64 GEMM on the DMMA tensor path (mma.sync.m8n8k4.f64): P[M x N] (+)= U[M x K] . V[N x K]^T with
 // both operands K-contiguous.  Used to re-evaluate near-tie rows (K9): M is the handful of flagged
 // rows, N the hidden width, K the full feature count, so the grid is (N tiles, M tiles, K splits)
-// and split partials are combined with fp64 atomics into a zeroed P.
+// and every split stores its partial into its own slab, summed in split order by k_f64_sum_splits.
 // Fragment layout of m8n8k4 (row.col): lane t holds A[t/4][t%4], B[t%4][t/4], C[t/4][2*(t%4) + {0,1}].
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
@@ -988,7 +988,7 @@ k_gemm_f64_mma(const double *__restrict__ u, long long u_ld, const double *__res
                 const long long gn = n0 + wn * 32 + j * 8 + 2 * (lane % 4) + e;
                 if (gm < M && gn < N) {
                     if (gridDim.z == 1) out[gm * out_ld + gn] = acc[i][j][e];
-                    else atomicAdd(out + gm * out_ld + gn, acc[i][j][e]);
+                    else out[(static_cast<long long>(blockIdx.z) * M + gm) * out_ld + gn] = acc[i][j][e];
                 }
             }
 }
@@ -1070,11 +1070,36 @@ k_gemm_f64_mma_skinny(const double *__restrict__ u, long long u_ld, const double
             const long long gn = n0 + warp * (8 * NT) + j * 8 + 2 * (lane % 4) + (e & 1);
             if (gm < M && gn < N) {
                 if (gridDim.z == 1) out[gm * out_ld + gn] = acc[j][e];
-                else atomicAdd(out + gm * out_ld + gn, acc[j][e]);
+                else out[(static_cast<long long>(blockIdx.z) * M + gm) * out_ld + gn] = acc[j][e];
             }
         }
 }
 
+// Split-K of the fp64 GEMMs: every split stores its partial tile into its own slab ws[split][M][N]; this kernel sums the
+// slabs in split order (the result does not depend on which CTA finished first, as fp64 atomics would make it) and applies
+// the bias / ReLU epilogue.
+__global__ void k_f64_sum_splits(const double *__restrict__ ws, int splits, int M, int N, double *__restrict__ out, long long out_ld,
+                                 const double *__restrict__ bias_m, const double *__restrict__ bias_n, int relu) {
+    const long long n = static_cast<long long>(M) * N;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        double x = 0.0;
+        for (int s = 0; s < splits; s++) x += ws[s * n + i];
+        const long long r = i / N, cc = i % N;
+        if (bias_m) x += bias_m[r];
+        if (bias_n) x += bias_n[cc];
+        if (relu) x = x > 0.0 ? x : 0.0;
+        out[r * out_ld + cc] = x;
+    }
+}
+static int sum_splits(Context *c, double *ws, int splits, int M, int N, double *out, int64_t out_ld, const F64Epilogue &e) {
+    const int64_t n = static_cast<int64_t>(M) * N;
+    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+    k_f64_sum_splits<<<blocks, 256, 0, c->stream>>>(ws, splits, M, N, out, out_ld, e.bias_m, e.bias_n, e.relu);
+    NB_LAUNCH_CHECK(c);
+    nb_free(ws);   // stream-ordered reuse: the pool hands the block out again only to work queued after this kernel
+    return NB200_OK;
+}
 __global__ void k_bias_relu_f64(double *__restrict__ p, int M, int N, long long ld, const double *__restrict__ bias_m,
                                 const double *__restrict__ bias_n, int relu) {
     const long long n = static_cast<long long>(M) * N;
@@ -1108,6 +1133,7 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
         const bool aligned = (u_sm % 2 == 0) && (v_sn % 2 == 0) && ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
         if (small && aligned && skinny_env && K >= 8192) {
             static const int cfg = getenv("NB200_F64_CFG") ? atoi(getenv("NB200_F64_CFG")) : 1;
+            bool epilogue_done = false;
             auto run = [&](auto kern, int BNs, int BKs, int ST, int ctas_per_sm) -> int {
                 const size_t smem = static_cast<size_t>(ST) * (16 + BNs) * (BKs + 4) * sizeof(double);
                 NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -1125,9 +1151,12 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
                 if (sp < 1) sp = 1;
                 const int64_t kp = round_up(ceil_div(K, sp), BKs);
                 sp = static_cast<int>(ceil_div(K, kp));
-                if (sp > 1) NB_CUDA(cudaMemset2DAsync(out, out_ld * sizeof(double), 0, static_cast<size_t>(N) * sizeof(double), M, c->stream));
+                double *ws = nullptr;
+                if (sp > 1) NB_CUDA(nb_malloc(&ws, static_cast<size_t>(sp) * M * N * sizeof(double)));
                 dim3 g2(static_cast<unsigned>(ceil_div(N, BNs)), static_cast<unsigned>(ceil_div(M, 16)), sp);
-                kern<<<g2, 128, smem, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kp, out, out_ld);
+                kern<<<g2, 128, smem, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kp, ws ? ws : out, ws ? N : out_ld);
+                NB_LAUNCH_CHECK(c);
+                if (ws) { epilogue_done = true; return sum_splits(c, ws, sp, M, N, out, out_ld, e); }
                 return NB200_OK;
             };
             // measured on the Amazon shape (15 x 1000 x 597,540, tools/f64_skinny_bench.py, profiles/r02_f64_skinny.txt):
@@ -1136,8 +1165,7 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
             // 19 TFLOP/s of DMMA.8x8x4 (m16n8k4 lowers to two of them); the HBM roofline is 0.73 ms.
             if (cfg == 1) NB_TRY(run(k_gemm_f64_mma_skinny<3, 16, 128>, 128, 16, 3, 3));
             else NB_TRY(run(k_gemm_f64_mma_skinny<3, 32, 64>, 64, 32, 3, 3));
-            NB_LAUNCH_CHECK(c);
-            if (e.bias_m || e.bias_n || e.relu) {
+            if (!epilogue_done && (e.bias_m || e.bias_n || e.relu)) {
                 const int64_t n = static_cast<int64_t>(M) * N;
                 const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
                 k_bias_relu_f64<<<blocks, 256, 0, c->stream>>>(out, M, N, out_ld, e.bias_m, e.bias_n, e.relu);
@@ -1147,11 +1175,13 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
         }
         const int64_t kper = round_up(ceil_div(K, splits), 16);
         splits = static_cast<int>(ceil_div(K, kper));
-        if (splits > 1) NB_CUDA(cudaMemset2DAsync(out, out_ld * sizeof(double), 0, static_cast<size_t>(N) * sizeof(double), M, c->stream));
+        double *ws = nullptr;
+        if (splits > 1) NB_CUDA(nb_malloc(&ws, static_cast<size_t>(splits) * M * N * sizeof(double)));
         dim3 grid(static_cast<unsigned>(ceil_div(N, BNm)), static_cast<unsigned>(ceil_div(M, BMm)), splits);
-        if (small) k_gemm_f64_mma<2, 1, 4><<<grid, 128, 0, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kper, out, out_ld);
-        else k_gemm_f64_mma<4, 2, 2><<<grid, 128, 0, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kper, out, out_ld);
+        if (small) k_gemm_f64_mma<2, 1, 4><<<grid, 128, 0, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kper, ws ? ws : out, ws ? N : out_ld);
+        else k_gemm_f64_mma<4, 2, 2><<<grid, 128, 0, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kper, ws ? ws : out, ws ? N : out_ld);
         NB_LAUNCH_CHECK(c);
+        if (ws) return sum_splits(c, ws, splits, M, N, out, out_ld, e);
         if (e.bias_m || e.bias_n || e.relu) {
             const int64_t n = static_cast<int64_t>(M) * N;
             const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
@@ -1173,11 +1203,13 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
     }
     int64_t kper = round_up(ceil_div(K, splits), 16);
     splits = static_cast<int>(ceil_div(K, kper));
-    if (splits > 1) NB_CUDA(cudaMemset2DAsync(out, out_ld * sizeof(double), 0, static_cast<size_t>(N) * sizeof(double), M, c->stream));
+    double *ws = nullptr;
+    if (splits > 1) NB_CUDA(nb_malloc(&ws, static_cast<size_t>(splits) * M * N * sizeof(double)));
     dim3 grid(static_cast<unsigned>(ceil_div(N, BN)), static_cast<unsigned>(ceil_div(M, BM)), splits);
-    if (skinny) k_gemm_f64<16, 256><<<grid, 256, 0, c->stream>>>(u, u_sm, u_sk, v, v_sn, v_sk, M, N, K, kper, out, out_ld);
-    else k_gemm_f64<64, 64><<<grid, 256, 0, c->stream>>>(u, u_sm, u_sk, v, v_sn, v_sk, M, N, K, kper, out, out_ld);
+    if (skinny) k_gemm_f64<16, 256><<<grid, 256, 0, c->stream>>>(u, u_sm, u_sk, v, v_sn, v_sk, M, N, K, kper, ws ? ws : out, ws ? N : out_ld);
+    else k_gemm_f64<64, 64><<<grid, 256, 0, c->stream>>>(u, u_sm, u_sk, v, v_sn, v_sk, M, N, K, kper, ws ? ws : out, ws ? N : out_ld);
     NB_LAUNCH_CHECK(c);
+    if (ws) return sum_splits(c, ws, splits, M, N, out, out_ld, e);
     if (e.bias_m || e.bias_n || e.relu) {
         const int64_t n = static_cast<int64_t>(M) * N;
         const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);

@@ -699,3 +699,17 @@ def test_unmodified_reference_network_drivers():
     assert len(pairs) >= 2      # the driver prints the first two values of each output row: labels, all 0 or 1
     r = _run([fc, "50", "40", "60", "40", "16", "2", "Y"], {"NB200_FC_SEED": "7"}, timeout=240)
     assert r.returncode != 0 and "batch size doesn't match" in (r.stdout + r.stderr)   # FullyConnectedNetwork.h:69-72
+
+
+@pytest.mark.parametrize("rows", [9, 100])
+def test_fp64_split_k_is_reproducible(nb, rows):
+    """The fp64 path splits a long K over many CTAs; the partial tiles are summed in split order (k_f64_sum_splits), so a
+    repeated call returns the same bits -- fp64 atomics would make the last bits depend on which CTA finished first."""
+    K, N = 40000, 300
+    a = nb.DeviceSet.create("rep", "a", rows, K, 1000, 1000); a.fill_synth(31)
+    b = nb.DeviceSet.create("rep", "b", N, K, 1000, 1000); b.fill_synth(32)
+    first = nb.gemm_blocks(nb.OP_NT, a, b, nb.EPI_NONE, None, nb.PREC_FP64, "rep", "c").download_dense()
+    want = a.download_dense() @ b.download_dense().T
+    assert np.abs(first - want).max() <= 1e-12 * np.abs(want).max()
+    for _ in range(3):
+        assert np.array_equal(nb.gemm_blocks(nb.OP_NT, a, b, nb.EPI_NONE, None, nb.PREC_FP64, "rep", "c").download_dense(), first)
