@@ -1,1 +1,1 @@
-NB200_WAIT_LOG2=38 timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02_launches.csv python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1; tail -1 gpurun_out/ncu_launch.log | cut -c1-200
+for d in 0 1 2; do NB200_F64_TMA_DEBUG=$d timeout 300 python tools/f64_skinny_bench.py 2>&1 | tail -1; done
