@@ -1,1 +1,2 @@
-for d in 0 1 2; do NB200_F64_TMA_DEBUG=$d timeout 300 python tools/f64_skinny_bench.py 2>&1 | tail -1; done
+timeout 2400 python -m pytest tests/ -x -q -m gpu > gpurun_out/pytest_gpu_full.log 2>&1; tail -4 gpurun_out/pytest_gpu_full.log
+timeout 900 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; tail -3 gpurun_out/smoke.log
