@@ -343,6 +343,10 @@ private:
             check(nb200_sum_blocks(x, y, nullptr, NB200_ACT_NONE, db.c_str(), out.c_str(), &o));
             return o;
         }
+        if ((as<FullyConnectedNetwork>(c) || as<SemanticClassifier>(c)) && num_devices() > 1 && scans_sharded(c->getIthInput(0)))
+            // these UDFs reinterpret whole blocks; a set split over devices at row granularity has no whole blocks
+            throw std::runtime_error(c->getComputationType() + ": a network UDF over a set sharded by NB200_DEVICES is not supported; "
+                                     "take the set out of NB200_SHARD_SETS");
         if (auto *net = as<FullyConnectedNetwork>(c)) {
             nb200_set *x = eval(c->getIthInput(0), db, "");
             int br = 0;

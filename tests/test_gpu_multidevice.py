@@ -94,3 +94,27 @@ def test_cpp_driver_shards_inputs_over_two_devices(oracle, tmp_path):
         assert np.array_equal(got[:, 0].astype(np.int32), ref[1]), ndev      # fused stage's labels, concatenated over devices
         assert np.array_equal(got[:, 1].astype(np.int32), ref[1]), ndev      # argmax of the `output` set read back
         assert np.abs(got[:, 2] - ref[0][:, 0]).max() <= 1e-2
+
+
+def test_network_udf_over_a_sharded_set_is_refused():
+    """FullyConnectedNetwork reinterprets whole blocks; with NB200_DEVICES=2 the rows of `inputs` are split over the devices
+    at row granularity, so the lowering refuses instead of evaluating half-empty blocks.  With the set taken out of
+    NB200_SHARD_SETS the same driver runs."""
+    import os
+    import subprocess
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from netsdb_b200 import build
+
+    exe = os.path.join(build.HOST_BIN, "FCProjTest_netsdb")
+    if not os.path.exists(exe):
+        pytest.skip("reference driver was not built (no reference tree at build time)")
+    args = [exe, "50", "40", "50", "40", "16", "2", "Y"]
+    r = subprocess.run(args, env=dict(os.environ, NB200_DEVICES="2", NB200_FC_SEED="7"), capture_output=True, text=True, timeout=240)
+    assert r.returncode != 0 and "sharded by NB200_DEVICES" in (r.stdout + r.stderr)
+    r = subprocess.run(args, env=dict(os.environ, NB200_DEVICES="2", NB200_FC_SEED="7", NB200_SHARD_SETS="none"), capture_output=True,
+                       text=True, timeout=240)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
