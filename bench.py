@@ -52,8 +52,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the baseline sample")
-    ap.add_argument("--config", default="c2", choices=["c2", "c4", "c5"],
-                    help="c2 (default): the Amazon-14K FF shape (C3 with --gpus N); c4: conv2d_memory_fusion; c5: word2vec (bench_configs.py)")
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c4", "c5"],
+                    help="c2 (default): the Amazon-14K FF shape (C3 with --gpus N); c1: the reference's own CPU-runnable FF case "
+                         "(1,000 x 1,024, hidden 1,024, 10 labels, 100 x 100 blocks); c4: conv2d_memory_fusion; c5: word2vec (bench_configs.py)")
     return ap.parse_args()
 
 
@@ -627,6 +628,8 @@ def run_e2e_side_format(a, capi, torch, dist, barrier, x, w1, wo, b1, bo, prec, 
 
 if __name__ == "__main__":
     args = parse()
+    if args.config == "c1":   # BASELINE.json configs[0]: the same FF path at the reference's own small size
+        args.batch, args.features, args.hidden, args.labels, args.block, args.config = 1000, 1024, 1024, 10, 100, "c2"
     if args.config != "c2":
         import bench_configs
 
