@@ -1,1 +1,6 @@
-timeout 600 python bench.py --batch 1000 --features 1024 --hidden 1024 --labels 10 --block 100 --steps 20 --warmup 5 > gpurun_out/bench_c1.json 2> gpurun_out/bench_c1.err; tail -c 1200 gpurun_out/bench_c1.json; tail -2 gpurun_out/bench_c1.err
+timeout 900 python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu-baseline 2>/dev/null | python3 -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); r=d['roofline']; print(d['value'], d['ms_per_step'], r['frac'], r['frac_sustained'], r['peak_sustained'], r['traffic'], r['hbm']['frac'])"
+timeout 300 python bench.py --config c1 --steps 20 --warmup 5 --no-e2e --no-cpu-baseline 2>/dev/null | python3 -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('c1', d['value'], d['ms_per_step'], d['config']['workload'])"
