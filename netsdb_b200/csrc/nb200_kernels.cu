@@ -1075,6 +1075,117 @@ k_gemm_f64_mma_skinny(const double *__restrict__ u, long long u_ld, const double
         }
 }
 
+// The same product with the operands brought in through REGISTERS: 256-bit loads (ld.global.nc.L1::no_allocate.v4.f64,
+// a warp instruction = 256 contiguous bytes of four rows) land in registers one stage ahead and are stored to a
+// double-buffered shared-memory tile after the multiplies of the current stage -- the access pattern the layer-1 stream kernel
+// reads its fp64 inputs with (6.1-6.4 TB/s in tools/hbm_pattern_bench.cu), where the cp.async version stops at 4.7 TB/s.
+// 16 x 128 tile, 32 doubles of K per stage, 8 warps (each 16 columns).  Needs rows whose pitch is a multiple of 4 doubles,
+// 32-byte aligned bases and K % 4 == 0.
+// Measured on the Amazon shape (1,000 x 597,540): with all 16 rows of the tile the kernel sits on the DMMA pipe -- 1.007 ms =
+// 19.4 TFLOP/s of DMMA.8x8x4, the only fp64 tensor primitive of sm_100 (m16n8k4 lowers to two of them) -- like the cp.async
+// version (1.025 ms); HALF (at most 8 rows: one DMMA.8x8x4 per fragment and step) takes 0.838 ms = 5.7 TB/s of W1, which the
+// cp.async version never reached whatever the DMMA work (4.7 TB/s).
+template <bool HALF>
+__global__ void __launch_bounds__(256, 2)
+k_gemm_f64_mma_skinny_ldg(const double *__restrict__ u, long long u_ld, const double *__restrict__ v, long long v_ld, int M, int N,
+                          long long K, long long k_per_split, double *__restrict__ out, long long out_ld) {
+    constexpr int BM = 16, BN = 128, BK = 32, LDS = BK + 4;
+    extern __shared__ __align__(16) double dyn_smem[];
+    double *su = dyn_smem;                       // [2][BM * LDS]
+    double *sv = dyn_smem + 2 * BM * LDS;        // [2][BN * LDS]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long n0 = static_cast<long long>(blockIdx.x) * BN;
+    const long long kbeg = static_cast<long long>(blockIdx.z) * k_per_split;
+    const long long kend = (kbeg + k_per_split < K) ? kbeg + k_per_split : K;
+    const int nk = kend > kbeg ? static_cast<int>((kend - kbeg + BK - 1) / BK) : 0;
+    // loads: lane = (row in group of 4, 32-byte piece of the 256-byte row segment)
+    const int lrow = lane >> 3, piece = lane & 7;
+    const double *vsrc[4];
+    uint32_t vdst[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int r = warp * 16 + i * 4 + lrow;
+        const long long gn = n0 + r;
+        vsrc[i] = gn < N ? v + gn * v_ld + kbeg + piece * 4 : nullptr;
+        vdst[i] = static_cast<uint32_t>(__cvta_generic_to_shared(sv + r * LDS + piece * 4));
+    }
+    const int ur = warp * 4 + lrow;              // warps 0..3 also bring in the U tile
+    const double *usrc = (warp < 4 && ur < M) ? u + static_cast<long long>(ur) * u_ld + kbeg + piece * 4 : nullptr;
+    const uint32_t udst = static_cast<uint32_t>(__cvta_generic_to_shared(su + ur * LDS + piece * 4));
+    double rv[4][4], ru[4];
+    auto load = [&](int kb) {
+        const long long koff = static_cast<long long>(kb) * BK;
+        const bool kin = kbeg + koff + piece * 4 < kend;   // K % 4 == 0: a piece is inside or outside as a whole
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (vsrc[i] && kin)
+                asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.f64 {%0, %1, %2, %3}, [%4];"
+                             : "=d"(rv[i][0]), "=d"(rv[i][1]), "=d"(rv[i][2]), "=d"(rv[i][3]) : "l"(vsrc[i] + koff));
+            else rv[i][0] = rv[i][1] = rv[i][2] = rv[i][3] = 0.0;
+        }
+        if (usrc && kin)
+            asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(ru[0]), "=d"(ru[1]), "=d"(ru[2]), "=d"(ru[3]) : "l"(usrc + koff));
+        else ru[0] = ru[1] = ru[2] = ru[3] = 0.0;
+    };
+    auto store = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t d = vdst[i] + buf * (BN * LDS * 8);
+            asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(d), "d"(rv[i][0]), "d"(rv[i][1]) : "memory");
+            asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(d + 16), "d"(rv[i][2]), "d"(rv[i][3]) : "memory");
+        }
+        if (warp < 4) {
+            const uint32_t d = udst + buf * (BM * LDS * 8);
+            asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(d), "d"(ru[0]), "d"(ru[1]) : "memory");
+            asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(d + 16), "d"(ru[2]), "d"(ru[3]) : "memory");
+        }
+    };
+    double acc[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; j++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) acc[j][e] = 0.0;
+    if (nk > 0) {
+        load(0);
+        store(0);
+        if (nk > 1) load(1);
+    }
+    __syncthreads();
+    for (int kb = 0; kb < nk; kb++) {
+        const int buf = kb & 1;
+        const double *pu = su + (buf * BM + lane / 4) * LDS + lane % 4;
+        const double *pv = sv + (buf * BN + warp * 16 + lane / 4) * LDS + lane % 4;
+#pragma unroll
+        for (int ks = 0; ks < BK; ks += 4) {
+            const double a0 = pu[ks], a1 = HALF ? 0.0 : pu[8 * LDS + ks];
+            const double b0 = pv[ks], b1 = pv[8 * LDS + ks];
+            if (HALF) {
+                dmma_m8n8k4(acc[0][0], acc[0][1], a0, b0);
+                dmma_m8n8k4(acc[1][0], acc[1][1], a0, b1);
+            } else {
+                dmma_m16n8k4(acc[0], a0, a1, b0);
+                dmma_m16n8k4(acc[1], a0, a1, b1);
+            }
+        }
+        if (kb + 1 < nk) {
+            store(buf ^ 1);                 // stage kb + 1 (in registers since the previous iteration) -> the other buffer,
+            if (kb + 2 < nk) load(kb + 2);  // whose readers finished before the barrier that ended iteration kb - 1
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 2; j++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const long long gm = (e >> 1) * 8 + lane / 4;
+            const long long gn = n0 + warp * 16 + j * 8 + 2 * (lane % 4) + (e & 1);
+            if (gm < M && gn < N) {
+                if (gridDim.z == 1) out[gm * out_ld + gn] = acc[j][e];
+                else out[(static_cast<long long>(blockIdx.z) * M + gm) * out_ld + gn] = acc[j][e];
+            }
+        }
+}
+
 // Split-K of the fp64 GEMMs: every split stores its partial tile into its own slab ws[split][M][N]; this kernel sums the
 // slabs in split order (the result does not depend on which CTA finished first, as fp64 atomics would make it) and applies
 // the bias / ReLU epilogue.
@@ -1134,6 +1245,35 @@ int launch_gemm_f64(Context *c, const double *u, int64_t u_sm, int64_t u_sk, con
         if (small && aligned && skinny_env && K >= 8192) {
             static const int cfg = getenv("NB200_F64_CFG") ? atoi(getenv("NB200_F64_CFG")) : 1;
             bool epilogue_done = false;
+            static const bool ldg_env = !(getenv("NB200_F64_LDG") && atoi(getenv("NB200_F64_LDG")) == 0);   // default on
+            if (ldg_env && (u_sm % 4 == 0) && (v_sn % 4 == 0) && (K % 4 == 0) &&
+                ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(v)) & 31) == 0) {
+                const size_t smem = static_cast<size_t>(2) * (16 + 128) * 36 * sizeof(double);
+                NB_CUDA(cudaFuncSetAttribute(k_gemm_f64_mma_skinny_ldg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+                NB_CUDA(cudaFuncSetAttribute(k_gemm_f64_mma_skinny_ldg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+                NB_CUDA(cudaFuncSetAttribute(k_gemm_f64_mma_skinny_ldg<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 74));
+                NB_CUDA(cudaFuncSetAttribute(k_gemm_f64_mma_skinny_ldg<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 74));
+                const int64_t tl = ceil_div(N, 128);
+                int sp = static_cast<int>(ceil_div(static_cast<int64_t>(2) * sms, tl));
+                if (sp > K / 2048) sp = static_cast<int>(K / 2048);
+                if (sp < 1) sp = 1;
+                const int64_t kp = round_up(ceil_div(K, sp), 32);
+                sp = static_cast<int>(ceil_div(K, kp));
+                double *ws = nullptr;
+                if (sp > 1) NB_CUDA(nb_malloc(&ws, static_cast<size_t>(sp) * M * N * sizeof(double)));
+                dim3 g2(static_cast<unsigned>(tl), 1, sp);
+                if (M <= 8) k_gemm_f64_mma_skinny_ldg<true><<<g2, 256, smem, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kp, ws ? ws : out, ws ? N : out_ld);
+                else k_gemm_f64_mma_skinny_ldg<false><<<g2, 256, smem, c->stream>>>(u, u_sm, v, v_sn, M, N, K, kp, ws ? ws : out, ws ? N : out_ld);
+                NB_LAUNCH_CHECK(c);
+                if (ws) return sum_splits(c, ws, sp, M, N, out, out_ld, e);
+                if (e.bias_m || e.bias_n || e.relu) {
+                    const int64_t n = static_cast<int64_t>(M) * N;
+                    const int blocks = static_cast<int>(ceil_div(n, 256) < 148 * 8 ? ceil_div(n, 256) : 148 * 8);
+                    k_bias_relu_f64<<<blocks, 256, 0, c->stream>>>(out, M, N, out_ld, e.bias_m, e.bias_n, e.relu);
+                    NB_LAUNCH_CHECK(c);
+                }
+                return NB200_OK;
+            }
             auto run = [&](auto kern, int BNs, int BKs, int ST, int ctas_per_sm) -> int {
                 const size_t smem = static_cast<size_t>(ST) * (16 + BNs) * (BKs + 4) * sizeof(double);
                 NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));

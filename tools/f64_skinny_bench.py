@@ -8,7 +8,7 @@ import torch
 sys.path.insert(0, ".")
 from netsdb_b200 import capi
 
-rows, K, N = 15, 597540, 1000
+rows, K, N = (int(sys.argv[1]) if len(sys.argv) > 1 else 15), 597540, 1000
 capi.init(0)
 torch.cuda.set_device(0)
 stream = torch.cuda.Stream()
