@@ -1,9 +1,5 @@
-cd netsdb_b200/host/bin
-for nd in 1 8; do NB200_DEVICES=$nd NB200_PRECISION=f16 timeout 600 ./FFTest 1000 1000 4000 8200 1000 64 /tmp/dump$nd.txt > /tmp/fftest$nd.log 2>&1; echo "FFTest NB200_DEVICES=$nd rc=$?"; tail -2 /tmp/fftest$nd.log; done
-python3 - <<'PY'
-import numpy as np
-a=np.loadtxt('/tmp/dump1.txt'); b=np.loadtxt('/tmp/dump8.txt')
-print('rows', a.shape, 'labels equal between 1 and 8 devices:', bool(np.array_equal(a[:,0],b[:,0]) and np.array_equal(a[:,1],b[:,1])), 'max prob diff', float(np.abs(a[:,2]-b[:,2]).max()))
-PY
-echo "== FFTestWithoutDeduplication_netsdb (unmodified reference driver) Amazon-14K NB200_DEVICES=8"
-NB200_DEVICES=8 NB200_DROPOUT_AS_ZERO=1 NB200_PRECISION=f16 timeout 1200 ./FFTestWithoutDeduplication_netsdb 1000 1000 10000 597540 1000 14588 ff Y 2>&1 | tail -4
+n=${NGPU:-8}
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus $n --steps 5 --warmup 3 > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err; tail -c 300 gpurun_out/bench_n$n.err; python3 -c "
+import json
+d=json.loads(open('gpurun_out/bench_n$n.json').read().strip().splitlines()[-1])
+print({k:d[k] for k in ('value','ms_per_step','scaling','n_gpus')}); print('e2e', d['e2e']['value'] if d['e2e'] else None, (d['e2e'].get('side_format') or {}).get('value') if d['e2e'] else None); print(d['weak_replicas']); print(d['strong_check']); print(d['ksharded']); print(d['breakdown_ms'])"
